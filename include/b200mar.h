@@ -1,0 +1,151 @@
+/* b200mar.h — C ABI of the B200-native NGswin hot path (libb200mar.so).
+ *
+ * Drop-in boundary for the N-gram window-attention transformer blocks of
+ * mpat247/TransMAR-GAN's generator (models/generator/ngswin.py::NGswin).  The reference is
+ * pure Python/PyTorch and has no FFI of its own; each entry point below replaces the
+ * reference *module method* cited beside it, and is what a ctypes / torch.library binding in
+ * the reference tree would call (see INTEGRATION.md for the stubs).
+ *
+ * Conventions (all entry points):
+ *   - every pointer is a DEVICE pointer to a contiguous, 16-byte aligned buffer owned by the
+ *     caller (no ownership transfer, nothing is allocated or freed here);
+ *   - `stream` is a cudaStream_t passed as void*; kernels are enqueued on it and the call
+ *     returns without synchronising (safe under CUDA-graph capture);
+ *   - return value: 0 on success, otherwise a cudaError_t (or -1 for an argument the path
+ *     does not support, e.g. a head count other than 4 or 6);
+ *   - token tensors are fp32 `[B, ph*pw, 64]`, row-major over (row, col), channels last
+ *     (models/generator/ngswin.py:172); parameters are in the reference state_dict layout
+ *     (nn.Linear weight `[out, in]`, conv weight `[out, in/groups, kh, kw]`);
+ *   - embed dim 64, window 8x8, MLP hidden 128, n-gram 2 are compile-time constants of the
+ *     reference's only configuration (models/generator/ngswin.py:43-49);
+ *   - `*_bwd` entry points ACCUMULATE (+=) into parameter-gradient buffers, so one zeroed
+ *     flat gradient bucket can be shared by all blocks; activation gradients are overwritten
+ *     unless stated otherwise.
+ *   - no CPU implementation exists behind this ABI: on a machine without an sm_100 GPU every
+ *     compute entry point returns cudaErrorNoKernelImageForDevice / cudaErrorNoDevice.
+ */
+#ifndef B200MAR_H
+#define B200MAR_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ABI version, bumped whenever a signature changes. */
+int b200mar_abi_version(void);
+/* Name of the last failing CUDA call of this thread (static string; never NULL). */
+const char* b200mar_last_error(void);
+/* 1 iff device `dev` is compute capability 10.x (B200); no kernels are launched. */
+int b200mar_device_ok(int dev);
+
+/* ---- a3: NGramContext.unigram_embed  (components/window_utils.py:36-38,78) --------------
+ * u[b,h,w,g] = bias[g] + sum_{k<2,i<8,j<8} weight[g,k,i,j] * z[b, 8h+i, 8w+j, 2g+k]
+ * z [B,ph,pw,64] -> u [B,wh,ww,32] (channels last).                                        */
+int b200mar_unigram_fwd(const float* z, const float* weight /*[32,2,8,8]*/,
+                        const float* bias /*[32]*/, float* u,
+                        int B, int ph, int pw, void* stream);
+/* dz += scatter(du * weight)  (dz must already hold the other contributions);
+ * dweight += , dbias += .                                                                  */
+int b200mar_unigram_bwd(const float* z, const float* weight, const float* du,
+                        float* dz, float* dweight, float* dbias,
+                        int B, int ph, int pw, void* stream);
+
+/* ---- a3: NGramContext.forward after the unigram conv (components/window_utils.py:43-90) --
+ * seq_refl_win_pad (fwd/bwd), 2x2 sliding WindowAttention(dim 32, nh heads, window 2),
+ * AvgPool2d(2), concat, 1x1 merge conv.  u [B,wh,ww,32] -> ctx [B,wh,ww,64].
+ * nh in {4,6}; head_dim = 32/nh (8 or 5).                                                  */
+int b200mar_ngram_ctx_fwd(const float* u,
+                          const float* qkv_w /*[3*na,32]*/, const float* qkv_b /*[3*na]*/,
+                          const float* proj_w /*[32,na]*/, const float* proj_b /*[32]*/,
+                          const float* logit_scale /*[nh]*/, const float* bias_table /*[9,nh]*/,
+                          const float* merge_w /*[64,64]*/, const float* merge_b /*[64]*/,
+                          float* ctx, int B, int wh, int ww, int nh, void* stream);
+int b200mar_ngram_ctx_bwd(const float* u, const float* dctx,
+                          const float* qkv_w, const float* qkv_b,
+                          const float* proj_w, const float* proj_b,
+                          const float* logit_scale, const float* bias_table,
+                          const float* merge_w, const float* merge_b,
+                          float* du,
+                          float* d_qkv_w, float* d_qkv_b, float* d_proj_w, float* d_proj_b,
+                          float* d_logit_scale, float* d_bias_table,
+                          float* d_merge_w, float* d_merge_b,
+                          int B, int wh, int ww, int nh, void* stream);
+
+/* ---- a4+a5+a6+a7+a8(first half): NGramWindowPartition + WindowAttention + unpartition +
+ * reverse roll + `x + norm1(.)`  (components/window_utils.py:127-147,
+ * components/attention.py:70-101, components/transformer_blocks.py:63-112,117) ------------
+ * For every (shifted) window: gather z+ctx with the cyclic shift folded into the address
+ * math, QKV, scaled-cosine logits * exp(min(logit_scale, ln 100)) + relative-position bias
+ * + analytic 9-region shift mask (-100), softmax, PV, proj, LayerNorm(norm1), residual,
+ * scatter back to the source token positions:  a = z + LN1(attn(partition(z + ctx))).
+ * shift in {0,4}; nh in {4,6} (head_dim 16 / 10).                                          */
+int b200mar_attn_fwd(const float* z, const float* ctx,
+                     const float* qkv_w /*[3A,64]*/, const float* qkv_b /*[3A]*/,
+                     const float* proj_w /*[64,A]*/, const float* proj_b /*[64]*/,
+                     const float* logit_scale /*[nh]*/, const float* bias_table /*[225,nh]*/,
+                     const float* ln_w /*[64]*/, const float* ln_b /*[64]*/,
+                     float* a, int B, int ph, int pw, int nh, int shift, void* stream);
+/* dz = da + scatter(dX) (overwrites dz); dctx += per-source-window sums of dX (dctx must be
+ * zeroed by the caller); parameter gradients are accumulated.                              */
+int b200mar_attn_bwd(const float* z, const float* ctx, const float* da,
+                     const float* qkv_w, const float* qkv_b,
+                     const float* proj_w, const float* proj_b,
+                     const float* logit_scale, const float* bias_table,
+                     const float* ln_w, const float* ln_b,
+                     float* dz, float* dctx,
+                     float* d_qkv_w, float* d_qkv_b, float* d_proj_w, float* d_proj_b,
+                     float* d_logit_scale, float* d_bias_table, float* d_ln_w, float* d_ln_b,
+                     int B, int ph, int pw, int nh, int shift, void* stream);
+
+/* ---- a8(second half)+a9: `x + norm2(ffn(x))` and the within-stage residual
+ * (components/transformer_blocks.py:119, components/encoder_decoder.py:138-141) -----------
+ * out = a + LN2(fc2(GELU_erf(fc1(a))));  if zsum != NULL: zsum = out + z (the next block's
+ * input).  out may be NULL when only zsum is wanted.  n_tok = B*ph*pw.                     */
+int b200mar_mlp_fwd(const float* a, const float* z,
+                    const float* fc1_w /*[128,64]*/, const float* fc1_b /*[128]*/,
+                    const float* fc2_w /*[64,128]*/, const float* fc2_b /*[64]*/,
+                    const float* ln_w, const float* ln_b,
+                    float* out, float* zsum, long long n_tok, void* stream);
+/* da = dout + d(MLP branch) (overwrites da); parameter gradients accumulated.             */
+int b200mar_mlp_bwd(const float* a, const float* dout,
+                    const float* fc1_w, const float* fc1_b,
+                    const float* fc2_w, const float* fc2_b,
+                    const float* ln_w, const float* ln_b,
+                    float* da,
+                    float* d_fc1_w, float* d_fc1_b, float* d_fc2_w, float* d_fc2_b,
+                    float* d_ln_w, float* d_ln_b, long long n_tok, void* stream);
+
+/* ---- a10: PatchMerging.forward (components/encoder_decoder.py:51-74) -------------------
+ * 2x2 gather in channel order (even,even),(even,odd),(odd,even),(odd,odd) -> LN(256) ->
+ * Linear(256->64, no bias).  x [B,ph,pw,64] -> y [B,ph/2,pw/2,64].                          */
+int b200mar_patch_merge_fwd(const float* x, const float* ln_w /*[256]*/, const float* ln_b,
+                            const float* red_w /*[64,256]*/, float* y,
+                            int B, int ph, int pw, void* stream);
+int b200mar_patch_merge_bwd(const float* x, const float* dy,
+                            const float* ln_w, const float* ln_b, const float* red_w,
+                            float* dx, float* d_ln_w, float* d_ln_b, float* d_red_w,
+                            int B, int ph, int pw, void* stream);
+
+/* ---- a12: pixel_shuffle_permute of the three encoder skips + channel concat
+ * (components/encoder_decoder.py:159-164,191-192) ----------------------------------------
+ * out[b, (h*s+a)*W + (w*s+c'), off_i + c] = x_i[b, h*pw_i + w, (c*s + a)*s + c'],  s = 2^i,
+ * channel blocks 64 | 16 | 4 -> out [B, H*W, 84].  inverse=1 runs the same map backwards
+ * (the gradient): reads `out`-layout data from `cat` and writes x0/x1/x2-layout buffers.   */
+int b200mar_pixel_shuffle_cat(float* x0 /*[B,H*W,64]*/, float* x1 /*[B,H*W/4,64]*/,
+                              float* x2 /*[B,H*W/16,64]*/, float* cat /*[B,H*W,84]*/,
+                              int B, int H, int W, int inverse, void* stream);
+
+/* ---- integer index maps (bit-exact contract of a4/a6/a7) -------------------------------
+ * tok_idx/ctx_idx [B*wh*ww, 64] int64: flat source token / source window of every window
+ * slot, exactly what the attention kernels use (same device function).                     */
+int b200mar_partition_index(long long* tok_idx, long long* ctx_idx,
+                            int B, int ph, int pw, int shift, void* stream);
+/* mask [wh*ww, 64, 64] fp32 (0 / -100) from the kernels' analytic region rule, and
+ * rel_index [64,64] int64 from the kernels' bias addressing.                               */
+int b200mar_shift_mask(float* mask, int ph, int pw, int shift, void* stream);
+int b200mar_rel_index(long long* rel_index, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200MAR_H */

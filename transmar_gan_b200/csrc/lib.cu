@@ -1,0 +1,28 @@
+// lib.cu — library-level plumbing of libb200mar.so: ABI version, error string, device probe.
+#include "common.cuh"
+#include "../../include/b200mar.h"
+
+namespace b200mar {
+const char*& last_error_ref() {
+  static thread_local const char* msg = "no error";
+  return msg;
+}
+int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+      n = 148;
+  }
+  return n;
+}
+}  // namespace b200mar
+
+extern "C" int b200mar_abi_version(void) { return 1; }
+extern "C" const char* b200mar_last_error(void) { return b200mar::last_error_ref(); }
+extern "C" int b200mar_device_ok(int dev) {
+  int major = 0;
+  if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) return 0;
+  return major == 10 ? 1 : 0;
+}

@@ -1,0 +1,408 @@
+// ngram_bwd.cu — backward of the N-gram context path (fp32).
+//   unigram_bwd  : gradient of the grouped 8x8/stride-8 conv (window_utils.py:36-38).
+//   ngram_ctx_bwd: gradient of reflect-pad + 2x2 sliding cosine attention + avg-pool + merge
+//                  (window_utils.py:43-90), one warp per window with full recompute.
+#include "common.cuh"
+#include "ngram_common.cuh"
+
+namespace b200mar {
+
+// ------------------------------------------------------------------------------- unigram
+// Warp w of every CTA owns window row i = w for all windows the CTA visits, so its 16 weight
+// gradients (8 columns x 2 channels per lane) live in registers for the whole kernel.
+__global__ void __launch_bounds__(kThreads) unigram_bwd_kernel(
+    const float* __restrict__ z, const float* __restrict__ w, const float* __restrict__ du,
+    float* __restrict__ dz, float* __restrict__ dw, float* __restrict__ db, int B, int ph, int pw) {
+  const int lane = threadIdx.x & 31, i = threadIdx.x >> 5;   // i = window row owned by this warp
+  const int wh = ph / kWin, ww = pw / kWin;
+  const int nwin = B * wh * ww;
+  float2 wr[kWin], acc[kWin];
+#pragma unroll
+  for (int j = 0; j < kWin; ++j) {
+    wr[j].x = w[lane * 128 + i * 8 + j];
+    wr[j].y = w[lane * 128 + 64 + i * 8 + j];
+    acc[j] = make_float2(0.f, 0.f);
+  }
+  float dbl = 0.f;
+  for (int win = blockIdx.x; win < nwin; win += gridDim.x) {
+    const int w0 = win % ww, h0 = (win / ww) % wh, b = win / (ww * wh);
+    const float g = du[(size_t)win * 32 + lane];
+    if (i == 0) dbl += g;
+    const size_t base = (((size_t)b * ph + h0 * kWin + i) * pw + w0 * kWin) * kDim + 2 * lane;
+    float2 zv[kWin], dv[kWin];
+#pragma unroll
+    for (int j = 0; j < kWin; ++j) {
+      zv[j] = *reinterpret_cast<const float2*>(z + base + j * kDim);
+      dv[j] = *reinterpret_cast<const float2*>(dz + base + j * kDim);
+    }
+#pragma unroll
+    for (int j = 0; j < kWin; ++j) {
+      dv[j].x = fmaf(wr[j].x, g, dv[j].x);
+      dv[j].y = fmaf(wr[j].y, g, dv[j].y);
+      *reinterpret_cast<float2*>(dz + base + j * kDim) = dv[j];
+      acc[j].x = fmaf(g, zv[j].x, acc[j].x);
+      acc[j].y = fmaf(g, zv[j].y, acc[j].y);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < kWin; ++j) {
+    atomicAdd(dw + lane * 128 + i * 8 + j, acc[j].x);
+    atomicAdd(dw + lane * 128 + 64 + i * 8 + j, acc[j].y);
+  }
+  if (i == 0) atomicAdd(db + lane, dbl);
+}
+
+// ------------------------------------------------------------------------------- context
+template <int NH>
+struct NgramSmemBwd {
+  using F = NgramSmem<NH>;
+  static constexpr int oDWqkv = F::oScratch;          // [96][33]
+  static constexpr int oDWp = oDWqkv + 96 * 33;       // [32][33]
+  static constexpr int oDWm = oDWp + 32 * 33;         // [64][65]
+  static constexpr int oDBias = oDWm + 64 * 65;       // [8][12]
+  static constexpr int oDScale = oDBias + 96;         // [8]
+  static constexpr int oScratch = oDScale + 8;
+  // per warp: tok[8][32] qkv[8][96] om[64] cat[64] g[64] dcat[64] dom[64] dqkv[8][96]
+  static constexpr int kScratchPerWarp = 256 + 768 + 64 * 5 + 768;
+  static constexpr int kFloats = oScratch + 8 * kScratchPerWarp;
+};
+
+template <int NH>
+__global__ void __launch_bounds__(kThreads) ngram_ctx_bwd_kernel(NgramParams p) {
+  using L = NgramSmem<NH>;
+  using LB = NgramSmemBwd<NH>;
+  constexpr int HD = L::HD, NA = L::NA;
+  extern __shared__ __align__(16) float smem[];
+  load_ngram_weights<NH>(smem, p);
+  for (int i = threadIdx.x; i < LB::oScratch - LB::oDWqkv; i += blockDim.x) smem[LB::oDWqkv + i] = 0.f;
+  __syncthreads();
+  const float* sWqkv = smem + L::oWqkv;
+  const float* sBqkv = smem + L::oBqkv;
+  const float* sWp = smem + L::oWp;
+  const float* sBp = smem + L::oBp;
+  const float* sWm = smem + L::oWm;
+  const float* sScale = smem + L::oScale;
+  const float* sBias = smem + L::oBias;
+  float* sDWqkv = smem + LB::oDWqkv;
+  float* sDWp = smem + LB::oDWp;
+  float* sDWm = smem + LB::oDWm;
+  float* sDBias = smem + LB::oDBias;
+  float* sDScale = smem + LB::oDScale;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float* sTok = smem + LB::oScratch + warp * LB::kScratchPerWarp;
+  float* sQkv = sTok + 256;
+  float* sOm = sQkv + 768;
+  float* sCat = sOm + 64;
+  float* sG = sCat + 64;
+  float* sDcat = sG + 64;
+  float* sDom = sDcat + 64;
+  float* sDqkv = sDom + 64;
+
+  float dbm[2] = {0.f, 0.f}, dbp = 0.f, dbq[3] = {0.f, 0.f, 0.f};
+
+  const int wh = p.wh, ww = p.ww;
+  const int nwin = p.B * wh * ww;
+  for (int win = blockIdx.x * 8 + warp; win < nwin; win += gridDim.x * 8) {
+    const int w0 = win % ww, h0 = (win / ww) % wh, b = win / (ww * wh);
+    int nbr[8];
+    // ================= forward recompute
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+      int r, c;
+      ngram_neighbour(t, h0, w0, wh, ww, r, c);
+      nbr[t] = ((b * wh + r) * ww + c) * 32;
+      sTok[t * 32 + lane] = p.u[(size_t)nbr[t] + lane];
+    }
+    __syncwarp();
+#pragma unroll
+    for (int jg = 0; jg < 3; ++jg) {
+      const int j = lane + 32 * jg;
+      if (j < 3 * NA) {
+        float acc[8];
+        const float bj = sBqkv[j];
+#pragma unroll
+        for (int t = 0; t < 8; ++t) acc[t] = bj;
+#pragma unroll 8
+        for (int c = 0; c < 32; ++c) {
+          const float wv = sWqkv[j * 33 + c];
+#pragma unroll
+          for (int t = 0; t < 8; ++t) acc[t] = fmaf(wv, sTok[t * 32 + c], acc[t]);
+        }
+#pragma unroll
+        for (int t = 0; t < 8; ++t) sQkv[t * 96 + j] = acc[t];
+      }
+    }
+    __syncwarp();
+    // per-(dir, head) state kept in registers between the forward and backward halves
+    float qn[4][HD], kn[4][HD], P[4][4], nq[4], nk[4];
+    const int dir = lane / NH, h = lane % NH;
+    const bool active = lane < 2 * NH;
+    if (active) {
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const float* row = sQkv + (dir * 4 + t) * 96;
+        float sq = 0.f, sk = 0.f;
+#pragma unroll
+        for (int d = 0; d < HD; ++d) {
+          qn[t][d] = row[h * HD + d];
+          kn[t][d] = row[NA + h * HD + d];
+          sq = fmaf(qn[t][d], qn[t][d], sq);
+          sk = fmaf(kn[t][d], kn[t][d], sk);
+        }
+        nq[t] = sqrtf(sq); nk[t] = sqrtf(sk);
+        const float iq = 1.0f / fmaxf(nq[t], kNormEps), ik = 1.0f / fmaxf(nk[t], kNormEps);
+#pragma unroll
+        for (int d = 0; d < HD; ++d) { qn[t][d] *= iq; kn[t][d] *= ik; }
+      }
+      float om[HD];
+#pragma unroll
+      for (int d = 0; d < HD; ++d) om[d] = 0.f;
+      const float scale = sScale[h];
+#pragma unroll
+      for (int pq = 0; pq < 4; ++pq) {
+        float mx = -INFINITY;
+#pragma unroll
+        for (int kq = 0; kq < 4; ++kq) {
+          float dot = 0.f;
+#pragma unroll
+          for (int d = 0; d < HD; ++d) dot = fmaf(qn[pq][d], kn[kq][d], dot);
+          P[pq][kq] = dot * scale + sBias[h * 12 + ngram_rel_index(pq, kq)];
+          mx = fmaxf(mx, P[pq][kq]);
+        }
+        float sum = 0.f;
+#pragma unroll
+        for (int kq = 0; kq < 4; ++kq) { P[pq][kq] = expf(P[pq][kq] - mx); sum += P[pq][kq]; }
+        const float inv = 1.0f / sum;
+#pragma unroll
+        for (int kq = 0; kq < 4; ++kq) {
+          P[pq][kq] *= inv;
+          const float* vrow = sQkv + (dir * 4 + kq) * 96 + 2 * NA + h * HD;
+#pragma unroll
+          for (int d = 0; d < HD; ++d) om[d] = fmaf(0.25f * P[pq][kq], vrow[d], om[d]);
+        }
+      }
+#pragma unroll
+      for (int d = 0; d < HD; ++d) sOm[dir * 32 + h * HD + d] = om[d];
+    }
+    __syncwarp();
+#pragma unroll
+    for (int dd = 0; dd < 2; ++dd) {
+      float acc = sBp[lane];
+#pragma unroll 6
+      for (int j = 0; j < NA; ++j) acc = fmaf(sWp[lane * 33 + j], sOm[dd * 32 + j], acc);
+      sCat[dd * 32 + lane] = acc;
+    }
+    // ================= backward
+    // ---- B1: merge conv
+#pragma unroll
+    for (int og = 0; og < 2; ++og) {
+      const float gv = p.dctx[(size_t)win * 64 + lane + 32 * og];
+      sG[lane + 32 * og] = gv;
+      dbm[og] += gv;
+    }
+    __syncwarp();
+#pragma unroll
+    for (int og = 0; og < 2; ++og) {
+      const int o = lane + 32 * og;
+      const float gv = sG[o];
+#pragma unroll 8
+      for (int c = 0; c < 64; ++c) atomicAdd(sDWm + o * 65 + c, gv * sCat[c]);
+    }
+#pragma unroll
+    for (int cg = 0; cg < 2; ++cg) {
+      const int c = lane + 32 * cg;
+      float acc = 0.f;
+#pragma unroll 8
+      for (int o = 0; o < 64; ++o) acc = fmaf(sWm[o * 65 + c], sG[o], acc);
+      sDcat[c] = acc;
+    }
+    __syncwarp();
+    // ---- B2: proj (applied to the token-mean, so its input gradient is dom)
+    dbp += sDcat[lane] + sDcat[32 + lane];
+    {
+      const float d0 = sDcat[lane], d1 = sDcat[32 + lane];
+#pragma unroll 6
+      for (int j = 0; j < NA; ++j)
+        atomicAdd(sDWp + lane * 33 + j, d0 * sOm[j] + d1 * sOm[32 + j]);
+    }
+    if (lane < NA) {
+#pragma unroll
+      for (int dd = 0; dd < 2; ++dd) {
+        float acc = 0.f;
+#pragma unroll 8
+        for (int c = 0; c < 32; ++c) acc = fmaf(sWp[c * 33 + lane], sDcat[dd * 32 + c], acc);
+        sDom[dd * 32 + lane] = acc;
+      }
+    }
+    __syncwarp();
+    // ---- B3: 4-token cosine attention backward per (dir, head)
+    if (active) {
+      const float scale = sScale[h];
+      float dom[HD], dPq[4];
+#pragma unroll
+      for (int d = 0; d < HD; ++d) dom[d] = sDom[dir * 32 + h * HD + d];
+#pragma unroll
+      for (int kq = 0; kq < 4; ++kq) {
+        const float* vrow = sQkv + (dir * 4 + kq) * 96 + 2 * NA + h * HD;
+        float acc = 0.f, colsum = 0.f;
+#pragma unroll
+        for (int d = 0; d < HD; ++d) acc = fmaf(dom[d], vrow[d], acc);
+        dPq[kq] = 0.25f * acc;                                   // dP[p][kq], identical for all p
+#pragma unroll
+        for (int pq = 0; pq < 4; ++pq) colsum += P[pq][kq];
+#pragma unroll
+        for (int d = 0; d < HD; ++d)                              // dv[kq][d]
+          sDqkv[(dir * 4 + kq) * 96 + 2 * NA + h * HD + d] = 0.25f * colsum * dom[d];
+      }
+      float dS[4][4], dsc = 0.f;
+#pragma unroll
+      for (int pq = 0; pq < 4; ++pq) {
+        float rowdot = 0.f;
+#pragma unroll
+        for (int kq = 0; kq < 4; ++kq) rowdot = fmaf(dPq[kq], P[pq][kq], rowdot);
+#pragma unroll
+        for (int kq = 0; kq < 4; ++kq) {
+          dS[pq][kq] = P[pq][kq] * (dPq[kq] - rowdot);
+          atomicAdd(sDBias + h * 12 + ngram_rel_index(pq, kq), dS[pq][kq]);
+          float cs = 0.f;
+#pragma unroll
+          for (int d = 0; d < HD; ++d) cs = fmaf(qn[pq][d], kn[kq][d], cs);
+          dsc = fmaf(dS[pq][kq], cs, dsc);
+        }
+      }
+      atomicAdd(sDScale + h, dsc);
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        float dqn[HD], dkn[HD], dotq = 0.f, dotk = 0.f;
+#pragma unroll
+        for (int d = 0; d < HD; ++d) {
+          float aq = 0.f, ak = 0.f;
+#pragma unroll
+          for (int o = 0; o < 4; ++o) {
+            aq = fmaf(dS[t][o], kn[o][d], aq);    // dqn[t] = s * sum_q dS[t][q] kn[q]
+            ak = fmaf(dS[o][t], qn[o][d], ak);    // dkn[t] = s * sum_p dS[p][t] qn[p]
+          }
+          dqn[d] = aq * scale; dkn[d] = ak * scale;
+          dotq = fmaf(qn[t][d], dqn[d], dotq);
+          dotk = fmaf(kn[t][d], dkn[d], dotk);
+        }
+        const float iq = 1.0f / fmaxf(nq[t], kNormEps), ik = 1.0f / fmaxf(nk[t], kNormEps);
+        const float pq_ = nq[t] >= kNormEps ? 1.f : 0.f, pk_ = nk[t] >= kNormEps ? 1.f : 0.f;
+        float* drow = sDqkv + (dir * 4 + t) * 96;
+#pragma unroll
+        for (int d = 0; d < HD; ++d) {
+          drow[h * HD + d] = (dqn[d] - pq_ * qn[t][d] * dotq) * iq;
+          drow[NA + h * HD + d] = (dkn[d] - pk_ * kn[t][d] * dotk) * ik;
+        }
+      }
+    }
+    __syncwarp();
+    // ---- B4: qkv Linear
+#pragma unroll
+    for (int jg = 0; jg < 3; ++jg) {
+      const int j = lane + 32 * jg;
+      if (j < 3 * NA) {
+        float g8[8], s = 0.f;
+#pragma unroll
+        for (int t = 0; t < 8; ++t) { g8[t] = sDqkv[t * 96 + j]; s += g8[t]; }
+        dbq[jg] += s;
+#pragma unroll 4
+        for (int c = 0; c < 32; ++c) {
+          float acc = 0.f;
+#pragma unroll
+          for (int t = 0; t < 8; ++t) acc = fmaf(g8[t], sTok[t * 32 + c], acc);
+          atomicAdd(sDWqkv + j * 33 + c, acc);
+        }
+      }
+    }
+    {
+      float dt[8];
+#pragma unroll
+      for (int t = 0; t < 8; ++t) dt[t] = 0.f;
+#pragma unroll 2
+      for (int j = 0; j < 3 * NA; ++j) {
+        const float wv = sWqkv[j * 33 + lane];
+#pragma unroll
+        for (int t = 0; t < 8; ++t) dt[t] = fmaf(wv, sDqkv[t * 96 + j], dt[t]);
+      }
+#pragma unroll
+      for (int t = 0; t < 8; ++t) atomicAdd(p.du + (size_t)nbr[t] + lane, dt[t]);
+    }
+    __syncwarp();
+  }
+
+  // ================= flush
+#pragma unroll
+  for (int og = 0; og < 2; ++og) atomicAdd(p.d_merge_b + lane + 32 * og, dbm[og]);
+  atomicAdd(p.d_proj_b + lane, dbp);
+#pragma unroll
+  for (int jg = 0; jg < 3; ++jg)
+    if (lane + 32 * jg < 3 * NA) atomicAdd(p.d_qkv_b + lane + 32 * jg, dbq[jg]);
+  __syncthreads();
+  for (int i = threadIdx.x; i < 3 * NA * 32; i += blockDim.x)
+    atomicAdd(p.d_qkv_w + i, sDWqkv[(i >> 5) * 33 + (i & 31)]);
+  for (int i = threadIdx.x; i < 32 * NA; i += blockDim.x)
+    atomicAdd(p.d_proj_w + i, sDWp[(i / NA) * 33 + (i % NA)]);
+  for (int i = threadIdx.x; i < 64 * 64; i += blockDim.x)
+    atomicAdd(p.d_merge_w + i, sDWm[(i >> 6) * 65 + (i & 63)]);
+  for (int i = threadIdx.x; i < NH * 9; i += blockDim.x)
+    atomicAdd(p.d_bias_table + (i % 9) * NH + i / 9, sDBias[(i / 9) * 12 + i % 9]);
+  if (threadIdx.x < NH && p.logit_scale[threadIdx.x] <= kLogitMax)
+    atomicAdd(p.d_logit_scale + threadIdx.x, sDScale[threadIdx.x] * sScale[threadIdx.x]);
+}
+
+template <int NH>
+static int launch_ngram_ctx_bwd(const NgramParams& p, cudaStream_t st) {
+  using LB = NgramSmemBwd<NH>;
+  const size_t smem = LB::kFloats * sizeof(float);
+  static bool configured = false;
+  if (!configured) {
+    B200MAR_CHECK(cudaFuncSetAttribute(ngram_ctx_bwd_kernel<NH>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = true;
+  }
+  const int nwin = p.B * p.wh * p.ww;
+  int grid = (nwin + 7) / 8;
+  if (grid > sm_count()) grid = sm_count();
+  B200MAR_CHECK(cudaMemsetAsync(p.du, 0, (size_t)nwin * 32 * sizeof(float), st));
+  ngram_ctx_bwd_kernel<NH><<<grid, kThreads, smem, st>>>(p);
+  B200MAR_CHECK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace b200mar
+
+extern "C" int b200mar_unigram_bwd(const float* z, const float* weight, const float* du, float* dz,
+                                   float* dweight, float* dbias, int B, int ph, int pw,
+                                   void* stream) {
+  using namespace b200mar;
+  if (ph % kWin || pw % kWin || ph < kWin || pw < kWin) return -1;
+  const int nwin = B * (ph / kWin) * (pw / kWin);
+  int grid = nwin;
+  if (grid > 4 * sm_count()) grid = 4 * sm_count();
+  unigram_bwd_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(z, weight, du, dz, dweight, dbias,
+                                                                  B, ph, pw);
+  B200MAR_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200mar_ngram_ctx_bwd(const float* u, const float* dctx, const float* qkv_w,
+                                     const float* qkv_b, const float* proj_w, const float* proj_b,
+                                     const float* logit_scale, const float* bias_table,
+                                     const float* merge_w, const float* merge_b, float* du,
+                                     float* d_qkv_w, float* d_qkv_b, float* d_proj_w,
+                                     float* d_proj_b, float* d_logit_scale, float* d_bias_table,
+                                     float* d_merge_w, float* d_merge_b, int B, int wh, int ww,
+                                     int nh, void* stream) {
+  using namespace b200mar;
+  if (wh < 2 || ww < 2) return -1;
+  NgramParams p{};
+  p.u = u; p.dctx = dctx; p.qkv_w = qkv_w; p.qkv_b = qkv_b; p.proj_w = proj_w; p.proj_b = proj_b;
+  p.logit_scale = logit_scale; p.bias_table = bias_table; p.merge_w = merge_w; p.merge_b = merge_b;
+  p.du = du; p.d_qkv_w = d_qkv_w; p.d_qkv_b = d_qkv_b; p.d_proj_w = d_proj_w; p.d_proj_b = d_proj_b;
+  p.d_logit_scale = d_logit_scale; p.d_bias_table = d_bias_table; p.d_merge_w = d_merge_w;
+  p.d_merge_b = d_merge_b; p.B = B; p.wh = wh; p.ww = ww;
+  if (nh == 6) return launch_ngram_ctx_bwd<6>(p, (cudaStream_t)stream);
+  if (nh == 4) return launch_ngram_ctx_bwd<4>(p, (cudaStream_t)stream);
+  return -1;
+}

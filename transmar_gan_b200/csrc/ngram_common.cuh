@@ -1,0 +1,88 @@
+// ngram_common.cuh — parameter block / smem layout of the N-gram context kernels.
+#pragma once
+#include "common.cuh"
+
+namespace b200mar {
+
+struct NgramParams {
+  const float* u;            // [B, wh, ww, 32] unigram embeddings (channels last)
+  const float* qkv_w;        // [3*NA, 32]
+  const float* qkv_b;        // [3*NA]
+  const float* proj_w;       // [32, NA]
+  const float* proj_b;       // [32]
+  const float* logit_scale;  // [nh]
+  const float* bias_table;   // [9, nh]
+  const float* merge_w;      // [64, 64]
+  const float* merge_b;      // [64]
+  float* ctx;                // [B, wh, ww, 64]
+  // backward only
+  const float* dctx;
+  float* du;
+  float* d_qkv_w; float* d_qkv_b; float* d_proj_w; float* d_proj_b;
+  float* d_logit_scale; float* d_bias_table; float* d_merge_w; float* d_merge_b;
+  int B, wh, ww;
+};
+
+template <int NH>
+struct NgramSmem {
+  static constexpr int HD = 32 / NH;          // 5 (6 heads) or 8 (4 heads)
+  static constexpr int NA = HD * NH;          // 30 or 32
+  static constexpr int oWqkv = 0;             // [96][33]
+  static constexpr int oBqkv = oWqkv + 96 * 33;
+  static constexpr int oWp = oBqkv + 96;      // [32][33]
+  static constexpr int oBp = oWp + 32 * 33;
+  static constexpr int oWm = oBp + 32;        // [64][65]
+  static constexpr int oBm = oWm + 64 * 65;
+  static constexpr int oScale = oBm + 64;     // [8]
+  static constexpr int oBias = oScale + 8;    // [NH][12]
+  static constexpr int oScratch = oBias + 8 * 12;
+  static constexpr int kScratchPerWarp = 8 * 32 + 8 * 96 + 64 + 64;
+  static constexpr int kFloatsFwd = oScratch + 8 * kScratchPerWarp;
+};
+
+// Neighbourhood token t (0..3 forward, 4..7 backward; within a direction t = 2*i + j,
+// row-offset major, window_utils.py:65) of window (h0,w0) -> source window (r,c) of the
+// unpadded unigram map.  Forward pad: row wh := row wh-2, column ww := column ww-2
+// (window_utils.py:49-54); backward pad: row -1 := row 1, column -1 := column 1 (:55-60).
+__device__ __forceinline__ void ngram_neighbour(int t, int h0, int w0, int wh, int ww, int& r,
+                                                int& c) {
+  const int i = (t >> 1) & 1, j = t & 1;
+  if (t < 4) {
+    r = h0 + i; if (r >= wh) r = wh - 2;
+    c = w0 + j; if (c >= ww) c = ww - 2;
+  } else {
+    r = h0 + i - 1; if (r < 0) r = 1;
+    c = w0 + j - 1; if (c < 0) c = 1;
+  }
+}
+// relative position index inside the 2x2 n-gram window (attention.py:9-18 with win 2)
+__device__ __forceinline__ int ngram_rel_index(int p, int q) {
+  return ((p >> 1) - (q >> 1) + 1) * 3 + ((p & 1) - (q & 1) + 1);
+}
+
+template <int NH>
+__device__ __forceinline__ void load_ngram_weights(float* smem, const NgramParams& p) {
+  using L = NgramSmem<NH>;
+  for (int i = threadIdx.x; i < 96 * 32; i += blockDim.x) {
+    const int r = i >> 5, c = i & 31;
+    smem[L::oWqkv + r * 33 + c] = r < 3 * L::NA ? p.qkv_w[r * 32 + c] : 0.f;
+  }
+  for (int i = threadIdx.x; i < 96; i += blockDim.x)
+    smem[L::oBqkv + i] = i < 3 * L::NA ? p.qkv_b[i] : 0.f;
+  for (int i = threadIdx.x; i < 32 * L::NA; i += blockDim.x) {
+    const int r = i / L::NA, c = i - r * L::NA;
+    smem[L::oWp + r * 33 + c] = p.proj_w[i];
+  }
+  for (int i = threadIdx.x; i < 32; i += blockDim.x) smem[L::oBp + i] = p.proj_b[i];
+  for (int i = threadIdx.x; i < 64 * 64; i += blockDim.x)
+    smem[L::oWm + (i >> 6) * 65 + (i & 63)] = p.merge_w[i];
+  for (int i = threadIdx.x; i < 64; i += blockDim.x) smem[L::oBm + i] = p.merge_b[i];
+  if (threadIdx.x < NH)
+    smem[L::oScale + threadIdx.x] = expf(fminf(p.logit_scale[threadIdx.x], kLogitMax));
+  for (int i = threadIdx.x; i < NH * 9; i += blockDim.x) {
+    const int h = i / 9, e = i - h * 9;
+    smem[L::oBias + h * 12 + e] = p.bias_table[e * NH + h];
+  }
+}
+
+}  // namespace b200mar

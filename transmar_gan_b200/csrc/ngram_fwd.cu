@@ -1,0 +1,219 @@
+// ngram_fwd.cu — N-gram context, forward (fp32).
+//   unigram_fwd : grouped 8x8/stride-8 conv (components/window_utils.py:36-38,78) as one
+//                 streaming pass over the token tensor, one warp per window.
+//   ngram_ctx_fwd: seq_refl_win_pad fwd/bwd (:43-61) + 2x2 sliding WindowAttention(dim 32)
+//                 (:63-73, attention.py:70-101) + AvgPool2d(2) + concat + 1x1 merge (:86-90),
+//                 one warp per window, reflect padding folded into the index math.
+#include "common.cuh"
+#include "ngram_common.cuh"
+
+namespace b200mar {
+
+// ------------------------------------------------------------------------------- unigram
+__global__ void __launch_bounds__(kThreads) unigram_fwd_kernel(
+    const float* __restrict__ z, const float* __restrict__ w, const float* __restrict__ bias,
+    float* __restrict__ u, int B, int ph, int pw) {
+  __shared__ __align__(16) float sW[kTok * kDim];  // [t = 8i+j][c = 2g+k]
+  for (int idx = threadIdx.x; idx < kTok * kDim; idx += blockDim.x) {
+    const int t = idx >> 6, c = idx & 63;
+    sW[idx] = w[(c >> 1) * 128 + (c & 1) * 64 + t];
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int wh = ph / kWin, ww = pw / kWin;
+  const int nwin = B * wh * ww;
+  const float bl = bias[lane];
+  for (int win = blockIdx.x * 8 + warp; win < nwin; win += gridDim.x * 8) {
+    const int w0 = win % ww, h0 = (win / ww) % wh, b = win / (ww * wh);
+    const float* base = z + (((size_t)b * ph + h0 * kWin) * pw + w0 * kWin) * kDim + 2 * lane;
+    float acc = 0.f;
+#pragma unroll 1
+    for (int i = 0; i < kWin; ++i) {
+      float2 v[kWin];
+#pragma unroll
+      for (int j = 0; j < kWin; ++j)
+        v[j] = *reinterpret_cast<const float2*>(base + ((size_t)i * pw + j) * kDim);
+#pragma unroll
+      for (int j = 0; j < kWin; ++j) {
+        const float2 wv = *reinterpret_cast<const float2*>(sW + (i * kWin + j) * kDim + 2 * lane);
+        acc = fmaf(v[j].x, wv.x, acc);
+        acc = fmaf(v[j].y, wv.y, acc);
+      }
+    }
+    u[(size_t)win * 32 + lane] = acc + bl;
+  }
+}
+
+// ------------------------------------------------------------------------------- context
+template <int NH>
+__global__ void __launch_bounds__(kThreads) ngram_ctx_fwd_kernel(NgramParams p) {
+  using L = NgramSmem<NH>;
+  constexpr int HD = L::HD, NA = L::NA;
+  extern __shared__ __align__(16) float smem[];
+  load_ngram_weights<NH>(smem, p);
+  __syncthreads();
+  const float* sWqkv = smem + L::oWqkv;
+  const float* sBqkv = smem + L::oBqkv;
+  const float* sWp = smem + L::oWp;
+  const float* sBp = smem + L::oBp;
+  const float* sWm = smem + L::oWm;
+  const float* sBm = smem + L::oBm;
+  const float* sScale = smem + L::oScale;
+  const float* sBias = smem + L::oBias;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float* sTok = smem + L::oScratch + warp * L::kScratchPerWarp;  // [8][32]
+  float* sQkv = sTok + 8 * 32;                                   // [8][96]
+  float* sOm = sQkv + 8 * 96;                                    // [64]  mean attention out per dir
+  float* sCat = sOm + 64;                                        // [64]
+
+  const int wh = p.wh, ww = p.ww;
+  const int nwin = p.B * wh * ww;
+  for (int win = blockIdx.x * 8 + warp; win < nwin; win += gridDim.x * 8) {
+    const int w0 = win % ww, h0 = (win / ww) % wh, b = win / (ww * wh);
+    // ---- the 8 neighbourhood tokens (4 forward, 4 backward), lane = channel
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+      int r, c;
+      ngram_neighbour(t, h0, w0, wh, ww, r, c);
+      sTok[t * 32 + lane] = p.u[((size_t)(b * wh + r) * ww + c) * 32 + lane];
+    }
+    __syncwarp();
+    // ---- qkv = Linear(32 -> 3*NA)
+#pragma unroll
+    for (int jg = 0; jg < 3; ++jg) {
+      const int j = lane + 32 * jg;
+      if (j < 3 * NA) {
+        float acc[8];
+        const float bj = sBqkv[j];
+#pragma unroll
+        for (int t = 0; t < 8; ++t) acc[t] = bj;
+#pragma unroll 8
+        for (int c = 0; c < 32; ++c) {
+          const float wv = sWqkv[j * 33 + c];
+#pragma unroll
+          for (int t = 0; t < 8; ++t) acc[t] = fmaf(wv, sTok[t * 32 + c], acc[t]);
+        }
+#pragma unroll
+        for (int t = 0; t < 8; ++t) sQkv[t * 96 + j] = acc[t];
+      }
+    }
+    __syncwarp();
+    // ---- 4-token cosine attention per (direction, head); mean over the 4 query tokens
+    if (lane < 2 * NH) {
+      const int dir = lane / NH, h = lane % NH;
+      float qn[4][HD], kn[4][HD];
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const float* row = sQkv + (dir * 4 + t) * 96;
+        float sq = 0.f, sk = 0.f;
+#pragma unroll
+        for (int d = 0; d < HD; ++d) {
+          qn[t][d] = row[h * HD + d];
+          kn[t][d] = row[NA + h * HD + d];
+          sq = fmaf(qn[t][d], qn[t][d], sq);
+          sk = fmaf(kn[t][d], kn[t][d], sk);
+        }
+        const float iq = 1.0f / fmaxf(sqrtf(sq), kNormEps), ik = 1.0f / fmaxf(sqrtf(sk), kNormEps);
+#pragma unroll
+        for (int d = 0; d < HD; ++d) { qn[t][d] *= iq; kn[t][d] *= ik; }
+      }
+      float om[HD];
+#pragma unroll
+      for (int d = 0; d < HD; ++d) om[d] = 0.f;
+      const float scale = sScale[h];
+#pragma unroll
+      for (int pq = 0; pq < 4; ++pq) {
+        float s[4], mx = -INFINITY;
+#pragma unroll
+        for (int kq = 0; kq < 4; ++kq) {
+          float dot = 0.f;
+#pragma unroll
+          for (int d = 0; d < HD; ++d) dot = fmaf(qn[pq][d], kn[kq][d], dot);
+          s[kq] = dot * scale + sBias[h * 12 + ngram_rel_index(pq, kq)];
+          mx = fmaxf(mx, s[kq]);
+        }
+        float sum = 0.f;
+#pragma unroll
+        for (int kq = 0; kq < 4; ++kq) { s[kq] = expf(s[kq] - mx); sum += s[kq]; }
+        const float inv = 0.25f / sum;   // softmax normalisation and the AvgPool2d(2) mean
+#pragma unroll
+        for (int kq = 0; kq < 4; ++kq) {
+          const float pv = s[kq] * inv;
+          const float* vrow = sQkv + (dir * 4 + kq) * 96 + 2 * NA + h * HD;
+#pragma unroll
+          for (int d = 0; d < HD; ++d) om[d] = fmaf(pv, vrow[d], om[d]);
+        }
+      }
+#pragma unroll
+      for (int d = 0; d < HD; ++d) sOm[dir * 32 + h * HD + d] = om[d];
+    }
+    __syncwarp();
+    // ---- proj (commutes with the mean): cat[dir*32 + c] = bp[c] + Wp[c,:] . om[dir]
+#pragma unroll
+    for (int dir = 0; dir < 2; ++dir) {
+      float acc = sBp[lane];
+#pragma unroll 6
+      for (int j = 0; j < NA; ++j) acc = fmaf(sWp[lane * 33 + j], sOm[dir * 32 + j], acc);
+      sCat[dir * 32 + lane] = acc;
+    }
+    __syncwarp();
+    // ---- merge 1x1 conv 64 -> 64
+#pragma unroll
+    for (int og = 0; og < 2; ++og) {
+      const int o = lane + 32 * og;
+      float acc = sBm[o];
+#pragma unroll 8
+      for (int c = 0; c < 64; ++c) acc = fmaf(sWm[o * 65 + c], sCat[c], acc);
+      p.ctx[(size_t)win * 64 + o] = acc;
+    }
+    __syncwarp();
+  }
+}
+
+template <int NH>
+static int launch_ngram_ctx_fwd(const NgramParams& p, cudaStream_t st) {
+  using L = NgramSmem<NH>;
+  const size_t smem = L::kFloatsFwd * sizeof(float);
+  static bool configured = false;
+  if (!configured) {
+    B200MAR_CHECK(cudaFuncSetAttribute(ngram_ctx_fwd_kernel<NH>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = true;
+  }
+  const int nwin = p.B * p.wh * p.ww;
+  int grid = (nwin + 7) / 8;
+  if (grid > 2 * sm_count()) grid = 2 * sm_count();
+  ngram_ctx_fwd_kernel<NH><<<grid, kThreads, smem, st>>>(p);
+  B200MAR_CHECK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace b200mar
+
+extern "C" int b200mar_unigram_fwd(const float* z, const float* weight, const float* bias, float* u,
+                                   int B, int ph, int pw, void* stream) {
+  using namespace b200mar;
+  if (ph % kWin || pw % kWin || ph < kWin || pw < kWin) return -1;
+  const int nwin = B * (ph / kWin) * (pw / kWin);
+  int grid = (nwin + 7) / 8;
+  if (grid > 8 * sm_count()) grid = 8 * sm_count();
+  unigram_fwd_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(z, weight, bias, u, B, ph, pw);
+  B200MAR_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200mar_ngram_ctx_fwd(const float* u, const float* qkv_w, const float* qkv_b,
+                                     const float* proj_w, const float* proj_b,
+                                     const float* logit_scale, const float* bias_table,
+                                     const float* merge_w, const float* merge_b, float* ctx, int B,
+                                     int wh, int ww, int nh, void* stream) {
+  using namespace b200mar;
+  if (wh < 2 || ww < 2) return -1;  // the reference raises for a single window row/column
+  NgramParams p{};
+  p.u = u; p.qkv_w = qkv_w; p.qkv_b = qkv_b; p.proj_w = proj_w; p.proj_b = proj_b;
+  p.logit_scale = logit_scale; p.bias_table = bias_table; p.merge_w = merge_w; p.merge_b = merge_b;
+  p.ctx = ctx; p.B = B; p.wh = wh; p.ww = ww;
+  if (nh == 6) return launch_ngram_ctx_fwd<6>(p, (cudaStream_t)stream);
+  if (nh == 4) return launch_ngram_ctx_fwd<4>(p, (cudaStream_t)stream);
+  return -1;
+}

@@ -1,0 +1,355 @@
+"""Drop-in `NGswin` generator whose N-gram window-attention blocks run on hand-written
+sm_100a CUDA kernels (libb200mar.so).
+
+Boundary contract: same constructor signature as the reference
+`models/generator/ngswin.py:43-49`, the same 554 `state_dict` entries (names, shapes, dtypes,
+order — parameters live in real nn.Linear / nn.Conv2d / nn.LayerNorm submodules carrying the
+reference attribute names so `netG.apply(weights_init)` and `load_state_dict(strict=True)`
+behave identically), and the same `forward(x: [B,1,H,W]) -> [B,1,H,W]`.
+
+What runs where
+  * CUDA kernels (this repo): unigram conv, n-gram context attention, fused shifted-window
+    partition + cosine attention + LN1 + residual, fused MLP + LN2 + residual(+within-stage
+    sum), PatchMerging, pixel-shuffle + concat — forward and backward.
+  * stock PyTorch/cuDNN inside the drop-in: shallow
+    3x3 conv, max-pools, cascade projections, bottleneck depthwise conv / pointwise linear,
+    final LayerNorm and the two reconstruction convs.
+There is NO CPU forward: calling the module on CPU tensors raises.
+"""
+from __future__ import annotations
+
+import math
+from itertools import repeat
+from typing import Tuple
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import ops
+
+WINDOW = 8
+
+
+def _pair(v) -> Tuple[int, int]:
+    return tuple(v) if isinstance(v, (tuple, list)) else (v, v)
+
+
+def _ntuple(v, n):
+    return tuple(v) if isinstance(v, (tuple, list)) else tuple(repeat(v, n))
+
+
+def relative_position_index(win: int) -> torch.Tensor:
+    """[win^2, win^2] int64 buffer, idx[p,q] = (p_i-q_i+win-1)*(2win-1) + (p_j-q_j+win-1)
+    (reference: components/attention.py:9-18)."""
+    t = torch.arange(win * win)
+    i, j = t // win, t % win
+    return ((i[:, None] - i[None, :] + win - 1) * (2 * win - 1)
+            + (j[:, None] - j[None, :] + win - 1)).to(torch.int64)
+
+
+def shift_attn_mask(ph: int, pw: int, window: int = WINDOW, shift: int = WINDOW // 2) -> torch.Tensor:
+    """[nW, 64, 64] fp32 buffer (0 / -100) kept only for state_dict parity — the kernels
+    evaluate the same 9-region rule analytically (reference: transformer_blocks.py:63-81)."""
+    def ids(n):
+        a = torch.arange(n)
+        return (a >= n - window).to(torch.int64) + (a >= n - shift).to(torch.int64)
+    rid = ids(ph)[:, None] * 3 + ids(pw)[None, :]
+    wh, ww = ph // window, pw // window
+    w = rid.reshape(wh, window, ww, window).permute(0, 2, 1, 3).reshape(wh * ww, window * window)
+    return ((w[:, None, :] != w[:, :, None]).to(torch.float32)) * -100.0
+
+
+# ------------------------------------------------------------------------------ containers
+class WindowAttention(nn.Module):
+    """Parameter container of a scaled-cosine window attention (attention.py:40-62)."""
+
+    def __init__(self, dim, num_heads, window_size, head_dim=None, qkv_bias=True):
+        super().__init__()
+        self.dim, self.num_heads, self.window = dim, num_heads, window_size
+        head_dim = head_dim or dim // num_heads
+        self.attn_dim = head_dim * num_heads
+        self.logit_scale = nn.Parameter(torch.log(10 * torch.ones((num_heads, 1, 1))))
+        self.relative_position_bias_table = nn.Parameter(
+            torch.zeros((2 * window_size - 1) ** 2, num_heads))
+        self.register_buffer("relative_position_index", relative_position_index(window_size))
+        self.qkv = nn.Linear(dim, self.attn_dim * 3, bias=qkv_bias)
+        self.proj = nn.Linear(self.attn_dim, dim)
+        nn.init.trunc_normal_(self.relative_position_bias_table, std=.02)
+
+
+class NGramContext(nn.Module):
+    def __init__(self, dim, window_size, ngram, num_heads):
+        super().__init__()
+        self.unigram_embed = nn.Conv2d(dim, dim // 2, kernel_size=window_size, stride=window_size,
+                                       padding=0, groups=dim // 2)
+        self.ngram_attn = WindowAttention(dim // 2, num_heads, ngram)
+        self.merge = nn.Conv2d(dim, dim, 1, 1, 0)
+
+
+class NGramWindowPartition(nn.Module):
+    def __init__(self, dim, window_size, ngram, num_heads, shift_size):
+        super().__init__()
+        self.shift_size = shift_size
+        self.ngram_context = NGramContext(dim, window_size, ngram, num_heads)
+
+
+class Mlp(nn.Module):
+    def __init__(self, dim, hidden):
+        super().__init__()
+        self.fc1 = nn.Linear(dim, hidden)
+        self.fc2 = nn.Linear(hidden, dim)
+
+
+class NSTB(nn.Module):
+    """N-Gram Swin Transformer Block; forward is two+two CUDA kernels (ops.NSTBFunction)."""
+
+    def __init__(self, dim, training_num_patches, ngram, num_heads, window_size, shift_size,
+                 head_dim=None, mlp_ratio=2., qkv_bias=True):
+        super().__init__()
+        self.num_heads, self.shift_size = num_heads, shift_size
+        self.ngram_window_partition = NGramWindowPartition(dim, window_size, ngram, num_heads,
+                                                           shift_size)
+        self.attn = WindowAttention(dim, num_heads, window_size, head_dim, qkv_bias)
+        mask = shift_attn_mask(*training_num_patches, window_size, shift_size) if shift_size > 0 else None
+        self.register_buffer("attn_mask", mask)
+        self.norm1 = nn.LayerNorm(dim)
+        self.ffn = Mlp(dim, int(dim * mlp_ratio))
+        self.norm2 = nn.LayerNorm(dim)
+
+    def kernel_params(self):
+        """The block's 24 parameter tensors in ops.NSTB_PARAM_NAMES order."""
+        c, a, f = self.ngram_window_partition.ngram_context, self.attn, self.ffn
+        g = c.ngram_attn
+        return (c.unigram_embed.weight, c.unigram_embed.bias, g.qkv.weight, g.qkv.bias,
+                g.proj.weight, g.proj.bias, g.logit_scale, g.relative_position_bias_table,
+                c.merge.weight, c.merge.bias,
+                a.qkv.weight, a.qkv.bias, a.proj.weight, a.proj.bias, a.logit_scale,
+                a.relative_position_bias_table, self.norm1.weight, self.norm1.bias,
+                f.fc1.weight, f.fc1.bias, f.fc2.weight, f.fc2.bias,
+                self.norm2.weight, self.norm2.bias)
+
+    def forward(self, z, num_patches, want_out=True, want_zsum=True):
+        ph, pw = num_patches
+        out, zsum = ops.NSTBFunction.apply(z, ph, pw, self.num_heads, self.shift_size, want_out,
+                                           want_zsum, *self.kernel_params())
+        return out, zsum
+
+
+class PatchMerging(nn.Module):
+    def __init__(self, dim, downsample_dim=None):
+        super().__init__()
+        self.norm = nn.LayerNorm(4 * dim)
+        self.reduction = nn.Linear(4 * dim, downsample_dim or dim, bias=False)
+
+    def forward(self, x, num_patches):
+        ph, pw = num_patches
+        y = ops.PatchMergeFunction.apply(x, ph, pw, self.norm.weight, self.norm.bias,
+                                         self.reduction.weight)
+        return y, (ph // 2, pw // 2)
+
+
+class _Stage(nn.Module):
+    """Shared body of EncoderLayer / DecoderLayer (encoder_decoder.py:135-145, :252-258)."""
+
+    def _build_blocks(self, dim, training_num_patches, ngram, depth, num_heads, window_size,
+                      head_dim, mlp_ratio, qkv_bias):
+        self.blocks = nn.Sequential(*[
+            NSTB(dim, training_num_patches, ngram, num_heads, window_size,
+                 0 if i % 2 == 0 else window_size // 2, head_dim, mlp_ratio, qkv_bias)
+            for i in range(depth)])
+
+    def _run_blocks(self, x, num_patches, need_sum_last):
+        """Block i consumes z_i = out_{i-1} + z_{i-1}; each block's MLP kernel emits that sum
+        for its successor, so intermediate `out` tensors are never written."""
+        z, n = x, len(self.blocks)
+        out = zsum = None
+        for i, blk in enumerate(self.blocks):
+            last = i == n - 1
+            out, zsum = blk(z, num_patches, want_out=last, want_zsum=(not last) or need_sum_last)
+            z = zsum
+        return out, zsum
+
+
+class EncoderLayer(_Stage):
+    def __init__(self, dim, training_num_patches, ngram, depth, num_heads, window_size,
+                 head_dim=None, mlp_ratio=2., qkv_bias=True, downsample=False, num_cas=1):
+        super().__init__()
+        self.across_cascade_proj = nn.Linear(dim * num_cas, dim) if num_cas != 1 else nn.Identity()
+        self._build_blocks(dim, training_num_patches, ngram, depth, num_heads, window_size,
+                           head_dim, mlp_ratio, qkv_bias)
+        self.downsample = PatchMerging(dim, dim) if downsample else None
+
+    def forward(self, x, num_patches):
+        x = self.across_cascade_proj(x).contiguous()
+        out, zsum = self._run_blocks(x, num_patches, need_sum_last=self.downsample is not None)
+        if self.downsample is None:
+            return out, out, num_patches
+        down, np2 = self.downsample(zsum, num_patches)
+        return out, down, np2
+
+
+class DecoderLayer(_Stage):
+    def __init__(self, dim, training_num_patches, ngram, depth, num_heads, window_size,
+                 head_dim=None, mlp_ratio=2., qkv_bias=True):
+        super().__init__()
+        self._build_blocks(dim, training_num_patches, ngram, depth, num_heads, window_size,
+                           head_dim, mlp_ratio, qkv_bias)
+
+    def forward(self, x, num_patches):
+        out, _ = self._run_blocks(x.contiguous(), num_patches, need_sum_last=False)
+        return out
+
+
+class ShallowExtractor(nn.Module):
+    def __init__(self, in_chans, out_chans):
+        super().__init__()
+        self.conv1 = nn.Conv2d(in_chans, out_chans, 3, 1, 1)
+
+    def forward(self, x):
+        return self.conv1(x)
+
+
+class SCDPBottleneck(nn.Module):
+    """pixel-Shuffle, Concat, Depth-wise conv, Point-wise projection (encoder_decoder.py:166-200)."""
+
+    def __init__(self, num_encoder_stages, enc_dim, dec_dim):
+        super().__init__()
+        self.concat_dim = sum(4 ** i for i in range(num_encoder_stages)) * (enc_dim // 16)
+        self.depthwise = nn.Conv2d(self.concat_dim, self.concat_dim, 3, 1, 1, groups=self.concat_dim)
+        self.pointwise = nn.Linear(self.concat_dim, dec_dim)
+        self.norm = nn.LayerNorm(dec_dim)
+
+    def forward(self, shallow, feats, H, W):
+        xs = []
+        s = shallow
+        for i, f in enumerate(feats):
+            if i > 0:
+                s = F.max_pool2d(s, 2)
+            skip = F.leaky_relu(s, 0.01).flatten(2).transpose(1, 2)      # pooling.py:32-37
+            xs.append((f + skip).contiguous())
+        cat = ops.PixelShuffleCatFunction.apply(xs[0], xs[1], xs[2], H, W)   # [B, HW, 84]
+        B = cat.shape[0]
+        x = cat.transpose(1, 2).reshape(B, self.concat_dim, H, W)
+        x = F.gelu(self.depthwise(x))
+        x = x.flatten(2).transpose(1, 2)
+        return self.norm(self.pointwise(x))
+
+
+class Reconstruction(nn.Sequential):
+    def __init__(self, dim, out_chans, upscale):
+        super().__init__()
+        self.add_module("before_shuffle", nn.Conv2d(dim, out_chans * upscale ** 2, 3, 1, 1))
+        self.add_module("to_origin", nn.Conv2d(out_chans, out_chans, 3, 1, 1))
+        self.add_module("tanh", nn.Tanh())
+
+
+# ------------------------------------------------------------------------------ the model
+class NGswin(nn.Module):
+    """B200-native drop-in for `models.generator.ngswin.NGswin` (reference ngswin.py:18-210)."""
+
+    def __init__(self, training_img_size=64, ngrams=(2, 2, 2, 2), in_chans=1, embed_dim=64,
+                 depths=(6, 4, 4), num_heads=(6, 4, 4), head_dim=None, dec_dim=64, dec_depths=6,
+                 dec_num_heads=6, dec_head_dim=None, target_mode='light_x1', window_size=8,
+                 mlp_ratio=2., qkv_bias=True, img_norm=True, drop_rate=0.0, attn_drop_rate=0.0,
+                 drop_path_rate=0.0, act_layer=nn.GELU, norm_layer=nn.LayerNorm, weight_init='',
+                 **kwargs):
+        assert target_mode in ['light_x1', 'light_x3', 'light_x4'], \
+            "'target mode' should be one of ['light_x1', 'light_x3', 'light_x4']"
+        super().__init__()
+        # The fused kernels implement the one configuration every caller of the reference
+        # instantiates (`NGswin()`, training/train_combined.py:226); anything else is refused
+        # loudly instead of silently computing something different.
+        unsupported = []
+        if embed_dim != 64 or dec_dim != 64: unsupported.append("embed_dim/dec_dim != 64")
+        if window_size != 8: unsupported.append("window_size != 8")
+        if tuple(ngrams) != (2, 2, 2, 2): unsupported.append("ngrams != (2,2,2,2)")
+        if len(depths) != 3 or len(num_heads) != 3: unsupported.append("other than 3 encoder stages")
+        if any(h not in (4, 6) for h in tuple(num_heads) + (dec_num_heads,)):
+            unsupported.append("head counts other than 4 or 6")
+        if head_dim is not None or dec_head_dim is not None: unsupported.append("explicit head_dim")
+        if float(mlp_ratio) != 2.0: unsupported.append("mlp_ratio != 2")
+        if not qkv_bias: unsupported.append("qkv_bias=False")
+        if drop_rate or attn_drop_rate or drop_path_rate: unsupported.append("non-zero drop rates")
+        if act_layer is not nn.GELU or norm_layer is not nn.LayerNorm:
+            unsupported.append("act_layer/norm_layer other than GELU/LayerNorm")
+        if target_mode != 'light_x1' or in_chans != 1: unsupported.append("target_mode/in_chans")
+        if unsupported:
+            raise NotImplementedError("transmar_gan_b200.NGswin: unsupported configuration: "
+                                      + "; ".join(unsupported))
+        self.training_img_size = _pair(training_img_size)
+        self.ngrams, self.embed_dim, self.depths, self.num_heads = ngrams, embed_dim, depths, num_heads
+        self.dec_dim, self.dec_depths, self.dec_num_heads = dec_dim, (dec_depths,), (dec_num_heads,)
+        self.window_size = window_size
+        self.num_encoder_stages, self.num_decoder_stages = len(depths), 1
+        self.scale = int(target_mode[-1])
+        self.img_norm = False                                   # reference ngswin.py:79
+        ts = self.training_img_size
+        self.shallow_extract = ShallowExtractor(in_chans, embed_dim)
+        for i in range(3):
+            self.add_module(f'encoder_layer{i + 1}', EncoderLayer(
+                embed_dim, (ts[0] // 2 ** i, ts[1] // 2 ** i), ngrams[i], depths[i], num_heads[i],
+                window_size, None, 2., qkv_bias, downsample=(i != 2), num_cas=i + 1))
+        self.bottleneck = SCDPBottleneck(3, embed_dim, dec_dim)
+        self.add_module('decoder_layer1', DecoderLayer(
+            dec_dim, (ts[0] // 2, ts[1] // 2), ngrams[3], dec_depths, dec_num_heads, window_size,
+            None, 2., qkv_bias))
+        self.norm = nn.LayerNorm(dec_dim)
+        self.to_target = Reconstruction(dec_dim, in_chans, self.scale)
+        self.apply(self._init_weights)
+
+    @staticmethod
+    def _init_weights(m):
+        # Swin-V2 manner (reference ngswin.py:140-148)
+        if isinstance(m, nn.Linear):
+            nn.init.trunc_normal_(m.weight, std=.02)
+            if m.bias is not None:
+                nn.init.constant_(m.bias, 0)
+        elif isinstance(m, nn.LayerNorm):
+            nn.init.constant_(m.bias, 0)
+            nn.init.constant_(m.weight, 1.0)
+
+    @torch.jit.ignore
+    def no_weight_decay(self):
+        return {n for n, _ in self.named_parameters() if 'relative_position_bias_table' in n}
+
+    def forward(self, x):
+        if not x.is_cuda:
+            raise RuntimeError("transmar_gan_b200.NGswin has no CPU path; move the module and the "
+                               "input to a B200 (`.cuda()`)")
+        _, _, H0, W0 = x.shape
+        unit = 4 * self.window_size
+        padh, padw = (unit - H0 % unit) % unit, (unit - W0 % unit) % unit
+        if padh or padw:
+            x = F.pad(x, (0, padw, 0, padh))                     # zeros right / bottom
+        B, _, H, W = x.shape
+        if H < 2 * unit or W < 2 * unit:
+            raise RuntimeError(f"input {H0}x{W0} pads to {H}x{W}; NGswin needs >= 64 per side "
+                               "(stage 3 must have 2x2 windows; the reference raises too)")
+        shallow = self.shallow_extract(x.float())
+        c0 = shallow.flatten(2).transpose(1, 2).contiguous()     # [B, HW, 64]
+        e1_, e1, np1 = self.encoder_layer1(c0, (H, W))
+        c1 = torch.cat([_token_maxpool(c0, H, W), e1], dim=-1)
+        e2_, e2, np2 = self.encoder_layer2(c1, np1)
+        c2 = torch.cat([_token_maxpool(c1, *np1), e2], dim=-1)
+        e3_, _, _ = self.encoder_layer3(c2, np2)
+        bt = self.bottleneck(shallow, [e1_, e2_, e3_], H, W)
+        dec = self.decoder_layer1(bt + e1_, (H, W))
+        dec = self.norm(dec) + c0                                # global skip (ngswin.py:204)
+        img = dec.transpose(1, 2).reshape(B, self.dec_dim, H, W)
+        out = self.to_target(img)
+        return out[:, :, :H0, :W0]
+
+    def flops(self, resolutions):
+        """Exact multiply-accumulate count of one forward, unpadded head dims."""
+        unit = 4 * self.window_size
+        H, W = resolutions
+        H += (unit - H % unit) % unit
+        W += (unit - W % unit) % unit
+        return H * W * 548013
+
+
+def _token_maxpool(x, ph, pw):
+    """InterPool (pooling.py:13-17): 2x2 max-pool on the token grid, channels last."""
+    B, T, C = x.shape
+    return x.reshape(B, ph // 2, 2, pw // 2, 2, C).amax(dim=(2, 4)).reshape(B, T // 4, C)

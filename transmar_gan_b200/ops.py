@@ -1,0 +1,346 @@
+"""torch custom ops (`torch.ops.b200mar.*`) over the C ABI of libb200mar.so, plus the
+block-level autograd functions built from them.
+
+Every op is a thin launcher: it allocates the outputs with torch (device memory is torch's
+job), passes raw device pointers + the current CUDA stream to the `extern "C"` entry point
+and raises on a non-zero return.  There is no CPU implementation: tensors must be CUDA fp32
+contiguous, otherwise a RuntimeError is raised (a fake/meta implementation is registered
+only so the ops can be traced / captured).
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Tuple
+
+import torch
+from torch import Tensor
+
+from . import _cabi
+
+_NS = "b200mar"
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _chk(*tensors: Tensor):
+    for t in tensors:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise RuntimeError("transmar_gan_b200 ops have no CPU path: tensor is on "
+                               f"{t.device}; move the module and its input to a B200 (cuda)")
+        if t.dtype != torch.float32 or not t.is_contiguous():
+            raise RuntimeError(f"b200mar ops need contiguous fp32 tensors, got {t.dtype}, "
+                               f"contiguous={t.is_contiguous()}")
+
+
+def _p(t: Optional[Tensor]) -> Optional[int]:
+    return None if t is None or t.numel() == 0 else t.data_ptr()
+
+
+# ------------------------------------------------------------------------------ n-gram context
+@torch.library.custom_op(f"{_NS}::unigram_fwd", mutates_args=())
+def unigram_fwd(z: Tensor, weight: Tensor, bias: Tensor, ph: int, pw: int) -> Tensor:
+    _chk(z, weight, bias)
+    B = z.shape[0]
+    u = torch.empty((B, ph // 8, pw // 8, 32), device=z.device, dtype=torch.float32)
+    _cabi.check(_cabi.lib().b200mar_unigram_fwd(_p(z), _p(weight), _p(bias), _p(u), B, ph, pw,
+                                                _stream()), "b200mar_unigram_fwd")
+    return u
+
+
+@unigram_fwd.register_fake
+def _(z, weight, bias, ph, pw):
+    return z.new_empty((z.shape[0], ph // 8, pw // 8, 32))
+
+
+@torch.library.custom_op(f"{_NS}::unigram_bwd", mutates_args=("dz", "dweight", "dbias"))
+def unigram_bwd(z: Tensor, weight: Tensor, du: Tensor, dz: Tensor, dweight: Tensor,
+                dbias: Tensor, ph: int, pw: int) -> None:
+    _chk(z, weight, du, dz, dweight, dbias)
+    _cabi.check(_cabi.lib().b200mar_unigram_bwd(_p(z), _p(weight), _p(du), _p(dz), _p(dweight),
+                                                _p(dbias), z.shape[0], ph, pw, _stream()),
+                "b200mar_unigram_bwd")
+
+
+@torch.library.custom_op(f"{_NS}::ngram_ctx_fwd", mutates_args=())
+def ngram_ctx_fwd(u: Tensor, qkv_w: Tensor, qkv_b: Tensor, proj_w: Tensor, proj_b: Tensor,
+                  logit_scale: Tensor, bias_table: Tensor, merge_w: Tensor, merge_b: Tensor,
+                  nh: int) -> Tensor:
+    _chk(u, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, merge_w, merge_b)
+    B, wh, ww, _ = u.shape
+    if wh < 2 or ww < 2:
+        raise RuntimeError("NGramContext needs at least 2x2 windows per stage "
+                           "(the reference raises for smaller inputs, SURVEY.md A.4)")
+    ctx = torch.empty((B, wh, ww, 64), device=u.device, dtype=torch.float32)
+    _cabi.check(_cabi.lib().b200mar_ngram_ctx_fwd(
+        _p(u), _p(qkv_w), _p(qkv_b), _p(proj_w), _p(proj_b), _p(logit_scale), _p(bias_table),
+        _p(merge_w), _p(merge_b), _p(ctx), B, wh, ww, nh, _stream()), "b200mar_ngram_ctx_fwd")
+    return ctx
+
+
+@ngram_ctx_fwd.register_fake
+def _(u, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, merge_w, merge_b, nh):
+    return u.new_empty((*u.shape[:3], 64))
+
+
+@torch.library.custom_op(f"{_NS}::ngram_ctx_bwd", mutates_args=("du", "grads"))
+def ngram_ctx_bwd(u: Tensor, dctx: Tensor, params: List[Tensor], du: Tensor,
+                  grads: List[Tensor], nh: int) -> None:
+    """params/grads order: qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, merge_w, merge_b"""
+    _chk(u, dctx, du, *params, *grads)
+    B, wh, ww, _ = u.shape
+    _cabi.check(_cabi.lib().b200mar_ngram_ctx_bwd(
+        _p(u), _p(dctx), *[_p(t) for t in params], _p(du), *[_p(t) for t in grads],
+        B, wh, ww, nh, _stream()), "b200mar_ngram_ctx_bwd")
+
+
+# ------------------------------------------------------------------------------ window attention
+@torch.library.custom_op(f"{_NS}::attn_fwd", mutates_args=())
+def attn_fwd(z: Tensor, ctx: Tensor, qkv_w: Tensor, qkv_b: Tensor, proj_w: Tensor, proj_b: Tensor,
+             logit_scale: Tensor, bias_table: Tensor, ln_w: Tensor, ln_b: Tensor,
+             ph: int, pw: int, nh: int, shift: int) -> Tensor:
+    _chk(z, ctx, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, ln_w, ln_b)
+    a = torch.empty_like(z)
+    _cabi.check(_cabi.lib().b200mar_attn_fwd(
+        _p(z), _p(ctx), _p(qkv_w), _p(qkv_b), _p(proj_w), _p(proj_b), _p(logit_scale),
+        _p(bias_table), _p(ln_w), _p(ln_b), _p(a), z.shape[0], ph, pw, nh, shift, _stream()),
+        "b200mar_attn_fwd")
+    return a
+
+
+@attn_fwd.register_fake
+def _(z, ctx, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, ln_w, ln_b, ph, pw, nh, shift):
+    return torch.empty_like(z)
+
+
+@torch.library.custom_op(f"{_NS}::attn_bwd", mutates_args=("dz", "dctx", "grads"))
+def attn_bwd(z: Tensor, ctx: Tensor, da: Tensor, params: List[Tensor], dz: Tensor, dctx: Tensor,
+             grads: List[Tensor], ph: int, pw: int, nh: int, shift: int) -> None:
+    """params/grads order: qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, ln_w, ln_b"""
+    _chk(z, ctx, da, dz, dctx, *params, *grads)
+    _cabi.check(_cabi.lib().b200mar_attn_bwd(
+        _p(z), _p(ctx), _p(da), *[_p(t) for t in params], _p(dz), _p(dctx),
+        *[_p(t) for t in grads], z.shape[0], ph, pw, nh, shift, _stream()), "b200mar_attn_bwd")
+
+
+# ------------------------------------------------------------------------------ MLP + LN2 + residual
+@torch.library.custom_op(f"{_NS}::mlp_fwd", mutates_args=())
+def mlp_fwd(a: Tensor, z: Optional[Tensor], fc1_w: Tensor, fc1_b: Tensor, fc2_w: Tensor,
+            fc2_b: Tensor, ln_w: Tensor, ln_b: Tensor, want_out: bool,
+            want_zsum: bool) -> Tuple[Tensor, Tensor]:
+    _chk(a, z, fc1_w, fc1_b, fc2_w, fc2_b, ln_w, ln_b)
+    out = torch.empty_like(a) if want_out else a.new_empty(0)
+    zsum = torch.empty_like(a) if want_zsum else a.new_empty(0)
+    n_tok = a.numel() // 64
+    _cabi.check(_cabi.lib().b200mar_mlp_fwd(
+        _p(a), _p(z), _p(fc1_w), _p(fc1_b), _p(fc2_w), _p(fc2_b), _p(ln_w), _p(ln_b), _p(out),
+        _p(zsum), n_tok, _stream()), "b200mar_mlp_fwd")
+    return out, zsum
+
+
+@mlp_fwd.register_fake
+def _(a, z, fc1_w, fc1_b, fc2_w, fc2_b, ln_w, ln_b, want_out, want_zsum):
+    return (torch.empty_like(a) if want_out else a.new_empty(0),
+            torch.empty_like(a) if want_zsum else a.new_empty(0))
+
+
+@torch.library.custom_op(f"{_NS}::mlp_bwd", mutates_args=("da", "grads"))
+def mlp_bwd(a: Tensor, dout: Tensor, params: List[Tensor], da: Tensor, grads: List[Tensor]) -> None:
+    """params/grads order: fc1_w, fc1_b, fc2_w, fc2_b, ln_w, ln_b"""
+    _chk(a, dout, da, *params, *grads)
+    _cabi.check(_cabi.lib().b200mar_mlp_bwd(
+        _p(a), _p(dout), *[_p(t) for t in params], _p(da), *[_p(t) for t in grads],
+        a.numel() // 64, _stream()), "b200mar_mlp_bwd")
+
+
+# ------------------------------------------------------------------------------ patch merging
+@torch.library.custom_op(f"{_NS}::patch_merge_fwd", mutates_args=())
+def patch_merge_fwd(x: Tensor, ln_w: Tensor, ln_b: Tensor, red_w: Tensor, ph: int,
+                    pw: int) -> Tensor:
+    _chk(x, ln_w, ln_b, red_w)
+    B = x.shape[0]
+    y = torch.empty((B, (ph // 2) * (pw // 2), 64), device=x.device, dtype=torch.float32)
+    _cabi.check(_cabi.lib().b200mar_patch_merge_fwd(_p(x), _p(ln_w), _p(ln_b), _p(red_w), _p(y),
+                                                    B, ph, pw, _stream()), "b200mar_patch_merge_fwd")
+    return y
+
+
+@patch_merge_fwd.register_fake
+def _(x, ln_w, ln_b, red_w, ph, pw):
+    return x.new_empty((x.shape[0], (ph // 2) * (pw // 2), 64))
+
+
+@torch.library.custom_op(f"{_NS}::patch_merge_bwd", mutates_args=("dx", "grads"))
+def patch_merge_bwd(x: Tensor, dy: Tensor, params: List[Tensor], dx: Tensor, grads: List[Tensor],
+                    ph: int, pw: int) -> None:
+    """params/grads order: ln_w, ln_b, red_w"""
+    _chk(x, dy, dx, *params, *grads)
+    _cabi.check(_cabi.lib().b200mar_patch_merge_bwd(
+        _p(x), _p(dy), *[_p(t) for t in params], _p(dx), *[_p(t) for t in grads],
+        x.shape[0], ph, pw, _stream()), "b200mar_patch_merge_bwd")
+
+
+# ------------------------------------------------------------------------------ pixel shuffle + cat
+@torch.library.custom_op(f"{_NS}::pixel_shuffle_cat", mutates_args=())
+def pixel_shuffle_cat(x0: Tensor, x1: Tensor, x2: Tensor, H: int, W: int) -> Tensor:
+    _chk(x0, x1, x2)
+    B = x0.shape[0]
+    cat = torch.empty((B, H * W, 84), device=x0.device, dtype=torch.float32)
+    _cabi.check(_cabi.lib().b200mar_pixel_shuffle_cat(_p(x0), _p(x1), _p(x2), _p(cat), B, H, W, 0,
+                                                      _stream()), "b200mar_pixel_shuffle_cat")
+    return cat
+
+
+@pixel_shuffle_cat.register_fake
+def _(x0, x1, x2, H, W):
+    return x0.new_empty((x0.shape[0], H * W, 84))
+
+
+@torch.library.custom_op(f"{_NS}::pixel_shuffle_cat_bwd", mutates_args=())
+def pixel_shuffle_cat_bwd(dcat: Tensor, H: int, W: int) -> Tuple[Tensor, Tensor, Tensor]:
+    _chk(dcat)
+    B = dcat.shape[0]
+    d0 = torch.empty((B, H * W, 64), device=dcat.device, dtype=torch.float32)
+    d1 = torch.empty((B, H * W // 4, 64), device=dcat.device, dtype=torch.float32)
+    d2 = torch.empty((B, H * W // 16, 64), device=dcat.device, dtype=torch.float32)
+    _cabi.check(_cabi.lib().b200mar_pixel_shuffle_cat(_p(d0), _p(d1), _p(d2), _p(dcat), B, H, W, 1,
+                                                      _stream()), "b200mar_pixel_shuffle_cat(inv)")
+    return d0, d1, d2
+
+
+@pixel_shuffle_cat_bwd.register_fake
+def _(dcat, H, W):
+    B = dcat.shape[0]
+    return (dcat.new_empty((B, H * W, 64)), dcat.new_empty((B, H * W // 4, 64)),
+            dcat.new_empty((B, H * W // 16, 64)))
+
+
+# ------------------------------------------------------------------------------ index maps
+def partition_index(B: int, ph: int, pw: int, shift: int, device) -> Tuple[Tensor, Tensor]:
+    n = B * (ph // 8) * (pw // 8)
+    tok = torch.empty((n, 64), dtype=torch.int64, device=device)
+    cwin = torch.empty((n, 64), dtype=torch.int64, device=device)
+    _cabi.check(_cabi.lib().b200mar_partition_index(tok.data_ptr(), cwin.data_ptr(), B, ph, pw,
+                                                    shift, _stream()), "b200mar_partition_index")
+    return tok, cwin
+
+
+def shift_mask(ph: int, pw: int, shift: int, device) -> Tensor:
+    m = torch.empty(((ph // 8) * (pw // 8), 64, 64), dtype=torch.float32, device=device)
+    _cabi.check(_cabi.lib().b200mar_shift_mask(m.data_ptr(), ph, pw, shift, _stream()),
+                "b200mar_shift_mask")
+    return m
+
+
+def rel_index(device) -> Tensor:
+    r = torch.empty((64, 64), dtype=torch.int64, device=device)
+    _cabi.check(_cabi.lib().b200mar_rel_index(r.data_ptr(), _stream()), "b200mar_rel_index")
+    return r
+
+
+# ------------------------------------------------------------------------------ autograd: NSTB
+# Parameter order of one NSTB as passed to NSTBFunction (24 tensors):
+NSTB_PARAM_NAMES = (
+    # n-gram context (10)
+    "ngram_window_partition.ngram_context.unigram_embed.weight",
+    "ngram_window_partition.ngram_context.unigram_embed.bias",
+    "ngram_window_partition.ngram_context.ngram_attn.qkv.weight",
+    "ngram_window_partition.ngram_context.ngram_attn.qkv.bias",
+    "ngram_window_partition.ngram_context.ngram_attn.proj.weight",
+    "ngram_window_partition.ngram_context.ngram_attn.proj.bias",
+    "ngram_window_partition.ngram_context.ngram_attn.logit_scale",
+    "ngram_window_partition.ngram_context.ngram_attn.relative_position_bias_table",
+    "ngram_window_partition.ngram_context.merge.weight",
+    "ngram_window_partition.ngram_context.merge.bias",
+    # window attention + norm1 (8)
+    "attn.qkv.weight", "attn.qkv.bias", "attn.proj.weight", "attn.proj.bias",
+    "attn.logit_scale", "attn.relative_position_bias_table", "norm1.weight", "norm1.bias",
+    # MLP + norm2 (6)
+    "ffn.fc1.weight", "ffn.fc1.bias", "ffn.fc2.weight", "ffn.fc2.bias",
+    "norm2.weight", "norm2.bias",
+)
+
+
+class NSTBFunction(torch.autograd.Function):
+    """One N-Gram Swin Transformer Block (components/transformer_blocks.py:114-120) plus the
+    within-stage residual sum (components/encoder_decoder.py:138-141):
+        out  = a + LN2(MLP(a)),  a = z + LN1(attn(partition(z + ctx(z))))
+        zsum = out + z            (input of the next block / of the stage's PatchMerging)
+    Saves only z, u, ctx, a; everything else is recomputed in the backward kernels."""
+
+    @staticmethod
+    def forward(ctx_, z, ph, pw, nh, shift, want_out, want_zsum, *params):
+        P = [p.detach() for p in params]
+        u = unigram_fwd(z, P[0], P[1], ph, pw)
+        c = ngram_ctx_fwd(u, P[2], P[3], P[4], P[5], P[6], P[7], P[8], P[9], nh)
+        a = attn_fwd(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw, nh, shift)
+        out, zsum = mlp_fwd(a, z if want_zsum else None, P[18], P[19], P[20], P[21], P[22], P[23],
+                            want_out, want_zsum)
+        ctx_.save_for_backward(z, u, c, a, *params)
+        ctx_.geom = (ph, pw, nh, shift)
+        ctx_.mark_non_differentiable(*([] if want_out else [out]), *([] if want_zsum else [zsum]))
+        return out, zsum
+
+    @staticmethod
+    def backward(ctx_, g_out, g_zsum):
+        z, u, c, a, *params = ctx_.saved_tensors
+        ph, pw, nh, shift = ctx_.geom
+        P = [p.detach() for p in params]
+        have_out = g_out is not None and g_out.numel() > 0
+        have_zs = g_zsum is not None and g_zsum.numel() > 0
+        if have_out and have_zs:
+            g = (g_out + g_zsum).contiguous()
+        else:
+            g = (g_out if have_out else g_zsum).contiguous()
+        # one zeroed flat buffer for all parameter gradients of the block
+        sizes = [p.numel() for p in P]
+        flat = torch.zeros(sum(sizes), device=z.device, dtype=torch.float32)
+        G, off = [], 0
+        for p, n in zip(P, sizes):
+            G.append(flat[off:off + n].view(p.shape))
+            off += n
+        da = torch.empty_like(a)
+        mlp_bwd(a, g, P[18:24], da, G[18:24])
+        dz = torch.empty_like(z)
+        dctx = torch.zeros_like(c)
+        attn_bwd(z, c, da, P[10:18], dz, dctx, G[10:18], ph, pw, nh, shift)
+        du = torch.empty_like(u)
+        ngram_ctx_bwd(u, dctx, P[2:10], du, G[2:10], nh)
+        unigram_bwd(z, P[0], du, dz, G[0], G[1], ph, pw)
+        if have_zs:
+            dz += g_zsum
+        return (dz, None, None, None, None, None, None, *G)
+
+
+class PatchMergeFunction(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx_, x, ph, pw, ln_w, ln_b, red_w):
+        y = patch_merge_fwd(x, ln_w.detach(), ln_b.detach(), red_w.detach(), ph, pw)
+        ctx_.save_for_backward(x, ln_w, ln_b, red_w)
+        ctx_.geom = (ph, pw)
+        return y
+
+    @staticmethod
+    def backward(ctx_, dy):
+        x, ln_w, ln_b, red_w = ctx_.saved_tensors
+        ph, pw = ctx_.geom
+        P = [ln_w.detach(), ln_b.detach(), red_w.detach()]
+        G = [torch.zeros_like(p) for p in P]
+        dx = torch.empty_like(x)
+        patch_merge_bwd(x, dy.contiguous(), P, dx, G, ph, pw)
+        return (dx, None, None, *G)
+
+
+class PixelShuffleCatFunction(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx_, x0, x1, x2, H, W):
+        ctx_.geom = (H, W)
+        return pixel_shuffle_cat(x0, x1, x2, H, W)
+
+    @staticmethod
+    def backward(ctx_, dcat):
+        H, W = ctx_.geom
+        d0, d1, d2 = pixel_shuffle_cat_bwd(dcat.contiguous(), H, W)
+        return d0, d1, d2, None, None
