@@ -1,0 +1,370 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200-native NGswin hot path.
+
+    python bench.py --gpus N --steps K --warmup W            # our arm
+    python bench.py --impl reference --gpus N --steps K ...  # CPU reference arm (oracle port)
+
+Metric (BASELINE.json): NGswin inference slices/sec.  Workload = BASELINE.json configs[1]:
+batch 32 synthetic single-channel 416x416 CT slices per GPU (SynDeepLesion slice size), W1
+weights, one "step" = one forward of one batch.  N > 1: one process per GPU, each rank runs
+the same workload on its own shard (inference replicas, no data-path collective; weak
+scaling); timing = barrier + synchronize on both sides, max over ranks.  A `train` object in
+the same JSON line reports the config-3 training step (fwd + bwd + Adam, batch 16 x 128x128
+per GPU) with the bucketed NCCL gradient all-reduce at N > 1.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "ngswin_inference_slices_per_sec"
+UNIT = "slices/s"
+H = W = 416
+BATCH = 32
+MACS_PER_PIXEL = 548013            # exact MACs per pixel of one forward
+ATTN6_FLOPS_PER_TOKEN = 2 * (11520 + 3840 + 3840 + 3840)   # qkv + QK^T + PV + proj, head_dim 10
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=BATCH)
+    ap.add_argument("--size", type=int, default=H)
+    ap.add_argument("--no-train", action="store_true", help="skip the training-step leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------ helpers
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                 "--format=csv,noheader,nounits", "-lms", "200"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); power.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(p):
+        d = json.load(open(p))
+        return d.get("hbm_gbs", 6650.0), d.get("bf16_tflops_sustained", 1400.0), "measured"
+    return 6650.0, 1400.0, "fallback"       # B200_PROFILING.md fallback figures
+
+
+def cpu_forward_time(size: int, runs: int):
+    """Oracle port of the reference forward on the host cores: seconds per 1-slice forward."""
+    from oracle import ngswin_oracle as O
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    sd = O.synthetic_state_dict("W1", seed=1)
+    x = O.synthetic_input(1, size, size, seed=999)
+    with torch.no_grad():
+        t0 = time.perf_counter()
+        O.ngswin_forward(x, sd)                      # warm-up (also bounds the leg's cost)
+        first = time.perf_counter() - t0
+        ts = []
+        for _ in range(runs):
+            t0 = time.perf_counter()
+            O.ngswin_forward(x, sd)
+            ts.append(time.perf_counter() - t0)
+            if sum(ts) + first > 40.0:
+                break
+    return sum(ts) / len(ts), threads, len(ts)
+
+
+# ------------------------------------------------------------------------------ reference arm
+def run_reference(args):
+    """`--impl reference`: the reference's CPU implementation of the path.  The reference is a
+    Python package that cannot travel to the GPU box (/root/reference does not exist there), so
+    this arm times the oracle port (oracle/ngswin_oracle.py, pinned to the reference to 1e-6)
+    on the host cores; each step is a bounded sample of the workload: ONE 416x416 slice."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import ngswin_oracle as O
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    sd = O.synthetic_state_dict("W1", seed=1)
+    x = O.synthetic_input(1, args.size, args.size, seed=999)
+    with torch.no_grad():
+        for _ in range(min(args.warmup, 1)):
+            O.ngswin_forward(x, sd)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            O.ngswin_forward(x, sd)
+        dt = time.perf_counter() - t0
+    v = args.steps / dt
+    sample = f"1 slice {args.size}x{args.size} per step (of the batch-{args.batch} workload), fp32, eval"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": f"NGswin inference, batch {args.batch} x 1x{args.size}x{args.size} "
+                               "synthetic CT slices (BASELINE.json configs[1])",
+                   "sample_per_step": sample},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+# ------------------------------------------------------------------------------ our arm
+def dist_setup(args):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    return rank, world, local
+
+
+def barrier(world):
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def max_over_ranks(ms, world):
+    if world == 1:
+        return ms
+    import torch.distributed as dist
+    t = torch.tensor([ms], device="cuda", dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return t.item()
+
+
+def build_model(kind="W1"):
+    """Random-init weights of the reference architecture (no checkpoint ships with the reference):
+    W1 = `NGswin()` + the callers' weights_init N(0,.02) (training/train_combined.py:207-217)."""
+    import transmar_gan_b200 as T
+    torch.manual_seed(1234)
+    m = T.NGswin()
+    g = torch.Generator().manual_seed(1)
+    with torch.no_grad():
+        for mod in m.modules():
+            if isinstance(mod, (torch.nn.Conv2d, torch.nn.Linear)):
+                mod.weight.copy_(torch.randn(mod.weight.shape, generator=g) * 0.02)
+                if mod.bias is not None:
+                    mod.bias.zero_()
+    return m.cuda()
+
+
+def time_inference(model, args, world, sampler):
+    """value leg: inputs resident in HBM; K forwards of one batch each, CUDA events."""
+    from transmar_gan_b200 import ops
+    B, S = args.batch, args.size
+    g = torch.Generator().manual_seed(999 + int(os.environ.get("RANK", "0")))
+    x = (torch.rand(B, 1, S, S, generator=g) * 2 - 1).cuda()
+    model.eval()
+    with torch.no_grad():
+        for _ in range(args.warmup):
+            model(x)
+        barrier(world)
+        ops.profile.reset(timed=("attn_fwd", "mlp_fwd"))
+        if sampler:
+            sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.steps):
+            y = model(x)
+        e1.record()
+        barrier(world)
+    clocks = sampler.stop() if sampler else None
+    ms = max_over_ranks(e0.elapsed_time(e1), world)
+    launches = ops.profile.launches
+    attn = [t for t, meta in ops.profile.elapsed("attn_fwd") if meta[1] == S and meta[3] == 6]
+    mlp = [t for t, meta in ops.profile.elapsed("mlp_fwd")]
+    ops.profile.reset()
+    return ms, launches, attn, mlp, clocks, y
+
+
+def time_e2e(model, args, world):
+    """e2e leg: the call a user makes — host (pinned) input -> model -> host output, copies timed."""
+    B, S = args.batch, args.size
+    xh = (torch.rand(B, 1, S, S) * 2 - 1).pin_memory()
+    yh = torch.empty(B, 1, S, S).pin_memory()
+    with torch.no_grad():
+        for _ in range(2):
+            yh.copy_(model(xh.cuda(non_blocking=True)), non_blocking=True)
+        barrier(world)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.steps):
+            yh.copy_(model(xh.cuda(non_blocking=True)), non_blocking=True)
+        e1.record()
+        barrier(world)
+    ms = max_over_ranks(e0.elapsed_time(e1), world)
+    return ms, xh.numel() * 4, yh.numel() * 4
+
+
+def time_train(args, rank, world):
+    """config-3 recipe per rank: y = netG(x); F.l1_loss(y,t).backward(); all-reduce; Adam.step()
+    (scripts/run_ablation_studies.py:1525-1535; Adam betas (.5,.999) lr 1e-4), batch 16 x 128x128."""
+    import torch.nn.functional as F
+    from transmar_gan_b200 import dp, ops
+    model = build_model().train()
+    dp.broadcast_parameters(model)
+    bucket = dp.FlatGradBucket(model.parameters())
+    opt = torch.optim.Adam(model.parameters(), lr=1e-4, betas=(0.5, 0.999))
+    B, S = 16, 128
+    g = torch.Generator().manual_seed(999 + rank)
+    x = (torch.rand(B, 1, S, S, generator=g) * 2 - 1).cuda()
+    t = (torch.rand(B, 1, S, S, generator=g) * 2 - 1).cuda()
+
+    def step():
+        bucket.zero()
+        loss = F.l1_loss(model(x), t)
+        loss.backward()
+        bucket.all_reduce()
+        opt.step()
+        return loss
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier(world)
+    ops.profile.reset()
+    steps = max(args.steps, 5)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        loss = step()
+    e1.record()
+    barrier(world)
+    ms = max_over_ranks(e0.elapsed_time(e1), world) / steps
+    launches = ops.profile.launches // steps
+    return {"steps_per_s": 1e3 / ms, "slices_per_s": world * B * 1e3 / ms, "ms_per_step": ms,
+            "per_gpu_batch": B, "size": S, "recipe": "fwd + L1 + bwd + flat-bucket all-reduce + Adam",
+            "allreduce_bytes": bucket.numel * 4 if world > 1 else 0,
+            "gpu_launches_per_step": launches, "final_loss": float(loss.item())}
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+        return
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a B200: the hot path has no CPU implementation "
+                         "(use --impl reference for the CPU reference arm)")
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    rank, world, local = dist_setup(args)
+    import transmar_gan_b200 as T
+    assert T._cabi.lib().b200mar_device_ok(local) == 1, "not an sm_100 device"
+    model = build_model()
+    sampler = ClockSampler(local) if rank == 0 else None
+    ms, launches, attn_ms, mlp_ms, clocks, _ = time_inference(model, args, world, sampler)
+    e2e_ms, h2d, d2h = time_e2e(model, args, world)
+    train = None if args.no_train else time_train(args, rank, world)
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        sec, threads, runs = cpu_forward_time(args.size, 3)
+        cpu = {"value": 1.0 / sec, "unit": UNIT, "cores": threads, "kind": "port",
+               "sample": f"{runs} timed 1-slice {args.size}x{args.size} forwards of the oracle port "
+                         f"(oracle/ngswin_oracle.py, torch CPU fp32, {threads} threads), 1 warm-up"}
+    if rank != 0:
+        return
+    K, B, S = args.steps, args.batch, args.size
+    slices = world * B * K
+    value = slices / (ms / 1e3)
+    hbm_peak, tf_peak, which = peaks()
+    tokens = B * S * S
+    attn_avg = sum(attn_ms) / max(len(attn_ms), 1)
+    ach = ATTN6_FLOPS_PER_TOKEN * tokens / (attn_avg / 1e3) / 1e12 if attn_ms else None
+    step_flops = 2 * MACS_PER_PIXEL * tokens
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K,
+        "warmup": args.warmup, "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"NGswin inference (BASELINE.json configs[1]), batch {B} x 1x{S}x{S} "
+                               "synthetic CT slices per GPU, W1 random-init weights, fp32 stream + "
+                               "fp32 accumulate (the parity-green mode)",
+                   "per_gpu_batch": B, "size": S, "parallelism": f"replicas x{world}",
+                   "l2_policy": "inputs larger than L2 (1.4 GB activation tensors vs 126 MB L2)"},
+        "clocks": clocks,
+        "e2e": {"value": slices / (e2e_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms / K},
+        "gpu_launches": launches,
+        "roofline": {"kernel": "attn_fwd_kernel<6> (fused partition + window attention + LN1 + residual)",
+                     "bound": "tensor", "achieved": ach, "peak": tf_peak, "unit": "TFLOP/s",
+                     "frac": (ach / tf_peak) if ach else None, "traffic": None,
+                     "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({which})",
+                     "algorithmic_flops_per_launch": ATTN6_FLOPS_PER_TOKEN * tokens,
+                     "avg_launch_ms": attn_avg, "launches_timed": len(attn_ms),
+                     "share_of_step": (sum(attn_ms) / ms) if attn_ms else None,
+                     "mlp_fwd_share_of_step": (sum(mlp_ms) / ms) if mlp_ms else None,
+                     "whole_step_tflops": step_flops / (ms / K / 1e3) / 1e12,
+                     "note": "fp32 SIMT kernel (round-1 correctness path): FMA pipe, no tcgen05 yet"},
+        "cpu_baseline": cpu,
+        "train": train,
+    }
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()
+    if torch.distributed.is_available() and torch.distributed.is_initialized():
+        torch.distributed.destroy_process_group()

@@ -35,6 +35,39 @@ def _chk(*tensors: Tensor):
                                f"contiguous={t.is_contiguous()}")
 
 
+class profile:
+    """Launch accounting for bench.py: `launches` counts every kernel-launching C-ABI call;
+    kernels named in `timed` get a CUDA-event pair recorded around their launch on the
+    launching stream (events are (start, end, meta) tuples, read with `elapsed`)."""
+    launches = 0
+    timed: set = set()
+    events: dict = {}
+
+    @classmethod
+    def reset(cls, timed=()):
+        cls.launches, cls.timed, cls.events = 0, set(timed), {}
+
+    @classmethod
+    def elapsed(cls, name):
+        """[(milliseconds, meta)] for every recorded launch of `name` (synchronises)."""
+        torch.cuda.synchronize()
+        return [(a.elapsed_time(b), m) for a, b, m in cls.events.get(name, [])]
+
+
+def _call(name: str, *args, meta=None):
+    fn = getattr(_cabi.lib(), "b200mar_" + name)
+    profile.launches += 1
+    if name in profile.timed:
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        code = fn(*args)
+        b.record()
+        profile.events.setdefault(name, []).append((a, b, meta if meta is not None else args[-6:-1]))
+    else:
+        code = fn(*args)
+    _cabi.check(code, "b200mar_" + name)
+
+
 def _p(t: Optional[Tensor]) -> Optional[int]:
     return None if t is None or t.numel() == 0 else t.data_ptr()
 
@@ -45,8 +78,8 @@ def unigram_fwd(z: Tensor, weight: Tensor, bias: Tensor, ph: int, pw: int) -> Te
     _chk(z, weight, bias)
     B = z.shape[0]
     u = torch.empty((B, ph // 8, pw // 8, 32), device=z.device, dtype=torch.float32)
-    _cabi.check(_cabi.lib().b200mar_unigram_fwd(_p(z), _p(weight), _p(bias), _p(u), B, ph, pw,
-                                                _stream()), "b200mar_unigram_fwd")
+    _call("unigram_fwd", _p(z), _p(weight), _p(bias), _p(u), B, ph, pw,
+                                                _stream())
     return u
 
 
@@ -59,9 +92,8 @@ def _(z, weight, bias, ph, pw):
 def unigram_bwd(z: Tensor, weight: Tensor, du: Tensor, dz: Tensor, dweight: Tensor,
                 dbias: Tensor, ph: int, pw: int) -> None:
     _chk(z, weight, du, dz, dweight, dbias)
-    _cabi.check(_cabi.lib().b200mar_unigram_bwd(_p(z), _p(weight), _p(du), _p(dz), _p(dweight),
-                                                _p(dbias), z.shape[0], ph, pw, _stream()),
-                "b200mar_unigram_bwd")
+    _call("unigram_bwd", _p(z), _p(weight), _p(du), _p(dz), _p(dweight),
+                                                _p(dbias), z.shape[0], ph, pw, _stream())
 
 
 @torch.library.custom_op(f"{_NS}::ngram_ctx_fwd", mutates_args=())
@@ -74,9 +106,8 @@ def ngram_ctx_fwd(u: Tensor, qkv_w: Tensor, qkv_b: Tensor, proj_w: Tensor, proj_
         raise RuntimeError("NGramContext needs at least 2x2 windows per stage "
                            "(the reference raises for smaller inputs, SURVEY.md A.4)")
     ctx = torch.empty((B, wh, ww, 64), device=u.device, dtype=torch.float32)
-    _cabi.check(_cabi.lib().b200mar_ngram_ctx_fwd(
-        _p(u), _p(qkv_w), _p(qkv_b), _p(proj_w), _p(proj_b), _p(logit_scale), _p(bias_table),
-        _p(merge_w), _p(merge_b), _p(ctx), B, wh, ww, nh, _stream()), "b200mar_ngram_ctx_fwd")
+    _call("ngram_ctx_fwd", _p(u), _p(qkv_w), _p(qkv_b), _p(proj_w), _p(proj_b), _p(logit_scale), _p(bias_table),
+        _p(merge_w), _p(merge_b), _p(ctx), B, wh, ww, nh, _stream())
     return ctx
 
 
@@ -91,9 +122,8 @@ def ngram_ctx_bwd(u: Tensor, dctx: Tensor, params: List[Tensor], du: Tensor,
     """params/grads order: qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, merge_w, merge_b"""
     _chk(u, dctx, du, *params, *grads)
     B, wh, ww, _ = u.shape
-    _cabi.check(_cabi.lib().b200mar_ngram_ctx_bwd(
-        _p(u), _p(dctx), *[_p(t) for t in params], _p(du), *[_p(t) for t in grads],
-        B, wh, ww, nh, _stream()), "b200mar_ngram_ctx_bwd")
+    _call("ngram_ctx_bwd", _p(u), _p(dctx), *[_p(t) for t in params], _p(du), *[_p(t) for t in grads],
+        B, wh, ww, nh, _stream())
 
 
 # ------------------------------------------------------------------------------ window attention
@@ -103,10 +133,8 @@ def attn_fwd(z: Tensor, ctx: Tensor, qkv_w: Tensor, qkv_b: Tensor, proj_w: Tenso
              ph: int, pw: int, nh: int, shift: int) -> Tensor:
     _chk(z, ctx, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, ln_w, ln_b)
     a = torch.empty_like(z)
-    _cabi.check(_cabi.lib().b200mar_attn_fwd(
-        _p(z), _p(ctx), _p(qkv_w), _p(qkv_b), _p(proj_w), _p(proj_b), _p(logit_scale),
-        _p(bias_table), _p(ln_w), _p(ln_b), _p(a), z.shape[0], ph, pw, nh, shift, _stream()),
-        "b200mar_attn_fwd")
+    _call("attn_fwd", _p(z), _p(ctx), _p(qkv_w), _p(qkv_b), _p(proj_w), _p(proj_b), _p(logit_scale),
+        _p(bias_table), _p(ln_w), _p(ln_b), _p(a), z.shape[0], ph, pw, nh, shift, _stream())
     return a
 
 
@@ -120,9 +148,8 @@ def attn_bwd(z: Tensor, ctx: Tensor, da: Tensor, params: List[Tensor], dz: Tenso
              grads: List[Tensor], ph: int, pw: int, nh: int, shift: int) -> None:
     """params/grads order: qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, ln_w, ln_b"""
     _chk(z, ctx, da, dz, dctx, *params, *grads)
-    _cabi.check(_cabi.lib().b200mar_attn_bwd(
-        _p(z), _p(ctx), _p(da), *[_p(t) for t in params], _p(dz), _p(dctx),
-        *[_p(t) for t in grads], z.shape[0], ph, pw, nh, shift, _stream()), "b200mar_attn_bwd")
+    _call("attn_bwd", _p(z), _p(ctx), _p(da), *[_p(t) for t in params], _p(dz), _p(dctx),
+        *[_p(t) for t in grads], z.shape[0], ph, pw, nh, shift, _stream())
 
 
 # ------------------------------------------------------------------------------ MLP + LN2 + residual
@@ -134,9 +161,8 @@ def mlp_fwd(a: Tensor, z: Optional[Tensor], fc1_w: Tensor, fc1_b: Tensor, fc2_w:
     out = torch.empty_like(a) if want_out else a.new_empty(0)
     zsum = torch.empty_like(a) if want_zsum else a.new_empty(0)
     n_tok = a.numel() // 64
-    _cabi.check(_cabi.lib().b200mar_mlp_fwd(
-        _p(a), _p(z), _p(fc1_w), _p(fc1_b), _p(fc2_w), _p(fc2_b), _p(ln_w), _p(ln_b), _p(out),
-        _p(zsum), n_tok, _stream()), "b200mar_mlp_fwd")
+    _call("mlp_fwd", _p(a), _p(z), _p(fc1_w), _p(fc1_b), _p(fc2_w), _p(fc2_b), _p(ln_w), _p(ln_b), _p(out),
+        _p(zsum), n_tok, _stream())
     return out, zsum
 
 
@@ -150,9 +176,8 @@ def _(a, z, fc1_w, fc1_b, fc2_w, fc2_b, ln_w, ln_b, want_out, want_zsum):
 def mlp_bwd(a: Tensor, dout: Tensor, params: List[Tensor], da: Tensor, grads: List[Tensor]) -> None:
     """params/grads order: fc1_w, fc1_b, fc2_w, fc2_b, ln_w, ln_b"""
     _chk(a, dout, da, *params, *grads)
-    _cabi.check(_cabi.lib().b200mar_mlp_bwd(
-        _p(a), _p(dout), *[_p(t) for t in params], _p(da), *[_p(t) for t in grads],
-        a.numel() // 64, _stream()), "b200mar_mlp_bwd")
+    _call("mlp_bwd", _p(a), _p(dout), *[_p(t) for t in params], _p(da), *[_p(t) for t in grads],
+        a.numel() // 64, _stream())
 
 
 # ------------------------------------------------------------------------------ patch merging
@@ -162,8 +187,8 @@ def patch_merge_fwd(x: Tensor, ln_w: Tensor, ln_b: Tensor, red_w: Tensor, ph: in
     _chk(x, ln_w, ln_b, red_w)
     B = x.shape[0]
     y = torch.empty((B, (ph // 2) * (pw // 2), 64), device=x.device, dtype=torch.float32)
-    _cabi.check(_cabi.lib().b200mar_patch_merge_fwd(_p(x), _p(ln_w), _p(ln_b), _p(red_w), _p(y),
-                                                    B, ph, pw, _stream()), "b200mar_patch_merge_fwd")
+    _call("patch_merge_fwd", _p(x), _p(ln_w), _p(ln_b), _p(red_w), _p(y),
+                                                    B, ph, pw, _stream())
     return y
 
 
@@ -177,9 +202,8 @@ def patch_merge_bwd(x: Tensor, dy: Tensor, params: List[Tensor], dx: Tensor, gra
                     ph: int, pw: int) -> None:
     """params/grads order: ln_w, ln_b, red_w"""
     _chk(x, dy, dx, *params, *grads)
-    _cabi.check(_cabi.lib().b200mar_patch_merge_bwd(
-        _p(x), _p(dy), *[_p(t) for t in params], _p(dx), *[_p(t) for t in grads],
-        x.shape[0], ph, pw, _stream()), "b200mar_patch_merge_bwd")
+    _call("patch_merge_bwd", _p(x), _p(dy), *[_p(t) for t in params], _p(dx), *[_p(t) for t in grads],
+        x.shape[0], ph, pw, _stream())
 
 
 # ------------------------------------------------------------------------------ pixel shuffle + cat
@@ -188,8 +212,8 @@ def pixel_shuffle_cat(x0: Tensor, x1: Tensor, x2: Tensor, H: int, W: int) -> Ten
     _chk(x0, x1, x2)
     B = x0.shape[0]
     cat = torch.empty((B, H * W, 84), device=x0.device, dtype=torch.float32)
-    _cabi.check(_cabi.lib().b200mar_pixel_shuffle_cat(_p(x0), _p(x1), _p(x2), _p(cat), B, H, W, 0,
-                                                      _stream()), "b200mar_pixel_shuffle_cat")
+    _call("pixel_shuffle_cat", _p(x0), _p(x1), _p(x2), _p(cat), B, H, W, 0,
+                                                      _stream())
     return cat
 
 
@@ -205,8 +229,8 @@ def pixel_shuffle_cat_bwd(dcat: Tensor, H: int, W: int) -> Tuple[Tensor, Tensor,
     d0 = torch.empty((B, H * W, 64), device=dcat.device, dtype=torch.float32)
     d1 = torch.empty((B, H * W // 4, 64), device=dcat.device, dtype=torch.float32)
     d2 = torch.empty((B, H * W // 16, 64), device=dcat.device, dtype=torch.float32)
-    _cabi.check(_cabi.lib().b200mar_pixel_shuffle_cat(_p(d0), _p(d1), _p(d2), _p(dcat), B, H, W, 1,
-                                                      _stream()), "b200mar_pixel_shuffle_cat(inv)")
+    _call("pixel_shuffle_cat", _p(d0), _p(d1), _p(d2), _p(dcat), B, H, W, 1,
+                                                      _stream())
     return d0, d1, d2
 
 
@@ -222,21 +246,20 @@ def partition_index(B: int, ph: int, pw: int, shift: int, device) -> Tuple[Tenso
     n = B * (ph // 8) * (pw // 8)
     tok = torch.empty((n, 64), dtype=torch.int64, device=device)
     cwin = torch.empty((n, 64), dtype=torch.int64, device=device)
-    _cabi.check(_cabi.lib().b200mar_partition_index(tok.data_ptr(), cwin.data_ptr(), B, ph, pw,
-                                                    shift, _stream()), "b200mar_partition_index")
+    _call("partition_index", tok.data_ptr(), cwin.data_ptr(), B, ph, pw,
+                                                    shift, _stream())
     return tok, cwin
 
 
 def shift_mask(ph: int, pw: int, shift: int, device) -> Tensor:
     m = torch.empty(((ph // 8) * (pw // 8), 64, 64), dtype=torch.float32, device=device)
-    _cabi.check(_cabi.lib().b200mar_shift_mask(m.data_ptr(), ph, pw, shift, _stream()),
-                "b200mar_shift_mask")
+    _call("shift_mask", m.data_ptr(), ph, pw, shift, _stream())
     return m
 
 
 def rel_index(device) -> Tensor:
     r = torch.empty((64, 64), dtype=torch.int64, device=device)
-    _cabi.check(_cabi.lib().b200mar_rel_index(r.data_ptr(), _stream()), "b200mar_rel_index")
+    _call("rel_index", r.data_ptr(), _stream())
     return r
 
 
