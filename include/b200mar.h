@@ -106,6 +106,21 @@ int b200mar_mlp_fwd(const float* a, const float* z,
                     const float* fc2_w /*[64,128]*/, const float* fc2_b /*[64]*/,
                     const float* ln_w, const float* ln_b,
                     float* out, float* zsum, long long n_tok, void* stream);
+/* Same contract as b200mar_mlp_fwd, computed on the tcgen05 tensor cores (kind::tf32 operands,
+ * fp32 accumulate in TMEM): 128-token tiles, two workers per persistent CTA.                */
+int b200mar_mlp_tc_fwd(const float* a, const float* z,
+                       const float* fc1_w, const float* fc1_b,
+                       const float* fc2_w, const float* fc2_b,
+                       const float* ln_w, const float* ln_b,
+                       float* out, float* zsum, long long n_tok, void* stream);
+/* 1 if a tensor-core kernel of this process ever timed out on an mbarrier (every wait is
+ * bounded so a descriptor bug cannot hang the device); 0 otherwise; -1 on a CUDA error.     */
+int b200mar_tc_error(void);
+/* Test hook: one 128xN tcgen05 tile product D = A*B^T (mode 0, B [N,K] K-major), D = A*B
+ * (mode 1, B [K,N] MN-major) or the same with A staged in TMEM (mode 2); accumulator placed at
+ * TMEM column col0.  A [128,K], D [128,N] row-major device buffers; N%16==0, K%8==0.        */
+int b200mar_tc_probe(const float* A, const float* B, float* D, int N, int K, int mode, int col0,
+                     void* stream);
 /* da = dout + d(MLP branch) (overwrites da); parameter gradients accumulated.             */
 int b200mar_mlp_bwd(const float* a, const float* dout,
                     const float* fc1_w, const float* fc1_b,

@@ -172,6 +172,31 @@ def _(a, z, fc1_w, fc1_b, fc2_w, fc2_b, ln_w, ln_b, want_out, want_zsum):
             torch.empty_like(a) if want_zsum else a.new_empty(0))
 
 
+@torch.library.custom_op(f"{_NS}::mlp_tc_fwd", mutates_args=())
+def mlp_tc_fwd(a: Tensor, z: Optional[Tensor], fc1_w: Tensor, fc1_b: Tensor, fc2_w: Tensor,
+               fc2_b: Tensor, ln_w: Tensor, ln_b: Tensor, want_out: bool,
+               want_zsum: bool) -> Tuple[Tensor, Tensor]:
+    """mlp_fwd on the tcgen05 tensor cores (TF32 operands, fp32 accumulate in TMEM)."""
+    _chk(a, z, fc1_w, fc1_b, fc2_w, fc2_b, ln_w, ln_b)
+    out = torch.empty_like(a) if want_out else a.new_empty(0)
+    zsum = torch.empty_like(a) if want_zsum else a.new_empty(0)
+    _call("mlp_tc_fwd", _p(a), _p(z), _p(fc1_w), _p(fc1_b), _p(fc2_w), _p(fc2_b), _p(ln_w), _p(ln_b),
+          _p(out), _p(zsum), a.numel() // 64, _stream())
+    return out, zsum
+
+
+@mlp_tc_fwd.register_fake
+def _(a, z, fc1_w, fc1_b, fc2_w, fc2_b, ln_w, ln_b, want_out, want_zsum):
+    return (torch.empty_like(a) if want_out else a.new_empty(0),
+            torch.empty_like(a) if want_zsum else a.new_empty(0))
+
+
+def tc_error() -> int:
+    """Non-zero if a tensor-core kernel hit its bounded mbarrier wait (a bug, never expected)."""
+    torch.cuda.synchronize()
+    return _cabi.lib().b200mar_tc_error()
+
+
 @torch.library.custom_op(f"{_NS}::mlp_bwd", mutates_args=("da", "grads"))
 def mlp_bwd(a: Tensor, dout: Tensor, params: List[Tensor], da: Tensor, grads: List[Tensor]) -> None:
     """params/grads order: fc1_w, fc1_b, fc2_w, fc2_b, ln_w, ln_b"""
