@@ -85,6 +85,15 @@ int b200mar_attn_fwd(const float* z, const float* ctx,
                      const float* logit_scale /*[nh]*/, const float* bias_table /*[225,nh]*/,
                      const float* ln_w /*[64]*/, const float* ln_b /*[64]*/,
                      float* a, int B, int ph, int pw, int nh, int shift, void* stream);
+/* Same contract as b200mar_attn_fwd, computed on the tcgen05 tensor cores (kind::tf32 operands,
+ * fp32 accumulate in TMEM): two windows (128 tokens) per tile, two workers per persistent CTA;
+ * q/k are normalised in fp32 before the down-conversion, softmax / LayerNorm / residual in fp32. */
+int b200mar_attn_tc_fwd(const float* z, const float* ctx,
+                        const float* qkv_w, const float* qkv_b,
+                        const float* proj_w, const float* proj_b,
+                        const float* logit_scale, const float* bias_table,
+                        const float* ln_w, const float* ln_b,
+                        float* a, int B, int ph, int pw, int nh, int shift, void* stream);
 /* dz = da + scatter(dX) (overwrites dz); dctx += per-source-window sums of dX (dctx must be
  * zeroed by the caller); parameter gradients are accumulated.                              */
 int b200mar_attn_bwd(const float* z, const float* ctx, const float* da,

@@ -31,6 +31,15 @@ def T():
     return pkg
 
 
+@pytest.fixture(autouse=True)
+def fp32_kernels(T):
+    """This module pins the fp32 (FMA-pipe) kernels to their tight tolerances; the tcgen05 TF32
+    kernels have their own parity tests in tests/test_gpu_tf32.py."""
+    old = T.ops.set_precision("fp32")
+    yield
+    T.ops.set_precision(old)
+
+
 def dev(sd, dtype=torch.float32):
     return {k: (v.to("cuda", dtype) if v.is_floating_point() else v.cuda()) for k, v in sd.items()}
 

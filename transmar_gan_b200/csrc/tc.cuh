@@ -12,6 +12,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include "tc_ldst.cuh"
 
 namespace b200mar {
 
@@ -105,6 +106,36 @@ __device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64
       "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
       ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
+// same, with the A operand (128 lanes x 8 fp32 columns per K step) read from TMEM
+__device__ __forceinline__ void mma_tf32_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc,
+                                            uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+// K-major operand pair with explicit k-chunk strides (bytes between successive 16-byte k-chunks):
+// K/8 MMAs, D (+)= A[128 x K] * B[N x K]^T.
+__device__ __forceinline__ void mma_ss_tf32(uint32_t tmem_d, uint32_t a_saddr, uint32_t lboA,
+                                            uint32_t b_saddr, uint32_t lboB, int K, uint32_t idesc,
+                                            bool accumulate_first) {
+#pragma unroll
+  for (int k = 0; k < K; k += 8) {
+    const uint64_t ad = smem_desc(a_saddr + (k >> 2) * lboA, lboA, 128);
+    const uint64_t bd = smem_desc(b_saddr + (k >> 2) * lboB, lboB, 128);
+    mma_tf32(tmem_d, ad, bd, idesc, (k > 0 || accumulate_first) ? 1u : 0u);
+  }
+}
+// A from TMEM columns [tmem_a, tmem_a + K), B K-major in shared memory
+__device__ __forceinline__ void mma_ts_tf32(uint32_t tmem_d, uint32_t tmem_a, uint32_t b_saddr,
+                                            uint32_t lboB, int K, uint32_t idesc, bool accumulate_first) {
+#pragma unroll
+  for (int k = 0; k < K; k += 8) {
+    const uint64_t bd = smem_desc(b_saddr + (k >> 2) * lboB, lboB, 128);
+    mma_tf32_ts(tmem_d, tmem_a + k, bd, idesc, (k > 0 || accumulate_first) ? 1u : 0u);
+  }
+}
 // Full-K product over a chunk-major operand pair: K/8 MMAs, each advancing both start
 // addresses by two 16-byte k-chunks (2*LBO).  rowsA/rowsB = tile heights (LBO = rows*16).
 __device__ __forceinline__ void mma_tile_tf32(uint32_t tmem_d, uint32_t a_saddr, int rowsA,
@@ -139,6 +170,11 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
       : "memory");
 #pragma unroll
   for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
 }
 // named barrier for one 128-thread worker (ids 1..15; 0 is __syncthreads)
 __device__ __forceinline__ void worker_sync(int id) {

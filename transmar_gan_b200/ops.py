@@ -9,6 +9,7 @@ only so the ops can be traced / captured).
 """
 from __future__ import annotations
 
+import os
 from typing import List, Optional, Tuple
 
 import torch
@@ -17,6 +18,25 @@ from torch import Tensor
 from . import _cabi
 
 _NS = "b200mar"
+
+# Arithmetic of the block GEMMs (qkv, QK^T, PV, proj, fc1, fc2):
+#   "tf32": tcgen05.mma kind::tf32 (10-bit-mantissa operands, fp32 accumulate in TMEM) — the fast path;
+#   "fp32": the fp32 FMA-pipe kernels (bit-for-bit fp32 operands), kept as the precision reference.
+# Both are sm_100a CUDA kernels of this library; neither is a fallback for the other.
+_PRECISION = os.environ.get("B200MAR_PRECISION", "tf32")
+
+
+def set_precision(mode: str) -> str:
+    """Select "tf32" (tensor cores) or "fp32" (FMA pipe) for the block kernels; returns the old mode."""
+    global _PRECISION
+    if mode not in ("tf32", "fp32"):
+        raise ValueError("precision must be 'tf32' or 'fp32'")
+    old, _PRECISION = _PRECISION, mode
+    return old
+
+
+def get_precision() -> str:
+    return _PRECISION
 
 
 def _stream() -> int:
@@ -139,6 +159,23 @@ def attn_fwd(z: Tensor, ctx: Tensor, qkv_w: Tensor, qkv_b: Tensor, proj_w: Tenso
 
 
 @attn_fwd.register_fake
+def _(z, ctx, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, ln_w, ln_b, ph, pw, nh, shift):
+    return torch.empty_like(z)
+
+
+@torch.library.custom_op(f"{_NS}::attn_tc_fwd", mutates_args=())
+def attn_tc_fwd(z: Tensor, ctx: Tensor, qkv_w: Tensor, qkv_b: Tensor, proj_w: Tensor, proj_b: Tensor,
+                logit_scale: Tensor, bias_table: Tensor, ln_w: Tensor, ln_b: Tensor,
+                ph: int, pw: int, nh: int, shift: int) -> Tensor:
+    """attn_fwd on the tcgen05 tensor cores (TF32 operands, fp32 accumulate in TMEM)."""
+    _chk(z, ctx, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, ln_w, ln_b)
+    a = torch.empty_like(z)
+    _call("attn_tc_fwd", _p(z), _p(ctx), _p(qkv_w), _p(qkv_b), _p(proj_w), _p(proj_b), _p(logit_scale),
+          _p(bias_table), _p(ln_w), _p(ln_b), _p(a), z.shape[0], ph, pw, nh, shift, _stream())
+    return a
+
+
+@attn_tc_fwd.register_fake
 def _(z, ctx, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, ln_w, ln_b, ph, pw, nh, shift):
     return torch.empty_like(z)
 
@@ -323,9 +360,11 @@ class NSTBFunction(torch.autograd.Function):
         P = [p.detach() for p in params]
         u = unigram_fwd(z, P[0], P[1], ph, pw)
         c = ngram_ctx_fwd(u, P[2], P[3], P[4], P[5], P[6], P[7], P[8], P[9], nh)
-        a = attn_fwd(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw, nh, shift)
-        out, zsum = mlp_fwd(a, z if want_zsum else None, P[18], P[19], P[20], P[21], P[22], P[23],
-                            want_out, want_zsum)
+        tc = _PRECISION == "tf32"
+        a = (attn_tc_fwd if tc else attn_fwd)(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16],
+                                              P[17], ph, pw, nh, shift)
+        out, zsum = (mlp_tc_fwd if tc else mlp_fwd)(a, z if want_zsum else None, P[18], P[19], P[20],
+                                                    P[21], P[22], P[23], want_out, want_zsum)
         ctx_.save_for_backward(z, u, c, a, *params)
         ctx_.geom = (ph, pw, nh, shift)
         ctx_.mark_non_differentiable(*([] if want_out else [out]), *([] if want_zsum else [zsum]))
