@@ -7,14 +7,16 @@
 // Per tile:
 //   gather X = z + ctx (cyclic shift folded into the address math)            -> smem A operand
 //   for each head h (QKV of head h+1 is issued while head h is in its epilogue):
-//     [q_h|k_h|v_h] = X * Wqkv[h]^T        3 MMAs 128x16x64 -> TMEM (double-buffered)
+//     [q_h|k_h|v_h] = X * Wqkv[h]^T        1 MMA 128x48x64 -> TMEM (double-buffered); the weight
+//                                           tile is re-packed per head as [q16|k16|v16] rows
 //     row-wise: +bias, F.normalize(q), F.normalize(k), q *= exp(min(logit_scale,ln100))*log2e
 //               -> smem operands Q_h, K_h (K-major) and V_h^T (K-major, padded chunk stride)
 //     S = Q_h K_h^T                         1 MMA 128x128x16 (both windows; the off-diagonal
 //                                           64x64 blocks are never read)
 //     row-wise: + relative-position bias (smem gather) + analytic shift mask, max, ex2, sum;
 //               unnormalised P written back to TMEM over S (tcgen05.st)
-//     O_h = P V_h                           2 MMAs 128x16x64, A operand = P from TMEM
+//     O_h = P [V_h(w0) | V_h(w1)]           1 MMA 128x32x64, A operand = P from TMEM; each row
+//                                           keeps the 16 columns of its own window
 //   Y = O Wp^T (1 MMA 128x64x64), +bias, LayerNorm (a whole row per thread), + z, scatter.
 // While one worker runs a CUDA-core epilogue the other owns the tensor pipe / load path.
 //
@@ -29,13 +31,15 @@ namespace b200mar {
 B200MAR_DEFINE_TC_ERROR_GETTER(tc_error_attn)
 
 constexpr float kLog2e = 1.4426950408889634f;
-constexpr int kVLd = 68;                       // floats between successive 16-byte key-chunks of V^T
+constexpr int kVLd = 132;                      // floats between successive 16-byte key-chunks of V^T
+                                               // (32 rows x 4 + 4: == 4 mod 32, conflict-free scalar stores)
 
 struct AttnTcSmem {                            // float offsets
-  static constexpr int oWqkv = 0;              // [192 rows][64 k] chunk-major (R = 192)
-  static constexpr int oWp = oWqkv + 192 * 64; // [64 rows][64 k]  chunk-major (R = 64)
+  static constexpr int kWRows = 288;           // 6 heads x [q16 | k16 | v16] (4 heads: 192 used)
+  static constexpr int oWqkv = 0;              // [288 rows][64 k] chunk-major (R = 288), per-head packed
+  static constexpr int oWp = oWqkv + kWRows * 64; // [64 rows][64 k]  chunk-major (R = 64)
   static constexpr int oBqkv = oWp + 64 * 64;
-  static constexpr int oBp = oBqkv + 192;
+  static constexpr int oBp = oBqkv + kWRows;
   static constexpr int oLnW = oBp + 64;
   static constexpr int oLnB = oLnW + 64;
   static constexpr int oScale = oLnB + 64;
@@ -46,8 +50,8 @@ struct AttnTcSmem {                            // float offsets
   static constexpr int wX = 0;                 // [128][64] chunk-major (R = 128): X, then O, then LN out
   static constexpr int wQ = wX + 128 * 64;     // [128][16] chunk-major
   static constexpr int wK = wQ + 128 * 16;     // [128][16] chunk-major
-  static constexpr int wV = wK + 128 * 16;     // 2 windows x V^T [16 d][64 keys], chunk stride kVLd
-  static constexpr int wTok = wV + 2 * 16 * kVLd;
+  static constexpr int wV = wK + 128 * 16;     // [V^T(w0) 16 d | V^T(w1) 16 d][64 keys], chunk stride kVLd
+  static constexpr int wTok = wV + 16 * kVLd;
   static constexpr int kWorkFloats = wTok + 3 * 128;
   static constexpr int kFloats = oWork + 2 * kWorkFloats;
   static_assert(oWork % 32 == 0 && kWorkFloats % 32 == 0, "128-byte aligned worker blocks");
@@ -57,7 +61,7 @@ struct AttnTcSmem {                            // float offsets
 // TMEM columns of one worker (256 of the CTA's 512)
 constexpr uint32_t kTQ = 0;      // 2 x 48: [q_h | k_h | v_h] accumulators, double-buffered over heads
 constexpr uint32_t kTS = 96;     // 128: S = Q K^T (both windows); P overwrites columns [0,64); Y at the end
-constexpr uint32_t kTO = 224;    // 2 x 16: O_h of window 0 / window 1
+constexpr uint32_t kTO = 224;    // 32: O_h, columns [0,16) from window 0's V, [16,32) from window 1's
 
 template <int NH>
 __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
@@ -74,7 +78,11 @@ __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
   float* sBias = smem + L::oBias;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::oBar);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L::oBar + 16);
-  const int tid = threadIdx.x, wk = tid >> 7, t = tid & 127, lane = tid & 31, wq = (tid >> 5) & 3;
+  const int tid = threadIdx.x, lane = tid & 31;
+  // warp-uniform ids (broadcast from lane 0 so that everything derived from them - smem / TMEM
+  // addresses, MMA descriptors - stays in uniform registers)
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  const int wk = warp >> 2, wq = warp & 3;
   float* sW = smem + L::oWork + wk * L::kWorkFloats;
   float* sX = sW + L::wX;
   float* sQ = sW + L::wQ;
@@ -88,11 +96,13 @@ __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
   uint64_t* barO = barQ + 3;
 
   // ---- stage the block's weights as K-major chunk-major operands (once per CTA)
-  for (int idx = tid; idx < 192 * 16; idx += 256) {
-    const int n = idx % 192, kc = idx / 192;
+  for (int idx = tid; idx < L::kWRows * 16; idx += 256) {
+    const int n = idx % L::kWRows, kc = idx / L::kWRows;      // packed row n = h*48 + part*16 + d
+    const int h = n / 48, part = (n % 48) >> 4, d = n & 15;
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (n < 3 * A) v = *reinterpret_cast<const float4*>(p.qkv_w + n * 64 + kc * 4);
-    *reinterpret_cast<float4*>(sWqkv + kc * (192 * 4) + n * 4) = v;
+    if (h < NH && d < HD)
+      v = *reinterpret_cast<const float4*>(p.qkv_w + (part * A + h * HD + d) * 64 + kc * 4);
+    *reinterpret_cast<float4*>(sWqkv + kc * (L::kWRows * 4) + n * 4) = v;
   }
   for (int idx = tid; idx < 64 * 16; idx += 256) {
     const int n = idx & 63, kc = idx >> 6;
@@ -100,13 +110,17 @@ __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
     if (kc * 4 < A) v = *reinterpret_cast<const float4*>(p.proj_w + n * A + kc * 4);
     *reinterpret_cast<float4*>(sWp + kc * 256 + n * 4) = v;
   }
-  if (tid < 192) sBqkv[tid] = tid < 3 * A ? p.qkv_b[tid] : 0.f;
+  for (int n = tid; n < L::kWRows; n += 256) {                 // bias in the same packed order
+    const int h = n / 48, part = (n % 48) >> 4, d = n & 15;
+    sBqkv[n] = (h < NH && d < HD) ? p.qkv_b[part * A + h * HD + d] : 0.f;
+  }
   if (tid < 64) { sBp[tid] = p.proj_b[tid]; sLnW[tid] = p.ln_w[tid]; sLnB[tid] = p.ln_b[tid]; }
   if (tid < NH) sScale[tid] = expf(fminf(p.logit_scale[tid], kLogitMax)) * kLog2e;
   for (int i = tid; i < NH * 225; i += 256) {
     const int h = i / 225, e = i - h * 225;
     sBias[h * 228 + e] = p.bias_table[e * NH + h] * kLog2e;
   }
+  for (int i = tid; i < 2 * L::kWorkFloats; i += 256) smem[L::oWork + i] = 0.f;
   if (tid == 0) {
     for (int i = 0; i < 8; ++i) tc::mbar_init(bars + i, 1);
     tc::fence_barrier_init();
@@ -121,9 +135,9 @@ __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
   const uint32_t lane_addr = (uint32_t)(wq * 32) << 16;
   const uint32_t xS = tc::smem_u32(sX), qS = tc::smem_u32(sQ), kS = tc::smem_u32(sK), vS = tc::smem_u32(sV);
   const uint32_t wqkvS = tc::smem_u32(sWqkv), wpS = tc::smem_u32(sWp);
-  constexpr uint32_t kI16 = tc::idesc_tf32(128, 16), kI64 = tc::idesc_tf32(128, 64),
-                     kI128 = tc::idesc_tf32(128, 128);
-  uint32_t phQ0 = 0, phQ1 = 0, phS = 0, phO = 0;
+  constexpr uint32_t kI32 = tc::idesc_tf32(128, 32), kI48 = tc::idesc_tf32(128, 48),
+                     kI64 = tc::idesc_tf32(128, 64), kI128 = tc::idesc_tf32(128, 128);
+  uint32_t phQ = 0, phS = 0, phO = 0;
 
   const Geom g = make_geom(p.B, p.ph, p.pw, p.shift);
   const int nwin = g.B * g.wh * g.ww;
@@ -132,12 +146,17 @@ __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
   const int wsel = row >> 6, lrow = row & 63;     // window of the pair, token inside the window
   const int bias_base = ((lrow >> 3) * 15 + (lrow & 7)) + 112;   // rel_index(r, c) = bias_base - (15 ci + cj)
 
+  // operand descriptors are built once; a K step of 8 advances the start-address field (>>4) by
+  // two k-chunks
+  const uint64_t dX = tc::smem_desc(xS, 2048, 128), dWqkv = tc::smem_desc(wqkvS, L::kWRows * 16, 128),
+                 dQ = tc::smem_desc(qS, 2048, 128), dK = tc::smem_desc(kS, 2048, 128),
+                 dV = tc::smem_desc(vS, kVLd * 4, 128), dWp = tc::smem_desc(wpS, 1024, 128);
   // [q_h | k_h | v_h] = X * Wqkv[rows of head h]^T -> TMEM buffer `buf` (issued by one thread)
   auto issue_qkv = [&](int h, int buf) {
+    const uint64_t db = dWqkv + (uint64_t)(h * 48);
 #pragma unroll
-    for (int part = 0; part < 3; ++part)
-      tc::mma_ss_tf32(tbase + kTQ + buf * 48 + part * 16, xS, 2048,
-                      wqkvS + (part * A + h * HD) * 16, 192 * 16, 64, kI16, false);
+    for (int ks = 0; ks < 8; ++ks)
+      tc::mma_tf32(tbase + kTQ + buf * 48, dX + ks * 256, db + ks * (2 * L::kWRows), kI48, ks > 0);
   };
 
   for (int tile = blockIdx.x * 2 + wk; tile < ntile; tile += gridDim.x * 2) {
@@ -155,17 +174,22 @@ __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
     // ---- gather X = z + ctx: coalesced 64-byte segments -> conflict-free 16-byte slots
     {
       const int q = lane >> 3, m8 = lane & 7;
+      float4 zv[16], cv[16];
+#pragma unroll
+      for (int it = 0; it < 16; ++it) {                    // all 32 loads in flight before any use
+        const int m = wq * 32 + (it >> 2) * 8 + m8, kc = (it & 3) * 4 + q;
+        const int tok = sTok[m];
+        zv[it] = cv[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (tok >= 0) {
+          zv[it] = __ldg(reinterpret_cast<const float4*>(p.z + (size_t)tok * 64 + kc * 4));
+          cv[it] = __ldg(reinterpret_cast<const float4*>(p.ctx + (size_t)sCwin[m] * 64 + kc * 4));
+        }
+      }
 #pragma unroll
       for (int it = 0; it < 16; ++it) {
         const int m = wq * 32 + (it >> 2) * 8 + m8, kc = (it & 3) * 4 + q;
-        const int tok = sTok[m];
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (tok >= 0) {
-          const float4 zv = *reinterpret_cast<const float4*>(p.z + (size_t)tok * 64 + kc * 4);
-          const float4 cv = *reinterpret_cast<const float4*>(p.ctx + (size_t)sCwin[m] * 64 + kc * 4);
-          v = make_float4(zv.x + cv.x, zv.y + cv.y, zv.z + cv.z, zv.w + cv.w);
-        }
-        *reinterpret_cast<float4*>(sX + kc * 512 + m * 4) = v;
+        *reinterpret_cast<float4*>(sX + kc * 512 + m * 4) =
+            make_float4(zv[it].x + cv[it].x, zv[it].y + cv[it].y, zv[it].z + cv[it].z, zv[it].w + cv[it].w);
       }
     }
     // ---- shift mask of this row as a 64-bit key set (analytic 9-region rule)
@@ -181,46 +205,44 @@ __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
     }
     tc::fence_async_smem();
     tc::worker_sync(1 + wk);
-    if (t == 0) {
+    if (wq == 0) {                                   // warp-uniform: one elected lane issues
       tc::tc_fence_after();
-      issue_qkv(0, 0);
-      tc::mma_commit(barQ);
+      if (tc::elect_one()) { issue_qkv(0, 0); tc::mma_commit(barQ); }
+      __syncwarp();
     }
 
+    // per-head attention outputs of this row; indexed by the (rolled) head loop, so the array
+    // lives in local memory: 10-16 stores per head, one 64-float read-back per tile
     float o[64];
 #pragma unroll
     for (int i = 0; i < 64; ++i) o[i] = 0.f;
     float inv_prev = 0.f;
 
-#pragma unroll
+#pragma unroll 1
     for (int h = 0; h < NH; ++h) {
       const int buf = h & 1;
       // ---- wait for [q|k|v]_h, start head h+1's projection behind it
-      if (buf == 0) { tc::mbar_wait(barQ, phQ0, &g_tc_error); phQ0 ^= 1; }
-      else          { tc::mbar_wait(barQ + 1, phQ1, &g_tc_error); phQ1 ^= 1; }
+      tc::mbar_wait(barQ + buf, (phQ >> buf) & 1u, &g_tc_error);
+      phQ ^= 1u << buf;
       tc::tc_fence_after();
-      if (h + 1 < NH && t == 0) {
-        issue_qkv(h + 1, buf ^ 1);
-        tc::mma_commit(barQ + (buf ^ 1));
-      }
       float qkv[48];
       tc::tmem_ld48(tbase + lane_addr + kTQ + buf * 48, qkv);
       float qs = 0.f, ks = 0.f;
+      {
+        const float* b = sBqkv + h * 48;               // packed [q16 | k16 | v16]; pad rows are exact zeros
 #pragma unroll
-      for (int d = 0; d < HD; ++d) {
-        qkv[d] += sBqkv[h * HD + d];
-        qkv[16 + d] += sBqkv[A + h * HD + d];
-        qkv[32 + d] += sBqkv[2 * A + h * HD + d];
-        qs = fmaf(qkv[d], qkv[d], qs);
-        ks = fmaf(qkv[16 + d], qkv[16 + d], ks);
+        for (int d = 0; d < HD; ++d) {
+          qkv[d] += b[d];
+          qkv[16 + d] += b[16 + d];
+          qkv[32 + d] += b[32 + d];
+          qs = fmaf(qkv[d], qkv[d], qs);
+          ks = fmaf(qkv[16 + d], qkv[16 + d], ks);
+        }
       }
       const float qmul = sScale[h] / fmaxf(sqrtf(qs), kNormEps);
       const float kmul = 1.0f / fmaxf(sqrtf(ks), kNormEps);
 #pragma unroll
-      for (int d = 0; d < 16; ++d) {
-        qkv[d] = d < HD ? qkv[d] * qmul : 0.f;
-        qkv[16 + d] = d < HD ? qkv[16 + d] * kmul : 0.f;
-      }
+      for (int d = 0; d < HD; ++d) { qkv[d] *= qmul; qkv[16 + d] *= kmul; }
       // ---- previous head's O (its PV MMAs read P from TMEM and V^T from smem: wait before reuse)
       if (h > 0) {
         tc::mbar_wait(barO, phO, &g_tc_error); phO ^= 1;
@@ -239,17 +261,25 @@ __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
             make_float4(qkv[16 + c * 4], qkv[16 + c * 4 + 1], qkv[16 + c * 4 + 2], qkv[16 + c * 4 + 3]);
       }
       {
-        float* vt = sV + wsel * (16 * kVLd) + (lrow >> 2) * kVLd + (lrow & 3);
+        float* vt = sV + (lrow >> 2) * kVLd + wsel * 64 + (lrow & 3);
 #pragma unroll
         for (int d = 0; d < HD; ++d) vt[d * 4] = qkv[32 + d];
       }
       tc::fence_async_smem();
       tc::tc_fence_before();
       tc::worker_sync(1 + wk);
-      if (t == 0) {
+      if (wq == 0) {
         tc::tc_fence_after();
-        tc::mma_ss_tf32(tbase + kTS, qS, 2048, kS, 2048, 16, kI128, false);
-        tc::mma_commit(barS);
+        if (tc::elect_one()) {
+          tc::mma_tf32(tbase + kTS, dQ, dK, kI128, 0u);
+          tc::mma_tf32(tbase + kTS, dQ + 256, dK + 256, kI128, 1u);
+          tc::mma_commit(barS);
+          if (h + 1 < NH) {                            // next head's projection, in the shadow of S_h
+            issue_qkv(h + 1, buf ^ 1);
+            tc::mma_commit(barQ + (buf ^ 1));
+          }
+        }
+        __syncwarp();
       }
       tc::mbar_wait(barS, phS, &g_tc_error); phS ^= 1;
       tc::tc_fence_after();
@@ -270,20 +300,24 @@ __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
         float mx = s[0];
 #pragma unroll
         for (int c = 1; c < 64; ++c) mx = fmaxf(mx, s[c]);
-        float sum = 0.f;
+        float sum4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-        for (int c = 0; c < 64; ++c) { s[c] = tc::ex2_approx(s[c] - mx); sum += s[c]; }
-        inv_prev = 1.0f / sum;
+        for (int c = 0; c < 64; ++c) { s[c] = tc::ex2_approx(s[c] - mx); sum4[c & 3] += s[c]; }
+        inv_prev = 1.0f / ((sum4[0] + sum4[1]) + (sum4[2] + sum4[3]));
         tc::tmem_st64(tbase + lane_addr + kTS, s);       // unnormalised P over S columns [0,64)
         tc::tmem_wait_st();
       }
       tc::tc_fence_before();
       tc::worker_sync(1 + wk);
-      if (t == 0) {
+      if (wq == 0) {
         tc::tc_fence_after();
-        tc::mma_ts_tf32(tbase + kTO, tbase + kTS, vS, kVLd * 4, 64, kI16, false);
-        tc::mma_ts_tf32(tbase + kTO + 16, tbase + kTS, vS + 16 * kVLd * 4, kVLd * 4, 64, kI16, false);
-        tc::mma_commit(barO);
+        if (tc::elect_one()) {
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)
+            tc::mma_tf32_ts(tbase + kTO, tbase + kTS + ks * 8, dV + ks * (2 * kVLd * 4 / 16), kI32, ks > 0);
+          tc::mma_commit(barO);
+        }
+        __syncwarp();
       }
     }
     // ---- last head's O, then the output projection
@@ -302,10 +336,14 @@ __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
     tc::fence_async_smem();
     tc::tc_fence_before();
     tc::worker_sync(1 + wk);
-    if (t == 0) {
+    if (wq == 0) {
       tc::tc_fence_after();
-      tc::mma_ss_tf32(tbase + kTS, xS, 2048, wpS, 1024, 64, kI64, false);
-      tc::mma_commit(barS);
+      if (tc::elect_one()) {
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) tc::mma_tf32(tbase + kTS, dX + ks * 256, dWp + ks * 128, kI64, ks > 0);
+        tc::mma_commit(barS);
+      }
+      __syncwarp();
     }
     tc::mbar_wait(barS, phS, &g_tc_error); phS ^= 1;
     tc::tc_fence_after();
@@ -334,15 +372,22 @@ __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
     // ---- residual + scatter back to the source token positions (same mapping as the gather)
     {
       const int q = lane >> 3, m8 = lane & 7;
+      float4 zv[16];
+#pragma unroll
+      for (int it = 0; it < 16; ++it) {
+        const int m = wq * 32 + (it >> 2) * 8 + m8, kc = (it & 3) * 4 + q;
+        const int tok = sTok[m];
+        zv[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (tok >= 0) zv[it] = __ldg(reinterpret_cast<const float4*>(p.z + (size_t)tok * 64 + kc * 4));
+      }
 #pragma unroll
       for (int it = 0; it < 16; ++it) {
         const int m = wq * 32 + (it >> 2) * 8 + m8, kc = (it & 3) * 4 + q;
         const int tok = sTok[m];
         if (tok >= 0) {
           const float4 y = *reinterpret_cast<const float4*>(sX + kc * 512 + m * 4);
-          const size_t gi = (size_t)tok * 64 + kc * 4;
-          const float4 zv = *reinterpret_cast<const float4*>(p.z + gi);
-          *reinterpret_cast<float4*>(p.a + gi) = make_float4(zv.x + y.x, zv.y + y.y, zv.z + y.z, zv.w + y.w);
+          *reinterpret_cast<float4*>(p.a + (size_t)tok * 64 + kc * 4) =
+              make_float4(zv[it].x + y.x, zv[it].y + y.y, zv[it].z + y.z, zv[it].w + y.w);
         }
       }
     }

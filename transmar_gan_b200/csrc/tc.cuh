@@ -176,6 +176,17 @@ __device__ __forceinline__ float ex2_approx(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+// one lane of a converged warp (the MMA issuer): warp-uniform branch + elect keeps the operands
+// of the following tcgen05.mma in uniform registers (no per-lane waterfall loop)
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
 // named barrier for one 128-thread worker (ids 1..15; 0 is __syncthreads)
 __device__ __forceinline__ void worker_sync(int id) {
   asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory");
