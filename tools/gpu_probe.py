@@ -38,3 +38,20 @@ for variant in (0, 1, 2, 3):
         run(N, K, 1, variant, col0)
 for (N, K, col0) in ((64, 64, 0), (16, 64, 16)):
     run(N, K, 2, 0, col0)
+
+
+def run16(N, K, mode, col0):
+    A = torch.randn(128, K, device="cuda")
+    B = torch.randn(N, K, device="cuda")
+    ref = (A.half().double() @ B.half().double().T).float()
+    D = torch.full((128, N), float("nan"), device="cuda")
+    rc = L.b200mar_tc_probe(A.data_ptr(), B.data_ptr(), D.data_ptr(), N, K, mode, col0,
+                            torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    print(f"f16 mode {mode} N={N:3d} K={K:3d} col0={col0:3d} rc={rc} err={(D - ref).abs().max().item():.2e} "
+          f"tc_error={ops.tc_error()}", flush=True)
+
+
+for mode in (4, 5):
+    for (N, K, col0) in ((64, 64, 0), (48, 64, 48), (64, 32, 96), (32, 128, 16), (32, 64, 0), (128, 128, 8)):
+        run16(N, K, mode, col0)

@@ -1,165 +1,196 @@
 // attn_tc.cu — fused N-gram window partition + scaled-cosine window attention + LN1 + residual,
-// forward, on the 5th-gen tensor cores (tcgen05.mma kind::tf32, fp32 accumulators in TMEM).
+// forward, on the 5th-gen tensor cores with fp32 accumulators in TMEM.  Operand formats:
+//   * kind::f16 with FP16 operands (11-bit significand, the same as TF32, at half the shared-
+//     memory footprint and twice the MMA rate) where the range is under control: X (every row
+//     scaled by a power of two to max|x| in [1,2)), the qkv weights (one power-of-two scale per
+//     matrix), the unit-norm Q and K;
+//   * kind::tf32 where magnitudes are data-dependent and LayerNorm / F.normalize downstream make
+//     RELATIVE precision matter at any scale: P V and the output projection.
+// The residual stream in HBM, q/k normalisation, softmax, LayerNorm and the residual add are fp32.
 //
-// One persistent CTA per SM = two independent 128-thread workers sharing the resident weights
-// (qkv 48 KB + proj 16 KB as chunk-major K-major operands, bias table, LN affine).  A worker
+// One persistent CTA per SM = THREE independent 128-thread workers sharing the resident weights
+// (qkv re-packed per head as [q16|k16|v16] rows, 36 KB; proj 8 KB; bias table; LN affine).  A worker
 // streams tiles of TWO (shifted) windows = 128 tokens; thread t owns token row t = TMEM lane t.
 // Per tile:
-//   gather X = z + ctx (cyclic shift folded into the address math)            -> smem A operand
-//   for each head h (QKV of head h+1 is issued while head h is in its epilogue):
-//     [q_h|k_h|v_h] = X * Wqkv[h]^T        1 MMA 128x48x64 -> TMEM (double-buffered); the weight
-//                                           tile is re-packed per head as [q16|k16|v16] rows
-//     row-wise: +bias, F.normalize(q), F.normalize(k), q *= exp(min(logit_scale,ln100))*log2e
-//               -> smem operands Q_h, K_h (K-major) and V_h^T (K-major, padded chunk stride)
-//     S = Q_h K_h^T                         1 MMA 128x128x16 (both windows; the off-diagonal
-//                                           64x64 blocks are never read)
-//     row-wise: + relative-position bias (smem gather) + analytic shift mask, max, ex2, sum;
-//               unnormalised P written back to TMEM over S (tcgen05.st)
-//     O_h = P [V_h(w0) | V_h(w1)]           1 MMA 128x32x64, A operand = P from TMEM; each row
-//                                           keeps the 16 columns of its own window
-//   Y = O Wp^T (1 MMA 128x64x64), +bias, LayerNorm (a whole row per thread), + z, scatter.
-// While one worker runs a CUDA-core epilogue the other owns the tensor pipe / load path.
+//   gather X = z + ctx (cyclic shift folded into the address math) -> fp16 smem A operand
+//   for each head h (QKV of head h+1 is issued in the shadow of S_h):
+//     [q_h|k_h|v_h] = X * Wqkv[h]^T      4 MMAs 128x48x16 -> TMEM (double-buffered over heads)
+//     row-wise fp32: +bias, F.normalize(q), F.normalize(k), q *= exp(min(logit_scale,ln100))*log2e
+//       -> Q' = [q | 0] / [0 | q] (window 0 / window 1 rows), K' = [k(w0) | k(w1)], so that ONE
+//          128x64x32 MMA gives every row the logits against its own window's 64 keys;
+//          V^T (rows = (window, d), keys contiguous)
+//     S = Q' K'^T                         2 MMAs 128x64x16
+//     row-wise fp32: + relative-position bias (smem gather) + analytic shift mask, max, ex2, sum;
+//       unnormalised P written back to TMEM over S (tcgen05.st)
+//     O_h = P [V_h(w0) | V_h(w1)]         8 MMAs 128x32x8 (tf32), A operand = P from TMEM, written
+//                                         over the dead [q|k|v]_h accumulator columns
+//   Y = O Wp^T (8 MMAs 128x64x8, tf32), +bias, LayerNorm (a whole row per thread), + z, scatter.
+// While one worker runs a CUDA-core epilogue the others own the tensor pipe / load path.
 //
 // Reference semantics: components/window_utils.py:127-147, components/attention.py:70-101,
-// components/transformer_blocks.py:63-112,117 (same contract as attn_fwd.cu, the fp32 SIMT kernel).
+// components/transformer_blocks.py:63-112,117 (same contract as attn_fwd.cu, the fp32 kernel).
 #include "common.cuh"
 #include "attn_common.cuh"
 #include "tc.cuh"
+#include <cuda_fp16.h>
 
 namespace b200mar {
 
 B200MAR_DEFINE_TC_ERROR_GETTER(tc_error_attn)
 
 constexpr float kLog2e = 1.4426950408889634f;
-constexpr int kVLd = 132;                      // floats between successive 16-byte key-chunks of V^T
-                                               // (32 rows x 4 + 4: == 4 mod 32, conflict-free scalar stores)
+constexpr int kWorkers = 3;
+constexpr int kVChunk = 528;                   // bytes between successive 4-key chunks of V^T (fp32):
+                                               // 32 rows x 16 B + 16 (== 4 words mod 32 banks)
 
-struct AttnTcSmem {                            // float offsets
+struct AttnTcSmem {                            // BYTE offsets
   static constexpr int kWRows = 288;           // 6 heads x [q16 | k16 | v16] (4 heads: 192 used)
-  static constexpr int oWqkv = 0;              // [288 rows][64 k] chunk-major (R = 288), per-head packed
-  static constexpr int oWp = oWqkv + kWRows * 64; // [64 rows][64 k]  chunk-major (R = 64)
-  static constexpr int oBqkv = oWp + 64 * 64;
-  static constexpr int oBp = oBqkv + kWRows;
-  static constexpr int oLnW = oBp + 64;
-  static constexpr int oLnB = oLnW + 64;
-  static constexpr int oScale = oLnB + 64;
-  static constexpr int oBias = oScale + 8;     // [6][228], pre-multiplied by log2(e)
-  static constexpr int oBar = oBias + 6 * 228; // 2 workers x 4 mbarriers (uint64) + tmem slot
-  static constexpr int oWork = oBar + 32;
-  // per worker
-  static constexpr int wX = 0;                 // [128][64] chunk-major (R = 128): X, then O, then LN out
-  static constexpr int wQ = wX + 128 * 64;     // [128][16] chunk-major
-  static constexpr int wK = wQ + 128 * 16;     // [128][16] chunk-major
-  static constexpr int wV = wK + 128 * 16;     // [V^T(w0) 16 d | V^T(w1) 16 d][64 keys], chunk stride kVLd
-  static constexpr int wTok = wV + 16 * kVLd;
-  static constexpr int kWorkFloats = wTok + 3 * 128;
-  static constexpr int kFloats = oWork + 2 * kWorkFloats;
-  static_assert(oWork % 32 == 0 && kWorkFloats % 32 == 0, "128-byte aligned worker blocks");
-  static_assert(kFloats * 4 <= 232448, "attn_tc shared memory exceeds 227 KB");
+  static constexpr int oWqkv = 0;              // fp16 [288 rows][64 k], 8-element k-chunks, R = 288
+  static constexpr int oWp = oWqkv + kWRows * 64 * 2;   // fp32 (tf32) [64 rows][64 k], 4-element k-chunks, R = 64
+  static constexpr int oBqkv = oWp + 64 * 64 * 4;       // fp32 [288], packed order
+  static constexpr int oBp = oBqkv + kWRows * 4;
+  static constexpr int oLnW = oBp + 256;
+  static constexpr int oLnB = oLnW + 256;
+  static constexpr int oScale = oLnB + 256;     // [0,6): logit scales, [6]: inverse of the qkv weight scale, [7]: scratch
+  static constexpr int oBias = oScale + 32;    // fp32 [6][228], pre-multiplied by log2(e)
+  static constexpr int oBar = oBias + 6 * 228 * 4;      // 3 workers x 4 mbarriers + tmem slot
+  static constexpr int oWork = ((oBar + 128 + 127) / 128) * 128;
+  // per worker; [X | Q | K | V] is also the 32 KB fp32 staging tile of the LayerNorm output
+  static constexpr int wX = 0;                 // fp16 [128][64] (R = 128): X, later O
+  static constexpr int wQ = wX + 128 * 64 * 2; // fp16 [128][32] (R = 128)
+  static constexpr int wK = wQ + 128 * 32 * 2; // fp16 [64][32]  (R = 64)
+  static constexpr int wV = wK + 64 * 32 * 2;  // fp32 [32 rows = (window, d)][64 keys], chunk stride kVChunk
+  static constexpr int wTok = wV + 16 * kVChunk;
+  static constexpr int kWorkBytes = ((wTok + 4 * 128 * 4 + 127) / 128) * 128;   // tok, cwin, region, row scale
+  static constexpr int kBytes = oWork + kWorkers * kWorkBytes;
+  static_assert(wTok >= 128 * 64 * 4, "fp32 staging tile must fit in [X|Q|K|V]");
+  static_assert(oBar % 8 == 0, "mbarrier alignment");
+  static_assert(kBytes <= 232448, "attn_tc shared memory exceeds 227 KB");
 };
 
-// TMEM columns of one worker (256 of the CTA's 512)
-constexpr uint32_t kTQ = 0;      // 2 x 48: [q_h | k_h | v_h] accumulators, double-buffered over heads
-constexpr uint32_t kTS = 96;     // 128: S = Q K^T (both windows); P overwrites columns [0,64); Y at the end
-constexpr uint32_t kTO = 224;    // 32: O_h, columns [0,16) from window 0's V, [16,32) from window 1's
+// TMEM columns of one worker (3 x 160 of the CTA's 512)
+constexpr uint32_t kTStride = 160;
+constexpr uint32_t kTQ = 0;      // 2 x 48: [q_h | k_h | v_h] accumulators, double-buffered over heads;
+                                 // O_h (32 columns) is written over buffer h&1 once it has been read
+constexpr uint32_t kTS = 96;     // 64: S; P (fp32) overwrites it; Y at the end
 
 template <int NH>
-__global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
+__global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnParams p) {
   using L = AttnTcSmem;
   constexpr int HD = kDim / NH, A = HD * NH;
-  extern __shared__ __align__(128) float smem[];
-  float* sWqkv = smem + L::oWqkv;
-  float* sWp = smem + L::oWp;
-  float* sBqkv = smem + L::oBqkv;
-  float* sBp = smem + L::oBp;
-  float* sLnW = smem + L::oLnW;
-  float* sLnB = smem + L::oLnB;
-  float* sScale = smem + L::oScale;
-  float* sBias = smem + L::oBias;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::oBar);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + L::oBar + 16);
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __half* sWqkv = reinterpret_cast<__half*>(smem_raw + L::oWqkv);
+  float* sWp = reinterpret_cast<float*>(smem_raw + L::oWp);
+  float* sBqkv = reinterpret_cast<float*>(smem_raw + L::oBqkv);
+  float* sBp = reinterpret_cast<float*>(smem_raw + L::oBp);
+  float* sLnW = reinterpret_cast<float*>(smem_raw + L::oLnW);
+  float* sLnB = reinterpret_cast<float*>(smem_raw + L::oLnB);
+  float* sScale = reinterpret_cast<float*>(smem_raw + L::oScale);
+  float* sBias = reinterpret_cast<float*>(smem_raw + L::oBias);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + L::oBar);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem_raw + L::oBar + kWorkers * 32);
   const int tid = threadIdx.x, lane = tid & 31;
   // warp-uniform ids (broadcast from lane 0 so that everything derived from them - smem / TMEM
   // addresses, MMA descriptors - stays in uniform registers)
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
   const int wk = warp >> 2, wq = warp & 3;
-  float* sW = smem + L::oWork + wk * L::kWorkFloats;
-  float* sX = sW + L::wX;
-  float* sQ = sW + L::wQ;
-  float* sK = sW + L::wK;
-  float* sV = sW + L::wV;
+  unsigned char* sW = smem_raw + L::oWork + wk * L::kWorkBytes;
+  unsigned char* sX = sW + L::wX;
+  unsigned char* sQ = sW + L::wQ;
+  unsigned char* sK = sW + L::wK;
+  unsigned char* sV = sW + L::wV;
+  float* sStage = reinterpret_cast<float*>(sW);            // fp32 [128][64] chunk-major, end of tile
   int* sTok = reinterpret_cast<int*>(sW + L::wTok);
   int* sCwin = sTok + 128;
   int* sReg = sCwin + 128;
+  float* sRowInv = reinterpret_cast<float*>(sReg + 128);
   uint64_t* barQ = bars + wk * 4;       // [2]
   uint64_t* barS = barQ + 2;
   uint64_t* barO = barQ + 3;
 
-  // ---- stage the block's weights as K-major chunk-major operands (once per CTA)
-  for (int idx = tid; idx < L::kWRows * 16; idx += 256) {
+  // ---- stage the block's weights as K-major operands (once per CTA).  The qkv matrix is scaled by
+  //      one power of two to max|w| in [1,2) so that fp16 keeps 11 significant bits at any scale.
+  uint32_t* sWmax = reinterpret_cast<uint32_t*>(sScale + 7);
+  if (tid == 0) *sWmax = 0u;
+  __syncthreads();
+  {
+    float m = 0.f;
+    for (int i = tid; i < 3 * A * 64; i += 128 * kWorkers) m = fmaxf(m, fabsf(p.qkv_w[i]));
+    atomicMax(sWmax, __float_as_uint(m));               // non-negative floats order like unsigned ints
+  }
+  __syncthreads();
+  uint32_t we = (*sWmax >> 23) & 0xFFu;
+  we = we < 1u ? 127u : (we > 253u ? 253u : we);
+  const float wsc = __uint_as_float((254u - we) << 23);   // 2^(127-we)
+  for (int idx = tid; idx < L::kWRows * 8; idx += 128 * kWorkers) {
     const int n = idx % L::kWRows, kc = idx / L::kWRows;      // packed row n = h*48 + part*16 + d
     const int h = n / 48, part = (n % 48) >> 4, d = n & 15;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (h < NH && d < HD)
-      v = *reinterpret_cast<const float4*>(p.qkv_w + (part * A + h * HD + d) * 64 + kc * 4);
-    *reinterpret_cast<float4*>(sWqkv + kc * (L::kWRows * 4) + n * 4) = v;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (h < NH && d < HD) {
+      const float4* src = reinterpret_cast<const float4*>(p.qkv_w + (part * A + h * HD + d) * 64 + kc * 8);
+      const float4 a = src[0], b = src[1];
+      v = make_uint4(tc::pack_f16(a.x * wsc, a.y * wsc), tc::pack_f16(a.z * wsc, a.w * wsc),
+                     tc::pack_f16(b.x * wsc, b.y * wsc), tc::pack_f16(b.z * wsc, b.w * wsc));
+    }
+    *reinterpret_cast<uint4*>(sWqkv + (size_t)kc * (L::kWRows * 8) + n * 8) = v;
   }
-  for (int idx = tid; idx < 64 * 16; idx += 256) {
+  for (int idx = tid; idx < 64 * 16; idx += 128 * kWorkers) {
     const int n = idx & 63, kc = idx >> 6;
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
     if (kc * 4 < A) v = *reinterpret_cast<const float4*>(p.proj_w + n * A + kc * 4);
     *reinterpret_cast<float4*>(sWp + kc * 256 + n * 4) = v;
   }
-  for (int n = tid; n < L::kWRows; n += 256) {                 // bias in the same packed order
+  for (int n = tid; n < L::kWRows; n += 128 * kWorkers) {      // bias in the same packed order
     const int h = n / 48, part = (n % 48) >> 4, d = n & 15;
     sBqkv[n] = (h < NH && d < HD) ? p.qkv_b[part * A + h * HD + d] : 0.f;
   }
   if (tid < 64) { sBp[tid] = p.proj_b[tid]; sLnW[tid] = p.ln_w[tid]; sLnB[tid] = p.ln_b[tid]; }
   if (tid < NH) sScale[tid] = expf(fminf(p.logit_scale[tid], kLogitMax)) * kLog2e;
-  for (int i = tid; i < NH * 225; i += 256) {
+  if (tid == 0) sScale[6] = __uint_as_float(we << 23);    // 2^(we-127)
+  for (int i = tid; i < NH * 225; i += 128 * kWorkers) {
     const int h = i / 225, e = i - h * 225;
     sBias[h * 228 + e] = p.bias_table[e * NH + h] * kLog2e;
   }
-  for (int i = tid; i < 2 * L::kWorkFloats; i += 256) smem[L::oWork + i] = 0.f;
   if (tid == 0) {
-    for (int i = 0; i < 8; ++i) tc::mbar_init(bars + i, 1);
+    for (int i = 0; i < 4 * kWorkers; ++i) tc::mbar_init(bars + i, 1);
     tc::fence_barrier_init();
   }
-  if (tid < 32) tc::tmem_alloc<512>(tmem_slot);
+  if (warp == 0) tc::tmem_alloc<512>(tmem_slot);
   tc::fence_async_smem();
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
 
-  const uint32_t tbase = *tmem_slot + wk * 256;
+  const uint32_t tbase = *tmem_slot + wk * kTStride;
   const uint32_t lane_addr = (uint32_t)(wq * 32) << 16;
-  const uint32_t xS = tc::smem_u32(sX), qS = tc::smem_u32(sQ), kS = tc::smem_u32(sK), vS = tc::smem_u32(sV);
-  const uint32_t wqkvS = tc::smem_u32(sWqkv), wpS = tc::smem_u32(sWp);
-  constexpr uint32_t kI32 = tc::idesc_tf32(128, 32), kI48 = tc::idesc_tf32(128, 48),
-                     kI64 = tc::idesc_tf32(128, 64), kI128 = tc::idesc_tf32(128, 128);
+  constexpr uint32_t kI48 = tc::idesc_f16(128, 48), kI64 = tc::idesc_f16(128, 64),
+                     kT32 = tc::idesc_tf32(128, 32), kT64 = tc::idesc_tf32(128, 64);
   uint32_t phQ = 0, phS = 0, phO = 0;
 
   const Geom g = make_geom(p.B, p.ph, p.pw, p.shift);
   const int nwin = g.B * g.wh * g.ww;
   const int ntile = (nwin + 1) >> 1;
   const int row = wq * 32 + lane;                 // token row of this thread == its TMEM lane
-  const int wsel = row >> 6, lrow = row & 63;     // window of the pair, token inside the window
+  const int wsel = wq >> 1, lrow = row & 63;      // window of the pair (warp-uniform), token inside it
   const int bias_base = ((lrow >> 3) * 15 + (lrow & 7)) + 112;   // rel_index(r, c) = bias_base - (15 ci + cj)
 
-  // operand descriptors are built once; a K step of 8 advances the start-address field (>>4) by
-  // two k-chunks
-  const uint64_t dX = tc::smem_desc(xS, 2048, 128), dWqkv = tc::smem_desc(wqkvS, L::kWRows * 16, 128),
-                 dQ = tc::smem_desc(qS, 2048, 128), dK = tc::smem_desc(kS, 2048, 128),
-                 dV = tc::smem_desc(vS, kVLd * 4, 128), dWp = tc::smem_desc(wpS, 1024, 128);
+  // operand descriptors are built once; one K = 16 step advances the start-address field (>>4)
+  // by two 8-element k-chunks
+  const uint64_t dX = tc::smem_desc(tc::smem_u32(sX), 2048, 128),   // also the fp32 O tile (same strides)
+                 dWqkv = tc::smem_desc(tc::smem_u32(sWqkv), L::kWRows * 16, 128),
+                 dQ = tc::smem_desc(tc::smem_u32(sQ), 2048, 128),
+                 dK = tc::smem_desc(tc::smem_u32(sK), 1024, 128),
+                 dV = tc::smem_desc(tc::smem_u32(sV), kVChunk, 128),
+                 dWp = tc::smem_desc(tc::smem_u32(sWp), 1024, 128);
   // [q_h | k_h | v_h] = X * Wqkv[rows of head h]^T -> TMEM buffer `buf` (issued by one thread)
   auto issue_qkv = [&](int h, int buf) {
     const uint64_t db = dWqkv + (uint64_t)(h * 48);
 #pragma unroll
-    for (int ks = 0; ks < 8; ++ks)
-      tc::mma_tf32(tbase + kTQ + buf * 48, dX + ks * 256, db + ks * (2 * L::kWRows), kI48, ks > 0);
+    for (int ks = 0; ks < 4; ++ks)
+      tc::mma_f16(tbase + kTQ + buf * 48, dX + ks * 256, db + ks * (2 * L::kWRows), kI48, ks > 0);
   };
 
-  for (int tile = blockIdx.x * 2 + wk; tile < ntile; tile += gridDim.x * 2) {
+  for (int tile = blockIdx.x * kWorkers + wk; tile < ntile; tile += gridDim.x * kWorkers) {
     // ---- slot table of the two windows
     {
       const int win = tile * 2 + wsel;
@@ -171,25 +202,57 @@ __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
       }
     }
     tc::worker_sync(1 + wk);
-    // ---- gather X = z + ctx: coalesced 64-byte segments -> conflict-free 16-byte slots
+    // ---- gather X = z + ctx -> fp16: coalesced 64-byte global segments, 8-byte smem slots.
+    //      Cosine attention is scale-invariant in q and k (F.normalize, eps 1e-12), so a row of
+    //      tiny activations (e.g. the zero-padded border) matters as much as any other: every row
+    //      is scaled by a power of two to max|x| in [1,2) before the fp16 conversion and the
+    //      exact inverse is applied to the fp32 accumulators in the qkv epilogue.
     {
       const int q = lane >> 3, m8 = lane & 7;
-      float4 zv[16], cv[16];
 #pragma unroll
-      for (int it = 0; it < 16; ++it) {                    // all 32 loads in flight before any use
-        const int m = wq * 32 + (it >> 2) * 8 + m8, kc = (it & 3) * 4 + q;
-        const int tok = sTok[m];
-        zv[it] = cv[it] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (tok >= 0) {
-          zv[it] = __ldg(reinterpret_cast<const float4*>(p.z + (size_t)tok * 64 + kc * 4));
-          cv[it] = __ldg(reinterpret_cast<const float4*>(p.ctx + (size_t)sCwin[m] * 64 + kc * 4));
+      for (int half = 0; half < 2; ++half) {
+        float4 xv[8];
+        {
+          float4 cv[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {                     // 16 loads in flight before any use
+            const int it = half * 8 + i;
+            const int m = wq * 32 + (it >> 2) * 8 + m8, kc = (it & 3) * 4 + q;
+            const int tok = sTok[m];
+            xv[i] = cv[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (tok >= 0) {
+              xv[i] = __ldg(reinterpret_cast<const float4*>(p.z + (size_t)tok * 64 + kc * 4));
+              cv[i] = __ldg(reinterpret_cast<const float4*>(p.ctx + (size_t)sCwin[m] * 64 + kc * 4));
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            xv[i].x += cv[i].x; xv[i].y += cv[i].y; xv[i].z += cv[i].z; xv[i].w += cv[i].w;
+          }
         }
-      }
 #pragma unroll
-      for (int it = 0; it < 16; ++it) {
-        const int m = wq * 32 + (it >> 2) * 8 + m8, kc = (it & 3) * 4 + q;
-        *reinterpret_cast<float4*>(sX + kc * 512 + m * 4) =
-            make_float4(zv[it].x + cv[it].x, zv[it].y + cv[it].y, zv[it].z + cv[it].z, zv[it].w + cv[it].w);
+        for (int j = 0; j < 2; ++j) {                       // two complete rows per half
+          float mxv = 0.f;
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float4 v = xv[j * 4 + i];
+            mxv = fmaxf(mxv, fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))));
+          }
+          mxv = fmaxf(mxv, __shfl_xor_sync(0xffffffffu, mxv, 8));
+          mxv = fmaxf(mxv, __shfl_xor_sync(0xffffffffu, mxv, 16));
+          uint32_t e = (__float_as_uint(mxv) >> 23) & 0xFFu;      // biased exponent of the row max
+          e = e < 1u ? 127u : (e > 253u ? 253u : e);              // all-zero / denormal row: scale 1
+          const float sc = __uint_as_float((254u - e) << 23);     // 2^(127-e)
+          const int m = wq * 32 + (half * 2 + j) * 8 + m8;
+          if (q == 0) sRowInv[m] = __uint_as_float(e << 23);      // 2^(e-127), exact inverse
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int kc = i * 4 + q;
+            const float4 v = xv[j * 4 + i];
+            *reinterpret_cast<uint2*>(sX + (kc >> 1) * 2048 + m * 16 + (kc & 1) * 8) =
+                make_uint2(tc::pack_f16(v.x * sc, v.y * sc), tc::pack_f16(v.z * sc, v.w * sc));
+          }
+        }
       }
     }
     // ---- shift mask of this row as a 64-bit key set (analytic 9-region rule)
@@ -211,17 +274,18 @@ __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
       __syncwarp();
     }
 
-    // per-head attention outputs of this row; indexed by the (rolled) head loop, so the array
-    // lives in local memory: 10-16 stores per head, one 64-float read-back per tile
+    // per-head attention outputs of this row; indexed by the (rolled) head loop, so the array lives
+    // in local memory: 10-16 stores per head, one 64-float read-back per tile
     float o[64];
 #pragma unroll
     for (int i = 0; i < 64; ++i) o[i] = 0.f;
+    const float xinv = sRowInv[row] * sScale[6];      // undoes the row scale of X and the scale of Wqkv
     float inv_prev = 0.f;
 
 #pragma unroll 1
     for (int h = 0; h < NH; ++h) {
       const int buf = h & 1;
-      // ---- wait for [q|k|v]_h, start head h+1's projection behind it
+      // ---- wait for [q|k|v]_h
       tc::mbar_wait(barQ + buf, (phQ >> buf) & 1u, &g_tc_error);
       phQ ^= 1u << buf;
       tc::tc_fence_after();
@@ -232,36 +296,43 @@ __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
         const float* b = sBqkv + h * 48;               // packed [q16 | k16 | v16]; pad rows are exact zeros
 #pragma unroll
         for (int d = 0; d < HD; ++d) {
-          qkv[d] += b[d];
-          qkv[16 + d] += b[16 + d];
-          qkv[32 + d] += b[32 + d];
+          qkv[d] = fmaf(qkv[d], xinv, b[d]);           // undo the row's power-of-two input scale
+          qkv[16 + d] = fmaf(qkv[16 + d], xinv, b[16 + d]);
+          qkv[32 + d] = fmaf(qkv[32 + d], xinv, b[32 + d]);
           qs = fmaf(qkv[d], qkv[d], qs);
           ks = fmaf(qkv[16 + d], qkv[16 + d], ks);
         }
       }
       const float qmul = sScale[h] / fmaxf(sqrtf(qs), kNormEps);
       const float kmul = 1.0f / fmaxf(sqrtf(ks), kNormEps);
+      uint32_t qp[8], kp[8];
 #pragma unroll
-      for (int d = 0; d < HD; ++d) { qkv[d] *= qmul; qkv[16 + d] *= kmul; }
-      // ---- previous head's O (its PV MMAs read P from TMEM and V^T from smem: wait before reuse)
+      for (int j = 0; j < 8; ++j) {
+        qp[j] = 2 * j < HD ? tc::pack_f16(qkv[2 * j] * qmul, qkv[2 * j + 1] * qmul) : 0u;
+        kp[j] = 2 * j < HD ? tc::pack_f16(qkv[16 + 2 * j] * kmul, qkv[16 + 2 * j + 1] * kmul) : 0u;
+      }
+      // ---- previous head's O: its PV MMAs read P (TMEM) and V^T (smem) and wrote O over the
+      //      accumulator buffer that [q|k|v]_{h+1} will reuse: read it before anything is reused
       if (h > 0) {
         tc::mbar_wait(barO, phO, &g_tc_error); phO ^= 1;
         tc::tc_fence_after();
         float ov[16];
-        tc::tmem_ld16(tbase + lane_addr + kTO + wsel * 16, ov);
+        tc::tmem_ld16(tbase + lane_addr + kTQ + (buf ^ 1) * 48 + wsel * 16, ov);
 #pragma unroll
         for (int d = 0; d < HD; ++d) o[(h - 1) * HD + d] = ov[d] * inv_prev;
       }
-      // ---- operands of head h: Q_h, K_h (rows = tokens), V_h^T (rows = d, keys contiguous)
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        *reinterpret_cast<float4*>(sQ + c * 512 + row * 4) =
-            make_float4(qkv[c * 4], qkv[c * 4 + 1], qkv[c * 4 + 2], qkv[c * 4 + 3]);
-        *reinterpret_cast<float4*>(sK + c * 512 + row * 4) =
-            make_float4(qkv[16 + c * 4], qkv[16 + c * 4 + 1], qkv[16 + c * 4 + 2], qkv[16 + c * 4 + 3]);
-      }
+      // ---- operands of head h: Q' = [q|0] or [0|q], K' = [k(w0)|k(w1)], V^T rows (window, d)
       {
-        float* vt = sV + (lrow >> 2) * kVLd + wsel * 64 + (lrow & 3);
+        const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
+        uint4* q0 = reinterpret_cast<uint4*>(sQ + row * 16);                 // k-chunk stride 2048 B
+        q0[(2 * wsel) * 128] = make_uint4(qp[0], qp[1], qp[2], qp[3]);
+        q0[(2 * wsel + 1) * 128] = make_uint4(qp[4], qp[5], qp[6], qp[7]);
+        q0[(2 - 2 * wsel) * 128] = z4;
+        q0[(3 - 2 * wsel) * 128] = z4;
+        uint4* k0 = reinterpret_cast<uint4*>(sK + lrow * 16);                // k-chunk stride 1024 B
+        k0[(2 * wsel) * 64] = make_uint4(kp[0], kp[1], kp[2], kp[3]);
+        k0[(2 * wsel + 1) * 64] = make_uint4(kp[4], kp[5], kp[6], kp[7]);
+        float* vt = reinterpret_cast<float*>(sV + (lrow >> 2) * kVChunk + wsel * 256) + (lrow & 3);
 #pragma unroll
         for (int d = 0; d < HD; ++d) vt[d * 4] = qkv[32 + d];
       }
@@ -271,8 +342,8 @@ __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
       if (wq == 0) {
         tc::tc_fence_after();
         if (tc::elect_one()) {
-          tc::mma_tf32(tbase + kTS, dQ, dK, kI128, 0u);
-          tc::mma_tf32(tbase + kTS, dQ + 256, dK + 256, kI128, 1u);
+          tc::mma_f16(tbase + kTS, dQ, dK, kI64, 0u);
+          tc::mma_f16(tbase + kTS, dQ + 256, dK + 128, kI64, 1u);
           tc::mma_commit(barS);
           if (h + 1 < NH) {                            // next head's projection, in the shadow of S_h
             issue_qkv(h + 1, buf ^ 1);
@@ -286,7 +357,7 @@ __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
       // ---- softmax of this row over its own window's 64 keys (log2 domain)
       {
         float s[64];
-        tc::tmem_ld64(tbase + lane_addr + kTS + wsel * 64, s);
+        tc::tmem_ld64(tbase + lane_addr + kTS, s);
         const float* bias = sBias + h * 228 + bias_base;
 #pragma unroll
         for (int c = 0; c < 64; ++c) s[c] += bias[-((c >> 3) * 15 + (c & 7))];
@@ -304,7 +375,7 @@ __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
 #pragma unroll
         for (int c = 0; c < 64; ++c) { s[c] = tc::ex2_approx(s[c] - mx); sum4[c & 3] += s[c]; }
         inv_prev = 1.0f / ((sum4[0] + sum4[1]) + (sum4[2] + sum4[3]));
-        tc::tmem_st64(tbase + lane_addr + kTS, s);       // unnormalised P over S columns [0,64)
+        tc::tmem_st64(tbase + lane_addr + kTS, s);       // unnormalised P (tf32 operand) over S
         tc::tmem_wait_st();
       }
       tc::tc_fence_before();
@@ -314,7 +385,7 @@ __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
         if (tc::elect_one()) {
 #pragma unroll
           for (int ks = 0; ks < 8; ++ks)
-            tc::mma_tf32_ts(tbase + kTO, tbase + kTS + ks * 8, dV + ks * (2 * kVLd * 4 / 16), kI32, ks > 0);
+            tc::mma_tf32_ts(tbase + kTQ + buf * 48, tbase + kTS + ks * 8, dV + ks * (2 * kVChunk / 16), kT32, ks > 0);
           tc::mma_commit(barO);
         }
         __syncwarp();
@@ -325,13 +396,13 @@ __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
       tc::mbar_wait(barO, phO, &g_tc_error); phO ^= 1;
       tc::tc_fence_after();
       float ov[16];
-      tc::tmem_ld16(tbase + lane_addr + kTO + wsel * 16, ov);
+      tc::tmem_ld16(tbase + lane_addr + kTQ + ((NH - 1) & 1) * 48 + wsel * 16, ov);
 #pragma unroll
       for (int d = 0; d < HD; ++d) o[(NH - 1) * HD + d] = ov[d] * inv_prev;
     }
 #pragma unroll
-    for (int kc = 0; kc < 16; ++kc)
-      *reinterpret_cast<float4*>(sX + kc * 512 + row * 4) =
+    for (int kc = 0; kc < 16; ++kc)                    // fp32 O tile over [X|Q|K|V] (all dead by now)
+      *reinterpret_cast<float4*>(sStage + kc * 512 + row * 4) =
           make_float4(o[kc * 4], o[kc * 4 + 1], o[kc * 4 + 2], o[kc * 4 + 3]);
     tc::fence_async_smem();
     tc::tc_fence_before();
@@ -340,14 +411,14 @@ __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
       tc::tc_fence_after();
       if (tc::elect_one()) {
 #pragma unroll
-        for (int ks = 0; ks < 8; ++ks) tc::mma_tf32(tbase + kTS, dX + ks * 256, dWp + ks * 128, kI64, ks > 0);
+        for (int ks = 0; ks < 8; ++ks) tc::mma_tf32(tbase + kTS, dX + ks * 256, dWp + ks * 128, kT64, ks > 0);
         tc::mma_commit(barS);
       }
       __syncwarp();
     }
     tc::mbar_wait(barS, phS, &g_tc_error); phS ^= 1;
     tc::tc_fence_after();
-    // ---- + proj bias, LayerNorm(norm1) of the row held in registers -> sX (own row)
+    // ---- + proj bias, LayerNorm(norm1) of the row held in registers -> fp32 staging tile (own row)
     {
       float y[64];
       tc::tmem_ld64(tbase + lane_addr + kTS, y);
@@ -361,7 +432,7 @@ __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
       const float rstd = 1.0f / sqrtf(var * (1.0f / 64.f) + kLnEps);
 #pragma unroll
       for (int kc = 0; kc < 16; ++kc)
-        *reinterpret_cast<float4*>(sX + kc * 512 + row * 4) =
+        *reinterpret_cast<float4*>(sStage + kc * 512 + row * 4) =
             make_float4(y[kc * 4 + 0] * rstd * sLnW[kc * 4 + 0] + sLnB[kc * 4 + 0],
                         y[kc * 4 + 1] * rstd * sLnW[kc * 4 + 1] + sLnB[kc * 4 + 1],
                         y[kc * 4 + 2] * rstd * sLnW[kc * 4 + 2] + sLnB[kc * 4 + 2],
@@ -372,22 +443,27 @@ __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
     // ---- residual + scatter back to the source token positions (same mapping as the gather)
     {
       const int q = lane >> 3, m8 = lane & 7;
-      float4 zv[16];
 #pragma unroll
-      for (int it = 0; it < 16; ++it) {
-        const int m = wq * 32 + (it >> 2) * 8 + m8, kc = (it & 3) * 4 + q;
-        const int tok = sTok[m];
-        zv[it] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (tok >= 0) zv[it] = __ldg(reinterpret_cast<const float4*>(p.z + (size_t)tok * 64 + kc * 4));
-      }
+      for (int half = 0; half < 2; ++half) {
+        float4 zv[8];
 #pragma unroll
-      for (int it = 0; it < 16; ++it) {
-        const int m = wq * 32 + (it >> 2) * 8 + m8, kc = (it & 3) * 4 + q;
-        const int tok = sTok[m];
-        if (tok >= 0) {
-          const float4 y = *reinterpret_cast<const float4*>(sX + kc * 512 + m * 4);
-          *reinterpret_cast<float4*>(p.a + (size_t)tok * 64 + kc * 4) =
-              make_float4(zv[it].x + y.x, zv[it].y + y.y, zv[it].z + y.z, zv[it].w + y.w);
+        for (int i = 0; i < 8; ++i) {
+          const int it = half * 8 + i;
+          const int m = wq * 32 + (it >> 2) * 8 + m8, kc = (it & 3) * 4 + q;
+          const int tok = sTok[m];
+          zv[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (tok >= 0) zv[i] = __ldg(reinterpret_cast<const float4*>(p.z + (size_t)tok * 64 + kc * 4));
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int it = half * 8 + i;
+          const int m = wq * 32 + (it >> 2) * 8 + m8, kc = (it & 3) * 4 + q;
+          const int tok = sTok[m];
+          if (tok >= 0) {
+            const float4 y = *reinterpret_cast<const float4*>(sStage + kc * 512 + m * 4);
+            *reinterpret_cast<float4*>(p.a + (size_t)tok * 64 + kc * 4) =
+                make_float4(zv[i].x + y.x, zv[i].y + y.y, zv[i].z + y.z, zv[i].w + y.w);
+          }
         }
       }
     }
@@ -395,12 +471,12 @@ __global__ void __launch_bounds__(256, 1) attn_tc_fwd_kernel(AttnParams p) {
   }
   tc::tc_fence_before();
   __syncthreads();
-  if (tid < 32) tc::tmem_dealloc<512>(*tmem_slot);
+  if (warp == 0) tc::tmem_dealloc<512>(*tmem_slot);
 }
 
 template <int NH>
 static int launch_attn_tc_fwd(const AttnParams& p, cudaStream_t st) {
-  const size_t smem = AttnTcSmem::kFloats * sizeof(float);
+  const size_t smem = AttnTcSmem::kBytes;
   static bool configured = false;
   if (!configured) {
     B200MAR_CHECK(cudaFuncSetAttribute(attn_tc_fwd_kernel<NH>,
@@ -409,9 +485,9 @@ static int launch_attn_tc_fwd(const AttnParams& p, cudaStream_t st) {
   }
   const int nwin = p.B * (p.ph / kWin) * (p.pw / kWin);
   const int ntile = (nwin + 1) / 2;
-  int grid = (ntile + 1) / 2;
+  int grid = (ntile + kWorkers - 1) / kWorkers;
   if (grid > sm_count()) grid = sm_count();
-  attn_tc_fwd_kernel<NH><<<grid, 256, smem, st>>>(p);
+  attn_tc_fwd_kernel<NH><<<grid, 128 * kWorkers, smem, st>>>(p);
   B200MAR_CHECK(cudaGetLastError());
   return 0;
 }

@@ -6,6 +6,7 @@
 // `col0` shifts the accumulator / TMEM-A base column to test unaligned column addressing.
 #include "common.cuh"
 #include "tc.cuh"
+#include <cuda_fp16.h>
 
 namespace b200mar {
 
@@ -121,11 +122,91 @@ __global__ void __launch_bounds__(128, 1) tc_probe_kernel(const float* __restric
   if (t < 32) tc::tmem_dealloc<512>(slot);
 }
 
+// fp16-operand variants: mode 4 = both operands K-major fp16 in shared memory (chunk-major, 8
+// elements per 16-byte chunk), mode 5 = A packed two-per-column in TMEM.
+__global__ void __launch_bounds__(128, 1) tc_probe_f16_kernel(const float* __restrict__ A,
+                                                              const float* __restrict__ B,
+                                                              float* __restrict__ D, int N, int K,
+                                                              int mode, int col0) {
+  extern __shared__ __align__(128) float smem[];
+  __half* sA = reinterpret_cast<__half*>(smem);          // [128][K]: (k/8)*(128*8) + r*8 + k%8
+  __half* sB = sA + 128 * K;                             // [N][K]  : (k/8)*(N*8) + n*8 + k%8
+  __shared__ uint64_t bar;
+  __shared__ uint32_t slot;
+  const int t = threadIdx.x, lane = t & 31, wq = t >> 5;
+  for (int idx = t; idx < 128 * K; idx += 128) {
+    const int r = idx / K, k = idx % K;
+    sA[(k >> 3) * 1024 + r * 8 + (k & 7)] = __float2half_rn(A[idx]);
+  }
+  for (int idx = t; idx < N * K; idx += 128) {
+    const int n = idx / K, k = idx % K;
+    sB[(k >> 3) * (N * 8) + n * 8 + (k & 7)] = __float2half_rn(B[idx]);
+  }
+  if (t == 0) { tc::mbar_init(&bar, 1); tc::fence_barrier_init(); }
+  if (t < 32) tc::tmem_alloc<512>(&slot);
+  tc::fence_async_smem();
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tbase = slot;
+  const uint32_t lane_addr = (uint32_t)(wq * 32) << 16;
+  const uint32_t dcol = col0, acol = 256 + col0;
+  const int row = wq * 32 + lane;
+  if (mode == 5) {
+    for (int c = 0; c < K / 2; c += 8) {                  // 8 columns = 16 fp16 per store
+      float v[16];
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        v[i] = __uint_as_float(tc::pack_f16(A[row * K + 2 * (c + i)], A[row * K + 2 * (c + i) + 1]));
+      asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                   ::"r"(tbase + lane_addr + acol + c), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]),
+                     "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7]) : "memory");
+    }
+    tc::tmem_wait_st();
+    tc::tc_fence_before();
+    __syncthreads();
+  }
+  if (wq == 0) {
+    tc::tc_fence_after();
+    if (tc::elect_one()) {
+      const uint32_t idesc = tc::idesc_f16(128, N);
+      const uint64_t da = tc::smem_desc(tc::smem_u32(sA), 2048, 128);
+      const uint64_t db = tc::smem_desc(tc::smem_u32(sB), N * 16, 128);
+      for (int k = 0; k < K; k += 16) {
+        if (mode == 5) tc::mma_f16_ts(tbase + dcol, tbase + acol + k / 2, db + (k >> 3) * N, idesc, k > 0);
+        else           tc::mma_f16(tbase + dcol, da + (k >> 3) * 128, db + (k >> 3) * N, idesc, k > 0);
+      }
+      tc::mma_commit(&bar);
+    }
+    __syncwarp();
+  }
+  tc::mbar_wait(&bar, 0, &g_tc_error);
+  tc::tc_fence_after();
+  for (int c = 0; c < N; c += 16) {
+    float v[16];
+    tc::tmem_ld16(tbase + lane_addr + dcol + c, v);
+#pragma unroll
+    for (int i = 0; i < 16; ++i) D[row * N + c + i] = v[i];
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (t < 32) tc::tmem_dealloc<512>(slot);
+}
+
 }  // namespace b200mar
 
 extern "C" int b200mar_tc_probe(const float* A, const float* B, float* D, int N, int K, int mode,
                                 int col0, void* stream) {
   using namespace b200mar;
+  if (mode == 4 || mode == 5) {
+    if (N % 16 || N < 16 || N > 256 || K % 16 || K < 16 || K > 128 || col0 < 0 || col0 + N > 256) return -1;
+    const size_t smem16 = (size_t)(128 * K + N * K) * 2;
+    B200MAR_CHECK(cudaFuncSetAttribute(tc_probe_f16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       200 * 1024));
+    tc_probe_f16_kernel<<<1, 128, smem16, (cudaStream_t)stream>>>(A, B, D, N, K, mode, col0);
+    B200MAR_CHECK(cudaGetLastError());
+    return 0;
+  }
   if (N % 16 || N < 16 || N > 256 || K % 8 || K < 8 || K > 128 || mode < 0 || (mode & 15) > 3) return -1;
   if ((mode & 15) != 3 && (col0 < 0 || col0 + N > 256 || col0 + K > 256)) return -1;
   const size_t smem = (size_t)(128 * K + (N + 1) * K + ((mode & 15) == 3 ? 4096 : 0)) * sizeof(float);
