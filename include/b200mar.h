@@ -159,6 +159,42 @@ int b200mar_pixel_shuffle_cat(float* x0 /*[B,H*W,64]*/, float* x1 /*[B,H*W/4,64]
                               float* x2 /*[B,H*W/16,64]*/, float* cat /*[B,H*W,84]*/,
                               int B, int H, int W, int inverse, void* stream);
 
+/* ---- a2, a9, a11, a12, a13, a14: the generator glue between the transformer stages, fused and
+ * kept in the channels-last token layout (inference path; training uses the stock-PyTorch
+ * composition of the same modules so that autograd covers it) ------------------------------
+ * a2  ShallowExtractor.conv1 (components/encoder_decoder.py:23-27) + the token rearrange of
+ *     ngswin.py:172:  x [B,1,H,W] -> c0 [B,H*W,64].                                          */
+int b200mar_shallow_tok_fwd(const float* x, const float* w /*[64,1,3,3]*/, const float* b /*[64]*/,
+                            float* c0, int B, int H, int W, void* stream);
+/* a11+a9 InterPool (components/pooling.py:13-17) of the cascade, torch.cat (ngswin.py:175,178)
+ *     and EncoderLayer.across_cascade_proj (components/encoder_decoder.py:117,136):
+ *     out[b,t,:] = w * cat(maxpool2x2(srcA)[t], maxpool2x2(srcB)[t] (if srcB), direct[t]) + bias.
+ *     srcA/srcB [B,2h,2wd,64], direct/out [B,h*wd,64], w [64,128] (srcB NULL) or [64,192];
+ *     poolA (optional) receives maxpool2x2(srcA).                                            */
+int b200mar_cascade_proj_fwd(const float* srcA, const float* srcB, const float* direct,
+                             const float* w, const float* bias, float* out, float* poolA,
+                             int B, int h, int wd, void* stream);
+/* a12 SCDPBottleneck front (components/encoder_decoder.py:159-164,191-192; pooling.py:32-37):
+ *     cat[b,t,:] = [ e1 + lrelu(c0) | shuffle2(e2 + lrelu(p0)) | shuffle4(e3 + lrelu(p00)) ],
+ *     p0 = maxpool2(c0), p00 = maxpool4(c0) (token-major), cat [B,H*W,84].                   */
+int b200mar_bottleneck_cat_fwd(const float* c0, const float* p0, const float* p00,
+                               const float* e1, const float* e2, const float* e3,
+                               float* cat, int B, int H, int W, void* stream);
+/* a12+a13 SCDPBottleneck tail (components/encoder_decoder.py:194-200) + the decoder input add
+ *     (ngswin.py:189): out = LN(pointwise(GELU(depthwise3x3(cat)))) + e1.                    */
+int b200mar_bottleneck_tail_fwd(const float* cat, const float* dw_w /*[84,1,3,3]*/,
+                                const float* dw_b, const float* pw_w /*[64,84]*/,
+                                const float* pw_b, const float* ln_w, const float* ln_b,
+                                const float* e1, float* out, int B, int H, int W, void* stream);
+/* a13+a14 decoder tail: LN(norm) + global skip (ngswin.py:190,204), Reconstruction
+ *     (components/reconstruction.py:14-19) and the crop of ngswin.py:208:
+ *     out [B,1,H0,W0] = tanh(conv3x3(conv3x3(LN(dec) + c0; w1,b1); w2,b2))[:H0,:W0].
+ *     taps [B,H*W,9] is caller-provided scratch.                                             */
+int b200mar_final_recon_fwd(const float* dec, const float* c0, const float* ln_w,
+                            const float* ln_b, const float* w1 /*[1,64,3,3]*/, const float* b1,
+                            const float* w2 /*[1,1,3,3]*/, const float* b2, float* taps,
+                            float* out, int B, int H, int W, int H0, int W0, void* stream);
+
 /* ---- integer index maps (bit-exact contract of a4/a6/a7) -------------------------------
  * tok_idx/ctx_idx [B*wh*ww, 64] int64: flat source token / source window of every window
  * slot, exactly what the attention kernels use (same device function).                     */

@@ -328,3 +328,18 @@ def test_training_step_reduces_loss(T):
         opt.step()
         losses.append(loss.item())
     assert losses[-1] < losses[0]
+
+
+def test_fused_glue_matches_composite_path(T):
+    """The fused inference glue (glue_fwd.cu: shallow conv, pool+concat+cascade projection,
+    bottleneck, LN + skip + reconstruction) against the stock-PyTorch composition that training
+    uses, same fp32 block kernels, incl. a size that needs padding + cropping."""
+    m = load_model(T, "W2")
+    for shape in ((2, 64, 96), (1, 100, 70)):
+        x = O.synthetic_input(*shape, seed=7).cuda()
+        with torch.no_grad():
+            y_fused = m(x)
+        with torch.enable_grad():
+            y_comp = m(x).detach()
+        assert y_fused.shape == y_comp.shape
+        assert (y_fused - y_comp).abs().max().item() < 2e-5

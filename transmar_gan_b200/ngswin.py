@@ -180,8 +180,9 @@ class EncoderLayer(_Stage):
                            head_dim, mlp_ratio, qkv_bias)
         self.downsample = PatchMerging(dim, dim) if downsample else None
 
-    def forward(self, x, num_patches):
-        x = self.across_cascade_proj(x).contiguous()
+    def forward(self, x, num_patches, projected=False):
+        if not projected:                                       # fused path projects beforehand
+            x = self.across_cascade_proj(x).contiguous()
         out, zsum = self._run_blocks(x, num_patches, need_sum_last=self.downsample is not None)
         if self.downsample is None:
             return out, out, num_patches
@@ -326,6 +327,8 @@ class NGswin(nn.Module):
         if H < 2 * unit or W < 2 * unit:
             raise RuntimeError(f"input {H0}x{W0} pads to {H}x{W}; NGswin needs >= 64 per side "
                                "(stage 3 must have 2x2 windows; the reference raises too)")
+        if not torch.is_grad_enabled():
+            return self._forward_fused(x.float().contiguous(), H0, W0)
         shallow = self.shallow_extract(x.float())
         c0 = shallow.flatten(2).transpose(1, 2).contiguous()     # [B, HW, 64]
         e1_, e1, np1 = self.encoder_layer1(c0, (H, W))
@@ -339,6 +342,29 @@ class NGswin(nn.Module):
         img = dec.transpose(1, 2).reshape(B, self.dec_dim, H, W)
         out = self.to_target(img)
         return out[:, :, :H0, :W0]
+
+    def _forward_fused(self, x, H0, W0):
+        """Inference path (no autograd): the glue between the stages runs as fused channels-last
+        CUDA kernels (glue_fwd.cu) - same arithmetic as the composite path above, which training
+        keeps so that autograd differentiates it."""
+        B, _, H, W = x.shape
+        se = self.shallow_extract.conv1
+        c0 = ops.shallow_tok_fwd(x, se.weight, se.bias)
+        e1_, e1, np1 = self.encoder_layer1(c0, (H, W))
+        l2, l3, bn, tt = self.encoder_layer2, self.encoder_layer3, self.bottleneck, self.to_target
+        x2, p0 = ops.cascade_proj_fwd(c0, None, e1, l2.across_cascade_proj.weight,
+                                      l2.across_cascade_proj.bias, H // 2, W // 2)
+        e2_, e2, np2 = l2(x2, np1, projected=True)
+        x3, p00 = ops.cascade_proj_fwd(p0, e1, e2, l3.across_cascade_proj.weight,
+                                       l3.across_cascade_proj.bias, H // 4, W // 4)
+        e3_, _, _ = l3(x3, np2, projected=True)
+        dec_in = ops.bottleneck_fwd(c0, p0, p00, e1_, e2_, e3_, bn.depthwise.weight, bn.depthwise.bias,
+                                    bn.pointwise.weight, bn.pointwise.bias, bn.norm.weight,
+                                    bn.norm.bias, H, W)
+        dec = self.decoder_layer1(dec_in, (H, W))
+        return ops.final_recon_fwd(dec, c0, self.norm.weight, self.norm.bias,
+                                   tt.before_shuffle.weight, tt.before_shuffle.bias,
+                                   tt.to_origin.weight, tt.to_origin.bias, H, W, H0, W0)
 
     def flops(self, resolutions):
         """Exact multiply-accumulate count of one forward, unpadded head dims."""

@@ -303,6 +303,54 @@ def _(dcat, H, W):
             dcat.new_empty((B, H * W // 16, 64)))
 
 
+# ------------------------------------------------------------------------------ fused glue (inference)
+def shallow_tok_fwd(x: Tensor, w: Tensor, b: Tensor) -> Tensor:
+    """ShallowExtractor conv3x3 written token-major: x [B,1,H,W] -> c0 [B,H*W,64]."""
+    _chk(x, w, b)
+    B, _, H, W = x.shape
+    c0 = torch.empty((B, H * W, 64), device=x.device, dtype=torch.float32)
+    _call("shallow_tok_fwd", _p(x), _p(w), _p(b), _p(c0), B, H, W, _stream())
+    return c0
+
+
+def cascade_proj_fwd(srcA: Tensor, srcB: Optional[Tensor], direct: Tensor, w: Tensor, bias: Tensor,
+                     h: int, wd: int, want_pool: bool = True) -> Tuple[Tensor, Optional[Tensor]]:
+    """InterPool + concat + across_cascade_proj; also returns maxpool2x2(srcA) when asked."""
+    _chk(srcA, srcB, direct, w, bias)
+    B = direct.shape[0]
+    out = torch.empty((B, h * wd, 64), device=direct.device, dtype=torch.float32)
+    pool = torch.empty_like(out) if want_pool else None
+    _call("cascade_proj_fwd", _p(srcA), _p(srcB), _p(direct), _p(w), _p(bias), _p(out), _p(pool),
+          B, h, wd, _stream())
+    return out, pool
+
+
+def bottleneck_fwd(c0: Tensor, p0: Tensor, p00: Tensor, e1: Tensor, e2: Tensor, e3: Tensor,
+                   dw_w: Tensor, dw_b: Tensor, pw_w: Tensor, pw_b: Tensor, ln_w: Tensor,
+                   ln_b: Tensor, H: int, W: int) -> Tensor:
+    """SCDPBottleneck + the decoder-input add: returns bottleneck(shallow, [e1,e2,e3]) + e1."""
+    _chk(c0, p0, p00, e1, e2, e3, dw_w, dw_b, pw_w, pw_b, ln_w, ln_b)
+    B = c0.shape[0]
+    cat = torch.empty((B, H * W, 84), device=c0.device, dtype=torch.float32)
+    _call("bottleneck_cat_fwd", _p(c0), _p(p0), _p(p00), _p(e1), _p(e2), _p(e3), _p(cat), B, H, W, _stream())
+    out = torch.empty_like(c0)
+    _call("bottleneck_tail_fwd", _p(cat), _p(dw_w), _p(dw_b), _p(pw_w), _p(pw_b), _p(ln_w), _p(ln_b),
+          _p(e1), _p(out), B, H, W, _stream())
+    return out
+
+
+def final_recon_fwd(dec: Tensor, c0: Tensor, ln_w: Tensor, ln_b: Tensor, w1: Tensor, b1: Tensor,
+                    w2: Tensor, b2: Tensor, H: int, W: int, H0: int, W0: int) -> Tensor:
+    """LN(norm) + global skip + Reconstruction (two 3x3 convs, tanh) + crop -> [B,1,H0,W0]."""
+    _chk(dec, c0, ln_w, ln_b, w1, b1, w2, b2)
+    B = dec.shape[0]
+    taps = torch.empty((B, H * W, 9), device=dec.device, dtype=torch.float32)
+    out = torch.empty((B, 1, H0, W0), device=dec.device, dtype=torch.float32)
+    _call("final_recon_fwd", _p(dec), _p(c0), _p(ln_w), _p(ln_b), _p(w1), _p(b1), _p(w2), _p(b2),
+          _p(taps), _p(out), B, H, W, H0, W0, _stream())
+    return out
+
+
 # ------------------------------------------------------------------------------ index maps
 def partition_index(B: int, ph: int, pw: int, shift: int, device) -> Tuple[Tensor, Tensor]:
     n = B * (ph // 8) * (pw // 8)
