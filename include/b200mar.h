@@ -93,7 +93,10 @@ int b200mar_attn_tc_fwd(const float* z, const float* ctx,
                         const float* proj_w, const float* proj_b,
                         const float* logit_scale, const float* bias_table,
                         const float* ln_w, const float* ln_b,
-                        float* a, int B, int ph, int pw, int nh, int shift, void* stream);
+                        float* a, int B, int ph, int pw, int nh, int shift, int residual,
+                        void* stream);
+/* residual = 1: a = z + LN1(attn) as above.  residual = 0: a = LN1(attn) only - the consumer
+ * (b200mar_mlp_tc_fwd with a_is_delta = 1) adds z, which it reads anyway.                   */
 /* dz = da + scatter(dX) (overwrites dz); dctx += per-source-window sums of dX (dctx must be
  * zeroed by the caller); parameter gradients are accumulated.                              */
 int b200mar_attn_bwd(const float* z, const float* ctx, const float* da,
@@ -121,7 +124,10 @@ int b200mar_mlp_tc_fwd(const float* a, const float* z,
                        const float* fc1_w, const float* fc1_b,
                        const float* fc2_w, const float* fc2_b,
                        const float* ln_w, const float* ln_b,
-                       float* out, float* zsum, long long n_tok, void* stream);
+                       float* out, float* zsum, float* a_out, int a_is_delta,
+                       long long n_tok, void* stream);
+/* a_is_delta = 1: `a` holds LN1(attn) only (b200mar_attn_tc_fwd with residual = 0) and the kernel
+ * forms a = z + a itself (z required); a_out (optional) receives that sum for the backward.   */
 /* 1 if a tensor-core kernel of this process ever timed out on an mbarrier (every wait is
  * bounded so a descriptor bug cannot hang the device); 0 otherwise; -1 on a CUDA error.     */
 int b200mar_tc_error(void);

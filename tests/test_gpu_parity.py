@@ -137,7 +137,7 @@ def test_nstb_vs_golden(T, golden_outputs, kind):
     for stage, nh, key in (("encoder_layer1", 6, "nstb6"), ("encoder_layer2", 4, "nstb4")):
         for bi in (0, 1):
             P = block_params(T, sd, f"{stage}.blocks.{bi}.")
-            out, _ = T.ops.NSTBFunction.apply(z, 24, 40, nh, 0 if bi == 0 else 4, True, False, *P)
+            out, _ = T.ops.NSTBFunction.apply(z, 24, 40, nh, 0 if bi == 0 else 4, True, False, False, *P)
             assert (out.cpu() - golden_outputs[(kind, key, bi)]).abs().max() < tol, (stage, bi)
     pm = T.ops.patch_merge_fwd(z, sd["encoder_layer1.downsample.norm.weight"],
                                sd["encoder_layer1.downsample.norm.bias"],
@@ -246,7 +246,7 @@ def test_nstb_backward_vs_oracle_autograd(T, kind, case, geom):
     # ---- CUDA kernels
     P = [sd[prefix + n].cuda().contiguous().requires_grad_(True) for n in T.ops.NSTB_PARAM_NAMES]
     zc = z.cuda().requires_grad_(True)
-    out, zsum = T.ops.NSTBFunction.apply(zc, ph, pw, nh, shift, True, True, *P)
+    out, zsum = T.ops.NSTBFunction.apply(zc, ph, pw, nh, shift, True, True, True, *P)
     loss = (out * w_out.cuda()).sum() + (zsum * w_zs.cuda()).sum()
     loss.backward()
     assert abs(loss.item() - loss64.item()) < 1e-3 * max(1.0, abs(loss64.item()))

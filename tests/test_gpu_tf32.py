@@ -43,6 +43,10 @@ def dev(sd):
     return {k: v.cuda() for k, v in sd.items()}
 
 
+def mx_tol(kind):
+    return 2e-2 if kind == "W1" else 1.5e-1
+
+
 CASES = [("encoder_layer1.blocks.0.", 6, 0), ("encoder_layer1.blocks.1.", 6, 4),
          ("encoder_layer2.blocks.0.", 4, 0), ("encoder_layer3.blocks.1.", 4, 4)]
 
@@ -75,7 +79,13 @@ def test_attn_and_mlp_tc_forward(T, kind, case, geom):
         m = F.linear(h, sd[prefix + "ffn.fc2.weight"], sd[prefix + "ffn.fc2.bias"])
         out_ref = a_ref + F.layer_norm(m, (64,), sd[prefix + "norm2.weight"], sd[prefix + "norm2.bias"], 1e-5)
     a = T.ops.attn_tc_fwd(z.cuda(), ctx.cuda(), *P[10:18], ph, pw, nh, shift)
-    out, zsum = T.ops.mlp_tc_fwd(a_ref.cuda(), z.cuda(), *P[18:24], True, True)
+    out, zsum, _ = T.ops.mlp_tc_fwd(a_ref.cuda(), z.cuda(), *P[18:24], True, True)
+    # the fused pair as the model runs it: attention writes LN1(attn) only, the MLP adds z
+    t = T.ops.attn_tc_fwd(z.cuda(), ctx.cuda(), *P[10:18], ph, pw, nh, shift, False)
+    assert torch.allclose(t + z.cuda(), a, atol=1e-5)
+    out2, zsum2, a2 = T.ops.mlp_tc_fwd(t, z.cuda(), *P[18:24], True, True, True, True)
+    assert torch.allclose(a2, a, atol=1e-5)
+    assert (out2.cpu() - out_ref).abs().max() < mx_tol(kind) and torch.allclose(zsum2, out2 + z.cuda(), atol=1e-5)
     da = (a.cpu() - a_ref).abs()
     do = (out.cpu() - out_ref).abs()
     mx, mean = (2e-2, 2e-3) if kind == "W1" else (1.5e-1, 5e-3)
@@ -151,3 +161,24 @@ def test_tf32_forward_fp32_backward_gradients(T, golden_outputs):
         errs.append(((named[n].grad.cpu().double() - gref.double()).norm() / gref.double().norm()).item())
     errs.sort()
     assert errs[len(errs) // 2] < 5e-2 and errs[-1] < 0.25, (errs[len(errs) // 2], errs[-1])
+
+
+def test_attn_tc_exact_softmax_fallback(T):
+    """The tensor-core attention shifts the logits by a per-head upper bound instead of the row
+    maximum; rows that would underflow take the exact max-subtracting path.  Force it: one huge
+    relative-position-bias entry lifts the bound ~290 octaves above every row that does not use it."""
+    prefix, nh = "encoder_layer1.blocks.1.", 6
+    sd = O.synthetic_state_dict("W1", seed=1)
+    sd[prefix + "attn.relative_position_bias_table"] = sd[prefix + "attn.relative_position_bias_table"].clone()
+    sd[prefix + "attn.relative_position_bias_table"][0, :] = 200.0       # (dy,dx) = (-7,-7): one key pair per window
+    sd[prefix + "attn.logit_scale"] = torch.full_like(sd[prefix + "attn.logit_scale"], 4.0)
+    B, ph, pw, shift = 1, 16, 24, 4
+    g = torch.Generator().manual_seed(3)
+    z = torch.randn(B, ph * pw, 64, generator=g)
+    ctx = torch.randn(B, (ph // 8) * (pw // 8), 64, generator=g) * 0.5
+    P = [sd[prefix + n].cuda().contiguous() for n in T.ops.NSTB_PARAM_NAMES]
+    a_tc = T.ops.attn_tc_fwd(z.cuda(), ctx.cuda(), *P[10:18], ph, pw, nh, shift)
+    a_32 = T.ops.attn_fwd(z.cuda(), ctx.cuda(), *P[10:18], ph, pw, nh, shift)
+    assert torch.isfinite(a_tc).all()
+    d = (a_tc - a_32).abs()
+    assert d.max() < 5e-2 and d.mean() < 3e-3, (d.max().item(), d.mean().item())

@@ -48,5 +48,8 @@ for pre, nh, (B, ph, pw) in (("encoder_layer1.blocks.1.", 6, (32, 416, 416)), ("
         print(f"attn tc nh={nh} shift={shift} B={B} {ph}x{pw}: {ms:.3f} ms per launch, {gb / ms * 1e3:.0f} GB/s "
               f"algorithmic (2 passes), tc_error {ops.tc_error()}", flush=True)
     a = torch.randn_like(z)
-    ms = timeit(lambda: ops.mlp_tc_fwd(a, z, *P[18:24], False, True))
+    ms = timeit(lambda: ops.mlp_tc_fwd(a, z, *P[18:24], False, True, True, False))
+    for shift in (0, 4):
+        ms2 = timeit(lambda: ops.attn_tc_fwd(z, c, *P[10:18], ph, pw, nh, shift, False))
+        print(f"attn tc (no residual) nh={nh} shift={shift}: {ms2:.3f} ms per launch")
     print(f"mlp tc B={B} {ph}x{pw}: {ms:.3f} ms per launch, {z.numel() * 4 * 3 / 1e9 / ms * 1e3:.0f} GB/s algorithmic (3 passes)")

@@ -33,11 +33,11 @@ SIGNATURES = {
     "b200mar_ngram_ctx_fwd": [_P] * 10 + [_I] * 4 + [_P],
     "b200mar_ngram_ctx_bwd": [_P] * 19 + [_I] * 4 + [_P],
     "b200mar_attn_fwd": [_P] * 11 + [_I] * 5 + [_P],
-    "b200mar_attn_tc_fwd": [_P] * 11 + [_I] * 5 + [_P],
+    "b200mar_attn_tc_fwd": [_P] * 11 + [_I] * 6 + [_P],
     "b200mar_attn_bwd": [_P] * 21 + [_I] * 5 + [_P],
     "b200mar_mlp_fwd": [_P] * 10 + [_L, _P],
     "b200mar_mlp_bwd": [_P] * 15 + [_L, _P],
-    "b200mar_mlp_tc_fwd": [_P] * 10 + [_L, _P],
+    "b200mar_mlp_tc_fwd": [_P] * 11 + [_I, _L, _P],
     "b200mar_tc_error": [],
     "b200mar_tc_probe": [_P] * 3 + [_I] * 4 + [_P],
     "b200mar_patch_merge_fwd": [_P] * 5 + [_I] * 3 + [_P],
@@ -78,7 +78,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
     def compile_one(src):
         obj = os.path.join(objdir, src[:-3] + ".o")
-        cmd = ["nvcc", *NVCC_FLAGS, "-I", INCLUDE, "-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = ["nvcc", *NVCC_FLAGS, *os.environ.get("B200MAR_NVCC_EXTRA", "").split(), "-I", INCLUDE, "-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         r = subprocess.run(cmd, capture_output=True, text=True)

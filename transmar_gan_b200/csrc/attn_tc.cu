@@ -38,6 +38,20 @@ namespace b200mar {
 
 B200MAR_DEFINE_TC_ERROR_GETTER(tc_error_attn)
 
+// Optional phase profile (compile with -DB200MAR_ATTN_PROF): cycles spent by one thread (block 0,
+// worker 0, lane 0 of warp 1) between successive PROF(i) marks, summed per phase i.
+#ifdef B200MAR_ATTN_PROF
+__device__ unsigned long long g_attn_prof[32];
+#define PROF_DECL __shared__ unsigned long long s_prof[32]; if (threadIdx.x < 32) s_prof[threadIdx.x] = 0; __syncthreads(); \
+  long long prof_t = clock64(); const bool prof_on = blockIdx.x == 0 && threadIdx.x == 32;
+#define PROF(i) do { if (prof_on) { const long long t_ = clock64(); s_prof[i] += (unsigned long long)(t_ - prof_t); prof_t = clock64(); } } while (0)
+#define PROF_FLUSH do { if (prof_on) for (int i_ = 0; i_ < 32; ++i_) g_attn_prof[i_] += s_prof[i_]; } while (0)
+#else
+#define PROF_DECL
+#define PROF(i)
+#define PROF_FLUSH
+#endif
+
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr int kWorkers = 3;
 constexpr int kVChunk = 528;                   // bytes between successive 4-key chunks of V^T (fp32):
@@ -52,8 +66,9 @@ struct AttnTcSmem {                            // BYTE offsets
   static constexpr int oLnW = oBp + 256;
   static constexpr int oLnB = oLnW + 256;
   static constexpr int oScale = oLnB + 256;     // [0,6): logit scales, [6]: inverse of the qkv weight scale, [7]: scratch
-  static constexpr int oBias = oScale + 32;    // fp32 [6][228], pre-multiplied by log2(e)
-  static constexpr int oBar = oBias + 6 * 228 * 4;      // 3 workers x 4 mbarriers + tmem slot
+  static constexpr int oBias = ((oScale + 32 + 15) / 16) * 16;   // fp32 [6 heads][4 copies][228]: copy s holds
+                                               // T'[j + s], T' = (bias - max bias - scale) * log2(e)
+  static constexpr int oBar = oBias + 6 * 4 * 228 * 4;  // 3 workers x 4 mbarriers + tmem slot
   static constexpr int oWork = ((oBar + 128 + 127) / 128) * 128;
   // per worker; [X | Q | K | V] is also the 32 KB fp32 staging tile of the LayerNorm output
   static constexpr int wX = 0;                 // fp16 [128][64] (R = 128): X, later O
@@ -74,7 +89,10 @@ constexpr uint32_t kTQ = 0;      // 2 x 48: [q_h | k_h | v_h] accumulators, doub
                                  // O_h (32 columns) is written over buffer h&1 once it has been read
 constexpr uint32_t kTS = 96;     // 64: S; P (fp32) overwrites it; Y at the end
 
-template <int NH>
+// RESID = true : a = z + LN1(attn)            (the op's standalone contract)
+// RESID = false: a = LN1(attn) only; the consumer (mlp_tc with a_is_delta) adds z, which it reads
+//                anyway, so this kernel never re-reads z for the residual.
+template <int NH, bool RESID>
 __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnParams p) {
   using L = AttnTcSmem;
   constexpr int HD = kDim / NH, A = HD * NH;
@@ -147,9 +165,16 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
   if (tid < 64) { sBp[tid] = p.proj_b[tid]; sLnW[tid] = p.ln_w[tid]; sLnB[tid] = p.ln_b[tid]; }
   if (tid < NH) sScale[tid] = expf(fminf(p.logit_scale[tid], kLogitMax)) * kLog2e;
   if (tid == 0) sScale[6] = __uint_as_float(we << 23);    // 2^(we-127)
-  for (int i = tid; i < NH * 225; i += 128 * kWorkers) {
-    const int h = i / 225, e = i - h * 225;
-    sBias[h * 228 + e] = p.bias_table[e * NH + h] * kLog2e;
+  // relative-position bias, shifted by an upper bound of the head's logits so that the softmax
+  // needs no row maximum: logit <= scale_h * 1 + max_e bias[e,h]  ->  exponent argument <= ~0.
+  // Four copies, copy s starting at table entry s, make every 4-key group one aligned LDS.128.
+  for (int i = tid; i < NH * 4 * 228; i += 128 * kWorkers) {
+    const int h = i / (4 * 228), r = i - h * (4 * 228), sft = r / 228, j = r - sft * 228;
+    float mb = -3.0e38f;
+    for (int e = 0; e < 225; ++e) mb = fmaxf(mb, p.bias_table[e * NH + h]);
+    const float bound = expf(fminf(p.logit_scale[h], kLogitMax)) + mb;
+    const int e = j + sft;
+    sBias[i] = e < 225 ? (p.bias_table[e * NH + h] - bound) * kLog2e : 0.f;
   }
   if (tid == 0) {
     for (int i = 0; i < 4 * kWorkers; ++i) tc::mbar_init(bars + i, 1);
@@ -173,6 +198,11 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
   const int row = wq * 32 + lane;                 // token row of this thread == its TMEM lane
   const int wsel = wq >> 1, lrow = row & 63;      // window of the pair (warp-uniform), token inside it
   const int bias_base = ((lrow >> 3) * 15 + (lrow & 7)) + 112;   // rel_index(r, c) = bias_base - (15 ci + cj)
+  // keys (ci, cj0..cj0+3) need table entries lo..lo+3, lo = bias_base - 15 ci - cj0 - 3; copy
+  // s = lo mod 4 = (bias_base + ci + 1) mod 4 holds them 16-byte aligned at offset lo - s.
+  int bias_off[4];
+#pragma unroll
+  for (int m = 0; m < 4; ++m) bias_off[m] = bias_base + 227 * ((bias_base + m + 1) & 3);
 
   // operand descriptors are built once; one K = 16 step advances the start-address field (>>4)
   // by two 8-element k-chunks
@@ -190,7 +220,18 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
       tc::mma_f16(tbase + kTQ + buf * 48, dX + ks * 256, db + ks * (2 * L::kWRows), kI48, ks > 0);
   };
 
+  PROF_DECL
   for (int tile = blockIdx.x * kWorkers + wk; tile < ntile; tile += gridDim.x * kWorkers) {
+    PROF(0);
+    // ---- L2 prefetch of the NEXT tile's token row of this thread (two 128-byte lines)
+    {
+      const int nwin_ = (tile + gridDim.x * kWorkers) * 2 + wsel;
+      if (nwin_ < nwin) {
+        const float* zr = p.z + (size_t)slot_of(g, nwin_, lrow).tok * 64;
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(zr));
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(zr + 32));
+      }
+    }
     // ---- slot table of the two windows
     {
       const int win = tile * 2 + wsel;
@@ -266,6 +307,7 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
         mhi |= (uint32_t)(reg[c + 32] != rg) << c;
       }
     }
+    PROF(1);                                         // slot table + gather
     tc::fence_async_smem();
     tc::worker_sync(1 + wk);
     if (wq == 0) {                                   // warp-uniform: one elected lane issues
@@ -273,6 +315,7 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
       if (tc::elect_one()) { issue_qkv(0, 0); tc::mma_commit(barQ); }
       __syncwarp();
     }
+    PROF(2);                                         // sync + first qkv issue
 
     // per-head attention outputs of this row; indexed by the (rolled) head loop, so the array lives
     // in local memory: 10-16 stores per head, one 64-float read-back per tile
@@ -289,6 +332,7 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
       tc::mbar_wait(barQ + buf, (phQ >> buf) & 1u, &g_tc_error);
       phQ ^= 1u << buf;
       tc::tc_fence_after();
+      PROF(3);                                         // wait [q|k|v]
       float qkv[48];
       tc::tmem_ld48(tbase + lane_addr + kTQ + buf * 48, qkv);
       float qs = 0.f, ks = 0.f;
@@ -303,8 +347,8 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
           ks = fmaf(qkv[16 + d], qkv[16 + d], ks);
         }
       }
-      const float qmul = sScale[h] / fmaxf(sqrtf(qs), kNormEps);
-      const float kmul = 1.0f / fmaxf(sqrtf(ks), kNormEps);
+      const float qmul = sScale[h] * rsqrtf(fmaxf(qs, kNormEps * kNormEps));   // v / max(|v|, eps)
+      const float kmul = rsqrtf(fmaxf(ks, kNormEps * kNormEps));
       uint32_t qp[8], kp[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
@@ -313,6 +357,7 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
       }
       // ---- previous head's O: its PV MMAs read P (TMEM) and V^T (smem) and wrote O over the
       //      accumulator buffer that [q|k|v]_{h+1} will reuse: read it before anything is reused
+      PROF(4);                                         // qkv ld + normalise + pack
       if (h > 0) {
         tc::mbar_wait(barO, phO, &g_tc_error); phO ^= 1;
         tc::tc_fence_after();
@@ -321,6 +366,7 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
 #pragma unroll
         for (int d = 0; d < HD; ++d) o[(h - 1) * HD + d] = ov[d] * inv_prev;
       }
+      PROF(5);                                         // wait PV(h-1) + O read
       // ---- operands of head h: Q' = [q|0] or [0|q], K' = [k(w0)|k(w1)], V^T rows (window, d)
       {
         const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
@@ -336,9 +382,11 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
 #pragma unroll
         for (int d = 0; d < HD; ++d) vt[d * 4] = qkv[32 + d];
       }
+      PROF(6);                                         // operand stores
       tc::fence_async_smem();
       tc::tc_fence_before();
       tc::worker_sync(1 + wk);
+      PROF(7);                                         // fence + sync
       if (wq == 0) {
         tc::tc_fence_after();
         if (tc::elect_one()) {
@@ -354,13 +402,29 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
       }
       tc::mbar_wait(barS, phS, &g_tc_error); phS ^= 1;
       tc::tc_fence_after();
-      // ---- softmax of this row over its own window's 64 keys (log2 domain)
+      PROF(8);                                         // S issue + wait
+      // ---- softmax of this row over its own window's 64 keys (log2 domain).  Fast path: the bias
+      //      table is pre-shifted by the head's logit upper bound, so p = ex2(s + bias') <= ~1 with
+      //      no row maximum; a row whose true maximum lies > 100 octaves below the bound (possible
+      //      only with logit scales near the ln(100) clamp) underflows and sends the whole worker
+      //      through the exact max-subtracting path below.
+      bool bad;
       {
         float s[64];
         tc::tmem_ld64(tbase + lane_addr + kTS, s);
-        const float* bias = sBias + h * 228 + bias_base;
+        const float* bh = sBias + h * (4 * 228);
 #pragma unroll
-        for (int c = 0; c < 64; ++c) s[c] += bias[-((c >> 3) * 15 + (c & 7))];
+        for (int ci = 0; ci < 8; ++ci) {
+          const float* bp = bh + bias_off[ci & 3];
+#pragma unroll
+          for (int g4 = 0; g4 < 2; ++g4) {
+            const float4 b = *reinterpret_cast<const float4*>(bp - (15 * ci + 4 * g4 + 3));
+            s[ci * 8 + g4 * 4 + 0] += b.w;
+            s[ci * 8 + g4 * 4 + 1] += b.z;
+            s[ci * 8 + g4 * 4 + 2] += b.y;
+            s[ci * 8 + g4 * 4 + 3] += b.x;
+          }
+        }
         if (mlo | mhi) {
 #pragma unroll
           for (int c = 0; c < 32; ++c) {
@@ -368,18 +432,52 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
             if ((mhi >> c) & 1u) s[c + 32] += -100.0f * kLog2e;
           }
         }
-        float mx = s[0];
-#pragma unroll
-        for (int c = 1; c < 64; ++c) mx = fmaxf(mx, s[c]);
         float sum4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-        for (int c = 0; c < 64; ++c) { s[c] = tc::ex2_approx(s[c] - mx); sum4[c & 3] += s[c]; }
-        inv_prev = 1.0f / ((sum4[0] + sum4[1]) + (sum4[2] + sum4[3]));
+        for (int c = 0; c < 64; ++c) { s[c] = tc::ex2_approx(s[c]); sum4[c & 3] += s[c]; }
+        const float sum = (sum4[0] + sum4[1]) + (sum4[2] + sum4[3]);
+        bad = !(sum >= 7.8886090522101181e-31f);         // 2^-100 (also catches NaN)
+        inv_prev = 1.0f / sum;
         tc::tmem_st64(tbase + lane_addr + kTS, s);       // unnormalised P (tf32 operand) over S
         tc::tmem_wait_st();
       }
+      PROF(9);                                         // softmax + P store
       tc::tc_fence_before();
-      tc::worker_sync(1 + wk);
+      const bool redo = tc::worker_sync_or(1 + wk, bad);
+      PROF(10);                                        // sync
+      if (redo) {
+        // ---- exact path (rare): recompute S (Q', K' are still in shared memory), subtract the row max
+        if (wq == 0) {
+          tc::tc_fence_after();
+          if (tc::elect_one()) {
+            tc::mma_f16(tbase + kTS, dQ, dK, kI64, 0u);
+            tc::mma_f16(tbase + kTS, dQ + 256, dK + 128, kI64, 1u);
+            tc::mma_commit(barS);
+          }
+          __syncwarp();
+        }
+        tc::mbar_wait(barS, phS, &g_tc_error); phS ^= 1;
+        tc::tc_fence_after();
+        float s[64];
+        tc::tmem_ld64(tbase + lane_addr + kTS, s);
+        const float* bias = sBias + h * (4 * 228) + bias_base;     // copy 0 = the unshifted-index table
+#pragma unroll 8
+        for (int c = 0; c < 64; ++c) {
+          s[c] += bias[-((c >> 3) * 15 + (c & 7))];
+          if (((c < 32 ? mlo >> c : mhi >> (c - 32)) & 1u)) s[c] += -100.0f * kLog2e;
+        }
+        float mx = s[0];
+#pragma unroll
+        for (int c = 1; c < 64; ++c) mx = fmaxf(mx, s[c]);
+        float sum = 0.f;
+#pragma unroll
+        for (int c = 0; c < 64; ++c) { s[c] = tc::ex2_approx(s[c] - mx); sum += s[c]; }
+        inv_prev = 1.0f / sum;
+        tc::tmem_st64(tbase + lane_addr + kTS, s);
+        tc::tmem_wait_st();
+        tc::tc_fence_before();
+        tc::worker_sync(1 + wk);
+      }
       if (wq == 0) {
         tc::tc_fence_after();
         if (tc::elect_one()) {
@@ -390,7 +488,9 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
         }
         __syncwarp();
       }
+      PROF(11);                                        // PV issue
     }
+    PROF(16);                                          // PV issue (last head)
     // ---- last head's O, then the output projection
     {
       tc::mbar_wait(barO, phO, &g_tc_error); phO ^= 1;
@@ -418,6 +518,7 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
     }
     tc::mbar_wait(barS, phS, &g_tc_error); phS ^= 1;
     tc::tc_fence_after();
+    PROF(12);                                          // O tile + proj issue + wait
     // ---- + proj bias, LayerNorm(norm1) of the row held in registers -> fp32 staging tile (own row)
     {
       float y[64];
@@ -438,8 +539,10 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
                         y[kc * 4 + 2] * rstd * sLnW[kc * 4 + 2] + sLnB[kc * 4 + 2],
                         y[kc * 4 + 3] * rstd * sLnW[kc * 4 + 3] + sLnB[kc * 4 + 3]);
     }
+    PROF(13);                                          // LN epilogue
     tc::tc_fence_before();
     tc::worker_sync(1 + wk);
+    PROF(14);
     // ---- residual + scatter back to the source token positions (same mapping as the gather)
     {
       const int q = lane >> 3, m8 = lane & 7;
@@ -452,7 +555,7 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
           const int m = wq * 32 + (it >> 2) * 8 + m8, kc = (it & 3) * 4 + q;
           const int tok = sTok[m];
           zv[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (tok >= 0) zv[i] = __ldg(reinterpret_cast<const float4*>(p.z + (size_t)tok * 64 + kc * 4));
+          if (RESID && tok >= 0) zv[i] = __ldg(reinterpret_cast<const float4*>(p.z + (size_t)tok * 64 + kc * 4));
         }
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
@@ -467,19 +570,32 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
         }
       }
     }
+    PROF(15);                                          // copy-out
     tc::worker_sync(1 + wk);
   }
+  PROF_FLUSH;
   tc::tc_fence_before();
   __syncthreads();
   if (warp == 0) tc::tmem_dealloc<512>(*tmem_slot);
 }
 
-template <int NH>
+#ifdef B200MAR_ATTN_PROF
+}  // namespace b200mar
+extern "C" int b200mar_attn_prof(unsigned long long* out32, int reset) {
+  unsigned long long z[32] = {0};
+  if (cudaMemcpyFromSymbol(out32, b200mar::g_attn_prof, sizeof(z)) != cudaSuccess) return -1;
+  if (reset && cudaMemcpyToSymbol(b200mar::g_attn_prof, z, sizeof(z)) != cudaSuccess) return -1;
+  return 0;
+}
+namespace b200mar {
+#endif
+
+template <int NH, bool RESID>
 static int launch_attn_tc_fwd(const AttnParams& p, cudaStream_t st) {
   const size_t smem = AttnTcSmem::kBytes;
   static bool configured = false;
   if (!configured) {
-    B200MAR_CHECK(cudaFuncSetAttribute(attn_tc_fwd_kernel<NH>,
+    B200MAR_CHECK(cudaFuncSetAttribute(attn_tc_fwd_kernel<NH, RESID>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = true;
   }
@@ -487,7 +603,7 @@ static int launch_attn_tc_fwd(const AttnParams& p, cudaStream_t st) {
   const int ntile = (nwin + 1) / 2;
   int grid = (ntile + kWorkers - 1) / kWorkers;
   if (grid > sm_count()) grid = sm_count();
-  attn_tc_fwd_kernel<NH><<<grid, 128 * kWorkers, smem, st>>>(p);
+  attn_tc_fwd_kernel<NH, RESID><<<grid, 128 * kWorkers, smem, st>>>(p);
   B200MAR_CHECK(cudaGetLastError());
   return 0;
 }
@@ -498,7 +614,7 @@ extern "C" int b200mar_attn_tc_fwd(const float* z, const float* ctx, const float
                                    const float* qkv_b, const float* proj_w, const float* proj_b,
                                    const float* logit_scale, const float* bias_table,
                                    const float* ln_w, const float* ln_b, float* a, int B, int ph,
-                                   int pw, int nh, int shift, void* stream) {
+                                   int pw, int nh, int shift, int residual, void* stream) {
   using namespace b200mar;
   if (ph % kWin || pw % kWin || ph < kWin || pw < kWin || (shift != 0 && shift != kShift)) return -1;
   if ((long long)B * ph * pw >= (1ll << 31)) return -1;
@@ -507,7 +623,7 @@ extern "C" int b200mar_attn_tc_fwd(const float* z, const float* ctx, const float
   p.logit_scale = logit_scale; p.bias_table = bias_table; p.ln_w = ln_w; p.ln_b = ln_b;
   p.a = a; p.B = B; p.ph = ph; p.pw = pw; p.shift = shift;
   cudaStream_t st = (cudaStream_t)stream;
-  if (nh == 6) return launch_attn_tc_fwd<6>(p, st);
-  if (nh == 4) return launch_attn_tc_fwd<4>(p, st);
+  if (nh == 6) return residual ? launch_attn_tc_fwd<6, true>(p, st) : launch_attn_tc_fwd<6, false>(p, st);
+  if (nh == 4) return residual ? launch_attn_tc_fwd<4, true>(p, st) : launch_attn_tc_fwd<4, false>(p, st);
   return -1;
 }

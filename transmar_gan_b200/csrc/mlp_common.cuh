@@ -15,6 +15,8 @@ struct MlpParams {
   const float* ln_b;    // [64]
   float* out;           // a + LN2(mlp(a))           (may be null)
   float* zsum;          // out + z                    (may be null)
+  float* a_out;         // mlp_tc with a_is_delta: the materialised a = z + delta (may be null)
+  int a_is_delta;       // mlp_tc: `a` holds LN1(attn) only and the kernel forms a = z + a
   // backward only
   const float* dout;
   float* da;

@@ -148,12 +148,23 @@ __global__ void __launch_bounds__(128 * kMlpWorkers, 1) mlp_tc_fwd_kernel(MlpPar
 #pragma unroll
       for (int half = 0; half < 2; ++half) {
         float4 xv[8];
+        {
+          float4 zv[8];
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int it = half * 8 + i;
-          const int m = wq * 32 + (it >> 2) * 8 + m8, kc = (it & 3) * 4 + q;
-          xv[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (m < valid) xv[i] = __ldg(reinterpret_cast<const float4*>(p.a + (size_t)(tok0 + m) * 64 + kc * 4));
+          for (int i = 0; i < 8; ++i) {
+            const int it = half * 8 + i;
+            const int m = wq * 32 + (it >> 2) * 8 + m8, kc = (it & 3) * 4 + q;
+            xv[i] = zv[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (m < valid) {
+              const size_t gi = (size_t)(tok0 + m) * 64 + kc * 4;
+              xv[i] = __ldg(reinterpret_cast<const float4*>(p.a + gi));
+              if (p.a_is_delta) zv[i] = __ldg(reinterpret_cast<const float4*>(p.z + gi));
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            xv[i].x += zv[i].x; xv[i].y += zv[i].y; xv[i].z += zv[i].z; xv[i].w += zv[i].w;
+          }
         }
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
@@ -261,7 +272,7 @@ __global__ void __launch_bounds__(128 * kMlpWorkers, 1) mlp_tc_fwd_kernel(MlpPar
           if (m < valid) {
             const size_t gi = (size_t)(tok0 + m) * 64 + kc * 4;
             av[i] = __ldg(reinterpret_cast<const float4*>(p.a + gi));
-            if (p.zsum) zv[i] = __ldg(reinterpret_cast<const float4*>(p.z + gi));
+            if (p.zsum || p.a_is_delta) zv[i] = __ldg(reinterpret_cast<const float4*>(p.z + gi));
           }
         }
 #pragma unroll
@@ -271,6 +282,10 @@ __global__ void __launch_bounds__(128 * kMlpWorkers, 1) mlp_tc_fwd_kernel(MlpPar
           if (m < valid) {
             const float4 y = *reinterpret_cast<const float4*>(sStage + kc * 512 + m * 4);
             const size_t gi = (size_t)(tok0 + m) * 64 + kc * 4;
+            if (p.a_is_delta) {
+              av[i].x += zv[i].x; av[i].y += zv[i].y; av[i].z += zv[i].z; av[i].w += zv[i].w;
+              if (p.a_out) *reinterpret_cast<float4*>(p.a_out + gi) = av[i];
+            }
             const float4 o = make_float4(av[i].x + y.x, av[i].y + y.y, av[i].z + y.z, av[i].w + y.w);
             if (p.out) *reinterpret_cast<float4*>(p.out + gi) = o;
             if (p.zsum)
@@ -292,13 +307,15 @@ __global__ void __launch_bounds__(128 * kMlpWorkers, 1) mlp_tc_fwd_kernel(MlpPar
 extern "C" int b200mar_mlp_tc_fwd(const float* a, const float* z, const float* fc1_w,
                                   const float* fc1_b, const float* fc2_w, const float* fc2_b,
                                   const float* ln_w, const float* ln_b, float* out, float* zsum,
-                                  long long n_tok, void* stream) {
+                                  float* a_out, int a_is_delta, long long n_tok, void* stream) {
   using namespace b200mar;
   if (n_tok <= 0 || n_tok % kTok) return -1;
-  if (zsum && !z) return -1;
+  if ((zsum || a_is_delta) && !z) return -1;
+  if (a_out && !a_is_delta) return -1;
   MlpParams p{};
   p.a = a; p.z = z; p.fc1_w = fc1_w; p.fc1_b = fc1_b; p.fc2_w = fc2_w; p.fc2_b = fc2_b;
   p.ln_w = ln_w; p.ln_b = ln_b; p.out = out; p.zsum = zsum; p.n_tok = n_tok;
+  p.a_out = a_out; p.a_is_delta = a_is_delta;
   const size_t smem = MlpTcSmem::kBytes;
   static bool configured = false;
   if (!configured) {

@@ -220,6 +220,17 @@ __device__ __forceinline__ void worker_sync(int id) {
   asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory");
 }
 
+// named barrier of one 128-thread worker with an OR reduction of a per-thread predicate
+__device__ __forceinline__ bool worker_sync_or(int id, bool pred) {
+  uint32_t r;
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\t"
+      "setp.ne.u32 q, %2, 0;\n\t"
+      "bar.red.or.pred p, %1, 128, q;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(r) : "r"(id), "r"((uint32_t)pred) : "memory");
+  return r != 0;
+}
 // chunk-major operand addressing (floats): element (r, k) of an R-row tile
 __device__ __forceinline__ int cm_off(int R, int r, int k) { return (k >> 2) * (R * 4) + r * 4 + (k & 3); }
 

@@ -132,7 +132,7 @@ class NSTB(nn.Module):
     def forward(self, z, num_patches, want_out=True, want_zsum=True):
         ph, pw = num_patches
         out, zsum = ops.NSTBFunction.apply(z, ph, pw, self.num_heads, self.shift_size, want_out,
-                                           want_zsum, *self.kernel_params())
+                                           want_zsum, torch.is_grad_enabled(), *self.kernel_params())
         return out, zsum
 
 

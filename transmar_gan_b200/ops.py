@@ -166,17 +166,20 @@ def _(z, ctx, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, ln_w, ln_b,
 @torch.library.custom_op(f"{_NS}::attn_tc_fwd", mutates_args=())
 def attn_tc_fwd(z: Tensor, ctx: Tensor, qkv_w: Tensor, qkv_b: Tensor, proj_w: Tensor, proj_b: Tensor,
                 logit_scale: Tensor, bias_table: Tensor, ln_w: Tensor, ln_b: Tensor,
-                ph: int, pw: int, nh: int, shift: int) -> Tensor:
-    """attn_fwd on the tcgen05 tensor cores (TF32 operands, fp32 accumulate in TMEM)."""
+                ph: int, pw: int, nh: int, shift: int, residual: bool = True) -> Tensor:
+    """attn_fwd on the tcgen05 tensor cores (fp16 / tf32 operands, fp32 accumulate in TMEM).
+    residual=False returns LN1(attn) only (mlp_tc_fwd with a_is_delta=True adds z)."""
     _chk(z, ctx, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, ln_w, ln_b)
     a = torch.empty_like(z)
     _call("attn_tc_fwd", _p(z), _p(ctx), _p(qkv_w), _p(qkv_b), _p(proj_w), _p(proj_b), _p(logit_scale),
-          _p(bias_table), _p(ln_w), _p(ln_b), _p(a), z.shape[0], ph, pw, nh, shift, _stream())
+          _p(bias_table), _p(ln_w), _p(ln_b), _p(a), z.shape[0], ph, pw, nh, shift, int(residual),
+          _stream(), meta=(z.shape[0], ph, pw, nh, shift))
     return a
 
 
 @attn_tc_fwd.register_fake
-def _(z, ctx, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, ln_w, ln_b, ph, pw, nh, shift):
+def _(z, ctx, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, ln_w, ln_b, ph, pw, nh, shift,
+      residual=True):
     return torch.empty_like(z)
 
 
@@ -211,21 +214,25 @@ def _(a, z, fc1_w, fc1_b, fc2_w, fc2_b, ln_w, ln_b, want_out, want_zsum):
 
 @torch.library.custom_op(f"{_NS}::mlp_tc_fwd", mutates_args=())
 def mlp_tc_fwd(a: Tensor, z: Optional[Tensor], fc1_w: Tensor, fc1_b: Tensor, fc2_w: Tensor,
-               fc2_b: Tensor, ln_w: Tensor, ln_b: Tensor, want_out: bool,
-               want_zsum: bool) -> Tuple[Tensor, Tensor]:
-    """mlp_fwd on the tcgen05 tensor cores (TF32 operands, fp32 accumulate in TMEM)."""
+               fc2_b: Tensor, ln_w: Tensor, ln_b: Tensor, want_out: bool, want_zsum: bool,
+               a_is_delta: bool = False, want_a: bool = False) -> Tuple[Tensor, Tensor, Tensor]:
+    """mlp_fwd on the tcgen05 tensor cores (fp16 operands, fp32 accumulate in TMEM).
+    a_is_delta=True: `a` holds LN1(attn) only and the kernel forms a = z + a itself; want_a
+    additionally materialises that sum (third result) for the backward."""
     _chk(a, z, fc1_w, fc1_b, fc2_w, fc2_b, ln_w, ln_b)
     out = torch.empty_like(a) if want_out else a.new_empty(0)
     zsum = torch.empty_like(a) if want_zsum else a.new_empty(0)
+    a_out = torch.empty_like(a) if want_a else a.new_empty(0)
     _call("mlp_tc_fwd", _p(a), _p(z), _p(fc1_w), _p(fc1_b), _p(fc2_w), _p(fc2_b), _p(ln_w), _p(ln_b),
-          _p(out), _p(zsum), a.numel() // 64, _stream())
-    return out, zsum
+          _p(out), _p(zsum), _p(a_out), int(a_is_delta), a.numel() // 64, _stream(), meta=(a.numel() // 64,))
+    return out, zsum, a_out
 
 
 @mlp_tc_fwd.register_fake
-def _(a, z, fc1_w, fc1_b, fc2_w, fc2_b, ln_w, ln_b, want_out, want_zsum):
+def _(a, z, fc1_w, fc1_b, fc2_w, fc2_b, ln_w, ln_b, want_out, want_zsum, a_is_delta=False, want_a=False):
     return (torch.empty_like(a) if want_out else a.new_empty(0),
-            torch.empty_like(a) if want_zsum else a.new_empty(0))
+            torch.empty_like(a) if want_zsum else a.new_empty(0),
+            torch.empty_like(a) if want_a else a.new_empty(0))
 
 
 def tc_error() -> int:
@@ -404,16 +411,23 @@ class NSTBFunction(torch.autograd.Function):
     Saves only z, u, ctx, a; everything else is recomputed in the backward kernels."""
 
     @staticmethod
-    def forward(ctx_, z, ph, pw, nh, shift, want_out, want_zsum, *params):
+    def forward(ctx_, z, ph, pw, nh, shift, want_out, want_zsum, save, *params):
         P = [p.detach() for p in params]
         u = unigram_fwd(z, P[0], P[1], ph, pw)
         c = ngram_ctx_fwd(u, P[2], P[3], P[4], P[5], P[6], P[7], P[8], P[9], nh)
-        tc = _PRECISION == "tf32"
-        a = (attn_tc_fwd if tc else attn_fwd)(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16],
-                                              P[17], ph, pw, nh, shift)
-        out, zsum = (mlp_tc_fwd if tc else mlp_fwd)(a, z if want_zsum else None, P[18], P[19], P[20],
-                                                    P[21], P[22], P[23], want_out, want_zsum)
-        ctx_.save_for_backward(z, u, c, a, *params)
+        if _PRECISION == "tf32":
+            # (attn_tc_fwd(residual=False) + mlp_tc_fwd(a_is_delta=True) moves the residual add into
+            # the MLP kernel; measured on B200 it costs the MLP more than it saves the attention)
+            a = attn_tc_fwd(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw, nh,
+                            shift, True)
+            out, zsum, _ = mlp_tc_fwd(a, z if want_zsum else None, P[18], P[19], P[20], P[21], P[22],
+                                      P[23], want_out, want_zsum, False, False)
+        else:
+            a = attn_fwd(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw, nh, shift)
+            out, zsum = mlp_fwd(a, z if want_zsum else None, P[18], P[19], P[20], P[21], P[22], P[23],
+                                want_out, want_zsum)
+        if save:
+            ctx_.save_for_backward(z, u, c, a, *params)
         ctx_.geom = (ph, pw, nh, shift)
         ctx_.mark_non_differentiable(*([] if want_out else [out]), *([] if want_zsum else [zsum]))
         return out, zsum
@@ -446,7 +460,7 @@ class NSTBFunction(torch.autograd.Function):
         unigram_bwd(z, P[0], du, dz, G[0], G[1], ph, pw)
         if have_zs:
             dz += g_zsum
-        return (dz, None, None, None, None, None, None, *G)
+        return (dz, None, None, None, None, None, None, None, *G)
 
 
 class PatchMergeFunction(torch.autograd.Function):
