@@ -118,8 +118,8 @@ int b200mar_mlp_fwd(const float* a, const float* z,
                     const float* fc2_w /*[64,128]*/, const float* fc2_b /*[64]*/,
                     const float* ln_w, const float* ln_b,
                     float* out, float* zsum, long long n_tok, void* stream);
-/* Same contract as b200mar_mlp_fwd, computed on the tcgen05 tensor cores (kind::tf32 operands,
- * fp32 accumulate in TMEM): 128-token tiles, two workers per persistent CTA.                */
+/* Same contract as b200mar_mlp_fwd, computed on the tcgen05 tensor cores (kind::f16 operands with
+ * power-of-two range scaling, fp32 accumulate in TMEM): 128-token tiles, four workers per CTA. */
 int b200mar_mlp_tc_fwd(const float* a, const float* z,
                        const float* fc1_w, const float* fc1_b,
                        const float* fc2_w, const float* fc2_b,
@@ -128,6 +128,16 @@ int b200mar_mlp_tc_fwd(const float* a, const float* z,
                        long long n_tok, void* stream);
 /* a_is_delta = 1: `a` holds LN1(attn) only (b200mar_attn_tc_fwd with residual = 0) and the kernel
  * forms a = z + a itself (z required); a_out (optional) receives that sum for the backward.   */
+/* In-place form for the blocks inside a stage (components/encoder_decoder.py:138-141 consumes
+ * only the sum): out = a + LN2(mlp(a)) (optional, may be NULL) and z_inout += out (optional, may be
+ * NULL; at least one of the two).  Same arithmetic as b200mar_mlp_tc_fwd; the stream moves through
+ * TMA bulk tensor loads/stores and the sum is a TMA reduce-add, so z is never read by the SMs.
+ * Returns -2/-3 if the driver's tensor-map encoder is unavailable / rejects the buffers.          */
+int b200mar_mlp_tma_fwd(const float* a, float* z_inout,
+                        const float* fc1_w, const float* fc1_b,
+                        const float* fc2_w, const float* fc2_b,
+                        const float* ln_w, const float* ln_b,
+                        float* out, long long n_tok, void* stream);
 /* 1 if a tensor-core kernel of this process ever timed out on an mbarrier (every wait is
  * bounded so a descriptor bug cannot hang the device); 0 otherwise; -1 on a CUDA error.     */
 int b200mar_tc_error(void);

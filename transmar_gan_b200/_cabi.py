@@ -38,6 +38,7 @@ SIGNATURES = {
     "b200mar_mlp_fwd": [_P] * 10 + [_L, _P],
     "b200mar_mlp_bwd": [_P] * 15 + [_L, _P],
     "b200mar_mlp_tc_fwd": [_P] * 11 + [_I, _L, _P],
+    "b200mar_mlp_tma_fwd": [_P] * 9 + [_L, _P],
     "b200mar_tc_error": [],
     "b200mar_tc_probe": [_P] * 3 + [_I] * 4 + [_P],
     "b200mar_patch_merge_fwd": [_P] * 5 + [_I] * 3 + [_P],

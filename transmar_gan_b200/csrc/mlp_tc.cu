@@ -17,6 +17,7 @@
 #include "common.cuh"
 #include "mlp_common.cuh"
 #include "tc.cuh"
+#include "tma.cuh"
 #include <cuda_fp16.h>
 
 namespace b200mar {
@@ -44,7 +45,7 @@ struct MlpTcSmem {                                   // BYTE offsets
 
 // GELU(x) = 0.5 x (1 + erf(x / sqrt 2)) with erf from Abramowitz & Stegun 7.1.26
 // (|error| <= 1.5e-7, two MUFU ops) instead of the ~25-instruction erff.
-__device__ __forceinline__ float gelu_fast(float x) {
+__device__ __forceinline__ float gelu_fast(float x, float half_scale) {
   const float z = fabsf(x) * 0.70710678118654752440f;
   const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
   float p = fmaf(1.061405429f, t, -1.453152027f);
@@ -53,9 +54,86 @@ __device__ __forceinline__ float gelu_fast(float x) {
   p = fmaf(p, t, 0.254829592f);
   const float e = tc::ex2_approx(-z * z * 1.4426950408889634f);
   const float erf_abs = fmaf(-p * t, e, 1.0f);       // erf(|x|/sqrt2)
-  const float hx = 0.5f * x;
+  const float hx = half_scale * x;
   return fmaf(hx, copysignf(erf_abs, x), hx);
 }
+
+// Power-of-two scale for a hidden row so that it cannot overflow fp16: |pre_j| <= amax * maxL1 + maxb
+// (amax = the power-of-two upper bound of the row's max|a|, maxL1 = max_j sum_k |W1[j][k]|,
+// maxb = max_j |b1[j]|) and |GELU(x)| <= |x|.  Returns 0.5 * scale (the GELU's half factor folded
+// in); *inv receives 1 / scale.  scale = 1 whenever the bound is below 2^15, i.e. always in practice.
+__device__ __forceinline__ float hidden_half_scale(float amax, float maxL1, float maxb, float* inv) {
+  const float bound = fmaf(amax, maxL1, maxb);
+  uint32_t eb = (__float_as_uint(bound) >> 23) & 0xFFu;            // bound < 2^(eb-126)
+  eb = eb < 141u ? 141u : (eb > 254u ? 254u : eb);
+  *inv = __uint_as_float((eb - 14u) << 23);
+  return __uint_as_float((267u - eb) << 23);                       // 0.5 * 2^(141-eb)
+}
+
+// Stage fc1/fc2 as fp16 K-major operands, each matrix scaled by one power of two (the inverse
+// scales go to sMisc[0], sMisc[1]); biases and LN affine as fp32.  Called by all `nthreads` threads;
+// contains __syncthreads().
+__device__ __forceinline__ void stage_mlp_weights_f16(const MlpParams& p, __half* sW1, __half* sW2,
+                                                      float* sB1, float* sB2, float* sLnW,
+                                                      float* sLnB, float* sMisc, int nthreads) {
+  const int tid = threadIdx.x;
+  uint32_t* sMax = reinterpret_cast<uint32_t*>(sMisc + 2);     // [2],[3]: scratch; [4]: maxL1; [5]: maxb
+  if (tid < 4) sMax[tid] = 0u;
+  __syncthreads();
+  {
+    float m1 = 0.f, m2 = 0.f;
+    for (int i = tid; i < 128 * 64; i += nthreads) {
+      m1 = fmaxf(m1, fabsf(p.fc1_w[i]));
+      m2 = fmaxf(m2, fabsf(p.fc2_w[i]));
+    }
+    atomicMax(sMax, __float_as_uint(m1));
+    atomicMax(sMax + 1, __float_as_uint(m2));
+  }
+  if (tid < 128) {
+    float l1 = 0.f;
+    for (int k = 0; k < 64; ++k) l1 += fabsf(p.fc1_w[tid * 64 + k]);
+    atomicMax(sMax + 2, __float_as_uint(l1));
+    atomicMax(sMax + 3, __float_as_uint(fabsf(p.fc1_b[tid])));
+  }
+  __syncthreads();
+  uint32_t e1 = (sMax[0] >> 23) & 0xFFu, e2 = (sMax[1] >> 23) & 0xFFu;
+  e1 = e1 < 1u ? 127u : (e1 > 253u ? 253u : e1);
+  e2 = e2 < 1u ? 127u : (e2 > 253u ? 253u : e2);
+  const float sc1 = __uint_as_float((254u - e1) << 23), sc2 = __uint_as_float((254u - e2) << 23);
+  __syncthreads();
+  if (tid == 0) { sMisc[0] = __uint_as_float(e1 << 23); sMisc[1] = __uint_as_float(e2 << 23); }
+  for (int idx = tid; idx < 128 * 8; idx += nthreads) {                 // fc1 [128][64]
+    const int n = idx & 127, kc = idx >> 7;
+    const float4* src = reinterpret_cast<const float4*>(p.fc1_w + n * 64 + kc * 8);
+    const float4 a = src[0], b = src[1];
+    *reinterpret_cast<uint4*>(sW1 + kc * 1024 + n * 8) =
+        make_uint4(tc::pack_f16(a.x * sc1, a.y * sc1), tc::pack_f16(a.z * sc1, a.w * sc1),
+                   tc::pack_f16(b.x * sc1, b.y * sc1), tc::pack_f16(b.z * sc1, b.w * sc1));
+  }
+  for (int idx = tid; idx < 64 * 16; idx += nthreads) {                 // fc2 [64][128]
+    const int n = idx & 63, kc = idx >> 6;
+    const float4* src = reinterpret_cast<const float4*>(p.fc2_w + n * 128 + kc * 8);
+    const float4 a = src[0], b = src[1];
+    *reinterpret_cast<uint4*>(sW2 + kc * 512 + n * 8) =
+        make_uint4(tc::pack_f16(a.x * sc2, a.y * sc2), tc::pack_f16(a.z * sc2, a.w * sc2),
+                   tc::pack_f16(b.x * sc2, b.y * sc2), tc::pack_f16(b.z * sc2, b.w * sc2));
+  }
+  if (tid < 128) sB1[tid] = p.fc1_b[tid];
+  if (tid < 64) { sB2[tid] = p.fc2_b[tid]; sLnW[tid] = p.ln_w[tid]; sLnB[tid] = p.ln_b[tid]; }
+}
+
+// Optional phase profile (compile with -DB200MAR_MLP_PROF): see attn_tc.cu.
+#ifdef B200MAR_MLP_PROF
+__device__ unsigned long long g_mlp_prof[32];
+#define PROF_DECL __shared__ unsigned long long s_prof[32]; if (threadIdx.x < 32) s_prof[threadIdx.x] = 0; __syncthreads(); \
+  long long prof_t = clock64(); const bool prof_on = blockIdx.x == 0 && threadIdx.x == 32;
+#define PROF(i) do { if (prof_on) { const long long t_ = clock64(); s_prof[i] += (unsigned long long)(t_ - prof_t); prof_t = clock64(); } } while (0)
+#define PROF_FLUSH do { if (prof_on) for (int i_ = 0; i_ < 32; ++i_) g_mlp_prof[i_] += s_prof[i_]; } while (0)
+#else
+#define PROF_DECL
+#define PROF(i)
+#define PROF_FLUSH
+#endif
 
 __global__ void __launch_bounds__(128 * kMlpWorkers, 1) mlp_tc_fwd_kernel(MlpParams p) {
   using L = MlpTcSmem;
@@ -79,44 +157,7 @@ __global__ void __launch_bounds__(128 * kMlpWorkers, 1) mlp_tc_fwd_kernel(MlpPar
   uint64_t* bar1 = bars + wk * 2;
   uint64_t* bar2 = bar1 + 1;
 
-  // ---- stage the weights as fp16 K-major operands, each scaled by one power of two
-  uint32_t* sMax = reinterpret_cast<uint32_t*>(sMisc + 2);
-  if (tid < 2) sMax[tid] = 0u;
-  __syncthreads();
-  {
-    float m1 = 0.f, m2 = 0.f;
-    for (int i = tid; i < 128 * 64; i += 128 * kMlpWorkers) {
-      m1 = fmaxf(m1, fabsf(p.fc1_w[i]));
-      m2 = fmaxf(m2, fabsf(p.fc2_w[i]));
-    }
-    atomicMax(sMax, __float_as_uint(m1));
-    atomicMax(sMax + 1, __float_as_uint(m2));
-  }
-  __syncthreads();
-  uint32_t e1 = (sMax[0] >> 23) & 0xFFu, e2 = (sMax[1] >> 23) & 0xFFu;
-  e1 = e1 < 1u ? 127u : (e1 > 253u ? 253u : e1);
-  e2 = e2 < 1u ? 127u : (e2 > 253u ? 253u : e2);
-  const float sc1 = __uint_as_float((254u - e1) << 23), sc2 = __uint_as_float((254u - e2) << 23);
-  __syncthreads();
-  if (tid == 0) { sMisc[0] = __uint_as_float(e1 << 23); sMisc[1] = __uint_as_float(e2 << 23); }
-  for (int idx = tid; idx < 128 * 8; idx += 128 * kMlpWorkers) {        // fc1 [128][64]
-    const int n = idx & 127, kc = idx >> 7;
-    const float4* src = reinterpret_cast<const float4*>(p.fc1_w + n * 64 + kc * 8);
-    const float4 a = src[0], b = src[1];
-    *reinterpret_cast<uint4*>(sW1 + kc * 1024 + n * 8) =
-        make_uint4(tc::pack_f16(a.x * sc1, a.y * sc1), tc::pack_f16(a.z * sc1, a.w * sc1),
-                   tc::pack_f16(b.x * sc1, b.y * sc1), tc::pack_f16(b.z * sc1, b.w * sc1));
-  }
-  for (int idx = tid; idx < 64 * 16; idx += 128 * kMlpWorkers) {        // fc2 [64][128]
-    const int n = idx & 63, kc = idx >> 6;
-    const float4* src = reinterpret_cast<const float4*>(p.fc2_w + n * 128 + kc * 8);
-    const float4 a = src[0], b = src[1];
-    *reinterpret_cast<uint4*>(sW2 + kc * 512 + n * 8) =
-        make_uint4(tc::pack_f16(a.x * sc2, a.y * sc2), tc::pack_f16(a.z * sc2, a.w * sc2),
-                   tc::pack_f16(b.x * sc2, b.y * sc2), tc::pack_f16(b.z * sc2, b.w * sc2));
-  }
-  if (tid < 128) sB1[tid] = p.fc1_b[tid];
-  if (tid < 64) { sB2[tid] = p.fc2_b[tid]; sLnW[tid] = p.ln_w[tid]; sLnB[tid] = p.ln_b[tid]; }
+  stage_mlp_weights_f16(p, sW1, sW2, sB1, sB2, sLnW, sLnB, sMisc, 128 * kMlpWorkers);
   if (tid == 0) {
     for (int i = 0; i < 2 * kMlpWorkers; ++i) tc::mbar_init(bars + i, 1);
     tc::fence_barrier_init();
@@ -138,8 +179,10 @@ __global__ void __launch_bounds__(128 * kMlpWorkers, 1) mlp_tc_fwd_kernel(MlpPar
   const float w1inv = sMisc[0], w2inv = sMisc[1];
 
   const long long ntile = (p.n_tok + 127) / 128;
+  PROF_DECL
   for (long long tile = (long long)blockIdx.x * kMlpWorkers + wk; tile < ntile;
        tile += (long long)gridDim.x * kMlpWorkers) {
+    PROF(0);
     const long long tok0 = tile * 128;
     const int valid = (int)((p.n_tok - tok0) < 128 ? (p.n_tok - tok0) : 128);
     // ---- load the 128x64 tile (coalesced 64-byte segments), row-scale, convert to fp16
@@ -191,8 +234,10 @@ __global__ void __launch_bounds__(128 * kMlpWorkers, 1) mlp_tc_fwd_kernel(MlpPar
         }
       }
     }
+    PROF(1);                                          // load + convert
     tc::fence_async_smem();
     tc::worker_sync(1 + wk);
+    PROF(2);
     // ---- fc1: D1 [128 x 128]
     if (wq == 0) {
       tc::tc_fence_after();
@@ -204,8 +249,11 @@ __global__ void __launch_bounds__(128 * kMlpWorkers, 1) mlp_tc_fwd_kernel(MlpPar
       __syncwarp();
     }
     const float ainv = sRowInv[row] * w1inv;
+    float hinv;
+    const float hhalf = hidden_half_scale(2.0f * sRowInv[row], sMisc[4], sMisc[5], &hinv);
     tc::mbar_wait(bar1, ph1, &g_tc_error); ph1 ^= 1;
     tc::tc_fence_after();
+    PROF(3);                                          // fc1 issue + wait
     // ---- GELU epilogue, two halves of 64 hidden columns; packed fp16 hidden -> TMEM [0,64)
 #pragma unroll 1
     for (int half = 0; half < 2; ++half) {
@@ -215,15 +263,17 @@ __global__ void __launch_bounds__(128 * kMlpWorkers, 1) mlp_tc_fwd_kernel(MlpPar
       const float* b1 = sB1 + half * 64;
 #pragma unroll
       for (int c = 0; c < 64; c += 2) {
-        const float g0 = gelu_fast(fmaf(v[c], ainv, b1[c]));
-        const float g1 = gelu_fast(fmaf(v[c + 1], ainv, b1[c + 1]));
+        const float g0 = gelu_fast(fmaf(v[c], ainv, b1[c]), hhalf);
+        const float g1 = gelu_fast(fmaf(v[c + 1], ainv, b1[c + 1]), hhalf);
         hp[c >> 1] = __uint_as_float(tc::pack_f16(g0, g1));
       }
       tc::tmem_st32(tbase + lane_addr + half * 32, hp);
     }
     tc::tmem_wait_st();
+    PROF(4);                                          // GELU
     tc::tc_fence_before();
     tc::worker_sync(1 + wk);
+    PROF(5);
     // ---- fc2: D2 [128 x 64] = H [128 x 128] W2^T, A operand from TMEM
     if (wq == 0) {
       tc::tc_fence_after();
@@ -236,13 +286,16 @@ __global__ void __launch_bounds__(128 * kMlpWorkers, 1) mlp_tc_fwd_kernel(MlpPar
     }
     tc::mbar_wait(bar2, ph2, &g_tc_error); ph2 ^= 1;
     tc::tc_fence_after();
+    PROF(6);                                          // fc2 issue + wait
     // ---- LayerNorm(norm2) of the row held in registers -> fp32 staging tile (over the A operand)
     {
       float y[64];
       tc::tmem_ld64(tbase + lane_addr + 64, y);
       float mean = 0.f;
 #pragma unroll
-      for (int i = 0; i < 64; ++i) { y[i] = fmaf(y[i], w2inv, sB2[i]); mean += y[i]; }
+      const float yinv = w2inv * hinv;
+#pragma unroll
+      for (int i = 0; i < 64; ++i) { y[i] = fmaf(y[i], yinv, sB2[i]); mean += y[i]; }
       mean *= (1.0f / 64.f);
       float var = 0.f;
 #pragma unroll
@@ -256,8 +309,10 @@ __global__ void __launch_bounds__(128 * kMlpWorkers, 1) mlp_tc_fwd_kernel(MlpPar
                         y[kc * 4 + 2] * rstd * sLnW[kc * 4 + 2] + sLnB[kc * 4 + 2],
                         y[kc * 4 + 3] * rstd * sLnW[kc * 4 + 3] + sLnB[kc * 4 + 3]);
     }
+    PROF(7);                                          // LN
     tc::tc_fence_before();
     tc::worker_sync(1 + wk);
+    PROF(8);
     // ---- coalesced copy-out (same mapping as the load): out = a + LN(.), zsum = out + z
     {
       const int q = lane >> 3, m8 = lane & 7;
@@ -295,8 +350,231 @@ __global__ void __launch_bounds__(128 * kMlpWorkers, 1) mlp_tc_fwd_kernel(MlpPar
         }
       }
     }
+    PROF(9);                                          // copy-out
     tc::worker_sync(1 + wk);
+    PROF(10);
   }
+  PROF_FLUSH;
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc<512>(*tmem_slot);
+}
+
+#ifdef B200MAR_MLP_PROF
+}  // namespace b200mar
+extern "C" int b200mar_mlp_prof(unsigned long long* out32, int reset) {
+  unsigned long long z[32] = {0};
+  if (cudaMemcpyFromSymbol(out32, b200mar::g_mlp_prof, sizeof(z)) != cudaSuccess) return -1;
+  if (reset && cudaMemcpyToSymbol(b200mar::g_mlp_prof, z, sizeof(z)) != cudaSuccess) return -1;
+  return 0;
+}
+namespace b200mar {
+#endif
+
+
+// ================================================================================================
+// mlp_tma_fwd_kernel — the same arithmetic with the residual stream moved by the TMA engine, for the
+// in-place form of the within-stage sum (z += out):
+//   * the fp32 `a` tile arrives by two bulk tensor loads (128 B-swizzled boxes, tma.cuh) into one of
+//     TWO 32 KB buffers per worker, the next tile's load being issued while this tile computes;
+//   * thread t reads its row from the swizzled tile (conflict-free), scales/packs it to fp16 and puts it
+//     in TMEM as the A operand of fc1 (no shared-memory A tile);
+//   * out = a + LN2(.) is written back IN PLACE over the a tile by the same thread, then one bulk
+//     tensor store (out) and/or one bulk tensor REDUCE-ADD into z (z += out: the next block's input)
+//     drain it - z itself is never read by the SMs.
+// Three workers per CTA, TMEM 160 columns each: D1 [0,128) -> H [0,64) / D2 [64,128), A [128,160).
+constexpr int kTmaWorkers = 3;
+
+struct MlpTmaSmem {                                  // BYTE offsets (weights as MlpTcSmem)
+  static constexpr int oBar = MlpTcSmem::oBar;       // 3 workers x 4 mbarriers + tmem slot
+  static constexpr int oWork = ((oBar + 128 + 1023) / 1024) * 1024;
+  static constexpr int kWorkBytes = 2 * 32768;       // two swizzled fp32 [128][64] tiles
+  static constexpr int kBytes = oWork + kTmaWorkers * kWorkBytes;
+  static_assert(kBytes <= 232448, "mlp_tma shared memory exceeds 227 KB");
+};
+
+__global__ void __launch_bounds__(128 * kTmaWorkers, 1)
+mlp_tma_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapZ,
+                   const __grid_constant__ CUtensorMap mapOut, MlpParams p) {
+  using L = MlpTcSmem;
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  __half* sW1 = reinterpret_cast<__half*>(smem_raw + L::oW1);
+  __half* sW2 = reinterpret_cast<__half*>(smem_raw + L::oW2);
+  float* sB1 = reinterpret_cast<float*>(smem_raw + L::oB1);
+  float* sB2 = reinterpret_cast<float*>(smem_raw + L::oB2);
+  float* sLnW = reinterpret_cast<float*>(smem_raw + L::oLnW);
+  float* sLnB = reinterpret_cast<float*>(smem_raw + L::oLnB);
+  float* sMisc = reinterpret_cast<float*>(smem_raw + L::oMisc);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + MlpTmaSmem::oBar);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem_raw + MlpTmaSmem::oBar + kTmaWorkers * 32);
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  const int wk = warp >> 2, wq = warp & 3;
+  unsigned char* sWk = smem_raw + MlpTmaSmem::oWork + wk * MlpTmaSmem::kWorkBytes;
+  uint64_t* full = bars + wk * 4;                    // [0],[1]: tile buffers; [2]: fc1; [3]: fc2
+  uint64_t* bar1 = full + 2;
+  uint64_t* bar2 = full + 3;
+
+  stage_mlp_weights_f16(p, sW1, sW2, sB1, sB2, sLnW, sLnB, sMisc, 128 * kTmaWorkers);
+  if (tid == 0) {
+    for (int i = 0; i < 4 * kTmaWorkers; ++i) tc::mbar_init(bars + i, 1);
+    tc::fence_barrier_init();
+    tma::prefetch_desc(&mapA); tma::prefetch_desc(&mapZ); tma::prefetch_desc(&mapOut);
+  }
+  if (warp == 0) tc::tmem_alloc<512>(tmem_slot);
+  tc::fence_async_smem();
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+
+  const uint32_t tbase = *tmem_slot + wk * 160;
+  const uint32_t lane_addr = (uint32_t)(wq * 32) << 16;
+  constexpr uint32_t kI128 = tc::idesc_f16(128, 128), kI64 = tc::idesc_f16(128, 64);
+  const uint64_t dW1 = tc::smem_desc(tc::smem_u32(sW1), 2048, 128),
+                 dW2 = tc::smem_desc(tc::smem_u32(sW2), 1024, 128);
+  const int row = wq * 32 + lane;
+  const float w1inv = sMisc[0], w2inv = sMisc[1];
+  const bool leader = wq == 0 && lane == 0;          // bulk groups are per thread: one fixed thread
+  uint32_t ph1 = 0, ph2 = 0;
+
+  const long long ntile = (p.n_tok + 127) / 128;
+  const long long stride = (long long)gridDim.x * kTmaWorkers;
+  long long tile = (long long)blockIdx.x * kTmaWorkers + wk;
+  if (leader && tile < ntile) {
+    tma::mbar_expect_tx(full, 32768);
+    tma::load_2d(&mapA, full, sWk, 0, (int)(tile * 128));
+    tma::load_2d(&mapA, full, sWk + 16384, 32, (int)(tile * 128));
+  }
+  PROF_DECL
+  for (uint32_t it = 0; tile < ntile; tile += stride, ++it) {
+    const int b = it & 1;
+    unsigned char* buf = sWk + b * 32768;
+    PROF(0);
+    tc::mbar_wait(full + b, (it >> 1) & 1, &g_tc_error);
+    PROF(1);                                          // wait for the a tile
+    // ---- own row -> power-of-two scale -> packed fp16 A operand in TMEM [128,160)
+    float ainv, hhalf, hinv;
+    {
+      float x[64];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const float4 v = *reinterpret_cast<const float4*>(buf + tma::tile_off(row, i));
+        x[4 * i] = v.x; x[4 * i + 1] = v.y; x[4 * i + 2] = v.z; x[4 * i + 3] = v.w;
+      }
+      float m0 = 0.f, m1 = 0.f, m2 = 0.f, m3 = 0.f;
+#pragma unroll
+      for (int i = 0; i < 64; i += 4) {
+        m0 = fmaxf(m0, fabsf(x[i])); m1 = fmaxf(m1, fabsf(x[i + 1]));
+        m2 = fmaxf(m2, fabsf(x[i + 2])); m3 = fmaxf(m3, fabsf(x[i + 3]));
+      }
+      uint32_t e = (__float_as_uint(fmaxf(fmaxf(m0, m1), fmaxf(m2, m3))) >> 23) & 0xFFu;
+      e = e < 1u ? 127u : (e > 253u ? 253u : e);
+      const float sc = __uint_as_float((254u - e) << 23);
+      ainv = __uint_as_float(e << 23) * w1inv;
+      hhalf = hidden_half_scale(2.0f * __uint_as_float(e << 23), sMisc[4], sMisc[5], &hinv);
+      float hp[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i)
+        hp[i] = __uint_as_float(tc::pack_f16(x[2 * i] * sc, x[2 * i + 1] * sc));
+      tc::tmem_st32(tbase + 128 + lane_addr, hp);
+    }
+    tc::tmem_wait_st();
+    tc::tc_fence_before();
+    tc::worker_sync(1 + wk);
+    PROF(2);                                          // row convert
+    // ---- fc1: D1 [128 x 128] = A (TMEM) W1^T; then prefetch the next tile into the other buffer
+    if (wq == 0) {
+      tc::tc_fence_after();
+      if (tc::elect_one()) {
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks)
+          tc::mma_f16_ts(tbase, tbase + 128 + ks * 8, dW1 + ks * 256, kI128, ks > 0);
+        tc::mma_commit(bar1);
+      }
+      __syncwarp();
+      if (lane == 0 && tile + stride < ntile) {
+        tma::wait_read_all();                         // the stores that drained the other buffer
+        unsigned char* nb = sWk + (b ^ 1) * 32768;
+        tma::mbar_expect_tx(full + (b ^ 1), 32768);
+        tma::load_2d(&mapA, full + (b ^ 1), nb, 0, (int)((tile + stride) * 128));
+        tma::load_2d(&mapA, full + (b ^ 1), nb + 16384, 32, (int)((tile + stride) * 128));
+      }
+      __syncwarp();
+    }
+    tc::mbar_wait(bar1, ph1, &g_tc_error); ph1 ^= 1;
+    tc::tc_fence_after();
+    PROF(3);
+    // ---- GELU epilogue, two halves of 64 hidden columns; packed fp16 hidden -> TMEM [0,64)
+#pragma unroll 1
+    for (int half = 0; half < 2; ++half) {
+      float v[64];
+      tc::tmem_ld64(tbase + lane_addr + half * 64, v);
+      float hp[32];
+      const float* b1 = sB1 + half * 64;
+#pragma unroll
+      for (int c = 0; c < 64; c += 2) {
+        const float g0 = gelu_fast(fmaf(v[c], ainv, b1[c]), hhalf);
+        const float g1 = gelu_fast(fmaf(v[c + 1], ainv, b1[c + 1]), hhalf);
+        hp[c >> 1] = __uint_as_float(tc::pack_f16(g0, g1));
+      }
+      tc::tmem_st32(tbase + lane_addr + half * 32, hp);
+    }
+    tc::tmem_wait_st();
+    PROF(4);
+    tc::tc_fence_before();
+    tc::worker_sync(1 + wk);
+    PROF(5);
+    if (wq == 0) {
+      tc::tc_fence_after();
+      if (tc::elect_one()) {
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          tc::mma_f16_ts(tbase + 64, tbase + ks * 8, dW2 + ks * 128, kI64, ks > 0);
+        tc::mma_commit(bar2);
+      }
+      __syncwarp();
+    }
+    tc::mbar_wait(bar2, ph2, &g_tc_error); ph2 ^= 1;
+    tc::tc_fence_after();
+    PROF(6);
+    // ---- LayerNorm(norm2) in registers; out = a + LN(.) in place over the a tile
+    {
+      float y[64];
+      tc::tmem_ld64(tbase + lane_addr + 64, y);
+      float mean = 0.f;
+#pragma unroll
+      const float yinv = w2inv * hinv;
+#pragma unroll
+      for (int i = 0; i < 64; ++i) { y[i] = fmaf(y[i], yinv, sB2[i]); mean += y[i]; }
+      mean *= (1.0f / 64.f);
+      float var = 0.f;
+#pragma unroll
+      for (int i = 0; i < 64; ++i) { y[i] -= mean; var = fmaf(y[i], y[i], var); }
+      const float rstd = 1.0f / sqrtf(var * (1.0f / 64.f) + kLnEps);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        float4* q = reinterpret_cast<float4*>(buf + tma::tile_off(row, i));
+        const float4 av = *q;
+        *q = make_float4(av.x + (y[4 * i + 0] * rstd * sLnW[4 * i + 0] + sLnB[4 * i + 0]),
+                         av.y + (y[4 * i + 1] * rstd * sLnW[4 * i + 1] + sLnB[4 * i + 1]),
+                         av.z + (y[4 * i + 2] * rstd * sLnW[4 * i + 2] + sLnB[4 * i + 2]),
+                         av.w + (y[4 * i + 3] * rstd * sLnW[4 * i + 3] + sLnB[4 * i + 3]));
+      }
+    }
+    PROF(7);
+    tc::fence_async_smem();                           // generic writes -> visible to the TMA engine
+    tc::tc_fence_before();
+    tc::worker_sync(1 + wk);
+    if (leader) {
+      const int r0 = (int)(tile * 128);
+      if (p.out) { tma::store_2d(&mapOut, buf, 0, r0); tma::store_2d(&mapOut, buf + 16384, 32, r0); }
+      if (p.zsum) { tma::reduce_add_2d(&mapZ, buf, 0, r0); tma::reduce_add_2d(&mapZ, buf + 16384, 32, r0); }
+      tma::commit_group();
+    }
+    PROF(8);
+  }
+  if (leader) tma::wait_all();
+  PROF_FLUSH;
   tc::tc_fence_before();
   __syncthreads();
   if (warp == 0) tc::tmem_dealloc<512>(*tmem_slot);
@@ -327,6 +605,35 @@ extern "C" int b200mar_mlp_tc_fwd(const float* a, const float* z, const float* f
   long long grid = (ntile + kMlpWorkers - 1) / kMlpWorkers;
   if (grid > sm_count()) grid = sm_count();
   mlp_tc_fwd_kernel<<<(int)grid, 128 * kMlpWorkers, smem, (cudaStream_t)stream>>>(p);
+  B200MAR_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200mar_mlp_tma_fwd(const float* a, float* z_inout, const float* fc1_w,
+                                   const float* fc1_b, const float* fc2_w, const float* fc2_b,
+                                   const float* ln_w, const float* ln_b, float* out,
+                                   long long n_tok, void* stream) {
+  using namespace b200mar;
+  if (n_tok <= 0 || n_tok % kTok || n_tok * 1 > 0x7fffffffLL) return -1;
+  if (!out && !z_inout) return -1;
+  MlpParams p{};
+  p.a = a; p.z = z_inout; p.fc1_w = fc1_w; p.fc1_b = fc1_b; p.fc2_w = fc2_w; p.fc2_b = fc2_b;
+  p.ln_w = ln_w; p.ln_b = ln_b; p.out = out; p.zsum = z_inout; p.n_tok = n_tok;
+  CUtensorMap mA, mZ, mO;
+  if (int rc = tma::encode_rows64(&mA, a, n_tok)) return rc;
+  if (int rc = tma::encode_rows64(&mZ, z_inout ? z_inout : a, n_tok)) return rc;
+  if (int rc = tma::encode_rows64(&mO, out ? out : a, n_tok)) return rc;
+  const size_t smem = MlpTmaSmem::kBytes;
+  static bool configured = false;
+  if (!configured) {
+    B200MAR_CHECK(cudaFuncSetAttribute(mlp_tma_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)smem));
+    configured = true;
+  }
+  const long long ntile = (n_tok + 127) / 128;
+  long long grid = (ntile + kTmaWorkers - 1) / kTmaWorkers;
+  if (grid > sm_count()) grid = sm_count();
+  mlp_tma_fwd_kernel<<<(int)grid, 128 * kTmaWorkers, smem, (cudaStream_t)stream>>>(mA, mZ, mO, p);
   B200MAR_CHECK(cudaGetLastError());
   return 0;
 }

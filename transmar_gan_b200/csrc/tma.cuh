@@ -1,0 +1,99 @@
+// tma.cuh — Tensor Memory Accelerator helpers (inline PTX, sm_100a): 2-D tiled tensor maps over the
+// token-major fp32 residual stream [n_tok][64], bulk tensor loads signalled on an mbarrier, bulk
+// tensor stores and reduce-add stores (bulk_group completion).
+//
+// Tile convention: a 128-token tile is moved as TWO boxes of [128 rows][32 floats] (inner extent
+// 128 B = the SWIZZLE_128B span).  In shared memory box h (channels 32h..32h+31) is a 16 KB block,
+// row r at byte r*128, and the 16-byte chunk c of that row sits at chunk slot c ^ (r & 7).  A thread
+// that owns row r and walks the chunks with a compile-time index therefore hits 8 distinct
+// 16-byte bank groups per quarter-warp: conflict-free whole-row access with static register indices.
+// Tile buffers must be 1024-byte aligned.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200mar {
+namespace tma {
+
+// byte offset of 16-byte chunk i (0..15) of row r inside a [2 boxes][128 rows][128 B] swizzled tile
+__device__ __forceinline__ uint32_t tile_off(int r, int i) {
+  return (uint32_t)((i >> 3) * 16384 + r * 128 + (((i & 7) ^ (r & 7)) << 4));
+}
+
+__device__ __forceinline__ void prefetch_desc(const CUtensorMap* m) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
+}
+
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(
+                   (uint32_t)__cvta_generic_to_shared(bar)),
+               "r"(bytes)
+               : "memory");
+}
+
+// global -> shared box load; completes `bytes of the box` on the mbarrier
+__device__ __forceinline__ void load_2d(const CUtensorMap* m, uint64_t* bar, void* smem_dst, int c0,
+                                        int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+
+// shared -> global box store (bulk_group)
+__device__ __forceinline__ void store_2d(const CUtensorMap* m, const void* smem_src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                   reinterpret_cast<uint64_t>(m)),
+               "r"((uint32_t)__cvta_generic_to_shared(smem_src)), "r"(c0), "r"(c1)
+               : "memory");
+}
+
+// shared -> global box reduction: global[box] += shared[box] (fp32 add, one add per element)
+__device__ __forceinline__ void reduce_add_2d(const CUtensorMap* m, const void* smem_src, int c0,
+                                              int c1) {
+  asm volatile(
+      "cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+          reinterpret_cast<uint64_t>(m)),
+      "r"((uint32_t)__cvta_generic_to_shared(smem_src)), "r"(c0), "r"(c1)
+      : "memory");
+}
+
+__device__ __forceinline__ void commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// all committed bulk groups of this thread have finished READING shared memory
+__device__ __forceinline__ void wait_read_all() {
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+// all committed bulk groups of this thread are complete (global writes performed)
+__device__ __forceinline__ void wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+// ---- host: tensor map over a token-major fp32 matrix [n_rows][64], box [128][32], 128 B swizzle.
+// cuTensorMapEncodeTiled is fetched through the runtime (no link-time libcuda dependency, so the
+// library also loads on a machine without a driver).
+inline int encode_rows64(CUtensorMap* out, const float* base, long long n_rows) {
+  typedef CUresult (*Fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                         const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                         CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                         CUtensorMapFloatOOBfill);
+  static Fn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess || !p)
+      return -2;
+    fn = reinterpret_cast<Fn>(p);
+  }
+  const cuuint64_t gdim[2] = {64, (cuuint64_t)n_rows};
+  const cuuint64_t gstride[1] = {256};
+  const cuuint32_t box[2] = {32, 128};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), gdim, gstride,
+                        box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -3;
+}
+
+}  // namespace tma
+}  // namespace b200mar

@@ -164,9 +164,15 @@ class _Stage(nn.Module):
         for its successor, so intermediate `out` tensors are never written."""
         z, n = x, len(self.blocks)
         out = zsum = None
+        inplace = not torch.is_grad_enabled() and ops.get_precision() == "tf32"
         for i, blk in enumerate(self.blocks):
             last = i == n - 1
-            out, zsum = blk(z, num_patches, want_out=last, want_zsum=(not last) or need_sum_last)
+            if inplace and i > 0:
+                # z is the previous block's zsum, private to this loop: the block adds into it
+                out, zsum = ops.nstb_infer_(z, *num_patches, blk.num_heads, blk.shift_size, last,
+                                            (not last) or need_sum_last, blk.kernel_params())
+            else:
+                out, zsum = blk(z, num_patches, want_out=last, want_zsum=(not last) or need_sum_last)
             z = zsum
         return out, zsum
 

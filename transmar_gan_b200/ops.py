@@ -235,6 +235,23 @@ def _(a, z, fc1_w, fc1_b, fc2_w, fc2_b, ln_w, ln_b, want_out, want_zsum, a_is_de
             torch.empty_like(a) if want_a else a.new_empty(0))
 
 
+@torch.library.custom_op(f"{_NS}::mlp_tma_fwd_", mutates_args=("z",))
+def mlp_tma_fwd_(a: Tensor, z: Optional[Tensor], fc1_w: Tensor, fc1_b: Tensor, fc2_w: Tensor,
+                 fc2_b: Tensor, ln_w: Tensor, ln_b: Tensor, want_out: bool) -> Tensor:
+    """In-place block tail: out = a + LN2(mlp(a)) (returned if want_out) and z += out (if z is given),
+    i.e. z becomes the next block's input.  TMA-fed variant of mlp_tc_fwd (same arithmetic)."""
+    _chk(a, z, fc1_w, fc1_b, fc2_w, fc2_b, ln_w, ln_b)
+    out = torch.empty_like(a) if want_out else a.new_empty(0)
+    _call("mlp_tma_fwd", _p(a), _p(z), _p(fc1_w), _p(fc1_b), _p(fc2_w), _p(fc2_b), _p(ln_w), _p(ln_b),
+          _p(out), a.numel() // 64, _stream(), meta=(a.numel() // 64,))
+    return out
+
+
+@mlp_tma_fwd_.register_fake
+def _(a, z, fc1_w, fc1_b, fc2_w, fc2_b, ln_w, ln_b, want_out):
+    return torch.empty_like(a) if want_out else a.new_empty(0)
+
+
 def tc_error() -> int:
     """Non-zero if a tensor-core kernel hit its bounded mbarrier wait (a bug, never expected)."""
     torch.cuda.synchronize()
@@ -401,6 +418,18 @@ NSTB_PARAM_NAMES = (
     "ffn.fc1.weight", "ffn.fc1.bias", "ffn.fc2.weight", "ffn.fc2.bias",
     "norm2.weight", "norm2.bias",
 )
+
+
+def nstb_infer_(z: Tensor, ph: int, pw: int, nh: int, shift: int, want_out: bool, want_zsum: bool,
+                params) -> Tuple[Tensor, Tensor]:
+    """Inference form of one NSTB for a PRIVATE stream buffer z (tensor-core precision only):
+    z is overwritten with zsum = out + z when want_zsum (the next block's input); nothing is saved."""
+    P = [p.detach() for p in params]
+    u = unigram_fwd(z, P[0], P[1], ph, pw)
+    c = ngram_ctx_fwd(u, P[2], P[3], P[4], P[5], P[6], P[7], P[8], P[9], nh)
+    a = attn_tc_fwd(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw, nh, shift, True)
+    out = mlp_tma_fwd_(a, z if want_zsum else None, P[18], P[19], P[20], P[21], P[22], P[23], want_out)
+    return out, (z if want_zsum else out.new_empty(0))
 
 
 class NSTBFunction(torch.autograd.Function):
