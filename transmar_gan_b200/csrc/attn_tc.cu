@@ -32,6 +32,7 @@
 #include "common.cuh"
 #include "attn_common.cuh"
 #include "tc.cuh"
+#include "tma.cuh"
 #include <cuda_fp16.h>
 
 namespace b200mar {
@@ -68,15 +69,15 @@ struct AttnTcSmem {                            // BYTE offsets
   static constexpr int oScale = oLnB + 256;     // [0,6): logit scales, [6]: inverse of the qkv weight scale, [7]: scratch
   static constexpr int oBias = ((oScale + 32 + 15) / 16) * 16;   // fp32 [6 heads][4 copies][228]: copy s holds
                                                // T'[j + s], T' = (bias - max bias - scale) * log2(e)
-  static constexpr int oBar = oBias + 6 * 4 * 228 * 4;  // 3 workers x 4 mbarriers + tmem slot
-  static constexpr int oWork = ((oBar + 128 + 127) / 128) * 128;
+  static constexpr int oBar = oBias + 6 * 4 * 228 * 4;  // 3 workers x 8 mbarrier slots (5 used) + tmem slot
+  static constexpr int oWork = ((oBar + 256 + 1023) / 1024) * 1024;   // 1 KB aligned: TMA 128 B swizzle
   // per worker; [X | Q | K | V] is also the 32 KB fp32 staging tile of the LayerNorm output
   static constexpr int wX = 0;                 // fp16 [128][64] (R = 128): X, later O
   static constexpr int wQ = wX + 128 * 64 * 2; // fp16 [128][32] (R = 128)
   static constexpr int wK = wQ + 128 * 32 * 2; // fp16 [64][32]  (R = 64)
   static constexpr int wV = wK + 64 * 32 * 2;  // fp32 [32 rows = (window, d)][64 keys], chunk stride kVChunk
   static constexpr int wTok = wV + 16 * kVChunk;
-  static constexpr int kWorkBytes = ((wTok + 4 * 128 * 4 + 127) / 128) * 128;   // tok, cwin, region, row scale
+  static constexpr int kWorkBytes = ((wTok + 4 * 128 * 4 + 1023) / 1024) * 1024;   // tok, cwin, region, row scale
   static constexpr int kBytes = oWork + kWorkers * kWorkBytes;
   static_assert(wTok >= 128 * 64 * 4, "fp32 staging tile must fit in [X|Q|K|V]");
   static_assert(oBar % 8 == 0, "mbarrier alignment");
@@ -93,10 +94,12 @@ constexpr uint32_t kTS = 96;     // 64: S; P (fp32) overwrites it; Y at the end
 // RESID = false: a = LN1(attn) only; the consumer (mlp_tc with a_is_delta) adds z, which it reads
 //                anyway, so this kernel never re-reads z for the residual.
 template <int NH, bool RESID>
-__global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnParams p) {
+__global__ void __launch_bounds__(128 * kWorkers, 1)
+attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_constant__ CUtensorMap mapA,
+                   AttnParams p) {
   using L = AttnTcSmem;
   constexpr int HD = kDim / NH, A = HD * NH;
-  extern __shared__ __align__(128) unsigned char smem_raw[];
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
   __half* sWqkv = reinterpret_cast<__half*>(smem_raw + L::oWqkv);
   float* sWp = reinterpret_cast<float*>(smem_raw + L::oWp);
   float* sBqkv = reinterpret_cast<float*>(smem_raw + L::oBqkv);
@@ -106,7 +109,7 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
   float* sScale = reinterpret_cast<float*>(smem_raw + L::oScale);
   float* sBias = reinterpret_cast<float*>(smem_raw + L::oBias);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + L::oBar);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem_raw + L::oBar + kWorkers * 32);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem_raw + L::oBar + kWorkers * 64);
   const int tid = threadIdx.x, lane = tid & 31;
   // warp-uniform ids (broadcast from lane 0 so that everything derived from them - smem / TMEM
   // addresses, MMA descriptors - stays in uniform registers)
@@ -118,13 +121,11 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
   unsigned char* sK = sW + L::wK;
   unsigned char* sV = sW + L::wV;
   float* sStage = reinterpret_cast<float*>(sW);            // fp32 [128][64] chunk-major, end of tile
-  int* sTok = reinterpret_cast<int*>(sW + L::wTok);
-  int* sCwin = sTok + 128;
-  int* sReg = sCwin + 128;
-  float* sRowInv = reinterpret_cast<float*>(sReg + 128);
-  uint64_t* barQ = bars + wk * 4;       // [2]
+  int* sReg = reinterpret_cast<int*>(sW + L::wTok) + 256;
+  uint64_t* barQ = bars + wk * 8;       // [2]
   uint64_t* barS = barQ + 2;
   uint64_t* barO = barQ + 3;
+  uint64_t* barZ = barQ + 4;            // TMA loads of the z tile
 
   // ---- stage the block's weights as K-major operands (once per CTA).  The qkv matrix is scaled by
   //      one power of two to max|w| in [1,2) so that fp16 keeps 11 significant bits at any scale.
@@ -177,8 +178,9 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
     sBias[i] = e < 225 ? (p.bias_table[e * NH + h] - bound) * kLog2e : 0.f;
   }
   if (tid == 0) {
-    for (int i = 0; i < 4 * kWorkers; ++i) tc::mbar_init(bars + i, 1);
+    for (int i = 0; i < 8 * kWorkers; ++i) tc::mbar_init(bars + i, 1);
     tc::fence_barrier_init();
+    tma::prefetch_desc(&mapZ); tma::prefetch_desc(&mapA);
   }
   if (warp == 0) tc::tmem_alloc<512>(tmem_slot);
   tc::fence_async_smem();
@@ -190,7 +192,7 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
   const uint32_t lane_addr = (uint32_t)(wq * 32) << 16;
   constexpr uint32_t kI48 = tc::idesc_f16(128, 48), kI64 = tc::idesc_f16(128, 64),
                      kT32 = tc::idesc_tf32(128, 32), kT64 = tc::idesc_tf32(128, 64);
-  uint32_t phQ = 0, phS = 0, phO = 0;
+  uint32_t phQ = 0, phS = 0, phO = 0, phZ = 0;
 
   const Geom g = make_geom(p.B, p.ph, p.pw, p.shift);
   const int nwin = g.B * g.wh * g.ww;
@@ -220,81 +222,109 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
       tc::mma_f16(tbase + kTQ + buf * 48, dX + ks * 256, db + ks * (2 * L::kWRows), kI48, ks > 0);
   };
 
+  // A window whose 8x8 token block is contiguous in the grid (all windows when shift = 0; all but the
+  // last window row / column when shifted) moves by TMA; the cyclically wrapped ones are rare
+  // (~4 %) and are read / written by their row threads directly.
+  auto tma_window = [&](int win, int& x0, int& y0, int& b) -> bool {
+    if (win >= nwin) return false;
+    const int w = win % g.ww, h = (win / g.ww) % g.wh;
+    b = win / (g.ww * g.wh);
+    x0 = w * kWin + g.shift;
+    y0 = h * kWin + g.shift;
+    return x0 + kWin <= g.pw && y0 + kWin <= g.ph;
+  };
+  // z tile of `tile_`: window w -> [2 channel halves][64 slots][128 B swizzled] at sW + w * 16 KB
+  auto issue_z_loads = [&](int tile_) {
+    int x0[2], y0[2], b[2];
+    const bool t0 = tma_window(tile_ * 2, x0[0], y0[0], b[0]);
+    const bool t1 = tma_window(tile_ * 2 + 1, x0[1], y0[1], b[1]);
+    if (!(t0 || t1)) return;
+    tma::mbar_expect_tx(barZ, ((int)t0 + (int)t1) * 16384);
+#pragma unroll
+    for (int w = 0; w < 2; ++w)
+      if (w == 0 ? t0 : t1) {
+        tma::load_4d(&mapZ, barZ, sW + w * 16384, 0, x0[w], y0[w], b[w]);
+        tma::load_4d(&mapZ, barZ, sW + w * 16384 + 8192, 32, x0[w], y0[w], b[w]);
+      }
+  };
+  const bool leader = wq == 0 && lane == 0;       // bulk groups are per thread: one fixed thread
+  const int tile_stride = gridDim.x * kWorkers;
+  // byte offset of 16-byte chunk i of this thread's row inside the swizzled z tile
+  const uint32_t zrow_off = (uint32_t)(wsel * 16384 + lrow * 128);
+  auto zoff = [&](int i) -> uint32_t {
+    return zrow_off + (uint32_t)((i >> 3) * 8192 + (((i & 7) ^ (lrow & 7)) << 4));
+  };
+  if (leader && (int)(blockIdx.x * kWorkers + wk) < ntile) issue_z_loads(blockIdx.x * kWorkers + wk);
+
   PROF_DECL
-  for (int tile = blockIdx.x * kWorkers + wk; tile < ntile; tile += gridDim.x * kWorkers) {
+  for (int tile = blockIdx.x * kWorkers + wk; tile < ntile; tile += tile_stride) {
     PROF(0);
-    // ---- L2 prefetch of the NEXT tile's token row of this thread (two 128-byte lines)
+    const int win = tile * 2 + wsel;
+    const bool wvalid = win < nwin;
+    int wx0, wy0, wb;
+    const bool use_tma = tma_window(win, wx0, wy0, wb);
+    bool any_tma;
     {
-      const int nwin_ = (tile + gridDim.x * kWorkers) * 2 + wsel;
-      if (nwin_ < nwin) {
-        const float* zr = p.z + (size_t)slot_of(g, nwin_, lrow).tok * 64;
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(zr));
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(zr + 32));
-      }
+      int d0, d1, d2;
+      any_tma = tma_window(tile * 2, d0, d1, d2) | tma_window(tile * 2 + 1, d0, d1, d2);
     }
-    // ---- slot table of the two windows
+    long long tok = 0;
+    float xinv;
     {
-      const int win = tile * 2 + wsel;
-      if (win < nwin) {
-        const Slot s = slot_of(g, win, lrow);
-        sTok[row] = (int)s.tok; sCwin[row] = s.cwin; sReg[row] = s.region;
+      // ---- X = z + ctx of this thread's token row.  Cosine attention is scale-invariant in q and k
+      //      (F.normalize, eps 1e-12), so a row of tiny activations (e.g. the zero-padded border)
+      //      matters as much as any other: every row is scaled by a power of two to max|x| in [1,2)
+      //      before the fp16 conversion and the exact inverse is applied to the fp32 accumulators.
+      float x[64];
+      if (wvalid) {
+        const Slot sl = slot_of(g, win, lrow);
+        tok = sl.tok;
+        sReg[row] = sl.region;
+        const float4* cp = reinterpret_cast<const float4*>(p.ctx + (size_t)sl.cwin * 64);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const float4 v = __ldg(cp + i);
+          x[4 * i] = v.x; x[4 * i + 1] = v.y; x[4 * i + 2] = v.z; x[4 * i + 3] = v.w;
+        }
       } else {
-        sTok[row] = -1; sCwin[row] = 0; sReg[row] = 0;
+        sReg[row] = 0;
+#pragma unroll
+        for (int i = 0; i < 64; ++i) x[i] = 0.f;
       }
-    }
-    tc::worker_sync(1 + wk);
-    // ---- gather X = z + ctx -> fp16: coalesced 64-byte global segments, 8-byte smem slots.
-    //      Cosine attention is scale-invariant in q and k (F.normalize, eps 1e-12), so a row of
-    //      tiny activations (e.g. the zero-padded border) matters as much as any other: every row
-    //      is scaled by a power of two to max|x| in [1,2) before the fp16 conversion and the
-    //      exact inverse is applied to the fp32 accumulators in the qkv epilogue.
-    {
-      const int q = lane >> 3, m8 = lane & 7;
+      if (any_tma) { tc::mbar_wait(barZ, phZ, &g_tc_error); phZ ^= 1; }
+      PROF(1);                                       // ctx + wait for the z tile
+      if (use_tma) {
 #pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        float4 xv[8];
-        {
-          float4 cv[8];
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {                     // 16 loads in flight before any use
-            const int it = half * 8 + i;
-            const int m = wq * 32 + (it >> 2) * 8 + m8, kc = (it & 3) * 4 + q;
-            const int tok = sTok[m];
-            xv[i] = cv[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (tok >= 0) {
-              xv[i] = __ldg(reinterpret_cast<const float4*>(p.z + (size_t)tok * 64 + kc * 4));
-              cv[i] = __ldg(reinterpret_cast<const float4*>(p.ctx + (size_t)sCwin[m] * 64 + kc * 4));
-            }
-          }
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            xv[i].x += cv[i].x; xv[i].y += cv[i].y; xv[i].z += cv[i].z; xv[i].w += cv[i].w;
-          }
+        for (int i = 0; i < 16; ++i) {
+          const float4 v = *reinterpret_cast<const float4*>(sW + zoff(i));
+          x[4 * i] += v.x; x[4 * i + 1] += v.y; x[4 * i + 2] += v.z; x[4 * i + 3] += v.w;
         }
+      } else if (wvalid) {
+        const float4* zp = reinterpret_cast<const float4*>(p.z + (size_t)tok * 64);
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {                       // two complete rows per half
-          float mxv = 0.f;
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const float4 v = xv[j * 4 + i];
-            mxv = fmaxf(mxv, fmaxf(fmaxf(fabsf(v.x), fabsf(v.y)), fmaxf(fabsf(v.z), fabsf(v.w))));
-          }
-          mxv = fmaxf(mxv, __shfl_xor_sync(0xffffffffu, mxv, 8));
-          mxv = fmaxf(mxv, __shfl_xor_sync(0xffffffffu, mxv, 16));
-          uint32_t e = (__float_as_uint(mxv) >> 23) & 0xFFu;      // biased exponent of the row max
-          e = e < 1u ? 127u : (e > 253u ? 253u : e);              // all-zero / denormal row: scale 1
-          const float sc = __uint_as_float((254u - e) << 23);     // 2^(127-e)
-          const int m = wq * 32 + (half * 2 + j) * 8 + m8;
-          if (q == 0) sRowInv[m] = __uint_as_float(e << 23);      // 2^(e-127), exact inverse
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const int kc = i * 4 + q;
-            const float4 v = xv[j * 4 + i];
-            *reinterpret_cast<uint2*>(sX + (kc >> 1) * 2048 + m * 16 + (kc & 1) * 8) =
-                make_uint2(tc::pack_f16(v.x * sc, v.y * sc), tc::pack_f16(v.z * sc, v.w * sc));
-          }
+        for (int i = 0; i < 16; ++i) {
+          const float4 v = __ldg(zp + i);
+          x[4 * i] += v.x; x[4 * i + 1] += v.y; x[4 * i + 2] += v.z; x[4 * i + 3] += v.w;
         }
       }
+      float m0 = 0.f, m1 = 0.f, m2 = 0.f, m3 = 0.f;
+#pragma unroll
+      for (int i = 0; i < 64; i += 4) {
+        m0 = fmaxf(m0, fabsf(x[i])); m1 = fmaxf(m1, fabsf(x[i + 1]));
+        m2 = fmaxf(m2, fabsf(x[i + 2])); m3 = fmaxf(m3, fabsf(x[i + 3]));
+      }
+      uint32_t e = (__float_as_uint(fmaxf(fmaxf(m0, m1), fmaxf(m2, m3))) >> 23) & 0xFFu;
+      e = e < 1u ? 127u : (e > 253u ? 253u : e);              // all-zero / denormal row: scale 1
+      const float sc = __uint_as_float((254u - e) << 23);     // 2^(127-e)
+      xinv = __uint_as_float(e << 23) * sScale[6];            // undoes the row scale and the Wqkv scale
+      tc::worker_sync(1 + wk);                       // every row is in registers: the tile may be overwritten
+#pragma unroll
+      for (int kc = 0; kc < 8; ++kc)                 // fp16 X operand, own row, one 16-byte slot per k-chunk
+        *reinterpret_cast<uint4*>(sX + kc * 2048 + row * 16) =
+            make_uint4(tc::pack_f16(x[8 * kc] * sc, x[8 * kc + 1] * sc),
+                       tc::pack_f16(x[8 * kc + 2] * sc, x[8 * kc + 3] * sc),
+                       tc::pack_f16(x[8 * kc + 4] * sc, x[8 * kc + 5] * sc),
+                       tc::pack_f16(x[8 * kc + 6] * sc, x[8 * kc + 7] * sc));
     }
     // ---- shift mask of this row as a 64-bit key set (analytic 9-region rule)
     uint32_t mlo = 0, mhi = 0;
@@ -307,7 +337,7 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
         mhi |= (uint32_t)(reg[c + 32] != rg) << c;
       }
     }
-    PROF(1);                                         // slot table + gather
+    PROF(17);                                        // row convert + mask
     tc::fence_async_smem();
     tc::worker_sync(1 + wk);
     if (wq == 0) {                                   // warp-uniform: one elected lane issues
@@ -322,7 +352,6 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
     float o[64];
 #pragma unroll
     for (int i = 0; i < 64; ++i) o[i] = 0.f;
-    const float xinv = sRowInv[row] * sScale[6];      // undoes the row scale of X and the scale of Wqkv
     float inv_prev = 0.f;
 
 #pragma unroll 1
@@ -519,7 +548,11 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
     tc::mbar_wait(barS, phS, &g_tc_error); phS ^= 1;
     tc::tc_fence_after();
     PROF(12);                                          // O tile + proj issue + wait
-    // ---- + proj bias, LayerNorm(norm1) of the row held in registers -> fp32 staging tile (own row)
+    // ---- the O tile is consumed: reload the z tile over it for the residual (an L2 hit; it lands
+    //      while the LayerNorm below runs)
+    if (RESID && leader) issue_z_loads(tile);
+    // ---- + proj bias, LayerNorm(norm1) of the row held in registers; a = z + LN(.) in place in the
+    //      z tile (TMA windows) or straight to global (wrapped windows)
     {
       float y[64];
       tc::tmem_ld64(tbase + lane_addr + kTS, y);
@@ -532,47 +565,52 @@ __global__ void __launch_bounds__(128 * kWorkers, 1) attn_tc_fwd_kernel(AttnPara
       for (int i = 0; i < 64; ++i) { y[i] -= mean; var = fmaf(y[i], y[i], var); }
       const float rstd = 1.0f / sqrtf(var * (1.0f / 64.f) + kLnEps);
 #pragma unroll
-      for (int kc = 0; kc < 16; ++kc)
-        *reinterpret_cast<float4*>(sStage + kc * 512 + row * 4) =
-            make_float4(y[kc * 4 + 0] * rstd * sLnW[kc * 4 + 0] + sLnB[kc * 4 + 0],
-                        y[kc * 4 + 1] * rstd * sLnW[kc * 4 + 1] + sLnB[kc * 4 + 1],
-                        y[kc * 4 + 2] * rstd * sLnW[kc * 4 + 2] + sLnB[kc * 4 + 2],
-                        y[kc * 4 + 3] * rstd * sLnW[kc * 4 + 3] + sLnB[kc * 4 + 3]);
-    }
-    PROF(13);                                          // LN epilogue
-    tc::tc_fence_before();
-    tc::worker_sync(1 + wk);
-    PROF(14);
-    // ---- residual + scatter back to the source token positions (same mapping as the gather)
-    {
-      const int q = lane >> 3, m8 = lane & 7;
+      for (int i = 0; i < 64; ++i) y[i] = y[i] * rstd * sLnW[i] + sLnB[i];
+      PROF(13);                                        // LN epilogue
+      if (RESID && any_tma) { tc::mbar_wait(barZ, phZ, &g_tc_error); phZ ^= 1; }
+      PROF(14);
+      if (use_tma) {
 #pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        float4 zv[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int it = half * 8 + i;
-          const int m = wq * 32 + (it >> 2) * 8 + m8, kc = (it & 3) * 4 + q;
-          const int tok = sTok[m];
-          zv[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (RESID && tok >= 0) zv[i] = __ldg(reinterpret_cast<const float4*>(p.z + (size_t)tok * 64 + kc * 4));
+        for (int i = 0; i < 16; ++i) {
+          float4* q = reinterpret_cast<float4*>(sW + zoff(i));
+          float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (RESID) v = *q;
+          *q = make_float4(v.x + y[4 * i], v.y + y[4 * i + 1], v.z + y[4 * i + 2], v.w + y[4 * i + 3]);
         }
+      } else if (wvalid) {
+        const float4* zp = reinterpret_cast<const float4*>(p.z + (size_t)tok * 64);
+        float4* ap = reinterpret_cast<float4*>(p.a + (size_t)tok * 64);
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int it = half * 8 + i;
-          const int m = wq * 32 + (it >> 2) * 8 + m8, kc = (it & 3) * 4 + q;
-          const int tok = sTok[m];
-          if (tok >= 0) {
-            const float4 y = *reinterpret_cast<const float4*>(sStage + kc * 512 + m * 4);
-            *reinterpret_cast<float4*>(p.a + (size_t)tok * 64 + kc * 4) =
-                make_float4(zv[i].x + y.x, zv[i].y + y.y, zv[i].z + y.z, zv[i].w + y.w);
-          }
+        for (int i = 0; i < 16; ++i) {
+          float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (RESID) v = __ldg(zp + i);
+          ap[i] = make_float4(v.x + y[4 * i], v.y + y[4 * i + 1], v.z + y[4 * i + 2], v.w + y[4 * i + 3]);
         }
       }
     }
-    PROF(15);                                          // copy-out
+    tc::fence_async_smem();                            // generic writes -> visible to the TMA engine
+    tc::tc_fence_before();
     tc::worker_sync(1 + wk);
+    if (leader) {
+      bool stored = false;
+#pragma unroll
+      for (int w = 0; w < 2; ++w) {
+        int x0, y0, b;
+        if (tma_window(tile * 2 + w, x0, y0, b)) {
+          tma::store_4d(&mapA, sW + w * 16384, 0, x0, y0, b);
+          tma::store_4d(&mapA, sW + w * 16384 + 8192, 32, x0, y0, b);
+          stored = true;
+        }
+      }
+      if (stored) tma::commit_group();
+      if (tile + tile_stride < ntile) {
+        tma::wait_read_all();                          // the stores have drained the tile buffer
+        issue_z_loads(tile + tile_stride);
+      }
+    }
+    PROF(15);                                          // store + next-tile load issue
   }
+  if (leader) tma::wait_all();
   PROF_FLUSH;
   tc::tc_fence_before();
   __syncthreads();
@@ -603,7 +641,10 @@ static int launch_attn_tc_fwd(const AttnParams& p, cudaStream_t st) {
   const int ntile = (nwin + 1) / 2;
   int grid = (ntile + kWorkers - 1) / kWorkers;
   if (grid > sm_count()) grid = sm_count();
-  attn_tc_fwd_kernel<NH, RESID><<<grid, 128 * kWorkers, smem, st>>>(p);
+  CUtensorMap mZ, mA;
+  if (int rc = tma::encode_windows(&mZ, p.z, p.B, p.ph, p.pw)) return rc;
+  if (int rc = tma::encode_windows(&mA, p.a, p.B, p.ph, p.pw)) return rc;
+  attn_tc_fwd_kernel<NH, RESID><<<grid, 128 * kWorkers, smem, st>>>(mZ, mA, p);
   B200MAR_CHECK(cudaGetLastError());
   return 0;
 }

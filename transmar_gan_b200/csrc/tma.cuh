@@ -60,6 +60,25 @@ __device__ __forceinline__ void reduce_add_2d(const CUtensorMap* m, const void* 
       : "memory");
 }
 
+// 4-D forms over the token grid [B][ph][pw][64] (coordinates fastest-first: channel, x, y, b)
+__device__ __forceinline__ void load_4d(const CUtensorMap* m, uint64_t* bar, void* smem_dst, int c0,
+                                        int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(c0), "r"(c1),
+      "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void store_4d(const CUtensorMap* m, const void* smem_src, int c0, int c1,
+                                         int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(
+          reinterpret_cast<uint64_t>(m)),
+      "r"((uint32_t)__cvta_generic_to_shared(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+
 __device__ __forceinline__ void commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // all committed bulk groups of this thread have finished READING shared memory
 __device__ __forceinline__ void wait_read_all() {
@@ -71,20 +90,42 @@ __device__ __forceinline__ void wait_all() { asm volatile("cp.async.bulk.wait_gr
 // ---- host: tensor map over a token-major fp32 matrix [n_rows][64], box [128][32], 128 B swizzle.
 // cuTensorMapEncodeTiled is fetched through the runtime (no link-time libcuda dependency, so the
 // library also loads on a machine without a driver).
-inline int encode_rows64(CUtensorMap* out, const float* base, long long n_rows) {
-  typedef CUresult (*Fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                         const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
-                         CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
-                         CUtensorMapFloatOOBfill);
-  static Fn fn = nullptr;
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+inline EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
   if (!fn) {
     void* p = nullptr;
     cudaDriverEntryPointQueryResult q;
     if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
         q != cudaDriverEntryPointSuccess || !p)
-      return -2;
-    fn = reinterpret_cast<Fn>(p);
+      return nullptr;
+    fn = reinterpret_cast<EncodeTiledFn>(p);
   }
+  return fn;
+}
+
+// ---- host: tensor map over the token grid [B][ph][pw][64] fp32; one box = half the channels of one
+// 8x8 window: [1][8 rows][8 tokens][32 floats] -> 64 smem rows (window slot t = 8*i + j) of 128 B,
+// 128 B swizzle (16-byte chunk c of slot t at chunk slot c ^ (t & 7)).
+inline int encode_windows(CUtensorMap* out, const float* base, int B, int ph, int pw) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) return -2;
+  const cuuint64_t gdim[4] = {64, (cuuint64_t)pw, (cuuint64_t)ph, (cuuint64_t)B};
+  const cuuint64_t gstride[3] = {256, (cuuint64_t)pw * 256, (cuuint64_t)ph * pw * 256};
+  const cuuint32_t box[4] = {32, 8, 8, 1};
+  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  const CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(base), gdim, gstride,
+                        box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -3;
+}
+
+inline int encode_rows64(CUtensorMap* out, const float* base, long long n_rows) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) return -2;
   const cuuint64_t gdim[2] = {64, (cuuint64_t)n_rows};
   const cuuint64_t gstride[1] = {256};
   const cuuint32_t box[2] = {32, 128};
