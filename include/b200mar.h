@@ -60,6 +60,16 @@ int b200mar_ngram_ctx_fwd(const float* u,
                           const float* logit_scale /*[nh]*/, const float* bias_table /*[9,nh]*/,
                           const float* merge_w /*[64,64]*/, const float* merge_b /*[64]*/,
                           float* ctx, int B, int wh, int ww, int nh, void* stream);
+/* Inference pair: the unigram pass also applies the n-gram attention's qkv Linear once per window
+ * (nq [B*wh*ww, 96], rows >= 3*NA zero); b200mar_ngram_ctx_pre_fwd gathers those rows instead of
+ * re-deriving them for every neighbourhood.  Same results as unigram_fwd + ngram_ctx_fwd.       */
+int b200mar_unigram_qkv_fwd(const float* z, const float* weight, const float* bias,
+                            const float* qkv_w, const float* qkv_b, float* nq,
+                            int B, int ph, int pw, int nh, void* stream);
+int b200mar_ngram_ctx_pre_fwd(const float* nq, const float* proj_w, const float* proj_b,
+                              const float* logit_scale, const float* bias_table,
+                              const float* merge_w, const float* merge_b, float* ctx,
+                              int B, int wh, int ww, int nh, void* stream);
 int b200mar_ngram_ctx_bwd(const float* u, const float* dctx,
                           const float* qkv_w, const float* qkv_b,
                           const float* proj_w, const float* proj_b,
@@ -161,6 +171,10 @@ int b200mar_mlp_bwd(const float* a, const float* dout,
 int b200mar_patch_merge_fwd(const float* x, const float* ln_w /*[256]*/, const float* ln_b,
                             const float* red_w /*[64,256]*/, float* y,
                             int B, int ph, int pw, void* stream);
+/* Same contract on TMA + tcgen05 (kind::tf32): stride-2 tensor-map boxes are the MMA A operands,
+ * LayerNorm folded around the GEMM (per-quadrant centring), TMA store.  ph, pw even.          */
+int b200mar_patch_merge_tc_fwd(const float* x, const float* ln_w, const float* ln_b,
+                               const float* red_w, float* y, int B, int ph, int pw, void* stream);
 int b200mar_patch_merge_bwd(const float* x, const float* dy,
                             const float* ln_w, const float* ln_b, const float* red_w,
                             float* dx, float* d_ln_w, float* d_ln_b, float* d_red_w,

@@ -343,3 +343,19 @@ def test_fused_glue_matches_composite_path(T):
             y_comp = m(x).detach()
         assert y_fused.shape == y_comp.shape
         assert (y_fused - y_comp).abs().max().item() < 2e-5
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("nh,B,ph,pw", [(6, 2, 16, 16), (6, 1, 24, 40), (4, 3, 32, 16), (6, 1, 416, 416)])
+def test_ngram_ctx_infer_matches_two_step(nh, B, ph, pw):
+    """Inference pair (unigram + per-window qkv, then gather) == unigram_fwd + ngram_ctx_fwd."""
+    from transmar_gan_b200 import ops
+    sd = {k: v.cuda() for k, v in O.synthetic_state_dict("W2", seed=5).items()}
+    pre = "encoder_layer1.blocks.3." if nh == 6 else "encoder_layer2.blocks.1."
+    P = [sd[pre + n].contiguous() for n in ops.NSTB_PARAM_NAMES[:10]]
+    g = torch.Generator().manual_seed(ph * pw + nh)
+    z = torch.randn(B, ph * pw, 64, generator=g).cuda()
+    ref = ops.ngram_ctx_fwd(ops.unigram_fwd(z, P[0], P[1], ph, pw), *P[2:10], nh)
+    got = ops.ngram_ctx_infer(z, *P, ph, pw, nh)
+    assert got.shape == ref.shape
+    assert (got - ref).abs().max().item() <= 2e-5 * max(1.0, ref.abs().max().item())

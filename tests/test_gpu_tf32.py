@@ -182,3 +182,48 @@ def test_attn_tc_exact_softmax_fallback(T):
     assert torch.isfinite(a_tc).all()
     d = (a_tc - a_32).abs()
     assert d.max() < 5e-2 and d.mean() < 3e-3, (d.max().item(), d.mean().item())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ntok", [64, 128, 192, 4160, 148 * 3 * 128 + 64])
+def test_mlp_tma_inplace_matches_mlp_tc(ntok):
+    """The TMA-fed in-place block tail (z += out, bulk reduce-add) is the same arithmetic as
+    mlp_tc_fwd: bit-identical out and zsum, including ragged last tiles and extreme rows."""
+    from transmar_gan_b200 import ops
+    sd = {k: v.cuda() for k, v in O.synthetic_state_dict("W2", seed=3).items()}
+    W = [sd["decoder_layer1.blocks.2." + n].contiguous() for n in ops.NSTB_PARAM_NAMES[18:24]]
+    g = torch.Generator().manual_seed(ntok)
+    a = (torch.randn(1, ntok, 64, generator=g) * 3).cuda()
+    z = torch.randn(1, ntok, 64, generator=g).cuda()
+    a[0, 0] = 0
+    a[0, 1] *= 1e-6
+    a[0, 2] *= 1e5                                   # would overflow an unscaled fp16 hidden row
+    out_ref, zsum_ref, _ = ops.mlp_tc_fwd(a, z, *W, True, True)
+    assert torch.isfinite(out_ref).all()
+    z1 = z.clone()
+    out = ops.mlp_tma_fwd_(a, z1, *W, True)
+    assert torch.equal(out, out_ref) and torch.equal(z1, zsum_ref)
+    z2 = z.clone()
+    assert ops.mlp_tma_fwd_(a, z2, *W, False).numel() == 0
+    assert torch.equal(z2, zsum_ref)
+    assert torch.equal(ops.mlp_tma_fwd_(a, None, *W, True), out_ref)
+    assert ops.tc_error() == 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("B,ph,pw", [(1, 16, 32), (2, 24, 40), (1, 64, 64), (2, 104, 104), (1, 8, 8)])
+def test_patch_merge_tc_matches_fp32_kernel(B, ph, pw):
+    """TMA + tcgen05 PatchMerging (tf32 operands, LayerNorm folded around the GEMM) vs the fp32
+    kernel: tf32-level agreement, ragged tiles (output grids that are not multiples of 16 x 8)."""
+    from transmar_gan_b200 import ops
+    sd = {k: v.cuda() for k, v in O.synthetic_state_dict("W2", seed=2).items()}
+    lw, lb, rw = (sd["encoder_layer2.downsample." + n].contiguous()
+                  for n in ("norm.weight", "norm.bias", "reduction.weight"))
+    g = torch.Generator().manual_seed(ph * 1000 + pw)
+    x = (torch.randn(B, ph * pw, 64, generator=g) * 2 + 0.7).cuda()     # non-zero mean rows
+    ref = ops.patch_merge_fwd(x, lw, lb, rw, ph, pw)
+    got = ops.patch_merge_tc_fwd(x, lw, lb, rw, ph, pw)
+    d = (ref - got).abs()
+    scale = ref.abs().max().item()
+    assert d.max().item() <= 1.5e-3 * scale and d.mean().item() <= 2e-4 * scale
+    assert ops.tc_error() == 0

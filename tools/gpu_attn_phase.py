@@ -17,8 +17,9 @@ ops.attn_tc_fwd(z, c, *P[10:18], ph, pw, 6, 0); torch.cuda.synchronize()
 L.b200mar_attn_prof(buf, 1)
 ops.attn_tc_fwd(z, c, *P[10:18], ph, pw, 6, 0); torch.cuda.synchronize()
 L.b200mar_attn_prof(buf, 1)
-names = ["loop top", "slot+gather", "sync+qkv0 issue", "wait qkv", "qkv ld+norm+pack", "wait PV+O read", "operand stores",
-         "fence+sync", "S issue+wait", "softmax+P st", "sync(or)", "PV issue", "Otile+proj+wait", "LN epilogue", "sync", "copy-out", "loop end"]
+names = ["loop top", "ctx + wait z tile", "sync+qkv0 issue", "wait qkv", "qkv ld+norm+pack", "wait PV+O read", "operand stores",
+         "fence+sync", "S issue+wait", "softmax+P st", "sync(or)", "PV issue", "Otile+proj+wait", "LN epilogue", "wait z reload",
+         "a in place+store+next load", "PV issue (last)", "row convert+mask"]
 tot = sum(buf)
 ntile = (B * (ph // 8) * (pw // 8) // 2 + 148 * 3 - 1) // (148 * 3)
 print("tiles per worker ~", ntile, "total cycles", tot, "per tile", tot / ntile)

@@ -31,6 +31,8 @@ SIGNATURES = {
     "b200mar_unigram_fwd": [_P] * 4 + [_I] * 3 + [_P],
     "b200mar_unigram_bwd": [_P] * 6 + [_I] * 3 + [_P],
     "b200mar_ngram_ctx_fwd": [_P] * 10 + [_I] * 4 + [_P],
+    "b200mar_unigram_qkv_fwd": [_P] * 6 + [_I] * 4 + [_P],
+    "b200mar_ngram_ctx_pre_fwd": [_P] * 8 + [_I] * 4 + [_P],
     "b200mar_ngram_ctx_bwd": [_P] * 19 + [_I] * 4 + [_P],
     "b200mar_attn_fwd": [_P] * 11 + [_I] * 5 + [_P],
     "b200mar_attn_tc_fwd": [_P] * 11 + [_I] * 6 + [_P],
@@ -42,6 +44,7 @@ SIGNATURES = {
     "b200mar_tc_error": [],
     "b200mar_tc_probe": [_P] * 3 + [_I] * 4 + [_P],
     "b200mar_patch_merge_fwd": [_P] * 5 + [_I] * 3 + [_P],
+    "b200mar_patch_merge_tc_fwd": [_P] * 5 + [_I] * 3 + [_P],
     "b200mar_patch_merge_bwd": [_P] * 9 + [_I] * 3 + [_P],
     "b200mar_pixel_shuffle_cat": [_P] * 4 + [_I] * 4 + [_P],
     "b200mar_shallow_tok_fwd": [_P] * 4 + [_I] * 3 + [_P],

@@ -20,13 +20,15 @@ int sm_count() {
 int tc_error_mlp();
 int tc_error_probe();
 int tc_error_attn();
+int tc_error_merge();
 }  // namespace b200mar
 
 // 1 if any tensor-core kernel of this process hit its bounded mbarrier wait (descriptor-bug guard)
 extern "C" int b200mar_tc_error(void) {
-  const int a = b200mar::tc_error_mlp(), b = b200mar::tc_error_probe(), c = b200mar::tc_error_attn();
-  if (a < 0 || b < 0 || c < 0) return -1;
-  return (a | b | c) ? 1 : 0;
+  const int a = b200mar::tc_error_mlp(), b = b200mar::tc_error_probe(), c = b200mar::tc_error_attn(),
+            d = b200mar::tc_error_merge();
+  if (a < 0 || b < 0 || c < 0 || d < 0) return -1;
+  return (a | b | c | d) ? 1 : 0;
 }
 
 extern "C" int b200mar_abi_version(void) { return 2; }

@@ -63,12 +63,14 @@ __device__ __forceinline__ int ngram_rel_index(int p, int q) {
 template <int NH>
 __device__ __forceinline__ void load_ngram_weights(float* smem, const NgramParams& p) {
   using L = NgramSmem<NH>;
-  for (int i = threadIdx.x; i < 96 * 32; i += blockDim.x) {
-    const int r = i >> 5, c = i & 31;
-    smem[L::oWqkv + r * 33 + c] = r < 3 * L::NA ? p.qkv_w[r * 32 + c] : 0.f;
+  if (p.qkv_w) {                               // null when the qkv rows are precomputed per window
+    for (int i = threadIdx.x; i < 96 * 32; i += blockDim.x) {
+      const int r = i >> 5, c = i & 31;
+      smem[L::oWqkv + r * 33 + c] = r < 3 * L::NA ? p.qkv_w[r * 32 + c] : 0.f;
+    }
+    for (int i = threadIdx.x; i < 96; i += blockDim.x)
+      smem[L::oBqkv + i] = i < 3 * L::NA ? p.qkv_b[i] : 0.f;
   }
-  for (int i = threadIdx.x; i < 96; i += blockDim.x)
-    smem[L::oBqkv + i] = i < 3 * L::NA ? p.qkv_b[i] : 0.f;
   for (int i = threadIdx.x; i < 32 * L::NA; i += blockDim.x) {
     const int r = i / L::NA, c = i - r * L::NA;
     smem[L::oWp + r * 33 + c] = p.proj_w[i];

@@ -44,8 +44,74 @@ __global__ void __launch_bounds__(kThreads) unigram_fwd_kernel(
   }
 }
 
+// Inference form: the same streaming pass also applies the n-gram attention's qkv Linear(32 -> 3*NA)
+// to the window's unigram embedding, once per window (ngram_ctx_fwd re-derives it for each of the
+// up to 8 neighbourhoods a window belongs to).  nq: [B*wh*ww][96] (rows >= 3*NA are zero).
+__global__ void __launch_bounds__(kThreads) unigram_qkv_fwd_kernel(
+    const float* __restrict__ z, const float* __restrict__ w, const float* __restrict__ bias,
+    const float* __restrict__ qkv_w, const float* __restrict__ qkv_b, int n_qkv,
+    float* __restrict__ nq, int B, int ph, int pw) {
+  __shared__ __align__(16) float sW[kTok * kDim];  // [t = 8i+j][c = 2g+k]
+  __shared__ __align__(16) float sWq[32 * 96];     // [c][j]
+  __shared__ __align__(16) float sU[8][32];
+  for (int idx = threadIdx.x; idx < kTok * kDim; idx += blockDim.x) {
+    const int t = idx >> 6, c = idx & 63;
+    sW[idx] = w[(c >> 1) * 128 + (c & 1) * 64 + t];
+  }
+  for (int idx = threadIdx.x; idx < 32 * 96; idx += blockDim.x) {
+    const int c = idx / 96, j = idx - c * 96;
+    sWq[idx] = j < n_qkv ? qkv_w[j * 32 + c] : 0.f;
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int wh = ph / kWin, ww = pw / kWin;
+  const int nwin = B * wh * ww;
+  const float bl = bias[lane];
+  float bq[3];
+#pragma unroll
+  for (int g = 0; g < 3; ++g) bq[g] = lane + 32 * g < n_qkv ? qkv_b[lane + 32 * g] : 0.f;
+  for (int win = blockIdx.x * 8 + warp; win < nwin; win += gridDim.x * 8) {
+    const int w0 = win % ww, h0 = (win / ww) % wh, b = win / (ww * wh);
+    const float* base = z + (((size_t)b * ph + h0 * kWin) * pw + w0 * kWin) * kDim + 2 * lane;
+    float acc = 0.f;
+#pragma unroll 1
+    for (int i = 0; i < kWin; ++i) {
+      float2 v[kWin];
+#pragma unroll
+      for (int j = 0; j < kWin; ++j)
+        v[j] = *reinterpret_cast<const float2*>(base + ((size_t)i * pw + j) * kDim);
+#pragma unroll
+      for (int j = 0; j < kWin; ++j) {
+        const float2 wv = *reinterpret_cast<const float2*>(sW + (i * kWin + j) * kDim + 2 * lane);
+        acc = fmaf(v[j].x, wv.x, acc);
+        acc = fmaf(v[j].y, wv.y, acc);
+      }
+    }
+    sU[warp][lane] = acc + bl;
+    __syncwarp();
+    float q0 = bq[0], q1 = bq[1], q2 = bq[2];
+#pragma unroll
+    for (int c4 = 0; c4 < 8; ++c4) {
+      const float4 uv = *reinterpret_cast<const float4*>(&sU[warp][c4 * 4]);
+      const float uu[4] = {uv.x, uv.y, uv.z, uv.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float* wr = sWq + (c4 * 4 + k) * 96 + lane;
+        q0 = fmaf(wr[0], uu[k], q0);
+        q1 = fmaf(wr[32], uu[k], q1);
+        q2 = fmaf(wr[64], uu[k], q2);
+      }
+    }
+    float* o = nq + (size_t)win * 96 + lane;
+    o[0] = q0; o[32] = q1; o[64] = q2;
+    __syncwarp();
+  }
+}
+
 // ------------------------------------------------------------------------------- context
-template <int NH>
+// PRE = true: p.u holds the per-window qkv rows [nwin][96] of unigram_qkv_fwd_kernel instead of the
+// unigram embeddings; the neighbourhood gather fetches them directly.
+template <int NH, bool PRE>
 __global__ void __launch_bounds__(kThreads) ngram_ctx_fwd_kernel(NgramParams p) {
   using L = NgramSmem<NH>;
   constexpr int HD = L::HD, NA = L::NA;
@@ -70,34 +136,48 @@ __global__ void __launch_bounds__(kThreads) ngram_ctx_fwd_kernel(NgramParams p) 
   const int nwin = p.B * wh * ww;
   for (int win = blockIdx.x * 8 + warp; win < nwin; win += gridDim.x * 8) {
     const int w0 = win % ww, h0 = (win / ww) % wh, b = win / (ww * wh);
-    // ---- the 8 neighbourhood tokens (4 forward, 4 backward), lane = channel
+    if (PRE) {
+      // ---- qkv rows of the 8 neighbourhood tokens (4 forward, 4 backward), precomputed per window
 #pragma unroll
-    for (int t = 0; t < 8; ++t) {
-      int r, c;
-      ngram_neighbour(t, h0, w0, wh, ww, r, c);
-      sTok[t * 32 + lane] = p.u[((size_t)(b * wh + r) * ww + c) * 32 + lane];
-    }
-    __syncwarp();
-    // ---- qkv = Linear(32 -> 3*NA)
-#pragma unroll
-    for (int jg = 0; jg < 3; ++jg) {
-      const int j = lane + 32 * jg;
-      if (j < 3 * NA) {
-        float acc[8];
-        const float bj = sBqkv[j];
-#pragma unroll
-        for (int t = 0; t < 8; ++t) acc[t] = bj;
-#pragma unroll 8
-        for (int c = 0; c < 32; ++c) {
-          const float wv = sWqkv[j * 33 + c];
-#pragma unroll
-          for (int t = 0; t < 8; ++t) acc[t] = fmaf(wv, sTok[t * 32 + c], acc[t]);
-        }
-#pragma unroll
-        for (int t = 0; t < 8; ++t) sQkv[t * 96 + j] = acc[t];
+      for (int t = 0; t < 8; ++t) {
+        int r, c;
+        ngram_neighbour(t, h0, w0, wh, ww, r, c);
+        const float* src = p.u + ((size_t)(b * wh + r) * ww + c) * 96 + lane;
+        sQkv[t * 96 + lane] = src[0];
+        sQkv[t * 96 + lane + 32] = src[32];
+        sQkv[t * 96 + lane + 64] = src[64];
       }
+      __syncwarp();
+    } else {
+      // ---- the 8 neighbourhood tokens (4 forward, 4 backward), lane = channel
+  #pragma unroll
+      for (int t = 0; t < 8; ++t) {
+        int r, c;
+        ngram_neighbour(t, h0, w0, wh, ww, r, c);
+        sTok[t * 32 + lane] = p.u[((size_t)(b * wh + r) * ww + c) * 32 + lane];
+      }
+      __syncwarp();
+      // ---- qkv = Linear(32 -> 3*NA)
+  #pragma unroll
+      for (int jg = 0; jg < 3; ++jg) {
+        const int j = lane + 32 * jg;
+        if (j < 3 * NA) {
+          float acc[8];
+          const float bj = sBqkv[j];
+  #pragma unroll
+          for (int t = 0; t < 8; ++t) acc[t] = bj;
+  #pragma unroll 8
+          for (int c = 0; c < 32; ++c) {
+            const float wv = sWqkv[j * 33 + c];
+  #pragma unroll
+            for (int t = 0; t < 8; ++t) acc[t] = fmaf(wv, sTok[t * 32 + c], acc[t]);
+          }
+  #pragma unroll
+          for (int t = 0; t < 8; ++t) sQkv[t * 96 + j] = acc[t];
+        }
+      }
+      __syncwarp();
     }
-    __syncwarp();
     // ---- 4-token cosine attention per (direction, head); mean over the 4 query tokens
     if (lane < 2 * NH) {
       const int dir = lane / NH, h = lane % NH;
@@ -170,20 +250,20 @@ __global__ void __launch_bounds__(kThreads) ngram_ctx_fwd_kernel(NgramParams p) 
   }
 }
 
-template <int NH>
+template <int NH, bool PRE>
 static int launch_ngram_ctx_fwd(const NgramParams& p, cudaStream_t st) {
   using L = NgramSmem<NH>;
   const size_t smem = L::kFloatsFwd * sizeof(float);
   static bool configured = false;
   if (!configured) {
-    B200MAR_CHECK(cudaFuncSetAttribute(ngram_ctx_fwd_kernel<NH>,
+    B200MAR_CHECK(cudaFuncSetAttribute(ngram_ctx_fwd_kernel<NH, PRE>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = true;
   }
   const int nwin = p.B * p.wh * p.ww;
   int grid = (nwin + 7) / 8;
   if (grid > 2 * sm_count()) grid = 2 * sm_count();
-  ngram_ctx_fwd_kernel<NH><<<grid, kThreads, smem, st>>>(p);
+  ngram_ctx_fwd_kernel<NH, PRE><<<grid, kThreads, smem, st>>>(p);
   B200MAR_CHECK(cudaGetLastError());
   return 0;
 }
@@ -213,7 +293,36 @@ extern "C" int b200mar_ngram_ctx_fwd(const float* u, const float* qkv_w, const f
   p.u = u; p.qkv_w = qkv_w; p.qkv_b = qkv_b; p.proj_w = proj_w; p.proj_b = proj_b;
   p.logit_scale = logit_scale; p.bias_table = bias_table; p.merge_w = merge_w; p.merge_b = merge_b;
   p.ctx = ctx; p.B = B; p.wh = wh; p.ww = ww;
-  if (nh == 6) return launch_ngram_ctx_fwd<6>(p, (cudaStream_t)stream);
-  if (nh == 4) return launch_ngram_ctx_fwd<4>(p, (cudaStream_t)stream);
+  if (nh == 6) return launch_ngram_ctx_fwd<6, false>(p, (cudaStream_t)stream);
+  if (nh == 4) return launch_ngram_ctx_fwd<4, false>(p, (cudaStream_t)stream);
+  return -1;
+}
+
+extern "C" int b200mar_unigram_qkv_fwd(const float* z, const float* weight, const float* bias,
+                                       const float* qkv_w, const float* qkv_b, float* nq, int B,
+                                       int ph, int pw, int nh, void* stream) {
+  using namespace b200mar;
+  if (ph % kWin || pw % kWin || ph < kWin || pw < kWin || (nh != 6 && nh != 4)) return -1;
+  const int nwin = B * (ph / kWin) * (pw / kWin);
+  int grid = (nwin + 7) / 8;
+  if (grid > 8 * sm_count()) grid = 8 * sm_count();
+  unigram_qkv_fwd_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(
+      z, weight, bias, qkv_w, qkv_b, 3 * (32 / nh) * nh, nq, B, ph, pw);
+  B200MAR_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200mar_ngram_ctx_pre_fwd(const float* nq, const float* proj_w, const float* proj_b,
+                                         const float* logit_scale, const float* bias_table,
+                                         const float* merge_w, const float* merge_b, float* ctx,
+                                         int B, int wh, int ww, int nh, void* stream) {
+  using namespace b200mar;
+  if (wh < 2 || ww < 2) return -1;
+  NgramParams p{};
+  p.u = nq; p.proj_w = proj_w; p.proj_b = proj_b;
+  p.logit_scale = logit_scale; p.bias_table = bias_table; p.merge_w = merge_w; p.merge_b = merge_b;
+  p.ctx = ctx; p.B = B; p.wh = wh; p.ww = ww;
+  if (nh == 6) return launch_ngram_ctx_fwd<6, true>(p, (cudaStream_t)stream);
+  if (nh == 4) return launch_ngram_ctx_fwd<4, true>(p, (cudaStream_t)stream);
   return -1;
 }

@@ -123,6 +123,23 @@ inline int encode_windows(CUtensorMap* out, const float* base, int B, int ph, in
   return r == CUDA_SUCCESS ? 0 : -3;
 }
 
+// ---- host: general form over a token grid [B][H][W][64] fp32: box = [1][by rows][bx tokens][32 floats]
+// taking every `step`-th token in x and y (step = 2: one parity class of the 2x2 PatchMerging
+// neighbourhood), 128 B swizzle.  The box lands as by*bx rows of 128 B, row = y*bx + x.
+inline int encode_grid(CUtensorMap* out, const float* base, int B, int H, int W, int bx, int by,
+                       int step) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) return -2;
+  const cuuint64_t gdim[4] = {64, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+  const cuuint64_t gstride[3] = {256, (cuuint64_t)W * 256, (cuuint64_t)H * W * 256};
+  const cuuint32_t box[4] = {32, (cuuint32_t)(bx * step), (cuuint32_t)(by * step), 1};
+  const cuuint32_t estr[4] = {1, (cuuint32_t)step, (cuuint32_t)step, 1};
+  const CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(base), gdim, gstride,
+                        box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -3;
+}
+
 inline int encode_rows64(CUtensorMap* out, const float* base, long long n_rows) {
   EncodeTiledFn fn = encode_tiled_fn();
   if (!fn) return -2;

@@ -144,6 +144,10 @@ class PatchMerging(nn.Module):
 
     def forward(self, x, num_patches):
         ph, pw = num_patches
+        if not torch.is_grad_enabled() and ops.get_precision() == "tf32":
+            y = ops.patch_merge_tc_fwd(x, self.norm.weight.detach(), self.norm.bias.detach(),
+                                       self.reduction.weight.detach(), ph, pw)
+            return y, (ph // 2, pw // 2)
         y = ops.PatchMergeFunction.apply(x, ph, pw, self.norm.weight, self.norm.bias,
                                          self.reduction.weight)
         return y, (ph // 2, pw // 2)
@@ -167,10 +171,14 @@ class _Stage(nn.Module):
         inplace = not torch.is_grad_enabled() and ops.get_precision() == "tf32"
         for i, blk in enumerate(self.blocks):
             last = i == n - 1
-            if inplace and i > 0:
-                # z is the previous block's zsum, private to this loop: the block adds into it
+            if inplace:
+                # the block adds its output into z (TMA reduce-add), so z must be private to this
+                # loop: the stage input is copied once, later blocks own the previous block's sum
+                want_zsum = (not last) or need_sum_last
+                if i == 0 and want_zsum:
+                    z = z.clone()
                 out, zsum = ops.nstb_infer_(z, *num_patches, blk.num_heads, blk.shift_size, last,
-                                            (not last) or need_sum_last, blk.kernel_params())
+                                            want_zsum, blk.kernel_params())
             else:
                 out, zsum = blk(z, num_patches, want_out=last, want_zsum=(not last) or need_sum_last)
             z = zsum

@@ -136,6 +136,31 @@ def _(u, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, merge_w, merge_b
     return u.new_empty((*u.shape[:3], 64))
 
 
+@torch.library.custom_op(f"{_NS}::ngram_ctx_infer", mutates_args=())
+def ngram_ctx_infer(z: Tensor, uni_w: Tensor, uni_b: Tensor, qkv_w: Tensor, qkv_b: Tensor,
+                    proj_w: Tensor, proj_b: Tensor, logit_scale: Tensor, bias_table: Tensor,
+                    merge_w: Tensor, merge_b: Tensor, ph: int, pw: int, nh: int) -> Tensor:
+    """ctx = ngram_ctx_fwd(unigram_fwd(z)) for inference: the unigram pass also applies the n-gram
+    qkv Linear once per window, the context kernel gathers those rows (two launches, same result)."""
+    _chk(z, uni_w, uni_b, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, merge_w, merge_b)
+    B, wh, ww = z.shape[0], ph // 8, pw // 8
+    if wh < 2 or ww < 2:
+        raise RuntimeError("NGramContext needs at least 2x2 windows per stage "
+                           "(the reference raises for smaller inputs, SURVEY.md A.4)")
+    nq = torch.empty((B, wh, ww, 96), device=z.device, dtype=torch.float32)
+    ctx = torch.empty((B, wh, ww, 64), device=z.device, dtype=torch.float32)
+    _call("unigram_qkv_fwd", _p(z), _p(uni_w), _p(uni_b), _p(qkv_w), _p(qkv_b), _p(nq), B, ph, pw, nh,
+          _stream())
+    _call("ngram_ctx_pre_fwd", _p(nq), _p(proj_w), _p(proj_b), _p(logit_scale), _p(bias_table),
+          _p(merge_w), _p(merge_b), _p(ctx), B, wh, ww, nh, _stream())
+    return ctx
+
+
+@ngram_ctx_infer.register_fake
+def _(z, uni_w, uni_b, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, merge_w, merge_b, ph, pw, nh):
+    return z.new_empty((z.shape[0], ph // 8, pw // 8, 64))
+
+
 @torch.library.custom_op(f"{_NS}::ngram_ctx_bwd", mutates_args=("du", "grads"))
 def ngram_ctx_bwd(u: Tensor, dctx: Tensor, params: List[Tensor], du: Tensor,
                   grads: List[Tensor], nh: int) -> None:
@@ -283,6 +308,22 @@ def _(x, ln_w, ln_b, red_w, ph, pw):
     return x.new_empty((x.shape[0], (ph // 2) * (pw // 2), 64))
 
 
+@torch.library.custom_op(f"{_NS}::patch_merge_tc_fwd", mutates_args=())
+def patch_merge_tc_fwd(x: Tensor, ln_w: Tensor, ln_b: Tensor, red_w: Tensor, ph: int,
+                       pw: int) -> Tensor:
+    """patch_merge_fwd on TMA + tcgen05 (tf32 operands, fp32 accumulate)."""
+    _chk(x, ln_w, ln_b, red_w)
+    B = x.shape[0]
+    y = torch.empty((B, (ph // 2) * (pw // 2), 64), device=x.device, dtype=torch.float32)
+    _call("patch_merge_tc_fwd", _p(x), _p(ln_w), _p(ln_b), _p(red_w), _p(y), B, ph, pw, _stream())
+    return y
+
+
+@patch_merge_tc_fwd.register_fake
+def _(x, ln_w, ln_b, red_w, ph, pw):
+    return x.new_empty((x.shape[0], (ph // 2) * (pw // 2), 64))
+
+
 @torch.library.custom_op(f"{_NS}::patch_merge_bwd", mutates_args=("dx", "grads"))
 def patch_merge_bwd(x: Tensor, dy: Tensor, params: List[Tensor], dx: Tensor, grads: List[Tensor],
                     ph: int, pw: int) -> None:
@@ -425,8 +466,7 @@ def nstb_infer_(z: Tensor, ph: int, pw: int, nh: int, shift: int, want_out: bool
     """Inference form of one NSTB for a PRIVATE stream buffer z (tensor-core precision only):
     z is overwritten with zsum = out + z when want_zsum (the next block's input); nothing is saved."""
     P = [p.detach() for p in params]
-    u = unigram_fwd(z, P[0], P[1], ph, pw)
-    c = ngram_ctx_fwd(u, P[2], P[3], P[4], P[5], P[6], P[7], P[8], P[9], nh)
+    c = ngram_ctx_infer(z, *P[0:10], ph, pw, nh)
     a = attn_tc_fwd(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw, nh, shift, True)
     out = mlp_tma_fwd_(a, z if want_zsum else None, P[18], P[19], P[20], P[21], P[22], P[23], want_out)
     return out, (z if want_zsum else out.new_empty(0))
