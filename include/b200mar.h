@@ -216,6 +216,12 @@ int b200mar_bottleneck_tail_fwd(const float* cat, const float* dw_w /*[84,1,3,3]
                                 const float* dw_b, const float* pw_w /*[64,84]*/,
                                 const float* pw_b, const float* ln_w, const float* ln_b,
                                 const float* e1, float* out, int B, int H, int W, void* stream);
+/* Same contract on TMA + tcgen05: one bulk tensor load per 18x10x84 halo (zero padding = the map's
+ * out-of-bounds fill), depthwise + GELU per token thread, pointwise as fp16 MMAs, TMA store.    */
+int b200mar_bottleneck_tail_tc_fwd(const float* cat, const float* dw_w, const float* dw_b,
+                                   const float* pw_w, const float* pw_b,
+                                   const float* ln_w, const float* ln_b,
+                                   const float* e1, float* out, int B, int H, int W, void* stream);
 /* a13+a14 decoder tail: LN(norm) + global skip (ngswin.py:190,204), Reconstruction
  *     (components/reconstruction.py:14-19) and the crop of ngswin.py:208:
  *     out [B,1,H0,W0] = tanh(conv3x3(conv3x3(LN(dec) + c0; w1,b1); w2,b2))[:H0,:W0].

@@ -227,3 +227,28 @@ def test_patch_merge_tc_matches_fp32_kernel(B, ph, pw):
     scale = ref.abs().max().item()
     assert d.max().item() <= 1.5e-3 * scale and d.mean().item() <= 2e-4 * scale
     assert ops.tc_error() == 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("B,H,W", [(1, 16, 16), (2, 24, 40), (1, 64, 64), (1, 104, 72)])
+def test_bottleneck_tc_matches_fp32_kernel(B, H, W):
+    """TMA-halo + tcgen05 SCDP bottleneck tail vs the fp32 kernel (conv zero padding comes from the
+    tensor map's out-of-bounds fill; ragged tiles when W is not a multiple of 16)."""
+    from transmar_gan_b200 import ops
+    sd = {k: v.cuda() for k, v in O.synthetic_state_dict("W2", seed=4).items()}
+    Wt = [sd["bottleneck." + n].contiguous() for n in
+          ("depthwise.weight", "depthwise.bias", "pointwise.weight", "pointwise.bias", "norm.weight", "norm.bias")]
+    g = torch.Generator().manual_seed(H * 1000 + W)
+    mk = lambda h, w: torch.randn(B, h * w, 64, generator=g).cuda()
+    args = [mk(H, W), mk(H // 2, W // 2), mk(H // 4, W // 4), mk(H, W), mk(H // 2, W // 2),
+            mk(H // 4, W // 4), *Wt, H, W]
+    old = ops.set_precision("fp32")
+    try:
+        ref = ops.bottleneck_fwd(*args)
+        ops.set_precision("tf32")
+        got = ops.bottleneck_fwd(*args)
+    finally:
+        ops.set_precision(old)
+    d = (ref - got).abs()
+    assert d.max().item() <= 6e-3 and d.mean().item() <= 6e-4
+    assert ops.tc_error() == 0

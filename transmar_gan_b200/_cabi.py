@@ -51,6 +51,7 @@ SIGNATURES = {
     "b200mar_cascade_proj_fwd": [_P] * 7 + [_I] * 3 + [_P],
     "b200mar_bottleneck_cat_fwd": [_P] * 7 + [_I] * 3 + [_P],
     "b200mar_bottleneck_tail_fwd": [_P] * 9 + [_I] * 3 + [_P],
+    "b200mar_bottleneck_tail_tc_fwd": [_P] * 9 + [_I] * 3 + [_P],
     "b200mar_final_recon_fwd": [_P] * 10 + [_I] * 5 + [_P],
     "b200mar_partition_index": [_P] * 2 + [_I] * 4 + [_P],
     "b200mar_shift_mask": [_P] + [_I] * 3 + [_P],

@@ -21,14 +21,15 @@ int tc_error_mlp();
 int tc_error_probe();
 int tc_error_attn();
 int tc_error_merge();
+int tc_error_bottleneck();
 }  // namespace b200mar
 
 // 1 if any tensor-core kernel of this process hit its bounded mbarrier wait (descriptor-bug guard)
 extern "C" int b200mar_tc_error(void) {
   const int a = b200mar::tc_error_mlp(), b = b200mar::tc_error_probe(), c = b200mar::tc_error_attn(),
-            d = b200mar::tc_error_merge();
-  if (a < 0 || b < 0 || c < 0 || d < 0) return -1;
-  return (a | b | c | d) ? 1 : 0;
+            d = b200mar::tc_error_merge(), e = b200mar::tc_error_bottleneck();
+  if (a < 0 || b < 0 || c < 0 || d < 0 || e < 0) return -1;
+  return (a | b | c | d | e) ? 1 : 0;
 }
 
 extern "C" int b200mar_abi_version(void) { return 2; }

@@ -18,6 +18,7 @@
 #include "mlp_common.cuh"
 #include "tc.cuh"
 #include "tma.cuh"
+#include "gelu_fast.cuh"
 #include <cuda_fp16.h>
 
 namespace b200mar {
@@ -42,21 +43,6 @@ struct MlpTcSmem {                                   // BYTE offsets
   static constexpr int kBytes = oWork + kMlpWorkers * kWorkBytes;
   static_assert(kBytes <= 232448, "mlp_tc shared memory exceeds 227 KB");
 };
-
-// GELU(x) = 0.5 x (1 + erf(x / sqrt 2)) with erf from Abramowitz & Stegun 7.1.26
-// (|error| <= 1.5e-7, two MUFU ops) instead of the ~25-instruction erff.
-__device__ __forceinline__ float gelu_fast(float x, float half_scale) {
-  const float z = fabsf(x) * 0.70710678118654752440f;
-  const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
-  float p = fmaf(1.061405429f, t, -1.453152027f);
-  p = fmaf(p, t, 1.421413741f);
-  p = fmaf(p, t, -0.284496736f);
-  p = fmaf(p, t, 0.254829592f);
-  const float e = tc::ex2_approx(-z * z * 1.4426950408889634f);
-  const float erf_abs = fmaf(-p * t, e, 1.0f);       // erf(|x|/sqrt2)
-  const float hx = half_scale * x;
-  return fmaf(hx, copysignf(erf_abs, x), hx);
-}
 
 // Power-of-two scale for a hidden row so that it cannot overflow fp16: |pre_j| <= amax * maxL1 + maxb
 // (amax = the power-of-two upper bound of the row's max|a|, maxL1 = max_j sum_k |W1[j][k]|,

@@ -140,6 +140,22 @@ inline int encode_grid(CUtensorMap* out, const float* base, int B, int H, int W,
   return r == CUDA_SUCCESS ? 0 : -3;
 }
 
+// ---- host: un-swizzled halo box over a channels-last grid [B][H][W][C] fp32 (C * 4 a multiple of
+// 16): box = [1][bh][bw][C]; out-of-bounds positions (negative or past the edge) are zero-filled,
+// which is exactly a convolution's zero padding.
+inline int encode_halo(CUtensorMap* out, const float* base, int B, int H, int W, int C, int bw, int bh) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) return -2;
+  const cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)B};
+  const cuuint64_t gstride[3] = {(cuuint64_t)C * 4, (cuuint64_t)W * C * 4, (cuuint64_t)H * W * C * 4};
+  const cuuint32_t box[4] = {(cuuint32_t)C, (cuuint32_t)bw, (cuuint32_t)bh, 1};
+  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  const CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(base), gdim, gstride,
+                        box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -3;
+}
+
 inline int encode_rows64(CUtensorMap* out, const float* base, long long n_rows) {
   EncodeTiledFn fn = encode_tiled_fn();
   if (!fn) return -2;

@@ -399,7 +399,7 @@ def bottleneck_fwd(c0: Tensor, p0: Tensor, p00: Tensor, e1: Tensor, e2: Tensor, 
     cat = torch.empty((B, H * W, 84), device=c0.device, dtype=torch.float32)
     _call("bottleneck_cat_fwd", _p(c0), _p(p0), _p(p00), _p(e1), _p(e2), _p(e3), _p(cat), B, H, W, _stream())
     out = torch.empty_like(c0)
-    _call("bottleneck_tail_fwd", _p(cat), _p(dw_w), _p(dw_b), _p(pw_w), _p(pw_b), _p(ln_w), _p(ln_b),
+    _call("bottleneck_tail_tc_fwd" if _PRECISION == "tf32" else "bottleneck_tail_fwd", _p(cat), _p(dw_w), _p(dw_b), _p(pw_w), _p(pw_b), _p(ln_w), _p(ln_b),
           _p(e1), _p(out), B, H, W, _stream())
     return out
 
