@@ -204,6 +204,11 @@ int b200mar_shallow_tok_fwd(const float* x, const float* w /*[64,1,3,3]*/, const
 int b200mar_cascade_proj_fwd(const float* srcA, const float* srcB, const float* direct,
                              const float* w, const float* bias, float* out, float* poolA,
                              int B, int h, int wd, void* stream);
+/* Same contract on TMA + tcgen05 (kind::tf32): stride-2 boxes + running max build the pooled
+ * operands in place, the direct tile is an MMA operand as delivered, TMA stores.              */
+int b200mar_cascade_proj_tc_fwd(const float* srcA, const float* srcB, const float* direct,
+                                const float* w, const float* bias, float* out, float* poolA,
+                                int B, int h, int wd, void* stream);
 /* a12 SCDPBottleneck front (components/encoder_decoder.py:159-164,191-192; pooling.py:32-37):
  *     cat[b,t,:] = [ e1 + lrelu(c0) | shuffle2(e2 + lrelu(p0)) | shuffle4(e3 + lrelu(p00)) ],
  *     p0 = maxpool2(c0), p00 = maxpool4(c0) (token-major), cat [B,H*W,84].                   */

@@ -252,3 +252,30 @@ def test_bottleneck_tc_matches_fp32_kernel(B, H, W):
     d = (ref - got).abs()
     assert d.max().item() <= 6e-3 and d.mean().item() <= 6e-4
     assert ops.tc_error() == 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("two", [False, True])
+@pytest.mark.parametrize("B,h,w", [(1, 8, 16), (2, 12, 20), (1, 32, 32), (2, 52, 36)])
+def test_cascade_proj_tc_matches_fp32_kernel(two, B, h, w):
+    """TMA + tcgen05 InterPool/concat/Linear vs the fp32 kernel; pooled features are bit-exact."""
+    from transmar_gan_b200 import ops
+    sd = {k: v.cuda() for k, v in O.synthetic_state_dict("W2", seed=6).items()}
+    lay = "encoder_layer3" if two else "encoder_layer2"
+    wt, bias = (sd[lay + ".across_cascade_proj." + n].contiguous() for n in ("weight", "bias"))
+    g = torch.Generator().manual_seed(h * 100 + w + int(two))
+    A = torch.randn(B, 4 * h * w, 64, generator=g).cuda()
+    Bs = torch.randn(B, 4 * h * w, 64, generator=g).cuda() if two else None
+    D = torch.randn(B, h * w, 64, generator=g).cuda()
+    old = ops.set_precision("fp32")
+    try:
+        ro, rp = ops.cascade_proj_fwd(A, Bs, D, wt, bias, h, w)
+        ops.set_precision("tf32")
+        go, gp = ops.cascade_proj_fwd(A, Bs, D, wt, bias, h, w)
+    finally:
+        ops.set_precision(old)
+    assert torch.equal(rp, gp)
+    d = (ro - go).abs()
+    scale = ro.abs().max().item()
+    assert d.max().item() <= 2e-3 * scale and d.mean().item() <= 2e-4 * scale
+    assert ops.tc_error() == 0

@@ -49,6 +49,7 @@ SIGNATURES = {
     "b200mar_pixel_shuffle_cat": [_P] * 4 + [_I] * 4 + [_P],
     "b200mar_shallow_tok_fwd": [_P] * 4 + [_I] * 3 + [_P],
     "b200mar_cascade_proj_fwd": [_P] * 7 + [_I] * 3 + [_P],
+    "b200mar_cascade_proj_tc_fwd": [_P] * 7 + [_I] * 3 + [_P],
     "b200mar_bottleneck_cat_fwd": [_P] * 7 + [_I] * 3 + [_P],
     "b200mar_bottleneck_tail_fwd": [_P] * 9 + [_I] * 3 + [_P],
     "b200mar_bottleneck_tail_tc_fwd": [_P] * 9 + [_I] * 3 + [_P],

@@ -157,7 +157,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
     const int n = idx & 63, kc = idx >> 6;
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
     if (kc * 4 < A) v = *reinterpret_cast<const float4*>(p.proj_w + n * A + kc * 4);
-    *reinterpret_cast<float4*>(sWp + kc * 256 + n * 4) = v;
+    *reinterpret_cast<float4*>(sWp + kc * 256 + n * 4) = tc::round_tf32(v);   // the MMA would truncate
   }
   for (int n = tid; n < L::kWRows; n += 128 * kWorkers) {      // bias in the same packed order
     const int h = n / 48, part = (n % 48) >> 4, d = n & 15;
@@ -409,7 +409,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
         k0[(2 * wsel + 1) * 64] = make_uint4(kp[4], kp[5], kp[6], kp[7]);
         float* vt = reinterpret_cast<float*>(sV + (lrow >> 2) * kVChunk + wsel * 256) + (lrow & 3);
 #pragma unroll
-        for (int d = 0; d < HD; ++d) vt[d * 4] = qkv[32 + d];
+        for (int d = 0; d < HD; ++d) vt[d * 4] = tc::round_tf32(qkv[32 + d]);
       }
       PROF(6);                                         // operand stores
       tc::fence_async_smem();
@@ -532,7 +532,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
 #pragma unroll
     for (int kc = 0; kc < 16; ++kc)                    // fp32 O tile over [X|Q|K|V] (all dead by now)
       *reinterpret_cast<float4*>(sStage + kc * 512 + row * 4) =
-          make_float4(o[kc * 4], o[kc * 4 + 1], o[kc * 4 + 2], o[kc * 4 + 3]);
+          tc::round_tf32(make_float4(o[kc * 4], o[kc * 4 + 1], o[kc * 4 + 2], o[kc * 4 + 3]));
     tc::fence_async_smem();
     tc::tc_fence_before();
     tc::worker_sync(1 + wk);

@@ -9,6 +9,8 @@
 //   final_dot9       LN(norm) + global skip, then the 64->1 conv's per-tap dots (ngswin.py:190,204; reconstruction.py:14)
 //   recon            tap gather (conv 64->1), conv3x3 1->1, tanh, crop           (reconstruction.py:14-19, ngswin.py:208)
 #include "common.cuh"
+#include "tc.cuh"
+#include "tma.cuh"
 #include "../../include/b200mar.h"
 
 namespace b200mar {
@@ -32,10 +34,11 @@ __global__ void __launch_bounds__(256) shallow_tok_kernel(const float* __restric
 #pragma unroll
     for (int k = 0; k < 9; ++k) wr[j][k] = w[(cq * 4 + j) * 9 + k];
   }
-  const long long npix = (long long)B * H * W;
-  for (long long pix = (long long)blockIdx.x * 16 + pl; pix < npix; pix += (long long)gridDim.x * 16) {
-    const int xx = (int)(pix % W), yy = (int)((pix / W) % H);
-    const float* img = x + (pix - (long long)yy * W - xx);
+  const unsigned npix = (unsigned)B * H * W;           // < 2^31 (checked by the launcher): 32-bit index math
+  for (unsigned pix = blockIdx.x * 16u + pl; pix < npix; pix += gridDim.x * 16u) {
+    const unsigned rowi = pix / (unsigned)W;
+    const int xx = (int)(pix - rowi * W), yy = (int)(rowi % (unsigned)H);
+    const float* img = x + (pix - (unsigned)yy * W - xx);
     float in[9];
 #pragma unroll
     for (int dy = 0; dy < 3; ++dy)
@@ -51,7 +54,7 @@ __global__ void __launch_bounds__(256) shallow_tok_kernel(const float* __restric
 #pragma unroll
       for (int k = 0; k < 9; ++k) o[j] = fmaf(wr[j][k], in[k], o[j]);
     }
-    *reinterpret_cast<float4*>(c0 + pix * 64 + cq * 4) = make_float4(o[0], o[1], o[2], o[3]);
+    *reinterpret_cast<float4*>(c0 + (size_t)pix * 64 + cq * 4) = make_float4(o[0], o[1], o[2], o[3]);
   }
 }
 
@@ -119,17 +122,18 @@ __global__ void __launch_bounds__(256) bottleneck_cat_kernel(
     const float* __restrict__ c0, const float* __restrict__ p0, const float* __restrict__ p00,
     const float* __restrict__ e1, const float* __restrict__ e2, const float* __restrict__ e3,
     float* __restrict__ cat, int B, int H, int W) {
-  const long long n = (long long)B * H * W * 21;
-  for (long long idx = (long long)blockIdx.x * 256 + threadIdx.x; idx < n; idx += (long long)gridDim.x * 256) {
-    const long long t = idx / 21;
-    const int g = (int)(idx - t * 21);
+  const unsigned n = (unsigned)B * H * W * 21u;         // < 2^31 (checked by the launcher)
+  for (unsigned idx = blockIdx.x * 256u + threadIdx.x; idx < n; idx += gridDim.x * 256u) {
+    const unsigned t = idx / 21u;
+    const int g = (int)(idx - t * 21u);
     float4 v;
     if (g < 16) {
-      const float4 a = ld4(e1 + t * 64 + g * 4), s = ld4(c0 + t * 64 + g * 4);
+      const float4 a = ld4(e1 + (size_t)t * 64 + g * 4), s = ld4(c0 + (size_t)t * 64 + g * 4);
       v = make_float4(a.x + leaky(s.x), a.y + leaky(s.y), a.z + leaky(s.z), a.w + leaky(s.w));
     } else {
-      const int xx = (int)(t % W), yy = (int)((t / W) % H);
-      const long long b = t / ((long long)W * H);
+      const unsigned rowi = t / (unsigned)W;
+      const int xx = (int)(t - rowi * W), yy = (int)(rowi % (unsigned)H);
+      const long long b = rowi / (unsigned)H;
       float o[4];
       if (g < 20) {                       // scale 2: channel c <- source channel (c*2 + y%2)*2 + x%2
         const long long lo = ((b * (H / 2) + yy / 2) * (W / 2) + xx / 2) * 64;
@@ -148,7 +152,7 @@ __global__ void __launch_bounds__(256) bottleneck_cat_kernel(
       }
       v = make_float4(o[0], o[1], o[2], o[3]);
     }
-    *reinterpret_cast<float4*>(cat + t * 84 + g * 4) = v;
+    *reinterpret_cast<float4*>(cat + (size_t)t * 84 + g * 4) = v;
   }
 }
 
@@ -275,6 +279,101 @@ __global__ void __launch_bounds__(256) final_dot9_kernel(const float* __restrict
   }
 }
 
+// TMA form of the same pass: 128-token tiles of dec and c0 arrive as 128 B-swizzled bulk tensor loads,
+// thread t owns token row t (LayerNorm and the nine 64-long dots run in registers, no shuffles); the
+// rows are pulled into registers first so that the next tile's loads overlap the arithmetic.
+constexpr int kDotWorkers = 3;
+struct Dot9Smem {
+  static constexpr int oW = 0;                        // fp32 [64 c][12] (9 taps, padded)
+  static constexpr int oLnW = oW + 64 * 12 * 4;
+  static constexpr int oLnB = oLnW + 256;
+  static constexpr int oBar = oLnB + 256;
+  static constexpr int oWork = ((oBar + 64 + 1023) / 1024) * 1024;
+  static constexpr int kWorkBytes = 2 * 32768;        // dec tile, c0 tile
+  static constexpr int kBytes = oWork + kDotWorkers * kWorkBytes;
+};
+__global__ void __launch_bounds__(128 * kDotWorkers, 1)
+final_dot9_tma_kernel(const __grid_constant__ CUtensorMap mapDec, const __grid_constant__ CUtensorMap mapC0,
+                      const float* __restrict__ ln_w, const float* __restrict__ ln_b,
+                      const float* __restrict__ w1, float* __restrict__ taps, long long ntok) {
+  using L = Dot9Smem;
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  float* sW = reinterpret_cast<float*>(smem_raw + L::oW);
+  float* sLnW = reinterpret_cast<float*>(smem_raw + L::oLnW);
+  float* sLnB = reinterpret_cast<float*>(smem_raw + L::oLnB);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + L::oBar);
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  const int wk = warp >> 2, wq = warp & 3;
+  unsigned char* sWk = smem_raw + L::oWork + wk * L::kWorkBytes;
+  uint64_t* bar = bars + wk;
+  for (int i = tid; i < 64 * 12; i += 128 * kDotWorkers) {
+    const int c = i / 12, k = i - c * 12;
+    sW[i] = k < 9 ? w1[c * 9 + k] : 0.f;
+  }
+  if (tid < 64) { sLnW[tid] = ln_w[tid]; sLnB[tid] = ln_b[tid]; }
+  if (tid == 0) {
+    for (int i = 0; i < kDotWorkers; ++i) tc::mbar_init(bars + i, 1);
+    tc::fence_barrier_init();
+    tma::prefetch_desc(&mapDec); tma::prefetch_desc(&mapC0);
+  }
+  tc::fence_async_smem();
+  __syncthreads();
+  const int row = wq * 32 + lane;
+  const bool leader = wq == 0 && lane == 0;
+  const long long ntile = (ntok + 127) / 128;
+  const long long stride = (long long)gridDim.x * kDotWorkers;
+  auto issue = [&](long long t_) {
+    tma::mbar_expect_tx(bar, 65536);
+    tma::load_2d(&mapDec, bar, sWk, 0, (int)(t_ * 128));
+    tma::load_2d(&mapDec, bar, sWk + 16384, 32, (int)(t_ * 128));
+    tma::load_2d(&mapC0, bar, sWk + 32768, 0, (int)(t_ * 128));
+    tma::load_2d(&mapC0, bar, sWk + 49152, 32, (int)(t_ * 128));
+  };
+  long long tile = (long long)blockIdx.x * kDotWorkers + wk;
+  if (leader && tile < ntile) issue(tile);
+  uint32_t ph = 0;
+  for (; tile < ntile; tile += stride) {
+    tc::mbar_wait(bar, ph, nullptr); ph ^= 1;
+    float y[64], c[64];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const float4 a = *reinterpret_cast<const float4*>(sWk + tma::tile_off(row, i));
+      const float4 b = *reinterpret_cast<const float4*>(sWk + 32768 + tma::tile_off(row, i));
+      y[4 * i] = a.x; y[4 * i + 1] = a.y; y[4 * i + 2] = a.z; y[4 * i + 3] = a.w;
+      c[4 * i] = b.x; c[4 * i + 1] = b.y; c[4 * i + 2] = b.z; c[4 * i + 3] = b.w;
+    }
+    tc::worker_sync(1 + wk);                           // rows are in registers: refill the buffers
+    if (leader && tile + stride < ntile) issue(tile + stride);
+    float mean = 0.f;
+#pragma unroll
+    for (int i = 0; i < 64; ++i) mean += y[i];
+    mean *= (1.0f / 64.f);
+    float var = 0.f;
+#pragma unroll
+    for (int i = 0; i < 64; ++i) { y[i] -= mean; var = fmaf(y[i], y[i], var); }
+    const float rstd = 1.0f / sqrtf(var * (1.0f / 64.f) + kLnEps);
+    float d[9];
+#pragma unroll
+    for (int k = 0; k < 9; ++k) d[k] = 0.f;
+#pragma unroll
+    for (int i = 0; i < 64; ++i) {
+      const float t = fmaf(y[i] * rstd, sLnW[i], sLnB[i]) + c[i];
+      const float4 wa = *reinterpret_cast<const float4*>(sW + i * 12);
+      const float4 wb = *reinterpret_cast<const float4*>(sW + i * 12 + 4);
+      const float wc = sW[i * 12 + 8];
+      d[0] = fmaf(t, wa.x, d[0]); d[1] = fmaf(t, wa.y, d[1]); d[2] = fmaf(t, wa.z, d[2]);
+      d[3] = fmaf(t, wa.w, d[3]); d[4] = fmaf(t, wb.x, d[4]); d[5] = fmaf(t, wb.y, d[5]);
+      d[6] = fmaf(t, wb.z, d[6]); d[7] = fmaf(t, wb.w, d[7]); d[8] = fmaf(t, wc, d[8]);
+    }
+    const long long tok = tile * 128 + row;
+    if (tok < ntok) {
+#pragma unroll
+      for (int k = 0; k < 9; ++k) taps[tok * 9 + k] = d[k];
+    }
+  }
+}
+
 // ------------------------------------------------------------------ reconstruction tail
 // out1 = b1 + sum_k taps[y+dy-1, x+dx-1][k] (zero outside), out = tanh(conv3x3(out1; w2) + b2), crop
 __global__ void __launch_bounds__(256) recon_kernel(const float* __restrict__ taps,
@@ -336,7 +435,7 @@ using namespace b200mar;
 
 extern "C" int b200mar_shallow_tok_fwd(const float* x, const float* w, const float* b, float* c0,
                                        int B, int H, int W, void* stream) {
-  if (B <= 0 || H <= 0 || W <= 0) return -1;
+  if (B <= 0 || H <= 0 || W <= 0 || (long long)B * H * W >= (1ll << 31)) return -1;
   shallow_tok_kernel<<<grid_for((long long)B * H * W, 16 * 8), 256, 0, (cudaStream_t)stream>>>(x, w, b, c0, B, H, W);
   B200MAR_CHECK(cudaGetLastError());
   return 0;
@@ -359,7 +458,7 @@ extern "C" int b200mar_cascade_proj_fwd(const float* srcA, const float* srcB, co
 extern "C" int b200mar_bottleneck_cat_fwd(const float* c0, const float* p0, const float* p00,
                                           const float* e1, const float* e2, const float* e3,
                                           float* cat, int B, int H, int W, void* stream) {
-  if (B <= 0 || H % 4 || W % 4) return -1;
+  if (B <= 0 || H % 4 || W % 4 || (long long)B * H * W * 21 >= (1ll << 31)) return -1;
   bottleneck_cat_kernel<<<grid_for((long long)B * H * W * 21, 256 * 4), 256, 0, (cudaStream_t)stream>>>(
       c0, p0, p00, e1, e2, e3, cat, B, H, W);
   B200MAR_CHECK(cudaGetLastError());
@@ -387,8 +486,23 @@ extern "C" int b200mar_final_recon_fwd(const float* dec, const float* c0, const 
                                        int B, int H, int W, int H0, int W0, void* stream) {
   if (B <= 0 || H <= 0 || W <= 0 || H0 > H || W0 > W) return -1;
   const long long ntok = (long long)B * H * W;
-  final_dot9_kernel<<<grid_for(ntok, 8 * 4), 256, 0, (cudaStream_t)stream>>>(dec, c0, ln_w, ln_b, w1, taps, ntok);
-  B200MAR_CHECK(cudaGetLastError());
+  {
+    CUtensorMap mD, mC;
+    if (int rc = tma::encode_rows64(&mD, dec, ntok)) return rc;
+    if (int rc = tma::encode_rows64(&mC, c0, ntok)) return rc;
+    static bool configured = false;
+    if (!configured) {
+      B200MAR_CHECK(cudaFuncSetAttribute(final_dot9_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)Dot9Smem::kBytes));
+      configured = true;
+    }
+    const long long ntile9 = (ntok + 127) / 128;
+    long long grid = (ntile9 + kDotWorkers - 1) / kDotWorkers;
+    if (grid > sm_count()) grid = sm_count();
+    final_dot9_tma_kernel<<<(int)grid, 128 * kDotWorkers, Dot9Smem::kBytes, (cudaStream_t)stream>>>(
+        mD, mC, ln_w, ln_b, w1, taps, ntok);
+    B200MAR_CHECK(cudaGetLastError());
+  }
   const int ntile = B * ((W + 31) / 32) * ((H + 7) / 8);
   recon_kernel<<<grid_for(ntile, 1), 256, 0, (cudaStream_t)stream>>>(taps, b1, w2, b2, out, B, H, W, H0, W0);
   B200MAR_CHECK(cudaGetLastError());

@@ -38,11 +38,7 @@ struct MergeTcSmem {                                 // BYTE offsets
   static_assert(kBytes <= 232448, "merge_tc shared memory exceeds 227 KB");
 };
 
-__device__ __forceinline__ float round_tf32(float x) {
-  uint32_t r;
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-  return __uint_as_float(r);
-}
+using tc::round_tf32;
 
 __device__ __forceinline__ uint64_t smem_desc_sw128(uint32_t saddr) {
   // K-major, 128 B swizzle: 8-row groups of 1024 B (SBO); LBO unused (1); layout type 2

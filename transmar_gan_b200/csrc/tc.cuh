@@ -177,6 +177,16 @@ __device__ __forceinline__ void mma_tile_tf32(uint32_t tmem_d, uint32_t a_saddr,
   }
 }
 // make all previously issued MMAs arrive on an mbarrier when they complete
+// fp32 -> tf32, round to nearest (the MMA itself ignores the low 13 mantissa bits, i.e. truncates)
+__device__ __forceinline__ float round_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+__device__ __forceinline__ float4 round_tf32(float4 v) {
+  return make_float4(round_tf32(v.x), round_tf32(v.y), round_tf32(v.z), round_tf32(v.w));
+}
+
 __device__ __forceinline__ void mma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
                ::"r"(smem_u32(bar)) : "memory");

@@ -385,8 +385,8 @@ def cascade_proj_fwd(srcA: Tensor, srcB: Optional[Tensor], direct: Tensor, w: Te
     B = direct.shape[0]
     out = torch.empty((B, h * wd, 64), device=direct.device, dtype=torch.float32)
     pool = torch.empty_like(out) if want_pool else None
-    _call("cascade_proj_fwd", _p(srcA), _p(srcB), _p(direct), _p(w), _p(bias), _p(out), _p(pool),
-          B, h, wd, _stream())
+    _call("cascade_proj_tc_fwd" if _PRECISION == "tf32" else "cascade_proj_fwd", _p(srcA), _p(srcB),
+          _p(direct), _p(w), _p(bias), _p(out), _p(pool), B, h, wd, _stream())
     return out, pool
 
 
