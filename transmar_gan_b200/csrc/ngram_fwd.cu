@@ -193,7 +193,9 @@ __global__ void __launch_bounds__(kThreads) ngram_ctx_fwd_kernel(NgramParams p) 
           sq = fmaf(qn[t][d], qn[t][d], sq);
           sk = fmaf(kn[t][d], kn[t][d], sk);
         }
-        const float iq = 1.0f / fmaxf(sqrtf(sq), kNormEps), ik = 1.0f / fmaxf(sqrtf(sk), kNormEps);
+        // 1 / max(||.||, eps): eps^2 = 1e-24 is a normal float, so max(sq, eps^2) under rsqrt is exact
+        const float iq = PRE ? rsqrtf(fmaxf(sq, kNormEps * kNormEps)) : 1.0f / fmaxf(sqrtf(sq), kNormEps);
+        const float ik = PRE ? rsqrtf(fmaxf(sk, kNormEps * kNormEps)) : 1.0f / fmaxf(sqrtf(sk), kNormEps);
 #pragma unroll
         for (int d = 0; d < HD; ++d) { qn[t][d] *= iq; kn[t][d] *= ik; }
       }
@@ -214,8 +216,8 @@ __global__ void __launch_bounds__(kThreads) ngram_ctx_fwd_kernel(NgramParams p) 
         }
         float sum = 0.f;
 #pragma unroll
-        for (int kq = 0; kq < 4; ++kq) { s[kq] = expf(s[kq] - mx); sum += s[kq]; }
-        const float inv = 0.25f / sum;   // softmax normalisation and the AvgPool2d(2) mean
+        for (int kq = 0; kq < 4; ++kq) { s[kq] = PRE ? __expf(s[kq] - mx) : expf(s[kq] - mx); sum += s[kq]; }
+        const float inv = PRE ? __fdividef(0.25f, sum) : 0.25f / sum;   // softmax normalisation and the AvgPool2d(2) mean
 #pragma unroll
         for (int kq = 0; kq < 4; ++kq) {
           const float pv = s[kq] * inv;
@@ -237,14 +239,19 @@ __global__ void __launch_bounds__(kThreads) ngram_ctx_fwd_kernel(NgramParams p) 
       sCat[dir * 32 + lane] = acc;
     }
     __syncwarp();
-    // ---- merge 1x1 conv 64 -> 64
-#pragma unroll
-    for (int og = 0; og < 2; ++og) {
-      const int o = lane + 32 * og;
-      float acc = sBm[o];
+    // ---- merge 1x1 conv 64 -> 64 (two outputs per lane, two partial sums each: short FMA chains)
+    {
+      const float* w0 = sWm + lane * 65;
+      const float* w1 = sWm + (lane + 32) * 65;
+      float a0 = sBm[lane], a1 = 0.f, b0 = sBm[lane + 32], b1 = 0.f;
 #pragma unroll 8
-      for (int c = 0; c < 64; ++c) acc = fmaf(sWm[o * 65 + c], sCat[c], acc);
-      p.ctx[(size_t)win * 64 + o] = acc;
+      for (int c = 0; c < 64; c += 2) {
+        const float c0 = sCat[c], c1 = sCat[c + 1];
+        a0 = fmaf(w0[c], c0, a0); a1 = fmaf(w0[c + 1], c1, a1);
+        b0 = fmaf(w1[c], c0, b0); b1 = fmaf(w1[c + 1], c1, b1);
+      }
+      p.ctx[(size_t)win * 64 + lane] = a0 + a1;
+      p.ctx[(size_t)win * 64 + lane + 32] = b0 + b1;
     }
     __syncwarp();
   }
@@ -262,7 +269,7 @@ static int launch_ngram_ctx_fwd(const NgramParams& p, cudaStream_t st) {
   }
   const int nwin = p.B * p.wh * p.ww;
   int grid = (nwin + 7) / 8;
-  if (grid > 2 * sm_count()) grid = 2 * sm_count();
+  if (grid > 3 * sm_count()) grid = 3 * sm_count();
   ngram_ctx_fwd_kernel<NH, PRE><<<grid, kThreads, smem, st>>>(p);
   B200MAR_CHECK(cudaGetLastError());
   return 0;
