@@ -13,6 +13,6 @@ z = torch.randn(B, ph * pw, 64, device="cuda")
 c = torch.randn(B, (ph // 8) * (pw // 8), 64, device="cuda") * 0.5
 for shift in (0, 4, 0, 4):
     a = ops.attn_tc_fwd(z, c, *P[10:18], ph, pw, 6, shift)
-    o = ops.mlp_tc_fwd(a, z, *P[18:24], False, True)
+    o = ops.mlp_tma_fwd_(a, z, *P[18:24], False)
 torch.cuda.synchronize()
 print("ok", ops.tc_error())

@@ -55,6 +55,9 @@ __device__ unsigned long long g_attn_prof[32];
 
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr int kWorkers = 3;
+constexpr int kBiasCopy = 232;                 // floats per shifted bias-table copy: == 8 mod 32, so the 8
+                                               // lanes of a quarter-warp (4 copies x 2 positions) hit 8
+                                               // distinct 16-byte bank groups with their LDS.128
 constexpr int kVChunk = 528;                   // bytes between successive 4-key chunks of V^T (fp32):
                                                // 32 rows x 16 B + 16 (== 4 words mod 32 banks)
 
@@ -67,9 +70,9 @@ struct AttnTcSmem {                            // BYTE offsets
   static constexpr int oLnW = oBp + 256;
   static constexpr int oLnB = oLnW + 256;
   static constexpr int oScale = oLnB + 256;     // [0,6): logit scales, [6]: inverse of the qkv weight scale, [7]: scratch
-  static constexpr int oBias = ((oScale + 32 + 15) / 16) * 16;   // fp32 [6 heads][4 copies][228]: copy s holds
+  static constexpr int oBias = ((oScale + 32 + 15) / 16) * 16;   // fp32 [6 heads][4 copies][kBiasCopy]: copy s holds
                                                // T'[j + s], T' = (bias - max bias - scale) * log2(e)
-  static constexpr int oBar = oBias + 6 * 4 * 228 * 4;  // 3 workers x 8 mbarrier slots (5 used) + tmem slot
+  static constexpr int oBar = oBias + 6 * 4 * kBiasCopy * 4;  // 3 workers x 8 mbarrier slots (5 used) + tmem slot
   static constexpr int oWork = ((oBar + 256 + 1023) / 1024) * 1024;   // 1 KB aligned: TMA 128 B swizzle
   // per worker; [X | Q | K | V] is also the 32 KB fp32 staging tile of the LayerNorm output
   static constexpr int wX = 0;                 // fp16 [128][64] (R = 128): X, later O
@@ -169,11 +172,16 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
   // relative-position bias, shifted by an upper bound of the head's logits so that the softmax
   // needs no row maximum: logit <= scale_h * 1 + max_e bias[e,h]  ->  exponent argument <= ~0.
   // Four copies, copy s starting at table entry s, make every 4-key group one aligned LDS.128.
-  for (int i = tid; i < NH * 4 * 228; i += 128 * kWorkers) {
-    const int h = i / (4 * 228), r = i - h * (4 * 228), sft = r / 228, j = r - sft * 228;
+  __shared__ float sBound[8];
+  if (tid < NH) {
     float mb = -3.0e38f;
-    for (int e = 0; e < 225; ++e) mb = fmaxf(mb, p.bias_table[e * NH + h]);
-    const float bound = expf(fminf(p.logit_scale[h], kLogitMax)) + mb;
+    for (int e = 0; e < 225; ++e) mb = fmaxf(mb, p.bias_table[e * NH + tid]);
+    sBound[tid] = expf(fminf(p.logit_scale[tid], kLogitMax)) + mb;
+  }
+  __syncthreads();
+  for (int i = tid; i < NH * 4 * kBiasCopy; i += 128 * kWorkers) {
+    const int h = i / (4 * kBiasCopy), r = i - h * (4 * kBiasCopy), sft = r / kBiasCopy, j = r - sft * kBiasCopy;
+    const float bound = sBound[h];
     const int e = j + sft;
     sBias[i] = e < 225 ? (p.bias_table[e * NH + h] - bound) * kLog2e : 0.f;
   }
@@ -204,7 +212,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
   // s = lo mod 4 = (bias_base + ci + 1) mod 4 holds them 16-byte aligned at offset lo - s.
   int bias_off[4];
 #pragma unroll
-  for (int m = 0; m < 4; ++m) bias_off[m] = bias_base + 227 * ((bias_base + m + 1) & 3);
+  for (int m = 0; m < 4; ++m) bias_off[m] = bias_base + (kBiasCopy - 1) * ((bias_base + m + 1) & 3);
 
   // operand descriptors are built once; one K = 16 step advances the start-address field (>>4)
   // by two 8-element k-chunks
@@ -441,7 +449,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
       {
         float s[64];
         tc::tmem_ld64(tbase + lane_addr + kTS, s);
-        const float* bh = sBias + h * (4 * 228);
+        const float* bh = sBias + h * (4 * kBiasCopy);
 #pragma unroll
         for (int ci = 0; ci < 8; ++ci) {
           const float* bp = bh + bias_off[ci & 3];
@@ -489,7 +497,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
         tc::tc_fence_after();
         float s[64];
         tc::tmem_ld64(tbase + lane_addr + kTS, s);
-        const float* bias = sBias + h * (4 * 228) + bias_base;     // copy 0 = the unshifted-index table
+        const float* bias = sBias + h * (4 * kBiasCopy) + bias_base;     // copy 0 = the unshifted-index table
 #pragma unroll 8
         for (int c = 0; c < 64; ++c) {
           s[c] += bias[-((c >> 3) * 15 + (c & 7))];
@@ -556,13 +564,14 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
     {
       float y[64];
       tc::tmem_ld64(tbase + lane_addr + kTS, y);
-      float mean = 0.f;
+      float mean4[4] = {0.f, 0.f, 0.f, 0.f};      // four partial sums: short dependency chains
 #pragma unroll
-      for (int i = 0; i < 64; ++i) { y[i] += sBp[i]; mean += y[i]; }
-      mean *= (1.0f / 64.f);
-      float var = 0.f;
+      for (int i = 0; i < 64; ++i) { y[i] += sBp[i]; mean4[i & 3] += y[i]; }
+      const float mean = ((mean4[0] + mean4[1]) + (mean4[2] + mean4[3])) * (1.0f / 64.f);
+      float var4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-      for (int i = 0; i < 64; ++i) { y[i] -= mean; var = fmaf(y[i], y[i], var); }
+      for (int i = 0; i < 64; ++i) { y[i] -= mean; var4[i & 3] = fmaf(y[i], y[i], var4[i & 3]); }
+      const float var = (var4[0] + var4[1]) + (var4[2] + var4[3]);
       const float rstd = 1.0f / sqrtf(var * (1.0f / 64.f) + kLnEps);
 #pragma unroll
       for (int i = 0; i < 64; ++i) y[i] = y[i] * rstd * sLnW[i] + sLnB[i];

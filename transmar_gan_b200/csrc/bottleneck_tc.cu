@@ -192,13 +192,14 @@ bottleneck_tc_kernel(const __grid_constant__ CUtensorMap mapCat, const __grid_co
     {
       float y[64];
       tc::tmem_ld64(tbase + lane_addr, y);
-      float mean = 0.f;
+      float mean4[4] = {0.f, 0.f, 0.f, 0.f};      // four partial sums: short dependency chains
 #pragma unroll
-      for (int i = 0; i < 64; ++i) { y[i] = fmaf(y[i], ainv, sPb[i]); mean += y[i]; }
-      mean *= (1.0f / 64.f);
-      float var = 0.f;
+      for (int i = 0; i < 64; ++i) { y[i] = fmaf(y[i], ainv, sPb[i]); mean4[i & 3] += y[i]; }
+      const float mean = ((mean4[0] + mean4[1]) + (mean4[2] + mean4[3])) * (1.0f / 64.f);
+      float var4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-      for (int i = 0; i < 64; ++i) { y[i] -= mean; var = fmaf(y[i], y[i], var); }
+      for (int i = 0; i < 64; ++i) { y[i] -= mean; var4[i & 3] = fmaf(y[i], y[i], var4[i & 3]); }
+      const float var = (var4[0] + var4[1]) + (var4[2] + var4[3]);
       const float rstd = 1.0f / sqrtf(var * (1.0f / 64.f) + kLnEps);
 #pragma unroll
       for (int i = 0; i < 16; ++i) {

@@ -345,13 +345,14 @@ final_dot9_tma_kernel(const __grid_constant__ CUtensorMap mapDec, const __grid_c
     }
     tc::worker_sync(1 + wk);                           // rows are in registers: refill the buffers
     if (leader && tile + stride < ntile) issue(tile + stride);
-    float mean = 0.f;
+    float mean4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-    for (int i = 0; i < 64; ++i) mean += y[i];
-    mean *= (1.0f / 64.f);
-    float var = 0.f;
+    for (int i = 0; i < 64; ++i) mean4[i & 3] += y[i];
+    const float mean = ((mean4[0] + mean4[1]) + (mean4[2] + mean4[3])) * (1.0f / 64.f);
+    float var4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-    for (int i = 0; i < 64; ++i) { y[i] -= mean; var = fmaf(y[i], y[i], var); }
+    for (int i = 0; i < 64; ++i) { y[i] -= mean; var4[i & 3] = fmaf(y[i], y[i], var4[i & 3]); }
+    const float var = (var4[0] + var4[1]) + (var4[2] + var4[3]);
     const float rstd = 1.0f / sqrtf(var * (1.0f / 64.f) + kLnEps);
     float d[9];
 #pragma unroll

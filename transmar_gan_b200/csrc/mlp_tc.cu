@@ -277,15 +277,15 @@ __global__ void __launch_bounds__(128 * kMlpWorkers, 1) mlp_tc_fwd_kernel(MlpPar
     {
       float y[64];
       tc::tmem_ld64(tbase + lane_addr + 64, y);
-      float mean = 0.f;
-#pragma unroll
+      float mean4[4] = {0.f, 0.f, 0.f, 0.f};          // four partial sums: short dependency chains
       const float yinv = w2inv * hinv;
 #pragma unroll
-      for (int i = 0; i < 64; ++i) { y[i] = fmaf(y[i], yinv, sB2[i]); mean += y[i]; }
-      mean *= (1.0f / 64.f);
-      float var = 0.f;
+      for (int i = 0; i < 64; ++i) { y[i] = fmaf(y[i], yinv, sB2[i]); mean4[i & 3] += y[i]; }
+      const float mean = ((mean4[0] + mean4[1]) + (mean4[2] + mean4[3])) * (1.0f / 64.f);
+      float var4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-      for (int i = 0; i < 64; ++i) { y[i] -= mean; var = fmaf(y[i], y[i], var); }
+      for (int i = 0; i < 64; ++i) { y[i] -= mean; var4[i & 3] = fmaf(y[i], y[i], var4[i & 3]); }
+      const float var = (var4[0] + var4[1]) + (var4[2] + var4[3]);
       const float rstd = 1.0f / sqrtf(var * (1.0f / 64.f) + kLnEps);
 #pragma unroll
       for (int kc = 0; kc < 16; ++kc)
@@ -527,15 +527,15 @@ mlp_tma_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
     {
       float y[64];
       tc::tmem_ld64(tbase + lane_addr + 64, y);
-      float mean = 0.f;
-#pragma unroll
+      float mean4[4] = {0.f, 0.f, 0.f, 0.f};          // four partial sums: short dependency chains
       const float yinv = w2inv * hinv;
 #pragma unroll
-      for (int i = 0; i < 64; ++i) { y[i] = fmaf(y[i], yinv, sB2[i]); mean += y[i]; }
-      mean *= (1.0f / 64.f);
-      float var = 0.f;
+      for (int i = 0; i < 64; ++i) { y[i] = fmaf(y[i], yinv, sB2[i]); mean4[i & 3] += y[i]; }
+      const float mean = ((mean4[0] + mean4[1]) + (mean4[2] + mean4[3])) * (1.0f / 64.f);
+      float var4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-      for (int i = 0; i < 64; ++i) { y[i] -= mean; var = fmaf(y[i], y[i], var); }
+      for (int i = 0; i < 64; ++i) { y[i] -= mean; var4[i & 3] = fmaf(y[i], y[i], var4[i & 3]); }
+      const float var = (var4[0] + var4[1]) + (var4[2] + var4[3]);
       const float rstd = 1.0f / sqrtf(var * (1.0f / 64.f) + kLnEps);
 #pragma unroll
       for (int i = 0; i < 16; ++i) {
