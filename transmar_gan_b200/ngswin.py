@@ -163,7 +163,7 @@ class _Stage(nn.Module):
                  0 if i % 2 == 0 else window_size // 2, head_dim, mlp_ratio, qkv_bias)
             for i in range(depth)])
 
-    def _run_blocks(self, x, num_patches, need_sum_last):
+    def _run_blocks(self, x, num_patches, need_sum_last, owned=False):
         """Block i consumes z_i = out_{i-1} + z_{i-1}; each block's MLP kernel emits that sum
         for its successor, so intermediate `out` tensors are never written."""
         z, n = x, len(self.blocks)
@@ -175,7 +175,7 @@ class _Stage(nn.Module):
                 # the block adds its output into z (TMA reduce-add), so z must be private to this
                 # loop: the stage input is copied once, later blocks own the previous block's sum
                 want_zsum = (not last) or need_sum_last
-                if i == 0 and want_zsum:
+                if i == 0 and want_zsum and not owned:
                     z = z.clone()
                 out, zsum = ops.nstb_infer_(z, *num_patches, blk.num_heads, blk.shift_size, last,
                                             want_zsum, blk.kernel_params())
@@ -197,7 +197,10 @@ class EncoderLayer(_Stage):
     def forward(self, x, num_patches, projected=False):
         if not projected:                                       # fused path projects beforehand
             x = self.across_cascade_proj(x).contiguous()
-        out, zsum = self._run_blocks(x, num_patches, need_sum_last=self.downsample is not None)
+        # a stage input this layer projected itself (or that the fused path produced for it alone) may be
+        # updated in place; encoder_layer1's input is the shallow feature map, which is reused later
+        out, zsum = self._run_blocks(x, num_patches, need_sum_last=self.downsample is not None,
+                                     owned=projected or not isinstance(self.across_cascade_proj, nn.Identity))
         if self.downsample is None:
             return out, out, num_patches
         down, np2 = self.downsample(zsum, num_patches)
@@ -211,8 +214,8 @@ class DecoderLayer(_Stage):
         self._build_blocks(dim, training_num_patches, ngram, depth, num_heads, window_size,
                            head_dim, mlp_ratio, qkv_bias)
 
-    def forward(self, x, num_patches):
-        out, _ = self._run_blocks(x.contiguous(), num_patches, need_sum_last=False)
+    def forward(self, x, num_patches, owned=False):
+        out, _ = self._run_blocks(x.contiguous(), num_patches, need_sum_last=False, owned=owned)
         return out
 
 
@@ -375,7 +378,7 @@ class NGswin(nn.Module):
         dec_in = ops.bottleneck_fwd(c0, p0, p00, e1_, e2_, e3_, bn.depthwise.weight, bn.depthwise.bias,
                                     bn.pointwise.weight, bn.pointwise.bias, bn.norm.weight,
                                     bn.norm.bias, H, W)
-        dec = self.decoder_layer1(dec_in, (H, W))
+        dec = self.decoder_layer1(dec_in, (H, W), owned=True)      # dec_in is not used again
         return ops.final_recon_fwd(dec, c0, self.norm.weight, self.norm.bias,
                                    tt.before_shuffle.weight, tt.before_shuffle.bias,
                                    tt.to_origin.weight, tt.to_origin.bias, H, W, H0, W0)
