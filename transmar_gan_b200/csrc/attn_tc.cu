@@ -410,8 +410,10 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
         uint4* q0 = reinterpret_cast<uint4*>(sQ + row * 16);                 // k-chunk stride 2048 B
         q0[(2 * wsel) * 128] = make_uint4(qp[0], qp[1], qp[2], qp[3]);
         q0[(2 * wsel + 1) * 128] = make_uint4(qp[4], qp[5], qp[6], qp[7]);
-        q0[(2 - 2 * wsel) * 128] = z4;
-        q0[(3 - 2 * wsel) * 128] = z4;
+        if (h == 0) {                                  // the other window's half stays zero for all heads
+          q0[(2 - 2 * wsel) * 128] = z4;
+          q0[(3 - 2 * wsel) * 128] = z4;
+        }
         uint4* k0 = reinterpret_cast<uint4*>(sK + lrow * 16);                // k-chunk stride 1024 B
         k0[(2 * wsel) * 64] = make_uint4(kp[0], kp[1], kp[2], kp[3]);
         k0[(2 * wsel + 1) * 64] = make_uint4(kp[4], kp[5], kp[6], kp[7]);

@@ -134,20 +134,32 @@ __global__ void __launch_bounds__(kThreads) ngram_ctx_fwd_kernel(NgramParams p) 
 
   const int wh = p.wh, ww = p.ww;
   const int nwin = p.B * wh * ww;
+  // PRE: the 8 neighbourhood rows of the NEXT window are fetched into registers while this window
+  // computes (24 loads in flight per lane hide the L2 latency of the gather)
+  float nxt[24];
+  auto fetch = [&](int win_) {
+    const int w0 = win_ % ww, h0 = (win_ / ww) % wh, b = win_ / (ww * wh);
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+      int r, c;
+      ngram_neighbour(t, h0, w0, wh, ww, r, c);
+      const float* src = p.u + ((size_t)(b * wh + r) * ww + c) * 96 + lane;
+      nxt[3 * t] = __ldg(src); nxt[3 * t + 1] = __ldg(src + 32); nxt[3 * t + 2] = __ldg(src + 64);
+    }
+  };
+  if (PRE && (int)(blockIdx.x * 8 + warp) < nwin) fetch(blockIdx.x * 8 + warp);
   for (int win = blockIdx.x * 8 + warp; win < nwin; win += gridDim.x * 8) {
     const int w0 = win % ww, h0 = (win / ww) % wh, b = win / (ww * wh);
     if (PRE) {
       // ---- qkv rows of the 8 neighbourhood tokens (4 forward, 4 backward), precomputed per window
 #pragma unroll
       for (int t = 0; t < 8; ++t) {
-        int r, c;
-        ngram_neighbour(t, h0, w0, wh, ww, r, c);
-        const float* src = p.u + ((size_t)(b * wh + r) * ww + c) * 96 + lane;
-        sQkv[t * 96 + lane] = src[0];
-        sQkv[t * 96 + lane + 32] = src[32];
-        sQkv[t * 96 + lane + 64] = src[64];
+        sQkv[t * 96 + lane] = nxt[3 * t];
+        sQkv[t * 96 + lane + 32] = nxt[3 * t + 1];
+        sQkv[t * 96 + lane + 64] = nxt[3 * t + 2];
       }
       __syncwarp();
+      if (win + (int)gridDim.x * 8 < nwin) fetch(win + gridDim.x * 8);
     } else {
       // ---- the 8 neighbourhood tokens (4 forward, 4 backward), lane = channel
   #pragma unroll
