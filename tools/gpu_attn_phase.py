@@ -21,7 +21,7 @@ names = ["loop top", "ctx + wait z tile", "sync+qkv0 issue", "wait qkv", "qkv ld
          "fence+sync", "S issue+wait", "softmax+P st", "sync(or)", "PV issue", "Otile+proj+wait", "LN epilogue", "wait z reload",
          "a in place+store+next load", "PV issue (last)", "row convert+mask"]
 tot = sum(buf)
-ntile = (B * (ph // 8) * (pw // 8) // 2 + 148 * 3 - 1) // (148 * 3)
+ntile = (B * (ph // 8) * (pw // 8) // 2 + 148 * 4 - 1) // (148 * 4)   # 4 workers per CTA (NH = 6)
 print("tiles per worker ~", ntile, "total cycles", tot, "per tile", tot / ntile)
 for i, n in enumerate(names):
     print(f"{i:2d} {n:22s} {buf[i] / ntile:9.0f} cyc/tile  {100 * buf[i] / tot:5.1f}%")

@@ -8,23 +8,26 @@
 //     RELATIVE precision matter at any scale: P V and the output projection.
 // The residual stream in HBM, q/k normalisation, softmax, LayerNorm and the residual add are fp32.
 //
-// One persistent CTA per SM = THREE independent 128-thread workers sharing the resident weights
-// (qkv re-packed per head as [q16|k16|v16] rows, 36 KB; proj 8 KB; bias table; LN affine).  A worker
-// streams tiles of TWO (shifted) windows = 128 tokens; thread t owns token row t = TMEM lane t.
-// Per tile:
-//   gather X = z + ctx (cyclic shift folded into the address math) -> fp16 smem A operand
+// One persistent CTA per SM = FOUR (6 heads) or THREE (4 heads) independent 128-thread workers sharing
+// the resident weights (qkv re-packed per head as [q|k|v] rows, 24 KB; proj 16 KB; bias table copies;
+// LN affine).  A worker streams tiles of TWO (shifted) windows = 128 tokens; thread t owns token row
+// t = TMEM lane t.  Per tile:
+//   z tile by TMA (4-D window boxes, 128 B swizzle; wrapped windows by direct row access);
+//   X = z + ctx, row-scaled -> fp16 smem A operand
 //   for each head h (QKV of head h+1 is issued in the shadow of S_h):
-//     [q_h|k_h|v_h] = X * Wqkv[h]^T      4 MMAs 128x48x16 -> TMEM (double-buffered over heads)
+//     [q_h|k_h|v_h] = X * Wqkv[h]^T      4 MMAs 128xHSx16 -> TMEM (double-buffered over heads)
 //     row-wise fp32: +bias, F.normalize(q), F.normalize(k), q *= exp(min(logit_scale,ln100))*log2e
 //       -> Q' = [q | 0] / [0 | q] (window 0 / window 1 rows), K' = [k(w0) | k(w1)], so that ONE
 //          128x64x32 MMA gives every row the logits against its own window's 64 keys;
 //          V^T (rows = (window, d), keys contiguous)
 //     S = Q' K'^T                         2 MMAs 128x64x16
-//     row-wise fp32: + relative-position bias (smem gather) + analytic shift mask, max, ex2, sum;
-//       unnormalised P written back to TMEM over S (tcgen05.st)
+//     row-wise fp32: + relative-position bias (pre-shifted by the head's logit bound: no row max)
+//       + analytic shift mask, ex2, sum; unnormalised P written back to TMEM over S (tcgen05.st)
 //     O_h = P [V_h(w0) | V_h(w1)]         8 MMAs 128x32x8 (tf32), A operand = P from TMEM, written
 //                                         over the dead [q|k|v]_h accumulator columns
-//   Y = O Wp^T (8 MMAs 128x64x8, tf32), +bias, LayerNorm (a whole row per thread), + z, scatter.
+//   O row -> TMEM (over the dead qkv buffers) = A operand of Y = O Wp^T (8 MMAs 128x64x8, tf32);
+//   meanwhile the z tile is fetched again (L2 hit); +bias, LayerNorm (a whole row per thread), + z in
+//   place, TMA store.
 // While one worker runs a CUDA-core epilogue the others own the tensor pipe / load path.
 //
 // Reference semantics: components/window_utils.py:127-147, components/attention.py:70-101,
@@ -54,15 +57,25 @@ __device__ unsigned long long g_attn_prof[32];
 #endif
 
 constexpr float kLog2e = 1.4426950408889634f;
-constexpr int kWorkers = 3;
+// workers (tiles in flight) per CTA.  NH = 6: heads are packed as [q10|k10|v10|0 0] = 32 accumulator
+// columns, so a worker needs 2 x 32 (qkv, double-buffered; O_h over the dead buffer) + 64 (S/P/Y) = 128
+// TMEM columns and FOUR fit; NH = 4 (head dim 16): 2 x 48 + 64 = 160 columns, three workers.
+template <int NH> struct Cfg {
+  static constexpr int kWorkers = NH == 6 ? 4 : 3;
+  static constexpr int HS = NH == 6 ? 32 : 48;     // packed rows / accumulator columns per head
+  static constexpr int PS = NH == 6 ? 10 : 16;     // stride of q, k, v inside a head's block
+  static constexpr uint32_t kTStride = 2 * HS + 64;
+  static constexpr uint32_t kTS = 2 * HS;          // S; P (fp32) overwrites it; Y at the end
+};
 constexpr int kBiasCopy = 232;                 // floats per shifted bias-table copy: == 8 mod 32, so the 8
                                                // lanes of a quarter-warp (4 copies x 2 positions) hit 8
                                                // distinct 16-byte bank groups with their LDS.128
 constexpr int kVChunk = 528;                   // bytes between successive 4-key chunks of V^T (fp32):
                                                // 32 rows x 16 B + 16 (== 4 words mod 32 banks)
 
-struct AttnTcSmem {                            // BYTE offsets
-  static constexpr int kWRows = 288;           // 6 heads x [q16 | k16 | v16] (4 heads: 192 used)
+template <int W>
+struct AttnTcSmem {                            // BYTE offsets (W workers)
+  static constexpr int kWRows = 192;           // 6 heads x [q10|k10|v10|0 0] or 4 heads x [q16|k16|v16]
   static constexpr int oWqkv = 0;              // fp16 [288 rows][64 k], 8-element k-chunks, R = 288
   static constexpr int oWp = oWqkv + kWRows * 64 * 2;   // fp32 (tf32) [64 rows][64 k], 4-element k-chunks, R = 64
   static constexpr int oBqkv = oWp + 64 * 64 * 4;       // fp32 [288], packed order
@@ -73,7 +86,7 @@ struct AttnTcSmem {                            // BYTE offsets
   static constexpr int oBias = ((oScale + 32 + 15) / 16) * 16;   // fp32 [6 heads][4 copies][kBiasCopy]: copy s holds
                                                // T'[j + s], T' = (bias - max bias - scale) * log2(e)
   static constexpr int oBar = oBias + 6 * 4 * kBiasCopy * 4;  // 3 workers x 8 mbarrier slots (5 used) + tmem slot
-  static constexpr int oWork = ((oBar + 256 + 1023) / 1024) * 1024;   // 1 KB aligned: TMA 128 B swizzle
+  static constexpr int oWork = ((oBar + 320 + 1023) / 1024) * 1024;   // 1 KB aligned: TMA 128 B swizzle
   // per worker; [X | Q | K | V] is also the 32 KB fp32 staging tile of the LayerNorm output
   static constexpr int wX = 0;                 // fp16 [128][64] (R = 128): X, later O
   static constexpr int wQ = wX + 128 * 64 * 2; // fp16 [128][32] (R = 128)
@@ -81,26 +94,26 @@ struct AttnTcSmem {                            // BYTE offsets
   static constexpr int wV = wK + 64 * 32 * 2;  // fp32 [32 rows = (window, d)][64 keys], chunk stride kVChunk
   static constexpr int wTok = wV + 16 * kVChunk;
   static constexpr int kWorkBytes = ((wTok + 4 * 128 * 4 + 1023) / 1024) * 1024;   // tok, cwin, region, row scale
-  static constexpr int kBytes = oWork + kWorkers * kWorkBytes;
+  static constexpr int kBytes = oWork + W * kWorkBytes;
   static_assert(wTok >= 128 * 64 * 4, "fp32 staging tile must fit in [X|Q|K|V]");
   static_assert(oBar % 8 == 0, "mbarrier alignment");
   static_assert(kBytes <= 232448, "attn_tc shared memory exceeds 227 KB");
 };
 
-// TMEM columns of one worker (3 x 160 of the CTA's 512)
-constexpr uint32_t kTStride = 160;
-constexpr uint32_t kTQ = 0;      // 2 x 48: [q_h | k_h | v_h] accumulators, double-buffered over heads;
-                                 // O_h (32 columns) is written over buffer h&1 once it has been read
-constexpr uint32_t kTS = 96;     // 64: S; P (fp32) overwrites it; Y at the end
+// TMEM columns of one worker: [0, 2 HS): [q_h | k_h | v_h] accumulators, double-buffered over heads
+// (O_h, 32 columns, is written over buffer h&1 once it has been read); [2 HS, 2 HS + 64): S / P / Y
+constexpr uint32_t kTQ = 0;
 
 // RESID = true : a = z + LN1(attn)            (the op's standalone contract)
 // RESID = false: a = LN1(attn) only; the consumer (mlp_tc with a_is_delta) adds z, which it reads
 //                anyway, so this kernel never re-reads z for the residual.
 template <int NH, bool RESID>
-__global__ void __launch_bounds__(128 * kWorkers, 1)
+__global__ void __launch_bounds__(128 * Cfg<NH>::kWorkers, 1)
 attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_constant__ CUtensorMap mapA,
                    AttnParams p) {
-  using L = AttnTcSmem;
+  constexpr int kWorkers = Cfg<NH>::kWorkers, HS = Cfg<NH>::HS, PS = Cfg<NH>::PS;
+  constexpr uint32_t kTStride = Cfg<NH>::kTStride, kTS = Cfg<NH>::kTS;
+  using L = AttnTcSmem<kWorkers>;
   constexpr int HD = kDim / NH, A = HD * NH;
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   __half* sWqkv = reinterpret_cast<__half*>(smem_raw + L::oWqkv);
@@ -123,7 +136,6 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
   unsigned char* sQ = sW + L::wQ;
   unsigned char* sK = sW + L::wK;
   unsigned char* sV = sW + L::wV;
-  float* sStage = reinterpret_cast<float*>(sW);            // fp32 [128][64] chunk-major, end of tile
   int* sReg = reinterpret_cast<int*>(sW + L::wTok) + 256;
   uint64_t* barQ = bars + wk * 8;       // [2]
   uint64_t* barS = barQ + 2;
@@ -145,10 +157,10 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
   we = we < 1u ? 127u : (we > 253u ? 253u : we);
   const float wsc = __uint_as_float((254u - we) << 23);   // 2^(127-we)
   for (int idx = tid; idx < L::kWRows * 8; idx += 128 * kWorkers) {
-    const int n = idx % L::kWRows, kc = idx / L::kWRows;      // packed row n = h*48 + part*16 + d
-    const int h = n / 48, part = (n % 48) >> 4, d = n & 15;
+    const int n = idx % L::kWRows, kc = idx / L::kWRows;      // packed row n = h*HS + part*PS + d
+    const int h = n / HS, part = (n % HS) / PS, d = (n % HS) % PS;
     uint4 v = make_uint4(0u, 0u, 0u, 0u);
-    if (h < NH && d < HD) {
+    if (h < NH && part < 3 && d < HD) {
       const float4* src = reinterpret_cast<const float4*>(p.qkv_w + (part * A + h * HD + d) * 64 + kc * 8);
       const float4 a = src[0], b = src[1];
       v = make_uint4(tc::pack_f16(a.x * wsc, a.y * wsc), tc::pack_f16(a.z * wsc, a.w * wsc),
@@ -163,8 +175,8 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
     *reinterpret_cast<float4*>(sWp + kc * 256 + n * 4) = tc::round_tf32(v);   // the MMA would truncate
   }
   for (int n = tid; n < L::kWRows; n += 128 * kWorkers) {      // bias in the same packed order
-    const int h = n / 48, part = (n % 48) >> 4, d = n & 15;
-    sBqkv[n] = (h < NH && d < HD) ? p.qkv_b[part * A + h * HD + d] : 0.f;
+    const int h = n / HS, part = (n % HS) / PS, d = (n % HS) % PS;
+    sBqkv[n] = (h < NH && part < 3 && d < HD) ? p.qkv_b[part * A + h * HD + d] : 0.f;
   }
   if (tid < 64) { sBp[tid] = p.proj_b[tid]; sLnW[tid] = p.ln_w[tid]; sLnB[tid] = p.ln_b[tid]; }
   if (tid < NH) sScale[tid] = expf(fminf(p.logit_scale[tid], kLogitMax)) * kLog2e;
@@ -198,7 +210,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
 
   const uint32_t tbase = *tmem_slot + wk * kTStride;
   const uint32_t lane_addr = (uint32_t)(wq * 32) << 16;
-  constexpr uint32_t kI48 = tc::idesc_f16(128, 48), kI64 = tc::idesc_f16(128, 64),
+  constexpr uint32_t kIqkv = tc::idesc_f16(128, HS), kI64 = tc::idesc_f16(128, 64),
                      kT32 = tc::idesc_tf32(128, 32), kT64 = tc::idesc_tf32(128, 64);
   uint32_t phQ = 0, phS = 0, phO = 0, phZ = 0;
 
@@ -224,10 +236,10 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
                  dWp = tc::smem_desc(tc::smem_u32(sWp), 1024, 128);
   // [q_h | k_h | v_h] = X * Wqkv[rows of head h]^T -> TMEM buffer `buf` (issued by one thread)
   auto issue_qkv = [&](int h, int buf) {
-    const uint64_t db = dWqkv + (uint64_t)(h * 48);
+    const uint64_t db = dWqkv + (uint64_t)(h * HS);
 #pragma unroll
     for (int ks = 0; ks < 4; ++ks)
-      tc::mma_f16(tbase + kTQ + buf * 48, dX + ks * 256, db + ks * (2 * L::kWRows), kI48, ks > 0);
+      tc::mma_f16(tbase + kTQ + buf * HS, dX + ks * 256, db + ks * (2 * L::kWRows), kIqkv, ks > 0);
   };
 
   // A window whose 8x8 token block is contiguous in the grid (all windows when shift = 0; all but the
@@ -370,18 +382,19 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
       phQ ^= 1u << buf;
       tc::tc_fence_after();
       PROF(3);                                         // wait [q|k|v]
-      float qkv[48];
-      tc::tmem_ld48(tbase + lane_addr + kTQ + buf * 48, qkv);
+      float qkv[HS];
+      if constexpr (HS == 32) tc::tmem_ld32(tbase + lane_addr + kTQ + buf * HS, qkv);
+      else tc::tmem_ld48(tbase + lane_addr + kTQ + buf * HS, qkv);
       float qs = 0.f, ks = 0.f;
       {
-        const float* b = sBqkv + h * 48;               // packed [q16 | k16 | v16]; pad rows are exact zeros
+        const float* b = sBqkv + h * HS;               // packed [q | k | v] with stride PS; pad rows are exact zeros
 #pragma unroll
         for (int d = 0; d < HD; ++d) {
           qkv[d] = fmaf(qkv[d], xinv, b[d]);           // undo the row's power-of-two input scale
-          qkv[16 + d] = fmaf(qkv[16 + d], xinv, b[16 + d]);
-          qkv[32 + d] = fmaf(qkv[32 + d], xinv, b[32 + d]);
+          qkv[PS + d] = fmaf(qkv[PS + d], xinv, b[PS + d]);
+          qkv[2 * PS + d] = fmaf(qkv[2 * PS + d], xinv, b[2 * PS + d]);
           qs = fmaf(qkv[d], qkv[d], qs);
-          ks = fmaf(qkv[16 + d], qkv[16 + d], ks);
+          ks = fmaf(qkv[PS + d], qkv[PS + d], ks);
         }
       }
       const float qmul = sScale[h] * rsqrtf(fmaxf(qs, kNormEps * kNormEps));   // v / max(|v|, eps)
@@ -390,7 +403,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         qp[j] = 2 * j < HD ? tc::pack_f16(qkv[2 * j] * qmul, qkv[2 * j + 1] * qmul) : 0u;
-        kp[j] = 2 * j < HD ? tc::pack_f16(qkv[16 + 2 * j] * kmul, qkv[16 + 2 * j + 1] * kmul) : 0u;
+        kp[j] = 2 * j < HD ? tc::pack_f16(qkv[PS + 2 * j] * kmul, qkv[PS + 2 * j + 1] * kmul) : 0u;
       }
       // ---- previous head's O: its PV MMAs read P (TMEM) and V^T (smem) and wrote O over the
       //      accumulator buffer that [q|k|v]_{h+1} will reuse: read it before anything is reused
@@ -399,7 +412,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
         tc::mbar_wait(barO, phO, &g_tc_error); phO ^= 1;
         tc::tc_fence_after();
         float ov[16];
-        tc::tmem_ld16(tbase + lane_addr + kTQ + (buf ^ 1) * 48 + wsel * 16, ov);
+        tc::tmem_ld16(tbase + lane_addr + kTQ + (buf ^ 1) * HS + wsel * 16, ov);
 #pragma unroll
         for (int d = 0; d < HD; ++d) o[(h - 1) * HD + d] = ov[d] * inv_prev;
       }
@@ -419,7 +432,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
         k0[(2 * wsel + 1) * 64] = make_uint4(kp[4], kp[5], kp[6], kp[7]);
         float* vt = reinterpret_cast<float*>(sV + (lrow >> 2) * kVChunk + wsel * 256) + (lrow & 3);
 #pragma unroll
-        for (int d = 0; d < HD; ++d) vt[d * 4] = tc::round_tf32(qkv[32 + d]);
+        for (int d = 0; d < HD; ++d) vt[d * 4] = tc::round_tf32(qkv[2 * PS + d]);
       }
       PROF(6);                                         // operand stores
       tc::fence_async_smem();
@@ -522,7 +535,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
         if (tc::elect_one()) {
 #pragma unroll
           for (int ks = 0; ks < 8; ++ks)
-            tc::mma_tf32_ts(tbase + kTQ + buf * 48, tbase + kTS + ks * 8, dV + ks * (2 * kVChunk / 16), kT32, ks > 0);
+            tc::mma_tf32_ts(tbase + kTQ + buf * HS, tbase + kTS + ks * 8, dV + ks * (2 * kVChunk / 16), kT32, ks > 0);
           tc::mma_commit(barO);
         }
         __syncwarp();
@@ -535,22 +548,29 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
       tc::mbar_wait(barO, phO, &g_tc_error); phO ^= 1;
       tc::tc_fence_after();
       float ov[16];
-      tc::tmem_ld16(tbase + lane_addr + kTQ + ((NH - 1) & 1) * 48 + wsel * 16, ov);
+      tc::tmem_ld16(tbase + lane_addr + kTQ + ((NH - 1) & 1) * HS + wsel * 16, ov);
 #pragma unroll
       for (int d = 0; d < HD; ++d) o[(NH - 1) * HD + d] = ov[d] * inv_prev;
     }
+    // ---- every MMA that read [X|Q'|K'|V^T] is complete: fetch the z tile again for the residual now
+    //      (an L2 hit), so that it lands behind the projection and the LayerNorm
+    if (RESID && leader) issue_z_loads(tile);
+    // ---- O row (tf32-rounded) -> TMEM over the dead [q|k|v] buffers: the A operand of the projection
+    {
+      float ot[64];
 #pragma unroll
-    for (int kc = 0; kc < 16; ++kc)                    // fp32 O tile over [X|Q|K|V] (all dead by now)
-      *reinterpret_cast<float4*>(sStage + kc * 512 + row * 4) =
-          tc::round_tf32(make_float4(o[kc * 4], o[kc * 4 + 1], o[kc * 4 + 2], o[kc * 4 + 3]));
-    tc::fence_async_smem();
+      for (int i = 0; i < 64; ++i) ot[i] = tc::round_tf32(o[i]);
+      tc::tmem_st64(tbase + lane_addr + kTQ, ot);
+      tc::tmem_wait_st();
+    }
     tc::tc_fence_before();
     tc::worker_sync(1 + wk);
     if (wq == 0) {
       tc::tc_fence_after();
       if (tc::elect_one()) {
 #pragma unroll
-        for (int ks = 0; ks < 8; ++ks) tc::mma_tf32(tbase + kTS, dX + ks * 256, dWp + ks * 128, kT64, ks > 0);
+        for (int ks = 0; ks < 8; ++ks)
+          tc::mma_tf32_ts(tbase + kTS, tbase + kTQ + ks * 8, dWp + ks * 128, kT64, ks > 0);
         tc::mma_commit(barS);
       }
       __syncwarp();
@@ -558,9 +578,6 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
     tc::mbar_wait(barS, phS, &g_tc_error); phS ^= 1;
     tc::tc_fence_after();
     PROF(12);                                          // O tile + proj issue + wait
-    // ---- the O tile is consumed: reload the z tile over it for the residual (an L2 hit; it lands
-    //      while the LayerNorm below runs)
-    if (RESID && leader) issue_z_loads(tile);
     // ---- + proj bias, LayerNorm(norm1) of the row held in registers; a = z + LN(.) in place in the
     //      z tile (TMA windows) or straight to global (wrapped windows)
     {
@@ -641,7 +658,8 @@ namespace b200mar {
 
 template <int NH, bool RESID>
 static int launch_attn_tc_fwd(const AttnParams& p, cudaStream_t st) {
-  const size_t smem = AttnTcSmem::kBytes;
+  constexpr int kWorkers = Cfg<NH>::kWorkers;
+  const size_t smem = AttnTcSmem<kWorkers>::kBytes;
   static bool configured = false;
   if (!configured) {
     B200MAR_CHECK(cudaFuncSetAttribute(attn_tc_fwd_kernel<NH, RESID>,
