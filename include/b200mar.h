@@ -164,6 +164,21 @@ int b200mar_mlp_bwd(const float* a, const float* dout,
                     float* da,
                     float* d_fc1_w, float* d_fc1_b, float* d_fc2_w, float* d_fc2_b,
                     float* d_ln_w, float* d_ln_b, long long n_tok, void* stream);
+/* mlp_bwd on the tcgen05 tensor cores (BF16 operands, fp32 accumulate; timm Mlp + norm2 backward,
+ * components/transformer_blocks.py:119).  `scratch` is a caller-owned device buffer of
+ * n_tok * 768 bytes (the bf16 operands a, g, dh, dy of the weight-gradient MMAs).            */
+int b200mar_mlp_bwd_tc(const float* a, const float* dout,
+                       const float* fc1_w, const float* fc1_b,
+                       const float* fc2_w, const float* fc2_b,
+                       const float* ln_w, const float* ln_b,
+                       float* da,
+                       float* d_fc1_w, float* d_fc1_b, float* d_fc2_w, float* d_fc2_b,
+                       float* d_ln_w, float* d_ln_b, void* scratch, long long n_tok, void* stream);
+/* Weight gradient of one nn.Linear on the tensor cores: dw[cout][cin] += sum_t g16[t][cout] *
+ * in16[t][cin] and (optionally, cin == 64) dbias[cout] += sum_t g16[t][cout]; in16 / g16 are
+ * row-major bf16 device buffers; cin in {64,128}, cout in {64,...,256} a multiple of 32.       */
+int b200mar_wgrad_tc(const void* in16, const void* g16, float* dw, float* dbias, long long n_tok,
+                     int cin, int cout, void* stream);
 
 /* ---- a10: PatchMerging.forward (components/encoder_decoder.py:51-74) -------------------
  * 2x2 gather in channel order (even,even),(even,odd),(odd,even),(odd,odd) -> LN(256) ->

@@ -1,0 +1,67 @@
+"""Scratch GPU check of the tensor-core backward kernels against the fp32 SIMT backward kernels."""
+import sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import transmar_gan_b200 as T
+from oracle import ngswin_oracle as O
+
+ops = T.ops
+torch.manual_seed(0)
+
+
+def timeit(fn, n=10):
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(n):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / n
+
+
+def rel(x, y):
+    return ((x - y).norm() / y.norm().clamp_min(1e-30)).item()
+
+
+# ---- wgrad alone
+for (T_, cin, cout) in ((128, 64, 128), (192, 64, 192), (4096 + 64, 128, 64), (100032, 64, 192)):
+    a = torch.randn(T_, cin, device="cuda").bfloat16()
+    g = torch.randn(T_, cout, device="cuda").bfloat16()
+    dw = torch.zeros(cout, cin, device="cuda")
+    db = torch.zeros(cout, device="cuda") if cin == 64 else None
+    ops.wgrad_tc(a, g, dw, db)
+    ref = g.double().T @ a.double()
+    msg = f"wgrad T={T_} cin={cin} cout={cout}: dw rel {rel(dw.double(), ref):.2e}"
+    if db is not None:
+        msg += f" dbias rel {rel(db.double(), g.double().sum(0)):.2e}"
+    print(msg, "tc_error", ops.tc_error(), flush=True)
+
+# ---- MLP backward
+for kind in ("W1", "W2"):
+    sd = {k: v.cuda() for k, v in O.synthetic_state_dict(kind, seed=1).items()}
+    P = [sd["encoder_layer1.blocks.1." + n].contiguous() for n in ops.NSTB_PARAM_NAMES][18:24]
+    for n_tok in (64, 128, 4096 + 64, 16 * 128 * 128):
+        a = torch.randn(n_tok, 64, device="cuda")
+        g = torch.randn(n_tok, 64, device="cuda") * 1e-3
+        outs = []
+        for fn in (ops.mlp_bwd, ops.mlp_bwd_tc):
+            da = torch.empty_like(a)
+            G = [torch.zeros_like(p) for p in P]
+            fn(a, g, P, da, G)
+            outs.append((da, G))
+        torch.cuda.synchronize()
+        (da0, G0), (da1, G1) = outs
+        names = ("fc1_w", "fc1_b", "fc2_w", "fc2_b", "ln_w", "ln_b")
+        print(f"{kind} mlp_bwd n_tok={n_tok}: da rel {rel(da1, da0):.2e} | " +
+              " ".join(f"{n} {rel(x, y):.2e}" for n, x, y in zip(names, G1, G0)),
+              "tc_error", ops.tc_error(), flush=True)
+    n_tok = 16 * 128 * 128
+    a = torch.randn(n_tok, 64, device="cuda")
+    g = torch.randn(n_tok, 64, device="cuda")
+    da = torch.empty_like(a)
+    G = [torch.zeros_like(p) for p in P]
+    print(f"mlp_bwd simt {timeit(lambda: ops.mlp_bwd(a, g, P, da, G)):.3f} ms, "
+          f"tc {timeit(lambda: ops.mlp_bwd_tc(a, g, P, da, G)):.3f} ms (n_tok={n_tok})", flush=True)

@@ -55,3 +55,22 @@ def run16(N, K, mode, col0):
 for mode in (4, 5):
     for (N, K, col0) in ((64, 64, 0), (48, 64, 48), (64, 32, 96), (32, 128, 16), (32, 64, 0), (128, 128, 8)):
         run16(N, K, mode, col0)
+
+
+def run_bf16(N, K, mode, col0):
+    """mode 6: D[m][n] = sum_k A[k][m] B[k][n] (both MN-major); mode 7: A [128][K] from TMEM, B [K][N] MN-major."""
+    A = torch.randn(K, 128, device="cuda") if mode == 6 else torch.randn(128, K, device="cuda")
+    B = torch.randn(K, N, device="cuda")
+    Ab, Bb = A.bfloat16().double(), B.bfloat16().double()
+    ref = ((Ab.T if mode == 6 else Ab) @ Bb).float()
+    D = torch.full((128, N), float("nan"), device="cuda")
+    rc = L.b200mar_tc_probe(A.data_ptr(), B.data_ptr(), D.data_ptr(), N, K, mode, col0,
+                            torch.cuda.current_stream().cuda_stream)
+    torch.cuda.synchronize()
+    print(f"bf16 mode {mode} N={N:3d} K={K:3d} col0={col0:3d} rc={rc} err={(D - ref).abs().max().item():.2e} "
+          f"tc_error={ops.tc_error()}", flush=True)
+
+
+for mode in (6, 7):
+    for (N, K, col0) in ((64, 128, 0), (64, 16, 0), (192, 128, 16), (128, 64, 32), (16, 32, 0), (256, 128, 0)):
+        run_bf16(N, K, mode, col0)

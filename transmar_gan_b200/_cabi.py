@@ -39,6 +39,8 @@ SIGNATURES = {
     "b200mar_attn_bwd": [_P] * 21 + [_I] * 5 + [_P],
     "b200mar_mlp_fwd": [_P] * 10 + [_L, _P],
     "b200mar_mlp_bwd": [_P] * 15 + [_L, _P],
+    "b200mar_mlp_bwd_tc": [_P] * 16 + [_L, _P],
+    "b200mar_wgrad_tc": [_P] * 4 + [_L, _I, _I, _P],
     "b200mar_mlp_tc_fwd": [_P] * 11 + [_I, _L, _P],
     "b200mar_mlp_tma_fwd": [_P] * 9 + [_L, _P],
     "b200mar_tc_error": [],

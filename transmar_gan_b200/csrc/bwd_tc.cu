@@ -1,0 +1,517 @@
+// bwd_tc.cu — tensor-core (tcgen05, BF16 operands, fp32 accumulate in TMEM) backward kernels shared by
+// the NSTB blocks:
+//
+//   wgrad_tc_kernel     dW[out][in] += sum_t G[t][out] * IN[t][in]  (+ dbias[out] += sum_t G[t][out])
+//                       The tokens are the K dimension of the MMA: a [128 tokens][C] chunk-major tile is
+//                       read as an MN-major operand (= its transpose), so neither operand is ever
+//                       transposed in memory; the partial dW of a persistent CTA stays in TMEM across all
+//                       of its tiles and is flushed once with coalesced atomics.  The bias gradient comes
+//                       out of the same MMAs through a block of ones appended to the IN tile (lane 64).
+//
+//   mlp_bwd_tc_kernel   backward of out = a + LN2(fc2(GELU(fc1(a)))) (components/transformer_blocks.py:119)
+//                       with one thread per token row (TMEM lane = row): fc1/fc2 are recomputed, LayerNorm
+//                       backward runs on the row held in registers, dg = dy W2 and da = dout + dh W1 are
+//                       MMAs whose A operand is written to TMEM by the row threads and whose B operand is
+//                       the SAME resident weight tile read MN-major.  The per-token operands of the weight
+//                       gradients (a, g, dh, dy as bf16) are exported for wgrad_tc_kernel; the column sums
+//                       (d_fc2_b, d_ln_w, d_ln_b) are reduced across the warp with a halving exchange.
+//
+// BF16 (fp32 range, 8-bit significand) is used for every backward operand: gradients span many orders of
+// magnitude, so the forward kernels' fp16 + power-of-two scaling is not carried over.
+#include "common.cuh"
+#include "tc.cuh"
+#include <cuda_bf16.h>
+
+namespace b200mar {
+
+B200MAR_DEFINE_TC_ERROR_GETTER(tc_error_bwd)
+
+// ------------------------------------------------------------------------------------------------
+// small helpers
+__device__ __forceinline__ float bf16_lo(uint32_t u) { return __uint_as_float(u << 16); }
+__device__ __forceinline__ float bf16_hi(uint32_t u) { return __uint_as_float(u & 0xFFFF0000u); }
+
+// Column sums over the 32 rows held by the lanes of a warp (one 64-vector per lane): after five
+// halving exchanges lane l holds the sums of columns 2l and 2l+1, which are added to s0 / s1.
+// `f(i)` yields element i of this lane's vector.
+template <int H>
+__device__ __forceinline__ void colsum_step(float* v, bool up, int mask) {
+#pragma unroll
+  for (int i = 0; i < H; ++i) {
+    const float send = up ? v[i] : v[i + H];
+    const float keep = up ? v[i + H] : v[i];
+    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, mask);
+  }
+}
+template <class F>
+__device__ __forceinline__ void warp_colsum64(F f, int lane, float& s0, float& s1) {
+  float v[32];
+  {
+    const bool up = lane & 16;
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      const float lo = f(i), hi = f(i + 32);
+      v[i] = (up ? hi : lo) + __shfl_xor_sync(0xffffffffu, up ? lo : hi, 16);
+    }
+  }
+  colsum_step<16>(v, lane & 8, 8);
+  colsum_step<8>(v, lane & 4, 4);
+  colsum_step<4>(v, lane & 2, 2);
+  colsum_step<2>(v, lane & 1, 1);
+  s0 += v[0];
+  s1 += v[1];
+}
+
+// GELU(x) = x Phi(x) and its derivative Phi(x) + x phi(x); erf from Abramowitz & Stegun 7.1.26
+// (|error| <= 1.5e-7), the Gaussian shares the exponential of the erf.
+__device__ __forceinline__ void gelu_and_grad(float x, float& g, float& gp) {
+  const float z = fabsf(x) * 0.70710678118654752440f;
+  const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
+  float p = fmaf(1.061405429f, t, -1.453152027f);
+  p = fmaf(p, t, 1.421413741f);
+  p = fmaf(p, t, -0.284496736f);
+  p = fmaf(p, t, 0.254829592f);
+  const float e = tc::ex2_approx(-z * z * 1.4426950408889634f);     // exp(-x^2/2)
+  const float erf_abs = fmaf(-p * t, e, 1.0f);
+  const float cdf = fmaf(0.5f, copysignf(erf_abs, x), 0.5f);
+  g = x * cdf;
+  gp = fmaf(x * 0.39894228040143267794f, e, cdf);
+}
+
+// ================================================================================================
+// wgrad_tc_kernel
+struct WgradParams {
+  const uint16_t* in;   // bf16 [n_tok][cin]
+  const uint16_t* g;    // bf16 [n_tok][cout]
+  float* dw;            // fp32 [cout][cin], accumulated with atomics
+  float* dbias;         // fp32 [cout] or null (cin == 64 only)
+  long long n_tok;
+  int cin, cout;
+};
+
+// coalesced copy of a [128][C] bf16 row-major global tile into a chunk-major smem tile (rows >= valid
+// are zero-filled): lane = (row%8, chunk%4) -> 64 contiguous bytes per row in global memory, 128
+// contiguous bytes per chunk in shared memory.
+__device__ __forceinline__ void load_tile16(unsigned char* sT, const uint16_t* gsrc, long long tok0,
+                                            int valid, int C, int warp, int lane) {
+  const int r8 = lane & 7, q4 = lane >> 3;
+  const int nitems = 16 * (C >> 5);                  // 16 row groups x C/32 chunk quads
+#pragma unroll 4
+  for (int it = warp; it < nitems; it += 4) {
+    const int row = (it & 15) * 8 + r8, chunk = (it >> 4) * 4 + q4;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (row < valid) v = __ldg(reinterpret_cast<const uint4*>(gsrc + (size_t)(tok0 + row) * C + chunk * 8));
+    *reinterpret_cast<uint4*>(sT + chunk * 2048 + row * 16) = v;
+  }
+}
+
+__global__ void __launch_bounds__(128) wgrad_tc_kernel(WgradParams p) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  __shared__ uint64_t bar;
+  __shared__ uint32_t slot;
+  unsigned char* sIN = smem_raw;                     // [128][cin]   chunk-major bf16
+  unsigned char* sOnes = sIN + p.cin * 256;          // [128][8]     one more chunk: ones for valid rows
+  unsigned char* sG = sOnes + 2048;                  // [128][cout]
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+
+  if (tid == 0) { tc::mbar_init(&bar, 1); tc::fence_barrier_init(); }
+  if (warp == 0) tc::tmem_alloc<256>(&slot);
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tbase = slot;
+  const uint32_t idesc = tc::idesc_bf16(128, p.cout, true, true);
+  const uint64_t dA = tc::desc_mnmajor16(tc::smem_u32(sIN), 128),
+                 dB = tc::desc_mnmajor16(tc::smem_u32(sG), 128);
+  const long long ntile = (p.n_tok + 127) / 128;
+  uint32_t ph = 0, first = 1;
+  for (long long tile = blockIdx.x; tile < ntile; tile += gridDim.x) {
+    const long long tok0 = tile * 128;
+    const int valid = (int)((p.n_tok - tok0) < 128 ? (p.n_tok - tok0) : 128);
+    load_tile16(sIN, p.in, tok0, valid, p.cin, warp, lane);
+    load_tile16(sG, p.g, tok0, valid, p.cout, warp, lane);
+    {
+      const uint32_t o = tid < valid ? 0x3F803F80u : 0u;   // bf16 1.0 pairs
+      *reinterpret_cast<uint4*>(sOnes + tid * 16) = make_uint4(o, o, o, o);
+    }
+    tc::fence_async_smem();
+    __syncthreads();
+    if (warp == 0) {
+      tc::tc_fence_after();
+      if (tc::elect_one()) {
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          tc::mma_f16(tbase, dA + ks * 16, dB + ks * 16, idesc, (first == 0u || ks > 0) ? 1u : 0u);
+        tc::mma_commit(&bar);
+      }
+      __syncwarp();
+    }
+    first = 0;
+    tc::mbar_wait(&bar, ph, &g_tc_error); ph ^= 1;    // the tiles may be overwritten after this
+    tc::tc_fence_after();
+  }
+  // ---- flush: lane = input channel, columns = output channels
+  if (first == 0u) {
+    const int ci = warp * 32 + lane;
+    const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
+    for (int c0 = 0; c0 < p.cout; c0 += 16) {
+      float v[16];
+      tc::tmem_ld16(tbase + lane_addr + c0, v);
+      if (ci < p.cin) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) atomicAdd(p.dw + (size_t)(c0 + i) * p.cin + ci, v[i]);
+      } else if (ci == 64 && p.dbias) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) atomicAdd(p.dbias + c0 + i, v[i]);
+      }
+    }
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc<256>(slot);
+}
+
+// ================================================================================================
+// mlp_bwd_tc_kernel
+struct MlpBwdTcParams {
+  const float* a;       // [n_tok][64]  block-tail input (post-attention stream)
+  const float* dout;    // [n_tok][64]  gradient of out = a + LN2(mlp(a))
+  const float* fc1_w; const float* fc1_b; const float* fc2_w; const float* fc2_b; const float* ln_w;
+  float* da;            // [n_tok][64]
+  uint16_t* a16;        // bf16 exports for the weight gradients
+  uint16_t* g16;        // [n_tok][128] GELU output
+  uint16_t* dh16;       // [n_tok][128] gradient of the fc1 pre-activation
+  uint16_t* dy16;       // [n_tok][64]  gradient of the fc2 output
+  float* d_fc2_b; float* d_ln_w; float* d_ln_b;
+  long long n_tok;
+};
+
+constexpr int kBwdWorkers = 2;
+
+struct MlpBwdSmem {                                  // BYTE offsets
+  static constexpr int oW1 = 0;                      // bf16 [128 hid rows][64 in ch], chunk-major R = 128
+  static constexpr int oW2 = oW1 + 128 * 64 * 2;     // bf16 [64 out rows][128 hid ch], R = 64
+  static constexpr int oB1 = oW2 + 64 * 128 * 2;     // fp32 [128]
+  static constexpr int oB2 = oB1 + 512;              // fp32 [64]
+  static constexpr int oLnW = oB2 + 256;             // fp32 [64]
+  static constexpr int oBar = oLnW + 256;            // kBwdWorkers x 4 mbarriers + tmem slot
+  static constexpr int kBytes = oBar + kBwdWorkers * 32 + 16;
+};
+
+__global__ void __launch_bounds__(128 * kBwdWorkers, 1) mlp_bwd_tc_kernel(MlpBwdTcParams p) {
+  using L = MlpBwdSmem;
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  unsigned char* sW1 = smem_raw + L::oW1;
+  unsigned char* sW2 = smem_raw + L::oW2;
+  float* sB1 = reinterpret_cast<float*>(smem_raw + L::oB1);
+  float* sB2 = reinterpret_cast<float*>(smem_raw + L::oB2);
+  float* sLnW = reinterpret_cast<float*>(smem_raw + L::oLnW);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + L::oBar);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem_raw + L::oBar + kBwdWorkers * 32);
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  const int wk = warp >> 2, wq = warp & 3;
+  uint64_t* bar = bars + wk * 4;                     // [0] fc1  [1] fc2  [2] dg  [3] da
+
+  // ---- stage the weights as bf16 chunk-major tiles
+  for (int idx = tid; idx < 128 * 8; idx += 128 * kBwdWorkers) {          // fc1 [128][64]
+    const int n = idx & 127, kc = idx >> 7;
+    const float4* src = reinterpret_cast<const float4*>(p.fc1_w + n * 64 + kc * 8);
+    const float4 x = src[0], y = src[1];
+    *reinterpret_cast<uint4*>(sW1 + kc * 2048 + n * 16) =
+        make_uint4(tc::pack_bf16(x.x, x.y), tc::pack_bf16(x.z, x.w), tc::pack_bf16(y.x, y.y), tc::pack_bf16(y.z, y.w));
+  }
+  for (int idx = tid; idx < 64 * 16; idx += 128 * kBwdWorkers) {          // fc2 [64][128]
+    const int n = idx & 63, kc = idx >> 6;
+    const float4* src = reinterpret_cast<const float4*>(p.fc2_w + n * 128 + kc * 8);
+    const float4 x = src[0], y = src[1];
+    *reinterpret_cast<uint4*>(sW2 + kc * 1024 + n * 16) =
+        make_uint4(tc::pack_bf16(x.x, x.y), tc::pack_bf16(x.z, x.w), tc::pack_bf16(y.x, y.y), tc::pack_bf16(y.z, y.w));
+  }
+  if (tid < 128) sB1[tid] = p.fc1_b[tid];
+  if (tid < 64) { sB2[tid] = p.fc2_b[tid]; sLnW[tid] = p.ln_w[tid]; }
+  if (tid == 0) {
+    for (int i = 0; i < 4 * kBwdWorkers; ++i) tc::mbar_init(bars + i, 1);
+    tc::fence_barrier_init();
+  }
+  if (warp == 0) tc::tmem_alloc<512>(tmem_slot);
+  tc::fence_async_smem();
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+
+  // TMEM columns of a worker (256):
+  //   [0,128)   D1 = fc1 pre-activation -> { g0 [0,32) | gp0 [32,64) | g1 [64,96) | gp1 [96,128) } packed bf16
+  //             (g: GELU output, A operand of fc2; gp: GELU derivative, later overwritten by dh, A operand of da)
+  //             -> dg quarters 0,1 over g0, g1
+  //   [128,192) D2 = fc2 output -> dg quarters 2,3 -> da accumulator
+  //   [192,224) a packed (A operand of fc1) -> dy packed (A operand of dg)
+  const uint32_t tbase = *tmem_slot + wk * 256;
+  const uint32_t lane_addr = (uint32_t)(wq * 32) << 16;
+  const uint32_t tl = tbase + lane_addr;
+  constexpr uint32_t cD2 = 128, cA = 192;
+  constexpr uint32_t kI128 = tc::idesc_bf16(128, 128), kI64 = tc::idesc_bf16(128, 64),
+                     kI32mn = tc::idesc_bf16(128, 32, false, true), kI64mn = tc::idesc_bf16(128, 64, false, true);
+  const uint64_t dW1k = tc::desc_kmajor16(tc::smem_u32(sW1), 128), dW2k = tc::desc_kmajor16(tc::smem_u32(sW2), 64),
+                 dW1mn = tc::desc_mnmajor16(tc::smem_u32(sW1), 128), dW2mn = tc::desc_mnmajor16(tc::smem_u32(sW2), 64);
+  const int row = wq * 32 + lane;
+  uint32_t ph = 0;
+  float db2_0 = 0.f, db2_1 = 0.f, dg_0 = 0.f, dg_1 = 0.f, dbe_0 = 0.f, dbe_1 = 0.f;   // columns 2*lane, 2*lane+1
+
+  const long long ntile = (p.n_tok + 127) / 128;
+  for (long long tile = (long long)blockIdx.x * kBwdWorkers + wk; tile < ntile;
+       tile += (long long)gridDim.x * kBwdWorkers) {
+    const long long tok = tile * 128 + row;
+    const bool ok = tok < p.n_tok;
+    // ---- P0: a row -> packed bf16 A operand in TMEM + export
+    {
+      uint32_t ap[32];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (ok) v = __ldg(reinterpret_cast<const float4*>(p.a + (size_t)tok * 64) + i);
+        ap[2 * i] = tc::pack_bf16(v.x, v.y);
+        ap[2 * i + 1] = tc::pack_bf16(v.z, v.w);
+      }
+      tc::tmem_st32(tl + cA, reinterpret_cast<const float(&)[32]>(ap));
+      if (ok) {
+        uint4* dst = reinterpret_cast<uint4*>(p.a16 + (size_t)tok * 64);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) dst[i] = make_uint4(ap[4 * i], ap[4 * i + 1], ap[4 * i + 2], ap[4 * i + 3]);
+      }
+    }
+    tc::tmem_wait_st();
+    tc::tc_fence_before();
+    tc::worker_sync(1 + wk);
+    if (wq == 0) {
+      tc::tc_fence_after();
+      if (tc::elect_one()) {
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks)
+          tc::mma_f16_ts(tbase, tbase + cA + ks * 8, dW1k + ks * 256, kI128, ks > 0);
+        tc::mma_commit(bar + 0);
+      }
+      __syncwarp();
+    }
+    tc::mbar_wait(bar + 0, ph, &g_tc_error);
+    tc::tc_fence_after();
+    // ---- P1: GELU and its derivative, two halves of 64 hidden channels
+#pragma unroll 1
+    for (int half = 0; half < 2; ++half) {
+      float v[64];
+      tc::tmem_ld64(tl + half * 64, v);
+      uint32_t gq[32], gpq[32];
+      const float* b1 = sB1 + half * 64;
+#pragma unroll
+      for (int c = 0; c < 64; c += 2) {
+        float g0, g1, d0, d1;
+        gelu_and_grad(v[c] + b1[c], g0, d0);
+        gelu_and_grad(v[c + 1] + b1[c + 1], g1, d1);
+        gq[c >> 1] = tc::pack_bf16(g0, g1);
+        gpq[c >> 1] = tc::pack_bf16(d0, d1);
+      }
+      tc::tmem_st32(tl + half * 64, reinterpret_cast<const float(&)[32]>(gq));
+      tc::tmem_st32(tl + half * 64 + 32, reinterpret_cast<const float(&)[32]>(gpq));
+      if (ok) {
+        uint4* dst = reinterpret_cast<uint4*>(p.g16 + (size_t)tok * 128 + half * 64);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) dst[i] = make_uint4(gq[4 * i], gq[4 * i + 1], gq[4 * i + 2], gq[4 * i + 3]);
+      }
+    }
+    tc::tmem_wait_st();
+    tc::tc_fence_before();
+    tc::worker_sync(1 + wk);
+    if (wq == 0) {
+      tc::tc_fence_after();
+      if (tc::elect_one()) {
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          tc::mma_f16_ts(tbase + cD2, tbase + (ks < 4 ? ks * 8 : 64 + (ks - 4) * 8), dW2k + ks * 128, kI64, ks > 0);
+        tc::mma_commit(bar + 1);
+      }
+      __syncwarp();
+    }
+    tc::mbar_wait(bar + 1, ph, &g_tc_error);
+    tc::tc_fence_after();
+    // ---- P2: LayerNorm backward on the row -> dy (packed bf16 A operand + export), column sums
+    {
+      float y[64];
+      tc::tmem_ld64(tl + cD2, y);
+      float m4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int i = 0; i < 64; ++i) { y[i] += sB2[i]; m4[i & 3] += y[i]; }
+      const float mean = ((m4[0] + m4[1]) + (m4[2] + m4[3])) * (1.0f / 64.f);
+      float v4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int i = 0; i < 64; ++i) { y[i] -= mean; v4[i & 3] = fmaf(y[i], y[i], v4[i & 3]); }
+      const float rstd = 1.0f / sqrtf(((v4[0] + v4[1]) + (v4[2] + v4[3])) * (1.0f / 64.f) + kLnEps);
+      float d[64];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (ok) v = __ldg(reinterpret_cast<const float4*>(p.dout + (size_t)tok * 64) + i);
+        d[4 * i] = v.x; d[4 * i + 1] = v.y; d[4 * i + 2] = v.z; d[4 * i + 3] = v.w;
+      }
+      float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int i = 0; i < 64; ++i) {
+        y[i] *= rstd;                                  // normalised row
+        const float t = d[i] * sLnW[i];
+        s1[i & 3] += t;
+        s2[i & 3] = fmaf(t, y[i], s2[i & 3]);
+      }
+      const float m1 = ((s1[0] + s1[1]) + (s1[2] + s1[3])) * (1.0f / 64.f);
+      const float m2 = ((s2[0] + s2[1]) + (s2[2] + s2[3])) * (1.0f / 64.f);
+      warp_colsum64([&](int i) { return d[i] * y[i]; }, lane, dg_0, dg_1);      // d_ln_w
+      warp_colsum64([&](int i) { return d[i]; }, lane, dbe_0, dbe_1);           // d_ln_b
+#pragma unroll
+      for (int i = 0; i < 64; ++i) y[i] = rstd * (fmaf(d[i], sLnW[i], -m1) - y[i] * m2);   // dy
+      warp_colsum64([&](int i) { return y[i]; }, lane, db2_0, db2_1);           // d_fc2_b
+      uint32_t dq[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) dq[i] = tc::pack_bf16(y[2 * i], y[2 * i + 1]);
+      tc::tmem_st32(tl + cA, reinterpret_cast<const float(&)[32]>(dq));
+      if (ok) {
+        uint4* dst = reinterpret_cast<uint4*>(p.dy16 + (size_t)tok * 64);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) dst[i] = make_uint4(dq[4 * i], dq[4 * i + 1], dq[4 * i + 2], dq[4 * i + 3]);
+      }
+    }
+    tc::tmem_wait_st();
+    tc::tc_fence_before();
+    tc::worker_sync(1 + wk);
+    // ---- dg = dy W2 in four quarters of 32 hidden channels (B = the fc2 tile read MN-major)
+    if (wq == 0) {
+      tc::tc_fence_after();
+      if (tc::elect_one()) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const uint32_t dcol = q == 0 ? 0u : (q == 1 ? 64u : (q == 2 ? 128u : 160u));
+#pragma unroll
+          for (int ks = 0; ks < 4; ++ks)
+            tc::mma_f16_ts(tbase + dcol, tbase + cA + ks * 8, dW2mn + q * 256 + ks * 16, kI32mn, ks > 0);
+        }
+        tc::mma_commit(bar + 2);
+      }
+      __syncwarp();
+    }
+    tc::mbar_wait(bar + 2, ph, &g_tc_error);
+    tc::tc_fence_after();
+    // ---- P3: dh = dg * GELU'(pre) -> packed bf16 over gp (A operand of da) + export
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint32_t dcol = q == 0 ? 0u : (q == 1 ? 64u : (q == 2 ? 128u : 160u));
+      const uint32_t gcol = q == 0 ? 32u : (q == 1 ? 48u : (q == 2 ? 96u : 112u));
+      float dg[32], gp[16];
+      tc::tmem_ld32(tl + dcol, dg);
+      tc::tmem_ld16(tl + gcol, gp);
+      uint32_t hq[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const uint32_t u = __float_as_uint(gp[i]);
+        hq[i] = tc::pack_bf16(dg[2 * i] * bf16_lo(u), dg[2 * i + 1] * bf16_hi(u));
+      }
+      tc::tmem_st16(tl + gcol, reinterpret_cast<const float(&)[16]>(hq));
+      if (ok) {
+        uint4* dst = reinterpret_cast<uint4*>(p.dh16 + (size_t)tok * 128 + q * 32);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) dst[i] = make_uint4(hq[4 * i], hq[4 * i + 1], hq[4 * i + 2], hq[4 * i + 3]);
+      }
+    }
+    tc::tmem_wait_st();
+    tc::tc_fence_before();
+    tc::worker_sync(1 + wk);
+    // ---- da = dout + dh W1 (B = the fc1 tile read MN-major)
+    if (wq == 0) {
+      tc::tc_fence_after();
+      if (tc::elect_one()) {
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          tc::mma_f16_ts(tbase + cD2, tbase + (ks < 4 ? 32 + ks * 8 : 96 + (ks - 4) * 8), dW1mn + ks * 16, kI64mn, ks > 0);
+        tc::mma_commit(bar + 3);
+      }
+      __syncwarp();
+    }
+    tc::mbar_wait(bar + 3, ph, &g_tc_error);
+    tc::tc_fence_after();
+    {
+      float v[64];
+      tc::tmem_ld64(tl + cD2, v);
+      if (ok) {
+        const float4* src = reinterpret_cast<const float4*>(p.dout + (size_t)tok * 64);
+        float4* dst = reinterpret_cast<float4*>(p.da + (size_t)tok * 64);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const float4 g = __ldg(src + i);
+          dst[i] = make_float4(g.x + v[4 * i], g.y + v[4 * i + 1], g.z + v[4 * i + 2], g.w + v[4 * i + 3]);
+        }
+      }
+    }
+    ph ^= 1;
+  }
+  // ---- flush the column sums (lane l of every warp holds columns 2l, 2l+1)
+  atomicAdd(p.d_fc2_b + 2 * lane, db2_0); atomicAdd(p.d_fc2_b + 2 * lane + 1, db2_1);
+  atomicAdd(p.d_ln_w + 2 * lane, dg_0);   atomicAdd(p.d_ln_w + 2 * lane + 1, dg_1);
+  atomicAdd(p.d_ln_b + 2 * lane, dbe_0);  atomicAdd(p.d_ln_b + 2 * lane + 1, dbe_1);
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc<512>(*tmem_slot);
+}
+
+static int launch_wgrad(const uint16_t* in16, const uint16_t* g16, float* dw, float* dbias, long long n_tok,
+                        int cin, int cout, cudaStream_t st) {
+  if (n_tok <= 0 || (cin != 64 && cin != 128) || cout % 32 || cout < 64 || cout > 256) return -1;
+  if (dbias && cin != 64) return -1;
+  WgradParams p{in16, g16, dw, dbias, n_tok, cin, cout};
+  // >= 100 KB keeps residency at two CTAs per SM (each owns 256 TMEM columns)
+  size_t smem = (size_t)cin * 256 + 2048 + (size_t)cout * 256;
+  if (smem < 100 * 1024) smem = 100 * 1024;
+  static bool configured = false;
+  if (!configured) {
+    B200MAR_CHECK(cudaFuncSetAttribute(wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+    configured = true;
+  }
+  const long long ntile = (n_tok + 127) / 128;
+  long long grid = ntile < 2LL * sm_count() ? ntile : 2LL * sm_count();
+  wgrad_tc_kernel<<<(int)grid, 128, smem, st>>>(p);
+  B200MAR_CHECK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace b200mar
+
+extern "C" int b200mar_wgrad_tc(const void* in16, const void* g16, float* dw, float* dbias, long long n_tok,
+                                int cin, int cout, void* stream) {
+  using namespace b200mar;
+  return launch_wgrad((const uint16_t*)in16, (const uint16_t*)g16, dw, dbias, n_tok, cin, cout, (cudaStream_t)stream);
+}
+
+extern "C" int b200mar_mlp_bwd_tc(const float* a, const float* dout, const float* fc1_w, const float* fc1_b,
+                                  const float* fc2_w, const float* fc2_b, const float* ln_w, const float* ln_b,
+                                  float* da, float* d_fc1_w, float* d_fc1_b, float* d_fc2_w, float* d_fc2_b,
+                                  float* d_ln_w, float* d_ln_b, void* scratch, long long n_tok, void* stream) {
+  using namespace b200mar;
+  (void)ln_b;
+  if (n_tok <= 0 || n_tok % kTok || !scratch) return -1;
+  uint16_t* s = (uint16_t*)scratch;                  // n_tok * 384 bf16
+  MlpBwdTcParams p{};
+  p.a = a; p.dout = dout; p.fc1_w = fc1_w; p.fc1_b = fc1_b; p.fc2_w = fc2_w; p.fc2_b = fc2_b; p.ln_w = ln_w;
+  p.da = da; p.a16 = s; p.g16 = s + n_tok * 64; p.dh16 = s + n_tok * 192; p.dy16 = s + n_tok * 320;
+  p.d_fc2_b = d_fc2_b; p.d_ln_w = d_ln_w; p.d_ln_b = d_ln_b; p.n_tok = n_tok;
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t smem = MlpBwdSmem::kBytes;
+  static bool configured = false;
+  if (!configured) {
+    B200MAR_CHECK(cudaFuncSetAttribute(mlp_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = true;
+  }
+  const long long ntile = (n_tok + 127) / 128;
+  long long grid = (ntile + kBwdWorkers - 1) / kBwdWorkers;
+  if (grid > sm_count()) grid = sm_count();
+  mlp_bwd_tc_kernel<<<(int)grid, 128 * kBwdWorkers, smem, st>>>(p);
+  B200MAR_CHECK(cudaGetLastError());
+  if (int rc = launch_wgrad(p.a16, p.dh16, d_fc1_w, d_fc1_b, n_tok, 64, 128, st)) return rc;   // dW1 [128][64], db1
+  if (int rc = launch_wgrad(p.g16, p.dy16, d_fc2_w, nullptr, n_tok, 128, 64, st)) return rc;  // dW2 [64][128]
+  return 0;
+}

@@ -101,6 +101,25 @@ __host__ __device__ constexpr uint32_t idesc_tf32(int M, int N) {
 __host__ __device__ constexpr uint32_t idesc_f16(int M, int N) {
   return (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
+// instruction descriptor, kind::f16 with BF16 operands (a_format = b_format = 1), fp32 accumulate;
+// a_mn / b_mn select an MN-major operand (bit 15 / 16: the transpose of a chunk-major tile, see below)
+__host__ __device__ constexpr uint32_t idesc_bf16(int M, int N, bool a_mn = false, bool b_mn = false) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | (a_mn ? (1u << 15) : 0u) | (b_mn ? (1u << 16) : 0u) |
+         ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+// two fp32 -> packed bf16x2 (lo = a, hi = b), round-to-nearest-even
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+  return r;
+}
+// A 16-bit chunk-major tile of R rows: element (row r, channel c) at byte (c/8)*(R*16) + r*16 + (c%8)*2.
+//   * as a K-major operand (M/N index = row, K = channel): smem_desc(base, LBO = R*16, SBO = 128),
+//     one K = 16 step advances the start by 2*R*16 bytes;
+//   * as an MN-major operand (M/N index = channel, K = row; i.e. the TRANSPOSE of the tile):
+//     smem_desc(base, LBO = 128, SBO = R*16), one K = 16 step (16 rows) advances the start by 256 bytes.
+__device__ __forceinline__ uint64_t desc_kmajor16(uint32_t saddr, int R) { return smem_desc(saddr, R * 16, 128); }
+__device__ __forceinline__ uint64_t desc_mnmajor16(uint32_t saddr, int R) { return smem_desc(saddr, 128, R * 16); }
 // kind::f16: one K = 16 step, operands K-major fp16 (8 elements per 16-byte k-chunk)
 __device__ __forceinline__ void mma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
                                         uint32_t idesc, uint32_t accumulate) {

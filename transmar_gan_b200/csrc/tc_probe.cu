@@ -7,6 +7,7 @@
 #include "common.cuh"
 #include "tc.cuh"
 #include <cuda_fp16.h>
+#include <cuda_bf16.h>
 
 namespace b200mar {
 
@@ -193,11 +194,94 @@ __global__ void __launch_bounds__(128, 1) tc_probe_f16_kernel(const float* __res
   if (t < 32) tc::tmem_dealloc<512>(slot);
 }
 
+// bf16 / MN-major variants (the layouts the backward kernels rely on):
+//   mode 6: D[m][n] = sum_k A[k][m] B[k][n], A [K][128] and B [K][N] both chunk-major tiles of K rows read
+//           as MN-major operands (the transposes of the tiles);
+//   mode 7: D = A B with A [128][K] packed two-per-column in TMEM and B [K][N] MN-major in shared memory.
+__global__ void __launch_bounds__(128, 1) tc_probe_bf16_kernel(const float* __restrict__ A,
+                                                               const float* __restrict__ B,
+                                                               float* __restrict__ D, int N, int K,
+                                                               int mode, int col0) {
+  extern __shared__ __align__(128) float smem[];
+  unsigned char* sA = reinterpret_cast<unsigned char*>(smem);       // [K rows][128 ch] chunk-major bf16
+  unsigned char* sB = sA + K * 128 * 2;                               // [K rows][N ch]
+  __shared__ uint64_t bar;
+  __shared__ uint32_t slot;
+  const int t = threadIdx.x, lane = t & 31, wq = t >> 5;
+  if (mode == 6)
+    for (int idx = t; idx < K * 128; idx += 128) {
+      const int k = idx / 128, m = idx % 128;
+      *reinterpret_cast<__nv_bfloat16*>(sA + (m >> 3) * (K * 16) + k * 16 + (m & 7) * 2) = __float2bfloat16_rn(A[idx]);
+    }
+  for (int idx = t; idx < K * N; idx += 128) {
+    const int k = idx / N, n = idx % N;
+    *reinterpret_cast<__nv_bfloat16*>(sB + (n >> 3) * (K * 16) + k * 16 + (n & 7) * 2) = __float2bfloat16_rn(B[idx]);
+  }
+  if (t == 0) { tc::mbar_init(&bar, 1); tc::fence_barrier_init(); }
+  if (t < 32) tc::tmem_alloc<512>(&slot);
+  tc::fence_async_smem();
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tbase = slot;
+  const uint32_t lane_addr = (uint32_t)(wq * 32) << 16;
+  const uint32_t dcol = col0, acol = 256 + col0;
+  const int row = wq * 32 + lane;
+  if (mode == 7) {
+    for (int c = 0; c < K / 2; c += 8) {
+      float v[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        v[i] = __uint_as_float(tc::pack_bf16(A[row * K + 2 * (c + i)], A[row * K + 2 * (c + i) + 1]));
+      asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};"
+                   ::"r"(tbase + lane_addr + acol + c), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]),
+                     "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7]) : "memory");
+    }
+    tc::tmem_wait_st();
+    tc::tc_fence_before();
+    __syncthreads();
+  }
+  if (wq == 0) {
+    tc::tc_fence_after();
+    if (tc::elect_one()) {
+      const uint32_t idesc = tc::idesc_bf16(128, N, mode == 6, true);
+      const uint64_t da = tc::desc_mnmajor16(tc::smem_u32(sA), K);
+      const uint64_t db = tc::desc_mnmajor16(tc::smem_u32(sB), K);
+      for (int k = 0; k < K; k += 16) {
+        if (mode == 7) tc::mma_f16_ts(tbase + dcol, tbase + acol + k / 2, db + (k >> 4) * 16, idesc, k > 0);
+        else           tc::mma_f16(tbase + dcol, da + (k >> 4) * 16, db + (k >> 4) * 16, idesc, k > 0);
+      }
+      tc::mma_commit(&bar);
+    }
+    __syncwarp();
+  }
+  tc::mbar_wait(&bar, 0, &g_tc_error);
+  tc::tc_fence_after();
+  for (int c = 0; c < N; c += 16) {
+    float v[16];
+    tc::tmem_ld16(tbase + lane_addr + dcol + c, v);
+#pragma unroll
+    for (int i = 0; i < 16; ++i) D[row * N + c + i] = v[i];
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (t < 32) tc::tmem_dealloc<512>(slot);
+}
+
 }  // namespace b200mar
 
 extern "C" int b200mar_tc_probe(const float* A, const float* B, float* D, int N, int K, int mode,
                                 int col0, void* stream) {
   using namespace b200mar;
+  if (mode == 6 || mode == 7) {
+    if (N % 16 || N < 16 || N > 256 || K % 16 || K < 16 || K > 128 || col0 < 0 || col0 + N > 256) return -1;
+    const size_t smem16 = (size_t)(128 * K + N * K) * 2;
+    B200MAR_CHECK(cudaFuncSetAttribute(tc_probe_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       200 * 1024));
+    tc_probe_bf16_kernel<<<1, 128, smem16, (cudaStream_t)stream>>>(A, B, D, N, K, mode, col0);
+    B200MAR_CHECK(cudaGetLastError());
+    return 0;
+  }
   if (mode == 4 || mode == 5) {
     if (N % 16 || N < 16 || N > 256 || K % 16 || K < 16 || K > 128 || col0 < 0 || col0 + N > 256) return -1;
     const size_t smem16 = (size_t)(128 * K + N * K) * 2;

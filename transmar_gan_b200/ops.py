@@ -291,6 +291,28 @@ def mlp_bwd(a: Tensor, dout: Tensor, params: List[Tensor], da: Tensor, grads: Li
         a.numel() // 64, _stream())
 
 
+@torch.library.custom_op(f"{_NS}::mlp_bwd_tc", mutates_args=("da", "grads"))
+def mlp_bwd_tc(a: Tensor, dout: Tensor, params: List[Tensor], da: Tensor, grads: List[Tensor]) -> None:
+    """mlp_bwd on the tcgen05 tensor cores (BF16 operands, fp32 accumulate): the row kernel exports the
+    bf16 operands of the weight gradients into a scratch buffer, two wgrad launches consume them."""
+    _chk(a, dout, da, *params, *grads)
+    n_tok = a.numel() // 64
+    scratch = torch.empty(n_tok * 384, device=a.device, dtype=torch.bfloat16)
+    _call("mlp_bwd_tc", _p(a), _p(dout), *[_p(t) for t in params], _p(da), *[_p(t) for t in grads],
+          scratch.data_ptr(), n_tok, _stream(), meta=(n_tok,))
+    profile.launches += 2                     # the entry point launches the row kernel + two wgrad kernels
+
+
+def wgrad_tc(in16: Tensor, g16: Tensor, dw: Tensor, dbias: Optional[Tensor]) -> None:
+    """dw[cout][cin] += g16^T in16 (and dbias += column sums of g16) on the tensor cores; bf16 inputs."""
+    for t in (in16, g16):
+        if not t.is_cuda or t.dtype != torch.bfloat16 or not t.is_contiguous():
+            raise RuntimeError("wgrad_tc needs contiguous CUDA bf16 operands")
+    _chk(dw, dbias)
+    _call("wgrad_tc", in16.data_ptr(), g16.data_ptr(), _p(dw), _p(dbias), in16.shape[0], in16.shape[1],
+          g16.shape[1], _stream(), meta=(in16.shape[0],))
+
+
 # ------------------------------------------------------------------------------ patch merging
 @torch.library.custom_op(f"{_NS}::patch_merge_fwd", mutates_args=())
 def patch_merge_fwd(x: Tensor, ln_w: Tensor, ln_b: Tensor, red_w: Tensor, ph: int,
@@ -520,7 +542,7 @@ class NSTBFunction(torch.autograd.Function):
             G.append(flat[off:off + n].view(p.shape))
             off += n
         da = torch.empty_like(a)
-        mlp_bwd(a, g, P[18:24], da, G[18:24])
+        (mlp_bwd_tc if _PRECISION == "tf32" else mlp_bwd)(a, g, P[18:24], da, G[18:24])
         dz = torch.empty_like(z)
         dctx = torch.zeros_like(c)
         attn_bwd(z, c, da, P[10:18], dz, dctx, G[10:18], ph, pw, nh, shift)
