@@ -118,6 +118,18 @@ int b200mar_attn_bwd(const float* z, const float* ctx, const float* da,
                      float* d_qkv_w, float* d_qkv_b, float* d_proj_w, float* d_proj_b,
                      float* d_logit_scale, float* d_bias_table, float* d_ln_w, float* d_ln_b,
                      int B, int ph, int pw, int nh, int shift, void* stream);
+/* attn_bwd on the tcgen05 tensor cores (fp16 / bf16 operands, fp32 accumulate): same contract; `scratch`
+ * is a caller-owned device buffer of ceil(B*(ph/8)*(pw/8)/2) * 128 * 768 bytes (window-order bf16
+ * operands of the weight gradients: X, O, dY, per-head packed d[q|k|v]).                       */
+int b200mar_attn_bwd_tc(const float* z, const float* ctx, const float* da,
+                     const float* qkv_w, const float* qkv_b,
+                     const float* proj_w, const float* proj_b,
+                     const float* logit_scale, const float* bias_table,
+                     const float* ln_w, const float* ln_b,
+                     float* dz, float* dctx,
+                     float* d_qkv_w, float* d_qkv_b, float* d_proj_w, float* d_proj_b,
+                     float* d_logit_scale, float* d_bias_table, float* d_ln_w, float* d_ln_b, void* scratch,
+                     int B, int ph, int pw, int nh, int shift, void* stream);
 
 /* ---- a8(second half)+a9: `x + norm2(ffn(x))` and the within-stage residual
  * (components/transformer_blocks.py:119, components/encoder_decoder.py:138-141) -----------

@@ -65,3 +65,40 @@ for kind in ("W1", "W2"):
     G = [torch.zeros_like(p) for p in P]
     print(f"mlp_bwd simt {timeit(lambda: ops.mlp_bwd(a, g, P, da, G)):.3f} ms, "
           f"tc {timeit(lambda: ops.mlp_bwd_tc(a, g, P, da, G)):.3f} ms (n_tok={n_tok})", flush=True)
+
+# ---- attention backward
+names = ("qkv_w", "qkv_b", "proj_w", "proj_b", "logit_scale", "bias_table", "ln_w", "ln_b")
+for kind in ("W1", "W2"):
+    sd = {k: v.cuda() for k, v in O.synthetic_state_dict(kind, seed=1).items()}
+    for pre, nh in (("encoder_layer1.blocks.1.", 6), ("encoder_layer2.blocks.1.", 4)):
+        P = [sd[pre + n].contiguous() for n in ops.NSTB_PARAM_NAMES][10:18]
+        for (B, ph, pw) in ((1, 16, 16), (1, 24, 40), (3, 24, 24)):
+            for shift in (0, 4):
+                z = torch.randn(B, ph * pw, 64, device="cuda")
+                c = torch.randn(B, (ph // 8) * (pw // 8), 64, device="cuda") * 0.5
+                da = torch.randn_like(z) * 1e-2
+                outs = []
+                for fn in (ops.attn_bwd, ops.attn_bwd_tc):
+                    dz = torch.empty_like(z)
+                    dctx = torch.zeros_like(c)
+                    G = [torch.zeros_like(p) for p in P]
+                    fn(z, c, da, P, dz, dctx, G, ph, pw, nh, shift)
+                    outs.append((dz, dctx, G))
+                torch.cuda.synchronize()
+                (dz0, dc0, G0), (dz1, dc1, G1) = outs
+                print(f"{kind} attn_bwd nh={nh} B={B} {ph}x{pw} shift={shift}: dz-da rel {rel(dz1 - da, dz0 - da):.2e} "
+                      f"dctx {rel(dc1, dc0):.2e} | " + " ".join(f"{n} {rel(x, y):.2e}" for n, x, y in zip(names, G1, G0)),
+                      "tc_error", ops.tc_error(), flush=True)
+sd = {k: v.cuda() for k, v in O.synthetic_state_dict("W1", seed=1).items()}
+for pre, nh, (B, ph, pw) in (("encoder_layer1.blocks.1.", 6, (16, 128, 128)), ("encoder_layer2.blocks.1.", 4, (16, 64, 64))):
+    P = [sd[pre + n].contiguous() for n in ops.NSTB_PARAM_NAMES][10:18]
+    z = torch.randn(B, ph * pw, 64, device="cuda")
+    c = torch.randn(B, (ph // 8) * (pw // 8), 64, device="cuda") * 0.5
+    da = torch.randn_like(z)
+    dz = torch.empty_like(z)
+    dctx = torch.zeros_like(c)
+    G = [torch.zeros_like(p) for p in P]
+    for shift in (0, 4):
+        print(f"attn_bwd nh={nh} shift={shift} B={B} {ph}x{pw}: simt "
+              f"{timeit(lambda: ops.attn_bwd(z, c, da, P, dz, dctx, G, ph, pw, nh, shift)):.3f} ms, tc "
+              f"{timeit(lambda: ops.attn_bwd_tc(z, c, da, P, dz, dctx, G, ph, pw, nh, shift)):.3f} ms", flush=True)

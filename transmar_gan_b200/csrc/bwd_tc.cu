@@ -21,62 +21,11 @@
 #include "common.cuh"
 #include "tc.cuh"
 #include <cuda_bf16.h>
+#include "bwd_common.cuh"
 
 namespace b200mar {
 
 B200MAR_DEFINE_TC_ERROR_GETTER(tc_error_bwd)
-
-// ------------------------------------------------------------------------------------------------
-// small helpers
-__device__ __forceinline__ float bf16_lo(uint32_t u) { return __uint_as_float(u << 16); }
-__device__ __forceinline__ float bf16_hi(uint32_t u) { return __uint_as_float(u & 0xFFFF0000u); }
-
-// Column sums over the 32 rows held by the lanes of a warp (one 64-vector per lane): after five
-// halving exchanges lane l holds the sums of columns 2l and 2l+1, which are added to s0 / s1.
-// `f(i)` yields element i of this lane's vector.
-template <int H>
-__device__ __forceinline__ void colsum_step(float* v, bool up, int mask) {
-#pragma unroll
-  for (int i = 0; i < H; ++i) {
-    const float send = up ? v[i] : v[i + H];
-    const float keep = up ? v[i + H] : v[i];
-    v[i] = keep + __shfl_xor_sync(0xffffffffu, send, mask);
-  }
-}
-template <class F>
-__device__ __forceinline__ void warp_colsum64(F f, int lane, float& s0, float& s1) {
-  float v[32];
-  {
-    const bool up = lane & 16;
-#pragma unroll
-    for (int i = 0; i < 32; ++i) {
-      const float lo = f(i), hi = f(i + 32);
-      v[i] = (up ? hi : lo) + __shfl_xor_sync(0xffffffffu, up ? lo : hi, 16);
-    }
-  }
-  colsum_step<16>(v, lane & 8, 8);
-  colsum_step<8>(v, lane & 4, 4);
-  colsum_step<4>(v, lane & 2, 2);
-  colsum_step<2>(v, lane & 1, 1);
-  s0 += v[0];
-  s1 += v[1];
-}
-
-// GELU(x) = x Phi(x) and its derivative Phi(x) + x phi(x); erf from Abramowitz & Stegun 7.1.26
-// (|error| <= 1.5e-7), the Gaussian shares the exponential of the erf.
-__device__ __forceinline__ void gelu_and_grad(float x, float& g, float& gp) {
-  const float z = fabsf(x) * 0.70710678118654752440f;
-  const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
-  float p = fmaf(1.061405429f, t, -1.453152027f);
-  p = fmaf(p, t, 1.421413741f);
-  p = fmaf(p, t, -0.284496736f);
-  p = fmaf(p, t, 0.254829592f);
-  const float e = tc::ex2_approx(-z * z * 1.4426950408889634f);     // exp(-x^2/2)
-  const float erf_abs = fmaf(-p * t, e, 1.0f);
-  const float cdf = fmaf(0.5f, copysignf(erf_abs, x), 0.5f);
-  g = x * cdf;
-  gp = fmaf(x * 0.39894228040143267794f, e, cdf);
-}
 
 // ================================================================================================
 // wgrad_tc_kernel
@@ -87,6 +36,8 @@ struct WgradParams {
   float* dbias;         // fp32 [cout] or null (cin == 64 only)
   long long n_tok;
   int cin, cout;
+  int ld, cin_valid;    // row stride of dw, input channels actually written
+  int hs, ps, hd, A;    // hs > 0: per-head packed [q|k|v] columns (see launch_wgrad)
 };
 
 // coalesced copy of a [128][C] bf16 row-major global tile into a chunk-major smem tile (rows >= valid
@@ -158,12 +109,17 @@ __global__ void __launch_bounds__(128) wgrad_tc_kernel(WgradParams p) {
     for (int c0 = 0; c0 < p.cout; c0 += 16) {
       float v[16];
       tc::tmem_ld16(tbase + lane_addr + c0, v);
-      if (ci < p.cin) {
+      const bool isw = ci < p.cin_valid, isb = ci == 64 && p.cin == 64 && p.dbias;
+      if (isw || isb) {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) atomicAdd(p.dw + (size_t)(c0 + i) * p.cin + ci, v[i]);
-      } else if (ci == 64 && p.dbias) {
-#pragma unroll
-        for (int i = 0; i < 16; ++i) atomicAdd(p.dbias + c0 + i, v[i]);
+        for (int i = 0; i < 16; ++i) {
+          int orow = c0 + i;
+          if (p.hs > 0) {
+            const int h = orow / p.hs, r = orow - h * p.hs, part = r / p.ps, d = r - part * p.ps;
+            orow = (part < 3 && d < p.hd) ? part * p.A + h * p.hd + d : -1;
+          }
+          if (orow >= 0) atomicAdd(isw ? p.dw + (size_t)orow * p.ld + ci : p.dbias + orow, v[i]);
+        }
       }
     }
   }
@@ -459,11 +415,12 @@ __global__ void __launch_bounds__(128 * kBwdWorkers, 1) mlp_bwd_tc_kernel(MlpBwd
   if (warp == 0) tc::tmem_dealloc<512>(*tmem_slot);
 }
 
-static int launch_wgrad(const uint16_t* in16, const uint16_t* g16, float* dw, float* dbias, long long n_tok,
-                        int cin, int cout, cudaStream_t st) {
+int launch_wgrad(const uint16_t* in16, const uint16_t* g16, float* dw, float* dbias, long long n_tok,
+                 int cin, int cout, int ld, int cin_valid, int hs, int ps, int hd, int A, cudaStream_t st) {
   if (n_tok <= 0 || (cin != 64 && cin != 128) || cout % 32 || cout < 64 || cout > 256) return -1;
   if (dbias && cin != 64) return -1;
-  WgradParams p{in16, g16, dw, dbias, n_tok, cin, cout};
+  if (cin_valid <= 0 || cin_valid > cin || ld < cin_valid) return -1;
+  WgradParams p{in16, g16, dw, dbias, n_tok, cin, cout, ld, cin_valid, hs, ps, hd, A};
   // >= 100 KB keeps residency at two CTAs per SM (each owns 256 TMEM columns)
   size_t smem = (size_t)cin * 256 + 2048 + (size_t)cout * 256;
   if (smem < 100 * 1024) smem = 100 * 1024;
@@ -484,7 +441,8 @@ static int launch_wgrad(const uint16_t* in16, const uint16_t* g16, float* dw, fl
 extern "C" int b200mar_wgrad_tc(const void* in16, const void* g16, float* dw, float* dbias, long long n_tok,
                                 int cin, int cout, void* stream) {
   using namespace b200mar;
-  return launch_wgrad((const uint16_t*)in16, (const uint16_t*)g16, dw, dbias, n_tok, cin, cout, (cudaStream_t)stream);
+  return launch_wgrad((const uint16_t*)in16, (const uint16_t*)g16, dw, dbias, n_tok, cin, cout, cin, cin, 0, 0, 0, 0,
+                      (cudaStream_t)stream);
 }
 
 extern "C" int b200mar_mlp_bwd_tc(const float* a, const float* dout, const float* fc1_w, const float* fc1_b,
@@ -511,7 +469,7 @@ extern "C" int b200mar_mlp_bwd_tc(const float* a, const float* dout, const float
   if (grid > sm_count()) grid = sm_count();
   mlp_bwd_tc_kernel<<<(int)grid, 128 * kBwdWorkers, smem, st>>>(p);
   B200MAR_CHECK(cudaGetLastError());
-  if (int rc = launch_wgrad(p.a16, p.dh16, d_fc1_w, d_fc1_b, n_tok, 64, 128, st)) return rc;   // dW1 [128][64], db1
-  if (int rc = launch_wgrad(p.g16, p.dy16, d_fc2_w, nullptr, n_tok, 128, 64, st)) return rc;  // dW2 [64][128]
+  if (int rc = launch_wgrad(p.a16, p.dh16, d_fc1_w, d_fc1_b, n_tok, 64, 128, 64, 64, 0, 0, 0, 0, st)) return rc;   // dW1 [128][64], db1
+  if (int rc = launch_wgrad(p.g16, p.dy16, d_fc2_w, nullptr, n_tok, 128, 64, 128, 128, 0, 0, 0, 0, st)) return rc;  // dW2 [64][128]
   return 0;
 }

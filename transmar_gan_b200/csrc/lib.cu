@@ -24,13 +24,14 @@ int tc_error_merge();
 int tc_error_bottleneck();
 int tc_error_cascade();
 int tc_error_bwd();
+int tc_error_attn_bwd();
 }  // namespace b200mar
 
 // 1 if any tensor-core kernel of this process hit its bounded mbarrier wait (descriptor-bug guard)
 extern "C" int b200mar_tc_error(void) {
   const int a = b200mar::tc_error_mlp(), b = b200mar::tc_error_probe(), c = b200mar::tc_error_attn(),
             d = b200mar::tc_error_merge(), e = b200mar::tc_error_bottleneck(),
-            f = b200mar::tc_error_cascade() | b200mar::tc_error_bwd();
+            f = b200mar::tc_error_cascade() | b200mar::tc_error_bwd() | b200mar::tc_error_attn_bwd();
   if (a < 0 || b < 0 || c < 0 || d < 0 || e < 0 || f < 0) return -1;
   return (a | b | c | d | e | f) ? 1 : 0;
 }

@@ -217,6 +217,21 @@ def attn_bwd(z: Tensor, ctx: Tensor, da: Tensor, params: List[Tensor], dz: Tenso
         *[_p(t) for t in grads], z.shape[0], ph, pw, nh, shift, _stream())
 
 
+@torch.library.custom_op(f"{_NS}::attn_bwd_tc", mutates_args=("dz", "dctx", "grads"))
+def attn_bwd_tc(z: Tensor, ctx: Tensor, da: Tensor, params: List[Tensor], dz: Tensor, dctx: Tensor,
+                grads: List[Tensor], ph: int, pw: int, nh: int, shift: int) -> None:
+    """attn_bwd on the tcgen05 tensor cores: the row kernel recomputes the forward and exports the bf16
+    operands of the weight gradients (window order) into a scratch buffer; a second row kernel forms
+    dz / dctx and two wgrad launches the qkv / proj weight gradients."""
+    _chk(z, ctx, da, dz, dctx, *params, *grads)
+    nwin = z.shape[0] * (ph // 8) * (pw // 8)
+    scratch = torch.empty(((nwin + 1) // 2) * 128 * 384, device=z.device, dtype=torch.bfloat16)
+    _call("attn_bwd_tc", _p(z), _p(ctx), _p(da), *[_p(t) for t in params], _p(dz), _p(dctx),
+          *[_p(t) for t in grads], scratch.data_ptr(), z.shape[0], ph, pw, nh, shift, _stream(),
+          meta=(z.shape[0], ph, pw, nh, shift))
+    profile.launches += 3                     # core + dx + two wgrad kernels behind one entry point
+
+
 # ------------------------------------------------------------------------------ MLP + LN2 + residual
 @torch.library.custom_op(f"{_NS}::mlp_fwd", mutates_args=())
 def mlp_fwd(a: Tensor, z: Optional[Tensor], fc1_w: Tensor, fc1_b: Tensor, fc2_w: Tensor,
@@ -545,7 +560,8 @@ class NSTBFunction(torch.autograd.Function):
         (mlp_bwd_tc if _PRECISION == "tf32" else mlp_bwd)(a, g, P[18:24], da, G[18:24])
         dz = torch.empty_like(z)
         dctx = torch.zeros_like(c)
-        attn_bwd(z, c, da, P[10:18], dz, dctx, G[10:18], ph, pw, nh, shift)
+        (attn_bwd_tc if _PRECISION == "tf32" else attn_bwd)(z, c, da, P[10:18], dz, dctx, G[10:18], ph, pw,
+                                                             nh, shift)
         du = torch.empty_like(u)
         ngram_ctx_bwd(u, dctx, P[2:10], du, G[2:10], nh)
         unigram_bwd(z, P[0], du, dz, G[0], G[1], ph, pw)
