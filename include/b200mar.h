@@ -32,7 +32,7 @@ extern "C" {
 #endif
 
 /* ABI version, bumped whenever a signature changes. */
-int b200mar_abi_version(void);
+int b200mar_abi_version(void);   /* 3 */
 /* Name of the last failing CUDA call of this thread (static string; never NULL). */
 const char* b200mar_last_error(void);
 /* 1 iff device `dev` is compute capability 10.x (B200); no kernels are launched. */
@@ -105,6 +105,15 @@ int b200mar_attn_tc_fwd(const float* z, const float* ctx,
                         const float* ln_w, const float* ln_b,
                         float* a, int B, int ph, int pw, int nh, int shift, int residual,
                         void* stream);
+/* Training forward: as b200mar_attn_tc_fwd(residual = 1) and, in addition, the pre-projection attention
+ * output O as bf16 [ceil(B*(ph/8)*(pw/8)/2)*128][64] in window order (o16) for b200mar_attn_bwd_tc.  */
+int b200mar_attn_tc_fwd_save(const float* z, const float* ctx,
+                        const float* qkv_w, const float* qkv_b,
+                        const float* proj_w, const float* proj_b,
+                        const float* logit_scale, const float* bias_table,
+                        const float* ln_w, const float* ln_b,
+                        float* a, void* o16, int B, int ph, int pw, int nh, int shift,
+                        void* stream);
 /* residual = 1: a = z + LN1(attn) as above.  residual = 0: a = LN1(attn) only - the consumer
  * (b200mar_mlp_tc_fwd with a_is_delta = 1) adds z, which it reads anyway.                   */
 /* dz = da + scatter(dX) (overwrites dz); dctx += per-source-window sums of dX (dctx must be
@@ -120,7 +129,8 @@ int b200mar_attn_bwd(const float* z, const float* ctx, const float* da,
                      int B, int ph, int pw, int nh, int shift, void* stream);
 /* attn_bwd on the tcgen05 tensor cores (fp16 / bf16 operands, fp32 accumulate): same contract; `scratch`
  * is a caller-owned device buffer of ceil(B*(ph/8)*(pw/8)/2) * 128 * 768 bytes (window-order bf16
- * operands of the weight gradients: X, O, dY, per-head packed d[q|k|v]).                       */
+ * operands of the weight gradients: X, O, dY, per-head packed d[q|k|v]).  o16_saved: the O tensor written
+ * by b200mar_attn_tc_fwd_save for the same inputs (skips the recomputation pass), or NULL.      */
 int b200mar_attn_bwd_tc(const float* z, const float* ctx, const float* da,
                      const float* qkv_w, const float* qkv_b,
                      const float* proj_w, const float* proj_b,
@@ -128,7 +138,7 @@ int b200mar_attn_bwd_tc(const float* z, const float* ctx, const float* da,
                      const float* ln_w, const float* ln_b,
                      float* dz, float* dctx,
                      float* d_qkv_w, float* d_qkv_b, float* d_proj_w, float* d_proj_b,
-                     float* d_logit_scale, float* d_bias_table, float* d_ln_w, float* d_ln_b, void* scratch,
+                     float* d_logit_scale, float* d_bias_table, float* d_ln_w, float* d_ln_b, void* scratch, const void* o16_saved,
                      int B, int ph, int pw, int nh, int shift, void* stream);
 
 /* ---- a8(second half)+a9: `x + norm2(ffn(x))` and the within-stage residual

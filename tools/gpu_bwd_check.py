@@ -85,7 +85,13 @@ for kind in ("W1", "W2"):
                     fn(z, c, da, P, dz, dctx, G, ph, pw, nh, shift)
                     outs.append((dz, dctx, G))
                 torch.cuda.synchronize()
+                a_s, o16 = ops.attn_tc_fwd_save(z, c, *P, ph, pw, nh, shift)
+                dz = torch.empty_like(z); dctx = torch.zeros_like(c); G = [torch.zeros_like(p) for p in P]
+                ops.attn_bwd_tc(z, c, da, P, dz, dctx, G, ph, pw, nh, shift, o16)
                 (dz0, dc0, G0), (dz1, dc1, G1) = outs
+                a_ref = ops.attn_tc_fwd(z, c, *P, ph, pw, nh, shift)
+                print(f"   saved-O path: fwd_save vs fwd max {(a_s - a_ref).abs().max().item():.1e}; dz-da rel {rel(dz - da, dz0 - da):.2e} "
+                      f"dctx {rel(dctx, dc0):.2e} | " + " ".join(f"{n} {rel(x, y):.2e}" for n, x, y in zip(names, G, G0)))
                 print(f"{kind} attn_bwd nh={nh} B={B} {ph}x{pw} shift={shift}: dz-da rel {rel(dz1 - da, dz0 - da):.2e} "
                       f"dctx {rel(dc1, dc0):.2e} | " + " ".join(f"{n} {rel(x, y):.2e}" for n, x, y in zip(names, G1, G0)),
                       "tc_error", ops.tc_error(), flush=True)
@@ -101,4 +107,6 @@ for pre, nh, (B, ph, pw) in (("encoder_layer1.blocks.1.", 6, (16, 128, 128)), ("
     for shift in (0, 4):
         print(f"attn_bwd nh={nh} shift={shift} B={B} {ph}x{pw}: simt "
               f"{timeit(lambda: ops.attn_bwd(z, c, da, P, dz, dctx, G, ph, pw, nh, shift)):.3f} ms, tc "
-              f"{timeit(lambda: ops.attn_bwd_tc(z, c, da, P, dz, dctx, G, ph, pw, nh, shift)):.3f} ms", flush=True)
+              f"{timeit(lambda: ops.attn_bwd_tc(z, c, da, P, dz, dctx, G, ph, pw, nh, shift)):.3f} ms, tc with saved O "
+              f"{timeit(lambda: ops.attn_bwd_tc(z, c, da, P, dz, dctx, G, ph, pw, nh, shift, ops.attn_tc_fwd_save(z, c, *P, ph, pw, nh, shift)[1])):.3f} ms (incl. fwd), fwd_save "
+              f"{timeit(lambda: ops.attn_tc_fwd_save(z, c, *P, ph, pw, nh, shift)):.3f} ms", flush=True)

@@ -30,6 +30,20 @@ namespace b200mar {
 
 B200MAR_DEFINE_TC_ERROR_GETTER(tc_error_attn_bwd)
 
+// Optional phase profile (compile with -DB200MAR_ABWD_PROF): cycles of one thread (block 0, thread 32)
+// between successive PROF(i) marks, summed per phase i; read with b200mar_abwd_prof().
+#ifdef B200MAR_ABWD_PROF
+__device__ unsigned long long g_abwd_prof[32];
+#define PROF_DECL __shared__ unsigned long long s_prof[32]; if (threadIdx.x < 32) s_prof[threadIdx.x] = 0; __syncthreads(); \
+  long long prof_t = clock64(); const bool prof_on = blockIdx.x == 0 && threadIdx.x == 32;
+#define PROF(i) do { if (prof_on) { const long long t_ = clock64(); s_prof[i] += (unsigned long long)(t_ - prof_t); prof_t = clock64(); } } while (0)
+#define PROF_FLUSH do { if (prof_on) for (int i_ = 0; i_ < 32; ++i_) g_abwd_prof[i_] += s_prof[i_]; } while (0)
+#else
+#define PROF_DECL
+#define PROF(i)
+#define PROF_FLUSH
+#endif
+
 constexpr float kLog2eB = 1.4426950408889634f;
 constexpr int kABWorkers = 2;
 constexpr int kBiasLdB = 228;
@@ -38,6 +52,7 @@ struct AttnBwdTcParams {
   AttnParams a;          // inputs, da, d_logit_scale, d_bias_table, d_ln_w, d_ln_b
   uint16_t* x16;         // bf16 [ntile*128][64]   X = z + ctx, window order
   uint16_t* o16;         // bf16 [ntile*128][64]   attention output before the projection (cols >= A zero)
+  const uint16_t* o16_saved;   // the same, saved by attn_tc_fwd_save: pass 1 is skipped when given
   uint16_t* dy16;        // bf16 [ntile*128][64]   gradient of the projection output
   uint16_t* dqkv16;      // bf16 [ntile*128][192]  per-head packed d[q|k|v]
 };
@@ -59,8 +74,8 @@ struct AttnBwdSmem {                           // BYTE offsets
   static constexpr int oScaleRaw = oScale + 32;         // fp32 [8]: scale_h
   static constexpr int oDScale = oScaleRaw + 32;        // fp32 [8]: accumulators of sum dS.cos
   static constexpr int oBias = oDScale + 32;   // fp32 [6][228] bias * log2e
-  static constexpr int oDBias = oBias + 6 * kBiasLdB * 4;   // fp32 [6][228] accumulators
-  static constexpr int oBar = oDBias + 6 * kBiasLdB * 4;    // workers x 4 mbarriers + tmem slot
+  static constexpr int oDBias = oBias + 6 * kBiasLdB * 4;   // fp32 [2 workers x 2 windows][6][228] accumulators
+  static constexpr int oBar = oDBias + 2 * kABWorkers * 6 * kBiasLdB * 4;    // workers x 4 mbarriers + tmem slot
   static constexpr int oWork = ((oBar + kABWorkers * 32 + 16 + 127) / 128) * 128;
   static constexpr int wX = 0;                 // fp16 [128][64]  R = 128
   static constexpr int wQ = wX + 16384;        // fp16 [128][32]  R = 128   Q' = [q|0] / [0|q]
@@ -171,8 +186,8 @@ __global__ void __launch_bounds__(128 * kABWorkers, 1) attn_bwd_core_kernel(Attn
   for (int i = tid; i < 6 * kBiasLdB; i += 128 * kABWorkers) {
     const int h = i / kBiasLdB, e = i - h * kBiasLdB;
     sBias[i] = (h < NH && e < 225) ? p.bias_table[e * NH + h] * kLog2eB : 0.f;
-    sDBias[i] = 0.f;
   }
+  for (int i = tid; i < 2 * kABWorkers * 6 * kBiasLdB; i += 128 * kABWorkers) sDBias[i] = 0.f;
   if (tid == 0) {
     for (int i = 0; i < 4 * kABWorkers; ++i) tc::mbar_init(bars + i, 1);
     tc::fence_barrier_init();
@@ -216,7 +231,9 @@ __global__ void __launch_bounds__(128 * kABWorkers, 1) attn_bwd_core_kernel(Attn
     }
   };
 
+  PROF_DECL
   for (int tile = blockIdx.x * kABWorkers + wk; tile < ntile; tile += gridDim.x * kABWorkers) {
+    PROF(0);
     const int win = tile * 2 + wsel;
     const bool wvalid = win < nwin;
     const size_t erow = (size_t)tile * 128 + row;            // row of the window-order exports
@@ -351,7 +368,21 @@ __global__ void __launch_bounds__(128 * kABWorkers, 1) attn_bwd_core_kernel(Attn
       for (int c = 0; c < 64; ++c) s[c] *= inv;
     };
 
+    PROF(1);                                                 // X tile, masks
     // ================================================================ pass 1: O, Y, dY, dO
+    if (pp.o16_saved) {
+      // ---- O row as saved by the forward -> packed bf16 A operand of Y = O Wp^T
+      uint32_t op[32];
+      const uint4* src = reinterpret_cast<const uint4*>(pp.o16_saved + erow * 64);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (wvalid) v = __ldg(src + i);
+        op[4 * i] = v.x; op[4 * i + 1] = v.y; op[4 * i + 2] = v.z; op[4 * i + 3] = v.w;
+      }
+      tc::tmem_st32(tl + cOp, reinterpret_cast<const float(&)[32]>(op));
+      tc::tmem_wait_st();
+    } else {
     float o[64];
 #pragma unroll
     for (int i = 0; i < 64; ++i) o[i] = 0.f;
@@ -405,6 +436,7 @@ __global__ void __launch_bounds__(128 * kABWorkers, 1) attn_bwd_core_kernel(Attn
         for (int i = 0; i < 8; ++i) dst[i] = make_uint4(op[4 * i], op[4 * i + 1], op[4 * i + 2], op[4 * i + 3]);
       }
       tc::tmem_wait_st();
+    }
     }
     tc::tc_fence_before();
     tc::worker_sync(1 + wk);
@@ -481,11 +513,13 @@ __global__ void __launch_bounds__(128 * kABWorkers, 1) attn_bwd_core_kernel(Attn
       tc::tmem_wait_st();
     }
 
+    PROF(2);                                                 // O / Y / LN backward / dO
     // ================================================================ pass 2: per-head gradients
 #pragma unroll 1
     for (int h = 0; h < NH; ++h) {
       float qn[16], kn[16], vv[16], iq, ik; bool qok, kok;
       head_qkv(h, qn, kn, vv, iq, ik, qok, kok);
+      PROF(3);                                               // [q|k|v]_h MMA + normalise + operand tiles
       {
         // dO_h of this row (bf16 pairs at packed column h*HD/2) -> [dO_h|0] / [0|dO_h] A operand and dO^T tile
         float dpk[16];
@@ -511,9 +545,11 @@ __global__ void __launch_bounds__(128 * kABWorkers, 1) attn_bwd_core_kernel(Attn
         *reinterpret_cast<uint4*>(sKb + (2 * wsel + 1) * 1024 + lrow * 16) = make_uint4(kb[4], kb[5], kb[6], kb[7]);
         tc::tmem_wait_st();
       }
+      PROF(4);                                               // dO_h operands
       tc::fence_async_smem();
       tc::tc_fence_before();
       tc::worker_sync(1 + wk);
+      PROF(5);                                               // sync
       // ---- S = Q'K'^T and dP = dO_h V^T
       issue([&] {
         tc::mma_f16(tbase + cS, dQ, dK, kIS, 0u);
@@ -524,10 +560,12 @@ __global__ void __launch_bounds__(128 * kABWorkers, 1) attn_bwd_core_kernel(Attn
       });
       tc::mbar_wait(barS, phS, &g_tc_error); phS ^= 1;
       tc::tc_fence_after();
+      PROF(6);                                               // S + dP MMAs
       {
         float s[64], dp[64];
         tc::tmem_ld64(tl + cS, s);
         softmax_row(h, s);                                  // s = P
+        PROF(7);                                             // softmax
         tc::tmem_ld64(tl + cP2, dp);
         float r4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
@@ -539,12 +577,10 @@ __global__ void __launch_bounds__(128 * kABWorkers, 1) attn_bwd_core_kernel(Attn
           *reinterpret_cast<uint4*>(sPT + (wsel * 8 + j) * 1024 + lrow * 16) =
               make_uint4(tc::pack_bf16(s[8 * j], s[8 * j + 1]), tc::pack_bf16(s[8 * j + 2], s[8 * j + 3]),
                          tc::pack_bf16(s[8 * j + 4], s[8 * j + 5]), tc::pack_bf16(s[8 * j + 6], s[8 * j + 7]));
-        float* dbias = sDBias + h * kBiasLdB + bias_base;
+        PROF(8);                                             // dP load, rowdot, P^T tile
 #pragma unroll
-        for (int c = 0; c < 64; ++c) {
-          dp[c] = s[c] * (dp[c] - rowdot);                  // dS
-          if (wvalid) atomicAdd(dbias - ((c >> 3) * 15 + (c & 7)), dp[c]);
-        }
+        for (int c = 0; c < 64; ++c) dp[c] = wvalid ? s[c] * (dp[c] - rowdot) : 0.f;   // dS
+        PROF(9);                                             // dS + bias-table scatter
         uint32_t ds[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) ds[i] = tc::pack_bf16(dp[2 * i], dp[2 * i + 1]);
@@ -555,9 +591,11 @@ __global__ void __launch_bounds__(128 * kABWorkers, 1) attn_bwd_core_kernel(Attn
               make_uint4(ds[4 * j], ds[4 * j + 1], ds[4 * j + 2], ds[4 * j + 3]);
         tc::tmem_wait_st();
       }
+      PROF(10);                                              // dS operands
       tc::fence_async_smem();
       tc::tc_fence_before();
       tc::worker_sync(1 + wk);
+      PROF(11);                                              // sync
       // ---- dV = P^T dO_h ; dqn = dS kn ; dkn = dS^T qn   (tokens of the window pair as K)
       issue([&] {
 #pragma unroll
@@ -568,8 +606,38 @@ __global__ void __launch_bounds__(128 * kABWorkers, 1) attn_bwd_core_kernel(Attn
         for (int ks = 0; ks < 4; ++ks) tc::mma_f16(tbase + cP2 + 32, dSTmn + ks * 16, dQTmn + ks * 16, kB32mm, ks > 0);
         tc::mma_commit(barO);
       });
+      // ---- relative-position-bias gradient of this head and tile, in the shadow of the MMAs: the table
+      //      entry of (query r, key c) depends on (ri - ci, rj - cj) only, so thread (window w, a, b) sums
+      //      the 64 entries dS[(w, (ci+a)%8, (cj+b)%8)][(ci, cj)] of the dS tile - they belong to the four
+      //      entries (a or a-8, b or b-8) - into its worker/window-private copy of the table: no atomics.
+      {
+        const int a8 = lrow >> 3, b8 = lrow & 7;
+        const unsigned char* base = sST + wsel * 8192;
+        float acc00 = 0.f, acc01 = 0.f, acc10 = 0.f, acc11 = 0.f;
+#pragma unroll
+        for (int ci = 0; ci < 8; ++ci) {
+          const int ri = (ci + a8) & 7;
+          float t0 = 0.f, t1 = 0.f;
+#pragma unroll
+          for (int cjs = 0; cjs < 8; ++cjs) {
+            const int cj = (cjs + 2 * a8) & 7;     // skewed per a: the four a-groups of a warp hit distinct banks
+            const int rj = (cj + b8) & 7;
+            const float v = __uint_as_float((uint32_t)(*reinterpret_cast<const unsigned short*>(
+                                base + ci * 1024 + (ri * 8 + rj) * 16 + cj * 2)) << 16);
+            if (cj + b8 >= 8) t1 += v; else t0 += v;
+          }
+          if (ci + a8 >= 8) { acc10 += t0; acc11 += t1; } else { acc00 += t0; acc01 += t1; }
+        }
+        float* tab = sDBias + ((wk * 2 + wsel) * 6 + h) * kBiasLdB;
+        tab[(a8 + 7) * 15 + b8 + 7] += acc00;
+        if (b8 > 0) tab[(a8 + 7) * 15 + b8 - 1] += acc01;
+        if (a8 > 0) tab[(a8 - 1) * 15 + b8 + 7] += acc10;
+        if (a8 > 0 && b8 > 0) tab[(a8 - 1) * 15 + b8 - 1] += acc11;
+      }
+      PROF(15);                                              // bias-table gradient
       tc::mbar_wait(barO, phO, &g_tc_error); phO ^= 1;
       tc::tc_fence_after();
+      PROF(12);                                              // dV / dqn / dkn MMAs
       {
         float dqn[16], dkn[16], dv[16];
         tc::tmem_ld16(tl + cP2 + wsel * 16, dqn);
@@ -607,10 +675,13 @@ __global__ void __launch_bounds__(128 * kABWorkers, 1) attn_bwd_core_kernel(Attn
                                 tc::pack_bf16(outv[8 * i + 4], outv[8 * i + 5]), tc::pack_bf16(outv[8 * i + 6], outv[8 * i + 7]));
         }
       }
+      PROF(13);                                              // normalize backward + export
       tc::tc_fence_before();
       tc::worker_sync(1 + wk);       // dV / dqn / dkn are read: the accumulators and tiles may be reused
+      PROF(14);                                              // sync
     }
   }
+  PROF_FLUSH;
 
   // ---- flush the CTA's parameter-gradient accumulators
   atomicAdd(p.d_ln_w + 2 * lane, dgam0); atomicAdd(p.d_ln_w + 2 * lane + 1, dgam1);
@@ -620,7 +691,10 @@ __global__ void __launch_bounds__(128 * kABWorkers, 1) attn_bwd_core_kernel(Attn
   if (tid < NH && p.logit_scale[tid] <= kLogitMax) atomicAdd(p.d_logit_scale + tid, sDScale[tid] * sScaleRaw[tid]);
   for (int i = tid; i < NH * 225; i += 128 * kABWorkers) {
     const int h = i / 225, e = i - h * 225;
-    atomicAdd(p.d_bias_table + e * NH + h, sDBias[h * kBiasLdB + e]);
+    float v = 0.f;
+#pragma unroll
+    for (int cpy = 0; cpy < 2 * kABWorkers; ++cpy) v += sDBias[(cpy * 6 + h) * kBiasLdB + e];
+    atomicAdd(p.d_bias_table + e * NH + h, v);
   }
   if (warp == 0) tc::tmem_dealloc<512>(*tmem_slot);
 }
@@ -760,6 +834,17 @@ __global__ void __launch_bounds__(128 * kDxWorkers, 1) attn_bwd_dx_kernel(AttnBw
   if (warp == 0) tc::tmem_dealloc<512>(*tmem_slot);
 }
 
+#ifdef B200MAR_ABWD_PROF
+}  // namespace b200mar
+extern "C" int b200mar_abwd_prof(unsigned long long* out32, int reset) {
+  unsigned long long z[32] = {0};
+  if (cudaMemcpyFromSymbol(out32, b200mar::g_abwd_prof, sizeof(z)) != cudaSuccess) return -1;
+  if (reset && cudaMemcpyToSymbol(b200mar::g_abwd_prof, z, sizeof(z)) != cudaSuccess) return -1;
+  return 0;
+}
+namespace b200mar {
+#endif
+
 template <int NH>
 static int launch_attn_bwd_tc(const AttnBwdTcParams& pp, cudaStream_t st) {
   const AttnParams& p = pp.a;
@@ -784,7 +869,7 @@ static int launch_attn_bwd_tc(const AttnBwdTcParams& pp, cudaStream_t st) {
   B200MAR_CHECK(cudaGetLastError());
   const long long n_rows = (long long)nwin * 64;
   if (int rc = launch_wgrad(pp.x16, pp.dqkv16, p.d_qkv_w, p.d_qkv_b, n_rows, 64, 192, 64, 64, HS, PS, HD, A, st)) return rc;
-  if (int rc = launch_wgrad(pp.o16, pp.dy16, p.d_proj_w, p.d_proj_b, n_rows, 64, 64, A, A, 0, 0, 0, 0, st)) return rc;
+  if (int rc = launch_wgrad(pp.o16_saved ? pp.o16_saved : pp.o16, pp.dy16, p.d_proj_w, p.d_proj_b, n_rows, 64, 64, A, A, 0, 0, 0, 0, st)) return rc;
   return 0;
 }
 
@@ -797,7 +882,8 @@ extern "C" int b200mar_attn_bwd_tc(const float* z, const float* ctx, const float
                                    float* dz, float* dctx, float* d_qkv_w, float* d_qkv_b,
                                    float* d_proj_w, float* d_proj_b, float* d_logit_scale,
                                    float* d_bias_table, float* d_ln_w, float* d_ln_b, void* scratch,
-                                   int B, int ph, int pw, int nh, int shift, void* stream) {
+                                   const void* o16_saved, int B, int ph, int pw, int nh, int shift,
+                                   void* stream) {
   using namespace b200mar;
   if (ph % kWin || pw % kWin || ph < kWin || pw < kWin || (shift != 0 && shift != kShift) || !scratch) return -1;
   if ((long long)B * ph * pw >= (1ll << 31)) return -1;
@@ -812,6 +898,7 @@ extern "C" int b200mar_attn_bwd_tc(const float* z, const float* ctx, const float
   const long long nwin = (long long)B * (ph / kWin) * (pw / kWin);
   const long long rows = ((nwin + 1) / 2) * 128;      // scratch: rows * 384 bf16
   uint16_t* s = (uint16_t*)scratch;
+  pp.o16_saved = (const uint16_t*)o16_saved;
   pp.x16 = s; pp.o16 = s + rows * 64; pp.dy16 = s + rows * 128; pp.dqkv16 = s + rows * 192;
   cudaStream_t st = (cudaStream_t)stream;
   if (nh == 6) return launch_attn_bwd_tc<6>(pp, st);

@@ -18,6 +18,8 @@ struct AttnParams {
   const float* ln_w;         // [64]
   const float* ln_b;         // [64]
   float* a;                  // fwd out: z + LN1(attn)
+  unsigned short* o16;       // attn_tc fwd (training): bf16 [ntile*128][64] pre-projection attention output,
+                             // window order, saved for attn_bwd_tc (null: not written)
   // backward only
   const float* da;
   float* dz;

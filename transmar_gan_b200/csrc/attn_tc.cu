@@ -107,7 +107,7 @@ constexpr uint32_t kTQ = 0;
 // RESID = true : a = z + LN1(attn)            (the op's standalone contract)
 // RESID = false: a = LN1(attn) only; the consumer (mlp_tc with a_is_delta) adds z, which it reads
 //                anyway, so this kernel never re-reads z for the residual.
-template <int NH, bool RESID>
+template <int NH, bool RESID, bool SAVEO>
 __global__ void __launch_bounds__(128 * Cfg<NH>::kWorkers, 1)
 attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_constant__ CUtensorMap mapA,
                    AttnParams p) {
@@ -561,6 +561,13 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
 #pragma unroll
       for (int i = 0; i < 64; ++i) ot[i] = tc::round_tf32(o[i]);
       tc::tmem_st64(tbase + lane_addr + kTQ, ot);
+      if (SAVEO && wvalid) {                             // bf16 copy for the backward (window order)
+        uint4* dst = reinterpret_cast<uint4*>(p.o16 + ((size_t)tile * 128 + row) * 64);
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          dst[i] = make_uint4(tc::pack_bf16(ot[8 * i], ot[8 * i + 1]), tc::pack_bf16(ot[8 * i + 2], ot[8 * i + 3]),
+                              tc::pack_bf16(ot[8 * i + 4], ot[8 * i + 5]), tc::pack_bf16(ot[8 * i + 6], ot[8 * i + 7]));
+      }
       tc::tmem_wait_st();
     }
     tc::tc_fence_before();
@@ -656,13 +663,13 @@ extern "C" int b200mar_attn_prof(unsigned long long* out32, int reset) {
 namespace b200mar {
 #endif
 
-template <int NH, bool RESID>
+template <int NH, bool RESID, bool SAVEO = false>
 static int launch_attn_tc_fwd(const AttnParams& p, cudaStream_t st) {
   constexpr int kWorkers = Cfg<NH>::kWorkers;
   const size_t smem = AttnTcSmem<kWorkers>::kBytes;
   static bool configured = false;
   if (!configured) {
-    B200MAR_CHECK(cudaFuncSetAttribute(attn_tc_fwd_kernel<NH, RESID>,
+    B200MAR_CHECK(cudaFuncSetAttribute(attn_tc_fwd_kernel<NH, RESID, SAVEO>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured = true;
   }
@@ -673,7 +680,7 @@ static int launch_attn_tc_fwd(const AttnParams& p, cudaStream_t st) {
   CUtensorMap mZ, mA;
   if (int rc = tma::encode_windows(&mZ, p.z, p.B, p.ph, p.pw)) return rc;
   if (int rc = tma::encode_windows(&mA, p.a, p.B, p.ph, p.pw)) return rc;
-  attn_tc_fwd_kernel<NH, RESID><<<grid, 128 * kWorkers, smem, st>>>(mZ, mA, p);
+  attn_tc_fwd_kernel<NH, RESID, SAVEO><<<grid, 128 * kWorkers, smem, st>>>(mZ, mA, p);
   B200MAR_CHECK(cudaGetLastError());
   return 0;
 }
@@ -695,5 +702,26 @@ extern "C" int b200mar_attn_tc_fwd(const float* z, const float* ctx, const float
   cudaStream_t st = (cudaStream_t)stream;
   if (nh == 6) return residual ? launch_attn_tc_fwd<6, true>(p, st) : launch_attn_tc_fwd<6, false>(p, st);
   if (nh == 4) return residual ? launch_attn_tc_fwd<4, true>(p, st) : launch_attn_tc_fwd<4, false>(p, st);
+  return -1;
+}
+
+// Training forward: a = z + LN1(attn) as b200mar_attn_tc_fwd(residual = 1) and, in addition, the
+// pre-projection attention output O as bf16 [ceil(nwin/2)*128][64] in window order (o16), which
+// b200mar_attn_bwd_tc consumes instead of recomputing it.
+extern "C" int b200mar_attn_tc_fwd_save(const float* z, const float* ctx, const float* qkv_w,
+                                        const float* qkv_b, const float* proj_w, const float* proj_b,
+                                        const float* logit_scale, const float* bias_table,
+                                        const float* ln_w, const float* ln_b, float* a, void* o16, int B,
+                                        int ph, int pw, int nh, int shift, void* stream) {
+  using namespace b200mar;
+  if (ph % kWin || pw % kWin || ph < kWin || pw < kWin || (shift != 0 && shift != kShift) || !o16) return -1;
+  if ((long long)B * ph * pw >= (1ll << 31)) return -1;
+  AttnParams p{};
+  p.z = z; p.ctx = ctx; p.qkv_w = qkv_w; p.qkv_b = qkv_b; p.proj_w = proj_w; p.proj_b = proj_b;
+  p.logit_scale = logit_scale; p.bias_table = bias_table; p.ln_w = ln_w; p.ln_b = ln_b;
+  p.a = a; p.o16 = (unsigned short*)o16; p.B = B; p.ph = ph; p.pw = pw; p.shift = shift;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (nh == 6) return launch_attn_tc_fwd<6, true, true>(p, st);
+  if (nh == 4) return launch_attn_tc_fwd<4, true, true>(p, st);
   return -1;
 }

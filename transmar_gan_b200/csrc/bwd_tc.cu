@@ -22,6 +22,7 @@
 #include "tc.cuh"
 #include <cuda_bf16.h>
 #include "bwd_common.cuh"
+#include "tma.cuh"
 
 namespace b200mar {
 
@@ -40,70 +41,73 @@ struct WgradParams {
   int hs, ps, hd, A;    // hs > 0: per-head packed [q|k|v] columns (see launch_wgrad)
 };
 
-// coalesced copy of a [128][C] bf16 row-major global tile into a chunk-major smem tile (rows >= valid
-// are zero-filled): lane = (row%8, chunk%4) -> 64 contiguous bytes per row in global memory, 128
-// contiguous bytes per chunk in shared memory.
-__device__ __forceinline__ void load_tile16(unsigned char* sT, const uint16_t* gsrc, long long tok0,
-                                            int valid, int C, int warp, int lane) {
-  const int r8 = lane & 7, q4 = lane >> 3;
-  const int nitems = 16 * (C >> 5);                  // 16 row groups x C/32 chunk quads
-#pragma unroll 4
-  for (int it = warp; it < nitems; it += 4) {
-    const int row = (it & 15) * 8 + r8, chunk = (it >> 4) * 4 + q4;
-    uint4 v = make_uint4(0u, 0u, 0u, 0u);
-    if (row < valid) v = __ldg(reinterpret_cast<const uint4*>(gsrc + (size_t)(tok0 + row) * C + chunk * 8));
-    *reinterpret_cast<uint4*>(sT + chunk * 2048 + row * 16) = v;
-  }
-}
+constexpr int kWgStages = 3;
 
-__global__ void __launch_bounds__(128) wgrad_tc_kernel(WgradParams p) {
+// One CTA per SM: the operand tiles arrive by TMA (3-D tensor maps that deliver a row-major bf16 matrix
+// chunk-major, tma.cuh) through a 3-stage ring; one elected thread is producer and MMA issuer; the partial
+// dW lives in TMEM until the CTA's last tile and is flushed with coalesced atomics.
+__global__ void __launch_bounds__(128) wgrad_tc_kernel(const __grid_constant__ CUtensorMap mapIn,
+                                                       const __grid_constant__ CUtensorMap mapG, WgradParams p) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  __shared__ uint64_t bar;
+  __shared__ uint64_t full[kWgStages], empty[kWgStages], done;
   __shared__ uint32_t slot;
-  unsigned char* sIN = smem_raw;                     // [128][cin]   chunk-major bf16
-  unsigned char* sOnes = sIN + p.cin * 256;          // [128][8]     one more chunk: ones for valid rows
-  unsigned char* sG = sOnes + 2048;                  // [128][cout]
   const int tid = threadIdx.x, lane = tid & 31;
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
-
-  if (tid == 0) { tc::mbar_init(&bar, 1); tc::fence_barrier_init(); }
+  // stage = [128][cin] IN tile | [128][8] ones (lane 64 of the accumulator = column sums of G) | [128][cout] G tile
+  const uint32_t in_bytes = p.cin * 256, g_bytes = p.cout * 256, stage_bytes = in_bytes + 2048 + g_bytes;
+  for (int s = 0; s < kWgStages; ++s)
+    *reinterpret_cast<uint4*>(smem_raw + s * stage_bytes + in_bytes + tid * 16) =
+        make_uint4(0x3F803F80u, 0x3F803F80u, 0x3F803F80u, 0x3F803F80u);
+  if (tid == 0) {
+    for (int s = 0; s < kWgStages; ++s) { tc::mbar_init(full + s, 1); tc::mbar_init(empty + s, 1); }
+    tc::mbar_init(&done, 1);
+    tc::fence_barrier_init();
+    tma::prefetch_desc(&mapIn); tma::prefetch_desc(&mapG);
+  }
   if (warp == 0) tc::tmem_alloc<256>(&slot);
+  tc::fence_async_smem();
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tbase = slot;
-  const uint32_t idesc = tc::idesc_bf16(128, p.cout, true, true);
-  const uint64_t dA = tc::desc_mnmajor16(tc::smem_u32(sIN), 128),
-                 dB = tc::desc_mnmajor16(tc::smem_u32(sG), 128);
   const long long ntile = (p.n_tok + 127) / 128;
-  uint32_t ph = 0, first = 1;
-  for (long long tile = blockIdx.x; tile < ntile; tile += gridDim.x) {
-    const long long tok0 = tile * 128;
-    const int valid = (int)((p.n_tok - tok0) < 128 ? (p.n_tok - tok0) : 128);
-    load_tile16(sIN, p.in, tok0, valid, p.cin, warp, lane);
-    load_tile16(sG, p.g, tok0, valid, p.cout, warp, lane);
-    {
-      const uint32_t o = tid < valid ? 0x3F803F80u : 0u;   // bf16 1.0 pairs
-      *reinterpret_cast<uint4*>(sOnes + tid * 16) = make_uint4(o, o, o, o);
-    }
-    tc::fence_async_smem();
-    __syncthreads();
-    if (warp == 0) {
-      tc::tc_fence_after();
-      if (tc::elect_one()) {
+  const long long my = (ntile - blockIdx.x + gridDim.x - 1) / gridDim.x;     // tiles of this CTA
+  if (warp == 0) {
+    if (tc::elect_one()) {
+      const uint32_t idesc = tc::idesc_bf16(128, p.cout, true, true);
+      auto load = [&](long long i) {
+        const int s = (int)(i % kWgStages);
+        unsigned char* st = smem_raw + s * stage_bytes;
+        const int r0 = (int)((blockIdx.x + i * gridDim.x) * 128);
+        tma::mbar_expect_tx(full + s, in_bytes + g_bytes);
+        tma::load_3d(&mapIn, full + s, st, 0, r0, 0);
+        tma::load_3d(&mapG, full + s, st + in_bytes + 2048, 0, r0, 0);
+      };
+      for (long long i = 0; i < kWgStages && i < my; ++i) load(i);
+      for (long long i = 0; i < my; ++i) {
+        const int s = (int)(i % kWgStages);
+        const uint32_t par = (uint32_t)((i / kWgStages) & 1);
+        tc::mbar_wait(full + s, par, &g_tc_error);
+        tc::tc_fence_after();
+        unsigned char* st = smem_raw + s * stage_bytes;
+        const uint64_t dA = tc::desc_mnmajor16(tc::smem_u32(st), 128),
+                       dB = tc::desc_mnmajor16(tc::smem_u32(st + in_bytes + 2048), 128);
 #pragma unroll
-        for (int ks = 0; ks < 8; ++ks)
-          tc::mma_f16(tbase, dA + ks * 16, dB + ks * 16, idesc, (first == 0u || ks > 0) ? 1u : 0u);
-        tc::mma_commit(&bar);
+        for (int ks = 0; ks < 8; ++ks) tc::mma_f16(tbase, dA + ks * 16, dB + ks * 16, idesc, (i > 0 || ks > 0) ? 1u : 0u);
+        tc::mma_commit(empty + s);
+        if (i + kWgStages < my) {                    // refill this stage once its MMAs have read it
+          tc::mbar_wait(empty + s, par, &g_tc_error);
+          load(i + kWgStages);
+        }
       }
-      __syncwarp();
+      tc::mma_commit(&done);
     }
-    first = 0;
-    tc::mbar_wait(&bar, ph, &g_tc_error); ph ^= 1;    // the tiles may be overwritten after this
-    tc::tc_fence_after();
+    __syncwarp();
   }
+  tc::mbar_wait(&done, 0, &g_tc_error);
+  tc::tc_fence_after();
   // ---- flush: lane = input channel, columns = output channels
-  if (first == 0u) {
+  if (my > 0) {
     const int ci = warp * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
     for (int c0 = 0; c0 < p.cout; c0 += 16) {
@@ -421,17 +425,20 @@ int launch_wgrad(const uint16_t* in16, const uint16_t* g16, float* dw, float* db
   if (dbias && cin != 64) return -1;
   if (cin_valid <= 0 || cin_valid > cin || ld < cin_valid) return -1;
   WgradParams p{in16, g16, dw, dbias, n_tok, cin, cout, ld, cin_valid, hs, ps, hd, A};
-  // >= 100 KB keeps residency at two CTAs per SM (each owns 256 TMEM columns)
-  size_t smem = (size_t)cin * 256 + 2048 + (size_t)cout * 256;
-  if (smem < 100 * 1024) smem = 100 * 1024;
+  const size_t smem = (size_t)kWgStages * ((size_t)cin * 256 + 2048 + (size_t)cout * 256);
   static bool configured = false;
   if (!configured) {
-    B200MAR_CHECK(cudaFuncSetAttribute(wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+    B200MAR_CHECK(cudaFuncSetAttribute(wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
     configured = true;
   }
+  if (smem > 224 * 1024) return -1;
+  CUtensorMap mIn, mG;
+  if (int rc = tma::encode_rows16_chunkmajor(&mIn, in16, n_tok, cin)) return rc;
+  if (int rc = tma::encode_rows16_chunkmajor(&mG, g16, n_tok, cout)) return rc;
   const long long ntile = (n_tok + 127) / 128;
-  long long grid = ntile < 2LL * sm_count() ? ntile : 2LL * sm_count();
-  wgrad_tc_kernel<<<(int)grid, 128, smem, st>>>(p);
+  long long grid = (ntile + 3) / 4;                  // >= 4 tiles per CTA: the flush is ~cout*cin atomics per CTA
+  if (grid > sm_count()) grid = sm_count();
+  wgrad_tc_kernel<<<(int)grid, 128, smem, st>>>(mIn, mG, p);
   B200MAR_CHECK(cudaGetLastError());
   return 0;
 }

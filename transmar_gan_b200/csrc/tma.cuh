@@ -60,6 +60,17 @@ __device__ __forceinline__ void reduce_add_2d(const CUtensorMap* m, const void* 
       : "memory");
 }
 
+// 3-D form (coordinates fastest-first)
+__device__ __forceinline__ void load_3d(const CUtensorMap* m, uint64_t* bar, void* smem_dst, int c0,
+                                        int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5}], [%2];" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(c0), "r"(c1),
+      "r"(c2)
+      : "memory");
+}
+
 // 4-D forms over the token grid [B][ph][pw][64] (coordinates fastest-first: channel, x, y, b)
 __device__ __forceinline__ void load_4d(const CUtensorMap* m, uint64_t* bar, void* smem_dst, int c0,
                                         int c1, int c2, int c3) {
@@ -151,6 +162,22 @@ inline int encode_halo(CUtensorMap* out, const float* base, int B, int H, int W,
   const cuuint32_t box[4] = {(cuuint32_t)C, (cuuint32_t)bw, (cuuint32_t)bh, 1};
   const cuuint32_t estr[4] = {1, 1, 1, 1};
   const CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(base), gdim, gstride,
+                        box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -3;
+}
+
+// ---- host: a row-major 16-bit matrix [n_rows][C] (C a multiple of 8) viewed as [C/8 chunks][n_rows][8]:
+// one box = [C/8][128 rows][8 elements] lands in shared memory CHUNK-MAJOR (chunk c at c*2048, row r at
+// r*16), i.e. as the no-swizzle tcgen05 operand tile of tc.cuh; rows past n_rows are zero-filled.
+inline int encode_rows16_chunkmajor(CUtensorMap* out, const void* base, long long n_rows, int C) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) return -2;
+  const cuuint64_t gdim[3] = {8, (cuuint64_t)n_rows, (cuuint64_t)(C / 8)};
+  const cuuint64_t gstride[2] = {(cuuint64_t)C * 2, 16};
+  const cuuint32_t box[3] = {8, 128, (cuuint32_t)(C / 8)};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  const CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), gdim, gstride,
                         box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                         CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS ? 0 : -3;

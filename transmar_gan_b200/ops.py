@@ -208,6 +208,28 @@ def _(z, ctx, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, ln_w, ln_b,
     return torch.empty_like(z)
 
 
+@torch.library.custom_op(f"{_NS}::attn_tc_fwd_save", mutates_args=())
+def attn_tc_fwd_save(z: Tensor, ctx: Tensor, qkv_w: Tensor, qkv_b: Tensor, proj_w: Tensor, proj_b: Tensor,
+                     logit_scale: Tensor, bias_table: Tensor, ln_w: Tensor, ln_b: Tensor,
+                     ph: int, pw: int, nh: int, shift: int) -> Tuple[Tensor, Tensor]:
+    """Training form of attn_tc_fwd: also returns the pre-projection attention output O (bf16,
+    [ceil(nwin/2)*128, 64], window order) that attn_bwd_tc consumes instead of recomputing it."""
+    _chk(z, ctx, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, ln_w, ln_b)
+    a = torch.empty_like(z)
+    nwin = z.shape[0] * (ph // 8) * (pw // 8)
+    o16 = torch.empty((((nwin + 1) // 2) * 128, 64), device=z.device, dtype=torch.bfloat16)
+    _call("attn_tc_fwd_save", _p(z), _p(ctx), _p(qkv_w), _p(qkv_b), _p(proj_w), _p(proj_b), _p(logit_scale),
+          _p(bias_table), _p(ln_w), _p(ln_b), _p(a), o16.data_ptr(), z.shape[0], ph, pw, nh, shift,
+          _stream(), meta=(z.shape[0], ph, pw, nh, shift))
+    return a, o16
+
+
+@attn_tc_fwd_save.register_fake
+def _(z, ctx, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, ln_w, ln_b, ph, pw, nh, shift):
+    nwin = z.shape[0] * (ph // 8) * (pw // 8)
+    return torch.empty_like(z), z.new_empty((((nwin + 1) // 2) * 128, 64), dtype=torch.bfloat16)
+
+
 @torch.library.custom_op(f"{_NS}::attn_bwd", mutates_args=("dz", "dctx", "grads"))
 def attn_bwd(z: Tensor, ctx: Tensor, da: Tensor, params: List[Tensor], dz: Tensor, dctx: Tensor,
              grads: List[Tensor], ph: int, pw: int, nh: int, shift: int) -> None:
@@ -219,16 +241,20 @@ def attn_bwd(z: Tensor, ctx: Tensor, da: Tensor, params: List[Tensor], dz: Tenso
 
 @torch.library.custom_op(f"{_NS}::attn_bwd_tc", mutates_args=("dz", "dctx", "grads"))
 def attn_bwd_tc(z: Tensor, ctx: Tensor, da: Tensor, params: List[Tensor], dz: Tensor, dctx: Tensor,
-                grads: List[Tensor], ph: int, pw: int, nh: int, shift: int) -> None:
+                grads: List[Tensor], ph: int, pw: int, nh: int, shift: int,
+                o16: Optional[Tensor] = None) -> None:
     """attn_bwd on the tcgen05 tensor cores: the row kernel recomputes the forward and exports the bf16
     operands of the weight gradients (window order) into a scratch buffer; a second row kernel forms
-    dz / dctx and two wgrad launches the qkv / proj weight gradients."""
+    dz / dctx and two wgrad launches the qkv / proj weight gradients.  o16: the O tensor of attn_tc_fwd_save
+    for the same inputs (skips the recomputation pass)."""
     _chk(z, ctx, da, dz, dctx, *params, *grads)
+    if o16 is not None and (o16.dtype != torch.bfloat16 or not o16.is_cuda or not o16.is_contiguous()):
+        raise RuntimeError("attn_bwd_tc: o16 must be the contiguous CUDA bf16 tensor of attn_tc_fwd_save")
     nwin = z.shape[0] * (ph // 8) * (pw // 8)
     scratch = torch.empty(((nwin + 1) // 2) * 128 * 384, device=z.device, dtype=torch.bfloat16)
     _call("attn_bwd_tc", _p(z), _p(ctx), _p(da), *[_p(t) for t in params], _p(dz), _p(dctx),
-          *[_p(t) for t in grads], scratch.data_ptr(), z.shape[0], ph, pw, nh, shift, _stream(),
-          meta=(z.shape[0], ph, pw, nh, shift))
+          *[_p(t) for t in grads], scratch.data_ptr(), None if o16 is None else o16.data_ptr(),
+          z.shape[0], ph, pw, nh, shift, _stream(), meta=(z.shape[0], ph, pw, nh, shift))
     profile.launches += 3                     # core + dx + two wgrad kernels behind one entry point
 
 
@@ -524,15 +550,22 @@ class NSTBFunction(torch.autograd.Function):
         if _PRECISION == "tf32":
             # (attn_tc_fwd(residual=False) + mlp_tc_fwd(a_is_delta=True) moves the residual add into
             # the MLP kernel; measured on B200 it costs the MLP more than it saves the attention)
-            a = attn_tc_fwd(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw, nh,
-                            shift, True)
+            if save:
+                a, o16 = attn_tc_fwd_save(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw,
+                                          nh, shift)
+            else:
+                a = attn_tc_fwd(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw, nh,
+                                shift, True)
             out, zsum, _ = mlp_tc_fwd(a, z if want_zsum else None, P[18], P[19], P[20], P[21], P[22],
                                       P[23], want_out, want_zsum, False, False)
         else:
             a = attn_fwd(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw, nh, shift)
             out, zsum = mlp_fwd(a, z if want_zsum else None, P[18], P[19], P[20], P[21], P[22], P[23],
                                 want_out, want_zsum)
-        if save:
+        ctx_.has_o16 = bool(save and _PRECISION == "tf32")
+        if ctx_.has_o16:
+            ctx_.save_for_backward(z, u, c, a, o16, *params)
+        elif save:
             ctx_.save_for_backward(z, u, c, a, *params)
         ctx_.geom = (ph, pw, nh, shift)
         ctx_.mark_non_differentiable(*([] if want_out else [out]), *([] if want_zsum else [zsum]))
@@ -540,7 +573,10 @@ class NSTBFunction(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx_, g_out, g_zsum):
-        z, u, c, a, *params = ctx_.saved_tensors
+        if ctx_.has_o16:
+            z, u, c, a, o16, *params = ctx_.saved_tensors
+        else:
+            (z, u, c, a, *params), o16 = ctx_.saved_tensors, None
         ph, pw, nh, shift = ctx_.geom
         P = [p.detach() for p in params]
         have_out = g_out is not None and g_out.numel() > 0
@@ -560,8 +596,11 @@ class NSTBFunction(torch.autograd.Function):
         (mlp_bwd_tc if _PRECISION == "tf32" else mlp_bwd)(a, g, P[18:24], da, G[18:24])
         dz = torch.empty_like(z)
         dctx = torch.zeros_like(c)
-        (attn_bwd_tc if _PRECISION == "tf32" else attn_bwd)(z, c, da, P[10:18], dz, dctx, G[10:18], ph, pw,
-                                                             nh, shift)
+        if o16 is not None:
+            attn_bwd_tc(z, c, da, P[10:18], dz, dctx, G[10:18], ph, pw, nh, shift, o16)
+        else:
+            (attn_bwd_tc if _PRECISION == "tf32" else attn_bwd)(z, c, da, P[10:18], dz, dctx, G[10:18], ph, pw,
+                                                                 nh, shift)
         du = torch.empty_like(u)
         ngram_ctx_bwd(u, dctx, P[2:10], du, G[2:10], nh)
         unigram_bwd(z, P[0], du, dz, G[0], G[1], ph, pw)
