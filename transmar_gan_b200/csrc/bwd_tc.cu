@@ -39,9 +39,10 @@ struct WgradParams {
   int cin, cout;
   int ld, cin_valid;    // row stride of dw, input channels actually written
   int hs, ps, hd, A;    // hs > 0: per-head packed [q|k|v] columns (see launch_wgrad)
+  int nstage;           // depth of the TMA ring (2 or 3)
 };
 
-constexpr int kWgStages = 3;
+constexpr int kWgStages = 3;      // ring depth (2 when three stages of the largest shape do not fit)
 
 // One CTA per SM: the operand tiles arrive by TMA (3-D tensor maps that deliver a row-major bf16 matrix
 // chunk-major, tma.cuh) through a 3-stage ring; one elected thread is producer and MMA issuer; the partial
@@ -55,7 +56,8 @@ __global__ void __launch_bounds__(128) wgrad_tc_kernel(const __grid_constant__ C
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
   // stage = [128][cin] IN tile | [128][8] ones (lane 64 of the accumulator = column sums of G) | [128][cout] G tile
   const uint32_t in_bytes = p.cin * 256, g_bytes = p.cout * 256, stage_bytes = in_bytes + 2048 + g_bytes;
-  for (int s = 0; s < kWgStages; ++s)
+  const int nstage = p.nstage;
+  for (int s = 0; s < nstage; ++s)
     *reinterpret_cast<uint4*>(smem_raw + s * stage_bytes + in_bytes + tid * 16) =
         make_uint4(0x3F803F80u, 0x3F803F80u, 0x3F803F80u, 0x3F803F80u);
   if (tid == 0) {
@@ -76,17 +78,17 @@ __global__ void __launch_bounds__(128) wgrad_tc_kernel(const __grid_constant__ C
     if (tc::elect_one()) {
       const uint32_t idesc = tc::idesc_bf16(128, p.cout, true, true);
       auto load = [&](long long i) {
-        const int s = (int)(i % kWgStages);
+        const int s = (int)(i % nstage);
         unsigned char* st = smem_raw + s * stage_bytes;
         const int r0 = (int)((blockIdx.x + i * gridDim.x) * 128);
         tma::mbar_expect_tx(full + s, in_bytes + g_bytes);
         tma::load_3d(&mapIn, full + s, st, 0, r0, 0);
         tma::load_3d(&mapG, full + s, st + in_bytes + 2048, 0, r0, 0);
       };
-      for (long long i = 0; i < kWgStages && i < my; ++i) load(i);
+      for (long long i = 0; i < nstage && i < my; ++i) load(i);
       for (long long i = 0; i < my; ++i) {
-        const int s = (int)(i % kWgStages);
-        const uint32_t par = (uint32_t)((i / kWgStages) & 1);
+        const int s = (int)(i % nstage);
+        const uint32_t par = (uint32_t)((i / nstage) & 1);
         tc::mbar_wait(full + s, par, &g_tc_error);
         tc::tc_fence_after();
         unsigned char* st = smem_raw + s * stage_bytes;
@@ -95,9 +97,9 @@ __global__ void __launch_bounds__(128) wgrad_tc_kernel(const __grid_constant__ C
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks) tc::mma_f16(tbase, dA + ks * 16, dB + ks * 16, idesc, (i > 0 || ks > 0) ? 1u : 0u);
         tc::mma_commit(empty + s);
-        if (i + kWgStages < my) {                    // refill this stage once its MMAs have read it
+        if (i + nstage < my) {                       // refill this stage once its MMAs have read it
           tc::mbar_wait(empty + s, par, &g_tc_error);
-          load(i + kWgStages);
+          load(i + nstage);
         }
       }
       tc::mma_commit(&done);
@@ -424,8 +426,10 @@ int launch_wgrad(const uint16_t* in16, const uint16_t* g16, float* dw, float* db
   if (n_tok <= 0 || (cin != 64 && cin != 128) || cout % 32 || cout < 64 || cout > 256) return -1;
   if (dbias && cin != 64) return -1;
   if (cin_valid <= 0 || cin_valid > cin || ld < cin_valid) return -1;
-  WgradParams p{in16, g16, dw, dbias, n_tok, cin, cout, ld, cin_valid, hs, ps, hd, A};
-  const size_t smem = (size_t)kWgStages * ((size_t)cin * 256 + 2048 + (size_t)cout * 256);
+  const size_t stage = (size_t)cin * 256 + 2048 + (size_t)cout * 256;
+  const int nstage = kWgStages * stage <= 224 * 1024 ? kWgStages : 2;
+  WgradParams p{in16, g16, dw, dbias, n_tok, cin, cout, ld, cin_valid, hs, ps, hd, A, nstage};
+  const size_t smem = nstage * stage;
   static bool configured = false;
   if (!configured) {
     B200MAR_CHECK(cudaFuncSetAttribute(wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
