@@ -20,9 +20,13 @@
 //       -> Q' = [q | 0] / [0 | q] (window 0 / window 1 rows), K' = [k(w0) | k(w1)], so that ONE
 //          128x64x32 MMA gives every row the logits against its own window's 64 keys;
 //          V^T (rows = (window, d), keys contiguous)
-//     S = Q' K'^T                         2 MMAs 128x64x16
-//     row-wise fp32: + relative-position bias (pre-shifted by the head's logit bound: no row max)
-//       + analytic shift mask, ex2, sum; unnormalised P written back to TMEM over S (tcgen05.st)
+//     S = Q' K'^T + Hot Bias_h^T          2 + 4 MMAs 128x64x16: the relative-position bias is added BY
+//                                         THE TENSOR CORE as a one-hot(query token) x bias-matrix product;
+//                                         both operands are Toeplitz and live compressed in shared memory
+//                                         (descriptor strides LBO = SBO make core matrices alias, below)
+//     row-wise fp32: (+ analytic shift mask on edge windows), ex2; unnormalised P written back to TMEM
+//       over S (tcgen05.st).  No row maximum, no bias adds, no row sum: the softmax denominator is a
+//       ones row of V^T (6 heads: head dim 10 of 16 accumulator columns), i.e. one more column of O_h
 //     O_h = P [V_h(w0) | V_h(w1)]         8 MMAs 128x32x8 (tf32), A operand = P from TMEM, written
 //                                         over the dead [q|k|v]_h accumulator columns
 //   O row -> TMEM (over the dead qkv buffers) = A operand of Y = O Wp^T (8 MMAs 128x64x8, tf32);
@@ -67,9 +71,16 @@ template <int NH> struct Cfg {
   static constexpr uint32_t kTStride = 2 * HS + 64;
   static constexpr uint32_t kTS = 2 * HS;          // S; P (fp32) overwrites it; Y at the end
 };
-constexpr int kBiasCopy = 232;                 // floats per shifted bias-table copy: == 8 mod 32, so the 8
-                                               // lanes of a quarter-warp (4 copies x 2 positions) hit 8
-                                               // distinct 16-byte bank groups with their LDS.128
+// Relative-position bias through the MMA.  Window POSITION q (thread row / key column) holds token
+// (7 - q/8, q%8): the window's token rows are visited bottom-up, so that for query token (ri, rj) and key
+// token (ci, cj) the K-chunk index of the one-hot operand (kc = ri) and the 8-row group of the key
+// (n/8 = 7 - ci) ADD to ri - ci + 7 = the row block of the 15x15 bias table.  With LBO = SBO = 128 B the
+// no-swizzle K-major descriptor places core matrix (group g, k-chunk kc) at byte (g + kc) * 128, hence
+//   bias operand of a head : 15 core matrices, matrix m = ri - ci + 7, element (cj, rj) = T[15 m + rj - cj + 7]
+//   one-hot operand        : 23 core matrices, identity at m = 7 (window 0 rows) and m = 15 (window 1), else 0
+// instead of 64x64 and 128x64 fp16 tiles.
+constexpr int kBiasTHead = 15 * 128;           // bytes of one head's compressed bias operand (fp16)
+constexpr int kHotBytes = 23 * 128;
 constexpr int kVChunk = 528;                   // bytes between successive 4-key chunks of V^T (fp32):
                                                // 32 rows x 16 B + 16 (== 4 words mod 32 banks)
 
@@ -83,9 +94,9 @@ struct AttnTcSmem {                            // BYTE offsets (W workers)
   static constexpr int oLnW = oBp + 256;
   static constexpr int oLnB = oLnW + 256;
   static constexpr int oScale = oLnB + 256;     // [0,6): logit scales, [6]: inverse of the qkv weight scale, [7]: scratch
-  static constexpr int oBias = ((oScale + 32 + 15) / 16) * 16;   // fp32 [6 heads][4 copies][kBiasCopy]: copy s holds
-                                               // T'[j + s], T' = (bias - max bias - scale) * log2(e)
-  static constexpr int oBar = oBias + 6 * 4 * kBiasCopy * 4;  // 3 workers x 8 mbarrier slots (5 used) + tmem slot
+  static constexpr int oBiasT = ((oScale + 32 + 127) / 128) * 128;   // fp16 [6 heads][15][8 cj][8 rj], * log2(e)
+  static constexpr int oHot = oBiasT + 6 * kBiasTHead;               // fp16 one-hot operand (23 core matrices)
+  static constexpr int oBar = oHot + kHotBytes;  // W workers x 8 mbarrier slots (5 used) + tmem slot
   static constexpr int oWork = ((oBar + 320 + 1023) / 1024) * 1024;   // 1 KB aligned: TMA 128 B swizzle
   // per worker; [X | Q | K | V] is also the 32 KB fp32 staging tile of the LayerNorm output
   static constexpr int wX = 0;                 // fp16 [128][64] (R = 128): X, later O
@@ -123,7 +134,8 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
   float* sLnW = reinterpret_cast<float*>(smem_raw + L::oLnW);
   float* sLnB = reinterpret_cast<float*>(smem_raw + L::oLnB);
   float* sScale = reinterpret_cast<float*>(smem_raw + L::oScale);
-  float* sBias = reinterpret_cast<float*>(smem_raw + L::oBias);
+  __half* sBiasT = reinterpret_cast<__half*>(smem_raw + L::oBiasT);
+  __half* sHot = reinterpret_cast<__half*>(smem_raw + L::oHot);
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + L::oBar);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem_raw + L::oBar + kWorkers * 64);
   const int tid = threadIdx.x, lane = tid & 31;
@@ -181,21 +193,23 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
   if (tid < 64) { sBp[tid] = p.proj_b[tid]; sLnW[tid] = p.ln_w[tid]; sLnB[tid] = p.ln_b[tid]; }
   if (tid < NH) sScale[tid] = expf(fminf(p.logit_scale[tid], kLogitMax)) * kLog2e;
   if (tid == 0) sScale[6] = __uint_as_float(we << 23);    // 2^(we-127)
-  // relative-position bias, shifted by an upper bound of the head's logits so that the softmax
-  // needs no row maximum: logit <= scale_h * 1 + max_e bias[e,h]  ->  exponent argument <= ~0.
-  // Four copies, copy s starting at table entry s, make every 4-key group one aligned LDS.128.
-  __shared__ float sBound[8];
+  // A head whose logits are bounded a priori, |cos * scale + bias| <= scale + max|bias| <= 60 octaves, needs
+  // no row maximum: p = ex2(s) can neither overflow (row sums <= 2^66) nor lose every term of a row (the
+  // row's own key is never masked).  Any other head (logit scales near the ln 100 clamp, huge biases)
+  // always takes the exact max-subtracting path.
+  __shared__ int sFast[8];
   if (tid < NH) {
-    float mb = -3.0e38f;
-    for (int e = 0; e < 225; ++e) mb = fmaxf(mb, p.bias_table[e * NH + tid]);
-    sBound[tid] = expf(fminf(p.logit_scale[tid], kLogitMax)) + mb;
+    float mb = 0.f;
+    for (int e = 0; e < 225; ++e) mb = fmaxf(mb, fabsf(p.bias_table[e * NH + tid]));
+    sFast[tid] = (expf(fminf(p.logit_scale[tid], kLogitMax)) + mb) * kLog2e <= 60.0f ? 1 : 0;
   }
-  __syncthreads();
-  for (int i = tid; i < NH * 4 * kBiasCopy; i += 128 * kWorkers) {
-    const int h = i / (4 * kBiasCopy), r = i - h * (4 * kBiasCopy), sft = r / kBiasCopy, j = r - sft * kBiasCopy;
-    const float bound = sBound[h];
-    const int e = j + sft;
-    sBias[i] = e < 225 ? (p.bias_table[e * NH + h] - bound) * kLog2e : 0.f;
+  for (int i = tid; i < NH * 15 * 64; i += 128 * kWorkers) {
+    const int h = i / 960, r = i - h * 960, m = r >> 6, cj = (r >> 3) & 7, rj = r & 7;
+    sBiasT[i] = __float2half_rn(p.bias_table[(m * 15 + rj - cj + 7) * NH + h] * kLog2e);
+  }
+  for (int i = tid; i < 23 * 64; i += 128 * kWorkers) {
+    const int m = i >> 6, j = (i >> 3) & 7, e = i & 7;
+    sHot[i] = __float2half_rn(((m == 7 || m == 15) && j == e) ? 1.0f : 0.0f);
   }
   if (tid == 0) {
     for (int i = 0; i < 8 * kWorkers; ++i) tc::mbar_init(bars + i, 1);
@@ -218,13 +232,8 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
   const int nwin = g.B * g.wh * g.ww;
   const int ntile = (nwin + 1) >> 1;
   const int row = wq * 32 + lane;                 // token row of this thread == its TMEM lane
-  const int wsel = wq >> 1, lrow = row & 63;      // window of the pair (warp-uniform), token inside it
-  const int bias_base = ((lrow >> 3) * 15 + (lrow & 7)) + 112;   // rel_index(r, c) = bias_base - (15 ci + cj)
-  // keys (ci, cj0..cj0+3) need table entries lo..lo+3, lo = bias_base - 15 ci - cj0 - 3; copy
-  // s = lo mod 4 = (bias_base + ci + 1) mod 4 holds them 16-byte aligned at offset lo - s.
-  int bias_off[4];
-#pragma unroll
-  for (int m = 0; m < 4; ++m) bias_off[m] = bias_base + (kBiasCopy - 1) * ((bias_base + m + 1) & 3);
+  const int wsel = wq >> 1, lrow = row & 63;      // window of the pair (warp-uniform), POSITION inside it
+  const int ltok = ((7 - (lrow >> 3)) << 3) | (lrow & 7);   // the window token at that position (rows bottom-up)
 
   // operand descriptors are built once; one K = 16 step advances the start-address field (>>4)
   // by two 8-element k-chunks
@@ -233,7 +242,9 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
                  dQ = tc::smem_desc(tc::smem_u32(sQ), 2048, 128),
                  dK = tc::smem_desc(tc::smem_u32(sK), 1024, 128),
                  dV = tc::smem_desc(tc::smem_u32(sV), kVChunk, 128),
-                 dWp = tc::smem_desc(tc::smem_u32(sWp), 1024, 128);
+                 dWp = tc::smem_desc(tc::smem_u32(sWp), 1024, 128),
+                 dHot = tc::smem_desc(tc::smem_u32(sHot), 128, 128),       // LBO = SBO: aliased core matrices
+                 dBiasT = tc::smem_desc(tc::smem_u32(sBiasT), 128, 128);
   // [q_h | k_h | v_h] = X * Wqkv[rows of head h]^T -> TMEM buffer `buf` (issued by one thread)
   auto issue_qkv = [&](int h, int buf) {
     const uint64_t db = dWqkv + (uint64_t)(h * HS);
@@ -270,15 +281,34 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
   const bool leader = wq == 0 && lane == 0;       // bulk groups are per thread: one fixed thread
   const int tile_stride = gridDim.x * kWorkers;
   // byte offset of 16-byte chunk i of this thread's row inside the swizzled z tile
-  const uint32_t zrow_off = (uint32_t)(wsel * 16384 + lrow * 128);
+  const uint32_t zrow_off = (uint32_t)(wsel * 16384 + ltok * 128);
   auto zoff = [&](int i) -> uint32_t {
-    return zrow_off + (uint32_t)((i >> 3) * 8192 + (((i & 7) ^ (lrow & 7)) << 4));
+    return zrow_off + (uint32_t)((i >> 3) * 8192 + (((i & 7) ^ (ltok & 7)) << 4));
+  };
+  // S_h = Q' K'^T + Hot Bias_h^T (issued by one thread)
+  auto issue_s = [&](int h) {
+    tc::mma_f16(tbase + kTS, dQ, dK, kI64, 0u);
+    tc::mma_f16(tbase + kTS, dQ + 256, dK + 128, kI64, 1u);
+    const uint64_t db = dBiasT + (uint64_t)(h * (kBiasTHead >> 4));
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) tc::mma_f16(tbase + kTS, dHot + ks * 16, db + ks * 16, kI64, 1u);
+  };
+  // L2 prefetch of a tile's z windows: the load at the end of the current tile then hits L2
+  auto prefetch_z = [&](int tile_) {
+    int x0, y0, b;
+#pragma unroll
+    for (int w = 0; w < 2; ++w)
+      if (tma_window(tile_ * 2 + w, x0, y0, b)) {
+        tma::prefetch_4d(&mapZ, 0, x0, y0, b);
+        tma::prefetch_4d(&mapZ, 32, x0, y0, b);
+      }
   };
   if (leader && (int)(blockIdx.x * kWorkers + wk) < ntile) issue_z_loads(blockIdx.x * kWorkers + wk);
 
   PROF_DECL
   for (int tile = blockIdx.x * kWorkers + wk; tile < ntile; tile += tile_stride) {
     PROF(0);
+    if (leader && tile + tile_stride < ntile) prefetch_z(tile + tile_stride);
     const int win = tile * 2 + wsel;
     const bool wvalid = win < nwin;
     int wx0, wy0, wb;
@@ -297,7 +327,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
       //      before the fp16 conversion and the exact inverse is applied to the fp32 accumulators.
       float x[64];
       if (wvalid) {
-        const Slot sl = slot_of(g, win, lrow);
+        const Slot sl = slot_of(g, win, ltok);
         tok = sl.tok;
         sReg[row] = sl.region;
         const float4* cp = reinterpret_cast<const float4*>(p.ctx + (size_t)sl.cwin * 64);
@@ -348,7 +378,8 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
     }
     // ---- shift mask of this row as a 64-bit key set (analytic 9-region rule)
     uint32_t mlo = 0, mhi = 0;
-    if (p.shift > 0) {
+    if (p.shift > 0 && wvalid &&
+        (win % g.ww == g.ww - 1 || (win / g.ww) % g.wh == g.wh - 1)) {   // only the last window row / column
       const int rg = sReg[row];
       const int* reg = sReg + wsel * 64;
 #pragma unroll
@@ -413,6 +444,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
         tc::tc_fence_after();
         float ov[16];
         tc::tmem_ld16(tbase + lane_addr + kTQ + (buf ^ 1) * HS + wsel * 16, ov);
+        if constexpr (NH == 6) inv_prev = 1.0f / ov[HD];   // the ones row of V^T: sum of the row's (tf32) P
 #pragma unroll
         for (int d = 0; d < HD; ++d) o[(h - 1) * HD + d] = ov[d] * inv_prev;
       }
@@ -433,6 +465,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
         float* vt = reinterpret_cast<float*>(sV + (lrow >> 2) * kVChunk + wsel * 256) + (lrow & 3);
 #pragma unroll
         for (int d = 0; d < HD; ++d) vt[d * 4] = tc::round_tf32(qkv[2 * PS + d]);
+        if (NH == 6 && h == 0) vt[HD * 4] = 1.0f;      // ones row (both windows): O column HD = row sum of P
       }
       PROF(6);                                         // operand stores
       tc::fence_async_smem();
@@ -442,8 +475,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
       if (wq == 0) {
         tc::tc_fence_after();
         if (tc::elect_one()) {
-          tc::mma_f16(tbase + kTS, dQ, dK, kI64, 0u);
-          tc::mma_f16(tbase + kTS, dQ + 256, dK + 128, kI64, 1u);
+          issue_s(h);
           tc::mma_commit(barS);
           if (h + 1 < NH) {                            // next head's projection, in the shadow of S_h
             issue_qkv(h + 1, buf ^ 1);
@@ -455,28 +487,12 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
       tc::mbar_wait(barS, phS, &g_tc_error); phS ^= 1;
       tc::tc_fence_after();
       PROF(8);                                         // S issue + wait
-      // ---- softmax of this row over its own window's 64 keys (log2 domain).  Fast path: the bias
-      //      table is pre-shifted by the head's logit upper bound, so p = ex2(s + bias') <= ~1 with
-      //      no row maximum; a row whose true maximum lies > 100 octaves below the bound (possible
-      //      only with logit scales near the ln(100) clamp) underflows and sends the whole worker
-      //      through the exact max-subtracting path below.
-      bool bad;
+      // ---- softmax of this row over its own window's 64 keys (log2 domain; S already holds the bias).
+      //      Fast heads (sFast): p = ex2(s) with no row maximum; other heads subtract the exact row maximum.
+      //      6 heads: the denominator comes out of the PV MMA (ones row of V^T); 4 heads: summed here.
       {
         float s[64];
         tc::tmem_ld64(tbase + lane_addr + kTS, s);
-        const float* bh = sBias + h * (4 * kBiasCopy);
-#pragma unroll
-        for (int ci = 0; ci < 8; ++ci) {
-          const float* bp = bh + bias_off[ci & 3];
-#pragma unroll
-          for (int g4 = 0; g4 < 2; ++g4) {
-            const float4 b = *reinterpret_cast<const float4*>(bp - (15 * ci + 4 * g4 + 3));
-            s[ci * 8 + g4 * 4 + 0] += b.w;
-            s[ci * 8 + g4 * 4 + 1] += b.z;
-            s[ci * 8 + g4 * 4 + 2] += b.y;
-            s[ci * 8 + g4 * 4 + 3] += b.x;
-          }
-        }
         if (mlo | mhi) {
 #pragma unroll
           for (int c = 0; c < 32; ++c) {
@@ -484,52 +500,30 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
             if ((mhi >> c) & 1u) s[c + 32] += -100.0f * kLog2e;
           }
         }
-        float sum4[4] = {0.f, 0.f, 0.f, 0.f};
+        if (sFast[h]) {
 #pragma unroll
-        for (int c = 0; c < 64; ++c) { s[c] = tc::ex2_approx(s[c]); sum4[c & 3] += s[c]; }
-        const float sum = (sum4[0] + sum4[1]) + (sum4[2] + sum4[3]);
-        bad = !(sum >= 7.8886090522101181e-31f);         // 2^-100 (also catches NaN)
-        inv_prev = 1.0f / sum;
+          for (int c = 0; c < 64; ++c) s[c] = tc::ex2_approx(s[c]);
+        } else {
+          float m4[4] = {s[0], s[1], s[2], s[3]};
+#pragma unroll
+          for (int c = 4; c < 64; ++c) m4[c & 3] = fmaxf(m4[c & 3], s[c]);
+          const float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+#pragma unroll
+          for (int c = 0; c < 64; ++c) s[c] = tc::ex2_approx(s[c] - mx);
+        }
+        if constexpr (NH != 6) {
+          float sum4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+          for (int c = 0; c < 64; ++c) sum4[c & 3] += s[c];
+          inv_prev = 1.0f / ((sum4[0] + sum4[1]) + (sum4[2] + sum4[3]));
+        }
         tc::tmem_st64(tbase + lane_addr + kTS, s);       // unnormalised P (tf32 operand) over S
         tc::tmem_wait_st();
       }
       PROF(9);                                         // softmax + P store
       tc::tc_fence_before();
-      const bool redo = tc::worker_sync_or(1 + wk, bad);
+      tc::worker_sync(1 + wk);
       PROF(10);                                        // sync
-      if (redo) {
-        // ---- exact path (rare): recompute S (Q', K' are still in shared memory), subtract the row max
-        if (wq == 0) {
-          tc::tc_fence_after();
-          if (tc::elect_one()) {
-            tc::mma_f16(tbase + kTS, dQ, dK, kI64, 0u);
-            tc::mma_f16(tbase + kTS, dQ + 256, dK + 128, kI64, 1u);
-            tc::mma_commit(barS);
-          }
-          __syncwarp();
-        }
-        tc::mbar_wait(barS, phS, &g_tc_error); phS ^= 1;
-        tc::tc_fence_after();
-        float s[64];
-        tc::tmem_ld64(tbase + lane_addr + kTS, s);
-        const float* bias = sBias + h * (4 * kBiasCopy) + bias_base;     // copy 0 = the unshifted-index table
-#pragma unroll 8
-        for (int c = 0; c < 64; ++c) {
-          s[c] += bias[-((c >> 3) * 15 + (c & 7))];
-          if (((c < 32 ? mlo >> c : mhi >> (c - 32)) & 1u)) s[c] += -100.0f * kLog2e;
-        }
-        float mx = s[0];
-#pragma unroll
-        for (int c = 1; c < 64; ++c) mx = fmaxf(mx, s[c]);
-        float sum = 0.f;
-#pragma unroll
-        for (int c = 0; c < 64; ++c) { s[c] = tc::ex2_approx(s[c] - mx); sum += s[c]; }
-        inv_prev = 1.0f / sum;
-        tc::tmem_st64(tbase + lane_addr + kTS, s);
-        tc::tmem_wait_st();
-        tc::tc_fence_before();
-        tc::worker_sync(1 + wk);
-      }
       if (wq == 0) {
         tc::tc_fence_after();
         if (tc::elect_one()) {
@@ -549,6 +543,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
       tc::tc_fence_after();
       float ov[16];
       tc::tmem_ld16(tbase + lane_addr + kTQ + ((NH - 1) & 1) * HS + wsel * 16, ov);
+      if constexpr (NH == 6) inv_prev = 1.0f / ov[HD];
 #pragma unroll
       for (int d = 0; d < HD; ++d) o[(NH - 1) * HD + d] = ov[d] * inv_prev;
     }
@@ -562,7 +557,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
       for (int i = 0; i < 64; ++i) ot[i] = tc::round_tf32(o[i]);
       tc::tmem_st64(tbase + lane_addr + kTQ, ot);
       if (SAVEO && wvalid) {                             // bf16 copy for the backward (window order)
-        uint4* dst = reinterpret_cast<uint4*>(p.o16 + ((size_t)tile * 128 + row) * 64);
+        uint4* dst = reinterpret_cast<uint4*>(p.o16 + ((size_t)tile * 128 + wsel * 64 + ltok) * 64);
 #pragma unroll
         for (int i = 0; i < 8; ++i)
           dst[i] = make_uint4(tc::pack_bf16(ot[8 * i], ot[8 * i + 1]), tc::pack_bf16(ot[8 * i + 2], ot[8 * i + 3]),

@@ -81,6 +81,13 @@ __device__ __forceinline__ void load_4d(const CUtensorMap* m, uint64_t* bar, voi
       "r"(c2), "r"(c3)
       : "memory");
 }
+// L2 prefetch of a box (no shared-memory destination, no completion signal)
+__device__ __forceinline__ void prefetch_4d(const CUtensorMap* m, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.prefetch.tensor.4d.L2.global.tile [%0, {%1, %2, %3, %4}];" ::"l"(
+                   reinterpret_cast<uint64_t>(m)),
+               "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
 __device__ __forceinline__ void store_4d(const CUtensorMap* m, const void* smem_src, int c0, int c1,
                                          int c2, int c3) {
   asm volatile(
