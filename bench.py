@@ -264,43 +264,44 @@ def time_e2e(model, args, world):
 
 def time_train(args, rank, world):
     """config-3 recipe per rank: y = netG(x); F.l1_loss(y,t).backward(); all-reduce; Adam.step()
-    (scripts/run_ablation_studies.py:1525-1535; Adam betas (.5,.999) lr 1e-4), batch 16 x 128x128."""
-    import torch.nn.functional as F
-    from transmar_gan_b200 import dp, ops
-    model = build_model().train()
-    dp.broadcast_parameters(model)
-    bucket = dp.FlatGradBucket(model.parameters())
-    opt = torch.optim.Adam(model.parameters(), lr=1e-4, betas=(0.5, 0.999))
+    (scripts/run_ablation_studies.py:1525-1535; Adam betas (.5,.999) lr 1e-4), batch 16 x 128x128,
+    through transmar_gan_b200.train.L1TrainStep: the step is captured once into CUDA graphs (fwd + L1 +
+    bwd | NCCL all-reduce of the flat bucket | Adam) and replayed; `eager_ms_per_step` times the same
+    recipe launched kernel by kernel from the host."""
+    from transmar_gan_b200 import dp, ops, train
     B, S = 16, 128
     g = torch.Generator().manual_seed(999 + rank)
     x = (torch.rand(B, 1, S, S, generator=g) * 2 - 1).cuda()
     t = (torch.rand(B, 1, S, S, generator=g) * 2 - 1).cuda()
-
-    def step():
-        bucket.zero()
-        loss = F.l1_loss(model(x), t)
-        loss.backward()
-        bucket.all_reduce()
-        opt.step()
-        return loss
-
-    for _ in range(max(args.warmup, 3)):
-        step()
-    barrier(world)
-    ops.profile.reset()
     steps = max(args.steps, 5)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(steps):
-        loss = step()
-    e1.record()
-    barrier(world)
-    ms = max_over_ranks(e0.elapsed_time(e1), world) / steps
-    launches = ops.profile.launches // steps
+    res = {}
+    for mode in ("eager", "graph"):
+        model = build_model().train()
+        dp.broadcast_parameters(model)
+        step = train.L1TrainStep(model, lr=1e-4, betas=(0.5, 0.999), graph=(mode == "graph"))
+        ops.profile.reset()
+        step(x, t)                                   # graph mode: warm-up steps + capture happen here
+        per_step = ops.profile.launches // (step._warmup + 1 if mode == "graph" else 1)
+        for _ in range(max(args.warmup, 3)):
+            step(x, t)
+        barrier(world)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            loss = step(x, t)
+        e1.record()
+        barrier(world)
+        res[mode] = (max_over_ranks(e0.elapsed_time(e1), world) / steps, per_step, float(loss.item()))
+        nbytes = step.bucket.numel * 4
+        del step, model
+    ms, launches, loss = res["graph"]
     return {"steps_per_s": 1e3 / ms, "slices_per_s": world * B * 1e3 / ms, "ms_per_step": ms,
-            "per_gpu_batch": B, "size": S, "recipe": "fwd + L1 + bwd + flat-bucket all-reduce + Adam",
-            "allreduce_bytes": bucket.numel * 4 if world > 1 else 0,
-            "gpu_launches_per_step": launches, "final_loss": float(loss.item())}
+            "eager_ms_per_step": res["eager"][0],
+            "per_gpu_batch": B, "size": S,
+            "recipe": "fwd + L1 + bwd + flat-bucket all-reduce + Adam, replayed from CUDA graphs "
+                      "(train.L1TrainStep)",
+            "allreduce_bytes": nbytes if world > 1 else 0,
+            "gpu_launches_per_step": launches, "final_loss": loss}
 
 
 def main():
