@@ -285,13 +285,16 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
   auto zoff = [&](int i) -> uint32_t {
     return zrow_off + (uint32_t)((i >> 3) * 8192 + (((i & 7) ^ (ltok & 7)) << 4));
   };
-  // S_h = Q' K'^T + Hot Bias_h^T (issued by one thread)
-  auto issue_s = [&](int h) {
-    tc::mma_f16(tbase + kTS, dQ, dK, kI64, 0u);
-    tc::mma_f16(tbase + kTS, dQ + 256, dK + 128, kI64, 1u);
+  // S_h = Hot Bias_h^T + Q' K'^T (issued by one thread).  The bias part does not depend on the tile: it
+  // is issued as soon as the S / P columns are free (tile start; PV_{h-1} complete), off the critical path.
+  auto issue_bias = [&](int h) {
     const uint64_t db = dBiasT + (uint64_t)(h * (kBiasTHead >> 4));
 #pragma unroll
-    for (int ks = 0; ks < 4; ++ks) tc::mma_f16(tbase + kTS, dHot + ks * 16, db + ks * 16, kI64, 1u);
+    for (int ks = 0; ks < 4; ++ks) tc::mma_f16(tbase + kTS, dHot + ks * 16, db + ks * 16, kI64, ks > 0);
+  };
+  auto issue_s = [&]() {
+    tc::mma_f16(tbase + kTS, dQ, dK, kI64, 1u);
+    tc::mma_f16(tbase + kTS, dQ + 256, dK + 128, kI64, 1u);
   };
   // L2 prefetch of a tile's z windows: the load at the end of the current tile then hits L2
   auto prefetch_z = [&](int tile_) {
@@ -393,7 +396,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
     tc::worker_sync(1 + wk);
     if (wq == 0) {                                   // warp-uniform: one elected lane issues
       tc::tc_fence_after();
-      if (tc::elect_one()) { issue_qkv(0, 0); tc::mma_commit(barQ); }
+      if (tc::elect_one()) { issue_qkv(0, 0); tc::mma_commit(barQ); issue_bias(0); }
       __syncwarp();
     }
     PROF(2);                                         // sync + first qkv issue
@@ -402,7 +405,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
     // in local memory: 10-16 stores per head, one 64-float read-back per tile
     float o[64];
 #pragma unroll
-    for (int i = 0; i < 64; ++i) o[i] = 0.f;
+    for (int i = A; i < 64; ++i) o[i] = 0.f;           // 6 heads: columns 60..63 are padding
     float inv_prev = 0.f;
 
 #pragma unroll 1
@@ -444,6 +447,10 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
         tc::tc_fence_after();
         float ov[16];
         tc::tmem_ld16(tbase + lane_addr + kTQ + (buf ^ 1) * HS + wsel * 16, ov);
+        if (wq == 0) {                                 // PV_{h-1} is complete: the S / P columns are free
+          if (tc::elect_one()) issue_bias(h);
+          __syncwarp();
+        }
         if constexpr (NH == 6) inv_prev = 1.0f / ov[HD];   // the ones row of V^T: sum of the row's (tf32) P
 #pragma unroll
         for (int d = 0; d < HD; ++d) o[(h - 1) * HD + d] = ov[d] * inv_prev;
@@ -475,7 +482,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
       if (wq == 0) {
         tc::tc_fence_after();
         if (tc::elect_one()) {
-          issue_s(h);
+          issue_s();
           tc::mma_commit(barS);
           if (h + 1 < NH) {                            // next head's projection, in the shadow of S_h
             issue_qkv(h + 1, buf ^ 1);

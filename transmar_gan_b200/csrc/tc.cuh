@@ -42,6 +42,7 @@ __device__ __forceinline__ void fence_barrier_init() {
 // Bounded wait on phase parity; returns false (and raises *err) on timeout.
 __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity, int* err) {
   const uint32_t addr = smem_u32(bar);
+#pragma unroll 1
   for (uint32_t spin = 0; spin < (1u << 22); ++spin) {
     uint32_t done;
     asm volatile(
