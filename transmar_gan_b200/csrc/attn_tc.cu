@@ -629,20 +629,33 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
     tc::tc_fence_before();
     tc::worker_sync(1 + wk);
     if (leader) {
-      bool stored = false;
+      // one bulk group per window half, so that the next tile's window 0 can be fetched as soon as the
+      // first store has drained its half of the buffer (the second store overlaps that load)
 #pragma unroll
       for (int w = 0; w < 2; ++w) {
         int x0, y0, b;
         if (tma_window(tile * 2 + w, x0, y0, b)) {
           tma::store_4d(&mapA, sW + w * 16384, 0, x0, y0, b);
           tma::store_4d(&mapA, sW + w * 16384 + 8192, 32, x0, y0, b);
-          stored = true;
         }
+        tma::commit_group();                           // (an empty group completes immediately)
       }
-      if (stored) tma::commit_group();
-      if (tile + tile_stride < ntile) {
-        tma::wait_read_all();                          // the stores have drained the tile buffer
-        issue_z_loads(tile + tile_stride);
+      const int nt = tile + tile_stride;
+      if (nt < ntile) {
+        int x0[2], y0[2], b[2];
+        const bool t0 = tma_window(nt * 2, x0[0], y0[0], b[0]);
+        const bool t1 = tma_window(nt * 2 + 1, x0[1], y0[1], b[1]);
+        if (t0 || t1) tma::mbar_expect_tx(barZ, ((int)t0 + (int)t1) * 16384);
+        tma::wait_read_1();                            // window-0 half drained
+        if (t0) {
+          tma::load_4d(&mapZ, barZ, sW, 0, x0[0], y0[0], b[0]);
+          tma::load_4d(&mapZ, barZ, sW + 8192, 32, x0[0], y0[0], b[0]);
+        }
+        tma::wait_read_all();
+        if (t1) {
+          tma::load_4d(&mapZ, barZ, sW + 16384, 0, x0[1], y0[1], b[1]);
+          tma::load_4d(&mapZ, barZ, sW + 16384 + 8192, 32, x0[1], y0[1], b[1]);
+        }
       }
     }
     PROF(15);                                          // store + next-tile load issue

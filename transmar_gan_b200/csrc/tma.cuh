@@ -102,6 +102,10 @@ __device__ __forceinline__ void commit_group() { asm volatile("cp.async.bulk.com
 __device__ __forceinline__ void wait_read_all() {
   asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
+// all but the most recent committed bulk group of this thread have finished reading shared memory
+__device__ __forceinline__ void wait_read_1() {
+  asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+}
 // all committed bulk groups of this thread are complete (global writes performed)
 __device__ __forceinline__ void wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
