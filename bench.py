@@ -46,6 +46,8 @@ def parse():
     ap.add_argument("--size", type=int, default=H)
     ap.add_argument("--no-train", action="store_true", help="skip the training-step leg")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-highres", action="store_true", help="skip the 1024x1024 inference leg (config 5)")
+    ap.add_argument("--no-gan", action="store_true", help="skip the full GAN training-step leg (config 4)")
     return ap.parse_args()
 
 
@@ -262,6 +264,28 @@ def time_e2e(model, args, world):
     return ms, xh.numel() * 4, yh.numel() * 4
 
 
+def time_highres(model, args, world):
+    """BASELINE config 5: inference at 1024 x 1024 (16 384 stage-1 windows per slice, analytic shift
+    mask), batch 4 per GPU, inputs resident in HBM."""
+    B, S = 4, 1024
+    g = torch.Generator().manual_seed(999 + int(os.environ.get("RANK", "0")))
+    x = (torch.rand(B, 1, S, S, generator=g) * 2 - 1).cuda()
+    steps = max(args.steps, 3)
+    with torch.no_grad():
+        for _ in range(3):
+            model(x)
+        barrier(world)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            model(x)
+        e1.record()
+        barrier(world)
+    ms = max_over_ranks(e0.elapsed_time(e1), world) / steps
+    return {"slices_per_s": world * B * 1e3 / ms, "ms_per_step": ms, "per_gpu_batch": B, "size": S,
+            "windows_per_slice": (S // 8) ** 2, "mpixels_per_s": world * B * S * S / ms / 1e3}
+
+
 def time_train(args, rank, world):
     """config-3 recipe per rank: y = netG(x); F.l1_loss(y,t).backward(); all-reduce; Adam.step()
     (scripts/run_ablation_studies.py:1525-1535; Adam betas (.5,.999) lr 1e-4), batch 16 x 128x128,
@@ -304,6 +328,62 @@ def time_train(args, rank, world):
             "gpu_launches_per_step": launches, "final_loss": loss}
 
 
+def time_train_gan(args, rank, world):
+    """BASELINE config 4: the full TransMAR-GAN step (training/train_combined.py:399-500) per rank, batch 16
+    x 128x128: 2 generator forwards + 1 generator backward on this repo's kernels, 4 discriminator forwards
+    + 2 backwards and the metal-aware losses on stock PyTorch (transmar_gan_b200/gan.py), one flat-bucket
+    all-reduce per network, through train.GANTrainStep (CUDA-graph replay).  lambda_phys = 0: torch-radon is
+    an absent submodule of the reference.  cuDNN runs with torch's default allow_tf32=True
+    for the discriminator, as in the reference's script."""
+    from transmar_gan_b200 import dp, gan, ops, train
+    B, S = 16, 128
+    g = torch.Generator().manual_seed(999 + rank)
+    ct = torch.rand(B, 1, S, S, generator=g) * 2 - 1
+    real = torch.rand(B, 1, S, S, generator=g) * 2 - 1
+    yy, xx = torch.meshgrid(torch.arange(S), torch.arange(S), indexing="ij")
+    ct[:, :, ((yy - 40) ** 2 + (xx - 70) ** 2) <= 36] = 1.0         # metal disc, r = 6 px (SURVEY.md §8d)
+    ct, real = ct.cuda(), real.cuda()
+    steps = max(args.steps, 5)
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = True
+    res = {}
+    try:
+        for mode in ("eager", "graph"):
+            netG = build_model().train()
+            torch.manual_seed(4321)
+            netD = gan.MultiScaleDiscriminator(2, 64, 5, 3, True).cuda().train()
+            netD.apply(gan.weights_init)
+            dp.broadcast_parameters(netG)
+            dp.broadcast_parameters(netD)
+            step = train.GANTrainStep(netG, netD, graph=(mode == "graph"))
+            ops.profile.reset()
+            step(ct, real)
+            per_step = ops.profile.launches // (step._warmup + 1 if mode == "graph" else 1)
+            for _ in range(max(args.warmup, 3)):
+                step(ct, real)
+            barrier(world)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(steps):
+                lD, lG = step(ct, real)
+            e1.record()
+            barrier(world)
+            res[mode] = (max_over_ranks(e0.elapsed_time(e1), world) / steps, per_step, float(lD.item()),
+                         float(lG.item()))
+            nbytes = (step.bucketG.numel * 4, step.bucketD.numel * 4)
+            del step, netG, netD
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
+    ms, launches, lD, lG = res["graph"]
+    return {"steps_per_s": 1e3 / ms, "slices_per_s": world * B * 1e3 / ms, "ms_per_step": ms,
+            "eager_ms_per_step": res["eager"][0], "per_gpu_batch": B, "size": S,
+            "recipe": "D step (G fwd no-grad, 2 D fwd, hinge, bwd, Adam) + G step (G fwd, 2 D fwd, hinge + FM + "
+                      "metal-aware L1/edge + metal consistency, bwd, Adam); lambda_phys = 0 (torch-radon absent); "
+                      "replayed from CUDA graphs (train.GANTrainStep)",
+            "allreduce_bytes": list(nbytes) if world > 1 else [0, 0],
+            "gpu_launches_per_step": launches, "final_loss_D": lD, "final_loss_G": lG}
+
+
 def main():
     args = parse()
     if args.impl == "reference":
@@ -321,7 +401,9 @@ def main():
     sampler = ClockSampler(local) if rank == 0 else None
     ms, launches, attn_ms, mlp_ms, clocks, _ = time_inference(model, args, world, sampler)
     e2e_ms, h2d, d2h = time_e2e(model, args, world)
+    highres = None if args.no_highres else time_highres(model, args, world)
     train = None if args.no_train else time_train(args, rank, world)
+    train_gan = None if (args.no_train or args.no_gan) else time_train_gan(args, rank, world)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         sec, threads, runs = cpu_forward_time(args.size, 3)
@@ -392,7 +474,9 @@ def main():
                              "the per-token fp32 epilogues (normalize, 384 exponentials, LayerNorm) on 12 "
                              "resident warps per SM, see profiles/r01_summary.md"},
         "cpu_baseline": cpu,
+        "highres": highres,
         "train": train,
+        "train_gan": train_gan,
     }
     print(json.dumps(out))
 

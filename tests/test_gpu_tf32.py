@@ -127,6 +127,34 @@ def test_whole_model_tf32_416(T):
     assert (y.double() - ref).abs().max().item() < 1e-3
 
 
+def test_whole_model_tf32_1024_highres(T):
+    """BASELINE config 5: 1024 x 1024 slice = 16 384 stage-1 windows, 127 + 127 masked edge windows per
+    shifted block (the reference would materialise 6 x 268 MB masks per forward; the kernels evaluate the
+    9-region rule analytically).  Checker: the oracle in float64 on the GPU."""
+    sd = O.synthetic_state_dict("W1", seed=3)
+    m = T.NGswin()
+    m.load_state_dict(sd, strict=True)
+    m = m.cuda().eval()
+    x = O.synthetic_input(1, 1024, 1024, seed=999).cuda()
+    with torch.no_grad():
+        y = m(x)
+        ref = O.ngswin_forward(x.double(), {k: (v.cuda().double() if v.is_floating_point() else v.cuda())
+                                            for k, v in sd.items()})
+    assert (y.double() - ref).abs().max().item() < 1e-3
+    del ref
+    torch.cuda.empty_cache()
+    # non-multiple-of-32 high-res input: zero padding on the right / bottom, cropped back
+    x2 = O.synthetic_input(1, 1000, 1010, seed=5).cuda()
+    with torch.no_grad():
+        y2 = m(x2)
+        old = T.ops.set_precision("fp32")
+        try:
+            y2_32 = m(x2)
+        finally:
+            T.ops.set_precision(old)
+    assert y2.shape == x2.shape and (y2 - y2_32).abs().max().item() < 1e-3
+
+
 def test_tf32_determinism_and_batch_independence(T):
     m = T.NGswin()
     m.load_state_dict(O.synthetic_state_dict("W1", seed=1), strict=True)
@@ -163,9 +191,10 @@ def test_tc_forward_tc_backward_gradients(T, golden_outputs):
 
 
 def test_attn_tc_exact_softmax_fallback(T):
-    """The tensor-core attention shifts the logits by a per-head upper bound instead of the row
-    maximum; rows that would underflow take the exact max-subtracting path.  Force it: one huge
-    relative-position-bias entry lifts the bound ~290 octaves above every row that does not use it."""
+    """The tensor-core attention skips the row maximum for heads whose logits are bounded a priori
+    ((scale + max|bias|) log2 e <= 60) and subtracts the exact row maximum for every other head.  Force the
+    exact path: one huge relative-position-bias entry (200, i.e. 288 octaves; it also exercises the fp16
+    bias operand of the one-hot MMA at a large magnitude)."""
     prefix, nh = "encoder_layer1.blocks.1.", 6
     sd = O.synthetic_state_dict("W1", seed=1)
     sd[prefix + "attn.relative_position_bias_table"] = sd[prefix + "attn.relative_position_bias_table"].clone()

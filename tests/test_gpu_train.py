@@ -45,3 +45,28 @@ def test_no_cpu_path():
     m = T.NGswin()
     with pytest.raises(Exception):
         train.L1TrainStep(m, graph=True)(torch.zeros(1, 1, 64, 64), torch.zeros(1, 1, 64, 64))
+
+
+def test_gan_graph_step_matches_eager():
+    """Full TransMAR-GAN step (BASELINE config 4) replayed from CUDA graphs vs launched eagerly."""
+    import transmar_gan_b200 as T
+    from transmar_gan_b200 import gan, train
+    from oracle import ngswin_oracle as O
+
+    def make(graph):
+        g = T.NGswin()
+        g.load_state_dict(O.synthetic_state_dict("W1", seed=1), strict=True)
+        torch.manual_seed(5)
+        d = gan.MultiScaleDiscriminator(2, 16, 5, 3, True)
+        d.apply(gan.weights_init)
+        return train.GANTrainStep(g.cuda().train(), d.cuda().train(), graph=graph)
+
+    ct = O.synthetic_input(2, 128, 128, seed=999)
+    ct[:, :, 30:40, 50:60] = 1.0
+    ct, real = ct.cuda(), O.synthetic_input(2, 128, 128, seed=1000).cuda()
+    se, sg = make(False), make(True)
+    le = [tuple(float(v) for v in se(ct, real)) for _ in range(3)]
+    lg = [tuple(float(v) for v in sg(ct, real)) for _ in range(3)]
+    assert abs(le[0][0] - lg[0][0]) < 1e-4 and abs(le[0][1] - lg[0][1]) < 1e-3 * abs(le[0][1]), (le, lg)
+    for (a, b), (c, d) in zip(le, lg):
+        assert abs(a - c) < 5e-3 * max(1.0, abs(a)) and abs(b - d) < 5e-3 * max(1.0, abs(b)), (le, lg)

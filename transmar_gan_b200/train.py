@@ -31,7 +31,7 @@ class L1TrainStep:
         self.model, self.group, self.use_graph = model, group, graph
         self.bucket = dp.FlatGradBucket(model.parameters())
         # capturable: the step counter lives on the device, so the update can be replayed from a graph
-        self.opt = torch.optim.Adam(model.parameters(), lr=lr, betas=betas, capturable=True)
+        self.opt = torch.optim.Adam(model.parameters(), lr=lr, betas=betas, capturable=bool(graph))
         self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
         self._warmup = max(int(warmup), 1)
         self._x = self._t = self._loss = None
@@ -103,3 +103,148 @@ class L1TrainStep:
             self.bucket.all_reduce(self.group)
             self._gB.replay()
         return self._loss
+
+
+class GANTrainStep:
+    """The full TransMAR-GAN step (training/train_combined.py:399-500; BASELINE config 4):
+
+        D step: fake = netG(ct) without grad; hinge loss of D(cat[ct, real]) / D(cat[ct, fake]); Adam (lrD)
+        G step: fake = netG(ct); logits, features = D(cat[ct, fake]); real features without grad;
+                L = 0.1 hinge_g + 10 FM + 1 metal-aware L1 + 0.2 metal-aware edge + 0.5 metal consistency
+                (+ 0.02 physics in the reference: torch-radon is an absent submodule there, so that term is
+                omitted); Adam (lrG)
+
+    = 2 generator forwards + 1 generator backward (this repo's kernels) and 4 discriminator forwards + 2
+    backwards (stock PyTorch / cuDNN, `gan.py`).  Data-parallel: one flat gradient bucket per network, each
+    all-reduced once per step.  During the G step the discriminator's parameters do not require grad (the
+    reference accumulates and then discards those gradients, `netD.zero_grad()` :404); results are identical.
+    With `graph=True` the step is replayed from CUDA graphs split at the two all-reduces.
+    `step(ct, real) -> (loss_D, loss_G)` as 0-d CUDA tensors."""
+
+    LAMBDAS = dict(adv=0.1, fm=10.0, rec=1.0, edge=0.2, metal=0.5)        # train_combined.py:108-113
+    METAL = dict(threshold=0.6, radius=5, beta=1.0, w_max=3.0)            # :116-119
+
+    def __init__(self, netG: torch.nn.Module, netD: torch.nn.Module, lrG: float = 1e-4, lrD: float = 2e-4,
+                 betas: Tuple[float, float] = (0.5, 0.999), graph: bool = True, group=None, warmup: int = 3):
+        from . import gan
+        self.gan, self.netG, self.netD, self.group, self.use_graph = gan, netG, netD, group, graph
+        self.bucketG = dp.FlatGradBucket(netG.parameters())
+        self.bucketD = dp.FlatGradBucket(netD.parameters())
+        self.optG = torch.optim.Adam(netG.parameters(), lr=lrG, betas=betas, capturable=bool(graph))
+        self.optD = torch.optim.Adam(netD.parameters(), lr=lrD, betas=betas, capturable=bool(graph))
+        self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+        self._warmup = max(int(warmup), 1)
+        self._graphs = None
+        self._ct = self._real = self._lD = self._lG = None
+
+    # -- the recipe, in the three pieces the all-reduces separate ---------------------------
+    def _d_fwd_bwd(self, ct, real):
+        self.bucketD.zero()
+        with torch.no_grad():
+            fake = self.netG(ct)
+        real_logits, _ = self.netD(torch.cat([ct, real], 1), return_features=False)
+        fake_logits, _ = self.netD(torch.cat([ct, fake], 1), return_features=False)
+        loss = self.gan.hinge_d_loss(real_logits, fake_logits)
+        loss.backward()
+        return loss.detach()
+
+    def _d_step_g_fwd_bwd(self, ct, real):
+        gan, lam, mt = self.gan, self.LAMBDAS, self.METAL
+        self.optD.step()
+        self.bucketG.zero()
+        for p in self.bucketD.params:
+            p.requires_grad_(False)
+        try:
+            fake = self.netG(ct)
+            fake_logits, fake_feats = self.netD(torch.cat([ct, fake], 1), return_features=True)
+            with torch.no_grad():
+                _, real_feats = self.netD(torch.cat([ct, real], 1), return_features=True)
+            M = gan.extract_metal_mask(ct, mt["threshold"])
+            w = gan.compute_weight_map(ct, mt["beta"], mt["radius"], mt["w_max"], mt["threshold"])
+            loss = (lam["adv"] * gan.hinge_g_loss(fake_logits)
+                    + lam["fm"] * gan.feature_matching_loss(real_feats, fake_feats)
+                    + lam["rec"] * gan.compute_metal_aware_loss(fake, real, ct, mt["beta"], mt["radius"],
+                                                                mt["w_max"], mt["threshold"])
+                    + lam["edge"] * gan.compute_metal_aware_edge_loss(fake, real, w)
+                    + lam["metal"] * gan.metal_consistency_loss(fake, real, M))
+            loss.backward()
+        finally:
+            for p in self.bucketD.params:
+                p.requires_grad_(True)
+        return loss.detach()
+
+    def _eager(self, ct, real):
+        lD = self._d_fwd_bwd(ct, real)
+        self.bucketD.all_reduce(self.group)
+        lG = self._d_step_g_fwd_bwd(ct, real)
+        self.bucketG.all_reduce(self.group)
+        self.optG.step()
+        return lD, lG
+
+    # -- capture --------------------------------------------------------------------------
+    def _snapshot(self):
+        mods = (self.netG, self.netD)
+        tensors = [t for m in mods for t in list(m.parameters()) + list(m.buffers())]
+        return tensors, [t.detach().clone() for t in tensors]
+
+    def _capture(self, ct, real):
+        if not ct.is_cuda:
+            raise RuntimeError("GANTrainStep: inputs must be CUDA tensors (there is no CPU path)")
+        self._ct, self._real = ct.clone(), real.clone()
+        fresh = not self.optG.state and not self.optD.state
+        if not fresh:
+            raise RuntimeError("GANTrainStep: capture the step before the first optimizer update")
+        tensors, snap = self._snapshot()           # warm-up must not count (weights, spectral-norm u/v, Adam)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(self._warmup):
+                self._eager(self._ct, self._real)
+        torch.cuda.current_stream().wait_stream(side)
+        with torch.no_grad():
+            for t, s in zip(tensors, snap):
+                t.copy_(s)
+            for opt in (self.optG, self.optD):
+                for st in opt.state.values():
+                    for v in st.values():
+                        if torch.is_tensor(v):
+                            v.zero_()
+        torch.cuda.synchronize()
+        g1 = torch.cuda.CUDAGraph()
+        if self.world == 1:
+            with torch.cuda.graph(g1):
+                self._lD = self._d_fwd_bwd(self._ct, self._real)
+                self._lG = self._d_step_g_fwd_bwd(self._ct, self._real)
+                self.optG.step()
+            self._graphs = (g1,)
+        else:
+            with torch.cuda.graph(g1):
+                self._lD = self._d_fwd_bwd(self._ct, self._real)
+            g2 = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g2, pool=g1.pool()):
+                self._lG = self._d_step_g_fwd_bwd(self._ct, self._real)
+            g3 = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g3, pool=g1.pool()):
+                self.optG.step()
+            self._graphs = (g1, g2, g3)
+
+    def __call__(self, ct: torch.Tensor, real: torch.Tensor):
+        if not self.use_graph:
+            return self._eager(ct, real)
+        if self._graphs is None:
+            self._capture(ct, real)
+        if ct.shape != self._ct.shape or real.shape != self._real.shape:
+            raise RuntimeError(f"GANTrainStep was captured for input {tuple(self._ct.shape)}; got {tuple(ct.shape)}")
+        if ct.data_ptr() != self._ct.data_ptr():
+            self._ct.copy_(ct, non_blocking=True)
+        if real.data_ptr() != self._real.data_ptr():
+            self._real.copy_(real, non_blocking=True)
+        if len(self._graphs) == 1:
+            self._graphs[0].replay()
+        else:
+            self._graphs[0].replay()
+            self.bucketD.all_reduce(self.group)
+            self._graphs[1].replay()
+            self.bucketG.all_reduce(self.group)
+            self._graphs[2].replay()
+        return self._lD, self._lG
