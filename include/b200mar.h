@@ -32,7 +32,7 @@ extern "C" {
 #endif
 
 /* ABI version, bumped whenever a signature changes. */
-int b200mar_abi_version(void);   /* 3 */
+int b200mar_abi_version(void);   /* 4 */
 /* Name of the last failing CUDA call of this thread (static string; never NULL). */
 const char* b200mar_last_error(void);
 /* 1 iff device `dev` is compute capability 10.x (B200); no kernels are launched. */
@@ -49,6 +49,12 @@ int b200mar_unigram_fwd(const float* z, const float* weight /*[32,2,8,8]*/,
 int b200mar_unigram_bwd(const float* z, const float* weight, const float* du,
                         float* dz, float* dweight, float* dbias,
                         int B, int ph, int pw, void* stream);
+/* Same, with one more addend: dz = dz + dz_add + scatter(du * weight).  dz_add (may be null) is the
+ * gradient of the within-stage sum z_{i+1} = z_i + out_i (components/encoder_decoder.py:138-141) that
+ * autograd would otherwise add with a separate elementwise pass.                              */
+int b200mar_unigram_bwd_add(const float* z, const float* weight, const float* du, float* dz,
+                            const float* dz_add, float* dweight, float* dbias, int B, int ph, int pw,
+                            void* stream);
 
 /* ---- a3: NGramContext.forward after the unigram conv (components/window_utils.py:43-90) --
  * seq_refl_win_pad (fwd/bwd), 2x2 sliding WindowAttention(dim 32, nh heads, window 2),

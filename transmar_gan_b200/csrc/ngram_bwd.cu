@@ -12,7 +12,8 @@ namespace b200mar {
 // gradients (8 columns x 2 channels per lane) live in registers for the whole kernel.
 __global__ void __launch_bounds__(kThreads) unigram_bwd_kernel(
     const float* __restrict__ z, const float* __restrict__ w, const float* __restrict__ du,
-    float* __restrict__ dz, float* __restrict__ dw, float* __restrict__ db, int B, int ph, int pw) {
+    float* __restrict__ dz, const float* __restrict__ dz_add, float* __restrict__ dw, float* __restrict__ db,
+    int B, int ph, int pw) {
   const int lane = threadIdx.x & 31, i = threadIdx.x >> 5;   // i = window row owned by this warp
   const int wh = ph / kWin, ww = pw / kWin;
   const int nwin = B * wh * ww;
@@ -34,6 +35,10 @@ __global__ void __launch_bounds__(kThreads) unigram_bwd_kernel(
     for (int j = 0; j < kWin; ++j) {
       zv[j] = *reinterpret_cast<const float2*>(z + base + j * kDim);
       dv[j] = *reinterpret_cast<const float2*>(dz + base + j * kDim);
+      if (dz_add) {                                   // gradient of the within-stage sum, folded in here
+        const float2 e = *reinterpret_cast<const float2*>(dz_add + base + j * kDim);
+        dv[j].x += e.x; dv[j].y += e.y;
+      }
     }
 #pragma unroll
     for (int j = 0; j < kWin; ++j) {
@@ -372,18 +377,24 @@ static int launch_ngram_ctx_bwd(const NgramParams& p, cudaStream_t st) {
 
 }  // namespace b200mar
 
-extern "C" int b200mar_unigram_bwd(const float* z, const float* weight, const float* du, float* dz,
-                                   float* dweight, float* dbias, int B, int ph, int pw,
-                                   void* stream) {
+extern "C" int b200mar_unigram_bwd_add(const float* z, const float* weight, const float* du, float* dz,
+                                       const float* dz_add, float* dweight, float* dbias, int B, int ph,
+                                       int pw, void* stream) {
   using namespace b200mar;
   if (ph % kWin || pw % kWin || ph < kWin || pw < kWin) return -1;
   const int nwin = B * (ph / kWin) * (pw / kWin);
   int grid = nwin;
   if (grid > 4 * sm_count()) grid = 4 * sm_count();
-  unigram_bwd_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(z, weight, du, dz, dweight, dbias,
+  unigram_bwd_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(z, weight, du, dz, dz_add, dweight, dbias,
                                                                   B, ph, pw);
   B200MAR_CHECK(cudaGetLastError());
   return 0;
+}
+
+extern "C" int b200mar_unigram_bwd(const float* z, const float* weight, const float* du, float* dz,
+                                   float* dweight, float* dbias, int B, int ph, int pw,
+                                   void* stream) {
+  return b200mar_unigram_bwd_add(z, weight, du, dz, nullptr, dweight, dbias, B, ph, pw, stream);
 }
 
 extern "C" int b200mar_ngram_ctx_bwd(const float* u, const float* dctx, const float* qkv_w,

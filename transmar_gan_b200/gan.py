@@ -13,7 +13,7 @@ Interface mirror (same names, arguments and state_dict keys as the reference):
     metal consistency).  `physics_loss_syn` (:222-253) needs torch-radon, which is an absent submodule of the
     reference: it is not restated and the step below runs with lambda_phys = 0.
   * `weights_init` - training/train_combined.py:207-217.
-Pinned against the reference by tests/test_gan_stock.py (fixtures from oracle/make_golden_gan.py).
+Pinned against the reference by tests/test_gan_stock.py (golden fixtures generated from the reference files).
 """
 from __future__ import annotations
 

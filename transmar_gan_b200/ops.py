@@ -39,6 +39,46 @@ def get_precision() -> str:
     return _PRECISION
 
 
+# Fused gradient accumulation.  Every backward kernel ACCUMULATES its parameter gradients with atomics, so
+# when a parameter already owns a contiguous fp32 `.grad` (e.g. a view into dp.FlatGradBucket, zeroed once
+# per step) the kernels can add straight into it and the autograd node returns None for that parameter:
+# no per-block zero-filled scratch, no 504 `grad += new` AccumulateGrad kernels per step.  Off by default
+# (plain autograd semantics: `torch.autograd.grad`, hooks on parameters); train.L1TrainStep /
+# train.GANTrainStep switch it on around their backward passes.
+_FUSED_GRAD_ACC = False
+
+
+class fused_grad_accumulation:
+    """Context manager: parameter gradients of the block kernels are accumulated directly into `p.grad`."""
+
+    def __init__(self, enabled: bool = True):
+        self.enabled = enabled
+
+    def __enter__(self):
+        global _FUSED_GRAD_ACC
+        self.prev, _FUSED_GRAD_ACC = _FUSED_GRAD_ACC, self.enabled
+        return self
+
+    def __exit__(self, *exc):
+        global _FUSED_GRAD_ACC
+        _FUSED_GRAD_ACC = self.prev
+        return False
+
+
+def _grad_targets(params):
+    """The parameters' own .grad tensors if every one of them can take atomic accumulation, else None."""
+    if not _FUSED_GRAD_ACC:
+        return None
+    out = []
+    for p in params:
+        g = p.grad
+        if (not p.requires_grad or g is None or g.dtype != torch.float32 or not g.is_contiguous()
+                or g.device != p.device or g.shape != p.shape):
+            return None
+        out.append(g)
+    return out
+
+
 def _stream() -> int:
     return torch.cuda.current_stream().cuda_stream
 
@@ -110,10 +150,13 @@ def _(z, weight, bias, ph, pw):
 
 @torch.library.custom_op(f"{_NS}::unigram_bwd", mutates_args=("dz", "dweight", "dbias"))
 def unigram_bwd(z: Tensor, weight: Tensor, du: Tensor, dz: Tensor, dweight: Tensor,
-                dbias: Tensor, ph: int, pw: int) -> None:
-    _chk(z, weight, du, dz, dweight, dbias)
-    _call("unigram_bwd", _p(z), _p(weight), _p(du), _p(dz), _p(dweight),
-                                                _p(dbias), z.shape[0], ph, pw, _stream())
+                dbias: Tensor, ph: int, pw: int, dz_add: Optional[Tensor] = None) -> None:
+    """dz += scatter(du * weight) (+ dz_add, the gradient of the within-stage sum, if given)."""
+    _chk(z, weight, du, dz, dweight, dbias, dz_add)
+    if dz_add is not None and dz_add.shape != dz.shape:
+        raise RuntimeError("unigram_bwd: dz_add must have the shape of dz")
+    _call("unigram_bwd_add", _p(z), _p(weight), _p(du), _p(dz), _p(dz_add), _p(dweight),
+          _p(dbias), z.shape[0], ph, pw, _stream())
 
 
 @torch.library.custom_op(f"{_NS}::ngram_ctx_fwd", mutates_args=())
@@ -585,13 +628,16 @@ class NSTBFunction(torch.autograd.Function):
             g = (g_out + g_zsum).contiguous()
         else:
             g = (g_out if have_out else g_zsum).contiguous()
-        # one zeroed flat buffer for all parameter gradients of the block
-        sizes = [p.numel() for p in P]
-        flat = torch.zeros(sum(sizes), device=z.device, dtype=torch.float32)
-        G, off = [], 0
-        for p, n in zip(P, sizes):
-            G.append(flat[off:off + n].view(p.shape))
-            off += n
+        G = _grad_targets(params)
+        fused = G is not None
+        if not fused:
+            # one zeroed flat buffer for all parameter gradients of the block
+            sizes = [p.numel() for p in P]
+            flat = torch.zeros(sum(sizes), device=z.device, dtype=torch.float32)
+            G, off = [], 0
+            for p, n in zip(P, sizes):
+                G.append(flat[off:off + n].view(p.shape))
+                off += n
         da = torch.empty_like(a)
         (mlp_bwd_tc if _PRECISION == "tf32" else mlp_bwd)(a, g, P[18:24], da, G[18:24])
         dz = torch.empty_like(z)
@@ -603,10 +649,9 @@ class NSTBFunction(torch.autograd.Function):
                                                                  nh, shift)
         du = torch.empty_like(u)
         ngram_ctx_bwd(u, dctx, P[2:10], du, G[2:10], nh)
-        unigram_bwd(z, P[0], du, dz, G[0], G[1], ph, pw)
-        if have_zs:
-            dz += g_zsum
-        return (dz, None, None, None, None, None, None, None, *G)
+        # dz = attention part + unigram part + gradient of the within-stage sum, in one pass
+        unigram_bwd(z, P[0], du, dz, G[0], G[1], ph, pw, g_zsum.contiguous() if have_zs else None)
+        return (dz, None, None, None, None, None, None, None, *([None] * len(G) if fused else G))
 
 
 class PatchMergeFunction(torch.autograd.Function):
@@ -622,10 +667,13 @@ class PatchMergeFunction(torch.autograd.Function):
         x, ln_w, ln_b, red_w = ctx_.saved_tensors
         ph, pw = ctx_.geom
         P = [ln_w.detach(), ln_b.detach(), red_w.detach()]
-        G = [torch.zeros_like(p) for p in P]
+        G = _grad_targets((ln_w, ln_b, red_w))
+        fused = G is not None
+        if not fused:
+            G = [torch.zeros_like(p) for p in P]
         dx = torch.empty_like(x)
         patch_merge_bwd(x, dy.contiguous(), P, dx, G, ph, pw)
-        return (dx, None, None, *G)
+        return (dx, None, None, *([None] * 3 if fused else G))
 
 
 class PixelShuffleCatFunction(torch.autograd.Function):

@@ -23,6 +23,11 @@ import torch.nn.functional as F
 from . import dp
 
 
+def _fused_acc():
+    from . import ops
+    return ops.fused_grad_accumulation(True)
+
+
 class L1TrainStep:
     """Callable `step(x, target) -> loss` (a 0-d CUDA tensor; reading it synchronises)."""
 
@@ -42,7 +47,8 @@ class L1TrainStep:
     def _fwd_bwd(self, x, t):
         self.bucket.zero()
         loss = F.l1_loss(self.model(x), t)
-        loss.backward()
+        with _fused_acc():                 # block kernels add their parameter gradients into the flat bucket
+            loss.backward()
         return loss.detach()
 
     def _eager(self, x, t):
@@ -167,7 +173,8 @@ class GANTrainStep:
                                                                 mt["w_max"], mt["threshold"])
                     + lam["edge"] * gan.compute_metal_aware_edge_loss(fake, real, w)
                     + lam["metal"] * gan.metal_consistency_loss(fake, real, M))
-            loss.backward()
+            with _fused_acc():
+                loss.backward()
         finally:
             for p in self.bucketD.params:
                 p.requires_grad_(True)
