@@ -299,6 +299,7 @@ def time_train(args, rank, world):
     t = (torch.rand(B, 1, S, S, generator=g) * 2 - 1).cuda()
     steps = max(args.steps, 5)
     res = {}
+    torch.backends.cudnn.benchmark = True            # the stock-PyTorch glue convolutions pick their fastest plan
     for mode in ("eager", "graph"):
         model = build_model().train()
         dp.broadcast_parameters(model)

@@ -599,8 +599,11 @@ class NSTBFunction(torch.autograd.Function):
             else:
                 a = attn_tc_fwd(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw, nh,
                                 shift, True)
-            out, zsum, _ = mlp_tc_fwd(a, z if want_zsum else None, P[18], P[19], P[20], P[21], P[22],
-                                      P[23], want_out, want_zsum, False, False)
+            # block tail on the TMA-fed kernel (2.5x the plain-load mlp_tc_fwd, bit-identical): z must
+            # survive for the backward, so the within-stage sum is a copy of z that the kernel's bulk
+            # reduce-add turns into z + out
+            zsum = z.clone() if want_zsum else z.new_empty(0)
+            out = mlp_tma_fwd_(a, zsum if want_zsum else None, P[18], P[19], P[20], P[21], P[22], P[23], want_out)
         else:
             a = attn_fwd(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw, nh, shift)
             out, zsum = mlp_fwd(a, z if want_zsum else None, P[18], P[19], P[20], P[21], P[22], P[23],

@@ -23,6 +23,14 @@ import torch.nn.functional as F
 from . import dp
 
 
+def _adam(params, lr, betas, graph):
+    """torch.optim.Adam as the reference configures it (training/train_combined.py:261-262); on CUDA
+    parameters the fused multi-tensor implementation, capturable when the step is replayed from a graph."""
+    params = list(params)
+    on_cuda = bool(params) and all(p.is_cuda for p in params)
+    return torch.optim.Adam(params, lr=lr, betas=betas, capturable=bool(graph), fused=True if on_cuda else None)
+
+
 def _fused_acc():
     from . import ops
     return ops.fused_grad_accumulation(True)
@@ -36,7 +44,7 @@ class L1TrainStep:
         self.model, self.group, self.use_graph = model, group, graph
         self.bucket = dp.FlatGradBucket(model.parameters())
         # capturable: the step counter lives on the device, so the update can be replayed from a graph
-        self.opt = torch.optim.Adam(model.parameters(), lr=lr, betas=betas, capturable=bool(graph))
+        self.opt = _adam(model.parameters(), lr, betas, graph)
         self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
         self._warmup = max(int(warmup), 1)
         self._x = self._t = self._loss = None
@@ -136,8 +144,8 @@ class GANTrainStep:
         self.gan, self.netG, self.netD, self.group, self.use_graph = gan, netG, netD, group, graph
         self.bucketG = dp.FlatGradBucket(netG.parameters())
         self.bucketD = dp.FlatGradBucket(netD.parameters())
-        self.optG = torch.optim.Adam(netG.parameters(), lr=lrG, betas=betas, capturable=bool(graph))
-        self.optD = torch.optim.Adam(netD.parameters(), lr=lrD, betas=betas, capturable=bool(graph))
+        self.optG = _adam(netG.parameters(), lrG, betas, graph)
+        self.optD = _adam(netD.parameters(), lrD, betas, graph)
         self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
         self._warmup = max(int(warmup), 1)
         self._graphs = None
