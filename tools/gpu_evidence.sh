@@ -12,7 +12,7 @@ python bench.py --steps 2 --warmup 3 --no-train --no-cpu --no-highres > $O/bench
 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file $O/launches_tc_b32.csv \
     python bench.py --steps 2 --warmup 3 --no-train --no-cpu --no-highres > $O/ncu_launches.log 2>&1
 python tools/gpu_train_prof.py 16 > $O/train_prof.log 2>&1 && \
-ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file $O/launches_train_b16x128.csv \
+ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off -c 4000 --csv --log-file $O/launches_train_b16x128.csv \
     python tools/gpu_train_prof.py 16 > $O/ncu_train.log 2>&1
 python tools/gpu_attn_prof.py 32 > $O/attn_prof.log 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:attn_tc_fwd -s 2 -c 1 -o $O/attn6 -f \

@@ -52,7 +52,16 @@ __global__ void __launch_bounds__(128) wgrad_tc_kernel(const __grid_constant__ C
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ uint64_t full[kWgStages], empty[kWgStages], done;
   __shared__ uint32_t slot;
+  __shared__ int sRowMap[256];                   // accumulator column -> row of dw / dbias (-1: padding)
   const int tid = threadIdx.x, lane = tid & 31;
+  for (int c = tid; c < p.cout; c += 128) {      // (per-head packed [q|k|v] columns: divisions done once, here)
+    int orow = c;
+    if (p.hs > 0) {
+      const int h = c / p.hs, r = c - h * p.hs, part = r / p.ps, d = r - part * p.ps;
+      orow = (part < 3 && d < p.hd) ? part * p.A + h * p.hd + d : -1;
+    }
+    sRowMap[c] = orow;
+  }
   const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
   // stage = [128][cin] IN tile | [128][8] ones (lane 64 of the accumulator = column sums of G) | [128][cout] G tile
   const uint32_t in_bytes = p.cin * 256, g_bytes = p.cout * 256, stage_bytes = in_bytes + 2048 + g_bytes;
@@ -112,18 +121,18 @@ __global__ void __launch_bounds__(128) wgrad_tc_kernel(const __grid_constant__ C
   if (my > 0) {
     const int ci = warp * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
-    for (int c0 = 0; c0 < p.cout; c0 += 16) {
+    // every CTA starts at a different 16-column group: the CTAs reach the flush together, and in the
+    // same order all of them would queue on the same L2 addresses
+    const int ngroup = p.cout >> 4;
+    const bool isw = ci < p.cin_valid, isb = ci == 64 && p.cin == 64 && p.dbias;
+    for (int it = 0; it < ngroup; ++it) {
+      const int c0 = ((it + (int)blockIdx.x) % ngroup) << 4;
       float v[16];
       tc::tmem_ld16(tbase + lane_addr + c0, v);
-      const bool isw = ci < p.cin_valid, isb = ci == 64 && p.cin == 64 && p.dbias;
       if (isw || isb) {
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
-          int orow = c0 + i;
-          if (p.hs > 0) {
-            const int h = orow / p.hs, r = orow - h * p.hs, part = r / p.ps, d = r - part * p.ps;
-            orow = (part < 3 && d < p.hd) ? part * p.A + h * p.hd + d : -1;
-          }
+          const int orow = sRowMap[c0 + i];
           if (orow >= 0) atomicAdd(isw ? p.dw + (size_t)orow * p.ld + ci : p.dbias + orow, v[i]);
         }
       }
