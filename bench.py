@@ -452,7 +452,7 @@ def main():
                      "frac": (ach_gbs / hbm_peak) if ach_gbs else None,
                      # dram__bytes_read.sum + dram__bytes_write.sum of one launch at the default
                      # config, from the ncu --set full capture summarised in profiles/r01_summary.md
-                     "traffic": 2.850e9 if (tc and B == 32 and S == 416) else None,
+                     "traffic": 4.438e9 if (tc and B == 32 and S == 416) else None,
                      "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({which})",
                      "algorithmic_bytes_per_launch": attn_bytes,
                      "avg_launch_ms": attn_avg, "launches_timed": len(attn_ms),
@@ -473,9 +473,11 @@ def main():
                      "whole_step_tflops": step_flops / (ms / K / 1e3) / 1e12,
                      "note": "bound = the larger of bytes/HBM-peak and flops/tensor-peak for this "
                              "kernel (0.43 ms vs 0.37 ms at batch 32 x 416^2); both fractions reported. "
-                             "ncu: 34 % issue-slot utilisation, 1.2 % tensor pipe - the kernel is held by "
-                             "the per-token fp32 epilogues (normalize, 384 exponentials, LayerNorm) on 12 "
-                             "resident warps per SM, see profiles/r01_summary.md"},
+                             "ncu: 42 % issue-slot utilisation, MUFU pipe 36 %, tensor pipe active 26 % of "
+                             "cycles - a tile is a latency chain of per-head MMA / barrier round trips and "
+                             "fp32 row epilogues (normalize, 384 exponentials, LayerNorm) on 16 resident warps "
+                             "per SM; traffic exceeds the algorithmic bytes by the per-head O row kept in "
+                             "local memory and L2 misses of the residual re-read, see profiles/r01_summary.md"},
         "cpu_baseline": cpu,
         "highres": highres,
         "train": train,
