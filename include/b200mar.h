@@ -223,6 +223,14 @@ int b200mar_patch_merge_bwd(const float* x, const float* dy,
                             float* dx, float* d_ln_w, float* d_ln_b, float* d_red_w,
                             int B, int ph, int pw, void* stream);
 
+/* ---- a12 / a13: LayerNorm(64) of the stage glue on the TRAINING path - SCDPBottleneck.norm
+ * (components/encoder_decoder.py:199-200) and NGswin.norm (ngswin.py:204); eps 1e-5, affine.
+ * x, y, dy, dx [n_tok,64].  bwd recomputes the row statistics from x; dweight += , dbias += .  */
+int b200mar_ln64_fwd(const float* x, const float* weight /*[64]*/, const float* bias /*[64]*/,
+                     float* y, long long n_tok, void* stream);
+int b200mar_ln64_bwd(const float* x, const float* dy, const float* weight, float* dx,
+                     float* dweight, float* dbias, long long n_tok, void* stream);
+
 /* ---- a12: pixel_shuffle_permute of the three encoder skips + channel concat
  * (components/encoder_decoder.py:159-164,191-192) ----------------------------------------
  * out[b, (h*s+a)*W + (w*s+c'), off_i + c] = x_i[b, h*pw_i + w, (c*s + a)*s + c'],  s = 2^i,

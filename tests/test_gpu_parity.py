@@ -359,3 +359,24 @@ def test_ngram_ctx_infer_matches_two_step(nh, B, ph, pw):
     got = ops.ngram_ctx_infer(z, *P, ph, pw, nh)
     assert got.shape == ref.shape
     assert (got - ref).abs().max().item() <= 2e-5 * max(1.0, ref.abs().max().item())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_tok", [1, 2, 33, 4096, 148 * 8 * 16 * 3 + 5])
+def test_ln64_fwd_bwd_vs_torch(n_tok):
+    """ln64.cu (LayerNorm(64) of the training-path stage glue: bottleneck.norm, NGswin.norm - ngswin.py:204)
+    against torch.nn.functional.layer_norm in float64, forward and backward, odd row counts included."""
+    import transmar_gan_b200 as T
+    g = torch.Generator().manual_seed(n_tok)
+    x = (torch.randn(n_tok, 64, generator=g) * 3 + 0.5).cuda().requires_grad_(True)
+    w = torch.randn(64, generator=g).cuda().requires_grad_(True)
+    b = torch.randn(64, generator=g).cuda().requires_grad_(True)
+    dy = torch.randn(n_tok, 64, generator=g).cuda()
+    y = T.ops.LayerNorm64Function.apply(x, w, b)
+    y.backward(dy)
+    x64, w64, b64 = (t.detach().double().requires_grad_(True) for t in (x, w, b))
+    y64 = torch.nn.functional.layer_norm(x64, (64,), w64, b64, 1e-5)
+    y64.backward(dy.double())
+    rel = lambda a, r: ((a.double() - r).norm() / r.norm().clamp_min(1e-30)).item()
+    assert rel(y, y64) < 1e-6
+    assert rel(x.grad, x64.grad) < 1e-5 and rel(w.grad, w64.grad) < 1e-5 and rel(b.grad, b64.grad) < 1e-5

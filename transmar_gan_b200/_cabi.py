@@ -51,6 +51,8 @@ SIGNATURES = {
     "b200mar_patch_merge_fwd": [_P] * 5 + [_I] * 3 + [_P],
     "b200mar_patch_merge_tc_fwd": [_P] * 5 + [_I] * 3 + [_P],
     "b200mar_patch_merge_bwd": [_P] * 9 + [_I] * 3 + [_P],
+    "b200mar_ln64_fwd": [_P] * 4 + [_L, _P],
+    "b200mar_ln64_bwd": [_P] * 6 + [_L, _P],
     "b200mar_pixel_shuffle_cat": [_P] * 4 + [_I] * 4 + [_P],
     "b200mar_shallow_tok_fwd": [_P] * 4 + [_I] * 3 + [_P],
     "b200mar_cascade_proj_fwd": [_P] * 7 + [_I] * 3 + [_P],

@@ -11,9 +11,9 @@ What runs where
   * CUDA kernels (this repo): unigram conv, n-gram context attention, fused shifted-window
     partition + cosine attention + LN1 + residual, fused MLP + LN2 + residual(+within-stage
     sum), PatchMerging, pixel-shuffle + concat — forward and backward.
-  * stock PyTorch/cuDNN inside the drop-in: shallow
-    3x3 conv, max-pools, cascade projections, bottleneck depthwise conv / pointwise linear,
-    final LayerNorm and the two reconstruction convs.
+  * stock PyTorch/cuDNN inside the drop-in's TRAINING path:
+    shallow 3x3 conv, max-pools, cascade projections, bottleneck depthwise conv / pointwise linear and
+    the two reconstruction convs (their LayerNorms run on ln64.cu; inference fuses all of this glue).
 There is NO CPU forward: calling the module on CPU tensors raises.
 """
 from __future__ import annotations
@@ -251,7 +251,7 @@ class SCDPBottleneck(nn.Module):
         x = cat.transpose(1, 2).reshape(B, self.concat_dim, H, W)
         x = F.gelu(self.depthwise(x))
         x = x.flatten(2).transpose(1, 2)
-        return self.norm(self.pointwise(x))
+        return ops.LayerNorm64Function.apply(self.pointwise(x), self.norm.weight, self.norm.bias)
 
 
 class Reconstruction(nn.Sequential):
@@ -355,7 +355,7 @@ class NGswin(nn.Module):
         e3_, _, _ = self.encoder_layer3(c2, np2)
         bt = self.bottleneck(shallow, [e1_, e2_, e3_], H, W)
         dec = self.decoder_layer1(bt + e1_, (H, W))
-        dec = self.norm(dec) + c0                                # global skip (ngswin.py:204)
+        dec = ops.LayerNorm64Function.apply(dec, self.norm.weight, self.norm.bias) + c0   # global skip (ngswin.py:204)
         img = dec.transpose(1, 2).reshape(B, self.dec_dim, H, W)
         out = self.to_target(img)
         return out[:, :, :H0, :W0]

@@ -679,6 +679,43 @@ class PatchMergeFunction(torch.autograd.Function):
         return (dx, None, None, *([None] * 3 if fused else G))
 
 
+def ln64_fwd(x: Tensor, weight: Tensor, bias: Tensor) -> Tensor:
+    """LayerNorm over the last (64-wide) dimension, eps 1e-5, affine (training-path stage glue)."""
+    _chk(x, weight, bias)
+    if x.shape[-1] != 64:
+        raise RuntimeError("ln64_fwd: the last dimension must be 64")
+    y = torch.empty_like(x)
+    _call("ln64_fwd", _p(x), _p(weight), _p(bias), _p(y), x.numel() // 64, _stream())
+    return y
+
+
+def ln64_bwd(x: Tensor, dy: Tensor, weight: Tensor, dx: Tensor, dweight: Tensor, dbias: Tensor) -> None:
+    """dx written; dweight += , dbias += (atomics)."""
+    _chk(x, dy, weight, dx, dweight, dbias)
+    _call("ln64_bwd", _p(x), _p(dy), _p(weight), _p(dx), _p(dweight), _p(dbias), x.numel() // 64, _stream())
+
+
+class LayerNorm64Function(torch.autograd.Function):
+    """nn.LayerNorm(64) of the stage glue (bottleneck.norm, NGswin.norm) on ln64.cu."""
+
+    @staticmethod
+    def forward(ctx_, x, weight, bias):
+        x = x.contiguous()
+        ctx_.save_for_backward(x, weight, bias)
+        return ln64_fwd(x, weight.detach(), bias.detach())
+
+    @staticmethod
+    def backward(ctx_, dy):
+        x, weight, bias = ctx_.saved_tensors
+        G = _grad_targets((weight, bias))
+        fused = G is not None
+        if not fused:
+            G = [torch.zeros_like(weight), torch.zeros_like(bias)]
+        dx = torch.empty_like(x)
+        ln64_bwd(x, dy.contiguous(), weight.detach(), dx, G[0], G[1])
+        return (dx, *((None, None) if fused else G))
+
+
 class PixelShuffleCatFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx_, x0, x1, x2, H, W):
