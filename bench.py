@@ -132,6 +132,28 @@ def cpu_forward_time(size: int, runs: int):
     return sum(ts) / len(ts), threads, len(ts)
 
 
+def gpu_eager_forward_time(size: int, batch: int = 4, runs: int = 3):
+    """The same oracle port (= the reference's PyTorch op sequence, materialised logits / masks / partition
+    copies and all) run eagerly in fp32 ON THE B200: the stock-PyTorch GPU baseline SURVEY.md §8d asks for
+    beside the CPU one.  Part of the cpu_baseline leg (reported baseline, never on the product path)."""
+    from oracle import ngswin_oracle as O
+    sd = {k: v.cuda() for k, v in O.synthetic_state_dict("W1", seed=1).items()}
+    x = O.synthetic_input(batch, size, size, seed=999).cuda()
+    with torch.no_grad():
+        for _ in range(2):
+            O.ngswin_forward(x, sd)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(runs):
+            O.ngswin_forward(x, sd)
+        e1.record()
+        torch.cuda.synchronize()
+    del sd, x
+    torch.cuda.empty_cache()
+    return e0.elapsed_time(e1) / 1e3 / runs / batch      # seconds per slice
+
+
 # ------------------------------------------------------------------------------ reference arm
 def run_reference(args):
     """`--impl reference`: the reference's CPU implementation of the path.  The reference is a
@@ -416,6 +438,11 @@ def main():
         cpu = {"value": 1.0 / sec, "unit": UNIT, "cores": threads, "kind": "port",
                "sample": f"{runs} timed 1-slice {args.size}x{args.size} forwards of the oracle port "
                          f"(oracle/ngswin_oracle.py, torch CPU fp32, {threads} threads), 1 warm-up"}
+        gsec = gpu_eager_forward_time(args.size)
+        cpu["gpu_eager"] = {"value": 1.0 / gsec, "unit": UNIT,
+                            "sample": f"the same oracle port (the reference's stock-PyTorch op sequence) run "
+                                      f"eagerly in fp32 on this B200, 3 timed batch-4 {args.size}x{args.size} "
+                                      "forwards, 2 warm-ups"}
     if rank != 0:
         return
     K, B, S = args.steps, args.batch, args.size

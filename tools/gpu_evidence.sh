@@ -8,6 +8,7 @@ mkdir -p $O
 python -m pytest tests -m gpu -x -q > $O/tests.log 2>&1; tail -2 $O/tests.log
 python bench.py > $O/bench.json 2> $O/bench.err || exit 1
 python bench.py --impl reference --steps 2 --warmup 1 > $O/bench_reference.json 2> $O/bench_reference.err
+python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke.log 2>&1; tail -3 $O/smoke.log
 python bench.py --steps 2 --warmup 3 --no-train --no-cpu --no-highres > $O/bench_short.json 2>/dev/null && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file $O/launches_tc_b32.csv \
     python bench.py --steps 2 --warmup 3 --no-train --no-cpu --no-highres > $O/ncu_launches.log 2>&1
