@@ -387,17 +387,17 @@ def time_train_gan(args, rank, world):
     torch.backends.cudnn.allow_tf32 = True
     res = {}
     try:
-        for mode in ("eager", "graph"):
+        for mode in ("eager", "graph", "graph+reuse_fake"):
             netG = build_model().train()
             torch.manual_seed(4321)
             netD = gan.MultiScaleDiscriminator(2, 64, 5, 3, True).cuda().train()
             netD.apply(gan.weights_init)
             dp.broadcast_parameters(netG)
             dp.broadcast_parameters(netD)
-            step = train.GANTrainStep(netG, netD, graph=(mode == "graph"))
+            step = train.GANTrainStep(netG, netD, graph=(mode != "eager"), reuse_fake=mode.endswith("reuse_fake"))
             ops.profile.reset()
             step(ct, real)
-            per_step = ops.profile.launches // (step._warmup + 1 if mode == "graph" else 1)
+            per_step = ops.profile.launches // (step._warmup + 1 if mode != "eager" else 1)
             for _ in range(max(args.warmup, 3)):
                 step(ct, real)
             barrier(world)
@@ -413,13 +413,16 @@ def time_train_gan(args, rank, world):
             del step, netG, netD
     finally:
         torch.backends.cudnn.allow_tf32 = old
-    mode = min(res, key=lambda k: res[k][0])
+    mode = min(("eager", "graph"), key=lambda k: res[k][0])      # the headline is the reference's two-forward recipe
     ms, launches, lD, lG = res[mode]
     return {"steps_per_s": 1e3 / ms, "slices_per_s": world * B * 1e3 / ms, "ms_per_step": ms, "mode": mode,
             "eager_ms_per_step": res["eager"][0], "graph_ms_per_step": res["graph"][0], "per_gpu_batch": B, "size": S,
+            "reuse_fake_ms_per_step": res["graph+reuse_fake"][0],
+            "reuse_fake_note": "opt-in GANTrainStep(reuse_fake=True): one generator forward per step, the D step "
+                               "sees fake.detach() (SURVEY.md 8f rank 3); not the headline",
             "recipe": "D step (G fwd no-grad, 2 D fwd, hinge, bwd, Adam) + G step (G fwd, 2 D fwd, hinge + FM + "
-                      "metal-aware L1/edge + metal consistency, bwd, Adam); lambda_phys = 0 (torch-radon absent); "
-                      "train.GANTrainStep, eager launches and CUDA-graph replay both timed",
+                      "metal-aware L1/edge + metal consistency from one fused kernel, bwd, Adam); lambda_phys = 0 "
+                      "(torch-radon absent); train.GANTrainStep, eager launches and CUDA-graph replay both timed",
             "allreduce_bytes": list(nbytes) if world > 1 else [0, 0],
             "gpu_launches_per_step": launches, "final_loss_D": lD, "final_loss_G": lG}
 

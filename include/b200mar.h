@@ -32,7 +32,7 @@ extern "C" {
 #endif
 
 /* ABI version, bumped whenever a signature changes. */
-int b200mar_abi_version(void);   /* 4 */
+int b200mar_abi_version(void);   /* 5 */
 /* Name of the last failing CUDA call of this thread (static string; never NULL). */
 const char* b200mar_last_error(void);
 /* 1 iff device `dev` is compute capability 10.x (B200); no kernels are launched. */
@@ -230,6 +230,19 @@ int b200mar_ln64_fwd(const float* x, const float* weight /*[64]*/, const float* 
                      float* y, long long n_tok, void* stream);
 int b200mar_ln64_bwd(const float* x, const float* dy, const float* weight, float* dx,
                      float* dweight, float* dbias, long long n_tok, void* stream);
+
+/* ---- the image-space terms of the generator loss, values and dL/dfake in one
+ * pass over (fake, real, ct), each [nimg, H, W] fp32 (losses/gan_losses.py:48-219 as combined in
+ * training/train_combined.py:456-485):
+ *   M = ct > threshold;  w = min(1 + beta * maxpool_{2r+1}(M), w_max);
+ *   rec = mean|w (fake-real)|;  edge = mean w (|gx(fake)-gx(real)| + |gy(fake)-gy(real)|) with forward
+ *   differences whose last column / row is replicated;  metal = mean|M (fake-real)|.
+ * sums4 += {rec, edge, metal, lam_rec*rec + lam_edge*edge + lam_metal*metal} (zeroed by the caller);
+ * dfake = d(sums4[3]) / d(fake), written (not accumulated).  H, W >= 2, 0 <= radius <= 32.   */
+int b200mar_metal_losses(const float* fake, const float* real, const float* ct, float* dfake,
+                         float* sums4, int nimg, int H, int W, int radius, float threshold,
+                         float beta, float w_max, float lam_rec, float lam_edge, float lam_metal,
+                         void* stream);
 
 /* ---- a12: pixel_shuffle_permute of the three encoder skips + channel concat
  * (components/encoder_decoder.py:159-164,191-192) ----------------------------------------

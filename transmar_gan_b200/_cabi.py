@@ -22,6 +22,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 _P = ctypes.c_void_p
 _I = ctypes.c_int
 _L = ctypes.c_longlong
+_F = ctypes.c_float
 
 # name -> argtypes ; every function returns int unless listed in _RESTYPES
 SIGNATURES = {
@@ -53,6 +54,7 @@ SIGNATURES = {
     "b200mar_patch_merge_bwd": [_P] * 9 + [_I] * 3 + [_P],
     "b200mar_ln64_fwd": [_P] * 4 + [_L, _P],
     "b200mar_ln64_bwd": [_P] * 6 + [_L, _P],
+    "b200mar_metal_losses": [_P] * 5 + [_I] * 4 + [_F] * 6 + [_P],
     "b200mar_pixel_shuffle_cat": [_P] * 4 + [_I] * 4 + [_P],
     "b200mar_shallow_tok_fwd": [_P] * 4 + [_I] * 3 + [_P],
     "b200mar_cascade_proj_fwd": [_P] * 7 + [_I] * 3 + [_P],

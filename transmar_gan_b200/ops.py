@@ -716,6 +716,46 @@ class LayerNorm64Function(torch.autograd.Function):
         return (dx, *((None, None) if fused else G))
 
 
+def metal_losses_(fake: Tensor, real: Tensor, ct: Tensor, dfake: Tensor, sums4: Tensor, lam_rec: float,
+                  lam_edge: float, lam_metal: float, threshold: float, beta: float, radius: int, w_max: float) -> None:
+    """sums4 += {rec, edge, metal, weighted total}; dfake = d total / d fake (metal_loss.cu)."""
+    _chk(fake, real, ct, dfake, sums4)
+    if fake.dim() < 2 or real.shape != fake.shape or ct.shape != fake.shape or dfake.shape != fake.shape:
+        raise RuntimeError("metal_losses: fake, real, ct and dfake must have the same [..., H, W] shape")
+    if sums4.numel() != 4:
+        raise RuntimeError("metal_losses: sums4 must hold 4 floats")
+    H, W = fake.shape[-2:]
+    _call("metal_losses", _p(fake), _p(real), _p(ct), _p(dfake), _p(sums4), fake.numel() // (H * W), H, W,
+          int(radius), float(threshold), float(beta), float(w_max), float(lam_rec), float(lam_edge),
+          float(lam_metal), _stream())
+
+
+class MetalLossFunction(torch.autograd.Function):
+    """total, parts = apply(fake, real, ct, lam_rec, lam_edge, lam_metal, threshold, beta, radius, w_max):
+    `total` = lam_rec * metal-aware L1 + lam_edge * metal-aware edge + lam_metal * metal consistency
+    (losses/gan_losses.py:115-219 with the weights of training/train_combined.py:456-485) as a 0-d tensor,
+    `parts` = the three unweighted means (not differentiable; for logging).  One kernel produces the values
+    and d total / d fake; backward is one multiply.  `real` and `ct` get no gradient (the reference never
+    asks for one)."""
+
+    @staticmethod
+    def forward(ctx_, fake, real, ct, lam_rec, lam_edge, lam_metal, threshold, beta, radius, w_max):
+        fake, real, ct = fake.contiguous(), real.contiguous(), ct.contiguous()
+        sums = torch.zeros(4, device=fake.device, dtype=torch.float32)
+        dfake = torch.empty_like(fake)
+        metal_losses_(fake.detach(), real.detach(), ct.detach(), dfake, sums, lam_rec, lam_edge, lam_metal,
+                      threshold, beta, radius, w_max)
+        ctx_.save_for_backward(dfake)
+        total, parts = sums[3].clone(), sums[:3].clone()    # not views: two independent outputs
+        ctx_.mark_non_differentiable(parts)
+        return total, parts
+
+    @staticmethod
+    def backward(ctx_, g_total, _g_parts):
+        (dfake,) = ctx_.saved_tensors
+        return (dfake * g_total,) + (None,) * 9
+
+
 class PixelShuffleCatFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx_, x0, x1, x2, H, W):

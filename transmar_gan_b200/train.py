@@ -135,15 +135,28 @@ class GANTrainStep:
     all-reduced once per step.  During the G step the discriminator's parameters do not require grad (the
     reference accumulates and then discards those gradients, `netD.zero_grad()` :404); results are identical.
     With `graph=True` the step is replayed from CUDA graphs split at the two all-reduces.
-    `step(ct, real) -> (loss_D, loss_G)` as 0-d CUDA tensors."""
+    `step(ct, real) -> (loss_D, loss_G)` as 0-d CUDA tensors.
+
+    `fused_losses` (default: on for CUDA modules): the metal-aware L1, edge and consistency terms and their
+    gradient come from ONE kernel (`ops.MetalLossFunction`) instead of six stock
+    pooling / elementwise passes and their backward; same arithmetic, summation order aside.
+    `reuse_fake` (default off): the generator runs ONCE per step, with grad, and the
+    D step sees `fake.detach()`.  The generator's weights do not change between the two forwards of the
+    reference recipe and it has no dropout, so the result is the same function of the same weights; only the
+    kernels differ (the no-grad forward runs the inference kernels), hence opt-in."""
 
     LAMBDAS = dict(adv=0.1, fm=10.0, rec=1.0, edge=0.2, metal=0.5)        # train_combined.py:108-113
     METAL = dict(threshold=0.6, radius=5, beta=1.0, w_max=3.0)            # :116-119
 
     def __init__(self, netG: torch.nn.Module, netD: torch.nn.Module, lrG: float = 1e-4, lrD: float = 2e-4,
-                 betas: Tuple[float, float] = (0.5, 0.999), graph: bool = True, group=None, warmup: int = 3):
+                 betas: Tuple[float, float] = (0.5, 0.999), graph: bool = True, group=None, warmup: int = 3,
+                 fused_losses: Optional[bool] = None, reuse_fake: bool = False):
         from . import gan
         self.gan, self.netG, self.netD, self.group, self.use_graph = gan, netG, netD, group, graph
+        on_cuda = next(netG.parameters()).is_cuda
+        self.fused_losses = on_cuda if fused_losses is None else bool(fused_losses)
+        self.reuse_fake = bool(reuse_fake)
+        self._fake = None
         self.bucketG = dp.FlatGradBucket(netG.parameters())
         self.bucketD = dp.FlatGradBucket(netD.parameters())
         self.optG = _adam(netG.parameters(), lrG, betas, graph)
@@ -156,8 +169,12 @@ class GANTrainStep:
     # -- the recipe, in the three pieces the all-reduces separate ---------------------------
     def _d_fwd_bwd(self, ct, real):
         self.bucketD.zero()
-        with torch.no_grad():
-            fake = self.netG(ct)
+        if self.reuse_fake:
+            self._fake = self.netG(ct)             # with grad: the G step below backpropagates through it
+            fake = self._fake.detach()
+        else:
+            with torch.no_grad():
+                fake = self.netG(ct)
         real_logits, _ = self.netD(torch.cat([ct, real], 1), return_features=False)
         fake_logits, _ = self.netD(torch.cat([ct, fake], 1), return_features=False)
         loss = self.gan.hinge_d_loss(real_logits, fake_logits)
@@ -171,18 +188,27 @@ class GANTrainStep:
         for p in self.bucketD.params:
             p.requires_grad_(False)
         try:
-            fake = self.netG(ct)
+            fake = self._fake if self.reuse_fake else self.netG(ct)
+            self._fake = None
             fake_logits, fake_feats = self.netD(torch.cat([ct, fake], 1), return_features=True)
             with torch.no_grad():
                 _, real_feats = self.netD(torch.cat([ct, real], 1), return_features=True)
-            M = gan.extract_metal_mask(ct, mt["threshold"])
-            w = gan.compute_weight_map(ct, mt["beta"], mt["radius"], mt["w_max"], mt["threshold"])
             loss = (lam["adv"] * gan.hinge_g_loss(fake_logits)
-                    + lam["fm"] * gan.feature_matching_loss(real_feats, fake_feats)
-                    + lam["rec"] * gan.compute_metal_aware_loss(fake, real, ct, mt["beta"], mt["radius"],
-                                                                mt["w_max"], mt["threshold"])
-                    + lam["edge"] * gan.compute_metal_aware_edge_loss(fake, real, w)
-                    + lam["metal"] * gan.metal_consistency_loss(fake, real, M))
+                    + lam["fm"] * gan.feature_matching_loss(real_feats, fake_feats))
+            if self.fused_losses:
+                from . import ops
+                image_terms, _ = ops.MetalLossFunction.apply(
+                    fake, real, ct, lam["rec"], lam["edge"], lam["metal"], mt["threshold"], mt["beta"],
+                    mt["radius"], mt["w_max"])
+                loss = loss + image_terms
+            else:
+                M = gan.extract_metal_mask(ct, mt["threshold"])
+                w = gan.compute_weight_map(ct, mt["beta"], mt["radius"], mt["w_max"], mt["threshold"])
+                loss = (loss
+                        + lam["rec"] * gan.compute_metal_aware_loss(fake, real, ct, mt["beta"], mt["radius"],
+                                                                    mt["w_max"], mt["threshold"])
+                        + lam["edge"] * gan.compute_metal_aware_edge_loss(fake, real, w)
+                        + lam["metal"] * gan.metal_consistency_loss(fake, real, M))
             with _fused_acc():
                 loss.backward()
         finally:
