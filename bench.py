@@ -16,6 +16,7 @@ from __future__ import annotations
 
 import argparse
 import json
+import math
 import os
 import subprocess
 import sys
@@ -387,14 +388,19 @@ def time_train_gan(args, rank, world):
     torch.backends.cudnn.allow_tf32 = True
     res = {}
     try:
-        for mode in ("eager", "graph", "graph+reuse_fake"):
+        for mode in ("eager", "graph", "graph+reuse_fake", "graph+physics"):
             netG = build_model().train()
             torch.manual_seed(4321)
             netD = gan.MultiScaleDiscriminator(2, 64, 5, 3, True).cuda().train()
             netD.apply(gan.weights_init)
             dp.broadcast_parameters(netG)
             dp.broadcast_parameters(netD)
-            step = train.GANTrainStep(netG, netD, graph=(mode != "eager"), reuse_fake=mode.endswith("reuse_fake"))
+            proj = None
+            if mode.endswith("physics"):                   # train_combined.py:269-271: 180 angles over [0, pi]
+                from transmar_gan_b200 import radon
+                proj = radon.Radon(S, torch.linspace(0, math.pi, 180))
+            step = train.GANTrainStep(netG, netD, graph=(mode != "eager"), reuse_fake=mode.endswith("reuse_fake"),
+                                      projector=proj)
             ops.profile.reset()
             step(ct, real)
             per_step = ops.profile.launches // (step._warmup + 1 if mode != "eager" else 1)
@@ -418,6 +424,10 @@ def time_train_gan(args, rank, world):
     return {"steps_per_s": 1e3 / ms, "slices_per_s": world * B * 1e3 / ms, "ms_per_step": ms, "mode": mode,
             "eager_ms_per_step": res["eager"][0], "graph_ms_per_step": res["graph"][0], "per_gpu_batch": B, "size": S,
             "reuse_fake_ms_per_step": res["graph+reuse_fake"][0],
+            "with_physics_ms_per_step": res["graph+physics"][0],
+            "with_physics_note": "GANTrainStep(projector=radon.Radon(128, 180 angles)), lambda_phys = 0.02: the "
+                                 "reference's full loss on this repo's Radon kernels (torch-radon restated, parity "
+                                 "unpinned); not the headline",
             "reuse_fake_note": "opt-in GANTrainStep(reuse_fake=True): one generator forward per step, the D step "
                                "sees fake.detach() (SURVEY.md 8f rank 3); not the headline",
             "recipe": "D step (G fwd no-grad, 2 D fwd, hinge, bwd, Adam) + G step (G fwd, 2 D fwd, hinge + FM + "

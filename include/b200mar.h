@@ -32,7 +32,7 @@ extern "C" {
 #endif
 
 /* ABI version, bumped whenever a signature changes. */
-int b200mar_abi_version(void);   /* 5 */
+int b200mar_abi_version(void);   /* 6 */
 /* Name of the last failing CUDA call of this thread (static string; never NULL). */
 const char* b200mar_last_error(void);
 /* 1 iff device `dev` is compute capability 10.x (B200); no kernels are launched. */
@@ -243,6 +243,20 @@ int b200mar_metal_losses(const float* fake, const float* real, const float* ct, 
                          float* sums4, int nimg, int H, int W, int radius, float threshold,
                          float beta, float w_max, float lam_rec, float lam_edge, float lam_metal,
                          void* stream);
+
+/* ---- parallel-beam Radon projector of the physics-consistency loss
+ * (training/train_combined.py:269-272 `Radon(PATCH_SIZE, angles)`; losses/gan_losses.py:222-253
+ * `projector.forward`).  torch-radon is an empty submodule of the reference: restated from its
+ * published algorithm, parity unpinned.
+ * fwd: img [nimg,H,W] -> sino [nimg,n_angles,det_count]; ray-driven, detector k on the line
+ *      x cos th + y sin th = (k - det_count/2 + 1/2) * det_spacing (image-centred coordinates),
+ *      <= 1-pixel steps sampled at their midpoints with bilinear interpolation, zero outside.
+ * bwd: sino -> img, pixel-driven backprojection with linear detector interpolation (what
+ *      torch-radon's autograd backward runs).  angles: device float[n_angles], n_angles <= 1024. */
+int b200mar_radon_fwd(const float* img, const float* angles, float* sino, int nimg, int H, int W,
+                      int n_angles, int det_count, float det_spacing, void* stream);
+int b200mar_radon_bwd(const float* sino, const float* angles, float* img, int nimg, int H, int W,
+                      int n_angles, int det_count, float det_spacing, void* stream);
 
 /* ---- a12: pixel_shuffle_permute of the three encoder skips + channel concat
  * (components/encoder_decoder.py:159-164,191-192) ----------------------------------------

@@ -55,6 +55,8 @@ SIGNATURES = {
     "b200mar_ln64_fwd": [_P] * 4 + [_L, _P],
     "b200mar_ln64_bwd": [_P] * 6 + [_L, _P],
     "b200mar_metal_losses": [_P] * 5 + [_I] * 4 + [_F] * 6 + [_P],
+    "b200mar_radon_fwd": [_P] * 3 + [_I] * 5 + [_F, _P],
+    "b200mar_radon_bwd": [_P] * 3 + [_I] * 5 + [_F, _P],
     "b200mar_pixel_shuffle_cat": [_P] * 4 + [_I] * 4 + [_P],
     "b200mar_shallow_tok_fwd": [_P] * 4 + [_I] * 3 + [_P],
     "b200mar_cascade_proj_fwd": [_P] * 7 + [_I] * 3 + [_P],

@@ -10,8 +10,9 @@ Interface mirror (same names, arguments and state_dict keys as the reference):
     to one logit channel, spectral normalisation on every convolution; scale s sees the input average-
     pooled s times.  `forward(x, return_features)` -> (list of logits, list of lists of features | None).
   * loss functions of losses/gan_losses.py:6-219 (hinge, feature matching, metal-aware L1 / edge,
-    metal consistency).  `physics_loss_syn` (:222-253) needs torch-radon, which is an absent submodule of the
-    reference: it is not restated and the step below runs with lambda_phys = 0.
+    metal consistency) and `physics_loss_syn` (:222-253), which takes the projector as an argument:
+    torch-radon is an absent submodule of the reference, `transmar_gan_b200.radon.Radon` is
+    this repo's projector with the same interface.
   * `weights_init` - training/train_combined.py:207-217.
 Pinned against the reference by tests/test_gan_stock.py (golden fixtures generated from the reference files).
 """
@@ -138,3 +139,11 @@ def compute_metal_aware_edge_loss(fake, real_cpu, w):
 
 def metal_consistency_loss(fake, real, M):
     return (M * (fake - real)).abs().mean()
+
+
+def physics_loss_syn(fake, real_cpu, M, projector):
+    """mean((1 - [P(M) > 0]) * |P(fake) - P(real)|): rays that cross metal do not count."""
+    sq = lambda t: t.squeeze(1) if t.shape[1] == 1 else t
+    proj_fake, proj_clean = projector.forward(sq(fake)), projector.forward(sq(real_cpu))
+    Mp = (projector.forward(sq(M)) > 0).float()
+    return ((1.0 - Mp) * (proj_fake - proj_clean).abs()).mean()

@@ -143,19 +143,23 @@ class GANTrainStep:
     `reuse_fake` (default off): the generator runs ONCE per step, with grad, and the
     D step sees `fake.detach()`.  The generator's weights do not change between the two forwards of the
     reference recipe and it has no dropout, so the result is the same function of the same weights; only the
-    kernels differ (the no-grad forward runs the inference kernels), hence opt-in."""
+    kernels differ (the no-grad forward runs the inference kernels), hence opt-in.
+    `projector` (default None = the term is left out): a `radon.Radon(size, angles)`; the G loss gains
+    `lambda_phys * physics_loss_syn(fake, real, M, projector)` as at train_combined.py:480,495."""
 
     LAMBDAS = dict(adv=0.1, fm=10.0, rec=1.0, edge=0.2, metal=0.5)        # train_combined.py:108-113
     METAL = dict(threshold=0.6, radius=5, beta=1.0, w_max=3.0)            # :116-119
 
     def __init__(self, netG: torch.nn.Module, netD: torch.nn.Module, lrG: float = 1e-4, lrD: float = 2e-4,
                  betas: Tuple[float, float] = (0.5, 0.999), graph: bool = True, group=None, warmup: int = 3,
-                 fused_losses: Optional[bool] = None, reuse_fake: bool = False):
+                 fused_losses: Optional[bool] = None, reuse_fake: bool = False, projector=None,
+                 lambda_phys: float = 0.02):
         from . import gan
         self.gan, self.netG, self.netD, self.group, self.use_graph = gan, netG, netD, group, graph
         on_cuda = next(netG.parameters()).is_cuda
         self.fused_losses = on_cuda if fused_losses is None else bool(fused_losses)
         self.reuse_fake = bool(reuse_fake)
+        self.projector, self.lambda_phys = projector, float(lambda_phys)      # train_combined.py:113,269-272
         self._fake = None
         self.bucketG = dp.FlatGradBucket(netG.parameters())
         self.bucketD = dp.FlatGradBucket(netD.parameters())
@@ -209,6 +213,9 @@ class GANTrainStep:
                                                                     mt["w_max"], mt["threshold"])
                         + lam["edge"] * gan.compute_metal_aware_edge_loss(fake, real, w)
                         + lam["metal"] * gan.metal_consistency_loss(fake, real, M))
+            if self.projector is not None and self.lambda_phys != 0.0:
+                M = gan.extract_metal_mask(ct, mt["threshold"])
+                loss = loss + self.lambda_phys * gan.physics_loss_syn(fake, real, M, self.projector)
             with _fused_acc():
                 loss.backward()
         finally:
