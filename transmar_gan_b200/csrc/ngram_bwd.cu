@@ -79,7 +79,9 @@ __global__ void __launch_bounds__(kThreads) ngram_ctx_bwd_kernel(NgramParams p) 
   constexpr int HD = L::HD, NA = L::NA;
   extern __shared__ __align__(16) float smem[];
   load_ngram_weights<NH>(smem, p);
-  for (int i = threadIdx.x; i < LB::oScratch - LB::oDWqkv; i += blockDim.x) smem[LB::oDWqkv + i] = 0.f;
+  // zero the gradient accumulators AND the per-warp scratch (pad rows / columns that are never written take
+  // part in the block-wide outer products below)
+  for (int i = threadIdx.x; i < LB::kFloats - LB::oDWqkv; i += blockDim.x) smem[LB::oDWqkv + i] = 0.f;
   __syncthreads();
   const float* sWqkv = smem + L::oWqkv;
   const float* sBqkv = smem + L::oBqkv;
@@ -88,9 +90,6 @@ __global__ void __launch_bounds__(kThreads) ngram_ctx_bwd_kernel(NgramParams p) 
   const float* sWm = smem + L::oWm;
   const float* sScale = smem + L::oScale;
   const float* sBias = smem + L::oBias;
-  float* sDWqkv = smem + LB::oDWqkv;
-  float* sDWp = smem + LB::oDWp;
-  float* sDWm = smem + LB::oDWm;
   float* sDBias = smem + LB::oDBias;
   float* sDScale = smem + LB::oDScale;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -104,10 +103,26 @@ __global__ void __launch_bounds__(kThreads) ngram_ctx_bwd_kernel(NgramParams p) 
   float* sDqkv = sDom + 64;
 
   float dbm[2] = {0.f, 0.f}, dbp = 0.f, dbq[3] = {0.f, 0.f, 0.f};
+  // Weight gradients are sums over windows of outer products of per-window vectors.  Every warp leaves its
+  // window's vectors in its scratch; then the 256 threads of the CTA each own 32 gradient elements in REGISTERS
+  // and add the 8 windows of the pass (no shared-memory atomics: those were ~8000 per window and 85 % of the
+  // kernel):  merge dW[o][c] += g[o] cat[c]           o = tid/4,  c = 16 (tid%4) .. +16
+  //           proj  dW[c][j] += dcat[d][c] om[d][j]   c = tid/8,  j =  4 (tid%8) .. +4   (both directions d)
+  //           qkv   dW[j][c] += dqkv[t][j] tok[t][c]  j = tid/8 + 32 i (i < 3),  c = 4 (tid%8) .. +4   (8 tokens t)
+  float accM[16], accP[4], accQ[12];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) accM[i] = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) accP[i] = 0.f;
+#pragma unroll
+  for (int i = 0; i < 12; ++i) accQ[i] = 0.f;
+  const float* sScr = smem + LB::oScratch;
 
   const int wh = p.wh, ww = p.ww;
   const int nwin = p.B * wh * ww;
-  for (int win = blockIdx.x * 8 + warp; win < nwin; win += gridDim.x * 8) {
+  for (int base = blockIdx.x * 8; base < nwin; base += gridDim.x * 8) {
+   const int win = base + warp;
+   if (win < nwin) {
     const int w0 = win % ww, h0 = (win / ww) % wh, b = win / (ww * wh);
     int nbr[8];
     // ================= forward recompute
@@ -207,13 +222,6 @@ __global__ void __launch_bounds__(kThreads) ngram_ctx_bwd_kernel(NgramParams p) 
     }
     __syncwarp();
 #pragma unroll
-    for (int og = 0; og < 2; ++og) {
-      const int o = lane + 32 * og;
-      const float gv = sG[o];
-#pragma unroll 8
-      for (int c = 0; c < 64; ++c) atomicAdd(sDWm + o * 65 + c, gv * sCat[c]);
-    }
-#pragma unroll
     for (int cg = 0; cg < 2; ++cg) {
       const int c = lane + 32 * cg;
       float acc = 0.f;
@@ -224,12 +232,6 @@ __global__ void __launch_bounds__(kThreads) ngram_ctx_bwd_kernel(NgramParams p) 
     __syncwarp();
     // ---- B2: proj (applied to the token-mean, so its input gradient is dom)
     dbp += sDcat[lane] + sDcat[32 + lane];
-    {
-      const float d0 = sDcat[lane], d1 = sDcat[32 + lane];
-#pragma unroll 6
-      for (int j = 0; j < NA; ++j)
-        atomicAdd(sDWp + lane * 33 + j, d0 * sOm[j] + d1 * sOm[32 + j]);
-    }
     if (lane < NA) {
 #pragma unroll
       for (int dd = 0; dd < 2; ++dd) {
@@ -307,17 +309,10 @@ __global__ void __launch_bounds__(kThreads) ngram_ctx_bwd_kernel(NgramParams p) 
     for (int jg = 0; jg < 3; ++jg) {
       const int j = lane + 32 * jg;
       if (j < 3 * NA) {
-        float g8[8], s = 0.f;
+        float s = 0.f;
 #pragma unroll
-        for (int t = 0; t < 8; ++t) { g8[t] = sDqkv[t * 96 + j]; s += g8[t]; }
+        for (int t = 0; t < 8; ++t) s += sDqkv[t * 96 + j];
         dbq[jg] += s;
-#pragma unroll 4
-        for (int c = 0; c < 32; ++c) {
-          float acc = 0.f;
-#pragma unroll
-          for (int t = 0; t < 8; ++t) acc = fmaf(g8[t], sTok[t * 32 + c], acc);
-          atomicAdd(sDWqkv + j * 33 + c, acc);
-        }
       }
     }
     {
@@ -333,7 +328,49 @@ __global__ void __launch_bounds__(kThreads) ngram_ctx_bwd_kernel(NgramParams p) 
 #pragma unroll
       for (int t = 0; t < 8; ++t) atomicAdd(p.du + (size_t)nbr[t] + lane, dt[t]);
     }
-    __syncwarp();
+   }
+    // ================= block-wide weight-gradient accumulation over the windows of this pass
+    __syncthreads();
+    {
+      const int nw = min(8, nwin - base);
+      const int tid = threadIdx.x;
+      const int mo = tid >> 2, mc = (tid & 3) * 16;
+      const int pc = tid >> 3, pj = (tid & 7) * 4;
+      for (int w = 0; w < nw; ++w) {
+        const float* scr = sScr + w * LB::kScratchPerWarp;
+        const float* wTok = scr;
+        const float* wOm = scr + 1024;
+        const float* wCat = scr + 1088;
+        const float* wG = scr + 1152;
+        const float* wDcat = scr + 1216;
+        const float* wDqkv = scr + 1344;
+        const float gv = wG[mo];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float4 c4 = *reinterpret_cast<const float4*>(wCat + mc + 4 * i);
+          accM[4 * i] = fmaf(gv, c4.x, accM[4 * i]); accM[4 * i + 1] = fmaf(gv, c4.y, accM[4 * i + 1]);
+          accM[4 * i + 2] = fmaf(gv, c4.z, accM[4 * i + 2]); accM[4 * i + 3] = fmaf(gv, c4.w, accM[4 * i + 3]);
+        }
+        {
+          const float d0 = wDcat[pc], d1 = wDcat[32 + pc];
+          const float4 o0 = *reinterpret_cast<const float4*>(wOm + pj);
+          const float4 o1 = *reinterpret_cast<const float4*>(wOm + 32 + pj);
+          accP[0] = fmaf(d0, o0.x, fmaf(d1, o1.x, accP[0])); accP[1] = fmaf(d0, o0.y, fmaf(d1, o1.y, accP[1]));
+          accP[2] = fmaf(d0, o0.z, fmaf(d1, o1.z, accP[2])); accP[3] = fmaf(d0, o0.w, fmaf(d1, o1.w, accP[3]));
+        }
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+          const float4 x4 = *reinterpret_cast<const float4*>(wTok + t * 32 + pj);
+#pragma unroll
+          for (int i = 0; i < 3; ++i) {
+            const float gq = wDqkv[t * 96 + pc + 32 * i];
+            accQ[4 * i] = fmaf(gq, x4.x, accQ[4 * i]); accQ[4 * i + 1] = fmaf(gq, x4.y, accQ[4 * i + 1]);
+            accQ[4 * i + 2] = fmaf(gq, x4.z, accQ[4 * i + 2]); accQ[4 * i + 3] = fmaf(gq, x4.w, accQ[4 * i + 3]);
+          }
+        }
+      }
+    }
+    __syncthreads();                                   // the scratch is rewritten by the next pass
   }
 
   // ================= flush
@@ -343,13 +380,24 @@ __global__ void __launch_bounds__(kThreads) ngram_ctx_bwd_kernel(NgramParams p) 
 #pragma unroll
   for (int jg = 0; jg < 3; ++jg)
     if (lane + 32 * jg < 3 * NA) atomicAdd(p.d_qkv_b + lane + 32 * jg, dbq[jg]);
+  {
+    const int tid = threadIdx.x;
+    const int mo = tid >> 2, mc = (tid & 3) * 16, pc = tid >> 3, pj = (tid & 7) * 4;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) atomicAdd(p.d_merge_w + mo * 64 + mc + i, accM[i]);
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      if (pj + i < NA) atomicAdd(p.d_proj_w + pc * NA + pj + i, accP[i]);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const int j = pc + 32 * i;
+      if (j < 3 * NA) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) atomicAdd(p.d_qkv_w + j * 32 + pj + k, accQ[4 * i + k]);
+      }
+    }
+  }
   __syncthreads();
-  for (int i = threadIdx.x; i < 3 * NA * 32; i += blockDim.x)
-    atomicAdd(p.d_qkv_w + i, sDWqkv[(i >> 5) * 33 + (i & 31)]);
-  for (int i = threadIdx.x; i < 32 * NA; i += blockDim.x)
-    atomicAdd(p.d_proj_w + i, sDWp[(i / NA) * 33 + (i % NA)]);
-  for (int i = threadIdx.x; i < 64 * 64; i += blockDim.x)
-    atomicAdd(p.d_merge_w + i, sDWm[(i >> 6) * 65 + (i & 63)]);
   for (int i = threadIdx.x; i < NH * 9; i += blockDim.x)
     atomicAdd(p.d_bias_table + (i % 9) * NH + i / 9, sDBias[(i / 9) * 12 + i % 9]);
   if (threadIdx.x < NH && p.logit_scale[threadIdx.x] <= kLogitMax)
