@@ -52,14 +52,17 @@ def _worker(rank, world, port, q):
 def test_flat_bucket_views_and_zero():
     m = _toy(0)
     b = dp.FlatGradBucket(m.parameters())
-    assert b.numel == sum(p.numel() for p in m.parameters())
+    assert b.param_numel == sum(p.numel() for p in m.parameters())
+    assert b.numel == b.flat.numel() == sum(-(-p.numel() // 4) * 4 for p in m.parameters())
     m(torch.randn(3, 8)).sum().backward()
-    off = 0
-    for p in m.parameters():                      # grads accumulate INTO the flat buffer
-        assert p.grad.data_ptr() == b.flat.data_ptr() + 4 * off
+    covered = torch.zeros(b.numel, dtype=torch.bool)
+    for p, off in zip(m.parameters(), b.offsets):  # grads accumulate INTO the flat buffer, views 16-byte aligned
+        assert off % 4 == 0 and p.grad.data_ptr() == b.flat.data_ptr() + 4 * off
         assert torch.equal(p.grad.flatten(), b.flat[off:off + p.numel()])
-        off += p.numel()
-    assert b.flat.abs().sum() > 0
+        covered[off:off + p.numel()] = True
+    assert b.flat.abs().sum() > 0 and b.flat[~covered].abs().sum() == 0     # the padding stays zero
+    packed = dp.FlatGradBucket(_toy(0).parameters(), align=1)
+    assert packed.numel == packed.param_numel
     b.zero()
     assert b.flat.abs().sum() == 0 and all(p.grad is not None for p in m.parameters())
     assert b.all_reduce() is None                 # single process: no-op

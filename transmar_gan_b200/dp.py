@@ -17,22 +17,28 @@ import torch.distributed as dist
 
 
 class FlatGradBucket:
-    """Owns one flat gradient buffer; every parameter's `.grad` is a view into it."""
+    """Owns one flat gradient buffer; every parameter's `.grad` is a view into it.  Views start on multiples of
+    `align` elements (4 fp32 = 16 bytes: the backward kernels then flush weight gradients with 16-byte vector
+    reductions); the padding stays zero and rides along in the all-reduce.  `numel` is the buffer's length
+    (what is exchanged), `param_numel` the number of gradient elements, `offsets[i]` the start of parameter i."""
 
-    def __init__(self, params: Iterable[torch.nn.Parameter]):
+    def __init__(self, params: Iterable[torch.nn.Parameter], align: int = 4):
         self.params: List[torch.nn.Parameter] = [p for p in params if p.requires_grad]
         if not self.params:
             raise ValueError("FlatGradBucket needs at least one trainable parameter")
         dev, dt = self.params[0].device, self.params[0].dtype
         if any(p.device != dev or p.dtype != dt for p in self.params):
             raise ValueError("all parameters of a bucket must share device and dtype")
-        self.numel = sum(p.numel() for p in self.params)
-        self.flat = torch.zeros(self.numel, device=dev, dtype=dt)
-        off = 0
+        align = max(int(align), 1)
+        self.param_numel = sum(p.numel() for p in self.params)
+        self.offsets, off = [], 0
         for p in self.params:
-            n = p.numel()
-            p.grad = self.flat[off:off + n].view_as(p)
-            off += n
+            self.offsets.append(off)
+            off += -(-p.numel() // align) * align
+        self.numel = off
+        self.flat = torch.zeros(self.numel, device=dev, dtype=dt)
+        for p, o in zip(self.params, self.offsets):
+            p.grad = self.flat[o:o + p.numel()].view_as(p)
 
     def zero(self):
         """Zero all gradients with one memset (keeps the views attached)."""
