@@ -71,32 +71,44 @@ __global__ void __launch_bounds__(kThreads, 1) patch_merge_fwd_kernel(MergeParam
 }
 
 // ------------------------------------------------------------------------ pixel shuffle + cat
-// One thread per element of the [B, H*W, 84] concat tensor.  Forward copies x_i -> cat,
-// inverse copies cat -> x_i (the permutation's transpose, i.e. its gradient).
-__global__ void pixel_shuffle_cat_kernel(float* __restrict__ x0, float* __restrict__ x1,
-                                         float* __restrict__ x2, float* __restrict__ cat, int B,
-                                         int H, int W, int inverse) {
-  const long long total = (long long)B * H * W * 84;
+// One thread per 16-byte group of the [B, H*W, 84] concat tensor (21 groups per token): groups 0..15 are a
+// straight float4 copy of the full-resolution skip, groups 16..19 / 20 gather four channels of the half- /
+// quarter-resolution skips (source channel stride 4 / 16).  Forward copies x_i -> cat, inverse copies
+// cat -> x_i (the permutation's transpose, i.e. its gradient).  Token coordinates in 32-bit arithmetic
+// (the launcher checks B*H*W < 2^31).
+__global__ void __launch_bounds__(256) pixel_shuffle_cat_kernel(float* __restrict__ x0, float* __restrict__ x1,
+                                                                float* __restrict__ x2, float* __restrict__ cat,
+                                                                int B, int H, int W, int inverse) {
+  const long long total = (long long)B * H * W * 21;
   for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total;
        idx += (long long)gridDim.x * blockDim.x) {
-    const int ch = (int)(idx % 84);
-    const long long tokf = idx / 84;
-    const int C = (int)(tokf % W);
-    const int R = (int)((tokf / W) % H);
-    const long long b = tokf / ((long long)W * H);
-    float* src;
-    if (ch < 64) {
-      src = x0 + tokf * 64 + ch;
-    } else if (ch < 80) {
-      const int c = ch - 64;   // s = 2: source channel (c*2 + a)*2 + c'
-      const int h = R >> 1, a = R & 1, w = C >> 1, cc = C & 1;
-      src = x1 + ((b * (H >> 1) + h) * (W >> 1) + w) * 64 + ((c * 2 + a) * 2 + cc);
-    } else {
-      const int c = ch - 80;   // s = 4
-      const int h = R >> 2, a = R & 3, w = C >> 2, cc = C & 3;
-      src = x2 + ((b * (H >> 2) + h) * (W >> 2) + w) * 64 + ((c * 4 + a) * 4 + cc);
+    const unsigned tok = (unsigned)(idx / 21);
+    const int g = (int)(idx - (long long)tok * 21);
+    float4* cp = reinterpret_cast<float4*>(cat + (size_t)tok * 84 + g * 4);
+    if (g < 16) {
+      float4* sp = reinterpret_cast<float4*>(x0 + (size_t)tok * 64 + g * 4);
+      if (inverse) *sp = *cp; else *cp = *sp;
+      continue;
     }
-    if (inverse) *src = cat[idx]; else cat[idx] = *src;
+    const unsigned C = tok % (unsigned)W, row = tok / (unsigned)W;
+    const unsigned R = row % (unsigned)H, b = row / (unsigned)H;
+    float* src;
+    int stride;
+    if (g < 20) {              // s = 2: channel c = 4 (g-16) + k  <-  source channel (c*2 + a)*2 + c'
+      const unsigned h = R >> 1, a = R & 1, w = C >> 1, cc = C & 1;
+      src = x1 + ((size_t)(b * (H >> 1) + h) * (W >> 1) + w) * 64 + (((g - 16) * 4 * 2 + a) * 2 + cc);
+      stride = 4;
+    } else {                   // s = 4: channel c = k  <-  source channel (c*4 + a)*4 + c'
+      const unsigned h = R >> 2, a = R & 3, w = C >> 2, cc = C & 3;
+      src = x2 + ((size_t)(b * (H >> 2) + h) * (W >> 2) + w) * 64 + (a * 4 + cc);
+      stride = 16;
+    }
+    if (inverse) {
+      const float4 v = *cp;
+      src[0] = v.x; src[stride] = v.y; src[2 * stride] = v.z; src[3 * stride] = v.w;
+    } else {
+      *cp = make_float4(src[0], src[stride], src[2 * stride], src[3 * stride]);
+    }
   }
 }
 
@@ -148,8 +160,8 @@ extern "C" int b200mar_patch_merge_fwd(const float* x, const float* ln_w, const 
 extern "C" int b200mar_pixel_shuffle_cat(float* x0, float* x1, float* x2, float* cat, int B, int H,
                                          int W, int inverse, void* stream) {
   using namespace b200mar;
-  if (H % 4 || W % 4) return -1;
-  const long long total = (long long)B * H * W * 84;
+  if (H % 4 || W % 4 || (long long)B * H * W >= (1ll << 31)) return -1;
+  const long long total = (long long)B * H * W * 21;      // 16-byte groups
   long long blocks = (total + 255) / 256;
   const long long cap = (long long)sm_count() * 16;
   if (blocks > cap) blocks = cap;

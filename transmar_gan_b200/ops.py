@@ -660,7 +660,8 @@ class NSTBFunction(torch.autograd.Function):
 class PatchMergeFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx_, x, ph, pw, ln_w, ln_b, red_w):
-        y = patch_merge_fwd(x, ln_w.detach(), ln_b.detach(), red_w.detach(), ph, pw)
+        fwd = patch_merge_tc_fwd if _PRECISION == "tf32" else patch_merge_fwd      # (the backward recomputes in fp32)
+        y = fwd(x, ln_w.detach(), ln_b.detach(), red_w.detach(), ph, pw)
         ctx_.save_for_backward(x, ln_w, ln_b, red_w)
         ctx_.geom = (ph, pw)
         return y
