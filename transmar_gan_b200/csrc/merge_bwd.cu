@@ -134,15 +134,24 @@ __global__ void __launch_bounds__(kThreads, 1) patch_merge_bwd_kernel(MergeParam
   // ---- flush
   if (tid < kDim) sColsum[tid] = colsum;
   __syncthreads();
+  // a thread's four columns are consecutive: one 16-byte vector reduction per (chunk, row) when the gradient
+  // buffer is 16-byte aligned (dp.FlatGradBucket views are), 4x fewer L2 operations than scalar atomics
+  const bool vec = (reinterpret_cast<uintptr_t>(p.d_red_w) & 15) == 0;
 #pragma unroll
   for (int chunk = 0; chunk < 4; ++chunk)
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
+    for (int i = 0; i < 4; ++i) {
+      const int n = gemm_row<true>(i), k0 = chunk * 64 + gemm_col<true>(0);
+      float v[4];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int n = gemm_row<true>(i), k = chunk * 64 + gemm_col<true>(j);
-        atomicAdd(p.d_red_w + n * 256 + k, sLnW[k] * accW[chunk][i][j] + sLnB[k] * sColsum[n]);
+      for (int j = 0; j < 4; ++j) v[j] = sLnW[k0 + j] * accW[chunk][i][j] + sLnB[k0 + j] * sColsum[n];
+      if (vec) {
+        atomicAdd(reinterpret_cast<float4*>(p.d_red_w + n * 256 + k0), make_float4(v[0], v[1], v[2], v[3]));
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) atomicAdd(p.d_red_w + n * 256 + k0 + j, v[j]);
       }
+    }
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     atomicAdd(p.d_ln_w + lane + 32 * i, dg[i]);

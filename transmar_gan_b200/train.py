@@ -10,8 +10,8 @@ A step at the reference's training crop (batch 16 x 128x128) is ~440 kernel laun
 microseconds long.  With `graph=True` the step is captured once into CUDA graphs (inputs are copied into
 static buffers) and every later call is a replay: part A = zero + forward + loss + backward, part B = Adam.
 On one process A and B are a single graph; with several ranks the NCCL all-reduce of the flat bucket runs
-between the two graphs on the same stream.  Measured on a B200 the L1 step is GPU-bound either way (20.9 ms
-replayed, 22.3 ms launched eagerly); the full GAN step gains more (33.7 vs 43.9 ms) because the stock
+between the two graphs on the same stream.  Measured on a B200 the L1 step is GPU-bound either way (20.5 ms
+replayed, 21.8 ms launched eagerly); the full GAN step gains more (33.2 vs 43.1 ms) because the stock
 PyTorch discriminator adds several hundred small launches.
 """
 from __future__ import annotations
