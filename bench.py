@@ -133,14 +133,15 @@ def cpu_forward_time(size: int, runs: int):
     return sum(ts) / len(ts), threads, len(ts)
 
 
-def gpu_eager_forward_time(size: int, batch: int = 4, runs: int = 3):
+def gpu_eager_forward_time(size: int, batch: int = 4, runs: int = 3, autocast_bf16: bool = False):
     """The same oracle port (= the reference's PyTorch op sequence, materialised logits / masks / partition
-    copies and all) run eagerly in fp32 ON THE B200: the stock-PyTorch GPU baseline SURVEY.md §8d asks for
-    beside the CPU one.  Part of the cpu_baseline leg (reported baseline, never on the product path)."""
+    copies and all) run eagerly ON THE B200, in fp32 or under torch.autocast(bf16): the stock-PyTorch GPU
+    baselines SURVEY.md §8d / BASELINE.md §3 ask for beside the CPU one.  Part of the cpu_baseline leg
+    (reported baselines, never on the product path)."""
     from oracle import ngswin_oracle as O
     sd = {k: v.cuda() for k, v in O.synthetic_state_dict("W1", seed=1).items()}
     x = O.synthetic_input(batch, size, size, seed=999).cuda()
-    with torch.no_grad():
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast_bf16):
         for _ in range(2):
             O.ngswin_forward(x, sd)
         torch.cuda.synchronize()
@@ -153,6 +154,69 @@ def gpu_eager_forward_time(size: int, batch: int = 4, runs: int = 3):
     del sd, x
     torch.cuda.empty_cache()
     return e0.elapsed_time(e1) / 1e3 / runs / batch      # seconds per slice
+
+
+class OracleNGswin(torch.nn.Module):
+    """BASELINE LEG ONLY: the oracle port (the reference's stock-PyTorch op sequence) as an nn.Module, so that
+    the reference's training recipes can be timed eagerly in fp32 on the same B200 (`train.gpu_eager`,
+    `train_gan.gpu_eager`).  Never on the product path."""
+
+    def __init__(self):
+        super().__init__()
+        from oracle import ngswin_oracle as O
+        self.O = O
+        self.names, self.consts = [], {}
+        self.params = torch.nn.ParameterList()
+        for k, v in O.synthetic_state_dict("W1", seed=1).items():
+            if v.is_floating_point() and not k.endswith("attn_mask"):
+                self.names.append(k)
+                self.params.append(torch.nn.Parameter(v.clone()))
+            else:
+                self.consts[k] = v
+
+    def forward(self, x):
+        p = dict(zip(self.names, self.params))
+        p.update({k: v.to(x.device) for k, v in self.consts.items()})
+        return self.O.ngswin_forward(x, p)
+
+
+def gpu_eager_train_times(args):
+    """The reference's two training recipes on stock eager PyTorch fp32 (oracle generator + this repo's stock
+    PyTorch discriminator / losses, pinned to the reference by tests/test_gan_stock.py) on this B200, batch 16
+    x 128x128: ms per step of config 3 (L1) and config 4 (full GAN step, lambda_phys = 0)."""
+    from transmar_gan_b200 import gan, train
+    B, S = 16, 128
+    g = torch.Generator().manual_seed(999)
+    x = (torch.rand(B, 1, S, S, generator=g) * 2 - 1).cuda()
+    t = (torch.rand(B, 1, S, S, generator=g) * 2 - 1).cuda()
+    out = {}
+
+    def timed(step, a, b, runs=3):
+        for _ in range(2):
+            step(a, b)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(runs):
+            step(a, b)
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / runs
+
+    netG = OracleNGswin().cuda().train()
+    out["l1_ms_per_step"] = timed(train.L1TrainStep(netG, lr=1e-4, betas=(0.5, 0.999), graph=False), x, t)
+    del netG
+    torch.cuda.empty_cache()
+    netG = OracleNGswin().cuda().train()
+    torch.manual_seed(4321)
+    netD = gan.MultiScaleDiscriminator(2, 64, 5, 3, True).cuda().train()
+    netD.apply(gan.weights_init)
+    out["gan_ms_per_step"] = timed(train.GANTrainStep(netG, netD, graph=False, fused_losses=False), x, t)
+    del netG, netD
+    torch.cuda.empty_cache()
+    out["sample"] = ("oracle port of the reference generator (stock PyTorch ops, fp32, allow_tf32 off) + stock "
+                     "discriminator / losses, eager launches, 3 timed steps after 2 warm-ups, batch 16 x 128x128")
+    return out
 
 
 # ------------------------------------------------------------------------------ reference arm
@@ -234,6 +298,112 @@ def max_over_ranks(ms, world):
     return t.item()
 
 
+def time_allreduce(bucket, world, iters=10):
+    """ms per all-reduce of one flat gradient bucket (CUDA events, max over ranks)."""
+    if world == 1:
+        return None
+    for _ in range(3):
+        bucket.all_reduce()
+    barrier(world)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        bucket.all_reduce()
+    e1.record()
+    barrier(world)
+    return max_over_ranks(e0.elapsed_time(e1), world) / iters
+
+
+def dp_check(rank, world):
+    """N > 1 only (an assertion leg: `pytest -m gpu` sees one GPU).  (a) every rank computes the L1 gradient of
+    ITS SHARD of one global batch on the fp32 kernels, the flat bucket is all-reduced (NCCL, avg) and compared
+    with the gradient of the whole global batch computed by this one process: relative L2 <= 1e-3 (the fp32
+    gradient gate; the two differ only by fp32 summation order).  (b) 10 CUDA-graph-replayed steps of the L1 and
+    of the full GAN recipe with DIFFERENT data per rank: parameters, Adam state and the discriminator's
+    spectral-norm power-iteration buffers must be BIT-IDENTICAL on all ranks afterwards (the u vectors depend
+    on the weights only, and every rank runs the same number of D forwards, so broadcast-once suffices)."""
+    import torch.distributed as dist
+    import torch.nn.functional as F
+    from transmar_gan_b200 import dp, gan, ops, train
+    res = {}
+    per, S = 4, 64
+    g = torch.Generator().manual_seed(7)
+    X = (torch.rand(world * per, 1, S, S, generator=g) * 2 - 1).cuda()
+    Tg = (torch.rand(world * per, 1, S, S, generator=g) * 2 - 1).cuda()
+    old = ops.set_precision("fp32")
+    try:
+        m = build_model().train()
+        dp.broadcast_parameters(m)
+        bucket = dp.FlatGradBucket(m.parameters())
+        F.l1_loss(m(X), Tg).backward()
+        full = bucket.flat.clone()
+        bucket.zero()
+        F.l1_loss(m(dp.shard_batch(X, rank, world)), dp.shard_batch(Tg, rank, world)).backward()
+        bucket.all_reduce()
+        res["grad_rel_l2_vs_full_batch"] = ((bucket.flat - full).norm() / full.norm()).item()
+        del m, bucket
+    finally:
+        ops.set_precision(old)
+
+    def spread(tensors):
+        """max over ranks of max |t_rank - t_rank0| over all tensors."""
+        worst = 0.0
+        for t in tensors:
+            ref = t.detach().clone()
+            dist.broadcast(ref, src=0)
+            worst = max(worst, (t.detach() - ref).abs().max().item() if t.numel() else 0.0)
+        w = torch.tensor([worst], device="cuda", dtype=torch.float64)
+        dist.all_reduce(w, op=dist.ReduceOp.MAX)
+        return w.item()
+
+    gr = torch.Generator().manual_seed(100 + rank)                 # different data on every rank
+    x = (torch.rand(8, 1, S, S, generator=gr) * 2 - 1).cuda()
+    t = (torch.rand(8, 1, S, S, generator=gr) * 2 - 1).cuda()
+    m = build_model().train()
+    dp.broadcast_parameters(m)
+    step = train.L1TrainStep(m, graph=True)
+    for _ in range(10):
+        step(x, t)
+    res["l1_param_spread_after_10_steps"] = spread(list(m.parameters()))
+    res["l1_adam_state_spread"] = spread([v for st in step.opt.state.values() for v in st.values() if torch.is_tensor(v)])
+    del step, m
+    netG = build_model().train()
+    torch.manual_seed(4321)
+    netD = gan.MultiScaleDiscriminator(2, 64, 5, 3, True).cuda().train()
+    netD.apply(gan.weights_init)
+    dp.broadcast_parameters(netG)
+    dp.broadcast_parameters(netD)
+    step = train.GANTrainStep(netG, netD, graph=True)
+    for _ in range(10):
+        step(x, t)
+    res["gan_G_param_spread_after_10_steps"] = spread(list(netG.parameters()))
+    res["gan_D_param_spread_after_10_steps"] = spread(list(netD.parameters()))
+    res["gan_D_spectral_norm_buffer_spread"] = spread(list(netD.buffers()))
+    res["ok"] = bool(res["grad_rel_l2_vs_full_batch"] <= 1e-3 and all(v == 0.0 for k, v in res.items() if "spread" in k))
+    del step, netG, netD
+    torch.cuda.empty_cache()
+    assert res["ok"], f"data-parallel check failed: {res}"
+    return res
+
+
+def ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel at the default config,
+    parsed from the newest committed ncu --set full summary (profiles/rNN_ncu_attn6.txt): (bytes, file) or
+    (None, None).  A profiler number about the same build, not something this run measured."""
+    import glob
+    import re
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_attn6.txt")))
+    if not files:
+        return None, None
+    tot, txt = 0.0, open(files[-1]).read()
+    for key in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+        m = re.search(re.escape(key) + r"\s+([0-9.]+)\s+(\w+)", txt)
+        if not m:
+            return None, None
+        tot += float(m.group(1)) * {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(m.group(2), float("nan"))
+    return tot, os.path.relpath(files[-1], ROOT)
+
+
 def build_model(kind="W1"):
     """Random-init weights of the reference architecture (no checkpoint ships with the reference):
     W1 = `NGswin()` + the callers' weights_init N(0,.02) (training/train_combined.py:207-217)."""
@@ -261,7 +431,9 @@ def time_inference(model, args, world, sampler):
         for _ in range(args.warmup):
             model(x)
         barrier(world)
-        tc = ops.get_precision() == "tf32"
+        rep = getattr(model, "precision_report", None)         # precision "auto": the measured per-unit plan
+        tc = ops.get_precision() == "tf32" or (ops.get_precision() == "auto" and rep is not None
+                                               and rep["units_on_tensor_cores"] == rep["units"])
         k_attn, k_mlp = ("attn_tc_fwd", "mlp_tma_fwd") if tc else ("attn_fwd", "mlp_fwd")
         ops.profile.reset(timed=(k_attn, k_mlp))
         if sampler:
@@ -322,6 +494,31 @@ def time_highres(model, args, world):
             "windows_per_slice": (S // 8) ** 2, "mpixels_per_s": world * B * S * S / ms / 1e3}
 
 
+def train_roofline(ms, B, S, gen_passes):
+    """Generator share of a training step against both rooflines.  FLOPs: `gen_passes` x the
+    exact forward count (fwd + bwd = 3 x forward for config 3; 2 fwd + 1 bwd = 4 x for config 4's
+    generator share; the stock-PyTorch discriminator is not counted, so the GAN figure is a lower bound of the
+    step's rate).  Bytes: the fp32 residual stream passes of the block kernels - forward 5 passes / block
+    (read z, write a, read a, reduce-add z: 2) + the bf16 O row saved for the backward (0.5); backward: MLP row
+    kernel (read a, g; write da; 1.5 of bf16 exports), attention row kernels (read z, da, O; write dz; 3 of
+    exports), wgrad (re-read the 4.5 of exports), unigram backward (read z, RMW dz: 3): 19.5 passes / block -
+    summed over the 20 blocks at their stage resolutions, 256 B per token and pass."""
+    hbm_peak, tf_peak, which = peaks()
+    tokens = B * S * S
+    flops = gen_passes * 2 * MACS_PER_PIXEL * tokens
+    blocks = 12 + 4 / 4 + 4 / 16                       # full-resolution block equivalents
+    fwd_b, bwd_b = 5.5 * 256 * tokens * blocks, 19.5 * 256 * tokens * blocks
+    nbytes = fwd_b * (gen_passes - 2) + bwd_b          # config 3: 1 fwd + 1 bwd; config 4: 2 fwd + 1 bwd
+    tfl = flops / (ms / 1e3) / 1e12
+    return {"achieved_tflops": tfl, "frac_of_tf32_peak": tfl / (tf_peak / 2.0),
+            "frac_of_bf16_peak": tfl / tf_peak, "algorithmic_flops_per_step": flops,
+            "algorithmic_bytes_per_step": nbytes, "achieved_gbs": nbytes / (ms / 1e3) / 1e9,
+            "bytes_frac": nbytes / (ms / 1e3) / 1e9 / hbm_peak,
+            "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained (/2 for tf32), hbm_gbs ({which})",
+            "note": "generator share only (the discriminator of config 4 is stock PyTorch); at 16 x 128^2 a block "
+                    "kernel is 2048 tiles of a few us - the step is latency / launch bound, neither roofline"}
+
+
 def time_train(args, rank, world):
     """config-3 recipe per rank: y = netG(x); F.l1_loss(y,t).backward(); all-reduce; Adam.step()
     (scripts/run_ablation_studies.py:1525-1535; Adam betas (.5,.999) lr 1e-4), batch 16 x 128x128,
@@ -340,6 +537,7 @@ def time_train(args, rank, world):
     for mode in ("eager", "graph"):
         model = build_model().train()
         dp.broadcast_parameters(model)
+        model.calibrate_precision()                  # precision "auto": measure the plan outside the launch count
         step = train.L1TrainStep(model, lr=1e-4, betas=(0.5, 0.999), graph=(mode == "graph"))
         ops.profile.reset()
         step(x, t)                                   # graph mode: warm-up steps + capture happen here
@@ -355,6 +553,7 @@ def time_train(args, rank, world):
         barrier(world)
         res[mode] = (max_over_ranks(e0.elapsed_time(e1), world) / steps, per_step, float(loss.item()))
         nbytes = step.bucket.numel * 4
+        ar_ms = time_allreduce(step.bucket, world)
         del step, model
     torch.backends.cudnn.allow_tf32 = False
     mode = min(res, key=lambda k: res[k][0])          # the step is GPU-bound: report the faster launch mode
@@ -364,7 +563,8 @@ def time_train(args, rank, world):
             "per_gpu_batch": B, "size": S,
             "recipe": "fwd + L1 + bwd (fused gradient accumulation into the flat bucket) + all-reduce + Adam "
                       "(train.L1TrainStep; eager launches and CUDA-graph replay both timed)",
-            "allreduce_bytes": nbytes if world > 1 else 0,
+            "allreduce_bytes": nbytes if world > 1 else 0, "allreduce_ms": ar_ms,
+            "roofline": train_roofline(ms, B, S, gen_passes=3),
             "gpu_launches_per_step": launches, "final_loss": loss}
 
 
@@ -395,6 +595,7 @@ def time_train_gan(args, rank, world):
             netD.apply(gan.weights_init)
             dp.broadcast_parameters(netG)
             dp.broadcast_parameters(netD)
+            netG.calibrate_precision()
             proj = None
             if mode.endswith("physics"):                   # train_combined.py:269-271: 180 angles over [0, pi]
                 from transmar_gan_b200 import radon
@@ -416,6 +617,8 @@ def time_train_gan(args, rank, world):
             res[mode] = (max_over_ranks(e0.elapsed_time(e1), world) / steps, per_step, float(lD.item()),
                          float(lG.item()))
             nbytes = (step.bucketG.numel * 4, step.bucketD.numel * 4)
+            ar_ms = None if world == 1 else {"generator_bucket": time_allreduce(step.bucketG, world),
+                                             "discriminator_bucket": time_allreduce(step.bucketD, world)}
             del step, netG, netD
     finally:
         torch.backends.cudnn.allow_tf32 = old
@@ -433,7 +636,8 @@ def time_train_gan(args, rank, world):
             "recipe": "D step (G fwd no-grad, 2 D fwd, hinge, bwd, Adam) + G step (G fwd, 2 D fwd, hinge + FM + "
                       "metal-aware L1/edge + metal consistency from one fused kernel, bwd, Adam); lambda_phys = 0 "
                       "(torch-radon absent); train.GANTrainStep, eager launches and CUDA-graph replay both timed",
-            "allreduce_bytes": list(nbytes) if world > 1 else [0, 0],
+            "allreduce_bytes": list(nbytes) if world > 1 else [0, 0], "allreduce_ms": ar_ms,
+            "roofline": train_roofline(ms, B, S, gen_passes=4),
             "gpu_launches_per_step": launches, "final_loss_D": lD, "final_loss_G": lG}
 
 
@@ -457,6 +661,8 @@ def main():
     highres = None if args.no_highres else time_highres(model, args, world)
     train = None if args.no_train else time_train(args, rank, world)
     train_gan = None if (args.no_train or args.no_gan) else time_train_gan(args, rank, world)
+    if train is not None and world > 1:
+        train["dp_check"] = dp_check(rank, world)
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         sec, threads, runs = cpu_forward_time(args.size, 3)
@@ -468,6 +674,20 @@ def main():
                             "sample": f"the same oracle port (the reference's stock-PyTorch op sequence) run "
                                       f"eagerly in fp32 on this B200, 3 timed batch-4 {args.size}x{args.size} "
                                       "forwards, 2 warm-ups"}
+        bsec = gpu_eager_forward_time(args.size, autocast_bf16=True)
+        cpu["gpu_eager_autocast_bf16"] = {"value": 1.0 / bsec, "unit": UNIT,
+                                          "sample": "the same, under torch.autocast('cuda', dtype=bfloat16) "
+                                                    "(BASELINE.md §3); its output differs from fp32 by ~5e-3 "
+                                                    "max-abs on W1 (SURVEY.md §7.3), outside the 1e-3 gate"}
+        if train is not None:
+            eg = gpu_eager_train_times(args)
+            train["gpu_eager"] = {"ms_per_step": eg["l1_ms_per_step"], "steps_per_s": 1e3 / eg["l1_ms_per_step"],
+                                  "sample": eg["sample"]}
+            train["vs_gpu_eager"] = eg["l1_ms_per_step"] / train["ms_per_step"]
+            if train_gan is not None:
+                train_gan["gpu_eager"] = {"ms_per_step": eg["gan_ms_per_step"],
+                                          "steps_per_s": 1e3 / eg["gan_ms_per_step"], "sample": eg["sample"]}
+                train_gan["vs_gpu_eager"] = eg["gan_ms_per_step"] / train_gan["ms_per_step"]
     if rank != 0:
         return
     K, B, S = args.steps, args.batch, args.size
@@ -476,7 +696,10 @@ def main():
     hbm_peak, tf_peak, which = peaks()
     tokens = B * S * S
     attn_avg = sum(attn_ms) / max(len(attn_ms), 1)
-    tc = T.ops.get_precision() == "tf32"
+    rep = getattr(model, "precision_report", None)
+    tc = T.ops.get_precision() == "tf32" or (T.ops.get_precision() == "auto" and rep is not None
+                                             and rep["units_on_tensor_cores"] == rep["units"])
+    traffic, traffic_src = ncu_traffic()
     # dominant kernel = fused window attention.  Algorithmic bytes per launch:
     # one read of z and one write of a, 64 fp32 channels per token; weights / ctx are L2-resident.
     attn_bytes = 2 * tokens * 64 * 4
@@ -496,6 +719,9 @@ def main():
                                ("on tcgen05 (FP16 / TF32 operands, fp32 accumulate in TMEM)" if tc
                                 else "on the fp32 FMA pipe"),
                    "precision": T.ops.get_precision(),
+                   "precision_plan": (None if rep is None else
+                                      {k: rep[k] for k in ("units_on_tensor_cores", "units", "tol", "probe",
+                                                           "err_all_tensor_core", "err_plan")}),
                    "per_gpu_batch": B, "size": S, "parallelism": f"replicas x{world}",
                    "l2_policy": "inputs larger than L2 (1.4 GB activation tensors vs 126 MB L2)"},
         "clocks": clocks,
@@ -505,9 +731,10 @@ def main():
         "roofline": {"kernel": kname,
                      "bound": "hbm", "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s",
                      "frac": (ach_gbs / hbm_peak) if ach_gbs else None,
-                     # dram__bytes_read.sum + dram__bytes_write.sum of one launch at the default
-                     # config, from the ncu --set full capture summarised in profiles/r01_summary.md
-                     "traffic": 4.438e9 if (tc and B == 32 and S == 416) else None,
+                     # dram__bytes_read.sum + dram__bytes_write.sum of one launch at the default config,
+                     # parsed from the newest committed ncu --set full summary (not measured by this run)
+                     "traffic": traffic if (tc and B == 32 and S == 416) else None,
+                     "traffic_source": traffic_src if (tc and B == 32 and S == 416) else None,
                      "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({which})",
                      "algorithmic_bytes_per_launch": attn_bytes,
                      "avg_launch_ms": attn_avg, "launches_timed": len(attn_ms),

@@ -179,11 +179,6 @@ int b200mar_mlp_tma_fwd(const float* a, float* z_inout,
 /* 1 if a tensor-core kernel of this process ever timed out on an mbarrier (every wait is
  * bounded so a descriptor bug cannot hang the device); 0 otherwise; -1 on a CUDA error.     */
 int b200mar_tc_error(void);
-/* Test hook: one 128xN tcgen05 tile product D = A*B^T (mode 0, B [N,K] K-major), D = A*B
- * (mode 1, B [K,N] MN-major) or the same with A staged in TMEM (mode 2); accumulator placed at
- * TMEM column col0.  A [128,K], D [128,N] row-major device buffers; N%16==0, K%8==0.        */
-int b200mar_tc_probe(const float* A, const float* B, float* D, int N, int K, int mode, int col0,
-                     void* stream);
 /* da = dout + d(MLP branch) (overwrites da); parameter gradients accumulated.             */
 int b200mar_mlp_bwd(const float* a, const float* dout,
                     const float* fc1_w, const float* fc1_b,

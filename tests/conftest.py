@@ -35,3 +35,10 @@ def golden_maps():
 def golden_contract():
     import torch
     return torch.load(os.path.join(GOLDEN, "state_dict_contract.pt"), weights_only=False)
+
+
+@pytest.fixture(scope="session")
+def golden_w3():
+    """W3 = trained-like weights + the unmodified reference's outputs on them (oracle/make_w3.py)."""
+    import torch
+    return torch.load(os.path.join(GOLDEN, "w3_trained.pt"), weights_only=False)

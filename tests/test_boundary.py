@@ -108,8 +108,14 @@ def test_no_cpu_forward(model):
 def test_no_weight_decay_and_flops(model):
     nwd = model.no_weight_decay()
     assert len(nwd) == 40 and all("relative_position_bias_table" in n for n in nwd)
-    assert model.flops((416, 416)) == 416 * 416 * 548013
-    assert model.flops((100, 70)) == 128 * 96 * 548013
+    # flops() reproduces the reference's analytic count (values printed by the unmodified reference's
+    # NGswin().flops(), models/generator/ngswin.py:212-238); flops_exact() is the exact MAC count
+    assert model.flops((416, 416)) == 97516238144
+    assert model.flops((64, 64)) == 2308080704
+    assert model.flops((100, 70)) == 6924233792
+    assert model.flops((1024, 1024)) == 590867599424
+    assert model.flops_exact((416, 416)) == 416 * 416 * 548013
+    assert model.flops_exact((100, 70)) == 128 * 96 * 548013
 
 
 def test_cabi_exports_every_declared_symbol():
@@ -131,3 +137,13 @@ def test_product_path_never_imports_oracle():
         if fn.endswith(".py"):
             src = open(os.path.join(pkg, fn)).read()
             assert "oracle" not in src, fn
+
+
+def test_flops_matches_live_reference(model):
+    """flops() against the unmodified reference's own method, when the reference tree is mounted."""
+    from oracle import ref_shim
+    if not ref_shim.reference_available():
+        pytest.skip("reference tree not mounted")
+    ref = ref_shim.load_reference()["NGswin"]()
+    for res in [(416, 416), (128, 128), (96, 160), (100, 70), (1024, 1024)]:
+        assert model.flops(res) == ref.flops(res)

@@ -6,8 +6,11 @@ Tolerances (written here, measured on B200):
     init recipe (W1), PSNR / SSIM against a synthetic target within 0.01 dB / 1e-4;
   * W2 is a deliberately adversarial stress set (weights x5, logit scales up to the ln(100) clamp):
     TF32 operand rounding (2^-11 relative) is amplified by x100 cosine logits and 20 LayerNorms;
-    the measured whole-model error is ~2e-2 and is bounded at 5e-2 here.  The fp32 kernels hold
-    3e-4 on the same set (tests/test_gpu_parity.py);
+    with EVERY unit FORCED onto the tensor cores (set_precision("tf32"), which this file uses to test
+    the tcgen05 kernels themselves) the whole-model error is ~2e-2; the W2 rows below only bound that
+    forced mode (a characterisation, not the parity gate).  The parity gate on W2 - 1e-3, un-relaxed -
+    is tests/test_gpu_auto_precision.py: the default mode measures a per-unit plan and runs the
+    offending units on the fp32 kernels, which hold 3e-4 on the same set (tests/test_gpu_parity.py);
   * per-kernel: LayerNorm output has unit scale, so max-abs is relative to ~4.
 """
 import pytest
@@ -97,6 +100,8 @@ def test_attn_and_mlp_tc_forward(T, kind, case, geom):
 @pytest.mark.parametrize("kind,gate", [("W1", 1e-3), ("W2", 5e-2)])
 @pytest.mark.parametrize("shape", [(1, 64, 64), (2, 96, 160), (1, 100, 70), (1, 128, 128)])
 def test_whole_model_tf32_vs_golden(T, golden_outputs, kind, gate, shape):
+    """Every unit FORCED onto tcgen05.  W1: the parity gate.  W2: bound of the forced mode only - the gate
+    for W2 (1e-3) is met by the default per-unit plan, tests/test_gpu_auto_precision.py."""
     B, H, W = shape
     m = T.NGswin()
     m.load_state_dict(O.synthetic_state_dict(kind, seed=1), strict=True)

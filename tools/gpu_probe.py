@@ -4,8 +4,15 @@ LBO/SBO conventions), 2 = A operand from TMEM."""
 import sys, os
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
+import ctypes, subprocess
 from transmar_gan_b200 import _cabi, ops
-L = _cabi.lib()
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "libtcprobe.so")
+if not os.path.isfile(_SO) or os.path.getmtime(_SO) < os.path.getmtime(os.path.join(_HERE, "tc_probe.cu")):
+    subprocess.check_call(["nvcc", *_cabi.NVCC_FLAGS, "-shared", "-I", _cabi.CSRC, "-I", _cabi.INCLUDE,
+                           os.path.join(_HERE, "tc_probe.cu"), "-o", _SO])
+L = ctypes.CDLL(_SO)
+L.b200mar_tc_probe.argtypes = [ctypes.c_void_p] * 3 + [ctypes.c_int] * 4 + [ctypes.c_void_p]
 torch.manual_seed(0)
 
 

@@ -4,6 +4,8 @@
 //   mode 1: D = A * Bm,  Bm [K,N] MN-major (N contiguous) from shared memory
 //   mode 2: as mode 1, but A is first moved into TMEM (tcgen05.st) and used as a TMEM operand
 // `col0` shifts the accumulator / TMEM-A base column to test unaligned column addressing.
+// Development tooling, NOT part of libb200mar.so: tools/gpu_probe.py builds it into tools/libtcprobe.so
+// (nvcc -I transmar_gan_b200/csrc) on demand.
 #include "common.cuh"
 #include "tc.cuh"
 #include <cuda_fp16.h>
@@ -12,6 +14,8 @@
 namespace b200mar {
 
 B200MAR_DEFINE_TC_ERROR_GETTER(tc_error_probe)
+const char*& last_error_ref() { static thread_local const char* m = "no error"; return m; }
+int sm_count() { return 148; }
 
 __global__ void __launch_bounds__(128, 1) tc_probe_kernel(const float* __restrict__ A,
                                                           const float* __restrict__ B,

@@ -14,7 +14,9 @@ from concurrent.futures import ThreadPoolExecutor
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
-LIB_PATH = os.path.join(_HERE, "libb200mar.so")
+# B200MAR_LIB: development override (e.g. a second build with -DB200MAR_ATTN_PROF for the phase profile);
+# the product library is always transmar_gan_b200/libb200mar.so
+LIB_PATH = os.environ.get("B200MAR_LIB") or os.path.join(_HERE, "libb200mar.so")
 INCLUDE = os.path.join(os.path.dirname(_HERE), "include")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC"]
@@ -48,7 +50,6 @@ SIGNATURES = {
     "b200mar_mlp_tc_fwd": [_P] * 11 + [_I, _L, _P],
     "b200mar_mlp_tma_fwd": [_P] * 9 + [_L, _P],
     "b200mar_tc_error": [],
-    "b200mar_tc_probe": [_P] * 3 + [_I] * 4 + [_P],
     "b200mar_patch_merge_fwd": [_P] * 5 + [_I] * 3 + [_P],
     "b200mar_patch_merge_tc_fwd": [_P] * 5 + [_I] * 3 + [_P],
     "b200mar_patch_merge_bwd": [_P] * 9 + [_I] * 3 + [_P],
@@ -90,7 +91,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     """nvcc -gencode arch=compute_100a,code=sm_100a … -shared → transmar_gan_b200/libb200mar.so"""
     if not force and not needs_build():
         return LIB_PATH
-    objdir = os.path.join(_HERE, "build")
+    tag = os.path.splitext(os.path.basename(LIB_PATH))[0].replace("libb200mar", "")
+    objdir = os.path.join(_HERE, "build" + tag)
     os.makedirs(objdir, exist_ok=True)
 
     def compile_one(src):

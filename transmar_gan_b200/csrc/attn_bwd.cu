@@ -433,11 +433,11 @@ template <int NH>
 static int launch_attn_bwd(const AttnParams& p, cudaStream_t st) {
   using L = AttnSmem<NH>;
   const size_t smem = L::kFloatsBwd * sizeof(float);
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce configured;
+  if (configured.first()) {
     B200MAR_CHECK(cudaFuncSetAttribute(attn_bwd_kernel<NH>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = true;
+    configured.done();
   }
   const int nwin = p.B * (p.ph / kWin) * (p.pw / kWin);
   const int grid = nwin < sm_count() ? nwin : sm_count();

@@ -849,13 +849,13 @@ template <int NH>
 static int launch_attn_bwd_tc(const AttnBwdTcParams& pp, cudaStream_t st) {
   const AttnParams& p = pp.a;
   constexpr int HS = BCfg<NH>::HS, PS = BCfg<NH>::PS, HD = BCfg<NH>::HD, A = BCfg<NH>::A;
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce configured;
+  if (configured.first()) {
     B200MAR_CHECK(cudaFuncSetAttribute(attn_bwd_core_kernel<NH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)AttnBwdSmem::kBytes));
     B200MAR_CHECK(cudaFuncSetAttribute(attn_bwd_dx_kernel<NH>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)AttnDxSmem::kBytes));
-    configured = true;
+    configured.done();
   }
   const int nwin = p.B * (p.ph / kWin) * (p.pw / kWin);
   const int ntile = (nwin + 1) / 2;

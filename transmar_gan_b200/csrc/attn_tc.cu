@@ -682,11 +682,11 @@ template <int NH, bool RESID, bool SAVEO = false>
 static int launch_attn_tc_fwd(const AttnParams& p, cudaStream_t st) {
   constexpr int kWorkers = Cfg<NH>::kWorkers;
   const size_t smem = AttnTcSmem<kWorkers>::kBytes;
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce configured;
+  if (configured.first()) {
     B200MAR_CHECK(cudaFuncSetAttribute(attn_tc_fwd_kernel<NH, RESID, SAVEO>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = true;
+    configured.done();
   }
   const int nwin = p.B * (p.ph / kWin) * (p.pw / kWin);
   const int ntile = (nwin + 1) / 2;

@@ -245,11 +245,11 @@ extern "C" int b200mar_bottleneck_tail_tc_fwd(const float* cat, const float* dw_
   if (int rc = tma::encode_grid(&mE, e1, B, H, W, 16, 8, 1)) return rc;
   if (int rc = tma::encode_grid(&mO, out, B, H, W, 16, 8, 1)) return rc;
   const size_t smem = BnSmem::kBytes;
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce configured;
+  if (configured.first()) {
     B200MAR_CHECK(cudaFuncSetAttribute(bottleneck_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)smem));
-    configured = true;
+    configured.done();
   }
   const int ntile = B * ((H + 7) / 8) * ((W + 15) / 16);
   int grid = (ntile + kBnWorkers - 1) / kBnWorkers;

@@ -439,10 +439,10 @@ int launch_wgrad(const uint16_t* in16, const uint16_t* g16, float* dw, float* db
   const int nstage = kWgStages * stage <= 224 * 1024 ? kWgStages : 2;
   WgradParams p{in16, g16, dw, dbias, n_tok, cin, cout, ld, cin_valid, hs, ps, hd, A, nstage};
   const size_t smem = nstage * stage;
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce configured;
+  if (configured.first()) {
     B200MAR_CHECK(cudaFuncSetAttribute(wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
-    configured = true;
+    configured.done();
   }
   if (smem > 224 * 1024) return -1;
   CUtensorMap mIn, mG;
@@ -479,10 +479,10 @@ extern "C" int b200mar_mlp_bwd_tc(const float* a, const float* dout, const float
   p.d_fc2_b = d_fc2_b; p.d_ln_w = d_ln_w; p.d_ln_b = d_ln_b; p.n_tok = n_tok;
   cudaStream_t st = (cudaStream_t)stream;
   const size_t smem = MlpBwdSmem::kBytes;
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce configured;
+  if (configured.first()) {
     B200MAR_CHECK(cudaFuncSetAttribute(mlp_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = true;
+    configured.done();
   }
   const long long ntile = (n_tok + 127) / 128;
   long long grid = (ntile + kBwdWorkers - 1) / kBwdWorkers;

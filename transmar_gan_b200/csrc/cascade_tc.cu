@@ -233,11 +233,11 @@ extern "C" int b200mar_cascade_proj_tc_fwd(const float* srcA, const float* srcB,
   if (int rc = tma::encode_grid(&mD, direct, B, h, wd, 16, 8, 1)) return rc;
   if (int rc = tma::encode_grid(&mO, out, B, h, wd, 16, 8, 1)) return rc;
   const size_t smem = CasSmem::kBytes;
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce configured;
+  if (configured.first()) {
     B200MAR_CHECK(cudaFuncSetAttribute(cascade_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)smem));
-    configured = true;
+    configured.done();
   }
   const int ntile = B * ((h + 7) / 8) * ((wd + 15) / 16);
   int grid = (ntile + kCasWorkers - 1) / kCasWorkers;

@@ -24,7 +24,21 @@ constexpr float kNormEps = 1e-12f;               // F.normalize eps, attention.p
 
 // ---------------------------------------------------------------- host-side error plumbing
 const char*& last_error_ref();
-int sm_count();
+int sm_count();                  // of the CURRENT device (cached per device)
+// "once per device" guard for per-function attributes (cudaFuncSetAttribute is per device, and a process may
+// drive several GPUs): `static DeviceOnce c; if (c.first()) { ...set attributes...; c.done(); }`
+struct DeviceOnce {
+  unsigned long long mask = 0;   // bit d set = configured on device d (d < 64; larger ordinals always reconfigure)
+  int dev = -1;
+  bool first() {
+    if (cudaGetDevice(&dev) != cudaSuccess) dev = -1;
+    if (dev < 0 || dev >= 64) return true;
+    return !((__atomic_load_n(&mask, __ATOMIC_ACQUIRE) >> dev) & 1ull);
+  }
+  void done() {
+    if (dev >= 0 && dev < 64) __atomic_fetch_or(&mask, 1ull << dev, __ATOMIC_RELEASE);
+  }
+};
 #define B200MAR_CHECK(call)                                                   \
   do {                                                                        \
     cudaError_t _e = (call);                                                  \

@@ -491,11 +491,11 @@ extern "C" int b200mar_final_recon_fwd(const float* dec, const float* c0, const 
     CUtensorMap mD, mC;
     if (int rc = tma::encode_rows64(&mD, dec, ntok)) return rc;
     if (int rc = tma::encode_rows64(&mC, c0, ntok)) return rc;
-    static bool configured = false;
-    if (!configured) {
+    static DeviceOnce configured;
+    if (configured.first()) {
       B200MAR_CHECK(cudaFuncSetAttribute(final_dot9_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)Dot9Smem::kBytes));
-      configured = true;
+      configured.done();
     }
     const long long ntile9 = (ntok + 127) / 128;
     long long grid = (ntile9 + kDotWorkers - 1) / kDotWorkers;

@@ -8,17 +8,16 @@ const char*& last_error_ref() {
   return msg;
 }
 int sm_count() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
-      n = 148;
-  }
+  static int cache[64] = {0};                 // per device ordinal: a process may drive several GPUs
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  if (dev >= 0 && dev < 64 && cache[dev] > 0) return cache[dev];
+  int n = 0;
+  if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+  if (dev >= 0 && dev < 64) cache[dev] = n;
   return n;
 }
 int tc_error_mlp();
-int tc_error_probe();
 int tc_error_attn();
 int tc_error_merge();
 int tc_error_bottleneck();
@@ -29,7 +28,7 @@ int tc_error_attn_bwd();
 
 // 1 if any tensor-core kernel of this process hit its bounded mbarrier wait (descriptor-bug guard)
 extern "C" int b200mar_tc_error(void) {
-  const int a = b200mar::tc_error_mlp(), b = b200mar::tc_error_probe(), c = b200mar::tc_error_attn(),
+  const int a = b200mar::tc_error_mlp(), b = 0, c = b200mar::tc_error_attn(),
             d = b200mar::tc_error_merge(), e = b200mar::tc_error_bottleneck(),
             f = b200mar::tc_error_cascade() | b200mar::tc_error_bwd() | b200mar::tc_error_attn_bwd();
   if (a < 0 || b < 0 || c < 0 || d < 0 || e < 0 || f < 0) return -1;

@@ -171,11 +171,11 @@ extern "C" int b200mar_patch_merge_bwd(const float* x, const float* dy, const fl
   p.x = x; p.dy = dy; p.ln_w = ln_w; p.ln_b = ln_b; p.red_w = red_w; p.dx = dx;
   p.d_ln_w = d_ln_w; p.d_ln_b = d_ln_b; p.d_red_w = d_red_w; p.B = B; p.ph = ph; p.pw = pw;
   const size_t smem = MergeSmem::kFloatsBwd * sizeof(float);
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce configured;
+  if (configured.first()) {
     B200MAR_CHECK(cudaFuncSetAttribute(patch_merge_bwd_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = true;
+    configured.done();
   }
   const long long ntile = ((long long)B * (ph / 2) * (pw / 2) + kTok - 1) / kTok;
   const int grid = (int)(ntile < sm_count() ? ntile : sm_count());

@@ -144,11 +144,11 @@ extern "C" int b200mar_patch_merge_fwd(const float* x, const float* ln_w, const 
   MergeParams p{};
   p.x = x; p.ln_w = ln_w; p.ln_b = ln_b; p.red_w = red_w; p.y = y; p.B = B; p.ph = ph; p.pw = pw;
   const size_t smem = MergeSmem::kFloatsFwd * sizeof(float);
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce configured;
+  if (configured.first()) {
     B200MAR_CHECK(cudaFuncSetAttribute(patch_merge_fwd_kernel,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = true;
+    configured.done();
   }
   const long long ntile = ((long long)B * (ph / 2) * (pw / 2) + kTok - 1) / kTok;
   const int grid = (int)(ntile < sm_count() ? ntile : sm_count());

@@ -231,11 +231,11 @@ extern "C" int b200mar_patch_merge_tc_fwd(const float* x, const float* ln_w, con
   if (int rc = tma::encode_grid(&mX, x, B, ph, pw, 16, 8, 2)) return rc;
   if (int rc = tma::encode_grid(&mY, y, B, ph / 2, pw / 2, 16, 8, 1)) return rc;
   const size_t smem = MergeTcSmem::kBytes;
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce configured;
+  if (configured.first()) {
     B200MAR_CHECK(cudaFuncSetAttribute(patch_merge_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)smem));
-    configured = true;
+    configured.done();
   }
   const int ntile = B * ((ph / 2 + 7) / 8) * ((pw / 2 + 15) / 16);
   int grid = (ntile + kMergeWorkers - 1) / kMergeWorkers;

@@ -178,11 +178,11 @@ extern "C" int b200mar_mlp_bwd(const float* a, const float* dout, const float* f
   p.ln_w = ln_w; p.ln_b = ln_b; p.da = da; p.d_fc1_w = d_fc1_w; p.d_fc1_b = d_fc1_b;
   p.d_fc2_w = d_fc2_w; p.d_fc2_b = d_fc2_b; p.d_ln_w = d_ln_w; p.d_ln_b = d_ln_b; p.n_tok = n_tok;
   const size_t smem = MlpSmem::kFloatsBwd * sizeof(float);
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce configured;
+  if (configured.first()) {
     B200MAR_CHECK(cudaFuncSetAttribute(mlp_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)smem));
-    configured = true;
+    configured.done();
   }
   const long long ntile = n_tok / kTok;
   const int grid = (int)(ntile < sm_count() ? ntile : sm_count());

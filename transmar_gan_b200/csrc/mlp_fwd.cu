@@ -98,11 +98,11 @@ extern "C" int b200mar_mlp_fwd(const float* a, const float* z, const float* fc1_
   p.a = a; p.z = z; p.fc1_w = fc1_w; p.fc1_b = fc1_b; p.fc2_w = fc2_w; p.fc2_b = fc2_b;
   p.ln_w = ln_w; p.ln_b = ln_b; p.out = out; p.zsum = zsum; p.n_tok = n_tok;
   const size_t smem = MlpSmem::kFloatsFwd * sizeof(float);
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce configured;
+  if (configured.first()) {
     B200MAR_CHECK(cudaFuncSetAttribute(mlp_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)smem));
-    configured = true;
+    configured.done();
   }
   const long long ntile = n_tok / kTok;
   const int grid = (int)(ntile < sm_count() ? ntile : sm_count());

@@ -581,11 +581,11 @@ extern "C" int b200mar_mlp_tc_fwd(const float* a, const float* z, const float* f
   p.ln_w = ln_w; p.ln_b = ln_b; p.out = out; p.zsum = zsum; p.n_tok = n_tok;
   p.a_out = a_out; p.a_is_delta = a_is_delta;
   const size_t smem = MlpTcSmem::kBytes;
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce configured;
+  if (configured.first()) {
     B200MAR_CHECK(cudaFuncSetAttribute(mlp_tc_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)smem));
-    configured = true;
+    configured.done();
   }
   const long long ntile = (n_tok + 127) / 128;
   long long grid = (ntile + kMlpWorkers - 1) / kMlpWorkers;
@@ -610,11 +610,11 @@ extern "C" int b200mar_mlp_tma_fwd(const float* a, float* z_inout, const float* 
   if (int rc = tma::encode_rows64(&mZ, z_inout ? z_inout : a, n_tok)) return rc;
   if (int rc = tma::encode_rows64(&mO, out ? out : a, n_tok)) return rc;
   const size_t smem = MlpTmaSmem::kBytes;
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce configured;
+  if (configured.first()) {
     B200MAR_CHECK(cudaFuncSetAttribute(mlp_tma_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)smem));
-    configured = true;
+    configured.done();
   }
   const long long ntile = (n_tok + 127) / 128;
   long long grid = (ntile + kTmaWorkers - 1) / kTmaWorkers;

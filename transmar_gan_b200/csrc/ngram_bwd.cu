@@ -427,11 +427,11 @@ template <int NH>
 static int launch_ngram_ctx_bwd(const NgramParams& p, cudaStream_t st) {
   using LB = NgramSmemBwd<NH>;
   const size_t smem = LB::kFloats * sizeof(float);
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce configured;
+  if (configured.first()) {
     B200MAR_CHECK(cudaFuncSetAttribute(ngram_ctx_bwd_kernel<NH>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = true;
+    configured.done();
   }
   const int nwin = p.B * p.wh * p.ww;
   int grid = (nwin + 7) / 8;

@@ -273,11 +273,11 @@ template <int NH, bool PRE>
 static int launch_ngram_ctx_fwd(const NgramParams& p, cudaStream_t st) {
   using L = NgramSmem<NH>;
   const size_t smem = L::kFloatsFwd * sizeof(float);
-  static bool configured = false;
-  if (!configured) {
+  static DeviceOnce configured;
+  if (configured.first()) {
     B200MAR_CHECK(cudaFuncSetAttribute(ngram_ctx_fwd_kernel<NH, PRE>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = true;
+    configured.done();
   }
   const int nwin = p.B * p.wh * p.ww;
   int grid = (nwin + 7) / 8;

@@ -7,8 +7,8 @@
 //     LBO = R*16 B (next 16-byte k-chunk).  A thread that owns row r writes one float4 per
 //     k-chunk and consecutive rows are consecutive 16-byte slots -> conflict-free;
 //   * accumulators are M = 128 rows (TMEM lane = row) x N fp32 columns, cta_group::1;
-//   * every mbarrier wait is bounded: on timeout a global error flag is raised and the wait
-//     returns, so a descriptor bug can never hang the GPU box.
+//   * every mbarrier wait is bounded (2^22 try_wait rounds, seconds): on timeout a global error flag is
+//     raised and the kernel TRAPS, so a descriptor bug can neither hang the GPU box nor be computed through.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -52,7 +52,12 @@ __device__ __forceinline__ bool mbar_wait(uint64_t* bar, uint32_t parity, int* e
         : "=r"(done) : "r"(addr), "r"(parity) : "memory");
     if (done) return true;
   }
+  // A barrier that never completes is a bug (bad descriptor, lost commit): raise the flag for
+  // b200mar_tc_error() and kill the kernel - continuing would consume unsynchronised TMEM / shared memory and
+  // silently corrupt outputs or gradients.  The trap surfaces as a CUDA error on the next runtime call.
   if (err) atomicExch(err, 1);
+  __threadfence_system();
+  __trap();
   return false;
 }
 

@@ -108,6 +108,7 @@ class NSTB(nn.Module):
                  head_dim=None, mlp_ratio=2., qkv_bias=True):
         super().__init__()
         self.num_heads, self.shift_size = num_heads, shift_size
+        self._mode = None          # "tf32" / "fp32" assigned by NGswin's precision plan; None = the selected mode
         self.ngram_window_partition = NGramWindowPartition(dim, window_size, ngram, num_heads,
                                                            shift_size)
         self.attn = WindowAttention(dim, num_heads, window_size, head_dim, qkv_bias)
@@ -144,7 +145,7 @@ class PatchMerging(nn.Module):
 
     def forward(self, x, num_patches):
         ph, pw = num_patches
-        if not torch.is_grad_enabled() and ops.get_precision() == "tf32":
+        if not torch.is_grad_enabled() and ops.effective_precision() == "tf32":
             y = ops.patch_merge_tc_fwd(x, self.norm.weight.detach(), self.norm.bias.detach(),
                                        self.reduction.weight.detach(), ph, pw)
             return y, (ph // 2, pw // 2)
@@ -168,19 +169,21 @@ class _Stage(nn.Module):
         for its successor, so intermediate `out` tensors are never written."""
         z, n = x, len(self.blocks)
         out = zsum = None
-        inplace = not torch.is_grad_enabled() and ops.get_precision() == "tf32"
+        private = owned                  # may z be updated in place?
         for i, blk in enumerate(self.blocks):
             last = i == n - 1
-            if inplace:
-                # the block adds its output into z (TMA reduce-add), so z must be private to this
-                # loop: the stage input is copied once, later blocks own the previous block's sum
-                want_zsum = (not last) or need_sum_last
-                if i == 0 and want_zsum and not owned:
-                    z = z.clone()
-                out, zsum = ops.nstb_infer_(z, *num_patches, blk.num_heads, blk.shift_size, last,
-                                            want_zsum, blk.kernel_params())
-            else:
-                out, zsum = blk(z, num_patches, want_out=last, want_zsum=(not last) or need_sum_last)
+            want_zsum = (not last) or need_sum_last
+            with ops.precision_scope(blk._mode):
+                if not torch.is_grad_enabled() and ops.effective_precision() == "tf32":
+                    # the block adds its output into z (TMA reduce-add), so z must be private to this
+                    # loop: the stage input is copied once, later blocks own the previous block's sum
+                    if want_zsum and not private:
+                        z = z.clone()
+                    out, zsum = ops.nstb_infer_(z, *num_patches, blk.num_heads, blk.shift_size, last,
+                                                want_zsum, blk.kernel_params())
+                else:
+                    out, zsum = blk(z, num_patches, want_out=last, want_zsum=want_zsum)
+            private = True               # zsum is this loop's own tensor (fresh, or the private z updated)
             z = zsum
         return out, zsum
 
@@ -331,10 +334,108 @@ class NGswin(nn.Module):
     def no_weight_decay(self):
         return {n for n, _ in self.named_parameters() if 'relative_position_bias_table' in n}
 
+    # ---------------------------------------------------------------- precision plan ("auto" mode)
+    def _units(self):
+        """The 21 units a precision plan covers: the 20 NSTBs in execution order, then the stage glue
+        (PatchMerging, cascade projections, bottleneck) as one unit."""
+        return [b for st in (self.encoder_layer1, self.encoder_layer2, self.encoder_layer3, self.decoder_layer1)
+                for b in st.blocks]
+
+    def _weights_key(self):
+        ps = list(self.parameters())
+        return (sum(p._version for p in ps), ps[0].data_ptr(), str(ps[0].device))
+
+    def _set_plan(self, plan):
+        blocks = self._units()
+        for b, m in zip(blocks, plan[:len(blocks)] if plan else [None] * len(blocks)):
+            b._mode = m
+        self._glue_mode = plan[len(blocks)] if plan else None
+
+    @torch.no_grad()
+    def calibrate_precision(self, tol: float = 4e-4, size: int = 96, seed: int = 4242):
+        """Measure, on a seeded probe slice, which units may run on the tensor cores (FP16 / TF32 operands)
+        without moving the model output by more than `tol` (default 0.4 of the 1e-3 parity gate, the margin
+        covering other inputs and larger images) relative to the all-fp32 kernels, and store that plan:
+        it is what precision "auto" executes.  All units pass on init-scale and trained-like weights; weight
+        sets whose x100 cosine logits amplify the 2^-11 operand rounding (the W2 stress set) fall back, unit
+        by unit, to the fp32 FMA-pipe kernels of this library.  Returns the report dict (also `.precision_report`)."""
+        p0 = next(self.parameters())
+        if not p0.is_cuda:
+            raise RuntimeError("calibrate_precision: move the module to a B200 first (there is no CPU path)")
+        g = torch.Generator().manual_seed(seed)
+        x = (torch.rand(1, 1, size, size, generator=g) * 2 - 1).to(p0.device)
+        n = len(self._units()) + 1
+        saved = [b._mode for b in self._units()] + [getattr(self, "_glue_mode", None)]
+
+        def run(plan):
+            self._set_plan(plan)
+            return self._forward_planned(x)
+
+        try:
+            ref = run(["fp32"] * n)
+            err_all = (run(["tf32"] * n) - ref).abs().max().item()
+            marginal = None
+            if err_all <= tol:
+                plan, err = ["tf32"] * n, err_all
+            else:
+                marginal = []
+                for u in range(n):
+                    trial = ["fp32"] * n
+                    trial[u] = "tf32"
+                    marginal.append((run(trial) - ref).abs().max().item())
+                plan, err = ["fp32"] * n, 0.0
+                for u in sorted(range(n), key=lambda i: marginal[i]):
+                    if marginal[u] > tol:
+                        break
+                    trial = list(plan)
+                    trial[u] = "tf32"
+                    e = (run(trial) - ref).abs().max().item()
+                    if e <= tol:
+                        plan, err = trial, e
+        finally:
+            self._set_plan(saved)
+        self._auto_plan, self._auto_key, self._auto_age = plan, self._weights_key(), 0
+        self.precision_report = {"tol": tol, "probe": f"1x1x{size}x{size} uniform[-1,1), seed {seed}",
+                                 "err_all_tensor_core": err_all, "err_plan": err,
+                                 "units_on_tensor_cores": sum(m == "tf32" for m in plan), "units": n,
+                                 "plan": list(plan), "marginal_err": marginal}
+        return self.precision_report
+
+    #: in train() mode the weights change every step: the plan is re-measured every this many forwards
+    AUTO_RECALIBRATE_EVERY = 500
+
+    def _auto_refresh(self):
+        capturing = torch.cuda.is_current_stream_capturing()
+        plan = getattr(self, "_auto_plan", None)
+        if plan is None:
+            if capturing:
+                raise RuntimeError("precision 'auto': call model.calibrate_precision() before CUDA-graph capture")
+            self.calibrate_precision()
+        elif not capturing:
+            self._auto_age += 1
+            if self.training:        # weights move a little every step: re-measure periodically
+                stale = self._auto_age >= self.AUTO_RECALIBRATE_EVERY
+            else:                    # eval: re-measure whenever the weights were modified or moved
+                stale = self._weights_key() != self._auto_key
+            if stale:
+                self.calibrate_precision()
+        return self._auto_plan
+
     def forward(self, x):
         if not x.is_cuda:
             raise RuntimeError("transmar_gan_b200.NGswin has no CPU path; move the module and the "
                                "input to a B200 (`.cuda()`)")
+        if ops.get_precision() == "auto" and not ops._SCOPE:
+            self._set_plan(self._auto_refresh())
+        else:
+            self._set_plan(None)
+        return self._forward_planned(x)
+
+    def _forward_planned(self, x):
+        with ops.precision_scope(getattr(self, "_glue_mode", None)):
+            return self._forward_impl(x)
+
+    def _forward_impl(self, x):
         _, _, H0, W0 = x.shape
         unit = 4 * self.window_size
         padh, padw = (unit - H0 % unit) % unit, (unit - W0 % unit) % unit
@@ -384,6 +485,58 @@ class NGswin(nn.Module):
                                    tt.to_origin.weight, tt.to_origin.bias, H, W, H0, W0)
 
     def flops(self, resolutions):
+        """The reference's analytic count, reproduced term by term (models/generator/ngswin.py:212-238 and the
+        `flops()` methods it sums: attention.py:103-115, window_utils.py:92-104, transformer_blocks.py:122-138,
+        encoder_decoder.py:29-33,76-83,147-157,202-213,260-266, pooling.py:19-23,39-49, reconstruction.py:21-29).
+        It counts MACs, adds LayerNorm / bias / activation terms, and over-counts the 6-head attention by taking
+        A = dim; `flops_exact()` is the exact MAC count the roofline uses."""
+        unit = 4 * self.window_size
+        D = self.embed_dim
+        H, W = resolutions
+        H += (unit - H % unit) % unit
+        W += (unit - W % unit) % unit
+
+        def attn(dim, nh, area, nwin):
+            f = area * dim * 3 * dim + 3 * dim
+            f += 2 * nh * area * (dim // nh) * area
+            f += area * dim * dim + dim
+            return f * nwin
+
+        def nstb(h, w, nh):
+            wh, ww = h // 8, w // 8
+            f = wh * ww * 64 * D + wh * ww * D                      # unigram embed
+            f += 2 * attn(D // 2, nh, 4, wh * ww) + wh * ww * 4 * D + wh * ww * D * D
+            f += attn(D, nh, 64, h // 8 * w // 8)                   # (S)W-MSA
+            f += h * w * D                                          # norm1
+            f = int(f + h * w * D * 2.0 * D + 2.0 * D + h * w * 2.0 * D * D + D)
+            return f + h * w * D                                    # norm2
+
+        def merge(h, w):
+            return h * w * 4 * D + (h // 2) * (w // 2) * 4 * D * D + D
+
+        f = H * W * 9 * D + H * W * D                                # shallow
+        f += sum(nstb(H, W, self.num_heads[0]) for _ in range(self.depths[0])) + merge(H, W)
+        f += (H // 2) * (W // 2) * 4 * D                             # inter_pool
+        h2, w2 = H // 2, W // 2
+        f += h2 * w2 * 2 * D * D + D + sum(nstb(h2, w2, self.num_heads[1]) for _ in range(self.depths[1]))
+        f += merge(h2, w2)
+        f += (h2 // 2) * (w2 // 2) * 4 * 2 * D
+        h3, w3 = H // 4, W // 4
+        f += h3 * w3 * 3 * D * D + D + sum(nstb(h3, w3, self.num_heads[2]) for _ in range(self.depths[2]))
+        for i in range(3):                                           # bottleneck pools (pooling.py:39-49)
+            hr, wr = H // 2, W // 2
+            for _ in range(i):
+                f += hr * wr * 4 * D
+                hr, wr = hr // 2, wr // 2
+            f += (H // 2 ** i) * (W // 2 ** i) * D
+        cd = self.bottleneck.concat_dim
+        f += H * W * 9 * cd + 2 * H * W * cd + H * W * cd * self.dec_dim + self.dec_dim
+        f += sum(nstb(H, W, self.dec_num_heads[0]) for _ in range(self.dec_depths[0]))
+        f += H * W * D                                               # norm
+        f += H * W * 9 * self.dec_dim + H * W + H * W * 9 + H * W    # reconstruction
+        return f
+
+    def flops_exact(self, resolutions):
         """Exact multiply-accumulate count of one forward, unpadded head dims."""
         unit = 4 * self.window_size
         H, W = resolutions

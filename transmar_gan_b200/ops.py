@@ -19,24 +19,62 @@ from . import _cabi
 
 _NS = "b200mar"
 
-# Arithmetic of the block GEMMs (qkv, QK^T, PV, proj, fc1, fc2):
-#   "tf32": tcgen05.mma kind::tf32 (10-bit-mantissa operands, fp32 accumulate in TMEM) — the fast path;
-#   "fp32": the fp32 FMA-pipe kernels (bit-for-bit fp32 operands), kept as the precision reference.
-# Both are sm_100a CUDA kernels of this library; neither is a fallback for the other.
-_PRECISION = os.environ.get("B200MAR_PRECISION", "tf32")
+# Arithmetic of the block GEMMs (qkv, QK^T, PV, proj, fc1, fc2) and of the glue GEMMs:
+#   "tf32": tcgen05.mma (FP16 / TF32 operands - 11-bit significands - fp32 accumulate in TMEM): the fast path;
+#   "fp32": the fp32 FMA-pipe kernels (bit-for-bit fp32 operands), the precision reference;
+#   "auto": (default) per-UNIT choice between the two, made by the model from a measured probe
+#           (NGswin.calibrate_precision: every unit - 20 NSTBs + the stage glue - runs on the tensor cores
+#           unless that moves the probe output by more than a fraction of the 1e-3 parity gate; weight sets
+#           whose x100 cosine logits amplify 2^-11 operand rounding past the gate, like the W2 stress set,
+#           are routed to the fp32 kernels instead of being computed out of tolerance).
+# All are sm_100a CUDA kernels of this library; none is a CPU or PyTorch fallback.
+_PRECISION = os.environ.get("B200MAR_PRECISION", "auto")
+_SCOPE: List[str] = []          # innermost precision_scope ("tf32" / "fp32"); empty = follow _PRECISION
 
 
 def set_precision(mode: str) -> str:
-    """Select "tf32" (tensor cores) or "fp32" (FMA pipe) for the block kernels; returns the old mode."""
+    """Select "auto" (per-unit, measured), "tf32" (tensor cores) or "fp32" (FMA pipe); returns the old mode."""
     global _PRECISION
-    if mode not in ("tf32", "fp32"):
-        raise ValueError("precision must be 'tf32' or 'fp32'")
+    if mode not in ("auto", "tf32", "fp32"):
+        raise ValueError("precision must be 'auto', 'tf32' or 'fp32'")
     old, _PRECISION = _PRECISION, mode
     return old
 
 
 def get_precision() -> str:
+    """The user-selected mode ("auto" / "tf32" / "fp32")."""
     return _PRECISION
+
+
+def effective_precision() -> str:
+    """What a kernel launched NOW computes in: the innermost precision_scope, else the selected mode
+    ("auto" outside any model-assigned scope = "tf32": the per-unit plan lives in the model)."""
+    if _SCOPE:
+        return _SCOPE[-1]
+    return "fp32" if _PRECISION == "fp32" else "tf32"
+
+
+class precision_scope:
+    """Context manager: kernels launched inside compute in `mode` ("tf32" / "fp32"; None = no change)."""
+
+    def __init__(self, mode: Optional[str]):
+        if mode not in (None, "tf32", "fp32"):
+            raise ValueError("precision_scope takes 'tf32', 'fp32' or None")
+        self.mode = mode
+
+    def __enter__(self):
+        if self.mode is not None:
+            _SCOPE.append(self.mode)
+        return self
+
+    def __exit__(self, *exc):
+        if self.mode is not None:
+            _SCOPE.pop()
+        return False
+
+
+def _tc() -> bool:
+    return effective_precision() == "tf32"
 
 
 # Fused gradient accumulation.  Every backward kernel ACCUMULATES its parameter gradients with atomics, so
@@ -79,11 +117,27 @@ def _grad_targets(params):
     return out
 
 
+# Device of the op being launched: set by _chk / _on from the op's tensors, read by _stream (the current
+# stream OF THAT DEVICE) and by _call (which makes it the current CUDA device around the C-ABI call, so a
+# model on cuda:1 launches on cuda:1 whatever the caller's current device is).
+_DEV: Optional[int] = None
+
+
+def _on(device) -> None:
+    global _DEV
+    device = torch.device(device)
+    if device.type != "cuda":
+        raise RuntimeError(f"transmar_gan_b200 ops have no CPU path (device {device})")
+    _DEV = device.index if device.index is not None else torch.cuda.current_device()
+
+
 def _stream() -> int:
-    return torch.cuda.current_stream().cuda_stream
+    return torch.cuda.current_stream(_DEV).cuda_stream
 
 
 def _chk(*tensors: Tensor):
+    global _DEV
+    dev = None
     for t in tensors:
         if t is None:
             continue
@@ -93,6 +147,12 @@ def _chk(*tensors: Tensor):
         if t.dtype != torch.float32 or not t.is_contiguous():
             raise RuntimeError(f"b200mar ops need contiguous fp32 tensors, got {t.dtype}, "
                                f"contiguous={t.is_contiguous()}")
+        if dev is None:
+            dev = t.device.index
+        elif t.device.index != dev:
+            raise RuntimeError(f"b200mar ops need all tensors on one device, got cuda:{dev} and {t.device}")
+    if dev is not None:
+        _DEV = dev
 
 
 class profile:
@@ -115,6 +175,9 @@ class profile:
 
 
 def _call(name: str, *args, meta=None):
+    if _DEV is not None and _DEV != torch.cuda.current_device():
+        with torch.cuda.device(_DEV):
+            return _call(name, *args, meta=meta)
     fn = getattr(_cabi.lib(), "b200mar_" + name)
     profile.launches += 1
     if name in profile.timed:
@@ -390,8 +453,8 @@ def mlp_bwd_tc(a: Tensor, dout: Tensor, params: List[Tensor], da: Tensor, grads:
 def wgrad_tc(in16: Tensor, g16: Tensor, dw: Tensor, dbias: Optional[Tensor]) -> None:
     """dw[cout][cin] += g16^T in16 (and dbias += column sums of g16) on the tensor cores; bf16 inputs."""
     for t in (in16, g16):
-        if not t.is_cuda or t.dtype != torch.bfloat16 or not t.is_contiguous():
-            raise RuntimeError("wgrad_tc needs contiguous CUDA bf16 operands")
+        if not t.is_cuda or t.dtype != torch.bfloat16 or not t.is_contiguous() or t.device != dw.device:
+            raise RuntimeError("wgrad_tc needs contiguous CUDA bf16 operands on the device of dw")
     _chk(dw, dbias)
     _call("wgrad_tc", in16.data_ptr(), g16.data_ptr(), _p(dw), _p(dbias), in16.shape[0], in16.shape[1],
           g16.shape[1], _stream(), meta=(in16.shape[0],))
@@ -491,7 +554,7 @@ def cascade_proj_fwd(srcA: Tensor, srcB: Optional[Tensor], direct: Tensor, w: Te
     B = direct.shape[0]
     out = torch.empty((B, h * wd, 64), device=direct.device, dtype=torch.float32)
     pool = torch.empty_like(out) if want_pool else None
-    _call("cascade_proj_tc_fwd" if _PRECISION == "tf32" else "cascade_proj_fwd", _p(srcA), _p(srcB),
+    _call("cascade_proj_tc_fwd" if _tc() else "cascade_proj_fwd", _p(srcA), _p(srcB),
           _p(direct), _p(w), _p(bias), _p(out), _p(pool), B, h, wd, _stream())
     return out, pool
 
@@ -505,7 +568,7 @@ def bottleneck_fwd(c0: Tensor, p0: Tensor, p00: Tensor, e1: Tensor, e2: Tensor, 
     cat = torch.empty((B, H * W, 84), device=c0.device, dtype=torch.float32)
     _call("bottleneck_cat_fwd", _p(c0), _p(p0), _p(p00), _p(e1), _p(e2), _p(e3), _p(cat), B, H, W, _stream())
     out = torch.empty_like(c0)
-    _call("bottleneck_tail_tc_fwd" if _PRECISION == "tf32" else "bottleneck_tail_fwd", _p(cat), _p(dw_w), _p(dw_b), _p(pw_w), _p(pw_b), _p(ln_w), _p(ln_b),
+    _call("bottleneck_tail_tc_fwd" if _tc() else "bottleneck_tail_fwd", _p(cat), _p(dw_w), _p(dw_b), _p(pw_w), _p(pw_b), _p(ln_w), _p(ln_b),
           _p(e1), _p(out), B, H, W, _stream())
     return out
 
@@ -527,6 +590,7 @@ def partition_index(B: int, ph: int, pw: int, shift: int, device) -> Tuple[Tenso
     n = B * (ph // 8) * (pw // 8)
     tok = torch.empty((n, 64), dtype=torch.int64, device=device)
     cwin = torch.empty((n, 64), dtype=torch.int64, device=device)
+    _on(tok.device)
     _call("partition_index", tok.data_ptr(), cwin.data_ptr(), B, ph, pw,
                                                     shift, _stream())
     return tok, cwin
@@ -534,12 +598,14 @@ def partition_index(B: int, ph: int, pw: int, shift: int, device) -> Tuple[Tenso
 
 def shift_mask(ph: int, pw: int, shift: int, device) -> Tensor:
     m = torch.empty(((ph // 8) * (pw // 8), 64, 64), dtype=torch.float32, device=device)
+    _on(m.device)
     _call("shift_mask", m.data_ptr(), ph, pw, shift, _stream())
     return m
 
 
 def rel_index(device) -> Tensor:
     r = torch.empty((64, 64), dtype=torch.int64, device=device)
+    _on(r.device)
     _call("rel_index", r.data_ptr(), _stream())
     return r
 
@@ -590,7 +656,8 @@ class NSTBFunction(torch.autograd.Function):
         P = [p.detach() for p in params]
         u = unigram_fwd(z, P[0], P[1], ph, pw)
         c = ngram_ctx_fwd(u, P[2], P[3], P[4], P[5], P[6], P[7], P[8], P[9], nh)
-        if _PRECISION == "tf32":
+        tc = ctx_.tc = _tc()                       # the backward runs in the mode the forward ran in
+        if tc:
             # (attn_tc_fwd(residual=False) + mlp_tc_fwd(a_is_delta=True) moves the residual add into
             # the MLP kernel; measured on B200 it costs the MLP more than it saves the attention)
             if save:
@@ -608,7 +675,7 @@ class NSTBFunction(torch.autograd.Function):
             a = attn_fwd(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw, nh, shift)
             out, zsum = mlp_fwd(a, z if want_zsum else None, P[18], P[19], P[20], P[21], P[22], P[23],
                                 want_out, want_zsum)
-        ctx_.has_o16 = bool(save and _PRECISION == "tf32")
+        ctx_.has_o16 = bool(save and tc)
         if ctx_.has_o16:
             ctx_.save_for_backward(z, u, c, a, o16, *params)
         elif save:
@@ -642,14 +709,13 @@ class NSTBFunction(torch.autograd.Function):
                 G.append(flat[off:off + n].view(p.shape))
                 off += n
         da = torch.empty_like(a)
-        (mlp_bwd_tc if _PRECISION == "tf32" else mlp_bwd)(a, g, P[18:24], da, G[18:24])
+        (mlp_bwd_tc if ctx_.tc else mlp_bwd)(a, g, P[18:24], da, G[18:24])
         dz = torch.empty_like(z)
         dctx = torch.zeros_like(c)
         if o16 is not None:
             attn_bwd_tc(z, c, da, P[10:18], dz, dctx, G[10:18], ph, pw, nh, shift, o16)
         else:
-            (attn_bwd_tc if _PRECISION == "tf32" else attn_bwd)(z, c, da, P[10:18], dz, dctx, G[10:18], ph, pw,
-                                                                 nh, shift)
+            (attn_bwd_tc if ctx_.tc else attn_bwd)(z, c, da, P[10:18], dz, dctx, G[10:18], ph, pw, nh, shift)
         du = torch.empty_like(u)
         ngram_ctx_bwd(u, dctx, P[2:10], du, G[2:10], nh)
         # dz = attention part + unigram part + gradient of the within-stage sum, in one pass
@@ -660,7 +726,7 @@ class NSTBFunction(torch.autograd.Function):
 class PatchMergeFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx_, x, ph, pw, ln_w, ln_b, red_w):
-        fwd = patch_merge_tc_fwd if _PRECISION == "tf32" else patch_merge_fwd      # (the backward recomputes in fp32)
+        fwd = patch_merge_tc_fwd if _tc() else patch_merge_fwd      # (the backward recomputes in fp32)
         y = fwd(x, ln_w.detach(), ln_b.detach(), red_w.detach(), ph, pw)
         ctx_.save_for_backward(x, ln_w, ln_b, red_w)
         ctx_.geom = (ph, pw)

@@ -38,6 +38,15 @@ def _fused_acc():
     return ops.fused_grad_accumulation(True)
 
 
+def _calibrate(model):
+    """Precision "auto": the per-unit plan is measured now - a CUDA-graph capture freezes whatever plan is in
+    force (NGswin re-measures it every AUTO_RECALIBRATE_EVERY eager training forwards, never during replay)."""
+    from . import ops
+    if ops.get_precision() == "auto" and hasattr(model, "calibrate_precision") and next(model.parameters()).is_cuda:
+        if getattr(model, "_auto_plan", None) is None or model._weights_key() != model._auto_key:
+            model.calibrate_precision()
+
+
 class L1TrainStep:
     """Callable `step(x, target) -> loss` (a 0-d CUDA tensor; reading it synchronises)."""
 
@@ -72,6 +81,7 @@ class L1TrainStep:
         if not x.is_cuda:
             raise RuntimeError("L1TrainStep: inputs must be CUDA tensors (there is no CPU path)")
         self._x, self._t = x.clone(), t.clone()
+        _calibrate(self.model)
         # the warm-up steps must not count: parameters and optimizer state are restored in place afterwards
         params = [p for g in self.opt.param_groups for p in g["params"]]
         snap_p = [p.detach().clone() for p in params]
@@ -118,7 +128,7 @@ class L1TrainStep:
         if self._gB is not None:
             self.bucket.all_reduce(self.group)
             self._gB.replay()
-        return self._loss
+        return self._loss.clone()       # the static loss buffer is overwritten by the next replay
 
 
 class GANTrainStep:
@@ -241,10 +251,11 @@ class GANTrainStep:
         if not ct.is_cuda:
             raise RuntimeError("GANTrainStep: inputs must be CUDA tensors (there is no CPU path)")
         self._ct, self._real = ct.clone(), real.clone()
-        fresh = not self.optG.state and not self.optD.state
-        if not fresh:
-            raise RuntimeError("GANTrainStep: capture the step before the first optimizer update")
+        _calibrate(self.netG)
         tensors, snap = self._snapshot()           # warm-up must not count (weights, spectral-norm u/v, Adam)
+        # optimizer state that already exists (a resumed checkpoint) is restored; state the warm-up creates is zeroed
+        snap_s = {id(p): {k: v.clone() for k, v in st.items() if torch.is_tensor(v)}
+                  for opt in (self.optG, self.optD) for p, st in opt.state.items() if st}
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
@@ -255,10 +266,11 @@ class GANTrainStep:
             for t, s in zip(tensors, snap):
                 t.copy_(s)
             for opt in (self.optG, self.optD):
-                for st in opt.state.values():
-                    for v in st.values():
+                for p, st in opt.state.items():
+                    old = snap_s.get(id(p))
+                    for k, v in st.items():
                         if torch.is_tensor(v):
-                            v.zero_()
+                            v.copy_(old[k]) if old is not None and k in old else v.zero_()
         torch.cuda.synchronize()
         g1 = torch.cuda.CUDAGraph()
         if self.world == 1:
@@ -297,4 +309,4 @@ class GANTrainStep:
             self._graphs[1].replay()
             self.bucketG.all_reduce(self.group)
             self._graphs[2].replay()
-        return self._lD, self._lG
+        return self._lD.clone(), self._lG.clone()   # the static buffers are overwritten by the next replay
