@@ -64,8 +64,11 @@ constexpr float kLog2e = 1.4426950408889634f;
 // workers (tiles in flight) per CTA.  NH = 6: heads are packed as [q10|k10|v10|0 0] = 32 accumulator
 // columns, so a worker needs 2 x 32 (qkv, double-buffered; O_h over the dead buffer) + 64 (S/P/Y) = 128
 // TMEM columns and FOUR fit; NH = 4 (head dim 16): 2 x 48 + 64 = 160 columns, three workers.
+#ifndef B200MAR_ATTN6_WORKERS
+#define B200MAR_ATTN6_WORKERS 4          // development knob (A/B builds through B200MAR_NVCC_EXTRA)
+#endif
 template <int NH> struct Cfg {
-  static constexpr int kWorkers = NH == 6 ? 4 : 3;
+  static constexpr int kWorkers = NH == 6 ? B200MAR_ATTN6_WORKERS : 3;
   static constexpr int HS = NH == 6 ? 32 : 48;     // packed rows / accumulator columns per head
   static constexpr int PS = NH == 6 ? 10 : 16;     // stride of q, k, v inside a head's block
   static constexpr uint32_t kTStride = 2 * HS + 64;

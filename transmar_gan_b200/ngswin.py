@@ -353,7 +353,9 @@ class NGswin(nn.Module):
 
     @torch.no_grad()
     def calibrate_precision(self, tol: float = 4e-4, size: int = 96, seed: int = 4242):
-        """Measure, on a seeded probe slice, which units may run on the tensor cores (FP16 / TF32 operands)
+        """Measure, on two seeded probe slices (one uniform noise, one structured: flat regions, soft ellipses,
+        a saturated disc, radial streaks - piecewise-constant content is what 11-bit operands are worst at, since
+        LayerNorm / F.normalize renormalise rows of almost identical values), which units may run on the tensor cores (FP16 / TF32 operands)
         without moving the model output by more than `tol` (default 0.4 of the 1e-3 parity gate, the margin
         covering other inputs and larger images) relative to the all-fp32 kernels, and store that plan:
         it is what precision "auto" executes.  All units pass on init-scale and trained-like weights; weight
@@ -362,8 +364,7 @@ class NGswin(nn.Module):
         p0 = next(self.parameters())
         if not p0.is_cuda:
             raise RuntimeError("calibrate_precision: move the module to a B200 first (there is no CPU path)")
-        g = torch.Generator().manual_seed(seed)
-        x = (torch.rand(1, 1, size, size, generator=g) * 2 - 1).to(p0.device)
+        x = _probe_slices(size, seed).to(p0.device)
         n = len(self._units()) + 1
         saved = [b._mode for b in self._units()] + [getattr(self, "_glue_mode", None)]
 
@@ -395,7 +396,7 @@ class NGswin(nn.Module):
         finally:
             self._set_plan(saved)
         self._auto_plan, self._auto_key, self._auto_age = plan, self._weights_key(), 0
-        self.precision_report = {"tol": tol, "probe": f"1x1x{size}x{size} uniform[-1,1), seed {seed}",
+        self.precision_report = {"tol": tol, "probe": f"2x1x{size}x{size} (uniform[-1,1) + structured phantom), seed {seed}",
                                  "err_all_tensor_core": err_all, "err_plan": err,
                                  "units_on_tensor_cores": sum(m == "tf32" for m in plan), "units": n,
                                  "plan": list(plan), "marginal_err": marginal}
@@ -543,6 +544,26 @@ class NGswin(nn.Module):
         H += (unit - H % unit) % unit
         W += (unit - W % unit) % unit
         return H * W * 548013
+
+
+def _probe_slices(size: int, seed: int) -> torch.Tensor:
+    """[2,1,size,size] calibration input in [-1,1]: slice 0 uniform noise, slice 1 a CT-like phantom (air
+    background, constant and softly shaded ellipses, a rectangle, a saturated "metal" disc with radial streaks,
+    weak noise).  Deterministic (CPU generator)."""
+    g = torch.Generator().manual_seed(seed)
+    noise = torch.rand(1, size, size, generator=g) * 2 - 1
+    yy, xx = torch.meshgrid(torch.linspace(-1, 1, size), torch.linspace(-1, 1, size), indexing="ij")
+    img = torch.full((size, size), -1.0)
+    for cx, cy, ax, ay, val, shade in ((-0.1, 0.0, 0.75, 0.6, -0.2, 0.15), (0.25, -0.2, 0.3, 0.22, 0.35, 0.0),
+                                       (-0.35, 0.25, 0.18, 0.3, 0.05, 0.1), (0.1, 0.4, 0.12, 0.1, 0.6, 0.0)):
+        d = ((xx - cx) / ax) ** 2 + ((yy - cy) / ay) ** 2
+        img = torch.where(d < 1.0, val + shade * (1 - d), img)
+    img[(xx.abs() < 0.5) & ((yy + 0.62).abs() < 0.05)] = 0.2
+    r = ((xx - 0.3) ** 2 + (yy - 0.15) ** 2).sqrt()
+    img = img + 0.3 * torch.cos(9 * torch.atan2(yy - 0.15, xx - 0.3) + 0.7) * torch.exp(-1.5 * r)
+    img = (img + 0.03 * torch.randn(size, size, generator=g)).clamp(-1, 1)
+    img[r < 7.0 / size] = 1.0
+    return torch.stack([noise, img[None]], 0)
 
 
 def _token_maxpool(x, ph, pw):
