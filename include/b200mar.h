@@ -76,6 +76,23 @@ int b200mar_ngram_ctx_pre_fwd(const float* nq, const float* proj_w, const float*
                               const float* logit_scale, const float* bias_table,
                               const float* merge_w, const float* merge_b, float* ctx,
                               int B, int wh, int ww, int nh, void* stream);
+/* NO-ALLOCATION variant of the inference pair above (b200mar_unigram_qkv_fwd + b200mar_ngram_ctx_pre_fwd in one
+ * call).  It has NO COUNTERPART IN THE REFERENCE and was added for callers
+ * that cannot call cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that forbid it): the nq scratch
+ * between the two kernels lives in a file-scope `static __device__` array of the library (6 MiB per GPU, held
+ * until the process exits) instead of a caller-allocated buffer; the call performs no cudaMalloc / cudaFree and
+ * calls no allocating routine.  Limit: B*(ph/8)*(pw/8) <= b200mar_ngram_ctx_infer_noalloc_max_windows() = 16384
+ * windows (one 1024x1024 slice, or six 416x416 slices, at stage 1); larger calls return -5 with a message in
+ * b200mar_last_error().  All calls share the array, which keeps the last call's contents (nothing needs to start
+ * at zero: every element read is written first); calls that OVERLAP on the GPU (different streams) race on it -
+ * serialise them.  ctx [B, ph/8, pw/8, 64] is bit-identical to the two-call form.                              */
+int b200mar_ngram_ctx_infer_noalloc(const float* z, const float* uni_w, const float* uni_b,
+                                    const float* qkv_w, const float* qkv_b,
+                                    const float* proj_w, const float* proj_b,
+                                    const float* logit_scale, const float* bias_table,
+                                    const float* merge_w, const float* merge_b, float* ctx,
+                                    int B, int ph, int pw, int nh, void* stream);
+int b200mar_ngram_ctx_infer_noalloc_max_windows(void);
 int b200mar_ngram_ctx_bwd(const float* u, const float* dctx,
                           const float* qkv_w, const float* qkv_b,
                           const float* proj_w, const float* proj_b,

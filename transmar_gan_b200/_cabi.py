@@ -37,6 +37,8 @@ SIGNATURES = {
     "b200mar_ngram_ctx_fwd": [_P] * 10 + [_I] * 4 + [_P],
     "b200mar_unigram_qkv_fwd": [_P] * 6 + [_I] * 4 + [_P],
     "b200mar_ngram_ctx_pre_fwd": [_P] * 8 + [_I] * 4 + [_P],
+    "b200mar_ngram_ctx_infer_noalloc": [_P] * 12 + [_I] * 4 + [_P],
+    "b200mar_ngram_ctx_infer_noalloc_max_windows": [],
     "b200mar_ngram_ctx_bwd": [_P] * 19 + [_I] * 4 + [_P],
     "b200mar_attn_fwd": [_P] * 11 + [_I] * 5 + [_P],
     "b200mar_attn_tc_fwd": [_P] * 11 + [_I] * 6 + [_P],

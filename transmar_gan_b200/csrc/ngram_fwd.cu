@@ -345,3 +345,64 @@ extern "C" int b200mar_ngram_ctx_pre_fwd(const float* nq, const float* proj_w, c
   if (nh == 4) return launch_ngram_ctx_fwd<4, true>(p, (cudaStream_t)stream);
   return -1;
 }
+
+// ------------------------------------------------------------------------------- no-allocation variant
+// b200mar_ngram_ctx_infer_noalloc = b200mar_unigram_qkv_fwd + b200mar_ngram_ctx_pre_fwd with the scratch between
+// the two kernels (nq, [windows][96] fp32) held in a file-scope device array instead of a caller-allocated
+// buffer, for callers that cannot allocate (CUDA-graph capture, tight serving loops).  No counterpart in the
+// reference.
+//   * limit: kNoAllocMaxWindows windows per call (6 MiB; one 1024x1024 slice or six 416x416 slices at stage 1);
+//     every GPU that loads the library holds the array until the process exits;
+//   * the array is shared by every call and keeps the last call's contents.  Nothing has to start at zero: the
+//     first kernel writes all 96 columns of every window row the second kernel reads.  Calls that overlap on
+//     the GPU (different streams) RACE on it - serialise them;
+//   * host code sees `g_nq_scratch` only as a stand-in symbol: its device address is looked up once per device,
+//     with that device current, through cudaGetSymbolAddress.
+namespace b200mar {
+constexpr int kNoAllocMaxWindows = 16384;
+static __device__ __align__(256) float g_nq_scratch[(size_t)kNoAllocMaxWindows * 96];
+
+static int nq_scratch_ptr(float** out) {
+  static float* cache[64] = {nullptr};
+  int dev = -1;
+  B200MAR_CHECK(cudaGetDevice(&dev));
+  if (dev >= 0 && dev < 64 && cache[dev]) { *out = cache[dev]; return 0; }
+  float* ptr = nullptr;
+  B200MAR_CHECK(cudaGetSymbolAddress((void**)&ptr, g_nq_scratch));
+  if (!ptr) { last_error_ref() = "cudaGetSymbolAddress(g_nq_scratch) returned null"; return -4; }
+  if (dev >= 0 && dev < 64) cache[dev] = ptr;
+  *out = ptr;
+  return 0;
+}
+}  // namespace b200mar
+
+extern "C" int b200mar_ngram_ctx_infer_noalloc_max_windows(void) { return b200mar::kNoAllocMaxWindows; }
+
+extern "C" int b200mar_ngram_ctx_infer_noalloc(const float* z, const float* uni_w, const float* uni_b,
+                                               const float* qkv_w, const float* qkv_b,
+                                               const float* proj_w, const float* proj_b,
+                                               const float* logit_scale, const float* bias_table,
+                                               const float* merge_w, const float* merge_b, float* ctx,
+                                               int B, int ph, int pw, int nh, void* stream) {
+  using namespace b200mar;
+  if (B <= 0 || ph % kWin || pw % kWin || ph < 2 * kWin || pw < 2 * kWin || (nh != 6 && nh != 4)) return -1;
+  const long long nwin = (long long)B * (ph / kWin) * (pw / kWin);
+  if (nwin > kNoAllocMaxWindows) {
+    last_error_ref() = "b200mar_ngram_ctx_infer_noalloc: B*(ph/8)*(pw/8) exceeds the 16384-window static scratch "
+                       "(use b200mar_unigram_qkv_fwd + b200mar_ngram_ctx_pre_fwd with a caller-owned buffer)";
+    return -5;
+  }
+  float* nq = nullptr;
+  if (int rc = nq_scratch_ptr(&nq)) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  int grid = ((int)nwin + 7) / 8;
+  if (grid > 8 * sm_count()) grid = 8 * sm_count();
+  unigram_qkv_fwd_kernel<<<grid, kThreads, 0, st>>>(z, uni_w, uni_b, qkv_w, qkv_b, 3 * (32 / nh) * nh, nq, B, ph, pw);
+  B200MAR_CHECK(cudaGetLastError());
+  NgramParams p{};
+  p.u = nq; p.proj_w = proj_w; p.proj_b = proj_b;
+  p.logit_scale = logit_scale; p.bias_table = bias_table; p.merge_w = merge_w; p.merge_b = merge_b;
+  p.ctx = ctx; p.B = B; p.wh = ph / kWin; p.ww = pw / kWin;
+  if (nh == 6) return launch_ngram_ctx_fwd<6, true>(p, st);
+  return launch_ngram_ctx_fwd<4, true>(p, st);
+}
