@@ -193,6 +193,31 @@ int b200mar_mlp_tma_fwd(const float* a, float* z_inout,
                         const float* fc2_w, const float* fc2_b,
                         const float* ln_w, const float* ln_b,
                         float* out, long long n_tok, void* stream);
+/* ---- precision mode "bf16" (BASELINE.json configs[1]: "bf16 on 1xB200"): the NSTB residual
+ * stream inside a stage is BF16 in HBM, which halves every pass of the three per-block kernels.  Arithmetic is
+ * unchanged (fp32 q/k normalisation, softmax, LayerNorm, residual adds; FP16 / TF32 tensor-core operands): rows are
+ * widened to fp32 on read and rounded to bf16 once, on write; z16 += out is a bf16 TMA reduce-add.  Same reference
+ * contracts as their fp32-stream siblings: components/window_utils.py:75-90 (unigram + n-gram qkv),
+ * components/attention.py:70-101 + transformer_blocks.py:83-117 (attention + LN1 + residual),
+ * transformer_blocks.py:119 + encoder_decoder.py:138-141 (MLP + LN2 + residual + within-stage sum).
+ * z16 / a16 / out16: bf16 [B*ph*pw, 64]; ctx, nq and every parameter: fp32.                                      */
+/* stage entry / exit of the mode: dst = bf16(src) (to_bf16 = 1) or dst = fp32(src) (to_bf16 = 0); n elements,
+ * n % 8 == 0 (the reference has no counterpart: its stream is fp32 throughout).                                  */
+int b200mar_cast_stream(const void* src, void* dst, long long n, int to_bf16, void* stream);
+int b200mar_unigram_qkv_fwd_s16(const void* z16, const float* weight, const float* bias,
+                                const float* qkv_w, const float* qkv_b, float* nq,
+                                int B, int ph, int pw, int nh, void* stream);
+int b200mar_attn_tc_fwd_s16(const void* z16, const float* ctx,
+                            const float* qkv_w, const float* qkv_b,
+                            const float* proj_w, const float* proj_b,
+                            const float* logit_scale, const float* bias_table,
+                            const float* ln_w, const float* ln_b,
+                            void* a16, int B, int ph, int pw, int nh, int shift, void* stream);
+int b200mar_mlp_tma_fwd_s16(const void* a16, void* z16_inout,
+                            const float* fc1_w, const float* fc1_b,
+                            const float* fc2_w, const float* fc2_b,
+                            const float* ln_w, const float* ln_b,
+                            void* out16, long long n_tok, void* stream);
 /* 1 if a tensor-core kernel of this process ever timed out on an mbarrier (every wait is
  * bounded so a descriptor bug cannot hang the device); 0 otherwise; -1 on a CUDA error.     */
 int b200mar_tc_error(void);

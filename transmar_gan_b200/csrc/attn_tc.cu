@@ -121,7 +121,10 @@ constexpr uint32_t kTQ = 0;
 // RESID = true : a = z + LN1(attn)            (the op's standalone contract)
 // RESID = false: a = LN1(attn) only; the consumer (mlp_tc with a_is_delta) adds z, which it reads
 //                anyway, so this kernel never re-reads z for the residual.
-template <int NH, bool RESID, bool SAVEO>
+// S16 = true : the residual stream (z in, a out) is BF16 in HBM (precision mode "bf16", BASELINE.json configs[1]):
+//               one 8 KB TMA box per window (64 tokens x 64 channels x 2 B = 128 B rows, 128 B swizzle), rows are
+//               widened to fp32 on read; the residual add runs in fp32 and a is rounded to bf16 once, on write.
+template <int NH, bool RESID, bool SAVEO, bool S16 = false>
 __global__ void __launch_bounds__(128 * Cfg<NH>::kWorkers, 1)
 attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_constant__ CUtensorMap mapA,
                    AttnParams p) {
@@ -268,25 +271,34 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
     return x0 + kWin <= g.pw && y0 + kWin <= g.ph;
   };
   // z tile of `tile_`: window w -> [2 channel halves][64 slots][128 B swizzled] at sW + w * 16 KB
+  // (S16: one box of [64 slots][128 B = 64 bf16] at sW + w * 8 KB)
+  constexpr int kWinBytes = S16 ? 8192 : 16384;
   auto issue_z_loads = [&](int tile_) {
     int x0[2], y0[2], b[2];
     const bool t0 = tma_window(tile_ * 2, x0[0], y0[0], b[0]);
     const bool t1 = tma_window(tile_ * 2 + 1, x0[1], y0[1], b[1]);
     if (!(t0 || t1)) return;
-    tma::mbar_expect_tx(barZ, ((int)t0 + (int)t1) * 16384);
+    tma::mbar_expect_tx(barZ, ((int)t0 + (int)t1) * kWinBytes);
 #pragma unroll
     for (int w = 0; w < 2; ++w)
       if (w == 0 ? t0 : t1) {
-        tma::load_4d(&mapZ, barZ, sW + w * 16384, 0, x0[w], y0[w], b[w]);
-        tma::load_4d(&mapZ, barZ, sW + w * 16384 + 8192, 32, x0[w], y0[w], b[w]);
+        tma::load_4d(&mapZ, barZ, sW + w * kWinBytes, 0, x0[w], y0[w], b[w]);
+        if constexpr (!S16) tma::load_4d(&mapZ, barZ, sW + w * kWinBytes + 8192, 32, x0[w], y0[w], b[w]);
       }
   };
   const bool leader = wq == 0 && lane == 0;       // bulk groups are per thread: one fixed thread
   const int tile_stride = gridDim.x * kWorkers;
   // byte offset of 16-byte chunk i of this thread's row inside the swizzled z tile
-  const uint32_t zrow_off = (uint32_t)(wsel * 16384 + ltok * 128);
-  auto zoff = [&](int i) -> uint32_t {
+  const uint32_t zrow_off = (uint32_t)(wsel * kWinBytes + ltok * 128);
+  auto zoff = [&](int i) -> uint32_t {      // fp32: i = 0..15 (4 floats each); S16: i = 0..7 (8 bf16 each)
     return zrow_off + (uint32_t)((i >> 3) * 8192 + (((i & 7) ^ (ltok & 7)) << 4));
+  };
+  // 8 bf16 (one 16-byte chunk) <-> 8 floats
+  auto widen8 = [](const uint4& v, float* f) {
+    f[0] = __uint_as_float(v.x << 16); f[1] = __uint_as_float(v.x & 0xFFFF0000u);
+    f[2] = __uint_as_float(v.y << 16); f[3] = __uint_as_float(v.y & 0xFFFF0000u);
+    f[4] = __uint_as_float(v.z << 16); f[5] = __uint_as_float(v.z & 0xFFFF0000u);
+    f[6] = __uint_as_float(v.w << 16); f[7] = __uint_as_float(v.w & 0xFFFF0000u);
   };
   // S_h = Hot Bias_h^T + Q' K'^T (issued by one thread).  The bias part does not depend on the tile: it
   // is issued as soon as the S / P columns are free (tile start; PV_{h-1} complete), off the critical path.
@@ -306,7 +318,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
     for (int w = 0; w < 2; ++w)
       if (tma_window(tile_ * 2 + w, x0, y0, b)) {
         tma::prefetch_4d(&mapZ, 0, x0, y0, b);
-        tma::prefetch_4d(&mapZ, 32, x0, y0, b);
+        if constexpr (!S16) tma::prefetch_4d(&mapZ, 32, x0, y0, b);
       }
   };
   if (leader && (int)(blockIdx.x * kWorkers + wk) < ntile) issue_z_loads(blockIdx.x * kWorkers + wk);
@@ -349,7 +361,19 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
       }
       if (any_tma) { tc::mbar_wait(barZ, phZ, &g_tc_error); phZ ^= 1; }
       PROF(1);                                       // ctx + wait for the z tile
-      if (use_tma) {
+      if constexpr (S16) {
+        if (use_tma || wvalid) {
+          const uint4* zp = reinterpret_cast<const uint4*>(reinterpret_cast<const unsigned short*>(p.z) + (size_t)tok * 64);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const uint4 v = use_tma ? *reinterpret_cast<const uint4*>(sW + zoff(i)) : __ldg(zp + i);
+            float f[8];
+            widen8(v, f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) x[8 * i + j] += f[j];
+          }
+        }
+      } else if (use_tma) {
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
           const float4 v = *reinterpret_cast<const float4*>(sW + zoff(i));
@@ -609,7 +633,23 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
       PROF(13);                                        // LN epilogue
       if (RESID && any_tma) { tc::mbar_wait(barZ, phZ, &g_tc_error); phZ ^= 1; }
       PROF(14);
-      if (use_tma) {
+      if constexpr (S16) {
+        if (use_tma || wvalid) {
+          const uint4* zp = reinterpret_cast<const uint4*>(reinterpret_cast<const unsigned short*>(p.z) + (size_t)tok * 64);
+          uint4* ap = reinterpret_cast<uint4*>(reinterpret_cast<unsigned short*>(p.a) + (size_t)tok * 64);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            uint4* q = reinterpret_cast<uint4*>(sW + zoff(i));
+            float f[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            if (RESID) widen8(use_tma ? *q : __ldg(zp + i), f);
+            const uint4 r = make_uint4(tc::pack_bf16(f[0] + y[8 * i], f[1] + y[8 * i + 1]),
+                                       tc::pack_bf16(f[2] + y[8 * i + 2], f[3] + y[8 * i + 3]),
+                                       tc::pack_bf16(f[4] + y[8 * i + 4], f[5] + y[8 * i + 5]),
+                                       tc::pack_bf16(f[6] + y[8 * i + 6], f[7] + y[8 * i + 7]));
+            if (use_tma) *q = r; else ap[i] = r;
+          }
+        }
+      } else if (use_tma) {
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
           float4* q = reinterpret_cast<float4*>(sW + zoff(i));
@@ -638,8 +678,8 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
       for (int w = 0; w < 2; ++w) {
         int x0, y0, b;
         if (tma_window(tile * 2 + w, x0, y0, b)) {
-          tma::store_4d(&mapA, sW + w * 16384, 0, x0, y0, b);
-          tma::store_4d(&mapA, sW + w * 16384 + 8192, 32, x0, y0, b);
+          tma::store_4d(&mapA, sW + w * kWinBytes, 0, x0, y0, b);
+          if constexpr (!S16) tma::store_4d(&mapA, sW + w * kWinBytes + 8192, 32, x0, y0, b);
         }
         tma::commit_group();                           // (an empty group completes immediately)
       }
@@ -648,16 +688,16 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
         int x0[2], y0[2], b[2];
         const bool t0 = tma_window(nt * 2, x0[0], y0[0], b[0]);
         const bool t1 = tma_window(nt * 2 + 1, x0[1], y0[1], b[1]);
-        if (t0 || t1) tma::mbar_expect_tx(barZ, ((int)t0 + (int)t1) * 16384);
+        if (t0 || t1) tma::mbar_expect_tx(barZ, ((int)t0 + (int)t1) * kWinBytes);
         tma::wait_read_1();                            // window-0 half drained
         if (t0) {
           tma::load_4d(&mapZ, barZ, sW, 0, x0[0], y0[0], b[0]);
-          tma::load_4d(&mapZ, barZ, sW + 8192, 32, x0[0], y0[0], b[0]);
+          if constexpr (!S16) tma::load_4d(&mapZ, barZ, sW + 8192, 32, x0[0], y0[0], b[0]);
         }
         tma::wait_read_all();
         if (t1) {
-          tma::load_4d(&mapZ, barZ, sW + 16384, 0, x0[1], y0[1], b[1]);
-          tma::load_4d(&mapZ, barZ, sW + 16384 + 8192, 32, x0[1], y0[1], b[1]);
+          tma::load_4d(&mapZ, barZ, sW + kWinBytes, 0, x0[1], y0[1], b[1]);
+          if constexpr (!S16) tma::load_4d(&mapZ, barZ, sW + kWinBytes + 8192, 32, x0[1], y0[1], b[1]);
         }
       }
     }
@@ -681,13 +721,13 @@ extern "C" int b200mar_attn_prof(unsigned long long* out32, int reset) {
 namespace b200mar {
 #endif
 
-template <int NH, bool RESID, bool SAVEO = false>
+template <int NH, bool RESID, bool SAVEO = false, bool S16 = false>
 static int launch_attn_tc_fwd(const AttnParams& p, cudaStream_t st) {
   constexpr int kWorkers = Cfg<NH>::kWorkers;
   const size_t smem = AttnTcSmem<kWorkers>::kBytes;
   static DeviceOnce configured;
   if (configured.first()) {
-    B200MAR_CHECK(cudaFuncSetAttribute(attn_tc_fwd_kernel<NH, RESID, SAVEO>,
+    B200MAR_CHECK(cudaFuncSetAttribute(attn_tc_fwd_kernel<NH, RESID, SAVEO, S16>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured.done();
   }
@@ -696,9 +736,14 @@ static int launch_attn_tc_fwd(const AttnParams& p, cudaStream_t st) {
   int grid = (ntile + kWorkers - 1) / kWorkers;
   if (grid > sm_count()) grid = sm_count();
   CUtensorMap mZ, mA;
-  if (int rc = tma::encode_windows(&mZ, p.z, p.B, p.ph, p.pw)) return rc;
-  if (int rc = tma::encode_windows(&mA, p.a, p.B, p.ph, p.pw)) return rc;
-  attn_tc_fwd_kernel<NH, RESID, SAVEO><<<grid, 128 * kWorkers, smem, st>>>(mZ, mA, p);
+  if constexpr (S16) {
+    if (int rc = tma::encode_windows16(&mZ, p.z, p.B, p.ph, p.pw)) return rc;
+    if (int rc = tma::encode_windows16(&mA, p.a, p.B, p.ph, p.pw)) return rc;
+  } else {
+    if (int rc = tma::encode_windows(&mZ, p.z, p.B, p.ph, p.pw)) return rc;
+    if (int rc = tma::encode_windows(&mA, p.a, p.B, p.ph, p.pw)) return rc;
+  }
+  attn_tc_fwd_kernel<NH, RESID, SAVEO, S16><<<grid, 128 * kWorkers, smem, st>>>(mZ, mA, p);
   B200MAR_CHECK(cudaGetLastError());
   return 0;
 }
@@ -720,6 +765,26 @@ extern "C" int b200mar_attn_tc_fwd(const float* z, const float* ctx, const float
   cudaStream_t st = (cudaStream_t)stream;
   if (nh == 6) return residual ? launch_attn_tc_fwd<6, true>(p, st) : launch_attn_tc_fwd<6, false>(p, st);
   if (nh == 4) return residual ? launch_attn_tc_fwd<4, true>(p, st) : launch_attn_tc_fwd<4, false>(p, st);
+  return -1;
+}
+
+// Precision mode "bf16" (BASELINE.json configs[1]): the same kernel with the residual stream in BF16 - z16 in,
+// a16 = bf16(z + LN1(attn)) out, both [B, ph*pw, 64] bf16; ctx and the parameters stay fp32.
+extern "C" int b200mar_attn_tc_fwd_s16(const void* z16, const float* ctx, const float* qkv_w,
+                                       const float* qkv_b, const float* proj_w, const float* proj_b,
+                                       const float* logit_scale, const float* bias_table,
+                                       const float* ln_w, const float* ln_b, void* a16, int B, int ph,
+                                       int pw, int nh, int shift, void* stream) {
+  using namespace b200mar;
+  if (ph % kWin || pw % kWin || ph < kWin || pw < kWin || (shift != 0 && shift != kShift)) return -1;
+  if ((long long)B * ph * pw >= (1ll << 31)) return -1;
+  AttnParams p{};
+  p.z = (const float*)z16; p.ctx = ctx; p.qkv_w = qkv_w; p.qkv_b = qkv_b; p.proj_w = proj_w; p.proj_b = proj_b;
+  p.logit_scale = logit_scale; p.bias_table = bias_table; p.ln_w = ln_w; p.ln_b = ln_b;
+  p.a = (float*)a16; p.B = B; p.ph = ph; p.pw = pw; p.shift = shift;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (nh == 6) return launch_attn_tc_fwd<6, true, false, true>(p, st);
+  if (nh == 4) return launch_attn_tc_fwd<4, true, false, true>(p, st);
   return -1;
 }
 

@@ -112,3 +112,45 @@ extern "C" int b200mar_ln64_bwd(const float* x, const float* dy, const float* we
   B200MAR_CHECK(cudaGetLastError());
   return 0;
 }
+
+// ------------------------------------------------------------------------------- stream casts (precision mode "bf16")
+// fp32 <-> bf16 of a token-major stream tensor at stage entry / exit: 8 elements per thread (one 32-byte read or
+// write per thread on the fp32 side, 16 bytes on the bf16 side), grid-stride.  n must be a multiple of 8.
+namespace b200mar {
+__global__ void __launch_bounds__(256) cast_f32_bf16_kernel(const float4* __restrict__ src, uint4* __restrict__ dst,
+                                                            long long n8) {
+  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < n8; i += (long long)gridDim.x * 256) {
+    const float4 a = __ldg(src + 2 * i), b = __ldg(src + 2 * i + 1);
+    uint32_t r0, r1, r2, r3;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r0) : "f"(a.y), "f"(a.x));
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r1) : "f"(a.w), "f"(a.z));
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r2) : "f"(b.y), "f"(b.x));
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r3) : "f"(b.w), "f"(b.z));
+    dst[i] = make_uint4(r0, r1, r2, r3);
+  }
+}
+__global__ void __launch_bounds__(256) cast_bf16_f32_kernel(const uint4* __restrict__ src, float4* __restrict__ dst,
+                                                            long long n8) {
+  for (long long i = blockIdx.x * 256ll + threadIdx.x; i < n8; i += (long long)gridDim.x * 256) {
+    const uint4 v = __ldg(src + i);
+    dst[2 * i] = make_float4(__uint_as_float(v.x << 16), __uint_as_float(v.x & 0xFFFF0000u),
+                             __uint_as_float(v.y << 16), __uint_as_float(v.y & 0xFFFF0000u));
+    dst[2 * i + 1] = make_float4(__uint_as_float(v.z << 16), __uint_as_float(v.z & 0xFFFF0000u),
+                                 __uint_as_float(v.w << 16), __uint_as_float(v.w & 0xFFFF0000u));
+  }
+}
+}  // namespace b200mar
+
+extern "C" int b200mar_cast_stream(const void* src, void* dst, long long n, int to_bf16, void* stream) {
+  using namespace b200mar;
+  if (n <= 0 || n % 8) return -1;
+  const long long n8 = n / 8;
+  long long grid = (n8 + 255) / 256;
+  if (grid > 16ll * sm_count()) grid = 16ll * sm_count();
+  if (to_bf16)
+    cast_f32_bf16_kernel<<<(int)grid, 256, 0, (cudaStream_t)stream>>>((const float4*)src, (uint4*)dst, n8);
+  else
+    cast_bf16_f32_kernel<<<(int)grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)src, (float4*)dst, n8);
+  B200MAR_CHECK(cudaGetLastError());
+  return 0;
+}

@@ -379,6 +379,10 @@ struct MlpTmaSmem {                                  // BYTE offsets (weights as
   static_assert(kBytes <= 232448, "mlp_tma shared memory exceeds 227 KB");
 };
 
+// S16 = true (precision mode "bf16"): a, z and out are BF16 in HBM; a tile is ONE 16 KB box of [128 rows][64 bf16
+// = 128 B] (128 B swizzle); rows are widened to fp32 on read, out = a + LN2(.) is formed in fp32 and rounded to
+// bf16 once, and z += out is a bf16 bulk reduce-add.
+template <bool S16>
 __global__ void __launch_bounds__(128 * kTmaWorkers, 1)
 mlp_tma_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapZ,
                    const __grid_constant__ CUtensorMap mapOut, MlpParams p) {
@@ -426,10 +430,13 @@ mlp_tma_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
   const long long ntile = (p.n_tok + 127) / 128;
   const long long stride = (long long)gridDim.x * kTmaWorkers;
   long long tile = (long long)blockIdx.x * kTmaWorkers + wk;
+  constexpr uint32_t kTileBytes = S16 ? 16384 : 32768;
+  // byte offset of 16-byte chunk i of row r in a bf16 tile (8 chunks of 8 bf16 per 128 B row)
+  auto off16 = [](int r, int i) -> uint32_t { return (uint32_t)(r * 128 + ((i ^ (r & 7)) << 4)); };
   if (leader && tile < ntile) {
-    tma::mbar_expect_tx(full, 32768);
+    tma::mbar_expect_tx(full, kTileBytes);
     tma::load_2d(&mapA, full, sWk, 0, (int)(tile * 128));
-    tma::load_2d(&mapA, full, sWk + 16384, 32, (int)(tile * 128));
+    if constexpr (!S16) tma::load_2d(&mapA, full, sWk + 16384, 32, (int)(tile * 128));
   }
   PROF_DECL
   for (uint32_t it = 0; tile < ntile; tile += stride, ++it) {
@@ -442,10 +449,21 @@ mlp_tma_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
     float ainv, hhalf, hinv;
     {
       float x[64];
+      if constexpr (S16) {
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const float4 v = *reinterpret_cast<const float4*>(buf + tma::tile_off(row, i));
-        x[4 * i] = v.x; x[4 * i + 1] = v.y; x[4 * i + 2] = v.z; x[4 * i + 3] = v.w;
+        for (int i = 0; i < 8; ++i) {
+          const uint4 v = *reinterpret_cast<const uint4*>(buf + off16(row, i));
+          x[8 * i + 0] = __uint_as_float(v.x << 16); x[8 * i + 1] = __uint_as_float(v.x & 0xFFFF0000u);
+          x[8 * i + 2] = __uint_as_float(v.y << 16); x[8 * i + 3] = __uint_as_float(v.y & 0xFFFF0000u);
+          x[8 * i + 4] = __uint_as_float(v.z << 16); x[8 * i + 5] = __uint_as_float(v.z & 0xFFFF0000u);
+          x[8 * i + 6] = __uint_as_float(v.w << 16); x[8 * i + 7] = __uint_as_float(v.w & 0xFFFF0000u);
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const float4 v = *reinterpret_cast<const float4*>(buf + tma::tile_off(row, i));
+          x[4 * i] = v.x; x[4 * i + 1] = v.y; x[4 * i + 2] = v.z; x[4 * i + 3] = v.w;
+        }
       }
       float m0 = 0.f, m1 = 0.f, m2 = 0.f, m3 = 0.f;
 #pragma unroll
@@ -481,9 +499,9 @@ mlp_tma_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
       if (lane == 0 && tile + stride < ntile) {
         tma::wait_read_all();                         // the stores that drained the other buffer
         unsigned char* nb = sWk + (b ^ 1) * 32768;
-        tma::mbar_expect_tx(full + (b ^ 1), 32768);
+        tma::mbar_expect_tx(full + (b ^ 1), kTileBytes);
         tma::load_2d(&mapA, full + (b ^ 1), nb, 0, (int)((tile + stride) * 128));
-        tma::load_2d(&mapA, full + (b ^ 1), nb + 16384, 32, (int)((tile + stride) * 128));
+        if constexpr (!S16) tma::load_2d(&mapA, full + (b ^ 1), nb + 16384, 32, (int)((tile + stride) * 128));
       }
       __syncwarp();
     }
@@ -537,14 +555,32 @@ mlp_tma_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
       for (int i = 0; i < 64; ++i) { y[i] -= mean; var4[i & 3] = fmaf(y[i], y[i], var4[i & 3]); }
       const float var = (var4[0] + var4[1]) + (var4[2] + var4[3]);
       const float rstd = 1.0f / sqrtf(var * (1.0f / 64.f) + kLnEps);
+      if constexpr (S16) {
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        float4* q = reinterpret_cast<float4*>(buf + tma::tile_off(row, i));
-        const float4 av = *q;
-        *q = make_float4(av.x + (y[4 * i + 0] * rstd * sLnW[4 * i + 0] + sLnB[4 * i + 0]),
-                         av.y + (y[4 * i + 1] * rstd * sLnW[4 * i + 1] + sLnB[4 * i + 1]),
-                         av.z + (y[4 * i + 2] * rstd * sLnW[4 * i + 2] + sLnB[4 * i + 2]),
-                         av.w + (y[4 * i + 3] * rstd * sLnW[4 * i + 3] + sLnB[4 * i + 3]));
+        for (int i = 0; i < 8; ++i) {
+          uint4* q = reinterpret_cast<uint4*>(buf + off16(row, i));
+          const uint4 v = *q;
+          const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+          uint32_t r[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int c = 8 * i + 2 * j;
+            const float lo = __uint_as_float(w[j] << 16) + (y[c] * rstd * sLnW[c] + sLnB[c]);
+            const float hi = __uint_as_float(w[j] & 0xFFFF0000u) + (y[c + 1] * rstd * sLnW[c + 1] + sLnB[c + 1]);
+            r[j] = tc::pack_bf16(lo, hi);
+          }
+          *q = make_uint4(r[0], r[1], r[2], r[3]);
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          float4* q = reinterpret_cast<float4*>(buf + tma::tile_off(row, i));
+          const float4 av = *q;
+          *q = make_float4(av.x + (y[4 * i + 0] * rstd * sLnW[4 * i + 0] + sLnB[4 * i + 0]),
+                           av.y + (y[4 * i + 1] * rstd * sLnW[4 * i + 1] + sLnB[4 * i + 1]),
+                           av.z + (y[4 * i + 2] * rstd * sLnW[4 * i + 2] + sLnB[4 * i + 2]),
+                           av.w + (y[4 * i + 3] * rstd * sLnW[4 * i + 3] + sLnB[4 * i + 3]));
+        }
       }
     }
     PROF(7);
@@ -553,8 +589,8 @@ mlp_tma_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
     tc::worker_sync(1 + wk);
     if (leader) {
       const int r0 = (int)(tile * 128);
-      if (p.out) { tma::store_2d(&mapOut, buf, 0, r0); tma::store_2d(&mapOut, buf + 16384, 32, r0); }
-      if (p.zsum) { tma::reduce_add_2d(&mapZ, buf, 0, r0); tma::reduce_add_2d(&mapZ, buf + 16384, 32, r0); }
+      if (p.out) { tma::store_2d(&mapOut, buf, 0, r0); if constexpr (!S16) tma::store_2d(&mapOut, buf + 16384, 32, r0); }
+      if (p.zsum) { tma::reduce_add_2d(&mapZ, buf, 0, r0); if constexpr (!S16) tma::reduce_add_2d(&mapZ, buf + 16384, 32, r0); }
       tma::commit_group();
     }
     PROF(8);
@@ -612,14 +648,44 @@ extern "C" int b200mar_mlp_tma_fwd(const float* a, float* z_inout, const float* 
   const size_t smem = MlpTmaSmem::kBytes;
   static DeviceOnce configured;
   if (configured.first()) {
-    B200MAR_CHECK(cudaFuncSetAttribute(mlp_tma_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    B200MAR_CHECK(cudaFuncSetAttribute(mlp_tma_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)smem));
     configured.done();
   }
   const long long ntile = (n_tok + 127) / 128;
   long long grid = (ntile + kTmaWorkers - 1) / kTmaWorkers;
   if (grid > sm_count()) grid = sm_count();
-  mlp_tma_fwd_kernel<<<(int)grid, 128 * kTmaWorkers, smem, (cudaStream_t)stream>>>(mA, mZ, mO, p);
+  mlp_tma_fwd_kernel<false><<<(int)grid, 128 * kTmaWorkers, smem, (cudaStream_t)stream>>>(mA, mZ, mO, p);
+  B200MAR_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// Precision mode "bf16": a16, z16 (in/out), out16 are BF16 [n_tok][64]; parameters fp32.
+extern "C" int b200mar_mlp_tma_fwd_s16(const void* a16, void* z16_inout, const float* fc1_w,
+                                       const float* fc1_b, const float* fc2_w, const float* fc2_b,
+                                       const float* ln_w, const float* ln_b, void* out16,
+                                       long long n_tok, void* stream) {
+  using namespace b200mar;
+  if (n_tok <= 0 || n_tok % kTok || n_tok * 1 > 0x7fffffffLL) return -1;
+  if (!out16 && !z16_inout) return -1;
+  MlpParams p{};
+  p.a = (const float*)a16; p.z = (const float*)z16_inout; p.fc1_w = fc1_w; p.fc1_b = fc1_b; p.fc2_w = fc2_w;
+  p.fc2_b = fc2_b; p.ln_w = ln_w; p.ln_b = ln_b; p.out = (float*)out16; p.zsum = (float*)z16_inout; p.n_tok = n_tok;
+  CUtensorMap mA, mZ, mO;
+  if (int rc = tma::encode_rows64_16(&mA, a16, n_tok)) return rc;
+  if (int rc = tma::encode_rows64_16(&mZ, z16_inout ? z16_inout : a16, n_tok)) return rc;
+  if (int rc = tma::encode_rows64_16(&mO, out16 ? out16 : a16, n_tok)) return rc;
+  const size_t smem = MlpTmaSmem::kBytes;
+  static DeviceOnce configured;
+  if (configured.first()) {
+    B200MAR_CHECK(cudaFuncSetAttribute(mlp_tma_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)smem));
+    configured.done();
+  }
+  const long long ntile = (n_tok + 127) / 128;
+  long long grid = (ntile + kTmaWorkers - 1) / kTmaWorkers;
+  if (grid > sm_count()) grid = sm_count();
+  mlp_tma_fwd_kernel<true><<<(int)grid, 128 * kTmaWorkers, smem, (cudaStream_t)stream>>>(mA, mZ, mO, p);
   B200MAR_CHECK(cudaGetLastError());
   return 0;
 }

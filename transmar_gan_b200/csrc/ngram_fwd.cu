@@ -47,6 +47,7 @@ __global__ void __launch_bounds__(kThreads) unigram_fwd_kernel(
 // Inference form: the same streaming pass also applies the n-gram attention's qkv Linear(32 -> 3*NA)
 // to the window's unigram embedding, once per window (ngram_ctx_fwd re-derives it for each of the
 // up to 8 neighbourhoods a window belongs to).  nq: [B*wh*ww][96] (rows >= 3*NA are zero).
+template <bool S16>
 __global__ void __launch_bounds__(kThreads) unigram_qkv_fwd_kernel(
     const float* __restrict__ z, const float* __restrict__ w, const float* __restrict__ bias,
     const float* __restrict__ qkv_w, const float* __restrict__ qkv_b, int n_qkv,
@@ -72,14 +73,22 @@ __global__ void __launch_bounds__(kThreads) unigram_qkv_fwd_kernel(
   for (int g = 0; g < 3; ++g) bq[g] = lane + 32 * g < n_qkv ? qkv_b[lane + 32 * g] : 0.f;
   for (int win = blockIdx.x * 8 + warp; win < nwin; win += gridDim.x * 8) {
     const int w0 = win % ww, h0 = (win / ww) % wh, b = win / (ww * wh);
-    const float* base = z + (((size_t)b * ph + h0 * kWin) * pw + w0 * kWin) * kDim + 2 * lane;
+    const size_t e0 = (((size_t)b * ph + h0 * kWin) * pw + w0 * kWin) * kDim + 2 * lane;   // element offset
+    const float* base = z + e0;
+    const unsigned short* base16 = reinterpret_cast<const unsigned short*>(z) + e0;        // S16: z is bf16
     float acc = 0.f;
 #pragma unroll 1
     for (int i = 0; i < kWin; ++i) {
       float2 v[kWin];
 #pragma unroll
-      for (int j = 0; j < kWin; ++j)
-        v[j] = *reinterpret_cast<const float2*>(base + ((size_t)i * pw + j) * kDim);
+      for (int j = 0; j < kWin; ++j) {
+        if constexpr (S16) {
+          const uint32_t u2 = *reinterpret_cast<const uint32_t*>(base16 + ((size_t)i * pw + j) * kDim);
+          v[j] = make_float2(__uint_as_float(u2 << 16), __uint_as_float(u2 & 0xFFFF0000u));
+        } else {
+          v[j] = *reinterpret_cast<const float2*>(base + ((size_t)i * pw + j) * kDim);
+        }
+      }
 #pragma unroll
       for (int j = 0; j < kWin; ++j) {
         const float2 wv = *reinterpret_cast<const float2*>(sW + (i * kWin + j) * kDim + 2 * lane);
@@ -325,8 +334,23 @@ extern "C" int b200mar_unigram_qkv_fwd(const float* z, const float* weight, cons
   const int nwin = B * (ph / kWin) * (pw / kWin);
   int grid = (nwin + 7) / 8;
   if (grid > 8 * sm_count()) grid = 8 * sm_count();
-  unigram_qkv_fwd_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(
+  unigram_qkv_fwd_kernel<false><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
       z, weight, bias, qkv_w, qkv_b, 3 * (32 / nh) * nh, nq, B, ph, pw);
+  B200MAR_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// Precision mode "bf16": the same pass over a BF16 stream z16 [B, ph*pw, 64]; nq stays fp32.
+extern "C" int b200mar_unigram_qkv_fwd_s16(const void* z16, const float* weight, const float* bias,
+                                           const float* qkv_w, const float* qkv_b, float* nq, int B,
+                                           int ph, int pw, int nh, void* stream) {
+  using namespace b200mar;
+  if (ph % kWin || pw % kWin || ph < kWin || pw < kWin || (nh != 6 && nh != 4)) return -1;
+  const int nwin = B * (ph / kWin) * (pw / kWin);
+  int grid = (nwin + 7) / 8;
+  if (grid > 8 * sm_count()) grid = 8 * sm_count();
+  unigram_qkv_fwd_kernel<true><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
+      (const float*)z16, weight, bias, qkv_w, qkv_b, 3 * (32 / nh) * nh, nq, B, ph, pw);
   B200MAR_CHECK(cudaGetLastError());
   return 0;
 }
@@ -397,7 +421,7 @@ extern "C" int b200mar_ngram_ctx_infer_noalloc(const float* z, const float* uni_
   cudaStream_t st = (cudaStream_t)stream;
   int grid = ((int)nwin + 7) / 8;
   if (grid > 8 * sm_count()) grid = 8 * sm_count();
-  unigram_qkv_fwd_kernel<<<grid, kThreads, 0, st>>>(z, uni_w, uni_b, qkv_w, qkv_b, 3 * (32 / nh) * nh, nq, B, ph, pw);
+  unigram_qkv_fwd_kernel<false><<<grid, kThreads, 0, st>>>(z, uni_w, uni_b, qkv_w, qkv_b, 3 * (32 / nh) * nh, nq, B, ph, pw);
   B200MAR_CHECK(cudaGetLastError());
   NgramParams p{};
   p.u = nq; p.proj_w = proj_w; p.proj_b = proj_b;

@@ -145,6 +145,35 @@ inline int encode_windows(CUtensorMap* out, const float* base, int B, int ph, in
   return r == CUDA_SUCCESS ? 0 : -3;
 }
 
+// ---- host: the same over a BF16 token grid [B][ph][pw][64] (precision mode "bf16"): one box = ALL 64 channels of
+// one 8x8 window: [1][8 rows][8 tokens][64 bf16 = 128 B] -> 64 smem rows of 128 B, 128 B swizzle.
+inline int encode_windows16(CUtensorMap* out, const void* base, int B, int ph, int pw) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) return -2;
+  const cuuint64_t gdim[4] = {64, (cuuint64_t)pw, (cuuint64_t)ph, (cuuint64_t)B};
+  const cuuint64_t gstride[3] = {128, (cuuint64_t)pw * 128, (cuuint64_t)ph * pw * 128};
+  const cuuint32_t box[4] = {64, 8, 8, 1};
+  const cuuint32_t estr[4] = {1, 1, 1, 1};
+  const CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), gdim, gstride,
+                        box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -3;
+}
+
+// ---- host: a token-major BF16 matrix [n_rows][64]: box [128 rows][64 bf16 = 128 B], 128 B swizzle (16 KB)
+inline int encode_rows64_16(CUtensorMap* out, const void* base, long long n_rows) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) return -2;
+  const cuuint64_t gdim[2] = {64, (cuuint64_t)n_rows};
+  const cuuint64_t gstride[1] = {128};
+  const cuuint32_t box[2] = {64, 128};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride,
+                        box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -3;
+}
+
 // ---- host: general form over a token grid [B][H][W][64] fp32: box = [1][by rows][bx tokens][32 floats]
 // taking every `step`-th token in x and y (step = 2: one parity class of the 2x2 PatchMerging
 // neighbourhood), 128 B swizzle.  The box lands as by*bx rows of 128 B, row = y*bx + x.

@@ -145,7 +145,7 @@ class PatchMerging(nn.Module):
 
     def forward(self, x, num_patches):
         ph, pw = num_patches
-        if not torch.is_grad_enabled() and ops.effective_precision() == "tf32":
+        if not torch.is_grad_enabled() and ops._tc():
             y = ops.patch_merge_tc_fwd(x, self.norm.weight.detach(), self.norm.bias.detach(),
                                        self.reduction.weight.detach(), ph, pw)
             return y, (ph // 2, pw // 2)
@@ -174,17 +174,34 @@ class _Stage(nn.Module):
             last = i == n - 1
             want_zsum = (not last) or need_sum_last
             with ops.precision_scope(blk._mode):
-                if not torch.is_grad_enabled() and ops.effective_precision() == "tf32":
-                    # the block adds its output into z (TMA reduce-add), so z must be private to this
-                    # loop: the stage input is copied once, later blocks own the previous block's sum
-                    if want_zsum and not private:
+                eff = ops.effective_precision()
+                if not torch.is_grad_enabled() and eff == "bf16":
+                    # precision mode "bf16": the stream lives in BF16 inside the stage (cast once at stage entry,
+                    # which also makes it private; cast back once at stage exit)
+                    if z.dtype != torch.bfloat16:
+                        z, private = ops.cast_stream(z.contiguous(), torch.bfloat16), True
+                    elif want_zsum and not private:
                         z = z.clone()
-                    out, zsum = ops.nstb_infer_(z, *num_patches, blk.num_heads, blk.shift_size, last,
-                                                want_zsum, blk.kernel_params())
+                    out, zsum = ops.nstb_infer_s16_(z, *num_patches, blk.num_heads, blk.shift_size, last,
+                                                    want_zsum, blk.kernel_params())
                 else:
-                    out, zsum = blk(z, num_patches, want_out=last, want_zsum=want_zsum)
+                    if z.dtype != torch.float32:
+                        z, private = ops.cast_stream(z, torch.float32), True
+                    if not torch.is_grad_enabled() and eff == "tf32":
+                        # the block adds its output into z (TMA reduce-add), so z must be private to this
+                        # loop: the stage input is copied once, later blocks own the previous block's sum
+                        if want_zsum and not private:
+                            z = z.clone()
+                        out, zsum = ops.nstb_infer_(z, *num_patches, blk.num_heads, blk.shift_size, last,
+                                                    want_zsum, blk.kernel_params())
+                    else:
+                        out, zsum = blk(z, num_patches, want_out=last, want_zsum=want_zsum)
             private = True               # zsum is this loop's own tensor (fresh, or the private z updated)
             z = zsum
+        if out is not None and out.dtype != torch.float32:
+            out = ops.cast_stream(out, torch.float32)
+        if zsum is not None and zsum.dtype != torch.float32:
+            zsum = ops.cast_stream(zsum, torch.float32) if need_sum_last else zsum.new_empty(0, dtype=torch.float32)
         return out, zsum
 
 
