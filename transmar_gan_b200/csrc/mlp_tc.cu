@@ -241,6 +241,7 @@ __global__ void __launch_bounds__(128 * kMlpWorkers, 1) mlp_tc_fwd_kernel(MlpPar
     tc::tc_fence_after();
     PROF(3);                                          // fc1 issue + wait
     // ---- GELU epilogue, two halves of 64 hidden columns; packed fp16 hidden -> TMEM [0,64)
+    const float hfull = hhalf + hhalf;                // gelu_sig takes the full hidden scale
 #pragma unroll 1
     for (int half = 0; half < 2; ++half) {
       float v[64];
@@ -249,8 +250,8 @@ __global__ void __launch_bounds__(128 * kMlpWorkers, 1) mlp_tc_fwd_kernel(MlpPar
       const float* b1 = sB1 + half * 64;
 #pragma unroll
       for (int c = 0; c < 64; c += 2) {
-        const float g0 = gelu_fast(fmaf(v[c], ainv, b1[c]), hhalf);
-        const float g1 = gelu_fast(fmaf(v[c + 1], ainv, b1[c + 1]), hhalf);
+        const float g0 = gelu_sig(fmaf(v[c], ainv, b1[c]), hfull);
+        const float g1 = gelu_sig(fmaf(v[c + 1], ainv, b1[c + 1]), hfull);
         hp[c >> 1] = __uint_as_float(tc::pack_f16(g0, g1));
       }
       tc::tmem_st32(tbase + lane_addr + half * 32, hp);
@@ -509,6 +510,7 @@ mlp_tma_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
     tc::tc_fence_after();
     PROF(3);
     // ---- GELU epilogue, two halves of 64 hidden columns; packed fp16 hidden -> TMEM [0,64)
+    const float hfull = hhalf + hhalf;                // gelu_sig takes the full hidden scale
 #pragma unroll 1
     for (int half = 0; half < 2; ++half) {
       float v[64];
@@ -517,8 +519,8 @@ mlp_tma_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
       const float* b1 = sB1 + half * 64;
 #pragma unroll
       for (int c = 0; c < 64; c += 2) {
-        const float g0 = gelu_fast(fmaf(v[c], ainv, b1[c]), hhalf);
-        const float g1 = gelu_fast(fmaf(v[c + 1], ainv, b1[c + 1]), hhalf);
+        const float g0 = gelu_sig(fmaf(v[c], ainv, b1[c]), hfull);
+        const float g1 = gelu_sig(fmaf(v[c + 1], ainv, b1[c + 1]), hfull);
         hp[c >> 1] = __uint_as_float(tc::pack_f16(g0, g1));
       }
       tc::tmem_st32(tbase + lane_addr + half * 32, hp);
