@@ -6,7 +6,7 @@ import torch
 import bench
 from transmar_gan_b200 import train
 torch.backends.cuda.matmul.allow_tf32 = False
-torch.backends.cudnn.allow_tf32 = False
+torch.backends.cudnn.allow_tf32 = True   # as bench.py's train leg (torch default)
 torch.backends.cudnn.benchmark = True
 m = bench.build_model().train()
 step = train.L1TrainStep(m, lr=1e-4, betas=(0.5, 0.999), graph=False)
