@@ -80,7 +80,9 @@ def test_fused_grad_accumulation_matches_autograd():
     tensor-core backward block re-quantises its operands to bf16, which turns a 1e-7 perturbation into
     rounding flips of 2^-8 relative size - measured run-to-run spread of the SAME computation: <= 2e-7 for the
     decoder / stage 3 / bottleneck (first in the backward), growing to 5e-3 at encoder_layer1.blocks.0.
-    So: the early-backward groups must agree to 1e-5, the whole gradient to 2e-2 (the bf16 gate of
+    Since round 2 the stock glue runs channels-last and cuDNN's weight-gradient kernel for the reconstruction
+    convolution (first op of the backward) accumulates with atomics too: measured spread of the early groups 3.6e-5.
+    So: the early-backward groups must agree to 2e-4, the whole gradient to 2e-2 (the bf16 gate of
     tests/test_gpu_bwd_tc.py is 3e-2)."""
     import torch.nn.functional as F
     import transmar_gan_b200 as T
@@ -105,7 +107,7 @@ def test_fused_grad_accumulation_matches_autograd():
 
     def check(got, ref, scale=1.0):
         cat = lambda L, idx=None: torch.cat([L[i].flatten() for i in (idx if idx is not None else range(len(L)))])
-        assert (cat(got, early) - scale * cat(ref, early)).norm() <= 1e-5 * scale * cat(ref, early).norm()
+        assert (cat(got, early) - scale * cat(ref, early)).norm() <= 2e-4 * scale * cat(ref, early).norm()
         assert (cat(got) - scale * cat(ref)).norm() <= 2e-2 * scale * cat(ref).norm()
 
     ref = grads(False)

@@ -258,19 +258,17 @@ class SCDPBottleneck(nn.Module):
         self.pointwise = nn.Linear(self.concat_dim, dec_dim)
         self.norm = nn.LayerNorm(dec_dim)
 
-    def forward(self, shallow, feats, H, W):
-        xs = []
-        s = shallow
-        for i, f in enumerate(feats):
-            if i > 0:
-                s = F.max_pool2d(s, 2)
-            skip = F.leaky_relu(s, 0.01).flatten(2).transpose(1, 2)      # pooling.py:32-37
-            xs.append((f + skip).contiguous())
+    def forward(self, pooled, feats, H, W):
+        """pooled = (c0, maxpool2(c0), maxpool4(c0)) TOKEN-MAJOR [B, T_i, 64] (the cascade path computes them anyway;
+        BottleneckPool of the reference pools the NCHW shallow map, pooling.py:32-37 - same values), feats =
+        (e1_, e2_, e3_).  Everything stays channels-last: the 84-channel tensor is handed to the depthwise
+        convolution as a channels_last view (no NCHW copies, no layout-conversion kernels)."""
+        xs = [(f + F.leaky_relu(s, 0.01)).contiguous() for s, f in zip(pooled, feats)]
         cat = ops.PixelShuffleCatFunction.apply(xs[0], xs[1], xs[2], H, W)   # [B, HW, 84]
         B = cat.shape[0]
-        x = cat.transpose(1, 2).reshape(B, self.concat_dim, H, W)
+        x = cat.view(B, H, W, self.concat_dim).permute(0, 3, 1, 2)           # NCHW view of NHWC memory
         x = F.gelu(self.depthwise(x))
-        x = x.flatten(2).transpose(1, 2)
+        x = x.permute(0, 2, 3, 1).reshape(B, H * W, self.concat_dim)         # a view when the conv kept NHWC
         return ops.LayerNorm64Function.apply(self.pointwise(x), self.norm.weight, self.norm.bias)
 
 
@@ -465,17 +463,20 @@ class NGswin(nn.Module):
                                "(stage 3 must have 2x2 windows; the reference raises too)")
         if not torch.is_grad_enabled():
             return self._forward_fused(x.float().contiguous(), H0, W0)
-        shallow = self.shallow_extract(x.float())
-        c0 = shallow.flatten(2).transpose(1, 2).contiguous()     # [B, HW, 64]
+        # stock-PyTorch glue of the training path, kept channels-last / token-major end to end
+        shallow = self.shallow_extract(x.float().contiguous(memory_format=torch.channels_last))
+        c0 = shallow.permute(0, 2, 3, 1).reshape(B, H * W, self.embed_dim).contiguous()   # [B, HW, 64]
         e1_, e1, np1 = self.encoder_layer1(c0, (H, W))
-        c1 = torch.cat([_token_maxpool(c0, H, W), e1], dim=-1)
+        p0 = _token_maxpool(c0, H, W)
+        c1 = torch.cat([p0, e1], dim=-1)
         e2_, e2, np2 = self.encoder_layer2(c1, np1)
-        c2 = torch.cat([_token_maxpool(c1, *np1), e2], dim=-1)
+        pc1 = _token_maxpool(c1, *np1)                           # [maxpool4(c0) | maxpool2(e1)]
+        c2 = torch.cat([pc1, e2], dim=-1)
         e3_, _, _ = self.encoder_layer3(c2, np2)
-        bt = self.bottleneck(shallow, [e1_, e2_, e3_], H, W)
+        bt = self.bottleneck((c0, p0, pc1[..., :self.embed_dim]), [e1_, e2_, e3_], H, W)
         dec = self.decoder_layer1(bt + e1_, (H, W))
         dec = ops.LayerNorm64Function.apply(dec, self.norm.weight, self.norm.bias) + c0   # global skip (ngswin.py:204)
-        img = dec.transpose(1, 2).reshape(B, self.dec_dim, H, W)
+        img = dec.view(B, H, W, self.dec_dim).permute(0, 3, 1, 2)                 # NCHW view of NHWC memory
         out = self.to_target(img)
         return out[:, :, :H0, :W0]
 
