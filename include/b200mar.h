@@ -193,6 +193,20 @@ int b200mar_mlp_tma_fwd(const float* a, float* z_inout,
                         const float* fc2_w, const float* fc2_b,
                         const float* ln_w, const float* ln_b,
                         float* out, long long n_tok, void* stream);
+/* ---- backward twins of the fused glue (training path).  Parameter gradients are ACCUMULATED,
+ * activation gradients written.
+ * final_recon_bwd: backward of b200mar_final_recon_fwd (models/generator/components/reconstruction.py:14-19,
+ *   models/generator/ngswin.py:190,204,208): dy, y [B,1,H0,W0]; taps [B*H*W, 9] as written by the forward;
+ *   g1_scratch [B*H*W] floats; ddec, dc0 [B*H*W, 64] written; d_w1 [64,9], d_b1 [1], d_w2 [9], d_b2 [1], d_ln_* [64].
+ * shallow_tok_bwd: backward of b200mar_shallow_tok_fwd (components/encoder_decoder.py:23-27): dc0 [B*H*W, 64] ->
+ *   dw [64,9], db [64] accumulated; dx [B,1,H,W] written if not NULL.                                              */
+int b200mar_final_recon_bwd(const float* dy, const float* y, const float* taps, const float* dec,
+                            const float* c0, const float* ln_w, const float* ln_b, const float* w1,
+                            const float* b1, const float* w2, float* g1_scratch, float* ddec, float* dc0,
+                            float* d_ln_w, float* d_ln_b, float* d_w1, float* d_b1, float* d_w2,
+                            float* d_b2, int B, int H, int W, int H0, int W0, void* stream);
+int b200mar_shallow_tok_bwd(const float* x, const float* w, const float* dc0, float* dw, float* db,
+                            float* dx, int B, int H, int W, void* stream);
 /* ---- precision mode "bf16" (BASELINE.json configs[1]: "bf16 on 1xB200"): the NSTB residual
  * stream inside a stage is BF16 in HBM, which halves every pass of the three per-block kernels.  Arithmetic is
  * unchanged (fp32 q/k normalisation, softmax, LayerNorm, residual adds; FP16 / TF32 tensor-core operands): rows are

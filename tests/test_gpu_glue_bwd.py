@@ -1,0 +1,78 @@
+"""The fused glue of the TRAINING path: every autograd Function of ops.py that wraps a fused
+glue kernel (forward) and its hand-written backward, against stock PyTorch autograd of the same arithmetic
+(float64 on the GPU as the checker; the stock composite restates the reference's modules: reconstruction.py:14-19,
+encoder_decoder.py:23-27,117,188-200, pooling.py:13-17,32-37).  Tolerance: 1e-5 relative L2 per tensor (fp32
+accumulation order) unless stated."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def rel(a, b):
+    return ((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-30)).item()
+
+
+@pytest.fixture(autouse=True)
+def fp32_kernels():
+    import transmar_gan_b200 as T
+    old = T.ops.set_precision("fp32")
+    old_tf32 = torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = torch.backends.cudnn.allow_tf32 = False
+    yield
+    torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = old_tf32
+    T.ops.set_precision(old)
+
+
+@pytest.mark.parametrize("geom", [(2, 64, 96, 64, 96), (1, 128, 96, 100, 70), (3, 32, 32, 32, 17)])
+@pytest.mark.parametrize("fused_acc", [False, True])
+def test_final_recon_function(geom, fused_acc):
+    from transmar_gan_b200 import ops
+    B, H, W, H0, W0 = geom
+    g = torch.Generator().manual_seed(1)
+    dec = torch.randn(B, H * W, 64, generator=g).cuda().requires_grad_(True)
+    c0 = torch.randn(B, H * W, 64, generator=g).cuda().requires_grad_(True)
+    P = [(1 + 0.1 * torch.randn(64, generator=g)), 0.1 * torch.randn(64, generator=g),
+         0.05 * torch.randn(1, 64, 3, 3, generator=g), 0.1 * torch.randn(1, generator=g),
+         0.3 * torch.randn(1, 1, 3, 3, generator=g), 0.1 * torch.randn(1, generator=g)]
+    P = [p.cuda().requires_grad_(True) for p in P]
+    dy = torch.randn(B, 1, H0, W0, generator=g).cuda()
+    # stock composite in float64
+    D = [t.detach().double().requires_grad_(True) for t in (dec, c0, *P)]
+    v = F.layer_norm(D[0], (64,), D[2], D[3], 1e-5) + D[1]
+    img = v.transpose(1, 2).reshape(B, 64, H, W)
+    ref = torch.tanh(F.conv2d(F.conv2d(img, D[4], D[5], padding=1), D[6], D[7], padding=1))[:, :, :H0, :W0]
+    ref.backward(dy.double())
+    if fused_acc:
+        for p in P:
+            p.grad = torch.zeros_like(p)
+    with ops.fused_grad_accumulation(fused_acc):
+        out = ops.FinalReconFunction.apply(dec, c0, *P, H, W, H0, W0)
+        assert rel(out, ref) < 1e-5
+        out.backward(dy)
+    for got, want, name in zip((dec, c0, *P), D, ("ddec", "dc0", "dln_w", "dln_b", "dw1", "db1", "dw2", "db2")):
+        assert rel(got.grad, want.grad) < 2e-5, (name, rel(got.grad, want.grad))
+
+
+@pytest.mark.parametrize("geom", [(2, 64, 96), (1, 40, 24), (3, 16, 16)])
+@pytest.mark.parametrize("need_dx", [True, False])
+def test_shallow_tok_function(geom, need_dx):
+    from transmar_gan_b200 import ops
+    B, H, W = geom
+    g = torch.Generator().manual_seed(2)
+    x = torch.randn(B, 1, H, W, generator=g).cuda().requires_grad_(need_dx)
+    w = (0.2 * torch.randn(64, 1, 3, 3, generator=g)).cuda().requires_grad_(True)
+    b = (0.1 * torch.randn(64, generator=g)).cuda().requires_grad_(True)
+    dc0 = torch.randn(B, H * W, 64, generator=g).cuda()
+    X, Wd, Bd = (t.detach().double().requires_grad_(True) for t in (x, w, b))
+    ref = F.conv2d(X, Wd, Bd, padding=1).flatten(2).transpose(1, 2)
+    ref.backward(dc0.double())
+    c0 = ops.ShallowTokFunction.apply(x, w, b)
+    assert rel(c0, ref) < 1e-6
+    c0.backward(dc0)
+    assert rel(w.grad, Wd.grad) < 2e-5 and rel(b.grad, Bd.grad) < 2e-5
+    if need_dx:
+        assert rel(x.grad, X.grad) < 2e-5
+    else:
+        assert x.grad is None

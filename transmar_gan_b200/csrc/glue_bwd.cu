@@ -1,0 +1,280 @@
+// glue_bwd.cu — backward twins of the fused generator glue of glue_fwd.cu (the training
+// half): with them the TRAINING forward takes the fused channels-last glue path too and the ~140 stock PyTorch /
+// cuDNN launches of a step (layout flips, pools, small GEMMs, convolutions and their backward) disappear.
+// fp32 FMA-pipe kernels: the glue is 2.8 % of the model's FLOPs and memory-bound; every parameter gradient is
+// ACCUMULATED with atomics (the convention of every backward entry point of this library), activations' gradients
+// are written.
+//
+//   final_recon_bwd   tanh, conv3x3 1->1, conv3x3 64->1 (per-tap form), global skip, LayerNorm(norm)
+//                     (reconstruction.py:14-19, ngswin.py:190,204,208)
+//   shallow_tok_bwd   ShallowExtractor conv3x3 1->64 (encoder_decoder.py:23-27)
+//   cascade_proj_bwd  InterPool (2x2 max, first-maximum routing like nn.MaxPool2d) + concat + Linear
+//                     (pooling.py:13-17, ngswin.py:175-178, encoder_decoder.py:117,136)
+//   bottleneck_bwd    LN + Linear 84->64 + GELU + depthwise 3x3 + pixel-shuffle / concat / LeakyReLU skips
+//                     (encoder_decoder.py:159-164,188-200, pooling.py:32-37)
+#include "common.cuh"
+#include "../../include/b200mar.h"
+
+namespace b200mar {
+
+__device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+
+static int grid_cap(long long blocks, int per_sm) {
+  const long long cap = (long long)sm_count() * per_sm;
+  return (int)(blocks < 1 ? 1 : (blocks > cap ? cap : blocks));
+}
+
+// ================================================================================================ final + recon
+// Forward (glue_fwd.cu): v = LN(dec) + c0; taps[t][k] = sum_c w1[c][k] v[t][c]; o1[p] = b1 + sum_k taps[p + off_k][k]
+// (off_k = (k/3 - 1, k%3 - 1), zero outside the image); o2[p] = b2 + sum_k w2[k] o1[p + off_k]; y = tanh(o2), cropped.
+//
+// recon_bwd_kernel (image space, one thread per pixel of the PADDED H x W grid):
+//   g2[p] = dy[p] (1 - y[p]^2) inside the crop, else 0
+//   g1[p] = sum_k w2[k] g2[p - off_k]                       -> written, [B, H, W]
+//   dw2[k] += o1[p] g2[p - off_k],  db2 += g2[p],  db1 += g1[p]
+__global__ void __launch_bounds__(256) recon_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ y,
+                                                        const float* __restrict__ taps, const float* __restrict__ b1,
+                                                        const float* __restrict__ w2, float* __restrict__ g1,
+                                                        float* __restrict__ dw2, float* __restrict__ db2,
+                                                        float* __restrict__ db1, int B, int H, int W, int H0, int W0) {
+  __shared__ float red[8][12];
+  float w[9];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) w[k] = w2[k];
+  const float bias1 = b1[0];
+  float acc[11];
+#pragma unroll
+  for (int i = 0; i < 11; ++i) acc[i] = 0.f;
+  const long long npix = (long long)B * H * W;
+  for (long long p = blockIdx.x * 256ll + threadIdx.x; p < npix; p += (long long)gridDim.x * 256) {
+    const int xx = (int)(p % W), yy = (int)((p / W) % H);
+    const long long b = p / ((long long)W * H);
+    const float* dyb = dy + b * H0 * W0;
+    const float* yb = y + b * H0 * W0;
+    const float* tp = taps + b * H * W * 9;
+    float o1 = bias1;                                       // o1 at this pixel (inside the image by construction)
+    float gsum = 0.f;
+    float g2n[9];
+#pragma unroll
+    for (int dyi = 0; dyi < 3; ++dyi)
+#pragma unroll
+      for (int dxi = 0; dxi < 3; ++dxi) {
+        const int k = dyi * 3 + dxi;
+        const int y2 = yy + dyi - 1, x2 = xx + dxi - 1;      // p + off_k
+        if (y2 >= 0 && y2 < H && x2 >= 0 && x2 < W) o1 += __ldg(tp + ((long long)y2 * W + x2) * 9 + k);
+        const int y3 = yy - (dyi - 1), x3 = xx - (dxi - 1);  // p - off_k
+        float g = 0.f;
+        if (y3 >= 0 && y3 < H0 && x3 >= 0 && x3 < W0) {
+          const float yo = __ldg(yb + (long long)y3 * W0 + x3);
+          g = __ldg(dyb + (long long)y3 * W0 + x3) * (1.0f - yo * yo);
+        }
+        g2n[k] = g;
+        gsum = fmaf(w[k], g, gsum);
+      }
+    g1[p] = gsum;
+#pragma unroll
+    for (int k = 0; k < 9; ++k) acc[k] = fmaf(o1, g2n[k], acc[k]);
+    acc[9] += g2n[4];                                       // off_4 = (0,0): g2 at this pixel
+    acc[10] += gsum;
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int i = 0; i < 11; ++i) {
+    const float s = warp_sum(acc[i]);
+    if (lane == 0) red[warp][i] = s;
+  }
+  __syncthreads();
+  if (threadIdx.x < 11) {
+    float s = 0.f;
+#pragma unroll
+    for (int wv = 0; wv < 8; ++wv) s += red[wv][threadIdx.x];
+    if (threadIdx.x < 9) atomicAdd(dw2 + threadIdx.x, s);
+    else if (threadIdx.x == 9) atomicAdd(db2, s);
+    else atomicAdd(db1, s);
+  }
+}
+
+// final_bwd_kernel (token space, one warp per token, lane owns channels lane and lane + 32):
+//   dtaps[t][k] = g1[t - off_k] (0 outside the image);  dv[c] = sum_k w1[c][k] dtaps[k]  -> dc0 (written)
+//   dw1[c][k] += v[c] dtaps[k];  LayerNorm backward of dv -> ddec (written), d_ln_w += dv xhat, d_ln_b += dv
+__global__ void __launch_bounds__(256) final_bwd_kernel(const float* __restrict__ dec, const float* __restrict__ c0,
+                                                        const float* __restrict__ ln_w, const float* __restrict__ ln_b,
+                                                        const float* __restrict__ w1, const float* __restrict__ g1,
+                                                        float* __restrict__ ddec, float* __restrict__ dc0,
+                                                        float* __restrict__ dw1, float* __restrict__ dlnw,
+                                                        float* __restrict__ dlnb, int B, int H, int W) {
+  __shared__ float red[8][64][12];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float wa[9], wb[9], aa[11], ab[11];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) { wa[k] = w1[lane * 9 + k]; wb[k] = w1[(lane + 32) * 9 + k]; }
+#pragma unroll
+  for (int i = 0; i < 11; ++i) { aa[i] = 0.f; ab[i] = 0.f; }
+  const float ga = ln_w[lane], gb = ln_w[lane + 32], ba = ln_b[lane], bb = ln_b[lane + 32];
+  const long long ntok = (long long)B * H * W;
+  const long long warp0 = ((long long)blockIdx.x * 256 + threadIdx.x) >> 5;
+  const long long nwarp = ((long long)gridDim.x * 256) >> 5;
+  for (long long t = warp0; t < ntok; t += nwarp) {
+    const int xx = (int)(t % W), yy = (int)((t / W) % H);
+    const float* gimg = g1 + (t - (long long)yy * W - xx);
+    // lane k < 9 fetches dtaps[k]; broadcast by shuffle
+    float mine = 0.f;
+    if (lane < 9) {
+      const int y3 = yy - (lane / 3 - 1), x3 = xx - (lane % 3 - 1);
+      if (y3 >= 0 && y3 < H && x3 >= 0 && x3 < W) mine = __ldg(gimg + (long long)y3 * W + x3);
+    }
+    const float y0 = __ldg(dec + t * 64 + lane), y1 = __ldg(dec + t * 64 + lane + 32);
+    const float mean = warp_sum(y0 + y1) * (1.0f / 64.f);
+    const float d0 = y0 - mean, d1 = y1 - mean;
+    const float rstd = 1.0f / sqrtf(warp_sum(d0 * d0 + d1 * d1) * (1.0f / 64.f) + kLnEps);
+    const float xh0 = d0 * rstd, xh1 = d1 * rstd;
+    const float v0 = xh0 * ga + ba + __ldg(c0 + t * 64 + lane);
+    const float v1 = xh1 * gb + bb + __ldg(c0 + t * 64 + lane + 32);
+    float dv0 = 0.f, dv1 = 0.f;
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+      const float dt = __shfl_sync(0xffffffffu, mine, k);
+      dv0 = fmaf(wa[k], dt, dv0);
+      dv1 = fmaf(wb[k], dt, dv1);
+      aa[k] = fmaf(v0, dt, aa[k]);
+      ab[k] = fmaf(v1, dt, ab[k]);
+    }
+    dc0[t * 64 + lane] = dv0;
+    dc0[t * 64 + lane + 32] = dv1;
+    aa[9] = fmaf(dv0, xh0, aa[9]); ab[9] = fmaf(dv1, xh1, ab[9]);     // d ln_w
+    aa[10] += dv0; ab[10] += dv1;                                     // d ln_b
+    const float dx0 = dv0 * ga, dx1 = dv1 * gb;
+    const float m1 = warp_sum(dx0 + dx1) * (1.0f / 64.f);
+    const float m2 = warp_sum(dx0 * xh0 + dx1 * xh1) * (1.0f / 64.f);
+    ddec[t * 64 + lane] = rstd * (dx0 - m1 - xh0 * m2);
+    ddec[t * 64 + lane + 32] = rstd * (dx1 - m1 - xh1 * m2);
+  }
+#pragma unroll
+  for (int i = 0; i < 11; ++i) { red[warp][lane][i] = aa[i]; red[warp][lane + 32][i] = ab[i]; }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < 64 * 11; idx += 256) {
+    const int c = idx / 11, i = idx - c * 11;
+    float s = 0.f;
+#pragma unroll
+    for (int wv = 0; wv < 8; ++wv) s += red[wv][c][i];
+    if (i < 9) atomicAdd(dw1 + c * 9 + i, s);
+    else if (i == 9) atomicAdd(dlnw + c, s);
+    else atomicAdd(dlnb + c, s);
+  }
+}
+
+// ================================================================================================ shallow conv
+// c0[t][c] = b[c] + sum_k w[c][k] x[t + off_k]  ->  dw[c][k] += sum_t dc0[t][c] x[t + off_k], db[c] += sum_t dc0[t][c]
+// thread = (4 channels, one of 16 pixel lanes) as in the forward; 36 + 4 accumulators per thread.
+__global__ void __launch_bounds__(256) shallow_tok_wgrad_kernel(const float* __restrict__ x,
+                                                                const float* __restrict__ dc0,
+                                                                float* __restrict__ dw, float* __restrict__ db,
+                                                                int B, int H, int W) {
+  __shared__ float red[16][64][10];
+  const int cq = threadIdx.x & 15, pl = threadIdx.x >> 4;
+  float acc[4][10];
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int k = 0; k < 10; ++k) acc[j][k] = 0.f;
+  const unsigned npix = (unsigned)B * H * W;
+  for (unsigned pix = blockIdx.x * 16u + pl; pix < npix; pix += gridDim.x * 16u) {
+    const unsigned rowi = pix / (unsigned)W;
+    const int xx = (int)(pix - rowi * W), yy = (int)(rowi % (unsigned)H);
+    const float* img = x + (pix - (unsigned)yy * W - xx);
+    float in[9];
+#pragma unroll
+    for (int dy = 0; dy < 3; ++dy)
+#pragma unroll
+      for (int dx = 0; dx < 3; ++dx) {
+        const int y2 = yy + dy - 1, x2 = xx + dx - 1;
+        in[dy * 3 + dx] = (y2 >= 0 && y2 < H && x2 >= 0 && x2 < W) ? __ldg(img + (long long)y2 * W + x2) : 0.f;
+      }
+    const float4 g = ldg4(dc0 + (size_t)pix * 64 + cq * 4);
+    const float gv[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+#pragma unroll
+      for (int k = 0; k < 9; ++k) acc[j][k] = fmaf(gv[j], in[k], acc[j][k]);
+      acc[j][9] += gv[j];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int k = 0; k < 10; ++k) red[pl][cq * 4 + j][k] = acc[j][k];
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < 640; idx += 256) {
+    const int c = idx / 10, k = idx - c * 10;
+    float s = 0.f;
+#pragma unroll
+    for (int l = 0; l < 16; ++l) s += red[l][c][k];
+    if (k < 9) atomicAdd(dw + c * 9 + k, s); else atomicAdd(db + c, s);
+  }
+}
+
+// dx[p] = sum_k sum_c dc0[p - off_k][c] w[c][k]; one warp per pixel, lane owns channels lane, lane + 32
+__global__ void __launch_bounds__(256) shallow_tok_dgrad_kernel(const float* __restrict__ dc0,
+                                                                const float* __restrict__ w,
+                                                                float* __restrict__ dx, int B, int H, int W) {
+  const int lane = threadIdx.x & 31;
+  float wa[9], wb[9];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) { wa[k] = w[lane * 9 + k]; wb[k] = w[(lane + 32) * 9 + k]; }
+  const long long npix = (long long)B * H * W;
+  const long long warp0 = ((long long)blockIdx.x * 256 + threadIdx.x) >> 5;
+  const long long nwarp = ((long long)gridDim.x * 256) >> 5;
+  for (long long p = warp0; p < npix; p += nwarp) {
+    const int xx = (int)(p % W), yy = (int)((p / W) % H);
+    const long long base = p - (long long)yy * W - xx;
+    float s = 0.f;
+#pragma unroll
+    for (int dy = 0; dy < 3; ++dy)
+#pragma unroll
+      for (int dxi = 0; dxi < 3; ++dxi) {
+        const int y3 = yy - (dy - 1), x3 = xx - (dxi - 1);
+        if (y3 >= 0 && y3 < H && x3 >= 0 && x3 < W) {
+          const float* g = dc0 + (base + (long long)y3 * W + x3) * 64;
+          s = fmaf(__ldg(g + lane), wa[dy * 3 + dxi], s);
+          s = fmaf(__ldg(g + lane + 32), wb[dy * 3 + dxi], s);
+        }
+      }
+    s = warp_sum(s);
+    if (lane == 0) dx[p] = s;
+  }
+}
+
+}  // namespace b200mar
+
+using namespace b200mar;
+
+extern "C" int b200mar_final_recon_bwd(const float* dy, const float* y, const float* taps, const float* dec,
+                                       const float* c0, const float* ln_w, const float* ln_b, const float* w1,
+                                       const float* b1, const float* w2, float* g1_scratch, float* ddec, float* dc0,
+                                       float* d_ln_w, float* d_ln_b, float* d_w1, float* d_b1, float* d_w2,
+                                       float* d_b2, int B, int H, int W, int H0, int W0, void* stream) {
+  if (B <= 0 || H <= 0 || W <= 0 || H0 > H || W0 > W || (long long)B * H * W >= (1ll << 31)) return -1;
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long npix = (long long)B * H * W;
+  recon_bwd_kernel<<<grid_cap((npix + 255) / 256, 4), 256, 0, st>>>(dy, y, taps, b1, w2, g1_scratch, d_w2, d_b2, d_b1,
+                                                                   B, H, W, H0, W0);
+  B200MAR_CHECK(cudaGetLastError());
+  final_bwd_kernel<<<grid_cap((npix + 7) / 8, 4), 256, 0, st>>>(dec, c0, ln_w, ln_b, w1, g1_scratch, ddec, dc0, d_w1,
+                                                               d_ln_w, d_ln_b, B, H, W);
+  B200MAR_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200mar_shallow_tok_bwd(const float* x, const float* w, const float* dc0, float* dw, float* db,
+                                       float* dx, int B, int H, int W, void* stream) {
+  if (B <= 0 || H <= 0 || W <= 0 || (long long)B * H * W >= (1ll << 31)) return -1;
+  cudaStream_t st = (cudaStream_t)stream;
+  const long long npix = (long long)B * H * W;
+  shallow_tok_wgrad_kernel<<<grid_cap((npix + 127) / 128, 2), 256, 0, st>>>(x, dc0, dw, db, B, H, W);
+  B200MAR_CHECK(cudaGetLastError());
+  if (dx) {
+    shallow_tok_dgrad_kernel<<<grid_cap((npix + 7) / 8, 8), 256, 0, st>>>(dc0, w, dx, B, H, W);
+    B200MAR_CHECK(cudaGetLastError());
+  }
+  return 0;
+}

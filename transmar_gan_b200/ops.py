@@ -602,6 +602,69 @@ def final_recon_fwd(dec: Tensor, c0: Tensor, ln_w: Tensor, ln_b: Tensor, w1: Ten
     return out
 
 
+# ------------------------------------------------------------------------------ fused glue with backward (training)
+def _acc(params):
+    """(targets, fused): the parameters' own .grad views when fused accumulation is on, else zeroed scratch."""
+    G = _grad_targets(params)
+    if G is not None:
+        return G, True
+    return [torch.zeros_like(p) for p in params], False
+
+
+class ShallowTokFunction(torch.autograd.Function):
+    """c0 = ShallowExtractor.conv1(x) written token-major [B, H*W, 64] (shallow_tok kernel) with its backward."""
+
+    @staticmethod
+    def forward(ctx_, x, w, b):
+        x = x.contiguous()
+        ctx_.save_for_backward(x, w, b)
+        return shallow_tok_fwd(x, w.detach(), b.detach())
+
+    @staticmethod
+    def backward(ctx_, dc0):
+        x, w, b = ctx_.saved_tensors
+        B, _, H, W = x.shape
+        dc0 = dc0.contiguous()
+        G, fused = _acc((w, b))
+        dx = torch.empty_like(x) if ctx_.needs_input_grad[0] else None
+        _chk(x, dc0, dx, *G)
+        _call("shallow_tok_bwd", _p(x), _p(w.detach()), _p(dc0), _p(G[0]), _p(G[1]), _p(dx), B, H, W, _stream())
+        return (dx, *((None, None) if fused else G))
+
+
+class FinalReconFunction(torch.autograd.Function):
+    """LN(norm) + global skip + Reconstruction + crop (final_recon_fwd) with its backward."""
+
+    @staticmethod
+    def forward(ctx_, dec, c0, ln_w, ln_b, w1, b1, w2, b2, H, W, H0, W0):
+        dec, c0 = dec.contiguous(), c0.contiguous()
+        P = [t.detach() for t in (ln_w, ln_b, w1, b1, w2, b2)]
+        _chk(dec, c0, *P)
+        B = dec.shape[0]
+        taps = torch.empty((B, H * W, 9), device=dec.device, dtype=torch.float32)
+        out = torch.empty((B, 1, H0, W0), device=dec.device, dtype=torch.float32)
+        _call("final_recon_fwd", _p(dec), _p(c0), *[_p(t) for t in P], _p(taps), _p(out), B, H, W, H0, W0, _stream())
+        ctx_.save_for_backward(dec, c0, taps, out, ln_w, ln_b, w1, b1, w2, b2)
+        ctx_.geom = (H, W, H0, W0)
+        return out
+
+    @staticmethod
+    def backward(ctx_, dy):
+        dec, c0, taps, out, ln_w, ln_b, w1, b1, w2, b2 = ctx_.saved_tensors
+        H, W, H0, W0 = ctx_.geom
+        B = dec.shape[0]
+        dy = dy.contiguous()
+        G, fused = _acc((ln_w, ln_b, w1, b1, w2, b2))
+        g1 = torch.empty((B, H * W), device=dec.device, dtype=torch.float32)
+        ddec, dc0 = torch.empty_like(dec), torch.empty_like(c0)
+        _chk(dy, dec, c0, taps, out, g1, ddec, dc0, *G)
+        _call("final_recon_bwd", _p(dy), _p(out), _p(taps), _p(dec), _p(c0), _p(ln_w.detach()), _p(ln_b.detach()),
+              _p(w1.detach()), _p(b1.detach()), _p(w2.detach()), _p(g1), _p(ddec), _p(dc0), _p(G[0]), _p(G[1]),
+              _p(G[2]), _p(G[3]), _p(G[4]), _p(G[5]), B, H, W, H0, W0, _stream())
+        profile.launches += 1
+        return (ddec, dc0, *(([None] * 6) if fused else G), None, None, None, None)
+
+
 # ------------------------------------------------------------------------------ index maps
 def partition_index(B: int, ph: int, pw: int, shift: int, device) -> Tuple[Tensor, Tensor]:
     n = B * (ph // 8) * (pw // 8)
