@@ -205,6 +205,13 @@ int b200mar_final_recon_bwd(const float* dy, const float* y, const float* taps, 
                             const float* b1, const float* w2, float* g1_scratch, float* ddec, float* dc0,
                             float* d_ln_w, float* d_ln_b, float* d_w1, float* d_b1, float* d_w2,
                             float* d_b2, int B, int H, int W, int H0, int W0, void* stream);
+/* cascade_proj_bwd: backward of b200mar_cascade_proj_fwd / _tc_fwd (components/pooling.py:13-17 InterPool with
+ *   nn.MaxPool2d's first-maximum routing, models/generator/ngswin.py:175-178, encoder_decoder.py:117,136): dout
+ *   [B*h*wd, 64]; dpool (may be NULL) = gradient arriving on the returned poolA; d_srcA / d_srcB [B*4*h*wd, 64] and
+ *   d_direct [B*h*wd, 64] written; dw [64, K], db [64] accumulated (K = 128 without srcB, 192 with).                */
+int b200mar_cascade_proj_bwd(const float* srcA, const float* srcB, const float* direct, const float* w,
+                             const float* dout, const float* dpool, float* d_srcA, float* d_srcB,
+                             float* d_direct, float* dw, float* db, int B, int h, int wd, void* stream);
 int b200mar_shallow_tok_bwd(const float* x, const float* w, const float* dc0, float* dw, float* db,
                             float* dx, int B, int H, int W, void* stream);
 /* ---- precision mode "bf16" (BASELINE.json configs[1]: "bf16 on 1xB200"): the NSTB residual

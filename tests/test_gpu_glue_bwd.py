@@ -76,3 +76,40 @@ def test_shallow_tok_function(geom, need_dx):
         assert rel(x.grad, X.grad) < 2e-5
     else:
         assert x.grad is None
+
+
+def _pool(x, B, h, wd):
+    """nn.MaxPool2d(2) on a token-major [B, 4*h*wd, C] map (first-maximum routing in the backward)."""
+    C = x.shape[-1]
+    y = F.max_pool2d(x.transpose(1, 2).reshape(B, C, 2 * h, 2 * wd), 2)
+    return y.flatten(2).transpose(1, 2)
+
+
+@pytest.mark.parametrize("geom", [(2, 16, 24), (1, 8, 8), (3, 12, 20)])
+@pytest.mark.parametrize("with_b", [False, True])
+@pytest.mark.parametrize("use_pool_grad", [True, False])
+def test_cascade_proj_function(geom, with_b, use_pool_grad):
+    from transmar_gan_b200 import ops
+    B, h, wd = geom
+    K = 192 if with_b else 128
+    g = torch.Generator().manual_seed(3)
+    srcA = torch.randn(B, 4 * h * wd, 64, generator=g).cuda().requires_grad_(True)
+    srcB = torch.randn(B, 4 * h * wd, 64, generator=g).cuda().requires_grad_(True) if with_b else None
+    direct = torch.randn(B, h * wd, 64, generator=g).cuda().requires_grad_(True)
+    w = (0.1 * torch.randn(64, K, generator=g)).cuda().requires_grad_(True)
+    b = (0.1 * torch.randn(64, generator=g)).cuda().requires_grad_(True)
+    dout = torch.randn(B, h * wd, 64, generator=g).cuda()
+    dpool = torch.randn(B, h * wd, 64, generator=g).cuda()
+    ins = [t for t in (srcA, srcB, direct, w, b) if t is not None]
+    D = [t.detach().double().requires_grad_(True) for t in ins]
+    dA, dB_, dD, dW, dBi = (D[0], D[1], D[2], D[3], D[4]) if with_b else (D[0], None, D[1], D[2], D[3])
+    pa = _pool(dA, B, h, wd)
+    cat = torch.cat([pa] + ([_pool(dB_, B, h, wd)] if with_b else []) + [dD], dim=-1)
+    ref = F.linear(cat, dW, dBi)
+    loss = (ref * dout.double()).sum() + ((pa * dpool.double()).sum() if use_pool_grad else 0.0)
+    loss.backward()
+    out, pool = ops.CascadeProjFunction.apply(srcA, srcB, direct, w, b, h, wd)
+    assert rel(out, ref) < 1e-5 and rel(pool, pa) < 1e-7
+    ((out * dout).sum() + ((pool * dpool).sum() if use_pool_grad else 0.0)).backward()
+    for got, want in zip(ins, D):
+        assert rel(got.grad, want.grad) < 2e-5, rel(got.grad, want.grad)

@@ -244,6 +244,136 @@ __global__ void __launch_bounds__(256) shallow_tok_dgrad_kernel(const float* __r
   }
 }
 
+// ================================================================================================ cascade proj
+// Forward: out[t] = W [64, K] cat(pool2x2(srcA)[t], pool2x2(srcB)[t] (optional), direct[t]) + bias, poolA = pool2x2(srcA).
+// Backward per tile of 64 output tokens: the concat tile is recomputed (pooling included), then
+//   dcat = dout W            (three 64x64x64 tile products)  -> d_direct written; pooled parts routed to the FIRST
+//                             maximum of each 2x2 neighbourhood (nn.MaxPool2d semantics, pooling.py:13-17); the
+//                             gradient arriving on the returned poolA (dpool, optional) joins part 0
+//   dW += dout^T cat, db += column sums of dout   (per-CTA partials in registers, one atomic flush)
+struct CascadeBwdParams {
+  const float* srcA; const float* srcB; const float* direct; const float* w;
+  const float* dout; const float* dpool;
+  float* d_srcA; float* d_srcB; float* d_direct; float* dw; float* db;
+  int B, h, wd, K;
+};
+__global__ void __launch_bounds__(kThreads, 1) cascade_proj_bwd_kernel(CascadeBwdParams p) {
+  extern __shared__ __align__(16) float smem[];
+  const int ld = p.K + 4;
+  float* sW = smem;                       // [64 n][ld]
+  float* sA = sW + 64 * ld;               // [64 tokens][ld]   the concat tile
+  float* sD = sA + 64 * ld;               // [64 tokens][68]   dout tile
+  float* sG = sD + 64 * kLd64;            // [64 tokens][68]   one 64-column chunk of dcat
+  const int tid = threadIdx.x;
+  load_matrix(sW, ld, p.w, 64, p.K, 64);
+  const long long ntok = (long long)p.B * p.h * p.wd;
+  const long long ntile = (ntok + 63) / 64;
+  const int W2 = 2 * p.wd, nchunk = p.K / 64, direct_part = nchunk - 1;
+  float accW[3][4][4];
+#pragma unroll
+  for (int q = 0; q < 3; ++q) zero_acc(accW[q]);
+  float accB = 0.f;
+  for (long long tile = blockIdx.x; tile < ntile; tile += gridDim.x) {
+    __syncthreads();
+    const long long t0 = tile * 64;
+    for (int idx = tid; idx < 64 * (p.K / 4); idx += kThreads) {
+      const int i = idx / (p.K / 4), c4 = (idx - i * (p.K / 4)) * 4;
+      const long long t = t0 + i;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (t < ntok) {
+        const int part = c4 >> 6, c = c4 & 63;
+        if (part == direct_part) {
+          v = ldg4(p.direct + t * 64 + c);
+        } else {
+          const int xx = (int)(t % p.wd), yy = (int)((t / p.wd) % p.h);
+          const long long b = t / ((long long)p.wd * p.h);
+          const float* s = (part == 0 ? p.srcA : p.srcB) + ((b * 2 * p.h + 2 * yy) * W2 + 2 * xx) * 64 + c;
+          const float4 a0 = ldg4(s), a1 = ldg4(s + 64), a2 = ldg4(s + (long long)W2 * 64), a3 = ldg4(s + (long long)W2 * 64 + 64);
+          v = make_float4(fmaxf(fmaxf(a0.x, a1.x), fmaxf(a2.x, a3.x)), fmaxf(fmaxf(a0.y, a1.y), fmaxf(a2.y, a3.y)),
+                          fmaxf(fmaxf(a0.z, a1.z), fmaxf(a2.z, a3.z)), fmaxf(fmaxf(a0.w, a1.w), fmaxf(a2.w, a3.w)));
+        }
+      }
+      *reinterpret_cast<float4*>(sA + i * ld + c4) = v;
+    }
+    for (int idx = tid; idx < 64 * 16; idx += kThreads) {
+      const int i = idx >> 4, c4 = (idx & 15) * 4;
+      const long long t = t0 + i;
+      *reinterpret_cast<float4*>(sD + i * kLd64 + c4) = t < ntok ? ldg4(p.dout + t * 64 + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    __syncthreads();
+    if (tid < 64) {
+      float s = 0.f;
+#pragma unroll 8
+      for (int i = 0; i < 64; ++i) s += sD[i * kLd64 + tid];
+      accB += s;
+    }
+#pragma unroll 1
+    for (int q = 0; q < nchunk; ++q) {
+      // dW[n][q*64 + k] += sum_i dout[i][n] cat[i][q*64 + k]
+      gemm64<true, true>(accW[q], sD, kLd64, sA + q * 64, ld, 64);
+      // dcat[i][q*64 + k] = sum_n dout[i][n] W[n][q*64 + k]
+      float acc[4][4]; zero_acc(acc);
+      gemm64<false, true>(acc, sD, kLd64, sW + q * 64, ld, 64);
+      if (q == direct_part) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const long long t = t0 + gemm_row<false>(i);
+          if (t < ntok)
+            *reinterpret_cast<float4*>(p.d_direct + t * 64 + gemm_col<true>(0)) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+        }
+      } else {
+        __syncthreads();                  // sG free (previous chunk's routing pass done)
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          *reinterpret_cast<float4*>(sG + gemm_row<false>(i) * kLd64 + gemm_col<true>(0)) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+        __syncthreads();
+        const float* src = q == 0 ? p.srcA : p.srcB;
+        float* dsrc = q == 0 ? p.d_srcA : p.d_srcB;
+        for (int idx = tid; idx < 64 * 16; idx += kThreads) {
+          const int i = idx >> 4, c = (idx & 15) * 4;
+          const long long t = t0 + i;
+          if (t >= ntok) continue;
+          float4 g = *reinterpret_cast<const float4*>(sG + i * kLd64 + c);
+          if (q == 0 && p.dpool) {
+            const float4 e = ldg4(p.dpool + t * 64 + c);
+            g.x += e.x; g.y += e.y; g.z += e.z; g.w += e.w;
+          }
+          const int xx = (int)(t % p.wd), yy = (int)((t / p.wd) % p.h);
+          const long long b = t / ((long long)p.wd * p.h);
+          const long long o = ((b * 2 * p.h + 2 * yy) * W2 + 2 * xx) * 64 + c;
+          const long long offs[4] = {0, 64, (long long)W2 * 64, (long long)W2 * 64 + 64};
+          float4 a[4];
+#pragma unroll
+          for (int s4 = 0; s4 < 4; ++s4) a[s4] = ldg4(src + o + offs[s4]);
+          const float gv[4] = {g.x, g.y, g.z, g.w};
+          float r[4][4];
+#pragma unroll
+          for (int ch = 0; ch < 4; ++ch) {
+            const float v0 = (&a[0].x)[ch], v1 = (&a[1].x)[ch], v2 = (&a[2].x)[ch], v3 = (&a[3].x)[ch];
+            int best = 0; float m = v0;
+            if (v1 > m) { m = v1; best = 1; }
+            if (v2 > m) { m = v2; best = 2; }
+            if (v3 > m) { m = v3; best = 3; }
+#pragma unroll
+            for (int s4 = 0; s4 < 4; ++s4) r[s4][ch] = best == s4 ? gv[ch] : 0.f;
+          }
+#pragma unroll
+          for (int s4 = 0; s4 < 4; ++s4)
+            *reinterpret_cast<float4*>(dsrc + o + offs[s4]) = make_float4(r[s4][0], r[s4][1], r[s4][2], r[s4][3]);
+        }
+      }
+    }
+  }
+  // flush the per-CTA partials
+  for (int q = 0; q < nchunk; ++q)
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        atomicAdd(p.dw + (size_t)gemm_row<true>(i) * p.K + q * 64 + gemm_col<true>(j), accW[q][i][j]);
+  if (tid < 64) atomicAdd(p.db + tid, accB);
+}
+
 }  // namespace b200mar
 
 using namespace b200mar;
@@ -276,5 +406,24 @@ extern "C" int b200mar_shallow_tok_bwd(const float* x, const float* w, const flo
     shallow_tok_dgrad_kernel<<<grid_cap((npix + 7) / 8, 8), 256, 0, st>>>(dc0, w, dx, B, H, W);
     B200MAR_CHECK(cudaGetLastError());
   }
+  return 0;
+}
+
+extern "C" int b200mar_cascade_proj_bwd(const float* srcA, const float* srcB, const float* direct, const float* w,
+                                        const float* dout, const float* dpool, float* d_srcA, float* d_srcB,
+                                        float* d_direct, float* dw, float* db, int B, int h, int wd, void* stream) {
+  if (B <= 0 || h <= 0 || wd <= 0 || !srcA || !direct || !dout || !d_srcA || !d_direct || (srcB && !d_srcB)) return -1;
+  CascadeBwdParams p{srcA, srcB, direct, w, dout, dpool, d_srcA, d_srcB, d_direct, dw, db, B, h, wd, srcB ? 192 : 128};
+  const size_t smem = ((size_t)2 * 64 * (p.K + 4) + 2 * 64 * kLd64) * sizeof(float);
+  static DeviceOnce configured;
+  if (configured.first()) {
+    B200MAR_CHECK(cudaFuncSetAttribute(cascade_proj_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)(((size_t)2 * 64 * 196 + 2 * 64 * kLd64) * sizeof(float))));
+    configured.done();
+  }
+  const long long ntile = ((long long)B * h * wd + 63) / 64;
+  const int grid = (int)(ntile < sm_count() ? ntile : sm_count());
+  cascade_proj_bwd_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(p);
+  B200MAR_CHECK(cudaGetLastError());
   return 0;
 }

@@ -632,6 +632,36 @@ class ShallowTokFunction(torch.autograd.Function):
         return (dx, *((None, None) if fused else G))
 
 
+class CascadeProjFunction(torch.autograd.Function):
+    """out, poolA = apply(srcA, srcB | None, direct, w, bias, h, wd): InterPool + concat + across_cascade_proj
+    (cascade_proj kernels) with its backward; poolA = maxpool2x2(srcA) is differentiable too."""
+
+    @staticmethod
+    def forward(ctx_, srcA, srcB, direct, w, bias, h, wd):
+        srcA, direct = srcA.contiguous(), direct.contiguous()
+        srcB = None if srcB is None else srcB.contiguous()
+        out, pool = cascade_proj_fwd(srcA, srcB, direct, w.detach(), bias.detach(), h, wd, True)
+        ctx_.save_for_backward(srcA, direct, w, bias, *(() if srcB is None else (srcB,)))
+        ctx_.geom = (h, wd)
+        return out, pool
+
+    @staticmethod
+    def backward(ctx_, dout, dpool):
+        srcA, direct, w, bias, *rest = ctx_.saved_tensors
+        srcB = rest[0] if rest else None
+        h, wd = ctx_.geom
+        B = direct.shape[0]
+        dout = dout.contiguous()
+        dpool = None if dpool is None else dpool.contiguous()
+        G, fused = _acc((w, bias))
+        d_srcA, d_direct = torch.empty_like(srcA), torch.empty_like(direct)
+        d_srcB = None if srcB is None else torch.empty_like(srcB)
+        _chk(srcA, srcB, direct, dout, dpool, d_srcA, d_srcB, d_direct, *G)
+        _call("cascade_proj_bwd", _p(srcA), _p(srcB), _p(direct), _p(w.detach()), _p(dout), _p(dpool), _p(d_srcA),
+              _p(d_srcB), _p(d_direct), _p(G[0]), _p(G[1]), B, h, wd, _stream())
+        return (d_srcA, d_srcB, d_direct, *((None, None) if fused else G), None, None)
+
+
 class FinalReconFunction(torch.autograd.Function):
     """LN(norm) + global skip + Reconstruction + crop (final_recon_fwd) with its backward."""
 
