@@ -212,6 +212,17 @@ int b200mar_final_recon_bwd(const float* dy, const float* y, const float* taps, 
 int b200mar_cascade_proj_bwd(const float* srcA, const float* srcB, const float* direct, const float* w,
                              const float* dout, const float* dpool, float* d_srcA, float* d_srcB,
                              float* d_direct, float* dw, float* db, int B, int h, int wd, void* stream);
+/* bottleneck_bwd: backward of b200mar_bottleneck_cat_fwd + b200mar_bottleneck_tail(_tc)_fwd (SCDPBottleneck,
+ *   components/encoder_decoder.py:159-164,188-200; BottleneckPool pooling.py:32-37; the "+ e1" of ngswin.py:189):
+ *   cat [B*H*W, 84] as written by the forward, dout [B*H*W, 64]; ddwc_scratch [B*H*W, 84] floats;
+ *   dc0, de1 [B*H*W, 64], dp0, de2 [B*H*W/4, 64], dp00, de3 [B*H*W/16, 64] written (de1 includes dout, the tail's
+ *   residual); d_dw_w [84,9], d_dw_b [84], d_pw_w [64,84], d_pw_b [64], d_ln_w, d_ln_b [64] accumulated.           */
+int b200mar_bottleneck_bwd(const float* cat, const float* dout, const float* c0, const float* p0,
+                           const float* p00, const float* dw_w, const float* dw_b, const float* pw_w,
+                           const float* pw_b, const float* ln_w, float* ddwc_scratch, float* dc0,
+                           float* dp0, float* dp00, float* de1, float* de2, float* de3, float* d_dw_w,
+                           float* d_dw_b, float* d_pw_w, float* d_pw_b, float* d_ln_w, float* d_ln_b,
+                           int B, int H, int W, void* stream);
 int b200mar_shallow_tok_bwd(const float* x, const float* w, const float* dc0, float* dw, float* db,
                             float* dx, int B, int H, int W, void* stream);
 /* ---- precision mode "bf16" (BASELINE.json configs[1]: "bf16 on 1xB200"): the NSTB residual

@@ -113,3 +113,38 @@ def test_cascade_proj_function(geom, with_b, use_pool_grad):
     ((out * dout).sum() + ((pool * dpool).sum() if use_pool_grad else 0.0)).backward()
     for got, want in zip(ins, D):
         assert rel(got.grad, want.grad) < 2e-5, rel(got.grad, want.grad)
+
+
+@pytest.mark.parametrize("geom", [(2, 32, 48), (1, 16, 16), (1, 64, 40)])
+def test_bottleneck_function(geom):
+    from transmar_gan_b200 import ops
+    B, H, W = geom
+    g = torch.Generator().manual_seed(4)
+    mk = lambda *s, sc=1.0: (sc * torch.randn(*s, generator=g)).cuda().requires_grad_(True)
+    c0, e1 = mk(B, H * W, 64), mk(B, H * W, 64)
+    p0, e2 = mk(B, H * W // 4, 64), mk(B, H * W // 4, 64)
+    p00, e3 = mk(B, H * W // 16, 64), mk(B, H * W // 16, 64)
+    dw_w, dw_b = mk(84, 1, 3, 3, sc=0.3), mk(84, sc=0.1)
+    pw_w, pw_b = mk(64, 84, sc=0.1), mk(64, sc=0.1)
+    ln_w = (1 + 0.1 * torch.randn(64, generator=g)).cuda().requires_grad_(True)
+    ln_b = mk(64, sc=0.1)
+    dout = torch.randn(B, H * W, 64, generator=g).cuda()
+    ins = [c0, p0, p00, e1, e2, e3, dw_w, dw_b, pw_w, pw_b, ln_w, ln_b]
+    D = [t.detach().double().requires_grad_(True) for t in ins]
+    from einops import rearrange
+    xs = []
+    for i, (s, f) in enumerate(((D[0], D[3]), (D[1], D[4]), (D[2], D[5]))):
+        x = f + F.leaky_relu(s, 0.01)
+        h, w = H // 2 ** i, W // 2 ** i
+        xs.append(rearrange(x, "b (h w) (c ch cw) -> b (h ch w cw) c", h=h, ch=2 ** i, cw=2 ** i))
+    cat = torch.cat(xs, dim=-1)
+    x = cat.transpose(1, 2).reshape(B, 84, H, W)
+    x = F.gelu(F.conv2d(x, D[6], D[7], padding=1, groups=84)).flatten(2).transpose(1, 2)
+    ref = F.layer_norm(F.linear(x, D[8], D[9]), (64,), D[10], D[11], 1e-5) + D[3]
+    ref.backward(dout.double())
+    out = ops.BottleneckFunction.apply(*ins, H, W)
+    assert rel(out, ref) < 1e-5
+    out.backward(dout)
+    names = "dc0 dp0 dp00 de1 de2 de3 d_dw_w d_dw_b d_pw_w d_pw_b d_ln_w d_ln_b".split()
+    for got, want, name in zip(ins, D, names):
+        assert rel(got.grad, want.grad) < 3e-5, (name, rel(got.grad, want.grad))

@@ -53,6 +53,7 @@ SIGNATURES = {
     "b200mar_mlp_tma_fwd": [_P] * 9 + [_L, _P],
     "b200mar_final_recon_bwd": [_P] * 19 + [_I] * 5 + [_P],
     "b200mar_cascade_proj_bwd": [_P] * 11 + [_I] * 3 + [_P],
+    "b200mar_bottleneck_bwd": [_P] * 23 + [_I] * 3 + [_P],
     "b200mar_shallow_tok_bwd": [_P] * 6 + [_I] * 3 + [_P],
     "b200mar_cast_stream": [_P, _P, _L, _I, _P],
     "b200mar_unigram_qkv_fwd_s16": [_P] * 6 + [_I] * 4 + [_P],

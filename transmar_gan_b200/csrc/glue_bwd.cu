@@ -374,6 +374,252 @@ __global__ void __launch_bounds__(kThreads, 1) cascade_proj_bwd_kernel(CascadeBw
   if (tid < 64) atomicAdd(p.db + tid, accB);
 }
 
+// ================================================================================================ bottleneck
+// Forward: cat [T, 84] = concat(e1 + leaky(c0), shuffle2(e2 + leaky(p0)), shuffle4(e3 + leaky(p00)));
+//          pre = depthwise3x3(cat) + b_dw; g = GELU(pre); y = W_pw g + b_pw; out = LN(y) + e1.
+// bottleneck_tail_bwd_kernel (one 8x8 spatial tile per pass, everything recomputed from the saved cat):
+//   LayerNorm backward of dout -> dy; d_ln_w += dout xhat, d_ln_b += dout; d_pw_b += dy; d_pw_w += dy^T g;
+//   ddwc = (dy W_pw) * GELU'(pre)  -> written to a [T, 84] scratch for the depthwise pass
+struct TailBwdSmem {
+  static constexpr int kLd = 132;                        // K = 84 padded to 128 (two 64-column chunks) + 4
+  static constexpr int oW = 0;                           // [64 n][132] pointwise weight (k >= 84 zero)
+  static constexpr int oDw = oW + 64 * kLd;              // [9][84] depthwise weight, tap-major
+  static constexpr int oDb = oDw + 9 * 84;               // [84]
+  static constexpr int oHalo = oDb + 84;                 // [100][84]
+  static constexpr int oPre = oHalo + 100 * 84;          // [64][132] pre-activation
+  static constexpr int oG = oPre + 64 * kLd;             // [64][132] GELU(pre)
+  static constexpr int oY = oG + 64 * kLd;               // [64][68]  y, then dy
+  static constexpr int kFloats = oY + 64 * kLd64;
+};
+struct TailBwdParams {
+  const float* cat; const float* dw_w; const float* dw_b; const float* pw_w; const float* pw_b;
+  const float* ln_w; const float* dout;
+  float* ddwc; float* d_pw_w; float* d_pw_b; float* d_ln_w; float* d_ln_b;
+  int B, H, W;
+};
+__global__ void __launch_bounds__(kThreads, 1) bottleneck_tail_bwd_kernel(TailBwdParams p) {
+  using L = TailBwdSmem;
+  extern __shared__ __align__(16) float smem[];
+  float* sW = smem + L::oW;
+  float* sDw = smem + L::oDw;
+  float* sDb = smem + L::oDb;
+  float* sHalo = smem + L::oHalo;
+  float* sPre = smem + L::oPre;
+  float* sG = smem + L::oG;
+  float* sY = smem + L::oY;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int idx = tid; idx < 64 * L::kLd; idx += kThreads) {
+    const int n = idx / L::kLd, k = idx - n * L::kLd;
+    sW[idx] = k < 84 ? p.pw_w[n * 84 + k] : 0.f;
+    sPre[idx] = 0.f;
+    sG[idx] = 0.f;                                       // pad columns stay zero
+  }
+  for (int idx = tid; idx < 9 * 84; idx += kThreads) sDw[idx] = p.dw_w[(idx % 84) * 9 + idx / 84];
+  for (int idx = tid; idx < 84; idx += kThreads) sDb[idx] = p.dw_b[idx];
+  float accW[2][4][4];
+  zero_acc(accW[0]); zero_acc(accW[1]);
+  float accB = 0.f, aLw0 = 0.f, aLw1 = 0.f, aLb0 = 0.f, aLb1 = 0.f;
+  const float g0 = p.ln_w[lane], g1 = p.ln_w[lane + 32];
+  const int th = p.H / 8, tw = p.W / 8;
+  const int ntile = p.B * th * tw;
+  for (int tile = blockIdx.x; tile < ntile; tile += gridDim.x) {
+    __syncthreads();
+    const int tx0 = (tile % tw) * 8, ty0 = ((tile / tw) % th) * 8, b = tile / (tw * th);
+    for (int idx = tid; idx < 100 * 21; idx += kThreads) {
+      const int hp = idx / 21, g = idx - hp * 21;
+      const int yy = ty0 + hp / 10 - 1, xx = tx0 + hp % 10 - 1;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (yy >= 0 && yy < p.H && xx >= 0 && xx < p.W)
+        v = ldg4(p.cat + (((long long)b * p.H + yy) * p.W + xx) * 84 + g * 4);
+      *reinterpret_cast<float4*>(sHalo + hp * 84 + g * 4) = v;
+    }
+    __syncthreads();
+    for (int idx = tid; idx < 64 * 84; idx += kThreads) {
+      const int t = idx / 84, c = idx - t * 84;
+      const int ty = t >> 3, tx = t & 7;
+      float a = sDb[c];
+#pragma unroll
+      for (int dy = 0; dy < 3; ++dy)
+#pragma unroll
+        for (int dx = 0; dx < 3; ++dx)
+          a = fmaf(sDw[(dy * 3 + dx) * 84 + c], sHalo[((ty + dy) * 10 + tx + dx) * 84 + c], a);
+      sPre[t * L::kLd + c] = a;
+      sG[t * L::kLd + c] = gelu_erf(a);
+    }
+    __syncthreads();
+    {                                                     // y = W_pw g + b_pw
+      float acc[4][4]; zero_acc(acc);
+      gemm64<false, false>(acc, sG, L::kLd, sW, L::kLd, 88);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int n = gemm_col<false>(j);
+        const float bias = __ldg(p.pw_b + n);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) sY[gemm_row<false>(i) * kLd64 + n] = acc[i][j] + bias;
+      }
+    }
+    __syncthreads();
+    // LayerNorm backward, one warp per token row; dy overwrites y in place
+#pragma unroll 1
+    for (int rr = 0; rr < 8; ++rr) {
+      const int m = warp * 8 + rr;
+      const float y0 = sY[m * kLd64 + lane], y1 = sY[m * kLd64 + lane + 32];
+      const float mean = warp_sum(y0 + y1) * (1.0f / 64.f);
+      const float d0 = y0 - mean, d1 = y1 - mean;
+      const float rstd = 1.0f / sqrtf(warp_sum(d0 * d0 + d1 * d1) * (1.0f / 64.f) + kLnEps);
+      const float xh0 = d0 * rstd, xh1 = d1 * rstd;
+      const long long tok = (((long long)b * p.H + ty0 + (m >> 3)) * p.W + tx0 + (m & 7)) * 64;
+      const float o0 = __ldg(p.dout + tok + lane), o1 = __ldg(p.dout + tok + lane + 32);
+      aLw0 = fmaf(o0, xh0, aLw0); aLw1 = fmaf(o1, xh1, aLw1); aLb0 += o0; aLb1 += o1;
+      const float dx0 = o0 * g0, dx1 = o1 * g1;
+      const float m1 = warp_sum(dx0 + dx1) * (1.0f / 64.f);
+      const float m2 = warp_sum(dx0 * xh0 + dx1 * xh1) * (1.0f / 64.f);
+      sY[m * kLd64 + lane] = rstd * (dx0 - m1 - xh0 * m2);
+      sY[m * kLd64 + lane + 32] = rstd * (dx1 - m1 - xh1 * m2);
+    }
+    __syncthreads();
+    if (tid < 64) {
+      float s2 = 0.f;
+#pragma unroll 8
+      for (int i = 0; i < 64; ++i) s2 += sY[i * kLd64 + tid];
+      accB += s2;
+    }
+#pragma unroll 1
+    for (int q = 0; q < 2; ++q) {
+      gemm64<true, true>(accW[q], sY, kLd64, sG + q * 64, L::kLd, 64);       // d_pw_w[n][q*64 + k]
+      float acc[4][4]; zero_acc(acc);
+      gemm64<false, true>(acc, sY, kLd64, sW + q * 64, L::kLd, 64);          // dg[i][q*64 + k]
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int m = gemm_row<false>(i);
+        const long long tok = ((long long)b * p.H + ty0 + (m >> 3)) * p.W + tx0 + (m & 7);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int k = q * 64 + gemm_col<true>(j);
+          if (k < 84) p.ddwc[tok * 84 + k] = acc[i][j] * gelu_erf_grad(sPre[m * L::kLd + k]);
+        }
+      }
+    }
+  }
+  for (int q = 0; q < 2; ++q)
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int k = q * 64 + gemm_col<true>(j);
+        if (k < 84) atomicAdd(p.d_pw_w + gemm_row<true>(i) * 84 + k, accW[q][i][j]);
+      }
+  if (tid < 64) atomicAdd(p.d_pw_b + tid, accB);
+  // LayerNorm affine gradients: lanes hold channels (lane, lane + 32); reduce over the 8 warps through smem
+  __syncthreads();
+  float* red = sY;                                        // [8 warps][4][32]
+  red[(warp * 4 + 0) * 32 + lane] = aLw0; red[(warp * 4 + 1) * 32 + lane] = aLw1;
+  red[(warp * 4 + 2) * 32 + lane] = aLb0; red[(warp * 4 + 3) * 32 + lane] = aLb1;
+  __syncthreads();
+  if (tid < 128) {
+    const int which = tid >> 5, l = tid & 31;
+    float s2 = 0.f;
+#pragma unroll
+    for (int wv = 0; wv < 8; ++wv) s2 += red[(wv * 4 + which) * 32 + l];
+    float* dst = which < 2 ? p.d_ln_w : p.d_ln_b;
+    atomicAdd(dst + l + 32 * (which & 1), s2);
+  }
+}
+
+// bottleneck_dw_bwd_kernel (one 8x8 tile per pass, halos of ddwc and of cat):
+//   dcat[t][c] = sum_k ddwc[t - off_k][c] w_dw[c][k];  d_dw_w[c][k] += sum_t ddwc[t][c] cat[t + off_k][c];  d_dw_b += ddwc
+//   then the concat / pixel-shuffle / LeakyReLU skips backwards:
+//     c < 64        : de1[t][c] = dcat + dout[t][c] (the tail's "+ e1"),  dc0[t][c] = dcat leaky'(c0[t][c])
+//     64 <= c < 80  : source (lo = (y/2, x/2), k = ((c-64)*2 + y%2)*2 + x%2): de2[lo][k] = dcat, dp0[lo][k] = dcat leaky'(p0)
+//     80 <= c < 84  : source (lo = (y/4, x/4), k = ((c-80)*4 + y%4)*4 + x%4): de3, dp00 likewise
+struct DwBwdParams {
+  const float* cat; const float* ddwc; const float* dw_w; const float* dout;
+  const float* c0; const float* p0; const float* p00;
+  float* dc0; float* dp0; float* dp00; float* de1; float* de2; float* de3;
+  float* d_dw_w; float* d_dw_b;
+  int B, H, W;
+};
+__global__ void __launch_bounds__(kThreads, 1) bottleneck_dw_bwd_kernel(DwBwdParams p) {
+  extern __shared__ __align__(16) float smem[];
+  float* sDw = smem;                      // [9][84]
+  float* sC = sDw + 9 * 84;               // [100][84] cat halo
+  float* sD = sC + 100 * 84;              // [100][84] ddwc halo
+  float* sRed = sD + 100 * 84;            // [3][84][10]
+  const int tid = threadIdx.x;
+  for (int idx = tid; idx < 9 * 84; idx += kThreads) sDw[idx] = p.dw_w[(idx % 84) * 9 + idx / 84];
+  float acc[10];
+#pragma unroll
+  for (int k = 0; k < 10; ++k) acc[k] = 0.f;
+  const int th = p.H / 8, tw = p.W / 8;
+  const int ntile = p.B * th * tw;
+  const int cmine = tid % 84, grp = tid / 84;            // threads 0..251: (group of tokens, channel)
+  for (int tile = blockIdx.x; tile < ntile; tile += gridDim.x) {
+    __syncthreads();
+    const int tx0 = (tile % tw) * 8, ty0 = ((tile / tw) % th) * 8, b = tile / (tw * th);
+    for (int idx = tid; idx < 100 * 21; idx += kThreads) {
+      const int hp = idx / 21, g = idx - hp * 21;
+      const int yy = ty0 + hp / 10 - 1, xx = tx0 + hp % 10 - 1;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f), d = v;
+      if (yy >= 0 && yy < p.H && xx >= 0 && xx < p.W) {
+        const long long o = (((long long)b * p.H + yy) * p.W + xx) * 84 + g * 4;
+        v = ldg4(p.cat + o);
+        d = ldg4(p.ddwc + o);
+      }
+      *reinterpret_cast<float4*>(sC + hp * 84 + g * 4) = v;
+      *reinterpret_cast<float4*>(sD + hp * 84 + g * 4) = d;
+    }
+    __syncthreads();
+    if (grp < 3) {                                        // depthwise weight / bias gradients
+      for (int t = grp; t < 64; t += 3) {
+        const int ty = t >> 3, tx = t & 7;
+        const float d = sD[((ty + 1) * 10 + tx + 1) * 84 + cmine];
+#pragma unroll
+        for (int dy = 0; dy < 3; ++dy)
+#pragma unroll
+          for (int dx = 0; dx < 3; ++dx)
+            acc[dy * 3 + dx] = fmaf(d, sC[((ty + dy) * 10 + tx + dx) * 84 + cmine], acc[dy * 3 + dx]);
+        acc[9] += d;
+      }
+    }
+    for (int idx = tid; idx < 64 * 84; idx += kThreads) {
+      const int t = idx / 84, c = idx - t * 84;
+      const int ty = t >> 3, tx = t & 7;
+      float g = 0.f;
+#pragma unroll
+      for (int dy = 0; dy < 3; ++dy)
+#pragma unroll
+        for (int dx = 0; dx < 3; ++dx)      // dcat[t] += ddwc[t - off_k] w[k], off_k = (dy-1, dx-1)
+          g = fmaf(sD[((ty + 2 - dy) * 10 + tx + 2 - dx) * 84 + c], sDw[(dy * 3 + dx) * 84 + c], g);
+      const int yy = ty0 + ty, xx = tx0 + tx;
+      if (c < 64) {
+        const long long o = (((long long)b * p.H + yy) * p.W + xx) * 64 + c;
+        p.de1[o] = g + __ldg(p.dout + o);
+        p.dc0[o] = __ldg(p.c0 + o) > 0.f ? g : 0.01f * g;
+      } else if (c < 80) {
+        const int k = (((c - 64) * 2 + (yy & 1)) * 2) + (xx & 1);
+        const long long o = (((long long)b * (p.H / 2) + yy / 2) * (p.W / 2) + xx / 2) * 64 + k;
+        p.de2[o] = g;
+        p.dp0[o] = __ldg(p.p0 + o) > 0.f ? g : 0.01f * g;
+      } else {
+        const int k = (((c - 80) * 4 + (yy & 3)) * 4) + (xx & 3);
+        const long long o = (((long long)b * (p.H / 4) + yy / 4) * (p.W / 4) + xx / 4) * 64 + k;
+        p.de3[o] = g;
+        p.dp00[o] = __ldg(p.p00 + o) > 0.f ? g : 0.01f * g;
+      }
+    }
+  }
+  __syncthreads();
+  if (grp < 3)
+#pragma unroll
+    for (int k = 0; k < 10; ++k) sRed[(grp * 84 + cmine) * 10 + k] = acc[k];
+  __syncthreads();
+  for (int idx = tid; idx < 84 * 10; idx += kThreads) {
+    const int c = idx / 10, k = idx - c * 10;
+    const float s2 = sRed[(0 * 84 + c) * 10 + k] + sRed[(1 * 84 + c) * 10 + k] + sRed[(2 * 84 + c) * 10 + k];
+    if (k < 9) atomicAdd(p.d_dw_w + c * 9 + k, s2); else atomicAdd(p.d_dw_b + c, s2);
+  }
+}
+
 }  // namespace b200mar
 
 using namespace b200mar;
@@ -424,6 +670,33 @@ extern "C" int b200mar_cascade_proj_bwd(const float* srcA, const float* srcB, co
   const long long ntile = ((long long)B * h * wd + 63) / 64;
   const int grid = (int)(ntile < sm_count() ? ntile : sm_count());
   cascade_proj_bwd_kernel<<<grid, kThreads, smem, (cudaStream_t)stream>>>(p);
+  B200MAR_CHECK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int b200mar_bottleneck_bwd(const float* cat, const float* dout, const float* c0, const float* p0,
+                                      const float* p00, const float* dw_w, const float* dw_b, const float* pw_w,
+                                      const float* pw_b, const float* ln_w, float* ddwc_scratch, float* dc0,
+                                      float* dp0, float* dp00, float* de1, float* de2, float* de3, float* d_dw_w,
+                                      float* d_dw_b, float* d_pw_w, float* d_pw_b, float* d_ln_w, float* d_ln_b,
+                                      int B, int H, int W, void* stream) {
+  if (B <= 0 || H % 8 || W % 8 || H <= 0 || W <= 0) return -1;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int ntile = B * (H / 8) * (W / 8);
+  const int grid = ntile < 2 * sm_count() ? ntile : 2 * sm_count();
+  static DeviceOnce configured;
+  const size_t smem1 = TailBwdSmem::kFloats * sizeof(float);
+  const size_t smem2 = (size_t)(9 * 84 + 2 * 100 * 84 + 3 * 84 * 10) * sizeof(float);
+  if (configured.first()) {
+    B200MAR_CHECK(cudaFuncSetAttribute(bottleneck_tail_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
+    B200MAR_CHECK(cudaFuncSetAttribute(bottleneck_dw_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+    configured.done();
+  }
+  TailBwdParams t{cat, dw_w, dw_b, pw_w, pw_b, ln_w, dout, ddwc_scratch, d_pw_w, d_pw_b, d_ln_w, d_ln_b, B, H, W};
+  bottleneck_tail_bwd_kernel<<<grid, kThreads, smem1, st>>>(t);
+  B200MAR_CHECK(cudaGetLastError());
+  DwBwdParams d{cat, ddwc_scratch, dw_w, dout, c0, p0, p00, dc0, dp0, dp00, de1, de2, de3, d_dw_w, d_dw_b, B, H, W};
+  bottleneck_dw_bwd_kernel<<<grid, kThreads, smem2, st>>>(d);
   B200MAR_CHECK(cudaGetLastError());
   return 0;
 }

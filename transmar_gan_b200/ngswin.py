@@ -11,9 +11,9 @@ What runs where
   * CUDA kernels (this repo): unigram conv, n-gram context attention, fused shifted-window
     partition + cosine attention + LN1 + residual, fused MLP + LN2 + residual(+within-stage
     sum), PatchMerging, pixel-shuffle + concat — forward and backward.
-  * stock PyTorch/cuDNN inside the drop-in's TRAINING path:
-    shallow 3x3 conv, max-pools, cascade projections, bottleneck depthwise conv / pointwise linear and
-    the two reconstruction convs (their LayerNorms run on ln64.cu; inference fuses all of this glue).
+  * the glue between the stages (shallow conv, InterPool + cascade projections, SCDPBottleneck, final LayerNorm +
+    skip + Reconstruction): fused channels-last kernels too, forward (glue_fwd.cu, *_tc.cu) and backward
+    (glue_bwd.cu); the stock nn.Conv2d / nn.Linear / nn.LayerNorm submodules only hold the parameters.
 There is NO CPU forward: calling the module on CPU tensors raises.
 """
 from __future__ import annotations
@@ -463,22 +463,30 @@ class NGswin(nn.Module):
                                "(stage 3 must have 2x2 windows; the reference raises too)")
         if not torch.is_grad_enabled():
             return self._forward_fused(x.float().contiguous(), H0, W0)
-        # stock-PyTorch glue of the training path, kept channels-last / token-major end to end
-        shallow = self.shallow_extract(x.float().contiguous(memory_format=torch.channels_last))
-        c0 = shallow.permute(0, 2, 3, 1).reshape(B, H * W, self.embed_dim).contiguous()   # [B, HW, 64]
+        return self._forward_train(x.float().contiguous(), H0, W0)
+
+    def _forward_train(self, x, H0, W0):
+        """Training path (autograd on): the same fused channels-last glue kernels as the inference path, each wrapped
+        in an autograd Function with a hand-written backward (glue_bwd.cu) - no stock PyTorch / cuDNN op is left
+        between the input image and the output image."""
+        B, _, H, W = x.shape
+        se = self.shallow_extract.conv1
+        l2, l3, bn, tt = self.encoder_layer2, self.encoder_layer3, self.bottleneck, self.to_target
+        c0 = ops.ShallowTokFunction.apply(x, se.weight, se.bias)
         e1_, e1, np1 = self.encoder_layer1(c0, (H, W))
-        p0 = _token_maxpool(c0, H, W)
-        c1 = torch.cat([p0, e1], dim=-1)
-        e2_, e2, np2 = self.encoder_layer2(c1, np1)
-        pc1 = _token_maxpool(c1, *np1)                           # [maxpool4(c0) | maxpool2(e1)]
-        c2 = torch.cat([pc1, e2], dim=-1)
-        e3_, _, _ = self.encoder_layer3(c2, np2)
-        bt = self.bottleneck((c0, p0, pc1[..., :self.embed_dim]), [e1_, e2_, e3_], H, W)
-        dec = self.decoder_layer1(bt + e1_, (H, W))
-        dec = ops.LayerNorm64Function.apply(dec, self.norm.weight, self.norm.bias) + c0   # global skip (ngswin.py:204)
-        img = dec.view(B, H, W, self.dec_dim).permute(0, 3, 1, 2)                 # NCHW view of NHWC memory
-        out = self.to_target(img)
-        return out[:, :, :H0, :W0]
+        x2, p0 = ops.CascadeProjFunction.apply(c0, None, e1, l2.across_cascade_proj.weight,
+                                               l2.across_cascade_proj.bias, H // 2, W // 2)
+        e2_, e2, np2 = l2(x2, np1, projected=True)
+        x3, p00 = ops.CascadeProjFunction.apply(p0, e1, e2, l3.across_cascade_proj.weight,
+                                                l3.across_cascade_proj.bias, H // 4, W // 4)
+        e3_, _, _ = l3(x3, np2, projected=True)
+        dec_in = ops.BottleneckFunction.apply(c0, p0, p00, e1_, e2_, e3_, bn.depthwise.weight, bn.depthwise.bias,
+                                              bn.pointwise.weight, bn.pointwise.bias, bn.norm.weight, bn.norm.bias,
+                                              H, W)
+        dec = self.decoder_layer1(dec_in, (H, W))
+        return ops.FinalReconFunction.apply(dec, c0, self.norm.weight, self.norm.bias, tt.before_shuffle.weight,
+                                            tt.before_shuffle.bias, tt.to_origin.weight, tt.to_origin.bias,
+                                            H, W, H0, W0)
 
     def _forward_fused(self, x, H0, W0):
         """Inference path (no autograd): the glue between the stages runs as fused channels-last

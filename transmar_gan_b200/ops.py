@@ -582,12 +582,17 @@ def bottleneck_fwd(c0: Tensor, p0: Tensor, p00: Tensor, e1: Tensor, e2: Tensor, 
     """SCDPBottleneck + the decoder-input add: returns bottleneck(shallow, [e1,e2,e3]) + e1."""
     _chk(c0, p0, p00, e1, e2, e3, dw_w, dw_b, pw_w, pw_b, ln_w, ln_b)
     B = c0.shape[0]
+    return _bottleneck_fwd_cat(c0, p0, p00, e1, e2, e3, dw_w, dw_b, pw_w, pw_b, ln_w, ln_b, H, W)[0]
+
+
+def _bottleneck_fwd_cat(c0, p0, p00, e1, e2, e3, dw_w, dw_b, pw_w, pw_b, ln_w, ln_b, H, W):
+    B = c0.shape[0]
     cat = torch.empty((B, H * W, 84), device=c0.device, dtype=torch.float32)
     _call("bottleneck_cat_fwd", _p(c0), _p(p0), _p(p00), _p(e1), _p(e2), _p(e3), _p(cat), B, H, W, _stream())
     out = torch.empty_like(c0)
     _call("bottleneck_tail_tc_fwd" if _tc() else "bottleneck_tail_fwd", _p(cat), _p(dw_w), _p(dw_b), _p(pw_w), _p(pw_b), _p(ln_w), _p(ln_b),
           _p(e1), _p(out), B, H, W, _stream())
-    return out
+    return out, cat
 
 
 def final_recon_fwd(dec: Tensor, c0: Tensor, ln_w: Tensor, ln_b: Tensor, w1: Tensor, b1: Tensor,
@@ -660,6 +665,38 @@ class CascadeProjFunction(torch.autograd.Function):
         _call("cascade_proj_bwd", _p(srcA), _p(srcB), _p(direct), _p(w.detach()), _p(dout), _p(dpool), _p(d_srcA),
               _p(d_srcB), _p(d_direct), _p(G[0]), _p(G[1]), B, h, wd, _stream())
         return (d_srcA, d_srcB, d_direct, *((None, None) if fused else G), None, None)
+
+
+class BottleneckFunction(torch.autograd.Function):
+    """dec_in = apply(c0, p0, p00, e1, e2, e3, dw_w, dw_b, pw_w, pw_b, ln_w, ln_b, H, W): SCDPBottleneck (skips,
+    pixel-shuffle, concat, depthwise 3x3, GELU, pointwise, LN) + e1 on the fused kernels, with its backward."""
+
+    @staticmethod
+    def forward(ctx_, c0, p0, p00, e1, e2, e3, dw_w, dw_b, pw_w, pw_b, ln_w, ln_b, H, W):
+        acts = [t.contiguous() for t in (c0, p0, p00, e1, e2, e3)]
+        P = [t.detach() for t in (dw_w, dw_b, pw_w, pw_b, ln_w, ln_b)]
+        _chk(*acts, *P)
+        out, cat = _bottleneck_fwd_cat(*acts, *P, H, W)
+        ctx_.save_for_backward(cat, acts[0], acts[1], acts[2], dw_w, dw_b, pw_w, pw_b, ln_w, ln_b)
+        ctx_.geom = (H, W)
+        return out
+
+    @staticmethod
+    def backward(ctx_, dout):
+        cat, c0, p0, p00, dw_w, dw_b, pw_w, pw_b, ln_w, ln_b = ctx_.saved_tensors
+        H, W = ctx_.geom
+        B = c0.shape[0]
+        dout = dout.contiguous()
+        G, fused = _acc((dw_w, dw_b, pw_w, pw_b, ln_w, ln_b))
+        ddwc = torch.empty_like(cat)
+        dc0, dp0, dp00 = torch.empty_like(c0), torch.empty_like(p0), torch.empty_like(p00)
+        de1, de2, de3 = torch.empty_like(c0), torch.empty_like(p0), torch.empty_like(p00)
+        _chk(cat, dout, c0, p0, p00, ddwc, dc0, dp0, dp00, de1, de2, de3, *G)
+        _call("bottleneck_bwd", _p(cat), _p(dout), _p(c0), _p(p0), _p(p00), _p(dw_w.detach()), _p(dw_b.detach()),
+              _p(pw_w.detach()), _p(pw_b.detach()), _p(ln_w.detach()), _p(ddwc), _p(dc0), _p(dp0), _p(dp00),
+              _p(de1), _p(de2), _p(de3), *[_p(g) for g in G], B, H, W, _stream())
+        profile.launches += 1
+        return (dc0, dp0, dp00, de1, de2, de3, *(([None] * 6) if fused else G), None, None)
 
 
 class FinalReconFunction(torch.autograd.Function):

@@ -38,24 +38,6 @@ def _fused_acc():
     return ops.fused_grad_accumulation(True)
 
 
-class _glue_tf32:
-    """While the block kernels compute with 11-bit-significand operands on the tensor cores (precision "tf32" /
-    "auto"), the stock-PyTorch Linear layers of the training-path glue (cascade projections, bottleneck
-    pointwise) may do the same: torch's fp32 SIMT GEMMs are replaced by its TF32 tensor-core ones for the
-    forward and backward of the step.  Precision "fp32" leaves torch's flag alone."""
-
-    def __enter__(self):
-        from . import ops
-        self.prev = torch.backends.cuda.matmul.allow_tf32
-        if ops.get_precision() != "fp32":
-            torch.backends.cuda.matmul.allow_tf32 = True
-        return self
-
-    def __exit__(self, *exc):
-        torch.backends.cuda.matmul.allow_tf32 = self.prev
-        return False
-
-
 def _calibrate(model):
     """Precision "auto": the per-unit plan is measured now - a CUDA-graph capture freezes whatever plan is in
     force (NGswin re-measures it every AUTO_RECALIBRATE_EVERY eager training forwards, never during replay)."""
@@ -83,10 +65,9 @@ class L1TrainStep:
     # -- the recipe -----------------------------------------------------------------------
     def _fwd_bwd(self, x, t):
         self.bucket.zero()
-        with _glue_tf32():
-            loss = F.l1_loss(self.model(x), t)
-            with _fused_acc():             # block kernels add their parameter gradients into the flat bucket
-                loss.backward()
+        loss = F.l1_loss(self.model(x), t)
+        with _fused_acc():                 # the kernels add their parameter gradients into the flat bucket
+            loss.backward()
         return loss.detach()
 
     def _eager(self, x, t):
@@ -203,8 +184,7 @@ class GANTrainStep:
     def _d_fwd_bwd(self, ct, real):
         self.bucketD.zero()
         if self.reuse_fake:
-            with _glue_tf32():
-                self._fake = self.netG(ct)         # with grad: the G step below backpropagates through it
+            self._fake = self.netG(ct)             # with grad: the G step below backpropagates through it
             fake = self._fake.detach()
         else:
             with torch.no_grad():
@@ -222,8 +202,7 @@ class GANTrainStep:
         for p in self.bucketD.params:
             p.requires_grad_(False)
         try:
-            with _glue_tf32():
-                fake = self._fake if self.reuse_fake else self.netG(ct)
+            fake = self._fake if self.reuse_fake else self.netG(ct)
             self._fake = None
             fake_logits, fake_feats = self.netD(torch.cat([ct, fake], 1), return_features=True)
             with torch.no_grad():
@@ -247,7 +226,7 @@ class GANTrainStep:
             if self.projector is not None and self.lambda_phys != 0.0:
                 M = gan.extract_metal_mask(ct, mt["threshold"])
                 loss = loss + self.lambda_phys * gan.physics_loss_syn(fake, real, M, self.projector)
-            with _fused_acc(), _glue_tf32():
+            with _fused_acc():
                 loss.backward()
         finally:
             for p in self.bucketD.params:
