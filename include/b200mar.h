@@ -205,14 +205,14 @@ int b200mar_final_recon_bwd(const float* dy, const float* y, const float* taps, 
                             const float* b1, const float* w2, float* g1_scratch, float* ddec, float* dc0,
                             float* d_ln_w, float* d_ln_b, float* d_w1, float* d_b1, float* d_w2,
                             float* d_b2, int B, int H, int W, int H0, int W0, void* stream);
-/* cascade_proj_bwd: backward of b200mar_cascade_proj_fwd / _tc_fwd (components/pooling.py:13-17 InterPool with
+/* cascade_proj_bwd: backward of the cascade_proj forward, fp32 or tcgen05 (components/pooling.py:13-17 InterPool with
  *   nn.MaxPool2d's first-maximum routing, models/generator/ngswin.py:175-178, encoder_decoder.py:117,136): dout
  *   [B*h*wd, 64]; dpool (may be NULL) = gradient arriving on the returned poolA; d_srcA / d_srcB [B*4*h*wd, 64] and
  *   d_direct [B*h*wd, 64] written; dw [64, K], db [64] accumulated (K = 128 without srcB, 192 with).                */
 int b200mar_cascade_proj_bwd(const float* srcA, const float* srcB, const float* direct, const float* w,
                              const float* dout, const float* dpool, float* d_srcA, float* d_srcB,
                              float* d_direct, float* dw, float* db, int B, int h, int wd, void* stream);
-/* bottleneck_bwd: backward of b200mar_bottleneck_cat_fwd + b200mar_bottleneck_tail(_tc)_fwd (SCDPBottleneck,
+/* bottleneck_bwd: backward of the bottleneck_cat + bottleneck_tail (fp32 or tcgen05) forward pair (SCDPBottleneck,
  *   components/encoder_decoder.py:159-164,188-200; BottleneckPool pooling.py:32-37; the "+ e1" of ngswin.py:189):
  *   cat [B*H*W, 84] as written by the forward, dout [B*H*W, 64]; ddwc_scratch [B*H*W, 84] floats;
  *   dc0, de1 [B*H*W, 64], dp0, de2 [B*H*W/4, 64], dp00, de3 [B*H*W/16, 64] written (de1 includes dout, the tail's
