@@ -381,15 +381,19 @@ __global__ void __launch_bounds__(kThreads, 1) cascade_proj_bwd_kernel(CascadeBw
 //   LayerNorm backward of dout -> dy; d_ln_w += dout xhat, d_ln_b += dout; d_pw_b += dy; d_pw_w += dy^T g;
 //   ddwc = (dy W_pw) * GELU'(pre)  -> written to a [T, 84] scratch for the depthwise pass
 struct TailBwdSmem {
-  static constexpr int kLd = 132;                        // K = 84 padded to 128 (two 64-column chunks) + 4
-  static constexpr int oW = 0;                           // [64 n][132] pointwise weight (k >= 84 zero)
-  static constexpr int oDw = oW + 64 * kLd;              // [9][84] depthwise weight, tap-major
+  // K = 84: the 64-column chunk 1 of a row reads columns 64..127, i.e. up to 28 floats into the NEXT row (stride 100)
+  // - harmless: those products land in output columns k >= 100, which are never used; kSlack keeps the last row's
+  // over-read inside the allocation.  105 KB in all: two CTAs per SM.
+  static constexpr int kLd = 100, kSlack = 32;
+  static constexpr int oW = 0;                           // [64 n][100] pointwise weight (k >= 84 zero)
+  static constexpr int oDw = oW + 64 * kLd + kSlack;     // [9][84] depthwise weight, tap-major
   static constexpr int oDb = oDw + 9 * 84;               // [84]
-  static constexpr int oHalo = oDb + 84;                 // [100][84]
-  static constexpr int oPre = oHalo + 100 * 84;          // [64][132] pre-activation
-  static constexpr int oG = oPre + 64 * kLd;             // [64][132] GELU(pre)
-  static constexpr int oY = oG + 64 * kLd;               // [64][68]  y, then dy
+  static constexpr int oHalo = oDb + 84;                 // [100][84] cat halo; ALIASED by the pre-activation tile
+  static constexpr int oPre = oHalo;                     // [64][100] pre-activation (written after the halo is dead)
+  static constexpr int oG = oHalo + 100 * 84;            // [64][100] GELU(pre)
+  static constexpr int oY = oG + 64 * kLd + kSlack;      // [64][68]  y, then dy
   static constexpr int kFloats = oY + 64 * kLd64;
+  static_assert(100 * 84 >= 64 * kLd + kSlack, "the pre-activation tile must fit in the halo buffer");
 };
 struct TailBwdParams {
   const float* cat; const float* dw_w; const float* dw_b; const float* pw_w; const float* pw_b;
@@ -397,7 +401,7 @@ struct TailBwdParams {
   float* ddwc; float* d_pw_w; float* d_pw_b; float* d_ln_w; float* d_ln_b;
   int B, H, W;
 };
-__global__ void __launch_bounds__(kThreads, 1) bottleneck_tail_bwd_kernel(TailBwdParams p) {
+__global__ void __launch_bounds__(kThreads, 2) bottleneck_tail_bwd_kernel(TailBwdParams p) {
   using L = TailBwdSmem;
   extern __shared__ __align__(16) float smem[];
   float* sW = smem + L::oW;
@@ -408,10 +412,9 @@ __global__ void __launch_bounds__(kThreads, 1) bottleneck_tail_bwd_kernel(TailBw
   float* sG = smem + L::oG;
   float* sY = smem + L::oY;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  for (int idx = tid; idx < 64 * L::kLd; idx += kThreads) {
+  for (int idx = tid; idx < 64 * L::kLd + L::kSlack; idx += kThreads) {
     const int n = idx / L::kLd, k = idx - n * L::kLd;
-    sW[idx] = k < 84 ? p.pw_w[n * 84 + k] : 0.f;
-    sPre[idx] = 0.f;
+    sW[idx] = (n < 64 && k < 84) ? p.pw_w[n * 84 + k] : 0.f;
     sG[idx] = 0.f;                                       // pad columns stay zero
   }
   for (int idx = tid; idx < 9 * 84; idx += kThreads) sDw[idx] = p.dw_w[(idx % 84) * 9 + idx / 84];
@@ -434,7 +437,10 @@ __global__ void __launch_bounds__(kThreads, 1) bottleneck_tail_bwd_kernel(TailBw
       *reinterpret_cast<float4*>(sHalo + hp * 84 + g * 4) = v;
     }
     __syncthreads();
-    for (int idx = tid; idx < 64 * 84; idx += kThreads) {
+    float pre[21];                                        // 64 * 84 / 256 elements per thread, staged in registers:
+#pragma unroll                                            // the pre-activation tile overwrites the halo buffer
+    for (int e = 0; e < 21; ++e) {
+      const int idx = tid + e * kThreads;
       const int t = idx / 84, c = idx - t * 84;
       const int ty = t >> 3, tx = t & 7;
       float a = sDb[c];
@@ -443,8 +449,15 @@ __global__ void __launch_bounds__(kThreads, 1) bottleneck_tail_bwd_kernel(TailBw
 #pragma unroll
         for (int dx = 0; dx < 3; ++dx)
           a = fmaf(sDw[(dy * 3 + dx) * 84 + c], sHalo[((ty + dy) * 10 + tx + dx) * 84 + c], a);
-      sPre[t * L::kLd + c] = a;
-      sG[t * L::kLd + c] = gelu_erf(a);
+      pre[e] = a;
+    }
+    __syncthreads();                                      // every halo read is done
+#pragma unroll
+    for (int e = 0; e < 21; ++e) {
+      const int idx = tid + e * kThreads;
+      const int t = idx / 84, c = idx - t * 84;
+      sPre[t * L::kLd + c] = pre[e];
+      sG[t * L::kLd + c] = gelu_erf(pre[e]);
     }
     __syncthreads();
     {                                                     // y = W_pw g + b_pw
