@@ -84,11 +84,11 @@ def test_plan_w1_all_tensor_cores_w2_not(models):
         with torch.no_grad():
             models[kind](x)
     r1, r2, r3 = (models[k].precision_report for k in ("W1", "W2", "W3"))
-    assert r1["units_on_tensor_cores"] == r1["units"] == 21, r1
-    assert r2["err_all_tensor_core"] > r2["tol"] and r2["units_on_tensor_cores"] < 21, r2
+    assert r1["units_on_tensor_cores"] == r1["units"] == 41, r1
+    assert r2["err_all_tensor_core"] > r2["tol"] and r2["units_on_tensor_cores"] < 41, r2
     for r in (r1, r2, r3):
         assert r["err_plan"] <= r["tol"]
-    print(f"[auto] W3 plan: {r3['units_on_tensor_cores']}/21 units on tcgen05, probe err all-tc "
+    print(f"[auto] W3 plan: {r3['units_on_tensor_cores']}/41 units on tcgen05, probe err all-tc "
           f"{r3['err_all_tensor_core']:.2e}, plan {r3['err_plan']:.2e}")
 
 
@@ -114,7 +114,7 @@ def test_trained_like_weights_on_structured_input(T, models, golden_w3):
         T.ops.set_precision(old)
     err_forced = (yf - ref).abs().max().item()
     rep = models["W3"].precision_report
-    print(f"[auto] W3 phantom: default mode {err_auto:.2e} ({rep['units_on_tensor_cores']}/21 units on tcgen05), "
+    print(f"[auto] W3 phantom: default mode {err_auto:.2e} ({rep['units_on_tensor_cores']}/41 units on tcgen05), "
           f"all units forced onto tcgen05 {err_forced:.2e}")
     assert err_auto < GATE, (err_auto, rep)
     assert err_forced < 3e-3, err_forced
@@ -124,7 +124,9 @@ def test_mixed_plan_plumbing(models, golden_outputs):
     """A hand-made alternating plan (tcgen05 / fp32 units interleaved, glue on fp32) exercises every hand-over
     between the in-place tensor-core blocks and the out-of-place fp32 blocks."""
     m = models["W1"]
-    plan = ["tf32" if i % 2 == 0 else "fp32" for i in range(20)] + ["fp32"]
+    # 41 units: (attention, MLP) of each of the 20 blocks, then the glue; the pattern of period 3 exercises all four
+    # combinations per block (tc/tc, tc/fp32, fp32/tc, fp32/fp32) and their hand-overs
+    plan = ["tf32" if i % 3 != 1 else "fp32" for i in range(40)] + ["fp32"]
     for shape in SHAPES[:3]:
         x = O.synthetic_input(*shape, seed=999).cuda()
         with torch.no_grad():
@@ -159,10 +161,10 @@ def test_recalibrates_when_weights_change(T):
     x = O.synthetic_input(1, 64, 64, seed=999).cuda()
     with torch.no_grad():
         m(x)
-        assert m.precision_report["units_on_tensor_cores"] == 21
+        assert m.precision_report["units_on_tensor_cores"] == 41
         m.load_state_dict(O.synthetic_state_dict("W2", seed=1), strict=True)
         m(x)
-    assert m.precision_report["units_on_tensor_cores"] < 21
+    assert m.precision_report["units_on_tensor_cores"] < 41
 
 
 def test_training_in_default_precision_matches_reference_gradients(T, golden_w3):

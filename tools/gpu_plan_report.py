@@ -19,7 +19,7 @@ for kind in ("W1", "W3", "W2"):
     if kind == "W3":
         x = gold["phantom_in"].cuda()
         with torch.no_grad():
-            n = 21
+            n = 41
             m._set_plan(["fp32"] * n); ref = m._forward_planned(x)
             print("  fp32 kernels vs reference on phantom:", f"{(ref.cpu() - gold['phantom_out']).abs().max().item():.2e}")
             for u in range(n):

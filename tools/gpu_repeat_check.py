@@ -16,18 +16,18 @@ def rep(name, plan):
     a = run(plan); a_cpu = a.cpu(); junk = torch.full((64, 1024, 1024), float("nan"), device="cuda"); del junk
     b = run(plan); c = run(plan)
     print(f"{name:28s} diff12 {(a - b).abs().max().item():.3e} diff23 {(b - c).abs().max().item():.3e} nan {torch.isnan(a).any().item() or torch.isnan(b).any().item()}", flush=True)
-n = 21
+n = 41
 rep("all fp32", ["fp32"] * n)
 rep("all tf32", ["tf32"] * n)
-rep("alt A (even tf32), glue fp32", ["tf32" if i % 2 == 0 else "fp32" for i in range(20)] + ["fp32"])
-rep("alt B (odd tf32), glue tf32", ["fp32" if i % 2 == 0 else "tf32" for i in range(20)] + ["tf32"])
-rep("blocks fp32, glue tf32", ["fp32"] * 20 + ["tf32"])
-rep("blocks tf32, glue fp32", ["tf32"] * 20 + ["fp32"])
-A = ["tf32" if i % 2 == 0 else "fp32" for i in range(20)] + ["fp32"]
-B = ["fp32" if i % 2 == 0 else "tf32" for i in range(20)] + ["tf32"]
+rep("alt A (even tf32), glue fp32", ["tf32" if i % 2 == 0 else "fp32" for i in range(40)] + ["fp32"])
+rep("alt B (odd tf32), glue tf32", ["fp32" if i % 2 == 0 else "tf32" for i in range(40)] + ["tf32"])
+rep("blocks fp32, glue tf32", ["fp32"] * 40 + ["tf32"])
+rep("blocks tf32, glue fp32", ["tf32"] * 40 + ["fp32"])
+A = ["tf32" if i % 2 == 0 else "fp32" for i in range(40)] + ["fp32"]
+B = ["fp32" if i % 2 == 0 else "tf32" for i in range(40)] + ["tf32"]
 ya = run(A).cpu(); yb = run(B).cpu(); yb2 = run(B).cpu(); ya2 = run(A).cpu()
 print("test sequence: B vs B", (yb - yb2).abs().max().item(), "A vs A", (ya - ya2).abs().max().item())
-for u in range(21):
+for u in range(41):
     plan = list(B); plan[u] = "fp32" if plan[u] == "tf32" else "tf32"
     a = run(plan); b = run(plan)
     if not torch.equal(a, b):

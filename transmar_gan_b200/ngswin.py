@@ -108,7 +108,8 @@ class NSTB(nn.Module):
                  head_dim=None, mlp_ratio=2., qkv_bias=True):
         super().__init__()
         self.num_heads, self.shift_size = num_heads, shift_size
-        self._mode = None          # "tf32" / "fp32" assigned by NGswin's precision plan; None = the selected mode
+        # "tf32" / "fp32" per half, assigned by NGswin's precision plan; None = the selected mode
+        self._mode_attn = self._mode_mlp = None
         self.ngram_window_partition = NGramWindowPartition(dim, window_size, ngram, num_heads,
                                                            shift_size)
         self.attn = WindowAttention(dim, num_heads, window_size, head_dim, qkv_bias)
@@ -173,9 +174,9 @@ class _Stage(nn.Module):
         for i, blk in enumerate(self.blocks):
             last = i == n - 1
             want_zsum = (not last) or need_sum_last
-            with ops.precision_scope(blk._mode):
-                eff = ops.effective_precision()
-                if not torch.is_grad_enabled() and eff == "bf16":
+            with ops.unit_precision(blk._mode_attn, blk._mode_mlp):
+                ea, em = ops.unit_modes()
+                if not torch.is_grad_enabled() and ea == "bf16" and em == "bf16":
                     # precision mode "bf16": the stream lives in BF16 inside the stage (cast once at stage entry,
                     # which also makes it private; cast back once at stage exit)
                     if z.dtype != torch.bfloat16:
@@ -187,15 +188,18 @@ class _Stage(nn.Module):
                 else:
                     if z.dtype != torch.float32:
                         z, private = ops.cast_stream(z, torch.float32), True
-                    if not torch.is_grad_enabled() and eff == "tf32":
+                    if torch.is_grad_enabled() or (ea == "fp32" and em == "fp32"):
+                        out, zsum = blk(z, num_patches, want_out=last, want_zsum=want_zsum)
+                    elif ea == "fp32" or em == "fp32":
+                        out, zsum = ops.nstb_infer_mixed_(z, *num_patches, blk.num_heads, blk.shift_size, last,
+                                                          want_zsum, blk.kernel_params(), ea, em, private)
+                    else:
                         # the block adds its output into z (TMA reduce-add), so z must be private to this
                         # loop: the stage input is copied once, later blocks own the previous block's sum
                         if want_zsum and not private:
                             z = z.clone()
                         out, zsum = ops.nstb_infer_(z, *num_patches, blk.num_heads, blk.shift_size, last,
                                                     want_zsum, blk.kernel_params())
-                    else:
-                        out, zsum = blk(z, num_patches, want_out=last, want_zsum=want_zsum)
             private = True               # zsum is this loop's own tensor (fresh, or the private z updated)
             z = zsum
         if out is not None and out.dtype != torch.float32:
@@ -351,8 +355,8 @@ class NGswin(nn.Module):
 
     # ---------------------------------------------------------------- precision plan ("auto" mode)
     def _units(self):
-        """The 21 units a precision plan covers: the 20 NSTBs in execution order, then the stage glue
-        (PatchMerging, cascade projections, bottleneck) as one unit."""
+        """The 20 NSTBs in execution order.  A precision plan covers 41 units: (attention half, MLP half) of
+        every block, then the stage glue (PatchMerging, cascade projections, bottleneck) as one unit."""
         return [b for st in (self.encoder_layer1, self.encoder_layer2, self.encoder_layer3, self.decoder_layer1)
                 for b in st.blocks]
 
@@ -362,9 +366,13 @@ class NGswin(nn.Module):
 
     def _set_plan(self, plan):
         blocks = self._units()
-        for b, m in zip(blocks, plan[:len(blocks)] if plan else [None] * len(blocks)):
-            b._mode = m
-        self._glue_mode = plan[len(blocks)] if plan else None
+        for i, b in enumerate(blocks):
+            b._mode_attn = plan[2 * i] if plan else None
+            b._mode_mlp = plan[2 * i + 1] if plan else None
+        self._glue_mode = plan[2 * len(blocks)] if plan else None
+
+    def _get_plan(self):
+        return [m for b in self._units() for m in (b._mode_attn, b._mode_mlp)] + [getattr(self, "_glue_mode", None)]
 
     @torch.no_grad()
     def calibrate_precision(self, tol: float = 4e-4, size: int = 96, seed: int = 4242):
@@ -380,8 +388,8 @@ class NGswin(nn.Module):
         if not p0.is_cuda:
             raise RuntimeError("calibrate_precision: move the module to a B200 first (there is no CPU path)")
         x = _probe_slices(size, seed).to(p0.device)
-        n = len(self._units()) + 1
-        saved = [b._mode for b in self._units()] + [getattr(self, "_glue_mode", None)]
+        n = 2 * len(self._units()) + 1
+        saved = self._get_plan()
 
         def run(plan):
             self._set_plan(plan)

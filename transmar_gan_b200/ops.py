@@ -76,6 +76,39 @@ class precision_scope:
         return False
 
 
+# Per-block override of the two halves of an NSTB (attention unit, MLP unit), set by the model's precision plan
+# around each block: a trained weight set typically needs the fp32 kernels for ONE attention unit only.
+_UNIT: List[Tuple[Optional[str], Optional[str]]] = []
+
+
+class unit_precision:
+    """Context manager: inside, the attention half and the MLP half of an NSTB compute in `attn` / `mlp`
+    ("tf32" / "fp32"; None = the surrounding mode)."""
+
+    def __init__(self, attn: Optional[str], mlp: Optional[str]):
+        for m in (attn, mlp):
+            if m not in (None, "tf32", "fp32"):
+                raise ValueError("unit_precision takes 'tf32', 'fp32' or None")
+        self.modes = (attn, mlp)
+
+    def __enter__(self):
+        _UNIT.append(self.modes)
+        return self
+
+    def __exit__(self, *exc):
+        _UNIT.pop()
+        return False
+
+
+def unit_modes() -> Tuple[str, str]:
+    """(attention mode, MLP mode) a block launched NOW computes in."""
+    base = effective_precision()
+    if _UNIT:
+        a, m = _UNIT[-1]
+        return (a or base, m or base)
+    return (base, base)
+
+
 def _tc() -> bool:
     """Tensor-core kernels?  ("bf16" = the tensor-core kernels over a bf16 residual stream, inference only;
     with autograd it behaves as "tf32": the training path keeps the fp32 stream.)"""
@@ -830,6 +863,24 @@ def nstb_infer_(z: Tensor, ph: int, pw: int, nh: int, shift: int, want_out: bool
     return out, (z if want_zsum else out.new_empty(0))
 
 
+def nstb_infer_mixed_(z: Tensor, ph: int, pw: int, nh: int, shift: int, want_out: bool, want_zsum: bool,
+                      params, attn_mode: str, mlp_mode: str, private: bool) -> Tuple[Tensor, Tensor]:
+    """Inference form of one NSTB whose two halves run in different modes (precision plan).  z is updated in
+    place only when the MLP half runs on the tensor cores AND `private` says the caller owns z."""
+    P = [p.detach() for p in params]
+    c = ngram_ctx_infer(z, *P[0:10], ph, pw, nh)
+    if attn_mode == "fp32":
+        a = attn_fwd(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw, nh, shift)
+    else:
+        a = attn_tc_fwd(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw, nh, shift, True)
+    if mlp_mode == "fp32":
+        return mlp_fwd(a, z if want_zsum else None, P[18], P[19], P[20], P[21], P[22], P[23], want_out, want_zsum)
+    if want_zsum and not private:
+        z = z.clone()
+    out = mlp_tma_fwd_(a, z if want_zsum else None, P[18], P[19], P[20], P[21], P[22], P[23], want_out)
+    return out, (z if want_zsum else out.new_empty(0))
+
+
 class NSTBFunction(torch.autograd.Function):
     """One N-Gram Swin Transformer Block (components/transformer_blocks.py:114-120) plus the
     within-stage residual sum (components/encoder_decoder.py:138-141):
@@ -842,8 +893,10 @@ class NSTBFunction(torch.autograd.Function):
         P = [p.detach() for p in params]
         u = unigram_fwd(z, P[0], P[1], ph, pw)
         c = ngram_ctx_fwd(u, P[2], P[3], P[4], P[5], P[6], P[7], P[8], P[9], nh)
-        tc = ctx_.tc = _tc()                       # the backward runs in the mode the forward ran in
-        if tc:
+        ma, mm = unit_modes()                      # the backward runs in the modes the forward ran in
+        tc_a = ctx_.tc_attn = ma != "fp32"
+        tc_m = ctx_.tc_mlp = mm != "fp32"
+        if tc_a:
             # (attn_tc_fwd(residual=False) + mlp_tc_fwd(a_is_delta=True) moves the residual add into
             # the MLP kernel; measured on B200 it costs the MLP more than it saves the attention)
             if save:
@@ -852,16 +905,18 @@ class NSTBFunction(torch.autograd.Function):
             else:
                 a = attn_tc_fwd(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw, nh,
                                 shift, True)
+        else:
+            a = attn_fwd(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw, nh, shift)
+        if tc_m:
             # block tail on the TMA-fed kernel (2.5x the plain-load mlp_tc_fwd, bit-identical): z must
             # survive for the backward, so the within-stage sum is a copy of z that the kernel's bulk
             # reduce-add turns into z + out
             zsum = z.clone() if want_zsum else z.new_empty(0)
             out = mlp_tma_fwd_(a, zsum if want_zsum else None, P[18], P[19], P[20], P[21], P[22], P[23], want_out)
         else:
-            a = attn_fwd(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw, nh, shift)
             out, zsum = mlp_fwd(a, z if want_zsum else None, P[18], P[19], P[20], P[21], P[22], P[23],
                                 want_out, want_zsum)
-        ctx_.has_o16 = bool(save and tc)
+        ctx_.has_o16 = bool(save and tc_a)
         if ctx_.has_o16:
             ctx_.save_for_backward(z, u, c, a, o16, *params)
         elif save:
@@ -895,13 +950,13 @@ class NSTBFunction(torch.autograd.Function):
                 G.append(flat[off:off + n].view(p.shape))
                 off += n
         da = torch.empty_like(a)
-        (mlp_bwd_tc if ctx_.tc else mlp_bwd)(a, g, P[18:24], da, G[18:24])
+        (mlp_bwd_tc if ctx_.tc_mlp else mlp_bwd)(a, g, P[18:24], da, G[18:24])
         dz = torch.empty_like(z)
         dctx = torch.zeros_like(c)
         if o16 is not None:
             attn_bwd_tc(z, c, da, P[10:18], dz, dctx, G[10:18], ph, pw, nh, shift, o16)
         else:
-            (attn_bwd_tc if ctx_.tc else attn_bwd)(z, c, da, P[10:18], dz, dctx, G[10:18], ph, pw, nh, shift)
+            (attn_bwd_tc if ctx_.tc_attn else attn_bwd)(z, c, da, P[10:18], dz, dctx, G[10:18], ph, pw, nh, shift)
         du = torch.empty_like(u)
         ngram_ctx_bwd(u, dctx, P[2:10], du, G[2:10], nh)
         # dz = attention part + unigram part + gradient of the within-stage sum, in one pass
