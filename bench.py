@@ -540,9 +540,10 @@ def time_trained_like(args, world):
     torch.cuda.empty_cache()
     return {"slices_per_s": world * B * 1e3 / ms, "ms_per_step": ms,
             "units_on_tensor_cores": rep["units_on_tensor_cores"], "units": rep["units"],
-            "plan": "".join("T" if p == "tf32" else "f" for p in rep["plan"]),
+            "plan": "".join({"tf32": "T", "tf32c": "C"}.get(p, "f") for p in rep["plan"]),
             "probe_err_all_tensor_core": rep["err_all_tensor_core"], "probe_err_plan": rep["err_plan"],
-            "note": "W3 = trained-like weights; plan letters: T = tcgen05 kernels, f = fp32 FMA-pipe kernels, in "
+            "note": "W3 = trained-like weights; plan letters: T = tcgen05 kernels, C = tcgen05 with the compensated (fp16 hi + lo) qkv projection, "
+                    "f = fp32 FMA-pipe kernels, in "
                     "execution order: (attention half, MLP half) of each of the 20 NSTBs, then the glue"}
 
 

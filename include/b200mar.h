@@ -137,6 +137,17 @@ int b200mar_attn_tc_fwd_save(const float* z, const float* ctx,
                         const float* ln_w, const float* ln_b,
                         float* a, void* o16, int B, int ph, int pw, int nh, int shift,
                         void* stream);
+/* Precision level "tf32c" of the per-unit plan: as b200mar_attn_tc_fwd(residual = 1), or as
+ * b200mar_attn_tc_fwd_save when o16 != NULL, with the qkv projection (models/generator/components/attention.py:75)
+ * on compensated FP16 hi + lo operand pairs: X = Xh + Xl, W = Wh + Wl, Xh Wh + Xl Wh + Xh Wl accumulated in fp32,
+ * i.e. ~22 significant bits instead of 11; two workers per persistent CTA.                                    */
+int b200mar_attn_tc_fwd_comp(const float* z, const float* ctx,
+                        const float* qkv_w, const float* qkv_b,
+                        const float* proj_w, const float* proj_b,
+                        const float* logit_scale, const float* bias_table,
+                        const float* ln_w, const float* ln_b,
+                        float* a, void* o16 /* may be NULL */, int B, int ph, int pw, int nh, int shift,
+                        void* stream);
 /* residual = 1: a = z + LN1(attn) as above.  residual = 0: a = LN1(attn) only - the consumer
  * (b200mar_mlp_tc_fwd with a_is_delta = 1) adds z, which it reads anyway.                   */
 /* dz = da + scatter(dX) (overwrites dz); dctx += per-source-window sums of dX (dctx must be

@@ -15,7 +15,9 @@ for kind in ("W1", "W3", "W2"):
     print(kind, "all-tc probe err", f"{r['err_all_tensor_core']:.2e}")
     print("  marginal:", " ".join(f"{e:.1e}" for e in r["marginal_err"]))
     r = m.calibrate_precision()
-    print("  plan:", "".join("T" if p == "tf32" else "f" for p in r["plan"]), f"err {r['err_plan']:.2e}")
+    if r.get("marginal_err_compensated"):
+        print("  compensated marginal:", " ".join("-" if e is None else f"{e:.1e}" for e in r["marginal_err_compensated"]))
+    print("  plan:", "".join({"tf32": "T", "tf32c": "C"}.get(p, "f") for p in r["plan"]), f"err {r['err_plan']:.2e}")
     if kind == "W3":
         x = gold["phantom_in"].cuda()
         with torch.no_grad():

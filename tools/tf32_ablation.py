@@ -14,9 +14,11 @@ def split(x):  # hi + lo, both tf32
     hi = tf32(x); return hi, tf32(x - hi)
 
 MODE = {}
+BLOCK_MODE = {}        # attention prefix -> {gemm name: mode}, overrides MODE for that block's attention GEMMs
+_CUR = [None]
 def mm(name, a, b):
     """a @ b with the configured rounding: 0 exact, 1 tf32 both, 2 = 3-pass split (hi*hi+hi*lo+lo*hi), 3 = lo only on a, 4 = lo only on b"""
-    m = MODE.get(name, 0)
+    m = BLOCK_MODE.get(_CUR[0], {}).get(name, MODE.get(name, 0))
     if m == 0: return a @ b
     if m == 1: return tf32(a) @ tf32(b)
     ah, al = split(a); bh, bl = split(b)
@@ -27,6 +29,7 @@ def mm(name, a, b):
 def window_attention(x, p, prefix, num_heads, win, mask=None):
     if win != 8: return ORIG(x, p, prefix, num_heads, win, mask)
     B_, N, C = x.shape
+    _CUR[0] = prefix
     qkv = mm("qkv", x, p[prefix + "qkv.weight"].t()) + p[prefix + "qkv.bias"]
     qkv = qkv.reshape(B_, N, 3, num_heads, -1).permute(2, 0, 3, 1, 4)
     q, k, v = qkv[0], qkv[1], qkv[2]
@@ -42,7 +45,9 @@ def window_attention(x, p, prefix, num_heads, win, mask=None):
         attn = (attn.reshape(B_ // nW, nW, num_heads, N, N) + mask[None, :, None]).reshape(B_, num_heads, N, N)
     attn = attn.softmax(dim=-1)
     out = mm("pv", attn, v).transpose(1, 2).reshape(B_, N, -1)
-    return mm("proj", out, p[prefix + "proj.weight"].t()) + p[prefix + "proj.bias"]
+    y = mm("proj", out, p[prefix + "proj.weight"].t()) + p[prefix + "proj.bias"]
+    _CUR[0] = None
+    return y
 
 ORIG = O.window_attention
 O.window_attention = window_attention
@@ -55,28 +60,29 @@ def linear(x, w, b=None):
     return _lin(x, w, b)
 O.F.linear = linear
 
-import sys as _sys
-kinds = _sys.argv[1:] or ["W1", "W2"]
-for kind in kinds:
-    if kind == "W3":      # trained-like weights on the structured phantom they were fitted to
-        gold = torch.load(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden",
-                                       "w3_trained.pt"), weights_only=False)
-        sd, x = gold["state_dict"], gold["phantom_in"][:1]
-    else:
-        sd = O.synthetic_state_dict(kind, seed=1)
-        x = O.synthetic_input(1, 64, 64, seed=999)
-    with torch.no_grad():
-        MODE.clear(); ref = O.ngswin_forward(x, sd)
-        for cfg in ({"qkv": 1}, {"qk": 1}, {"pv": 1}, {"proj": 1}, {"fc1": 1}, {"fc2": 1},
-                    dict(qkv=1, qk=1, pv=1, proj=1, fc1=1, fc2=1),
-                    dict(qkv=2, qk=2, pv=2, proj=2, fc1=2, fc2=2),
-                    dict(qkv=2, qk=1, pv=1, proj=1, fc1=1, fc2=1),
-                    dict(qkv=2, qk=2, pv=1, proj=1, fc1=1, fc2=1),
-                    dict(qkv=1, qk=1, pv=1, proj=1, fc1=2, fc2=2),
-                    dict(qkv=2, qk=2, pv=2, proj=2, fc1=1, fc2=1),
-                    dict(qkv=3, qk=1, pv=1, proj=1, fc1=1, fc2=1),
-                    dict(qkv=4, qk=1, pv=1, proj=1, fc1=1, fc2=1),
-                    dict(qkv=3, qk=3, pv=1, proj=1, fc1=1, fc2=1)):
-            MODE.clear(); MODE.update(cfg)
-            y = O.ngswin_forward(x, sd)
-            print(kind, cfg, f"max-abs {(y - ref).abs().max().item():.2e}", flush=True)
+if __name__ == "__main__":
+    import sys as _sys
+    kinds = _sys.argv[1:] or ["W1", "W2"]
+    for kind in kinds:
+        if kind == "W3":      # trained-like weights on the structured phantom they were fitted to
+            gold = torch.load(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden",
+                                           "w3_trained.pt"), weights_only=False)
+            sd, x = gold["state_dict"], gold["phantom_in"][:1]
+        else:
+            sd = O.synthetic_state_dict(kind, seed=1)
+            x = O.synthetic_input(1, 64, 64, seed=999)
+        with torch.no_grad():
+            MODE.clear(); ref = O.ngswin_forward(x, sd)
+            for cfg in ({"qkv": 1}, {"qk": 1}, {"pv": 1}, {"proj": 1}, {"fc1": 1}, {"fc2": 1},
+                        dict(qkv=1, qk=1, pv=1, proj=1, fc1=1, fc2=1),
+                        dict(qkv=2, qk=2, pv=2, proj=2, fc1=2, fc2=2),
+                        dict(qkv=2, qk=1, pv=1, proj=1, fc1=1, fc2=1),
+                        dict(qkv=2, qk=2, pv=1, proj=1, fc1=1, fc2=1),
+                        dict(qkv=1, qk=1, pv=1, proj=1, fc1=2, fc2=2),
+                        dict(qkv=2, qk=2, pv=2, proj=2, fc1=1, fc2=1),
+                        dict(qkv=3, qk=1, pv=1, proj=1, fc1=1, fc2=1),
+                        dict(qkv=4, qk=1, pv=1, proj=1, fc1=1, fc2=1),
+                        dict(qkv=3, qk=3, pv=1, proj=1, fc1=1, fc2=1)):
+                MODE.clear(); MODE.update(cfg)
+                y = O.ngswin_forward(x, sd)
+                print(kind, cfg, f"max-abs {(y - ref).abs().max().item():.2e}", flush=True)

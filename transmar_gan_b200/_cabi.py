@@ -45,6 +45,7 @@ SIGNATURES = {
     "b200mar_attn_bwd": [_P] * 21 + [_I] * 5 + [_P],
     "b200mar_attn_bwd_tc": [_P] * 23 + [_I] * 5 + [_P],
     "b200mar_attn_tc_fwd_save": [_P] * 12 + [_I] * 5 + [_P],
+    "b200mar_attn_tc_fwd_comp": [_P] * 12 + [_I] * 5 + [_P],
     "b200mar_mlp_fwd": [_P] * 10 + [_L, _P],
     "b200mar_mlp_bwd": [_P] * 15 + [_L, _P],
     "b200mar_mlp_bwd_tc": [_P] * 16 + [_L, _P],

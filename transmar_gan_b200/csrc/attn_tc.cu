@@ -87,7 +87,12 @@ constexpr int kHotBytes = 23 * 128;
 constexpr int kVChunk = 528;                   // bytes between successive 4-key chunks of V^T (fp32):
                                                // 32 rows x 16 B + 16 (== 4 words mod 32 banks)
 
-template <int W>
+// COMP (precision level "tf32c"): the qkv projection runs on fp16 hi + lo operand PAIRS (X = Xh + Xl, W = Wh + Wl,
+// three MMA passes Xh Wh + Xl Wh + Xh Wl into the same fp32 accumulator), i.e. at ~22 significant bits instead of
+// 11.  The lo copies cost 24 KB (weights) + 16 KB per worker (X), which leaves room for TWO workers.
+template <int NH, bool COMP> struct AttnWorkers { static constexpr int value = COMP ? 2 : Cfg<NH>::kWorkers; };
+
+template <int W, bool COMP = false>
 struct AttnTcSmem {                            // BYTE offsets (W workers)
   static constexpr int kWRows = 192;           // 6 heads x [q10|k10|v10|0 0] or 4 heads x [q16|k16|v16]
   static constexpr int oWqkv = 0;              // fp16 [288 rows][64 k], 8-element k-chunks, R = 288
@@ -100,14 +105,16 @@ struct AttnTcSmem {                            // BYTE offsets (W workers)
   static constexpr int oBiasT = ((oScale + 32 + 127) / 128) * 128;   // fp16 [6 heads][15][8 cj][8 rj], * log2(e)
   static constexpr int oHot = oBiasT + 6 * kBiasTHead;               // fp16 one-hot operand (23 core matrices)
   static constexpr int oBar = oHot + kHotBytes;  // W workers x 8 mbarrier slots (5 used) + tmem slot
-  static constexpr int oWork = ((oBar + 320 + 1023) / 1024) * 1024;   // 1 KB aligned: TMA 128 B swizzle
+  static constexpr int oWqkvLo = ((oBar + 320 + 127) / 128) * 128;    // COMP: fp16 lo parts, same layout as oWqkv
+  static constexpr int oWork = ((oWqkvLo + (COMP ? kWRows * 64 * 2 : 0) + 1023) / 1024) * 1024;   // 1 KB aligned: TMA 128 B swizzle
   // per worker; [X | Q | K | V] is also the 32 KB fp32 staging tile of the LayerNorm output
   static constexpr int wX = 0;                 // fp16 [128][64] (R = 128): X, later O
   static constexpr int wQ = wX + 128 * 64 * 2; // fp16 [128][32] (R = 128)
   static constexpr int wK = wQ + 128 * 32 * 2; // fp16 [64][32]  (R = 64)
   static constexpr int wV = wK + 64 * 32 * 2;  // fp32 [32 rows = (window, d)][64 keys], chunk stride kVChunk
   static constexpr int wTok = wV + 16 * kVChunk;
-  static constexpr int kWorkBytes = ((wTok + 4 * 128 * 4 + 1023) / 1024) * 1024;   // tok, cwin, region, row scale
+  static constexpr int wXlo = ((wTok + 4 * 128 * 4 + 127) / 128) * 128;            // COMP: fp16 [128][64] lo parts of X
+  static constexpr int kWorkBytes = ((wXlo + (COMP ? 128 * 64 * 2 : 0) + 1023) / 1024) * 1024;   // tok, cwin, region, row scale
   static constexpr int kBytes = oWork + W * kWorkBytes;
   static_assert(wTok >= 128 * 64 * 4, "fp32 staging tile must fit in [X|Q|K|V]");
   static_assert(oBar % 8 == 0, "mbarrier alignment");
@@ -124,13 +131,13 @@ constexpr uint32_t kTQ = 0;
 // S16 = true : the residual stream (z in, a out) is BF16 in HBM (precision mode "bf16", BASELINE.json configs[1]):
 //               one 8 KB TMA box per window (64 tokens x 64 channels x 2 B = 128 B rows, 128 B swizzle), rows are
 //               widened to fp32 on read; the residual add runs in fp32 and a is rounded to bf16 once, on write.
-template <int NH, bool RESID, bool SAVEO, bool S16 = false>
-__global__ void __launch_bounds__(128 * Cfg<NH>::kWorkers, 1)
+template <int NH, bool RESID, bool SAVEO, bool S16 = false, bool COMP = false>
+__global__ void __launch_bounds__(128 * AttnWorkers<NH, COMP>::value, 1)
 attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_constant__ CUtensorMap mapA,
                    AttnParams p) {
-  constexpr int kWorkers = Cfg<NH>::kWorkers, HS = Cfg<NH>::HS, PS = Cfg<NH>::PS;
+  constexpr int kWorkers = AttnWorkers<NH, COMP>::value, HS = Cfg<NH>::HS, PS = Cfg<NH>::PS;
   constexpr uint32_t kTStride = Cfg<NH>::kTStride, kTS = Cfg<NH>::kTS;
-  using L = AttnTcSmem<kWorkers>;
+  using L = AttnTcSmem<kWorkers, COMP>;
   constexpr int HD = kDim / NH, A = HD * NH;
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   __half* sWqkv = reinterpret_cast<__half*>(smem_raw + L::oWqkv);
@@ -185,6 +192,16 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
                      tc::pack_f16(b.x * wsc, b.y * wsc), tc::pack_f16(b.z * wsc, b.w * wsc));
     }
     *reinterpret_cast<uint4*>(sWqkv + (size_t)kc * (L::kWRows * 8) + n * 8) = v;
+    if constexpr (COMP) {                      // lo = fp16(w * wsc - hi): exact difference, 11 more bits
+      uint4 l = make_uint4(0u, 0u, 0u, 0u);
+      if (h < NH && part < 3 && d < HD) {
+        const float4* src = reinterpret_cast<const float4*>(p.qkv_w + (part * A + h * HD + d) * 64 + kc * 8);
+        const float4 a = src[0], b = src[1];
+        l = make_uint4(tc::lo_f16(a.x * wsc, a.y * wsc, v.x), tc::lo_f16(a.z * wsc, a.w * wsc, v.y),
+                       tc::lo_f16(b.x * wsc, b.y * wsc, v.z), tc::lo_f16(b.z * wsc, b.w * wsc, v.w));
+      }
+      *reinterpret_cast<uint4*>(smem_raw + L::oWqkvLo + ((size_t)kc * (L::kWRows * 8) + n * 8) * 2) = l;
+    }
   }
   for (int idx = tid; idx < 64 * 16; idx += 128 * kWorkers) {
     const int n = idx & 63, kc = idx >> 6;
@@ -251,12 +268,22 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
                  dWp = tc::smem_desc(tc::smem_u32(sWp), 1024, 128),
                  dHot = tc::smem_desc(tc::smem_u32(sHot), 128, 128),       // LBO = SBO: aliased core matrices
                  dBiasT = tc::smem_desc(tc::smem_u32(sBiasT), 128, 128);
+  const uint64_t dXlo = tc::smem_desc(tc::smem_u32(sW + L::wXlo), 2048, 128),
+                 dWqkvLo = tc::smem_desc(tc::smem_u32(smem_raw + L::oWqkvLo), L::kWRows * 16, 128);
   // [q_h | k_h | v_h] = X * Wqkv[rows of head h]^T -> TMEM buffer `buf` (issued by one thread)
   auto issue_qkv = [&](int h, int buf) {
     const uint64_t db = dWqkv + (uint64_t)(h * HS);
 #pragma unroll
     for (int ks = 0; ks < 4; ++ks)
       tc::mma_f16(tbase + kTQ + buf * HS, dX + ks * 256, db + ks * (2 * L::kWRows), kIqkv, ks > 0);
+    if constexpr (COMP) {                      // + Xl Wh + Xh Wl (the lo x lo term is below fp32 resolution)
+      const uint64_t dl = dWqkvLo + (uint64_t)(h * HS);
+#pragma unroll
+      for (int ks = 0; ks < 4; ++ks) {
+        tc::mma_f16(tbase + kTQ + buf * HS, dXlo + ks * 256, db + ks * (2 * L::kWRows), kIqkv, 1u);
+        tc::mma_f16(tbase + kTQ + buf * HS, dX + ks * 256, dl + ks * (2 * L::kWRows), kIqkv, 1u);
+      }
+    }
   };
 
   // A window whose 8x8 token block is contiguous in the grid (all windows when shift = 0; all but the
@@ -399,12 +426,19 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
       xinv = __uint_as_float(e << 23) * sScale[6];            // undoes the row scale and the Wqkv scale
       tc::worker_sync(1 + wk);                       // every row is in registers: the tile may be overwritten
 #pragma unroll
-      for (int kc = 0; kc < 8; ++kc)                 // fp16 X operand, own row, one 16-byte slot per k-chunk
-        *reinterpret_cast<uint4*>(sX + kc * 2048 + row * 16) =
-            make_uint4(tc::pack_f16(x[8 * kc] * sc, x[8 * kc + 1] * sc),
-                       tc::pack_f16(x[8 * kc + 2] * sc, x[8 * kc + 3] * sc),
-                       tc::pack_f16(x[8 * kc + 4] * sc, x[8 * kc + 5] * sc),
-                       tc::pack_f16(x[8 * kc + 6] * sc, x[8 * kc + 7] * sc));
+      for (int kc = 0; kc < 8; ++kc) {               // fp16 X operand, own row, one 16-byte slot per k-chunk
+        const uint4 hv = make_uint4(tc::pack_f16(x[8 * kc] * sc, x[8 * kc + 1] * sc),
+                                    tc::pack_f16(x[8 * kc + 2] * sc, x[8 * kc + 3] * sc),
+                                    tc::pack_f16(x[8 * kc + 4] * sc, x[8 * kc + 5] * sc),
+                                    tc::pack_f16(x[8 * kc + 6] * sc, x[8 * kc + 7] * sc));
+        *reinterpret_cast<uint4*>(sX + kc * 2048 + row * 16) = hv;
+        if constexpr (COMP)
+          *reinterpret_cast<uint4*>(sW + L::wXlo + kc * 2048 + row * 16) =
+              make_uint4(tc::lo_f16(x[8 * kc] * sc, x[8 * kc + 1] * sc, hv.x),
+                         tc::lo_f16(x[8 * kc + 2] * sc, x[8 * kc + 3] * sc, hv.y),
+                         tc::lo_f16(x[8 * kc + 4] * sc, x[8 * kc + 5] * sc, hv.z),
+                         tc::lo_f16(x[8 * kc + 6] * sc, x[8 * kc + 7] * sc, hv.w));
+      }
     }
     // ---- shift mask of this row as a 64-bit key set (analytic 9-region rule)
     uint32_t mlo = 0, mhi = 0;
@@ -550,6 +584,10 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
 #pragma unroll
           for (int c = 0; c < 64; ++c) sum4[c & 3] += s[c];
           inv_prev = 1.0f / ((sum4[0] + sum4[1]) + (sum4[2] + sum4[3]));
+        }
+        if constexpr (COMP) {                            // the MMA truncates tf32 operands: round P to nearest
+#pragma unroll
+          for (int c = 0; c < 64; ++c) s[c] = tc::round_tf32(s[c]);
         }
         tc::tmem_st64(tbase + lane_addr + kTS, s);       // unnormalised P (tf32 operand) over S
         tc::tmem_wait_st();
@@ -721,13 +759,13 @@ extern "C" int b200mar_attn_prof(unsigned long long* out32, int reset) {
 namespace b200mar {
 #endif
 
-template <int NH, bool RESID, bool SAVEO = false, bool S16 = false>
+template <int NH, bool RESID, bool SAVEO = false, bool S16 = false, bool COMP = false>
 static int launch_attn_tc_fwd(const AttnParams& p, cudaStream_t st) {
-  constexpr int kWorkers = Cfg<NH>::kWorkers;
-  const size_t smem = AttnTcSmem<kWorkers>::kBytes;
+  constexpr int kWorkers = AttnWorkers<NH, COMP>::value;
+  const size_t smem = AttnTcSmem<kWorkers, COMP>::kBytes;
   static DeviceOnce configured;
   if (configured.first()) {
-    B200MAR_CHECK(cudaFuncSetAttribute(attn_tc_fwd_kernel<NH, RESID, SAVEO, S16>,
+    B200MAR_CHECK(cudaFuncSetAttribute(attn_tc_fwd_kernel<NH, RESID, SAVEO, S16, COMP>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     configured.done();
   }
@@ -743,7 +781,7 @@ static int launch_attn_tc_fwd(const AttnParams& p, cudaStream_t st) {
     if (int rc = tma::encode_windows(&mZ, p.z, p.B, p.ph, p.pw)) return rc;
     if (int rc = tma::encode_windows(&mA, p.a, p.B, p.ph, p.pw)) return rc;
   }
-  attn_tc_fwd_kernel<NH, RESID, SAVEO, S16><<<grid, 128 * kWorkers, smem, st>>>(mZ, mA, p);
+  attn_tc_fwd_kernel<NH, RESID, SAVEO, S16, COMP><<<grid, 128 * kWorkers, smem, st>>>(mZ, mA, p);
   B200MAR_CHECK(cudaGetLastError());
   return 0;
 }
@@ -765,6 +803,28 @@ extern "C" int b200mar_attn_tc_fwd(const float* z, const float* ctx, const float
   cudaStream_t st = (cudaStream_t)stream;
   if (nh == 6) return residual ? launch_attn_tc_fwd<6, true>(p, st) : launch_attn_tc_fwd<6, false>(p, st);
   if (nh == 4) return residual ? launch_attn_tc_fwd<4, true>(p, st) : launch_attn_tc_fwd<4, false>(p, st);
+  return -1;
+}
+
+// Precision level "tf32c": as b200mar_attn_tc_fwd(residual = 1) / b200mar_attn_tc_fwd_save (o16 != NULL) with the qkv
+// projection on compensated fp16 hi + lo operand pairs (two workers per SM; see AttnTcSmem).
+extern "C" int b200mar_attn_tc_fwd_comp(const float* z, const float* ctx, const float* qkv_w,
+                                        const float* qkv_b, const float* proj_w, const float* proj_b,
+                                        const float* logit_scale, const float* bias_table,
+                                        const float* ln_w, const float* ln_b, float* a, void* o16, int B,
+                                        int ph, int pw, int nh, int shift, void* stream) {
+  using namespace b200mar;
+  if (ph % kWin || pw % kWin || ph < kWin || pw < kWin || (shift != 0 && shift != kShift)) return -1;
+  if ((long long)B * ph * pw >= (1ll << 31)) return -1;
+  AttnParams p{};
+  p.z = z; p.ctx = ctx; p.qkv_w = qkv_w; p.qkv_b = qkv_b; p.proj_w = proj_w; p.proj_b = proj_b;
+  p.logit_scale = logit_scale; p.bias_table = bias_table; p.ln_w = ln_w; p.ln_b = ln_b;
+  p.a = a; p.o16 = (unsigned short*)o16; p.B = B; p.ph = ph; p.pw = pw; p.shift = shift;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (nh == 6) return o16 ? launch_attn_tc_fwd<6, true, true, false, true>(p, st)
+                          : launch_attn_tc_fwd<6, true, false, false, true>(p, st);
+  if (nh == 4) return o16 ? launch_attn_tc_fwd<4, true, true, false, true>(p, st)
+                          : launch_attn_tc_fwd<4, true, false, false, true>(p, st);
   return -1;
 }
 

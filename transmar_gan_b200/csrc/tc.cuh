@@ -12,6 +12,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <cuda_fp16.h>
 #include "tc_ldst.cuh"
 
 namespace b200mar {
@@ -149,6 +150,12 @@ __device__ __forceinline__ uint32_t pack_f16(float a, float b) {
   uint32_t r;
   asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
   return r;
+}
+// lo part of an fp16 hi + lo pair: fp16x2(a - hi.lo16, b - hi.hi16) for hi = pack_f16(a, b).  The differences are
+// exact in fp32; |lo| <= 2^-11 |value|, and below 2^-14 the fp16 subnormals still resolve 2^-24 absolute.
+__device__ __forceinline__ uint32_t lo_f16(float a, float b, uint32_t hi) {
+  const float2 h = __half22float2(*reinterpret_cast<const __half2*>(&hi));
+  return pack_f16(a - h.x, b - h.y);
 }
 // D[tmem] (+)= A[smem] * B[smem]^T, one K = 8 step.  Issued by ONE thread.
 __device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,

@@ -83,12 +83,12 @@ _UNIT: List[Tuple[Optional[str], Optional[str]]] = []
 
 class unit_precision:
     """Context manager: inside, the attention half and the MLP half of an NSTB compute in `attn` / `mlp`
-    ("tf32" / "fp32"; None = the surrounding mode)."""
+    ("tf32" / "fp32"; None = the surrounding mode).  The attention half has a third level, "tf32c": the
+    tensor-core kernel with the qkv projection on compensated fp16 hi + lo operand pairs."""
 
     def __init__(self, attn: Optional[str], mlp: Optional[str]):
-        for m in (attn, mlp):
-            if m not in (None, "tf32", "fp32"):
-                raise ValueError("unit_precision takes 'tf32', 'fp32' or None")
+        if attn not in (None, "tf32", "tf32c", "fp32") or mlp not in (None, "tf32", "fp32"):
+            raise ValueError("unit_precision takes 'tf32', 'fp32' or None (attention half also 'tf32c')")
         self.modes = (attn, mlp)
 
     def __enter__(self):
@@ -347,11 +347,19 @@ def _(z, ctx, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, ln_w, ln_b,
 @torch.library.custom_op(f"{_NS}::attn_tc_fwd", mutates_args=())
 def attn_tc_fwd(z: Tensor, ctx: Tensor, qkv_w: Tensor, qkv_b: Tensor, proj_w: Tensor, proj_b: Tensor,
                 logit_scale: Tensor, bias_table: Tensor, ln_w: Tensor, ln_b: Tensor,
-                ph: int, pw: int, nh: int, shift: int, residual: bool = True) -> Tensor:
+                ph: int, pw: int, nh: int, shift: int, residual: bool = True, comp: bool = False) -> Tensor:
     """attn_fwd on the tcgen05 tensor cores (fp16 / tf32 operands, fp32 accumulate in TMEM).
-    residual=False returns LN1(attn) only (mlp_tc_fwd with a_is_delta=True adds z)."""
+    residual=False returns LN1(attn) only (mlp_tc_fwd with a_is_delta=True adds z).
+    comp=True (precision level "tf32c", residual only): qkv projection on fp16 hi + lo operand pairs."""
     _chk(z, ctx, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, ln_w, ln_b)
     a = torch.empty_like(z)
+    if comp:
+        if not residual:
+            raise ValueError("attn_tc_fwd: comp=True needs residual=True")
+        _call("attn_tc_fwd_comp", _p(z), _p(ctx), _p(qkv_w), _p(qkv_b), _p(proj_w), _p(proj_b), _p(logit_scale),
+              _p(bias_table), _p(ln_w), _p(ln_b), _p(a), 0, z.shape[0], ph, pw, nh, shift,
+              _stream(), meta=(z.shape[0], ph, pw, nh, shift))
+        return a
     _call("attn_tc_fwd", _p(z), _p(ctx), _p(qkv_w), _p(qkv_b), _p(proj_w), _p(proj_b), _p(logit_scale),
           _p(bias_table), _p(ln_w), _p(ln_b), _p(a), z.shape[0], ph, pw, nh, shift, int(residual),
           _stream(), meta=(z.shape[0], ph, pw, nh, shift))
@@ -360,28 +368,28 @@ def attn_tc_fwd(z: Tensor, ctx: Tensor, qkv_w: Tensor, qkv_b: Tensor, proj_w: Te
 
 @attn_tc_fwd.register_fake
 def _(z, ctx, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, ln_w, ln_b, ph, pw, nh, shift,
-      residual=True):
+      residual=True, comp=False):
     return torch.empty_like(z)
 
 
 @torch.library.custom_op(f"{_NS}::attn_tc_fwd_save", mutates_args=())
 def attn_tc_fwd_save(z: Tensor, ctx: Tensor, qkv_w: Tensor, qkv_b: Tensor, proj_w: Tensor, proj_b: Tensor,
                      logit_scale: Tensor, bias_table: Tensor, ln_w: Tensor, ln_b: Tensor,
-                     ph: int, pw: int, nh: int, shift: int) -> Tuple[Tensor, Tensor]:
+                     ph: int, pw: int, nh: int, shift: int, comp: bool = False) -> Tuple[Tensor, Tensor]:
     """Training form of attn_tc_fwd: also returns the pre-projection attention output O (bf16,
     [ceil(nwin/2)*128, 64], window order) that attn_bwd_tc consumes instead of recomputing it."""
     _chk(z, ctx, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, ln_w, ln_b)
     a = torch.empty_like(z)
     nwin = z.shape[0] * (ph // 8) * (pw // 8)
     o16 = torch.empty((((nwin + 1) // 2) * 128, 64), device=z.device, dtype=torch.bfloat16)
-    _call("attn_tc_fwd_save", _p(z), _p(ctx), _p(qkv_w), _p(qkv_b), _p(proj_w), _p(proj_b), _p(logit_scale),
+    _call("attn_tc_fwd_comp" if comp else "attn_tc_fwd_save", _p(z), _p(ctx), _p(qkv_w), _p(qkv_b), _p(proj_w), _p(proj_b), _p(logit_scale),
           _p(bias_table), _p(ln_w), _p(ln_b), _p(a), o16.data_ptr(), z.shape[0], ph, pw, nh, shift,
           _stream(), meta=(z.shape[0], ph, pw, nh, shift))
     return a, o16
 
 
 @attn_tc_fwd_save.register_fake
-def _(z, ctx, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, ln_w, ln_b, ph, pw, nh, shift):
+def _(z, ctx, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, ln_w, ln_b, ph, pw, nh, shift, comp=False):
     nwin = z.shape[0] * (ph // 8) * (pw // 8)
     return torch.empty_like(z), z.new_empty((((nwin + 1) // 2) * 128, 64), dtype=torch.bfloat16)
 
@@ -872,7 +880,8 @@ def nstb_infer_mixed_(z: Tensor, ph: int, pw: int, nh: int, shift: int, want_out
     if attn_mode == "fp32":
         a = attn_fwd(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw, nh, shift)
     else:
-        a = attn_tc_fwd(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw, nh, shift, True)
+        a = attn_tc_fwd(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw, nh, shift, True,
+                        attn_mode == "tf32c")
     if mlp_mode == "fp32":
         return mlp_fwd(a, z if want_zsum else None, P[18], P[19], P[20], P[21], P[22], P[23], want_out, want_zsum)
     if want_zsum and not private:
@@ -901,10 +910,10 @@ class NSTBFunction(torch.autograd.Function):
             # the MLP kernel; measured on B200 it costs the MLP more than it saves the attention)
             if save:
                 a, o16 = attn_tc_fwd_save(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw,
-                                          nh, shift)
+                                          nh, shift, ma == "tf32c")
             else:
                 a = attn_tc_fwd(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw, nh,
-                                shift, True)
+                                shift, True, ma == "tf32c")
         else:
             a = attn_fwd(z, c, P[10], P[11], P[12], P[13], P[14], P[15], P[16], P[17], ph, pw, nh, shift)
         if tc_m:
