@@ -1,6 +1,6 @@
-"""GPU tests of precision level "tf32c" (DESIGN.md §5.2): the tensor-core attention kernel with the qkv projection
-(models/generator/components/attention.py:75) on compensated FP16 hi + lo operand pairs, through the C ABI
-(`b200mar_attn_tc_fwd_comp`).
+"""GPU tests of precision level "tf32c" (DESIGN.md §5.2): the tensor-core attention kernel with all four GEMMs of
+models/generator/components/attention.py:75-101 (qkv, q k^T, P v, proj) on compensated operand PAIRS (fp16 hi + lo,
+bf16 hi + mid for P and V), three MMA passes per product, through the C ABI (`b200mar_attn_tc_fwd_comp`).
 
   * kernel level: same contract and tolerances as `attn_tc_fwd` against the oracle, never worse than it, and much
     closer to the fp32 kernel on rows with a large common-mode component (what trained weights produce in flat image
@@ -74,8 +74,10 @@ def test_comp_kernel_against_oracle(T, case, geom):
     a = T.ops.attn_tc_fwd(z.cuda(), ctx.cuda(), *P[10:18], ph, pw, nh, shift, True, False).cpu()
     c = T.ops.attn_tc_fwd(z.cuda(), ctx.cuda(), *P[10:18], ph, pw, nh, shift, True, True).cpu()
     dc, da = (c - ref).abs(), (a - ref).abs()
-    assert dc.max() < 2e-2 and dc.mean() < 2e-3, (dc.max().item(), dc.mean().item())
-    assert dc.mean() <= da.mean() * 1.02 + 1e-7, (dc.mean().item(), da.mean().item())
+    print(f"[tf32c] {prefix} {geom}: max / mean abs error plain {da.max().item():.1e} / {da.mean().item():.1e}, "
+          f"compensated {dc.max().item():.1e} / {dc.mean().item():.1e}")
+    assert dc.max() < 1e-3 and dc.mean() < 5e-5, (dc.max().item(), dc.mean().item())
+    assert dc.mean() * 10 < da.mean(), (dc.mean().item(), da.mean().item())
     # the training form: same a, and the saved pre-projection O equals the plain kernel's within bf16 rounding
     c2, o2 = T.ops.attn_tc_fwd_save(z.cuda(), ctx.cuda(), *P[10:18], ph, pw, nh, shift, True)
     _, o1 = T.ops.attn_tc_fwd_save(z.cuda(), ctx.cuda(), *P[10:18], ph, pw, nh, shift, False)
@@ -91,7 +93,8 @@ def test_comp_kernel_against_oracle(T, case, geom):
 def test_comp_recovers_common_mode_rows(T, case):
     """Rows = one large common vector + a small per-token variation, sharp logits (scale at the ln 100 clamp): the
     11-bit roundings of X and W_qkv are relative to the common mode while q and k live in the variation.  Error
-    against the float64 oracle: the compensated kernel must be at least 3x closer than the plain one."""
+    against the float64 oracle: the compensated kernel must be at least 100x closer than the plain one and within 2x
+    of the fp32 FMA-pipe kernel."""
     prefix, nh, shift = case
     B, ph, pw = 2, 32, 48
     sd = O.synthetic_state_dict("W1", seed=1)
@@ -114,7 +117,7 @@ def test_comp_recovers_common_mode_rows(T, case):
     f = T.ops.attn_fwd(z.cuda(), ctx.cuda(), *P[10:18], ph, pw, nh, shift).cpu().double()
     ea, ec, ef = ((t - ref).abs().mean().item() for t in (a, c, f))
     print(f"[tf32c] {prefix} common-mode rows: mean abs error plain {ea:.2e}, compensated {ec:.2e}, fp32 kernel {ef:.2e}")
-    assert ec * 3 < ea, (ea, ec, ef)
+    assert ec * 100 < ea and ec < 2 * ef + 1e-6, (ea, ec, ef)
 
 
 @pytest.fixture(scope="module")
@@ -137,8 +140,7 @@ def test_trained_like_weights_block0_compensated(T, w3_model, golden_w3):
     finally:
         m._set_plan(saved)
     print(f"[tf32c] W3 phantom, every unit on tcgen05: block 0 attention plain {e_plain:.2e}, compensated {e_comp:.2e}")
-    assert e_comp < GATE < e_plain * 1.5, (e_plain, e_comp)
-    assert e_comp < 0.6 * e_plain
+    assert e_comp < 0.5 * GATE < e_plain, (e_plain, e_comp)
 
 
 def test_default_plan_on_trained_like_weights(T, w3_model, golden_w3):
@@ -151,7 +153,8 @@ def test_default_plan_on_trained_like_weights(T, w3_model, golden_w3):
           f"{rep['err_plan']:.2e} (all 11-bit: {rep['err_all_tensor_core']:.2e}); marginal of unit 0: "
           f"{rep['marginal_err'][0]:.2e} -> {rep['marginal_err_compensated'][0]:.2e}")
     assert (y - golden_w3["phantom_out"]).abs().max().item() < GATE
-    assert plan[0] in ("tf32c", "fp32") and rep["units_on_tensor_cores"] >= 40, rep
+    assert plan[0] == "tf32c" and rep["units_on_tensor_cores"] == 41 and rep["units_compensated"] >= 1, rep
+    assert rep["marginal_err_compensated"][0] < 2e-5, rep["marginal_err_compensated"][0]
     assert rep["err_plan"] <= rep["tol"]
     assert all(p in ("tf32", "fp32") for p in plan[1::2]) and plan[40] in ("tf32", "fp32")   # only attention halves
 

@@ -87,9 +87,14 @@ constexpr int kHotBytes = 23 * 128;
 constexpr int kVChunk = 528;                   // bytes between successive 4-key chunks of V^T (fp32):
                                                // 32 rows x 16 B + 16 (== 4 words mod 32 banks)
 
-// COMP (precision level "tf32c"): the qkv projection runs on fp16 hi + lo operand PAIRS (X = Xh + Xl, W = Wh + Wl,
-// three MMA passes Xh Wh + Xl Wh + Xh Wl into the same fp32 accumulator), i.e. at ~22 significant bits instead of
-// 11.  The lo copies cost 24 KB (weights) + 16 KB per worker (X), which leaves room for TWO workers.
+// COMP (precision level "tf32c"): every GEMM of the block runs on operand PAIRS, three MMA passes
+// Ah Bh + Al Bh + Ah Bl into the same fp32 accumulator:
+//   qkv  : X = Xh + Xl, Wqkv = Wh + Wl (fp16, power-of-two row / matrix scales)            ~22 bits
+//   q k^T: Q' = Qh + Ql, K' = Kh + Kl (fp16)                                                ~22 bits
+//   P V  : P = Ph + Pm (BF16 pair in TMEM; always the max-subtracting softmax, so P <= 1),
+//          V = Vh + Vm (BF16 pair: no range scaling needed)                                 ~16 bits
+//   proj : O = Oh + Ol (fp16, power-of-two row scale, smem), Wp = Wh + Wl (fp16)            ~22 bits
+// The lo copies cost 24 KB (weights) + 32 KB per worker, which leaves room for TWO workers.
 template <int NH, bool COMP> struct AttnWorkers { static constexpr int value = COMP ? 2 : Cfg<NH>::kWorkers; };
 
 template <int W, bool COMP = false>
@@ -113,8 +118,13 @@ struct AttnTcSmem {                            // BYTE offsets (W workers)
   static constexpr int wK = wQ + 128 * 32 * 2; // fp16 [64][32]  (R = 64)
   static constexpr int wV = wK + 64 * 32 * 2;  // fp32 [32 rows = (window, d)][64 keys], chunk stride kVChunk
   static constexpr int wTok = wV + 16 * kVChunk;
-  static constexpr int wXlo = ((wTok + 4 * 128 * 4 + 127) / 128) * 128;            // COMP: fp16 [128][64] lo parts of X
-  static constexpr int kWorkBytes = ((wXlo + (COMP ? 128 * 64 * 2 : 0) + 1023) / 1024) * 1024;   // tok, cwin, region, row scale
+  // COMP only, outside the staging alias: lo parts of X, Q', K' (+ 4 KB) = 32 KB; after the last head the same
+  // 32 KB hold the fp16 hi | lo parts of the attention output O, the A operands of the projection
+  static constexpr int wXlo = ((wTok + 4 * 128 * 4 + 127) / 128) * 128;            // fp16 [128][64]
+  static constexpr int wQlo = wXlo + 128 * 64 * 2;                                 // fp16 [128][32]
+  static constexpr int wKlo = wQlo + 128 * 32 * 2;                                 // fp16 [64][32]
+  static constexpr int wOhi = wXlo, wOlo = wQlo;                                   // fp16 [128][64] each
+  static constexpr int kWorkBytes = ((wXlo + (COMP ? 2 * 128 * 64 * 2 : 0) + 1023) / 1024) * 1024;   // tok, cwin, region, row scale
   static constexpr int kBytes = oWork + W * kWorkBytes;
   static_assert(wTok >= 128 * 64 * 4, "fp32 staging tile must fit in [X|Q|K|V]");
   static_assert(oBar % 8 == 0, "mbarrier alignment");
@@ -203,11 +213,40 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
       *reinterpret_cast<uint4*>(smem_raw + L::oWqkvLo + ((size_t)kc * (L::kWRows * 8) + n * 8) * 2) = l;
     }
   }
-  for (int idx = tid; idx < 64 * 16; idx += 128 * kWorkers) {
-    const int n = idx & 63, kc = idx >> 6;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (kc * 4 < A) v = *reinterpret_cast<const float4*>(p.proj_w + n * A + kc * 4);
-    *reinterpret_cast<float4*>(sWp + kc * 256 + n * 4) = tc::round_tf32(v);   // the MMA would truncate
+  __shared__ float sProjInv;                   // COMP: inverse of the projection weights' power-of-two scale
+  if constexpr (COMP) {
+    __shared__ uint32_t sPmax;
+    if (tid == 0) sPmax = 0u;
+    __syncthreads();
+    float m = 0.f;
+    for (int i = tid; i < 64 * A; i += 128 * kWorkers) m = fmaxf(m, fabsf(p.proj_w[i]));
+    atomicMax(&sPmax, __float_as_uint(m));
+    __syncthreads();
+    uint32_t pe = (sPmax >> 23) & 0xFFu;
+    pe = pe < 1u ? 127u : (pe > 253u ? 253u : pe);
+    const float psc = __uint_as_float((254u - pe) << 23);
+    if (tid == 0) sProjInv = __uint_as_float(pe << 23);
+    // fp16 [64 rows n][64 k], 8-element k-chunks (R = 64): hi at oWp, lo at oWp + 8 KB
+    for (int idx = tid; idx < 64 * 8; idx += 128 * kWorkers) {
+      const int n = idx & 63, kc = idx >> 6;
+      float w[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) w[j] = kc * 8 + j < A ? p.proj_w[n * A + kc * 8 + j] * psc : 0.f;
+      const uint4 hv = make_uint4(tc::pack_f16(w[0], w[1]), tc::pack_f16(w[2], w[3]),
+                                  tc::pack_f16(w[4], w[5]), tc::pack_f16(w[6], w[7]));
+      unsigned char* dst = smem_raw + L::oWp + kc * 1024 + n * 16;
+      *reinterpret_cast<uint4*>(dst) = hv;
+      *reinterpret_cast<uint4*>(dst + 8192) =
+          make_uint4(tc::lo_f16(w[0], w[1], hv.x), tc::lo_f16(w[2], w[3], hv.y),
+                     tc::lo_f16(w[4], w[5], hv.z), tc::lo_f16(w[6], w[7], hv.w));
+    }
+  } else {
+    for (int idx = tid; idx < 64 * 16; idx += 128 * kWorkers) {
+      const int n = idx & 63, kc = idx >> 6;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (kc * 4 < A) v = *reinterpret_cast<const float4*>(p.proj_w + n * A + kc * 4);
+      *reinterpret_cast<float4*>(sWp + kc * 256 + n * 4) = tc::round_tf32(v);   // the MMA would truncate
+    }
   }
   for (int n = tid; n < L::kWRows; n += 128 * kWorkers) {      // bias in the same packed order
     const int h = n / HS, part = (n % HS) / PS, d = (n % HS) % PS;
@@ -269,7 +308,17 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
                  dHot = tc::smem_desc(tc::smem_u32(sHot), 128, 128),       // LBO = SBO: aliased core matrices
                  dBiasT = tc::smem_desc(tc::smem_u32(sBiasT), 128, 128);
   const uint64_t dXlo = tc::smem_desc(tc::smem_u32(sW + L::wXlo), 2048, 128),
-                 dWqkvLo = tc::smem_desc(tc::smem_u32(smem_raw + L::oWqkvLo), L::kWRows * 16, 128);
+                 dWqkvLo = tc::smem_desc(tc::smem_u32(smem_raw + L::oWqkvLo), L::kWRows * 16, 128),
+                 dQlo = tc::smem_desc(tc::smem_u32(sW + L::wQlo), 2048, 128),
+                 dKlo = tc::smem_desc(tc::smem_u32(sW + L::wKlo), 1024, 128),
+                 // COMP: V^T as a BF16 pair, [32 rows = (window, d)][64 keys] in 8-key chunks of stride kVChunk
+                 dVh = tc::smem_desc(tc::smem_u32(sV), kVChunk, 128),
+                 dVm = tc::smem_desc(tc::smem_u32(sV + 8 * kVChunk), kVChunk, 128),
+                 dOhi = tc::smem_desc(tc::smem_u32(sW + L::wOhi), 2048, 128),
+                 dOlo = tc::smem_desc(tc::smem_u32(sW + L::wOlo), 2048, 128),
+                 dWpH = tc::smem_desc(tc::smem_u32(smem_raw + L::oWp), 1024, 128),
+                 dWpL = tc::smem_desc(tc::smem_u32(smem_raw + L::oWp + 8192), 1024, 128);
+  constexpr uint32_t kIpv = tc::idesc_bf16(128, 32);   // (a mixed fp16 x bf16 descriptor is an illegal instruction)
   // [q_h | k_h | v_h] = X * Wqkv[rows of head h]^T -> TMEM buffer `buf` (issued by one thread)
   auto issue_qkv = [&](int h, int buf) {
     const uint64_t db = dWqkv + (uint64_t)(h * HS);
@@ -337,6 +386,12 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
   auto issue_s = [&]() {
     tc::mma_f16(tbase + kTS, dQ, dK, kI64, 1u);
     tc::mma_f16(tbase + kTS, dQ + 256, dK + 128, kI64, 1u);
+    if constexpr (COMP) {
+      tc::mma_f16(tbase + kTS, dQlo, dK, kI64, 1u);
+      tc::mma_f16(tbase + kTS, dQlo + 256, dK + 128, kI64, 1u);
+      tc::mma_f16(tbase + kTS, dQ, dKlo, kI64, 1u);
+      tc::mma_f16(tbase + kTS, dQ + 256, dKlo + 128, kI64, 1u);
+    }
   };
   // L2 prefetch of a tile's z windows: the load at the end of the current tile then hits L2
   auto prefetch_z = [&](int tile_) {
@@ -495,10 +550,15 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
       const float qmul = sScale[h] * rsqrtf(fmaxf(qs, kNormEps * kNormEps));   // v / max(|v|, eps)
       const float kmul = rsqrtf(fmaxf(ks, kNormEps * kNormEps));
       uint32_t qp[8], kp[8];
+      [[maybe_unused]] uint32_t ql[8], kl[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         qp[j] = 2 * j < HD ? tc::pack_f16(qkv[2 * j] * qmul, qkv[2 * j + 1] * qmul) : 0u;
         kp[j] = 2 * j < HD ? tc::pack_f16(qkv[PS + 2 * j] * kmul, qkv[PS + 2 * j + 1] * kmul) : 0u;
+        if constexpr (COMP) {
+          ql[j] = 2 * j < HD ? tc::lo_f16(qkv[2 * j] * qmul, qkv[2 * j + 1] * qmul, qp[j]) : 0u;
+          kl[j] = 2 * j < HD ? tc::lo_f16(qkv[PS + 2 * j] * kmul, qkv[PS + 2 * j + 1] * kmul, kp[j]) : 0u;
+        }
       }
       // ---- previous head's O: its PV MMAs read P (TMEM) and V^T (smem) and wrote O over the
       //      accumulator buffer that [q|k|v]_{h+1} will reuse: read it before anything is reused
@@ -530,10 +590,34 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
         uint4* k0 = reinterpret_cast<uint4*>(sK + lrow * 16);                // k-chunk stride 1024 B
         k0[(2 * wsel) * 64] = make_uint4(kp[0], kp[1], kp[2], kp[3]);
         k0[(2 * wsel + 1) * 64] = make_uint4(kp[4], kp[5], kp[6], kp[7]);
+        if constexpr (COMP) {
+          uint4* ql0 = reinterpret_cast<uint4*>(sW + L::wQlo + row * 16);
+          ql0[(2 * wsel) * 128] = make_uint4(ql[0], ql[1], ql[2], ql[3]);
+          ql0[(2 * wsel + 1) * 128] = make_uint4(ql[4], ql[5], ql[6], ql[7]);
+          if (h == 0) {
+            ql0[(2 - 2 * wsel) * 128] = z4;
+            ql0[(3 - 2 * wsel) * 128] = z4;
+          }
+          uint4* kl0 = reinterpret_cast<uint4*>(sW + L::wKlo + lrow * 16);
+          kl0[(2 * wsel) * 64] = make_uint4(kl[0], kl[1], kl[2], kl[3]);
+          kl0[(2 * wsel + 1) * 64] = make_uint4(kl[4], kl[5], kl[6], kl[7]);
+          // V^T as a BF16 pair: element ((window, d), key) at (key / 8) * kVChunk + (window * 16 + d) * 16 + (key % 8) * 2
+          unsigned short* vh = reinterpret_cast<unsigned short*>(sV + (lrow >> 3) * kVChunk + wsel * 256) + (lrow & 7);
+          unsigned short* vm = vh + 8 * kVChunk / 2;
+#pragma unroll
+          for (int d = 0; d < HD; ++d) {
+            const float v = qkv[2 * PS + d];
+            const uint32_t hb = tc::pack_bf16(v, 0.f) & 0xFFFFu;
+            vh[d * 8] = (unsigned short)hb;
+            vm[d * 8] = (unsigned short)(tc::pack_bf16(v - __uint_as_float(hb << 16), 0.f) & 0xFFFFu);
+          }
+          if (NH == 6 && h == 0) { vh[HD * 8] = 0x3F80u; vm[HD * 8] = 0u; }   // ones row: O column HD = row sum of P
+        } else {
         float* vt = reinterpret_cast<float*>(sV + (lrow >> 2) * kVChunk + wsel * 256) + (lrow & 3);
 #pragma unroll
         for (int d = 0; d < HD; ++d) vt[d * 4] = tc::round_tf32(qkv[2 * PS + d]);
         if (NH == 6 && h == 0) vt[HD * 4] = 1.0f;      // ones row (both windows): O column HD = row sum of P
+        }
       }
       PROF(6);                                         // operand stores
       tc::fence_async_smem();
@@ -568,7 +652,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
             if ((mhi >> c) & 1u) s[c + 32] += -100.0f * kLog2e;
           }
         }
-        if (sFast[h]) {
+        if (!COMP && sFast[h]) {
 #pragma unroll
           for (int c = 0; c < 64; ++c) s[c] = tc::ex2_approx(s[c]);
         } else {
@@ -585,11 +669,19 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
           for (int c = 0; c < 64; ++c) sum4[c & 3] += s[c];
           inv_prev = 1.0f / ((sum4[0] + sum4[1]) + (sum4[2] + sum4[3]));
         }
-        if constexpr (COMP) {                            // the MMA truncates tf32 operands: round P to nearest
+        if constexpr (COMP) {                            // P <= 1 as a BF16 pair: hi in columns [0,32), mid in [32,64)
+          float ph[32], pl[32];
 #pragma unroll
-          for (int c = 0; c < 64; ++c) s[c] = tc::round_tf32(s[c]);
+          for (int j = 0; j < 32; ++j) {
+            const uint32_t hv = tc::pack_bf16(s[2 * j], s[2 * j + 1]);
+            ph[j] = __uint_as_float(hv);
+            pl[j] = __uint_as_float(tc::lo_bf16(s[2 * j], s[2 * j + 1], hv));
+          }
+          tc::tmem_st32(tbase + lane_addr + kTS, ph);
+          tc::tmem_st32(tbase + lane_addr + kTS + 32, pl);
+        } else {
+          tc::tmem_st64(tbase + lane_addr + kTS, s);     // unnormalised P (tf32 operand) over S
         }
-        tc::tmem_st64(tbase + lane_addr + kTS, s);       // unnormalised P (tf32 operand) over S
         tc::tmem_wait_st();
       }
       PROF(9);                                         // softmax + P store
@@ -599,9 +691,18 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
       if (wq == 0) {
         tc::tc_fence_after();
         if (tc::elect_one()) {
+          if constexpr (COMP) {                          // Ph Vh + Pm Vh + Ph Vm, K = 16 keys per step
 #pragma unroll
-          for (int ks = 0; ks < 8; ++ks)
-            tc::mma_tf32_ts(tbase + kTQ + buf * HS, tbase + kTS + ks * 8, dV + ks * (2 * kVChunk / 16), kT32, ks > 0);
+            for (int ks = 0; ks < 4; ++ks) {
+              tc::mma_f16_ts(tbase + kTQ + buf * HS, tbase + kTS + ks * 8, dVh + ks * (2 * kVChunk / 16), kIpv, ks > 0);
+              tc::mma_f16_ts(tbase + kTQ + buf * HS, tbase + kTS + 32 + ks * 8, dVh + ks * (2 * kVChunk / 16), kIpv, 1u);
+              tc::mma_f16_ts(tbase + kTQ + buf * HS, tbase + kTS + ks * 8, dVm + ks * (2 * kVChunk / 16), kIpv, 1u);
+            }
+          } else {
+#pragma unroll
+            for (int ks = 0; ks < 8; ++ks)
+              tc::mma_tf32_ts(tbase + kTQ + buf * HS, tbase + kTS + ks * 8, dV + ks * (2 * kVChunk / 16), kT32, ks > 0);
+          }
           tc::mma_commit(barO);
         }
         __syncwarp();
@@ -623,11 +724,38 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
     //      (an L2 hit), so that it lands behind the projection and the LayerNorm
     if (RESID && leader) issue_z_loads(tile);
     // ---- O row (tf32-rounded) -> TMEM over the dead [q|k|v] buffers: the A operand of the projection
+    [[maybe_unused]] float oinv = 1.0f;
     {
       float ot[64];
+      if constexpr (COMP) {                            // O as an fp16 pair in shared memory, row-scaled like X
+        float m0 = 0.f, m1 = 0.f;
 #pragma unroll
-      for (int i = 0; i < 64; ++i) ot[i] = tc::round_tf32(o[i]);
-      tc::tmem_st64(tbase + lane_addr + kTQ, ot);
+        for (int i = 0; i < 64; i += 2) { m0 = fmaxf(m0, fabsf(o[i])); m1 = fmaxf(m1, fabsf(o[i + 1])); }
+        uint32_t e = (__float_as_uint(fmaxf(m0, m1)) >> 23) & 0xFFu;
+        e = e < 1u ? 127u : (e > 253u ? 253u : e);
+        const float sc = __uint_as_float((254u - e) << 23);
+        oinv = __uint_as_float(e << 23) * sProjInv;
+#pragma unroll
+        for (int i = 0; i < 64; ++i) ot[i] = o[i];
+#pragma unroll
+        for (int kc = 0; kc < 8; ++kc) {
+          const uint4 hv = make_uint4(tc::pack_f16(o[8 * kc] * sc, o[8 * kc + 1] * sc),
+                                      tc::pack_f16(o[8 * kc + 2] * sc, o[8 * kc + 3] * sc),
+                                      tc::pack_f16(o[8 * kc + 4] * sc, o[8 * kc + 5] * sc),
+                                      tc::pack_f16(o[8 * kc + 6] * sc, o[8 * kc + 7] * sc));
+          *reinterpret_cast<uint4*>(sW + L::wOhi + kc * 2048 + row * 16) = hv;
+          *reinterpret_cast<uint4*>(sW + L::wOlo + kc * 2048 + row * 16) =
+              make_uint4(tc::lo_f16(o[8 * kc] * sc, o[8 * kc + 1] * sc, hv.x),
+                         tc::lo_f16(o[8 * kc + 2] * sc, o[8 * kc + 3] * sc, hv.y),
+                         tc::lo_f16(o[8 * kc + 4] * sc, o[8 * kc + 5] * sc, hv.z),
+                         tc::lo_f16(o[8 * kc + 6] * sc, o[8 * kc + 7] * sc, hv.w));
+        }
+        tc::fence_async_smem();
+      } else {
+#pragma unroll
+        for (int i = 0; i < 64; ++i) ot[i] = tc::round_tf32(o[i]);
+        tc::tmem_st64(tbase + lane_addr + kTQ, ot);
+      }
       if (SAVEO && wvalid) {                             // bf16 copy for the backward (window order)
         uint4* dst = reinterpret_cast<uint4*>(p.o16 + ((size_t)tile * 128 + wsel * 64 + ltok) * 64);
 #pragma unroll
@@ -642,9 +770,18 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
     if (wq == 0) {
       tc::tc_fence_after();
       if (tc::elect_one()) {
+        if constexpr (COMP) {                          // Oh Wh + Ol Wh + Oh Wl (fp16, K = 16 per step)
 #pragma unroll
-        for (int ks = 0; ks < 8; ++ks)
-          tc::mma_tf32_ts(tbase + kTS, tbase + kTQ + ks * 8, dWp + ks * 128, kT64, ks > 0);
+          for (int ks = 0; ks < 4; ++ks) {
+            tc::mma_f16(tbase + kTS, dOhi + ks * 256, dWpH + ks * 128, kI64, ks > 0);
+            tc::mma_f16(tbase + kTS, dOlo + ks * 256, dWpH + ks * 128, kI64, 1u);
+            tc::mma_f16(tbase + kTS, dOhi + ks * 256, dWpL + ks * 128, kI64, 1u);
+          }
+        } else {
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)
+            tc::mma_tf32_ts(tbase + kTS, tbase + kTQ + ks * 8, dWp + ks * 128, kT64, ks > 0);
+        }
         tc::mma_commit(barS);
       }
       __syncwarp();
@@ -659,7 +796,10 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
       tc::tmem_ld64(tbase + lane_addr + kTS, y);
       float mean4[4] = {0.f, 0.f, 0.f, 0.f};      // four partial sums: short dependency chains
 #pragma unroll
-      for (int i = 0; i < 64; ++i) { y[i] += sBp[i]; mean4[i & 3] += y[i]; }
+      for (int i = 0; i < 64; ++i) {
+        if constexpr (COMP) y[i] = fmaf(y[i], oinv, sBp[i]); else y[i] += sBp[i];
+        mean4[i & 3] += y[i];
+      }
       const float mean = ((mean4[0] + mean4[1]) + (mean4[2] + mean4[3])) * (1.0f / 64.f);
       float var4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll

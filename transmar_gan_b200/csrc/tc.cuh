@@ -157,6 +157,10 @@ __device__ __forceinline__ uint32_t lo_f16(float a, float b, uint32_t hi) {
   const float2 h = __half22float2(*reinterpret_cast<const __half2*>(&hi));
   return pack_f16(a - h.x, b - h.y);
 }
+// second term of a BF16 pair: bf16x2(a - hi.lo16, b - hi.hi16) for hi = pack_bf16(a, b); 16 significant bits in all
+__device__ __forceinline__ uint32_t lo_bf16(float a, float b, uint32_t hi) {
+  return pack_bf16(a - __uint_as_float(hi << 16), b - __uint_as_float(hi & 0xFFFF0000u));
+}
 // D[tmem] (+)= A[smem] * B[smem]^T, one K = 8 step.  Issued by ONE thread.
 __device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
                                          uint32_t idesc, uint32_t accumulate) {
