@@ -542,7 +542,7 @@ def time_trained_like(args, world):
             "units_on_tensor_cores": rep["units_on_tensor_cores"], "units": rep["units"],
             "plan": "".join({"tf32": "T", "tf32c": "C"}.get(p, "f") for p in rep["plan"]),
             "probe_err_all_tensor_core": rep["err_all_tensor_core"], "probe_err_plan": rep["err_plan"],
-            "note": "W3 = trained-like weights; plan letters: T = tcgen05 kernels, C = tcgen05 with the compensated (fp16 hi + lo) qkv projection, "
+            "note": "W3 = trained-like weights; plan letters: T = tcgen05 kernels, C = compensated tensor-core attention (operand pairs, 3 MMA passes), "
                     "f = fp32 FMA-pipe kernels, in "
                     "execution order: (attention half, MLP half) of each of the 20 NSTBs, then the glue"}
 
@@ -607,7 +607,7 @@ def time_train(args, rank, world):
     t = (torch.rand(B, 1, S, S, generator=g) * 2 - 1).cuda()
     steps = max(args.steps, 5)
     res = {}
-    torch.backends.cudnn.benchmark = True            # the stock-PyTorch glue convolutions pick their fastest plan
+    torch.backends.cudnn.benchmark = True            # (only the discriminator of config 4 still runs cuDNN convolutions)
     torch.backends.cudnn.allow_tf32 = True           # torch's default, which the reference's scripts leave untouched
     for mode in ("eager", "graph"):
         model = build_model().train()

@@ -204,6 +204,14 @@ int b200mar_mlp_tma_fwd(const float* a, float* z_inout,
                         const float* fc2_w, const float* fc2_b,
                         const float* ln_w, const float* ln_b,
                         float* out, long long n_tok, void* stream);
+/* Precision level "tf32c" of the MLP half: the same contract with fc1 / fc2
+ * (models/generator/components/transformer_blocks.py:119) on compensated FP16 hi + lo operand pairs (three MMA
+ * passes, ~22 significant bits) and the 1.5e-7 erf GELU; two workers per persistent CTA.                    */
+int b200mar_mlp_tma_fwd_comp(const float* a, float* z_inout,
+                        const float* fc1_w, const float* fc1_b,
+                        const float* fc2_w, const float* fc2_b,
+                        const float* ln_w, const float* ln_b,
+                        float* out, long long n_tok, void* stream);
 /* ---- backward twins of the fused glue (training path).  Parameter gradients are ACCUMULATED,
  * activation gradients written.
  * final_recon_bwd: backward of b200mar_final_recon_fwd (models/generator/components/reconstruction.py:14-19,

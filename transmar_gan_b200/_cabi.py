@@ -52,6 +52,7 @@ SIGNATURES = {
     "b200mar_wgrad_tc": [_P] * 4 + [_L, _I, _I, _P],
     "b200mar_mlp_tc_fwd": [_P] * 11 + [_I, _L, _P],
     "b200mar_mlp_tma_fwd": [_P] * 9 + [_L, _P],
+    "b200mar_mlp_tma_fwd_comp": [_P] * 9 + [_L, _P],
     "b200mar_final_recon_bwd": [_P] * 19 + [_I] * 5 + [_P],
     "b200mar_cascade_proj_bwd": [_P] * 11 + [_I] * 3 + [_P],
     "b200mar_bottleneck_bwd": [_P] * 23 + [_I] * 3 + [_P],

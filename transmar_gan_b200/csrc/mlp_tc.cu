@@ -61,7 +61,8 @@ __device__ __forceinline__ float hidden_half_scale(float amax, float maxL1, floa
 // contains __syncthreads().
 __device__ __forceinline__ void stage_mlp_weights_f16(const MlpParams& p, __half* sW1, __half* sW2,
                                                       float* sB1, float* sB2, float* sLnW,
-                                                      float* sLnB, float* sMisc, int nthreads) {
+                                                      float* sLnB, float* sMisc, int nthreads,
+                                                      __half* sW1lo = nullptr, __half* sW2lo = nullptr) {
   const int tid = threadIdx.x;
   uint32_t* sMax = reinterpret_cast<uint32_t*>(sMisc + 2);     // [2],[3]: scratch; [4]: maxL1; [5]: maxb
   if (tid < 4) sMax[tid] = 0u;
@@ -92,17 +93,25 @@ __device__ __forceinline__ void stage_mlp_weights_f16(const MlpParams& p, __half
     const int n = idx & 127, kc = idx >> 7;
     const float4* src = reinterpret_cast<const float4*>(p.fc1_w + n * 64 + kc * 8);
     const float4 a = src[0], b = src[1];
-    *reinterpret_cast<uint4*>(sW1 + kc * 1024 + n * 8) =
-        make_uint4(tc::pack_f16(a.x * sc1, a.y * sc1), tc::pack_f16(a.z * sc1, a.w * sc1),
-                   tc::pack_f16(b.x * sc1, b.y * sc1), tc::pack_f16(b.z * sc1, b.w * sc1));
+    const uint4 hv = make_uint4(tc::pack_f16(a.x * sc1, a.y * sc1), tc::pack_f16(a.z * sc1, a.w * sc1),
+                                tc::pack_f16(b.x * sc1, b.y * sc1), tc::pack_f16(b.z * sc1, b.w * sc1));
+    *reinterpret_cast<uint4*>(sW1 + kc * 1024 + n * 8) = hv;
+    if (sW1lo)                                                          // compensated level: lo = fp16(w - hi)
+      *reinterpret_cast<uint4*>(sW1lo + kc * 1024 + n * 8) =
+          make_uint4(tc::lo_f16(a.x * sc1, a.y * sc1, hv.x), tc::lo_f16(a.z * sc1, a.w * sc1, hv.y),
+                     tc::lo_f16(b.x * sc1, b.y * sc1, hv.z), tc::lo_f16(b.z * sc1, b.w * sc1, hv.w));
   }
   for (int idx = tid; idx < 64 * 16; idx += nthreads) {                 // fc2 [64][128]
     const int n = idx & 63, kc = idx >> 6;
     const float4* src = reinterpret_cast<const float4*>(p.fc2_w + n * 128 + kc * 8);
     const float4 a = src[0], b = src[1];
-    *reinterpret_cast<uint4*>(sW2 + kc * 512 + n * 8) =
-        make_uint4(tc::pack_f16(a.x * sc2, a.y * sc2), tc::pack_f16(a.z * sc2, a.w * sc2),
-                   tc::pack_f16(b.x * sc2, b.y * sc2), tc::pack_f16(b.z * sc2, b.w * sc2));
+    const uint4 hv = make_uint4(tc::pack_f16(a.x * sc2, a.y * sc2), tc::pack_f16(a.z * sc2, a.w * sc2),
+                                tc::pack_f16(b.x * sc2, b.y * sc2), tc::pack_f16(b.z * sc2, b.w * sc2));
+    *reinterpret_cast<uint4*>(sW2 + kc * 512 + n * 8) = hv;
+    if (sW2lo)
+      *reinterpret_cast<uint4*>(sW2lo + kc * 512 + n * 8) =
+          make_uint4(tc::lo_f16(a.x * sc2, a.y * sc2, hv.x), tc::lo_f16(a.z * sc2, a.w * sc2, hv.y),
+                     tc::lo_f16(b.x * sc2, b.y * sc2, hv.z), tc::lo_f16(b.z * sc2, b.w * sc2, hv.w));
   }
   if (tid < 128) sB1[tid] = p.fc1_b[tid];
   if (tid < 64) { sB2[tid] = p.fc2_b[tid]; sLnW[tid] = p.ln_w[tid]; sLnB[tid] = p.ln_b[tid]; }
@@ -372,22 +381,35 @@ namespace b200mar {
 // Three workers per CTA, TMEM 160 columns each: D1 [0,128) -> H [0,64) / D2 [64,128), A [128,160).
 constexpr int kTmaWorkers = 3;
 
-struct MlpTmaSmem {                                  // BYTE offsets (weights as MlpTcSmem)
+// COMP (precision level "tf32c" of the MLP half): fc1 and fc2 on fp16 hi + lo operand PAIRS, three MMA passes
+// Ah Wh + Al Wh + Ah Wl into the same fp32 accumulator (~22 significant bits instead of 11), the A&S-erf GELU
+// (1.5e-7) instead of the sigmoid-form fit.  The lo weight copies cost 32 KB and the A / H operand pairs 192 TMEM
+// columns per worker: D1 [0,128) -> H hi | lo per 64-column half ([0,32) | [32,64), [64,96) | [96,128)),
+// A hi | lo [128,160) | [160,192) -> D2 [128,192): TWO workers.
+template <bool COMP>
+struct MlpTmaSmemT {                                 // BYTE offsets (weights as MlpTcSmem)
+  static constexpr int kWorkers = COMP ? 2 : kTmaWorkers;
   static constexpr int oBar = MlpTcSmem::oBar;       // 3 workers x 4 mbarriers + tmem slot
-  static constexpr int oWork = ((oBar + 128 + 1023) / 1024) * 1024;
+  static constexpr int oW1lo = ((oBar + 128 + 127) / 128) * 128;     // COMP: fp16 lo parts, layouts of oW1 / oW2
+  static constexpr int oW2lo = oW1lo + 128 * 64 * 2;
+  static constexpr int oWork = (((COMP ? oW2lo + 64 * 128 * 2 : oBar + 128) + 1023) / 1024) * 1024;
   static constexpr int kWorkBytes = 2 * 32768;       // two swizzled fp32 [128][64] tiles
-  static constexpr int kBytes = oWork + kTmaWorkers * kWorkBytes;
+  static constexpr int kBytes = oWork + kWorkers * kWorkBytes;
   static_assert(kBytes <= 232448, "mlp_tma shared memory exceeds 227 KB");
 };
+using MlpTmaSmem = MlpTmaSmemT<false>;
 
 // S16 = true (precision mode "bf16"): a, z and out are BF16 in HBM; a tile is ONE 16 KB box of [128 rows][64 bf16
 // = 128 B] (128 B swizzle); rows are widened to fp32 on read, out = a + LN2(.) is formed in fp32 and rounded to
 // bf16 once, and z += out is a bf16 bulk reduce-add.
-template <bool S16>
-__global__ void __launch_bounds__(128 * kTmaWorkers, 1)
+template <bool S16, bool COMP = false>
+__global__ void __launch_bounds__(128 * MlpTmaSmemT<COMP>::kWorkers, 1)
 mlp_tma_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapZ,
                    const __grid_constant__ CUtensorMap mapOut, MlpParams p) {
   using L = MlpTcSmem;
+  using MlpTmaSmem = MlpTmaSmemT<COMP>;
+  constexpr int kTmaWorkers = MlpTmaSmem::kWorkers;
+  constexpr uint32_t kTStride = COMP ? 192 : 160, kTA = 128, kTD2 = COMP ? 128 : 64;
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   __half* sW1 = reinterpret_cast<__half*>(smem_raw + L::oW1);
   __half* sW2 = reinterpret_cast<__half*>(smem_raw + L::oW2);
@@ -406,7 +428,9 @@ mlp_tma_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
   uint64_t* bar1 = full + 2;
   uint64_t* bar2 = full + 3;
 
-  stage_mlp_weights_f16(p, sW1, sW2, sB1, sB2, sLnW, sLnB, sMisc, 128 * kTmaWorkers);
+  stage_mlp_weights_f16(p, sW1, sW2, sB1, sB2, sLnW, sLnB, sMisc, 128 * kTmaWorkers,
+                        COMP ? reinterpret_cast<__half*>(smem_raw + MlpTmaSmem::oW1lo) : nullptr,
+                        COMP ? reinterpret_cast<__half*>(smem_raw + MlpTmaSmem::oW2lo) : nullptr);
   if (tid == 0) {
     for (int i = 0; i < 4 * kTmaWorkers; ++i) tc::mbar_init(bars + i, 1);
     tc::fence_barrier_init();
@@ -418,11 +442,13 @@ mlp_tma_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
   __syncthreads();
   tc::tc_fence_after();
 
-  const uint32_t tbase = *tmem_slot + wk * 160;
+  const uint32_t tbase = *tmem_slot + wk * kTStride;
   const uint32_t lane_addr = (uint32_t)(wq * 32) << 16;
   constexpr uint32_t kI128 = tc::idesc_f16(128, 128), kI64 = tc::idesc_f16(128, 64);
   const uint64_t dW1 = tc::smem_desc(tc::smem_u32(sW1), 2048, 128),
-                 dW2 = tc::smem_desc(tc::smem_u32(sW2), 1024, 128);
+                 dW2 = tc::smem_desc(tc::smem_u32(sW2), 1024, 128),
+                 dW1lo = tc::smem_desc(tc::smem_u32(smem_raw + MlpTmaSmem::oW1lo), 2048, 128),
+                 dW2lo = tc::smem_desc(tc::smem_u32(smem_raw + MlpTmaSmem::oW2lo), 1024, 128);
   const int row = wq * 32 + lane;
   const float w1inv = sMisc[0], w2inv = sMisc[1];
   const bool leader = wq == 0 && lane == 0;          // bulk groups are per thread: one fixed thread
@@ -481,7 +507,14 @@ mlp_tma_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
 #pragma unroll
       for (int i = 0; i < 32; ++i)
         hp[i] = __uint_as_float(tc::pack_f16(x[2 * i] * sc, x[2 * i + 1] * sc));
-      tc::tmem_st32(tbase + 128 + lane_addr, hp);
+      tc::tmem_st32(tbase + kTA + lane_addr, hp);
+      if constexpr (COMP) {
+        float lp[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+          lp[i] = __uint_as_float(tc::lo_f16(x[2 * i] * sc, x[2 * i + 1] * sc, __float_as_uint(hp[i])));
+        tc::tmem_st32(tbase + kTA + 32 + lane_addr, lp);
+      }
     }
     tc::tmem_wait_st();
     tc::tc_fence_before();
@@ -492,8 +525,13 @@ mlp_tma_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
       tc::tc_fence_after();
       if (tc::elect_one()) {
 #pragma unroll
-        for (int ks = 0; ks < 4; ++ks)
-          tc::mma_f16_ts(tbase, tbase + 128 + ks * 8, dW1 + ks * 256, kI128, ks > 0);
+        for (int ks = 0; ks < 4; ++ks) {
+          tc::mma_f16_ts(tbase, tbase + kTA + ks * 8, dW1 + ks * 256, kI128, ks > 0);
+          if constexpr (COMP) {
+            tc::mma_f16_ts(tbase, tbase + kTA + 32 + ks * 8, dW1 + ks * 256, kI128, 1u);
+            tc::mma_f16_ts(tbase, tbase + kTA + ks * 8, dW1lo + ks * 256, kI128, 1u);
+          }
+        }
         tc::mma_commit(bar1);
       }
       __syncwarp();
@@ -517,13 +555,27 @@ mlp_tma_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
       tc::tmem_ld64(tbase + lane_addr + half * 64, v);
       float hp[32];
       const float* b1 = sB1 + half * 64;
+      if constexpr (COMP) {                           // exact-erf GELU, hidden row as an fp16 hi | lo pair
+        float lp[32];
 #pragma unroll
-      for (int c = 0; c < 64; c += 2) {
-        const float g0 = gelu_sig(fmaf(v[c], ainv, b1[c]), hfull);
-        const float g1 = gelu_sig(fmaf(v[c + 1], ainv, b1[c + 1]), hfull);
-        hp[c >> 1] = __uint_as_float(tc::pack_f16(g0, g1));
+        for (int c = 0; c < 64; c += 2) {
+          const float g0 = gelu_fast(fmaf(v[c], ainv, b1[c]), hhalf);
+          const float g1 = gelu_fast(fmaf(v[c + 1], ainv, b1[c + 1]), hhalf);
+          const uint32_t hv = tc::pack_f16(g0, g1);
+          hp[c >> 1] = __uint_as_float(hv);
+          lp[c >> 1] = __uint_as_float(tc::lo_f16(g0, g1, hv));
+        }
+        tc::tmem_st32(tbase + lane_addr + half * 64, hp);
+        tc::tmem_st32(tbase + lane_addr + half * 64 + 32, lp);
+      } else {
+#pragma unroll
+        for (int c = 0; c < 64; c += 2) {
+          const float g0 = gelu_sig(fmaf(v[c], ainv, b1[c]), hfull);
+          const float g1 = gelu_sig(fmaf(v[c + 1], ainv, b1[c + 1]), hfull);
+          hp[c >> 1] = __uint_as_float(tc::pack_f16(g0, g1));
+        }
+        tc::tmem_st32(tbase + lane_addr + half * 32, hp);
       }
-      tc::tmem_st32(tbase + lane_addr + half * 32, hp);
     }
     tc::tmem_wait_st();
     PROF(4);
@@ -534,8 +586,16 @@ mlp_tma_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
       tc::tc_fence_after();
       if (tc::elect_one()) {
 #pragma unroll
-        for (int ks = 0; ks < 8; ++ks)
-          tc::mma_f16_ts(tbase + 64, tbase + ks * 8, dW2 + ks * 128, kI64, ks > 0);
+        for (int ks = 0; ks < 8; ++ks) {
+          if constexpr (COMP) {
+            const uint32_t ah = tbase + (ks < 4 ? 0 : 64) + (ks & 3) * 8;
+            tc::mma_f16_ts(tbase + kTD2, ah, dW2 + ks * 128, kI64, ks > 0);
+            tc::mma_f16_ts(tbase + kTD2, ah + 32, dW2 + ks * 128, kI64, 1u);
+            tc::mma_f16_ts(tbase + kTD2, ah, dW2lo + ks * 128, kI64, 1u);
+          } else {
+            tc::mma_f16_ts(tbase + 64, tbase + ks * 8, dW2 + ks * 128, kI64, ks > 0);
+          }
+        }
         tc::mma_commit(bar2);
       }
       __syncwarp();
@@ -546,7 +606,7 @@ mlp_tma_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
     // ---- LayerNorm(norm2) in registers; out = a + LN(.) in place over the a tile
     {
       float y[64];
-      tc::tmem_ld64(tbase + lane_addr + 64, y);
+      tc::tmem_ld64(tbase + lane_addr + kTD2, y);
       float mean4[4] = {0.f, 0.f, 0.f, 0.f};          // four partial sums: short dependency chains
       const float yinv = w2inv * hinv;
 #pragma unroll
@@ -658,6 +718,38 @@ extern "C" int b200mar_mlp_tma_fwd(const float* a, float* z_inout, const float* 
   long long grid = (ntile + kTmaWorkers - 1) / kTmaWorkers;
   if (grid > sm_count()) grid = sm_count();
   mlp_tma_fwd_kernel<false><<<(int)grid, 128 * kTmaWorkers, smem, (cudaStream_t)stream>>>(mA, mZ, mO, p);
+  B200MAR_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// Precision level "tf32c" of the MLP half: same contract as b200mar_mlp_tma_fwd, fc1 / fc2 on compensated fp16
+// hi + lo operand pairs and the 1.5e-7 erf GELU (two workers per SM).
+extern "C" int b200mar_mlp_tma_fwd_comp(const float* a, float* z_inout, const float* fc1_w,
+                                        const float* fc1_b, const float* fc2_w, const float* fc2_b,
+                                        const float* ln_w, const float* ln_b, float* out,
+                                        long long n_tok, void* stream) {
+  using namespace b200mar;
+  if (n_tok <= 0 || n_tok % kTok || n_tok * 1 > 0x7fffffffLL) return -1;
+  if (!out && !z_inout) return -1;
+  MlpParams p{};
+  p.a = a; p.z = z_inout; p.fc1_w = fc1_w; p.fc1_b = fc1_b; p.fc2_w = fc2_w; p.fc2_b = fc2_b;
+  p.ln_w = ln_w; p.ln_b = ln_b; p.out = out; p.zsum = z_inout; p.n_tok = n_tok;
+  CUtensorMap mA, mZ, mO;
+  if (int rc = tma::encode_rows64(&mA, a, n_tok)) return rc;
+  if (int rc = tma::encode_rows64(&mZ, z_inout ? z_inout : a, n_tok)) return rc;
+  if (int rc = tma::encode_rows64(&mO, out ? out : a, n_tok)) return rc;
+  using S = MlpTmaSmemT<true>;
+  const size_t smem = S::kBytes;
+  static DeviceOnce configured;
+  if (configured.first()) {
+    B200MAR_CHECK(cudaFuncSetAttribute(mlp_tma_fwd_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)smem));
+    configured.done();
+  }
+  const long long ntile = (n_tok + 127) / 128;
+  long long grid = (ntile + S::kWorkers - 1) / S::kWorkers;
+  if (grid > sm_count()) grid = sm_count();
+  mlp_tma_fwd_kernel<false, true><<<(int)grid, 128 * S::kWorkers, smem, (cudaStream_t)stream>>>(mA, mZ, mO, p);
   B200MAR_CHECK(cudaGetLastError());
   return 0;
 }

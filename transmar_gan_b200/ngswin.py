@@ -382,10 +382,11 @@ class NGswin(nn.Module):
         representative slices `x` [B,1,H,W] (recommended for real data), which units may run on the tensor cores (FP16 / TF32 operands)
         without moving the model output by more than `tol` (default 0.4 of the 1e-3 parity gate, the margin
         covering other inputs and larger images) relative to the all-fp32 kernels, and store that plan:
-        it is what precision "auto" executes.  An attention half that fails at 11-bit operands is tried at the
-        compensated level "tf32c" (qkv projection on fp16 hi + lo pairs, still tcgen05) before it falls back to
-        the fp32 FMA-pipe kernel.  All units pass on init-scale weights; trained-like weights need "tf32c" for
-        the first block; the W2 stress set (x100 cosine logits) sends its leading blocks to fp32.  Returns the report dict (also `.precision_report`)."""
+        it is what precision "auto" executes.  A block half that fails at 11-bit operands is tried at the
+        compensated level "tf32c" (every GEMM of the half on operand pairs, three MMA passes, still tcgen05,
+        fp32-level error) before it falls back to the fp32 FMA-pipe kernel.  All units pass on init-scale weights;
+        trained-like weights need "tf32c" for the first block's attention; the W2 stress set (x100 cosine logits)
+        needs it for its leading blocks.  Returns the report dict (also `.precision_report`)."""
         p0 = next(self.parameters())
         if not p0.is_cuda:
             raise RuntimeError("calibrate_precision: move the module to a B200 first (there is no CPU path)")
@@ -404,7 +405,7 @@ class NGswin(nn.Module):
         def dist(ys, refs):
             return max((y - r).abs().max().item() for y, r in zip(ys, refs))
 
-        n_attn = 2 * len(self._units())                     # even indices below this are attention halves
+        n_blk = 2 * len(self._units())                      # units below this are block halves (the last is the glue)
 
         try:
             ref = run(["fp32"] * n)
@@ -419,9 +420,8 @@ class NGswin(nn.Module):
                     return dist(run(trial), ref)
 
                 marginal = [alone(u, "tf32") for u in range(n)]
-                # attention halves that fail at 11-bit operands get a second chance at the compensated level
-                marginal_c = [alone(u, "tf32c") if (u < n_attn and u % 2 == 0 and marginal[u] > tol) else None
-                              for u in range(n)]
+                # block halves that fail at 11-bit operands get a second chance at the compensated level
+                marginal_c = [alone(u, "tf32c") if (u < n_blk and marginal[u] > tol) else None for u in range(n)]
                 level = ["tf32" if marginal[u] <= tol else ("tf32c" if marginal_c[u] is not None else None)
                          for u in range(n)]
                 cost = [marginal[u] if level[u] == "tf32" else marginal_c[u] for u in range(n)]
@@ -429,8 +429,7 @@ class NGswin(nn.Module):
                 for u in sorted((u for u in range(n) if level[u]), key=lambda i: cost[i]):
                     if cost[u] > tol:
                         break
-                    for lv in ([level[u]] if level[u] == "tf32c" or not (u < n_attn and u % 2 == 0)
-                               else ["tf32", "tf32c"]):
+                    for lv in ([level[u]] if level[u] == "tf32c" or u >= n_blk else ["tf32", "tf32c"]):
                         trial = list(plan)
                         trial[u] = lv
                         e = dist(run(trial), ref)

@@ -83,12 +83,12 @@ _UNIT: List[Tuple[Optional[str], Optional[str]]] = []
 
 class unit_precision:
     """Context manager: inside, the attention half and the MLP half of an NSTB compute in `attn` / `mlp`
-    ("tf32" / "fp32"; None = the surrounding mode).  The attention half has a third level, "tf32c": the
-    tensor-core kernel with the qkv projection on compensated fp16 hi + lo operand pairs."""
+    ("tf32" / "tf32c" / "fp32"; None = the surrounding mode).  "tf32c" is the compensated tensor-core level: every
+    GEMM of the half on operand pairs, three MMA passes, fp32-level error."""
 
     def __init__(self, attn: Optional[str], mlp: Optional[str]):
-        if attn not in (None, "tf32", "tf32c", "fp32") or mlp not in (None, "tf32", "fp32"):
-            raise ValueError("unit_precision takes 'tf32', 'fp32' or None (attention half also 'tf32c')")
+        if attn not in (None, "tf32", "tf32c", "fp32") or mlp not in (None, "tf32", "tf32c", "fp32"):
+            raise ValueError("unit_precision takes 'tf32', 'tf32c', 'fp32' or None")
         self.modes = (attn, mlp)
 
     def __enter__(self):
@@ -467,18 +467,19 @@ def _(a, z, fc1_w, fc1_b, fc2_w, fc2_b, ln_w, ln_b, want_out, want_zsum, a_is_de
 
 @torch.library.custom_op(f"{_NS}::mlp_tma_fwd_", mutates_args=("z",))
 def mlp_tma_fwd_(a: Tensor, z: Optional[Tensor], fc1_w: Tensor, fc1_b: Tensor, fc2_w: Tensor,
-                 fc2_b: Tensor, ln_w: Tensor, ln_b: Tensor, want_out: bool) -> Tensor:
+                 fc2_b: Tensor, ln_w: Tensor, ln_b: Tensor, want_out: bool, comp: bool = False) -> Tensor:
     """In-place block tail: out = a + LN2(mlp(a)) (returned if want_out) and z += out (if z is given),
-    i.e. z becomes the next block's input.  TMA-fed variant of mlp_tc_fwd (same arithmetic)."""
+    i.e. z becomes the next block's input.  TMA-fed variant of mlp_tc_fwd (same arithmetic).
+    comp=True (precision level "tf32c"): fc1 / fc2 on compensated fp16 hi + lo operand pairs."""
     _chk(a, z, fc1_w, fc1_b, fc2_w, fc2_b, ln_w, ln_b)
     out = torch.empty_like(a) if want_out else a.new_empty(0)
-    _call("mlp_tma_fwd", _p(a), _p(z), _p(fc1_w), _p(fc1_b), _p(fc2_w), _p(fc2_b), _p(ln_w), _p(ln_b),
+    _call("mlp_tma_fwd_comp" if comp else "mlp_tma_fwd", _p(a), _p(z), _p(fc1_w), _p(fc1_b), _p(fc2_w), _p(fc2_b), _p(ln_w), _p(ln_b),
           _p(out), a.numel() // 64, _stream(), meta=(a.numel() // 64,))
     return out
 
 
 @mlp_tma_fwd_.register_fake
-def _(a, z, fc1_w, fc1_b, fc2_w, fc2_b, ln_w, ln_b, want_out):
+def _(a, z, fc1_w, fc1_b, fc2_w, fc2_b, ln_w, ln_b, want_out, comp=False):
     return torch.empty_like(a) if want_out else a.new_empty(0)
 
 
@@ -886,7 +887,8 @@ def nstb_infer_mixed_(z: Tensor, ph: int, pw: int, nh: int, shift: int, want_out
         return mlp_fwd(a, z if want_zsum else None, P[18], P[19], P[20], P[21], P[22], P[23], want_out, want_zsum)
     if want_zsum and not private:
         z = z.clone()
-    out = mlp_tma_fwd_(a, z if want_zsum else None, P[18], P[19], P[20], P[21], P[22], P[23], want_out)
+    out = mlp_tma_fwd_(a, z if want_zsum else None, P[18], P[19], P[20], P[21], P[22], P[23], want_out,
+                       mlp_mode == "tf32c")
     return out, (z if want_zsum else out.new_empty(0))
 
 
@@ -921,7 +923,8 @@ class NSTBFunction(torch.autograd.Function):
             # survive for the backward, so the within-stage sum is a copy of z that the kernel's bulk
             # reduce-add turns into z + out
             zsum = z.clone() if want_zsum else z.new_empty(0)
-            out = mlp_tma_fwd_(a, zsum if want_zsum else None, P[18], P[19], P[20], P[21], P[22], P[23], want_out)
+            out = mlp_tma_fwd_(a, zsum if want_zsum else None, P[18], P[19], P[20], P[21], P[22], P[23], want_out,
+                               mm == "tf32c")
         else:
             out, zsum = mlp_fwd(a, z if want_zsum else None, P[18], P[19], P[20], P[21], P[22], P[23],
                                 want_out, want_zsum)
