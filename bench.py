@@ -507,18 +507,22 @@ def time_bf16_stream(model, args, world, y_default):
                     "inference only; not the headline (outside the 1e-3 gate by construction)"}
 
 
-def time_trained_like(args, world):
+def time_trained_like(args, world, kind="W3"):
     """The default mode on TRAINED-LIKE weights (W3: the unmodified reference trained for 400 steps on structured
-    slices, tests/golden/w3_trained.pt): the measured precision plan sends the unit(s) that 11-bit operands cannot
-    carry within the parity gate to the fp32 kernels, which costs throughput.  Reported so that the
-    W1 headline is not mistaken for what a trained checkpoint gets; None if the fixture is absent."""
-    path = os.path.join(ROOT, "tests", "golden", "w3_trained.pt")
-    if not os.path.isfile(path):
-        return None
+    slices, tests/golden/w3_trained.pt) or on the W2 STRESS set: the measured precision plan runs the unit(s) that
+    11-bit operands cannot carry within the parity gate at the compensated tensor-core level (or, failing that, on the
+    fp32 kernels), which costs throughput.  Reported so that the W1 headline is not mistaken for what
+    a trained checkpoint gets; None if the fixture is absent."""
     import transmar_gan_b200 as T
-    gold = torch.load(path, weights_only=False)
     m = T.NGswin()
-    m.load_state_dict(gold["state_dict"], strict=True)
+    if kind == "W3":
+        path = os.path.join(ROOT, "tests", "golden", "w3_trained.pt")
+        if not os.path.isfile(path):
+            return None
+        m.load_state_dict(torch.load(path, weights_only=False)["state_dict"], strict=True)
+    else:
+        from oracle import ngswin_oracle as O          # weight recipe only (the oracle's synthetic W2 set)
+        m.load_state_dict(O.synthetic_state_dict(kind, seed=1), strict=True)
     m = m.cuda().eval()
     B, S = args.batch, args.size
     g = torch.Generator().manual_seed(999 + int(os.environ.get("RANK", "0")))
@@ -542,9 +546,11 @@ def time_trained_like(args, world):
             "units_on_tensor_cores": rep["units_on_tensor_cores"], "units": rep["units"],
             "plan": "".join({"tf32": "T", "tf32c": "C"}.get(p, "f") for p in rep["plan"]),
             "probe_err_all_tensor_core": rep["err_all_tensor_core"], "probe_err_plan": rep["err_plan"],
-            "note": "W3 = trained-like weights; plan letters: T = tcgen05 kernels, C = compensated tensor-core attention (operand pairs, 3 MMA passes), "
-                    "f = fp32 FMA-pipe kernels, in "
-                    "execution order: (attention half, MLP half) of each of the 20 NSTBs, then the glue"}
+            "units_compensated": rep.get("units_compensated", 0), "weights": kind,
+            "note": "W3 = trained-like weights, W2 = stress set (weights x5, logit scales at the ln 100 clamp); plan "
+                    "letters: T = tcgen05 kernels at 11-bit operands, C = compensated tensor-core kernel (operand "
+                    "pairs, 3 MMA passes, fp32-level error), f = fp32 FMA-pipe kernel, in execution order: "
+                    "(attention half, MLP half) of each of the 20 NSTBs, then the glue"}
 
 
 def time_highres(model, args, world):
@@ -736,6 +742,7 @@ def main():
     bf16_stream = time_bf16_stream(model, args, world, y_default)
     del y_default
     trained_like = None if args.no_highres else time_trained_like(args, world)
+    stress_set = None if args.no_highres else time_trained_like(args, world, kind="W2")
     highres = None if args.no_highres else time_highres(model, args, world)
     train = None if args.no_train else time_train(args, rank, world)
     train_gan = None if (args.no_train or args.no_gan) else time_train_gan(args, rank, world)
@@ -843,7 +850,7 @@ def main():
                              "local memory and L2 misses of the residual re-read, see profiles/r01_summary.md"},
         "cpu_baseline": cpu,
         "bf16_stream": bf16_stream,
-        "trained_like": trained_like,
+        "trained_like": trained_like, "stress_set": stress_set,
         "highres": highres,
         "train": train,
         "train_gan": train_gan,

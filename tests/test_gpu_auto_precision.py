@@ -77,15 +77,17 @@ def test_default_precision_meets_gate(models, golden_outputs, golden_w3, kind, s
 
 
 def test_plan_w1_all_tensor_cores_w2_not(models):
-    """The benchmarked configuration (W1) runs every unit on tcgen05; the stress set does not (its
-    all-tensor-core probe error exceeds the calibration tolerance); every plan's own probe error is within it."""
+    """The benchmarked configuration (W1) runs every unit on tcgen05 at 11-bit operands; the stress set cannot (its
+    all-11-bit probe error exceeds the calibration tolerance) and moves units to the compensated level / the fp32
+    kernels; every plan's own probe error is within the tolerance."""
     x = O.synthetic_input(1, 64, 64, seed=999).cuda()
     for kind in ("W1", "W2", "W3"):
         with torch.no_grad():
             models[kind](x)
     r1, r2, r3 = (models[k].precision_report for k in ("W1", "W2", "W3"))
-    assert r1["units_on_tensor_cores"] == r1["units"] == 41, r1
-    assert r2["err_all_tensor_core"] > r2["tol"] and r2["units_on_tensor_cores"] < 41, r2
+    assert r1["units_on_tensor_cores"] == r1["units"] == 41 and r1["units_compensated"] == 0, r1
+    assert r2["err_all_tensor_core"] > r2["tol"], r2
+    assert sum(p == "tf32" for p in r2["plan"]) < 41 and r2["units_compensated"] + 41 - r2["units_on_tensor_cores"] >= 3, r2
     for r in (r1, r2, r3):
         assert r["err_plan"] <= r["tol"]
     print(f"[auto] W3 plan: {r3['units_on_tensor_cores']}/41 units on tcgen05, probe err all-tc "
@@ -138,6 +140,12 @@ def test_mixed_plan_plumbing(models, golden_outputs):
         assert (y - ref).abs().max().item() < GATE and (y2 - ref).abs().max().item() < GATE
         with torch.no_grad():
             assert torch.equal(m._forward_planned(x).cpu(), y2)      # repeatable, input not clobbered
+        # all three levels interleaved (period 3 against the (attention, MLP) period 2: every pairing occurs)
+        with torch.no_grad():
+            m._set_plan([("tf32", "tf32c", "fp32")[i % 3] for i in range(40)] + ["tf32"])
+            y3 = m._forward_planned(x).cpu()
+            assert torch.equal(m._forward_planned(x).cpu(), y3)
+        assert (y3 - ref).abs().max().item() < GATE
 
 
 def test_stress_set_at_slice_size(T):
@@ -164,7 +172,7 @@ def test_recalibrates_when_weights_change(T):
         assert m.precision_report["units_on_tensor_cores"] == 41
         m.load_state_dict(O.synthetic_state_dict("W2", seed=1), strict=True)
         m(x)
-    assert m.precision_report["units_on_tensor_cores"] < 41
+    assert sum(p == "tf32" for p in m.precision_report["plan"]) < 41
 
 
 def test_training_in_default_precision_matches_reference_gradients(T, golden_w3):
