@@ -338,10 +338,18 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
   // A window whose 8x8 token block is contiguous in the grid (all windows when shift = 0; all but the
   // last window row / column when shifted) moves by TMA; the cyclically wrapped ones are rare
   // (~4 %) and are read / written by their row threads directly.
+  // (window index -> (w, h, b) by multiply-shift: the tile loop contains no integer division)
+  const FastDiv fdWW = make_fastdiv((uint32_t)g.ww), fdWWH = make_fastdiv((uint32_t)(g.ww * g.wh));
+  auto win_pos = [&](int win, int& w, int& h, int& b) {
+    b = (int)fdiv((uint32_t)win, fdWWH);
+    const int rem = win - b * (g.ww * g.wh);
+    h = (int)fdiv((uint32_t)rem, fdWW);
+    w = rem - h * g.ww;
+  };
   auto tma_window = [&](int win, int& x0, int& y0, int& b) -> bool {
     if (win >= nwin) return false;
-    const int w = win % g.ww, h = (win / g.ww) % g.wh;
-    b = win / (g.ww * g.wh);
+    int w, h;
+    win_pos(win, w, h, b);
     x0 = w * kWin + g.shift;
     y0 = h * kWin + g.shift;
     return x0 + kWin <= g.pw && y0 + kWin <= g.ph;
@@ -413,6 +421,8 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
     const bool wvalid = win < nwin;
     int wx0, wy0, wb;
     const bool use_tma = tma_window(win, wx0, wy0, wb);
+    int pw_ = 0, ph_ = 0, pb_ = 0;                  // (w, h, b) of this thread's window
+    if (wvalid) win_pos(win, pw_, ph_, pb_);
     bool any_tma;
     {
       int d0, d1, d2;
@@ -427,7 +437,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
       //      before the fp16 conversion and the exact inverse is applied to the fp32 accumulators.
       float x[64];
       if (wvalid) {
-        const Slot sl = slot_of(g, win, ltok);
+        const Slot sl = slot_of(g, pw_, ph_, pb_, ltok);
         tok = sl.tok;
         sReg[row] = sl.region;
         const float4* cp = reinterpret_cast<const float4*>(p.ctx + (size_t)sl.cwin * 64);
@@ -497,8 +507,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
     }
     // ---- shift mask of this row as a 64-bit key set (analytic 9-region rule)
     uint32_t mlo = 0, mhi = 0;
-    if (p.shift > 0 && wvalid &&
-        (win % g.ww == g.ww - 1 || (win / g.ww) % g.wh == g.wh - 1)) {   // only the last window row / column
+    if (p.shift > 0 && wvalid && (pw_ == g.ww - 1 || ph_ == g.wh - 1)) {   // only the last window row / column
       const int rg = sReg[row];
       const int* reg = sReg + wsel * 64;
 #pragma unroll

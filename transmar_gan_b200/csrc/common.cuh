@@ -77,6 +77,36 @@ __device__ __forceinline__ Slot slot_of(const Geom& g, int win, int t) {
   s.region = rid * 3 + cid;
   return s;
 }
+// The same for a window given by its coordinates (callers that decompose `win` without integer divisions).
+__device__ __forceinline__ Slot slot_of(const Geom& g, int w, int h, int b, int t) {
+  const int R = h * kWin + (t >> 3);
+  const int C = w * kWin + (t & 7);
+  int r = R + g.shift; if (r >= g.ph) r -= g.ph;
+  int c = C + g.shift; if (c >= g.pw) c -= g.pw;
+  Slot s;
+  s.tok = ((long long)b * g.ph + r) * g.pw + c;
+  s.cwin = (b * g.wh + (r >> 3)) * g.ww + (c >> 3);
+  const int rid = R < g.ph - kWin ? 0 : (R < g.ph - kShift ? 1 : 2);
+  const int cid = C < g.pw - kWin ? 0 : (C < g.pw - kShift ? 1 : 2);
+  s.region = rid * 3 + cid;
+  return s;
+}
+// Division by a loop-invariant divisor without the ~25-instruction IDIV sequence (3 of them on the XU pipe):
+// Granlund-Montgomery round-up multiplier, exact for every 32-bit n and d >= 1.
+struct FastDiv { uint32_t m, s1, s2; };
+__host__ __device__ inline FastDiv make_fastdiv(uint32_t d) {
+  uint32_t l = 0;
+  while ((1ull << l) < d) ++l;
+  FastDiv f;
+  f.m = (uint32_t)((((1ull << l) - d) << 32) / d + 1);
+  f.s1 = l < 1u ? l : 1u;
+  f.s2 = l > 0u ? l - 1u : 0u;
+  return f;
+}
+__device__ __forceinline__ uint32_t fdiv(uint32_t n, const FastDiv& f) {
+  const uint32_t t = __umulhi(f.m, n);
+  return (t + ((n - t) >> f.s1)) >> f.s2;
+}
 // relative-position index of (query p, key q) inside an 8x8 window, attention.py:9-18
 __device__ __forceinline__ int rel_index(int p, int q) {
   return ((p >> 3) - (q >> 3) + 7) * 15 + ((p & 7) - (q & 7) + 7);
