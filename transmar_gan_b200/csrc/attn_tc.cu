@@ -338,18 +338,11 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
   // A window whose 8x8 token block is contiguous in the grid (all windows when shift = 0; all but the
   // last window row / column when shifted) moves by TMA; the cyclically wrapped ones are rare
   // (~4 %) and are read / written by their row threads directly.
-  // (window index -> (w, h, b) by multiply-shift: the tile loop contains no integer division)
-  const FastDiv fdWW = make_fastdiv((uint32_t)g.ww), fdWWH = make_fastdiv((uint32_t)(g.ww * g.wh));
-  auto win_pos = [&](int win, int& w, int& h, int& b) {
-    b = (int)fdiv((uint32_t)win, fdWWH);
-    const int rem = win - b * (g.ww * g.wh);
-    h = (int)fdiv((uint32_t)rem, fdWW);
-    w = rem - h * g.ww;
-  };
+  // (window index -> (w, h, b) by multiply-shift, common.cuh: the tile loop contains no integer division)
   auto tma_window = [&](int win, int& x0, int& y0, int& b) -> bool {
     if (win >= nwin) return false;
     int w, h;
-    win_pos(win, w, h, b);
+    win_pos(g, win, w, h, b);
     x0 = w * kWin + g.shift;
     y0 = h * kWin + g.shift;
     return x0 + kWin <= g.pw && y0 + kWin <= g.ph;
@@ -422,7 +415,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
     int wx0, wy0, wb;
     const bool use_tma = tma_window(win, wx0, wy0, wb);
     int pw_ = 0, ph_ = 0, pb_ = 0;                  // (w, h, b) of this thread's window
-    if (wvalid) win_pos(win, pw_, ph_, pb_);
+    if (wvalid) win_pos(g, win, pw_, ph_, pb_);
     bool any_tma;
     {
       int d0, d1, d2;

@@ -46,51 +46,6 @@ struct DeviceOnce {
   } while (0)
 
 // ---------------------------------------------------------------- window geometry
-struct Geom {
-  int B, ph, pw, wh, ww, shift;
-};
-__host__ __device__ inline Geom make_geom(int B, int ph, int pw, int shift) {
-  Geom g; g.B = B; g.ph = ph; g.pw = pw; g.wh = ph / kWin; g.ww = pw / kWin; g.shift = shift;
-  return g;
-}
-// Window `win` = (b,h,w) row-major, slot t = 8*i + j of the (shifted) window.
-// Source row/col in the unshifted token grid: r=(8h+i+s)%ph, c=(8w+j+s)%pw
-// (window_utils.py:134-145: context added per unshifted window, then roll(-s,-s), then partition).
-struct Slot {
-  long long tok;   // flat token index  b*ph*pw + r*pw + c
-  int cwin;        // flat source window index b*wh*ww + (r/8)*ww + c/8
-  int region;      // 9-region id of the shifted-frame position (transformer_blocks.py:63-76)
-};
-__device__ __forceinline__ Slot slot_of(const Geom& g, int win, int t) {
-  const int w = win % g.ww;
-  const int h = (win / g.ww) % g.wh;
-  const int b = win / (g.ww * g.wh);
-  const int R = h * kWin + (t >> 3);
-  const int C = w * kWin + (t & 7);
-  int r = R + g.shift; if (r >= g.ph) r -= g.ph;
-  int c = C + g.shift; if (c >= g.pw) c -= g.pw;
-  Slot s;
-  s.tok = ((long long)b * g.ph + r) * g.pw + c;
-  s.cwin = (b * g.wh + (r >> 3)) * g.ww + (c >> 3);
-  const int rid = R < g.ph - kWin ? 0 : (R < g.ph - kShift ? 1 : 2);
-  const int cid = C < g.pw - kWin ? 0 : (C < g.pw - kShift ? 1 : 2);
-  s.region = rid * 3 + cid;
-  return s;
-}
-// The same for a window given by its coordinates (callers that decompose `win` without integer divisions).
-__device__ __forceinline__ Slot slot_of(const Geom& g, int w, int h, int b, int t) {
-  const int R = h * kWin + (t >> 3);
-  const int C = w * kWin + (t & 7);
-  int r = R + g.shift; if (r >= g.ph) r -= g.ph;
-  int c = C + g.shift; if (c >= g.pw) c -= g.pw;
-  Slot s;
-  s.tok = ((long long)b * g.ph + r) * g.pw + c;
-  s.cwin = (b * g.wh + (r >> 3)) * g.ww + (c >> 3);
-  const int rid = R < g.ph - kWin ? 0 : (R < g.ph - kShift ? 1 : 2);
-  const int cid = C < g.pw - kWin ? 0 : (C < g.pw - kShift ? 1 : 2);
-  s.region = rid * 3 + cid;
-  return s;
-}
 // Division by a loop-invariant divisor without the ~25-instruction IDIV sequence (3 of them on the XU pipe):
 // Granlund-Montgomery round-up multiplier, exact for every 32-bit n and d >= 1.
 struct FastDiv { uint32_t m, s1, s2; };
@@ -106,6 +61,62 @@ __host__ __device__ inline FastDiv make_fastdiv(uint32_t d) {
 __device__ __forceinline__ uint32_t fdiv(uint32_t n, const FastDiv& f) {
   const uint32_t t = __umulhi(f.m, n);
   return (t + ((n - t) >> f.s1)) >> f.s2;
+}
+struct Geom {
+  int B, ph, pw, wh, ww, shift;
+  FastDiv fww, fwwh;             // division by ww and by ww * wh (window index -> (w, h, b))
+};
+__host__ __device__ inline Geom make_geom(int B, int ph, int pw, int shift) {
+  Geom g; g.B = B; g.ph = ph; g.pw = pw; g.wh = ph / kWin; g.ww = pw / kWin; g.shift = shift;
+  g.fww = make_fastdiv((uint32_t)g.ww); g.fwwh = make_fastdiv((uint32_t)(g.ww * g.wh));
+  return g;
+}
+// window index -> (w, h, b), row-major over (b, h, w); no integer division
+struct WinDiv {                  // for kernels that carry (wh, ww) instead of a Geom
+  int ww, wwh;
+  FastDiv fww, fwwh;
+};
+__host__ __device__ inline WinDiv make_windiv(int wh, int ww) {
+  WinDiv d; d.ww = ww; d.wwh = ww * wh; d.fww = make_fastdiv((uint32_t)ww); d.fwwh = make_fastdiv((uint32_t)(ww * wh));
+  return d;
+}
+__device__ __forceinline__ void win_pos(const WinDiv& d, int win, int& w, int& h, int& b) {
+  b = (int)fdiv((uint32_t)win, d.fwwh);
+  const int rem = win - b * d.wwh;
+  h = (int)fdiv((uint32_t)rem, d.fww);
+  w = rem - h * d.ww;
+}
+__device__ __forceinline__ void win_pos(const Geom& g, int win, int& w, int& h, int& b) {
+  b = (int)fdiv((uint32_t)win, g.fwwh);
+  const int rem = win - b * (g.ww * g.wh);
+  h = (int)fdiv((uint32_t)rem, g.fww);
+  w = rem - h * g.ww;
+}
+// Window `win` = (b,h,w) row-major, slot t = 8*i + j of the (shifted) window.
+// Source row/col in the unshifted token grid: r=(8h+i+s)%ph, c=(8w+j+s)%pw
+// (window_utils.py:134-145: context added per unshifted window, then roll(-s,-s), then partition).
+struct Slot {
+  long long tok;   // flat token index  b*ph*pw + r*pw + c
+  int cwin;        // flat source window index b*wh*ww + (r/8)*ww + c/8
+  int region;      // 9-region id of the shifted-frame position (transformer_blocks.py:63-76)
+};
+__device__ __forceinline__ Slot slot_of(const Geom& g, int w, int h, int b, int t) {
+  const int R = h * kWin + (t >> 3);
+  const int C = w * kWin + (t & 7);
+  int r = R + g.shift; if (r >= g.ph) r -= g.ph;
+  int c = C + g.shift; if (c >= g.pw) c -= g.pw;
+  Slot s;
+  s.tok = ((long long)b * g.ph + r) * g.pw + c;
+  s.cwin = (b * g.wh + (r >> 3)) * g.ww + (c >> 3);
+  const int rid = R < g.ph - kWin ? 0 : (R < g.ph - kShift ? 1 : 2);
+  const int cid = C < g.pw - kWin ? 0 : (C < g.pw - kShift ? 1 : 2);
+  s.region = rid * 3 + cid;
+  return s;
+}
+__device__ __forceinline__ Slot slot_of(const Geom& g, int win, int t) {
+  int w, h, b;
+  win_pos(g, win, w, h, b);
+  return slot_of(g, w, h, b, t);
 }
 // relative-position index of (query p, key q) inside an 8x8 window, attention.py:9-18
 __device__ __forceinline__ int rel_index(int p, int q) {

@@ -17,6 +17,7 @@ __global__ void __launch_bounds__(kThreads) unigram_bwd_kernel(
   const int lane = threadIdx.x & 31, i = threadIdx.x >> 5;   // i = window row owned by this warp
   const int wh = ph / kWin, ww = pw / kWin;
   const int nwin = B * wh * ww;
+  const WinDiv wdiv = make_windiv(wh, ww);
   float2 wr[kWin], acc[kWin];
 #pragma unroll
   for (int j = 0; j < kWin; ++j) {
@@ -26,7 +27,8 @@ __global__ void __launch_bounds__(kThreads) unigram_bwd_kernel(
   }
   float dbl = 0.f;
   for (int win = blockIdx.x; win < nwin; win += gridDim.x) {
-    const int w0 = win % ww, h0 = (win / ww) % wh, b = win / (ww * wh);
+    int w0, h0, b;
+    win_pos(wdiv, win, w0, h0, b);
     const float g = du[(size_t)win * 32 + lane];
     if (i == 0) dbl += g;
     const size_t base = (((size_t)b * ph + h0 * kWin + i) * pw + w0 * kWin) * kDim + 2 * lane;
@@ -134,10 +136,12 @@ __global__ void __launch_bounds__(kThreads) ngram_ctx_bwd_kernel(NgramParams p) 
 
   const int wh = p.wh, ww = p.ww;
   const int nwin = p.B * wh * ww;
+  const WinDiv wdiv = make_windiv(wh, ww);
   for (int base = blockIdx.x * 8; base < nwin; base += gridDim.x * 8) {
    const int win = base + warp;
    if (win < nwin) {
-    const int w0 = win % ww, h0 = (win / ww) % wh, b = win / (ww * wh);
+    int w0, h0, b;
+    win_pos(wdiv, win, w0, h0, b);
     int nbr[8];
     // ================= forward recompute
 #pragma unroll

@@ -22,9 +22,11 @@ __global__ void __launch_bounds__(kThreads) unigram_fwd_kernel(
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int wh = ph / kWin, ww = pw / kWin;
   const int nwin = B * wh * ww;
+  const WinDiv wdiv = make_windiv(wh, ww);
   const float bl = bias[lane];
   for (int win = blockIdx.x * 8 + warp; win < nwin; win += gridDim.x * 8) {
-    const int w0 = win % ww, h0 = (win / ww) % wh, b = win / (ww * wh);
+    int w0, h0, b;
+    win_pos(wdiv, win, w0, h0, b);
     const float* base = z + (((size_t)b * ph + h0 * kWin) * pw + w0 * kWin) * kDim + 2 * lane;
     float acc = 0.f;
 #pragma unroll 1
@@ -67,12 +69,14 @@ __global__ void __launch_bounds__(kThreads) unigram_qkv_fwd_kernel(
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int wh = ph / kWin, ww = pw / kWin;
   const int nwin = B * wh * ww;
+  const WinDiv wdiv = make_windiv(wh, ww);
   const float bl = bias[lane];
   float bq[3];
 #pragma unroll
   for (int g = 0; g < 3; ++g) bq[g] = lane + 32 * g < n_qkv ? qkv_b[lane + 32 * g] : 0.f;
   for (int win = blockIdx.x * 8 + warp; win < nwin; win += gridDim.x * 8) {
-    const int w0 = win % ww, h0 = (win / ww) % wh, b = win / (ww * wh);
+    int w0, h0, b;
+    win_pos(wdiv, win, w0, h0, b);
     const size_t e0 = (((size_t)b * ph + h0 * kWin) * pw + w0 * kWin) * kDim + 2 * lane;   // element offset
     const float* base = z + e0;
     const unsigned short* base16 = reinterpret_cast<const unsigned short*>(z) + e0;        // S16: z is bf16
@@ -143,11 +147,13 @@ __global__ void __launch_bounds__(kThreads) ngram_ctx_fwd_kernel(NgramParams p) 
 
   const int wh = p.wh, ww = p.ww;
   const int nwin = p.B * wh * ww;
+  const WinDiv wdiv = make_windiv(wh, ww);
   // PRE: the 8 neighbourhood rows of the NEXT window are fetched into registers while this window
   // computes (24 loads in flight per lane hide the L2 latency of the gather)
   float nxt[24];
   auto fetch = [&](int win_) {
-    const int w0 = win_ % ww, h0 = (win_ / ww) % wh, b = win_ / (ww * wh);
+    int w0, h0, b;
+    win_pos(wdiv, win_, w0, h0, b);
 #pragma unroll
     for (int t = 0; t < 8; ++t) {
       int r, c;
@@ -158,7 +164,8 @@ __global__ void __launch_bounds__(kThreads) ngram_ctx_fwd_kernel(NgramParams p) 
   };
   if (PRE && (int)(blockIdx.x * 8 + warp) < nwin) fetch(blockIdx.x * 8 + warp);
   for (int win = blockIdx.x * 8 + warp; win < nwin; win += gridDim.x * 8) {
-    const int w0 = win % ww, h0 = (win / ww) % wh, b = win / (ww * wh);
+    int w0, h0, b;
+    win_pos(wdiv, win, w0, h0, b);
     if (PRE) {
       // ---- qkv rows of the 8 neighbourhood tokens (4 forward, 4 backward), precomputed per window
 #pragma unroll
