@@ -206,56 +206,73 @@ __global__ void __launch_bounds__(kThreads) ngram_ctx_fwd_kernel(NgramParams p) 
       }
       __syncwarp();
     }
-    // ---- 4-token cosine attention per (direction, head); mean over the 4 query tokens
-    if (lane < 2 * NH) {
-      const int dir = lane / NH, h = lane % NH;
-      float qn[4][HD], kn[4][HD];
-#pragma unroll
-      for (int t = 0; t < 4; ++t) {
-        const float* row = sQkv + (dir * 4 + t) * 96;
-        float sq = 0.f, sk = 0.f;
-#pragma unroll
-        for (int d = 0; d < HD; ++d) {
-          qn[t][d] = row[h * HD + d];
-          kn[t][d] = row[NA + h * HD + d];
-          sq = fmaf(qn[t][d], qn[t][d], sq);
-          sk = fmaf(kn[t][d], kn[t][d], sk);
-        }
-        // 1 / max(||.||, eps): eps^2 = 1e-24 is a normal float, so max(sq, eps^2) under rsqrt is exact
-        const float iq = PRE ? rsqrtf(fmaxf(sq, kNormEps * kNormEps)) : 1.0f / fmaxf(sqrtf(sq), kNormEps);
-        const float ik = PRE ? rsqrtf(fmaxf(sk, kNormEps * kNormEps)) : 1.0f / fmaxf(sqrtf(sk), kNormEps);
-#pragma unroll
-        for (int d = 0; d < HD; ++d) { qn[t][d] *= iq; kn[t][d] *= ik; }
-      }
+    // ---- 4-token cosine attention per (direction, head); mean over the 4 query tokens.  A (direction, head)
+    //      pair is shared by QG adjacent lanes, each owning 4 / QG of the query tokens (2 * NH * QG = 24 or 32
+    //      busy lanes instead of 2 * NH); the partial means are combined with shuffles.
+    {
+      constexpr int QG = NH == 6 ? 2 : 4, QPL = 4 / QG;    // query groups per (dir, head), queries per lane
+      const bool busy = lane < 2 * NH * QG;
+      const int pair = busy ? lane / QG : 0, qg = lane % QG;
+      const int dir = pair / NH, h = pair % NH;
       float om[HD];
 #pragma unroll
       for (int d = 0; d < HD; ++d) om[d] = 0.f;
-      const float scale = sScale[h];
+      if (busy) {
+        float kn[4][HD], vv[4][HD];
 #pragma unroll
-      for (int pq = 0; pq < 4; ++pq) {
-        float s[4], mx = -INFINITY;
+        for (int t = 0; t < 4; ++t) {
+          const float* row = sQkv + (dir * 4 + t) * 96;
+          float sk = 0.f;
 #pragma unroll
-        for (int kq = 0; kq < 4; ++kq) {
-          float dot = 0.f;
+          for (int d = 0; d < HD; ++d) {
+            kn[t][d] = row[NA + h * HD + d];
+            vv[t][d] = row[2 * NA + h * HD + d];
+            sk = fmaf(kn[t][d], kn[t][d], sk);
+          }
+          // 1 / max(||.||, eps): eps^2 = 1e-24 is a normal float, so max(sq, eps^2) under rsqrt is exact
+          const float ik = PRE ? rsqrtf(fmaxf(sk, kNormEps * kNormEps)) : 1.0f / fmaxf(sqrtf(sk), kNormEps);
 #pragma unroll
-          for (int d = 0; d < HD; ++d) dot = fmaf(qn[pq][d], kn[kq][d], dot);
-          s[kq] = dot * scale + sBias[h * 12 + ngram_rel_index(pq, kq)];
-          mx = fmaxf(mx, s[kq]);
+          for (int d = 0; d < HD; ++d) kn[t][d] *= ik;
         }
-        float sum = 0.f;
+        const float scale = sScale[h];
 #pragma unroll
-        for (int kq = 0; kq < 4; ++kq) { s[kq] = PRE ? __expf(s[kq] - mx) : expf(s[kq] - mx); sum += s[kq]; }
-        const float inv = PRE ? __fdividef(0.25f, sum) : 0.25f / sum;   // softmax normalisation and the AvgPool2d(2) mean
+        for (int qi = 0; qi < QPL; ++qi) {
+          const int pq = qg * QPL + qi;
+          const float* row = sQkv + (dir * 4 + pq) * 96;
+          float qn[HD], sq = 0.f;
 #pragma unroll
-        for (int kq = 0; kq < 4; ++kq) {
-          const float pv = s[kq] * inv;
-          const float* vrow = sQkv + (dir * 4 + kq) * 96 + 2 * NA + h * HD;
+          for (int d = 0; d < HD; ++d) { qn[d] = row[h * HD + d]; sq = fmaf(qn[d], qn[d], sq); }
+          const float iq = (PRE ? rsqrtf(fmaxf(sq, kNormEps * kNormEps)) : 1.0f / fmaxf(sqrtf(sq), kNormEps)) * scale;
+          float s[4], mx = -INFINITY;
 #pragma unroll
-          for (int d = 0; d < HD; ++d) om[d] = fmaf(pv, vrow[d], om[d]);
+          for (int kq = 0; kq < 4; ++kq) {
+            float dot = 0.f;
+#pragma unroll
+            for (int d = 0; d < HD; ++d) dot = fmaf(qn[d], kn[kq][d], dot);
+            s[kq] = fmaf(dot, iq, sBias[h * 12 + ngram_rel_index(pq, kq)]);
+            mx = fmaxf(mx, s[kq]);
+          }
+          float sum = 0.f;
+#pragma unroll
+          for (int kq = 0; kq < 4; ++kq) { s[kq] = PRE ? __expf(s[kq] - mx) : expf(s[kq] - mx); sum += s[kq]; }
+          const float inv = PRE ? __fdividef(0.25f, sum) : 0.25f / sum;   // softmax normalisation and the AvgPool2d(2) mean
+#pragma unroll
+          for (int kq = 0; kq < 4; ++kq) {
+            const float pv = s[kq] * inv;
+#pragma unroll
+            for (int d = 0; d < HD; ++d) om[d] = fmaf(pv, vv[kq][d], om[d]);
+          }
         }
       }
 #pragma unroll
-      for (int d = 0; d < HD; ++d) sOm[dir * 32 + h * HD + d] = om[d];
+      for (int d = 0; d < HD; ++d) {
+#pragma unroll
+        for (int o = 1; o < QG; o <<= 1) om[d] += __shfl_xor_sync(0xffffffffu, om[d], o);
+      }
+      if (busy && qg == 0) {
+#pragma unroll
+        for (int d = 0; d < HD; ++d) sOm[dir * 32 + h * HD + d] = om[d];
+      }
     }
     __syncwarp();
     // ---- proj (commutes with the mean): cat[dir*32 + c] = bp[c] + Wp[c,:] . om[dir]
