@@ -36,7 +36,7 @@ struct NgramSmem {
   static constexpr int oScale = oBm + 64;     // [8]
   static constexpr int oBias = oScale + 8;    // [NH][12]
   static constexpr int oScratch = oBias + 8 * 12;
-  static constexpr int kScratchPerWarp = 8 * 32 + 8 * 96 + 64 + 64;
+  static constexpr int kScratchPerWarp = 8 * 32 + 8 * 96 + 4 * 64;   // tok / cat (4 windows) | qkv | om (4 windows)
   static constexpr int kFloatsFwd = oScratch + 8 * kScratchPerWarp;
 };
 

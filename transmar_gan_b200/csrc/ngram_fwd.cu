@@ -140,10 +140,13 @@ __global__ void __launch_bounds__(kThreads) ngram_ctx_fwd_kernel(NgramParams p) 
   const float* sScale = smem + L::oScale;
   const float* sBias = smem + L::oBias;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  float* sTok = smem + L::oScratch + warp * L::kScratchPerWarp;  // [8][32]
+  // per-warp scratch.  The proj / merge matrix-vector products are done for FOUR windows at a time so that one pass
+  // over the weights in shared memory serves four outputs (the kernel is bound by shared-memory instruction issue):
+  // sOm4 / sCat4 hold the four windows' vectors interleaved, [channel][window], and are read as float4.
+  float* sTok = smem + L::oScratch + warp * L::kScratchPerWarp;  // [8][32] (non-PRE, inside a window); then sCat4
+  float* sCat4 = sTok;                                           // [64][4]
   float* sQkv = sTok + 8 * 32;                                   // [8][96]
-  float* sOm = sQkv + 8 * 96;                                    // [64]  mean attention out per dir
-  float* sCat = sOm + 64;                                        // [64]
+  float* sOm4 = sQkv + 8 * 96;                                   // [64][4]  mean attention out per dir
 
   const int wh = p.wh, ww = p.ww;
   const int nwin = p.B * wh * ww;
@@ -162,141 +165,178 @@ __global__ void __launch_bounds__(kThreads) ngram_ctx_fwd_kernel(NgramParams p) 
       nxt[3 * t] = __ldg(src); nxt[3 * t + 1] = __ldg(src + 32); nxt[3 * t + 2] = __ldg(src + 64);
     }
   };
-  if (PRE && (int)(blockIdx.x * 8 + warp) < nwin) fetch(blockIdx.x * 8 + warp);
-  for (int win = blockIdx.x * 8 + warp; win < nwin; win += gridDim.x * 8) {
-    int w0, h0, b;
-    win_pos(wdiv, win, w0, h0, b);
-    if (PRE) {
-      // ---- qkv rows of the 8 neighbourhood tokens (4 forward, 4 backward), precomputed per window
+  const int ngroup = (nwin + 3) >> 2, gstride = gridDim.x * 8;
+  if (PRE && (int)(blockIdx.x * 8 + warp) < ngroup) fetch((blockIdx.x * 8 + warp) * 4);
+  for (int grp = blockIdx.x * 8 + warp; grp < ngroup; grp += gstride) {
+#pragma unroll 1
+    for (int k = 0; k < 4; ++k) {
+      const int win = grp * 4 + k;
+      if (win >= nwin) {                                         // ragged last group: zero vectors
+        sOm4[lane * 4 + k] = 0.f; sOm4[(lane + 32) * 4 + k] = 0.f;
+        continue;
+      }
+      int w0, h0, b;
+      win_pos(wdiv, win, w0, h0, b);
+      if (PRE) {
+        // ---- qkv rows of the 8 neighbourhood tokens (4 forward, 4 backward), precomputed per window
 #pragma unroll
-      for (int t = 0; t < 8; ++t) {
-        sQkv[t * 96 + lane] = nxt[3 * t];
-        sQkv[t * 96 + lane + 32] = nxt[3 * t + 1];
-        sQkv[t * 96 + lane + 64] = nxt[3 * t + 2];
-      }
-      __syncwarp();
-      if (win + (int)gridDim.x * 8 < nwin) fetch(win + gridDim.x * 8);
-    } else {
-      // ---- the 8 neighbourhood tokens (4 forward, 4 backward), lane = channel
-  #pragma unroll
-      for (int t = 0; t < 8; ++t) {
-        int r, c;
-        ngram_neighbour(t, h0, w0, wh, ww, r, c);
-        sTok[t * 32 + lane] = p.u[((size_t)(b * wh + r) * ww + c) * 32 + lane];
-      }
-      __syncwarp();
-      // ---- qkv = Linear(32 -> 3*NA)
-  #pragma unroll
-      for (int jg = 0; jg < 3; ++jg) {
-        const int j = lane + 32 * jg;
-        if (j < 3 * NA) {
-          float acc[8];
-          const float bj = sBqkv[j];
-  #pragma unroll
-          for (int t = 0; t < 8; ++t) acc[t] = bj;
-  #pragma unroll 8
-          for (int c = 0; c < 32; ++c) {
-            const float wv = sWqkv[j * 33 + c];
-  #pragma unroll
-            for (int t = 0; t < 8; ++t) acc[t] = fmaf(wv, sTok[t * 32 + c], acc[t]);
+        for (int t = 0; t < 8; ++t) {
+          sQkv[t * 96 + lane] = nxt[3 * t];
+          sQkv[t * 96 + lane + 32] = nxt[3 * t + 1];
+          sQkv[t * 96 + lane + 64] = nxt[3 * t + 2];
+        }
+        __syncwarp();
+        const int nw = k < 3 ? win + 1 : (grp + gstride) * 4;
+        if (nw < nwin) fetch(nw);
+      } else {
+        // ---- the 8 neighbourhood tokens (4 forward, 4 backward), lane = channel
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+          int r, c;
+          ngram_neighbour(t, h0, w0, wh, ww, r, c);
+          sTok[t * 32 + lane] = p.u[((size_t)(b * wh + r) * ww + c) * 32 + lane];
+        }
+        __syncwarp();
+        // ---- qkv = Linear(32 -> 3*NA)
+#pragma unroll
+        for (int jg = 0; jg < 3; ++jg) {
+          const int j = lane + 32 * jg;
+          if (j < 3 * NA) {
+            float acc[8];
+            const float bj = sBqkv[j];
+#pragma unroll
+            for (int t = 0; t < 8; ++t) acc[t] = bj;
+#pragma unroll 8
+            for (int c = 0; c < 32; ++c) {
+              const float wv = sWqkv[j * 33 + c];
+#pragma unroll
+              for (int t = 0; t < 8; ++t) acc[t] = fmaf(wv, sTok[t * 32 + c], acc[t]);
+            }
+#pragma unroll
+            for (int t = 0; t < 8; ++t) sQkv[t * 96 + j] = acc[t];
           }
-  #pragma unroll
-          for (int t = 0; t < 8; ++t) sQkv[t * 96 + j] = acc[t];
+        }
+        __syncwarp();
+      }
+      // ---- 4-token cosine attention per (direction, head); mean over the 4 query tokens.  A (direction, head)
+      //      pair is shared by QG adjacent lanes, each owning 4 / QG of the query tokens (2 * NH * QG = 24 or 32
+      //      busy lanes instead of 2 * NH); the partial means are combined with shuffles.
+      {
+        constexpr int QG = NH == 6 ? 2 : 4, QPL = 4 / QG;    // query groups per (dir, head), queries per lane
+        const bool busy = lane < 2 * NH * QG;
+        const int pair = busy ? lane / QG : 0, qg = lane % QG;
+        const int dir = pair / NH, h = pair % NH;
+        float om[HD];
+#pragma unroll
+        for (int d = 0; d < HD; ++d) om[d] = 0.f;
+        if (busy) {
+          float kn[4][HD], vv[4][HD];
+#pragma unroll
+          for (int t = 0; t < 4; ++t) {
+            const float* row = sQkv + (dir * 4 + t) * 96;
+            float sk = 0.f;
+#pragma unroll
+            for (int d = 0; d < HD; ++d) {
+              kn[t][d] = row[NA + h * HD + d];
+              vv[t][d] = row[2 * NA + h * HD + d];
+              sk = fmaf(kn[t][d], kn[t][d], sk);
+            }
+            // 1 / max(||.||, eps): eps^2 = 1e-24 is a normal float, so max(sq, eps^2) under rsqrt is exact
+            const float ik = PRE ? rsqrtf(fmaxf(sk, kNormEps * kNormEps)) : 1.0f / fmaxf(sqrtf(sk), kNormEps);
+#pragma unroll
+            for (int d = 0; d < HD; ++d) kn[t][d] *= ik;
+          }
+          const float scale = sScale[h];
+#pragma unroll
+          for (int qi = 0; qi < QPL; ++qi) {
+            const int pq = qg * QPL + qi;
+            const float* row = sQkv + (dir * 4 + pq) * 96;
+            float qn[HD], sq = 0.f;
+#pragma unroll
+            for (int d = 0; d < HD; ++d) { qn[d] = row[h * HD + d]; sq = fmaf(qn[d], qn[d], sq); }
+            const float iq = (PRE ? rsqrtf(fmaxf(sq, kNormEps * kNormEps)) : 1.0f / fmaxf(sqrtf(sq), kNormEps)) * scale;
+            float s[4], mx = -INFINITY;
+#pragma unroll
+            for (int kq = 0; kq < 4; ++kq) {
+              float dot = 0.f;
+#pragma unroll
+              for (int d = 0; d < HD; ++d) dot = fmaf(qn[d], kn[kq][d], dot);
+              s[kq] = fmaf(dot, iq, sBias[h * 12 + ngram_rel_index(pq, kq)]);
+              mx = fmaxf(mx, s[kq]);
+            }
+            float sum = 0.f;
+#pragma unroll
+            for (int kq = 0; kq < 4; ++kq) { s[kq] = PRE ? __expf(s[kq] - mx) : expf(s[kq] - mx); sum += s[kq]; }
+            const float inv = PRE ? __fdividef(0.25f, sum) : 0.25f / sum;   // softmax normalisation and the AvgPool2d(2) mean
+#pragma unroll
+            for (int kq = 0; kq < 4; ++kq) {
+              const float pv = s[kq] * inv;
+#pragma unroll
+              for (int d = 0; d < HD; ++d) om[d] = fmaf(pv, vv[kq][d], om[d]);
+            }
+          }
+        }
+#pragma unroll
+        for (int d = 0; d < HD; ++d) {
+#pragma unroll
+          for (int o = 1; o < QG; o <<= 1) om[d] += __shfl_xor_sync(0xffffffffu, om[d], o);
+        }
+        if (busy && qg == 0) {
+#pragma unroll
+          for (int d = 0; d < HD; ++d) sOm4[(dir * 32 + h * HD + d) * 4 + k] = om[d];
         }
       }
       __syncwarp();
     }
-    // ---- 4-token cosine attention per (direction, head); mean over the 4 query tokens.  A (direction, head)
-    //      pair is shared by QG adjacent lanes, each owning 4 / QG of the query tokens (2 * NH * QG = 24 or 32
-    //      busy lanes instead of 2 * NH); the partial means are combined with shuffles.
+    // ---- proj (commutes with the mean), four windows: cat[k][dir*32 + c] = bp[c] + Wp[c,:] . om[k][dir]
     {
-      constexpr int QG = NH == 6 ? 2 : 4, QPL = 4 / QG;    // query groups per (dir, head), queries per lane
-      const bool busy = lane < 2 * NH * QG;
-      const int pair = busy ? lane / QG : 0, qg = lane % QG;
-      const int dir = pair / NH, h = pair % NH;
-      float om[HD];
+      float acc[2][4];
 #pragma unroll
-      for (int d = 0; d < HD; ++d) om[d] = 0.f;
-      if (busy) {
-        float kn[4][HD], vv[4][HD];
+      for (int dir = 0; dir < 2; ++dir)
 #pragma unroll
-        for (int t = 0; t < 4; ++t) {
-          const float* row = sQkv + (dir * 4 + t) * 96;
-          float sk = 0.f;
-#pragma unroll
-          for (int d = 0; d < HD; ++d) {
-            kn[t][d] = row[NA + h * HD + d];
-            vv[t][d] = row[2 * NA + h * HD + d];
-            sk = fmaf(kn[t][d], kn[t][d], sk);
-          }
-          // 1 / max(||.||, eps): eps^2 = 1e-24 is a normal float, so max(sq, eps^2) under rsqrt is exact
-          const float ik = PRE ? rsqrtf(fmaxf(sk, kNormEps * kNormEps)) : 1.0f / fmaxf(sqrtf(sk), kNormEps);
-#pragma unroll
-          for (int d = 0; d < HD; ++d) kn[t][d] *= ik;
-        }
-        const float scale = sScale[h];
-#pragma unroll
-        for (int qi = 0; qi < QPL; ++qi) {
-          const int pq = qg * QPL + qi;
-          const float* row = sQkv + (dir * 4 + pq) * 96;
-          float qn[HD], sq = 0.f;
-#pragma unroll
-          for (int d = 0; d < HD; ++d) { qn[d] = row[h * HD + d]; sq = fmaf(qn[d], qn[d], sq); }
-          const float iq = (PRE ? rsqrtf(fmaxf(sq, kNormEps * kNormEps)) : 1.0f / fmaxf(sqrtf(sq), kNormEps)) * scale;
-          float s[4], mx = -INFINITY;
-#pragma unroll
-          for (int kq = 0; kq < 4; ++kq) {
-            float dot = 0.f;
-#pragma unroll
-            for (int d = 0; d < HD; ++d) dot = fmaf(qn[d], kn[kq][d], dot);
-            s[kq] = fmaf(dot, iq, sBias[h * 12 + ngram_rel_index(pq, kq)]);
-            mx = fmaxf(mx, s[kq]);
-          }
-          float sum = 0.f;
-#pragma unroll
-          for (int kq = 0; kq < 4; ++kq) { s[kq] = PRE ? __expf(s[kq] - mx) : expf(s[kq] - mx); sum += s[kq]; }
-          const float inv = PRE ? __fdividef(0.25f, sum) : 0.25f / sum;   // softmax normalisation and the AvgPool2d(2) mean
-#pragma unroll
-          for (int kq = 0; kq < 4; ++kq) {
-            const float pv = s[kq] * inv;
-#pragma unroll
-            for (int d = 0; d < HD; ++d) om[d] = fmaf(pv, vv[kq][d], om[d]);
-          }
-        }
-      }
-#pragma unroll
-      for (int d = 0; d < HD; ++d) {
-#pragma unroll
-        for (int o = 1; o < QG; o <<= 1) om[d] += __shfl_xor_sync(0xffffffffu, om[d], o);
-      }
-      if (busy && qg == 0) {
-#pragma unroll
-        for (int d = 0; d < HD; ++d) sOm[dir * 32 + h * HD + d] = om[d];
-      }
-    }
-    __syncwarp();
-    // ---- proj (commutes with the mean): cat[dir*32 + c] = bp[c] + Wp[c,:] . om[dir]
-#pragma unroll
-    for (int dir = 0; dir < 2; ++dir) {
-      float acc = sBp[lane];
+        for (int k = 0; k < 4; ++k) acc[dir][k] = sBp[lane];
 #pragma unroll 6
-      for (int j = 0; j < NA; ++j) acc = fmaf(sWp[lane * 33 + j], sOm[dir * 32 + j], acc);
-      sCat[dir * 32 + lane] = acc;
+      for (int j = 0; j < NA; ++j) {
+        const float w = sWp[lane * 33 + j];
+#pragma unroll
+        for (int dir = 0; dir < 2; ++dir) {
+          const float4 o4 = *reinterpret_cast<const float4*>(sOm4 + (dir * 32 + j) * 4);
+          acc[dir][0] = fmaf(w, o4.x, acc[dir][0]); acc[dir][1] = fmaf(w, o4.y, acc[dir][1]);
+          acc[dir][2] = fmaf(w, o4.z, acc[dir][2]); acc[dir][3] = fmaf(w, o4.w, acc[dir][3]);
+        }
+      }
+      __syncwarp();                                              // (non-PRE: sTok is dead, sCat4 may overwrite it)
+#pragma unroll
+      for (int dir = 0; dir < 2; ++dir)
+        *reinterpret_cast<float4*>(sCat4 + (dir * 32 + lane) * 4) =
+            make_float4(acc[dir][0], acc[dir][1], acc[dir][2], acc[dir][3]);
     }
     __syncwarp();
-    // ---- merge 1x1 conv 64 -> 64 (two outputs per lane, two partial sums each: short FMA chains)
+    // ---- merge 1x1 conv 64 -> 64, four windows (two outputs per lane, two partial sums each: short FMA chains)
     {
       const float* w0 = sWm + lane * 65;
       const float* w1 = sWm + (lane + 32) * 65;
-      float a0 = sBm[lane], a1 = 0.f, b0 = sBm[lane + 32], b1 = 0.f;
-#pragma unroll 8
+      float a0[4], a1[4], b0[4], b1[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) { a0[k] = sBm[lane]; a1[k] = 0.f; b0[k] = sBm[lane + 32]; b1[k] = 0.f; }
+#pragma unroll 4
       for (int c = 0; c < 64; c += 2) {
-        const float c0 = sCat[c], c1 = sCat[c + 1];
-        a0 = fmaf(w0[c], c0, a0); a1 = fmaf(w0[c + 1], c1, a1);
-        b0 = fmaf(w1[c], c0, b0); b1 = fmaf(w1[c + 1], c1, b1);
+        const float4 c0 = *reinterpret_cast<const float4*>(sCat4 + c * 4);
+        const float4 c1 = *reinterpret_cast<const float4*>(sCat4 + c * 4 + 4);
+        const float u0 = w0[c], u1 = w0[c + 1], v0 = w1[c], v1 = w1[c + 1];
+        a0[0] = fmaf(u0, c0.x, a0[0]); a0[1] = fmaf(u0, c0.y, a0[1]); a0[2] = fmaf(u0, c0.z, a0[2]); a0[3] = fmaf(u0, c0.w, a0[3]);
+        a1[0] = fmaf(u1, c1.x, a1[0]); a1[1] = fmaf(u1, c1.y, a1[1]); a1[2] = fmaf(u1, c1.z, a1[2]); a1[3] = fmaf(u1, c1.w, a1[3]);
+        b0[0] = fmaf(v0, c0.x, b0[0]); b0[1] = fmaf(v0, c0.y, b0[1]); b0[2] = fmaf(v0, c0.z, b0[2]); b0[3] = fmaf(v0, c0.w, b0[3]);
+        b1[0] = fmaf(v1, c1.x, b1[0]); b1[1] = fmaf(v1, c1.y, b1[1]); b1[2] = fmaf(v1, c1.z, b1[2]); b1[3] = fmaf(v1, c1.w, b1[3]);
       }
-      p.ctx[(size_t)win * 64 + lane] = a0 + a1;
-      p.ctx[(size_t)win * 64 + lane + 32] = b0 + b1;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int win = grp * 4 + k;
+        if (win < nwin) {
+          p.ctx[(size_t)win * 64 + lane] = a0[k] + a1[k];
+          p.ctx[(size_t)win * 64 + lane + 32] = b0[k] + b1[k];
+        }
+      }
     }
     __syncwarp();
   }
@@ -313,7 +353,7 @@ static int launch_ngram_ctx_fwd(const NgramParams& p, cudaStream_t st) {
     configured.done();
   }
   const int nwin = p.B * p.wh * p.ww;
-  int grid = (nwin + 7) / 8;
+  int grid = ((nwin + 3) / 4 + 7) / 8;               // a warp takes groups of four windows
   if (grid > 3 * sm_count()) grid = 3 * sm_count();
   ngram_ctx_fwd_kernel<NH, PRE><<<grid, kThreads, smem, st>>>(p);
   B200MAR_CHECK(cudaGetLastError());
