@@ -49,14 +49,17 @@ __global__ void __launch_bounds__(kThreads) unigram_fwd_kernel(
 // Inference form: the same streaming pass also applies the n-gram attention's qkv Linear(32 -> 3*NA)
 // to the window's unigram embedding, once per window (ngram_ctx_fwd re-derives it for each of the
 // up to 8 neighbourhoods a window belongs to).  nq: [B*wh*ww][96] (rows >= 3*NA are zero).
+// Four windows per warp and pass: the kernel was bound by shared-memory instruction issue (ncu: 31 % of the stalls
+// MIO throttle, DRAM at 57 %), so each conv weight and each qkv weight read from shared memory now serves four
+// windows, and four windows' rows (8 KB per warp) are in flight at a time.
 template <bool S16>
-__global__ void __launch_bounds__(kThreads) unigram_qkv_fwd_kernel(
+__global__ void __launch_bounds__(kThreads, 2) unigram_qkv_fwd_kernel(
     const float* __restrict__ z, const float* __restrict__ w, const float* __restrict__ bias,
     const float* __restrict__ qkv_w, const float* __restrict__ qkv_b, int n_qkv,
     float* __restrict__ nq, int B, int ph, int pw) {
   __shared__ __align__(16) float sW[kTok * kDim];  // [t = 8i+j][c = 2g+k]
   __shared__ __align__(16) float sWq[32 * 96];     // [c][j]
-  __shared__ __align__(16) float sU[8][32];
+  __shared__ __align__(16) float sU[8][32 * 4];    // per warp: [channel][window of the group]
   for (int idx = threadIdx.x; idx < kTok * kDim; idx += blockDim.x) {
     const int t = idx >> 6, c = idx & 63;
     sW[idx] = w[(c >> 1) * 128 + (c & 1) * 64 + t];
@@ -74,49 +77,74 @@ __global__ void __launch_bounds__(kThreads) unigram_qkv_fwd_kernel(
   float bq[3];
 #pragma unroll
   for (int g = 0; g < 3; ++g) bq[g] = lane + 32 * g < n_qkv ? qkv_b[lane + 32 * g] : 0.f;
-  for (int win = blockIdx.x * 8 + warp; win < nwin; win += gridDim.x * 8) {
-    int w0, h0, b;
-    win_pos(wdiv, win, w0, h0, b);
-    const size_t e0 = (((size_t)b * ph + h0 * kWin) * pw + w0 * kWin) * kDim + 2 * lane;   // element offset
-    const float* base = z + e0;
-    const unsigned short* base16 = reinterpret_cast<const unsigned short*>(z) + e0;        // S16: z is bf16
-    float acc = 0.f;
+  const int ngroup = (nwin + 3) >> 2;
+  for (int grp = blockIdx.x * 8 + warp; grp < ngroup; grp += gridDim.x * 8) {
+    size_t e0[4];                                     // element offset of (window k, row 0, token 0, channel 2*lane)
+    bool ok[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int win = grp * 4 + k;
+      ok[k] = win < nwin;
+      int w0, h0, b;
+      win_pos(wdiv, ok[k] ? win : 0, w0, h0, b);
+      e0[k] = (((size_t)b * ph + h0 * kWin) * pw + w0 * kWin) * kDim + 2 * lane;
+    }
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll 1
     for (int i = 0; i < kWin; ++i) {
-      float2 v[kWin];
+      float2 v[4][kWin];
 #pragma unroll
-      for (int j = 0; j < kWin; ++j) {
-        if constexpr (S16) {
-          const uint32_t u2 = *reinterpret_cast<const uint32_t*>(base16 + ((size_t)i * pw + j) * kDim);
-          v[j] = make_float2(__uint_as_float(u2 << 16), __uint_as_float(u2 & 0xFFFF0000u));
-        } else {
-          v[j] = *reinterpret_cast<const float2*>(base + ((size_t)i * pw + j) * kDim);
+      for (int k = 0; k < 4; ++k) {
+#pragma unroll
+        for (int j = 0; j < kWin; ++j) {
+          const size_t e = e0[k] + ((size_t)i * pw + j) * kDim;
+          if (!ok[k]) {
+            v[k][j] = make_float2(0.f, 0.f);
+          } else if constexpr (S16) {
+            const uint32_t u2 = *reinterpret_cast<const uint32_t*>(reinterpret_cast<const unsigned short*>(z) + e);
+            v[k][j] = make_float2(__uint_as_float(u2 << 16), __uint_as_float(u2 & 0xFFFF0000u));
+          } else {
+            v[k][j] = *reinterpret_cast<const float2*>(z + e);
+          }
         }
       }
 #pragma unroll
       for (int j = 0; j < kWin; ++j) {
         const float2 wv = *reinterpret_cast<const float2*>(sW + (i * kWin + j) * kDim + 2 * lane);
-        acc = fmaf(v[j].x, wv.x, acc);
-        acc = fmaf(v[j].y, wv.y, acc);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          acc[k] = fmaf(v[k][j].x, wv.x, acc[k]);
+          acc[k] = fmaf(v[k][j].y, wv.y, acc[k]);
+        }
       }
     }
-    sU[warp][lane] = acc + bl;
+    *reinterpret_cast<float4*>(&sU[warp][lane * 4]) = make_float4(acc[0] + bl, acc[1] + bl, acc[2] + bl, acc[3] + bl);
     __syncwarp();
-    float q0 = bq[0], q1 = bq[1], q2 = bq[2];
+    float q[3][4];
 #pragma unroll
-    for (int c4 = 0; c4 < 8; ++c4) {
-      const float4 uv = *reinterpret_cast<const float4*>(&sU[warp][c4 * 4]);
-      const float uu[4] = {uv.x, uv.y, uv.z, uv.w};
+    for (int g = 0; g < 3; ++g)
+#pragma unroll
+      for (int k = 0; k < 4; ++k) q[g][k] = bq[g];
+#pragma unroll 8
+    for (int c = 0; c < 32; ++c) {
+      const float4 u4 = *reinterpret_cast<const float4*>(&sU[warp][c * 4]);
+      const float uu[4] = {u4.x, u4.y, u4.z, u4.w};
+      const float* wr = sWq + c * 96 + lane;
+      const float w0 = wr[0], w1 = wr[32], w2 = wr[64];
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
-        const float* wr = sWq + (c4 * 4 + k) * 96 + lane;
-        q0 = fmaf(wr[0], uu[k], q0);
-        q1 = fmaf(wr[32], uu[k], q1);
-        q2 = fmaf(wr[64], uu[k], q2);
+        q[0][k] = fmaf(w0, uu[k], q[0][k]);
+        q[1][k] = fmaf(w1, uu[k], q[1][k]);
+        q[2][k] = fmaf(w2, uu[k], q[2][k]);
       }
     }
-    float* o = nq + (size_t)win * 96 + lane;
-    o[0] = q0; o[32] = q1; o[64] = q2;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      if (ok[k]) {
+        float* o = nq + (size_t)(grp * 4 + k) * 96 + lane;
+        o[0] = q[0][k]; o[32] = q[1][k]; o[64] = q[2][k];
+      }
+    }
     __syncwarp();
   }
 }
@@ -396,8 +424,8 @@ extern "C" int b200mar_unigram_qkv_fwd(const float* z, const float* weight, cons
   using namespace b200mar;
   if (ph % kWin || pw % kWin || ph < kWin || pw < kWin || (nh != 6 && nh != 4)) return -1;
   const int nwin = B * (ph / kWin) * (pw / kWin);
-  int grid = (nwin + 7) / 8;
-  if (grid > 8 * sm_count()) grid = 8 * sm_count();
+  int grid = ((nwin + 3) / 4 + 7) / 8;               // a warp takes groups of four windows
+  if (grid > 2 * sm_count()) grid = 2 * sm_count();
   unigram_qkv_fwd_kernel<false><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
       z, weight, bias, qkv_w, qkv_b, 3 * (32 / nh) * nh, nq, B, ph, pw);
   B200MAR_CHECK(cudaGetLastError());
@@ -411,8 +439,8 @@ extern "C" int b200mar_unigram_qkv_fwd_s16(const void* z16, const float* weight,
   using namespace b200mar;
   if (ph % kWin || pw % kWin || ph < kWin || pw < kWin || (nh != 6 && nh != 4)) return -1;
   const int nwin = B * (ph / kWin) * (pw / kWin);
-  int grid = (nwin + 7) / 8;
-  if (grid > 8 * sm_count()) grid = 8 * sm_count();
+  int grid = ((nwin + 3) / 4 + 7) / 8;
+  if (grid > 2 * sm_count()) grid = 2 * sm_count();
   unigram_qkv_fwd_kernel<true><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
       (const float*)z16, weight, bias, qkv_w, qkv_b, 3 * (32 / nh) * nh, nq, B, ph, pw);
   B200MAR_CHECK(cudaGetLastError());
@@ -483,8 +511,8 @@ extern "C" int b200mar_ngram_ctx_infer_noalloc(const float* z, const float* uni_
   float* nq = nullptr;
   if (int rc = nq_scratch_ptr(&nq)) return rc;
   cudaStream_t st = (cudaStream_t)stream;
-  int grid = ((int)nwin + 7) / 8;
-  if (grid > 8 * sm_count()) grid = 8 * sm_count();
+  int grid = (((int)nwin + 3) / 4 + 7) / 8;          // a warp takes groups of four windows
+  if (grid > 2 * sm_count()) grid = 2 * sm_count();
   unigram_qkv_fwd_kernel<false><<<grid, kThreads, 0, st>>>(z, uni_w, uni_b, qkv_w, qkv_b, 3 * (32 / nh) * nh, nq, B, ph, pw);
   B200MAR_CHECK(cudaGetLastError());
   NgramParams p{};
