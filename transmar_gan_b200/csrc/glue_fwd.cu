@@ -26,7 +26,10 @@ __global__ void __launch_bounds__(256) shallow_tok_kernel(const float* __restric
                                                           const float* __restrict__ w,
                                                           const float* __restrict__ b,
                                                           float* __restrict__ c0, int B, int H, int W) {
-  const int cq = threadIdx.x & 15, pl = threadIdx.x >> 4;      // 4 channels, 16 pixels per pass
+  // 16 threads (4 channels each) per group of FOUR consecutive pixels of a row: the 3 x 6 input patch is loaded once
+  // for the four outputs and the pixel index is decomposed once per group, by multiply-shift (the kernel was
+  // instruction-bound at 45 % of its HBM floor: two integer divisions and nine guarded loads per float4 written)
+  const int cq = threadIdx.x & 15, pl = threadIdx.x >> 4;
   float wr[4][9], br[4];
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
@@ -34,27 +37,41 @@ __global__ void __launch_bounds__(256) shallow_tok_kernel(const float* __restric
 #pragma unroll
     for (int k = 0; k < 9; ++k) wr[j][k] = w[(cq * 4 + j) * 9 + k];
   }
-  const unsigned npix = (unsigned)B * H * W;           // < 2^31 (checked by the launcher): 32-bit index math
-  for (unsigned pix = blockIdx.x * 16u + pl; pix < npix; pix += gridDim.x * 16u) {
-    const unsigned rowi = pix / (unsigned)W;
-    const int xx = (int)(pix - rowi * W), yy = (int)(rowi % (unsigned)H);
-    const float* img = x + (pix - (unsigned)yy * W - xx);
-    float in[9];
+  const unsigned gw = ((unsigned)W + 3u) / 4u;
+  const unsigned ngrp = (unsigned)B * H * gw;          // < 2^31 (checked by the launcher): 32-bit index math
+  const FastDiv fgw = make_fastdiv(gw), fH = make_fastdiv((unsigned)H);
+  for (unsigned g = blockIdx.x * 16u + pl; g < ngrp; g += gridDim.x * 16u) {
+    const unsigned rowi = fdiv(g, fgw);                // b * H + y
+    const int x0 = (int)(g - rowi * gw) * 4;
+    const unsigned bb = fdiv(rowi, fH);
+    const int yy = (int)(rowi - bb * (unsigned)H);
+    const float* img = x + (size_t)bb * H * W;
+    float in[3][6];
 #pragma unroll
-    for (int dy = 0; dy < 3; ++dy)
+    for (int dy = 0; dy < 3; ++dy) {
+      const int y2 = yy + dy - 1;
+      const bool rowok = y2 >= 0 && y2 < H;
 #pragma unroll
-      for (int dx = 0; dx < 3; ++dx) {
-        const int y2 = yy + dy - 1, x2 = xx + dx - 1;
-        in[dy * 3 + dx] = (y2 >= 0 && y2 < H && x2 >= 0 && x2 < W) ? __ldg(img + (long long)y2 * W + x2) : 0.f;
+      for (int dx = 0; dx < 6; ++dx) {
+        const int x2 = x0 + dx - 1;
+        in[dy][dx] = (rowok && x2 >= 0 && x2 < W) ? __ldg(img + (size_t)y2 * W + x2) : 0.f;
       }
-    float o[4];
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      o[j] = br[j];
-#pragma unroll
-      for (int k = 0; k < 9; ++k) o[j] = fmaf(wr[j][k], in[k], o[j]);
     }
-    *reinterpret_cast<float4*>(c0 + (size_t)pix * 64 + cq * 4) = make_float4(o[0], o[1], o[2], o[3]);
+#pragma unroll
+    for (int px = 0; px < 4; ++px) {
+      if (x0 + px < W) {
+        float o[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          o[j] = br[j];
+#pragma unroll
+          for (int dy = 0; dy < 3; ++dy)
+#pragma unroll
+            for (int dx = 0; dx < 3; ++dx) o[j] = fmaf(wr[j][dy * 3 + dx], in[dy][px + dx], o[j]);
+        }
+        *reinterpret_cast<float4*>(c0 + ((size_t)rowi * W + x0 + px) * 64 + cq * 4) = make_float4(o[0], o[1], o[2], o[3]);
+      }
+    }
   }
 }
 
@@ -123,17 +140,19 @@ __global__ void __launch_bounds__(256) bottleneck_cat_kernel(
     const float* __restrict__ e1, const float* __restrict__ e2, const float* __restrict__ e3,
     float* __restrict__ cat, int B, int H, int W) {
   const unsigned n = (unsigned)B * H * W * 21u;         // < 2^31 (checked by the launcher)
+  const FastDiv fW = make_fastdiv((unsigned)W), fH = make_fastdiv((unsigned)H);
   for (unsigned idx = blockIdx.x * 256u + threadIdx.x; idx < n; idx += gridDim.x * 256u) {
-    const unsigned t = idx / 21u;
+    const unsigned t = idx / 21u;                       // (compile-time divisor: multiply-shift already)
     const int g = (int)(idx - t * 21u);
     float4 v;
     if (g < 16) {
       const float4 a = ld4(e1 + (size_t)t * 64 + g * 4), s = ld4(c0 + (size_t)t * 64 + g * 4);
       v = make_float4(a.x + leaky(s.x), a.y + leaky(s.y), a.z + leaky(s.z), a.w + leaky(s.w));
     } else {
-      const unsigned rowi = t / (unsigned)W;
-      const int xx = (int)(t - rowi * W), yy = (int)(rowi % (unsigned)H);
-      const long long b = rowi / (unsigned)H;
+      const unsigned rowi = fdiv(t, fW);
+      const unsigned bq = fdiv(rowi, fH);
+      const int xx = (int)(t - rowi * W), yy = (int)(rowi - bq * (unsigned)H);
+      const long long b = bq;
       float o[4];
       if (g < 20) {                       // scale 2: channel c <- source channel (c*2 + y%2)*2 + x%2
         const long long lo = ((b * (H / 2) + yy / 2) * (W / 2) + xx / 2) * 64;
@@ -437,7 +456,7 @@ using namespace b200mar;
 extern "C" int b200mar_shallow_tok_fwd(const float* x, const float* w, const float* b, float* c0,
                                        int B, int H, int W, void* stream) {
   if (B <= 0 || H <= 0 || W <= 0 || (long long)B * H * W >= (1ll << 31)) return -1;
-  shallow_tok_kernel<<<grid_for((long long)B * H * W, 16 * 8), 256, 0, (cudaStream_t)stream>>>(x, w, b, c0, B, H, W);
+  shallow_tok_kernel<<<grid_for((long long)B * H * ((W + 3) / 4), 16 * 4), 256, 0, (cudaStream_t)stream>>>(x, w, b, c0, B, H, W);
   B200MAR_CHECK(cudaGetLastError());
   return 0;
 }
