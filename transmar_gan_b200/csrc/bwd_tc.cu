@@ -18,6 +18,7 @@
 //
 // BF16 (fp32 range, 8-bit significand) is used for every backward operand: gradients span many orders of
 // magnitude, so the forward kernels' fp16 + power-of-two scaling is not carried over.
+#include <cstdlib>
 #include "common.cuh"
 #include "tc.cuh"
 #include <cuda_bf16.h>
@@ -430,6 +431,325 @@ __global__ void __launch_bounds__(128 * kBwdWorkers, 1) mlp_bwd_tc_kernel(MlpBwd
   if (warp == 0) tc::tmem_dealloc<512>(*tmem_slot);
 }
 
+// ================================================================================================
+// mlp_bwd_tma_kernel - the same arithmetic with every global access of the tile moved by the TMA engine.
+// The plain kernel above reads / writes each token row from its own thread (32 different 128-byte lines per warp
+// instruction, 144 such instructions per thread and tile): ~3 K LSU cycles per warp and tile, i.e. ~85 us of its
+// 130 us at 262 k tokens.  Here the a and dout tiles arrive as 128 B-swizzled boxes (prefetched one tile ahead), the
+// four bf16 exports and da are staged in shared memory in the same swizzled row layout (a row thread touches only
+// its own 128-byte rows, conflict-free) and leave as bulk tensor stores.  Three 32 KB buffers per worker, each
+// reused twice per tile; a buffer written in phase k is stored after the worker barrier that ends phase k and is
+// known to be free again after the barrier that ends phase k + 1 (the leader waits for the bulk read before it):
+//   bufA: a tile -> a16 (over box 0, own rows) -> next a tile (loaded after the barrier of phase 1)
+//   bufD: dout tile (row kept in registers) -> dy16 (over box 0) -> da tile -> next dout tile
+//   bufG: g16 -> dh16
+struct MlpBwdTmaSmem {
+  static constexpr int oWork = ((MlpBwdSmem::oBar + kBwdWorkers * 64 + 16 + 1023) / 1024) * 1024;   // 8 mbarrier slots per worker
+  static constexpr int kWorkBytes = 3 * 32768;
+  static constexpr int kBytes = oWork + kBwdWorkers * kWorkBytes;
+  static_assert(kBytes <= 232448, "mlp_bwd_tma shared memory exceeds 227 KB");
+};
+
+__global__ void __launch_bounds__(128 * kBwdWorkers, 1)
+mlp_bwd_tma_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapDout,
+                   const __grid_constant__ CUtensorMap mapDa, const __grid_constant__ CUtensorMap mapA16,
+                   const __grid_constant__ CUtensorMap mapG16, const __grid_constant__ CUtensorMap mapDh16,
+                   const __grid_constant__ CUtensorMap mapDy16, MlpBwdTcParams p) {
+  using L = MlpBwdSmem;
+  using LT = MlpBwdTmaSmem;
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  unsigned char* sW1 = smem_raw + L::oW1;
+  unsigned char* sW2 = smem_raw + L::oW2;
+  float* sB1 = reinterpret_cast<float*>(smem_raw + L::oB1);
+  float* sB2 = reinterpret_cast<float*>(smem_raw + L::oB2);
+  float* sLnW = reinterpret_cast<float*>(smem_raw + L::oLnW);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + L::oBar);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem_raw + L::oBar + kBwdWorkers * 64);
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  const int wk = warp >> 2, wq = warp & 3;
+  uint64_t* bar = bars + wk * 8;                     // [0] fc1  [1] fc2  [2] dg  [3] da  [4] a tile  [5] dout tile
+  uint64_t* barA = bar + 4;
+  uint64_t* barD = bar + 5;
+  unsigned char* bufA = smem_raw + LT::oWork + wk * LT::kWorkBytes;   // a tile (fp32) -> a16 staging (box-0 region)
+  unsigned char* bufD = bufA + 32768;                                 // dout tile -> dy16 staging -> da tile
+  unsigned char* bufG = bufA + 65536;                                 // g16 staging -> dh16 staging
+  const bool leader = wq == 0 && lane == 0;          // bulk groups are per thread: one fixed thread
+  // byte offset of 16-byte chunk i (8 bf16) of row r in a bf16 [128 rows][128 B] tile (128 B swizzle)
+  auto off16 = [](int r, int i) -> uint32_t { return (uint32_t)(r * 128 + ((i ^ (r & 7)) << 4)); };
+
+  // ---- stage the weights as bf16 chunk-major tiles
+  for (int idx = tid; idx < 128 * 8; idx += 128 * kBwdWorkers) {          // fc1 [128][64]
+    const int n = idx & 127, kc = idx >> 7;
+    const float4* src = reinterpret_cast<const float4*>(p.fc1_w + n * 64 + kc * 8);
+    const float4 x = src[0], y = src[1];
+    *reinterpret_cast<uint4*>(sW1 + kc * 2048 + n * 16) =
+        make_uint4(tc::pack_bf16(x.x, x.y), tc::pack_bf16(x.z, x.w), tc::pack_bf16(y.x, y.y), tc::pack_bf16(y.z, y.w));
+  }
+  for (int idx = tid; idx < 64 * 16; idx += 128 * kBwdWorkers) {          // fc2 [64][128]
+    const int n = idx & 63, kc = idx >> 6;
+    const float4* src = reinterpret_cast<const float4*>(p.fc2_w + n * 128 + kc * 8);
+    const float4 x = src[0], y = src[1];
+    *reinterpret_cast<uint4*>(sW2 + kc * 1024 + n * 16) =
+        make_uint4(tc::pack_bf16(x.x, x.y), tc::pack_bf16(x.z, x.w), tc::pack_bf16(y.x, y.y), tc::pack_bf16(y.z, y.w));
+  }
+  if (tid < 128) sB1[tid] = p.fc1_b[tid];
+  if (tid < 64) { sB2[tid] = p.fc2_b[tid]; sLnW[tid] = p.ln_w[tid]; }
+  if (tid == 0) {
+    for (int i = 0; i < 8 * kBwdWorkers; ++i) tc::mbar_init(bars + i, 1);
+    tc::fence_barrier_init();
+    tma::prefetch_desc(&mapA); tma::prefetch_desc(&mapDout); tma::prefetch_desc(&mapDa); tma::prefetch_desc(&mapA16);
+    tma::prefetch_desc(&mapG16); tma::prefetch_desc(&mapDh16); tma::prefetch_desc(&mapDy16);
+  }
+  if (warp == 0) tc::tmem_alloc<512>(tmem_slot);
+  tc::fence_async_smem();
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+
+  // TMEM columns of a worker (256):
+  //   [0,128)   D1 = fc1 pre-activation -> { g0 [0,32) | gp0 [32,64) | g1 [64,96) | gp1 [96,128) } packed bf16
+  //             (g: GELU output, A operand of fc2; gp: GELU derivative, later overwritten by dh, A operand of da)
+  //             -> dg quarters 0,1 over g0, g1
+  //   [128,192) D2 = fc2 output -> dg quarters 2,3 -> da accumulator
+  //   [192,224) a packed (A operand of fc1) -> dy packed (A operand of dg)
+  const uint32_t tbase = *tmem_slot + wk * 256;
+  const uint32_t lane_addr = (uint32_t)(wq * 32) << 16;
+  const uint32_t tl = tbase + lane_addr;
+  constexpr uint32_t cD2 = 128, cA = 192;
+  constexpr uint32_t kI128 = tc::idesc_bf16(128, 128), kI64 = tc::idesc_bf16(128, 64),
+                     kI32mn = tc::idesc_bf16(128, 32, false, true), kI64mn = tc::idesc_bf16(128, 64, false, true);
+  const uint64_t dW1k = tc::desc_kmajor16(tc::smem_u32(sW1), 128), dW2k = tc::desc_kmajor16(tc::smem_u32(sW2), 64),
+                 dW1mn = tc::desc_mnmajor16(tc::smem_u32(sW1), 128), dW2mn = tc::desc_mnmajor16(tc::smem_u32(sW2), 64);
+  const int row = wq * 32 + lane;
+  uint32_t ph = 0;
+  float db2_0 = 0.f, db2_1 = 0.f, dg_0 = 0.f, dg_1 = 0.f, dbe_0 = 0.f, dbe_1 = 0.f;   // columns 2*lane, 2*lane+1
+
+  const long long ntile = (p.n_tok + 127) / 128;
+  const long long tstride = (long long)gridDim.x * kBwdWorkers;
+  auto load_tile = [&](const CUtensorMap* m, uint64_t* b, unsigned char* dst, long long t) {
+    tma::mbar_expect_tx(b, 32768);
+    tma::load_2d(m, b, dst, 0, (int)(t * 128));
+    tma::load_2d(m, b, dst + 16384, 32, (int)(t * 128));
+  };
+  if (leader && (long long)blockIdx.x * kBwdWorkers + wk < ntile) {
+    load_tile(&mapA, barA, bufA, (long long)blockIdx.x * kBwdWorkers + wk);
+    load_tile(&mapDout, barD, bufD, (long long)blockIdx.x * kBwdWorkers + wk);
+  }
+  for (long long tile = (long long)blockIdx.x * kBwdWorkers + wk; tile < ntile; tile += tstride) {
+    const int r0 = (int)(tile * 128);
+    // ---- P0: a row -> packed bf16 A operand in TMEM + export
+    {
+      uint32_t ap[32];
+      tc::mbar_wait(barA, ph, &g_tc_error);             // the a tile (rows past n_tok are zero-filled by the TMA)
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const float4 v = *reinterpret_cast<const float4*>(bufA + tma::tile_off(row, i));
+        ap[2 * i] = tc::pack_bf16(v.x, v.y);
+        ap[2 * i + 1] = tc::pack_bf16(v.z, v.w);
+      }
+      tc::tmem_st32(tl + cA, reinterpret_cast<const float(&)[32]>(ap));
+      // a16 export: the bf16 row over this thread's OWN fp32 row bytes of box 0 (already in registers)
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        *reinterpret_cast<uint4*>(bufA + off16(row, i)) = make_uint4(ap[4 * i], ap[4 * i + 1], ap[4 * i + 2], ap[4 * i + 3]);
+    }
+    tc::tmem_wait_st();
+    tc::fence_async_smem();
+    tc::tc_fence_before();
+    if (leader) tma::wait_read_all();                  // every store of the previous tile has left bufG / bufD
+    tc::worker_sync(1 + wk);
+    if (leader) { tma::store_2d(&mapA16, bufA, 0, r0); tma::commit_group(); }
+    if (wq == 0) {
+      tc::tc_fence_after();
+      if (tc::elect_one()) {
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks)
+          tc::mma_f16_ts(tbase, tbase + cA + ks * 8, dW1k + ks * 256, kI128, ks > 0);
+        tc::mma_commit(bar + 0);
+      }
+      __syncwarp();
+    }
+    tc::mbar_wait(bar + 0, ph, &g_tc_error);
+    tc::tc_fence_after();
+    // ---- P1: GELU and its derivative, two halves of 64 hidden channels
+#pragma unroll 1
+    for (int half = 0; half < 2; ++half) {
+      float v[64];
+      tc::tmem_ld64(tl + half * 64, v);
+      uint32_t gq[32], gpq[32];
+      const float* b1 = sB1 + half * 64;
+#pragma unroll
+      for (int c = 0; c < 64; c += 2) {
+        float g0, g1, d0, d1;
+        gelu_and_grad(v[c] + b1[c], g0, d0);
+        gelu_and_grad(v[c + 1] + b1[c + 1], g1, d1);
+        gq[c >> 1] = tc::pack_bf16(g0, g1);
+        gpq[c >> 1] = tc::pack_bf16(d0, d1);
+      }
+      tc::tmem_st32(tl + half * 64, reinterpret_cast<const float(&)[32]>(gq));
+      tc::tmem_st32(tl + half * 64 + 32, reinterpret_cast<const float(&)[32]>(gpq));
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        *reinterpret_cast<uint4*>(bufG + half * 16384 + off16(row, i)) =
+            make_uint4(gq[4 * i], gq[4 * i + 1], gq[4 * i + 2], gq[4 * i + 3]);
+    }
+    tc::tmem_wait_st();
+    tc::fence_async_smem();
+    tc::tc_fence_before();
+    if (leader) tma::wait_read_all();                  // the a16 store has left bufA
+    tc::worker_sync(1 + wk);
+    if (leader) {
+      tma::store_2d(&mapG16, bufG, 0, r0); tma::store_2d(&mapG16, bufG + 16384, 64, r0); tma::commit_group();
+      if (tile + tstride < ntile) load_tile(&mapA, barA, bufA, tile + tstride);
+    }
+    if (wq == 0) {
+      tc::tc_fence_after();
+      if (tc::elect_one()) {
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          tc::mma_f16_ts(tbase + cD2, tbase + (ks < 4 ? ks * 8 : 64 + (ks - 4) * 8), dW2k + ks * 128, kI64, ks > 0);
+        tc::mma_commit(bar + 1);
+      }
+      __syncwarp();
+    }
+    tc::mbar_wait(bar + 1, ph, &g_tc_error);
+    tc::tc_fence_after();
+    // ---- P2: LayerNorm backward on the row -> dy (packed bf16 A operand + export), column sums
+    float d[64];                                       // the dout row: read once, reused for da at the tile's end
+    {
+      float y[64];
+      tc::tmem_ld64(tl + cD2, y);
+      float m4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int i = 0; i < 64; ++i) { y[i] += sB2[i]; m4[i & 3] += y[i]; }
+      const float mean = ((m4[0] + m4[1]) + (m4[2] + m4[3])) * (1.0f / 64.f);
+      float v4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int i = 0; i < 64; ++i) { y[i] -= mean; v4[i & 3] = fmaf(y[i], y[i], v4[i & 3]); }
+      const float rstd = 1.0f / sqrtf(((v4[0] + v4[1]) + (v4[2] + v4[3])) * (1.0f / 64.f) + kLnEps);
+      tc::mbar_wait(barD, ph, &g_tc_error);             // the dout tile
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const float4 v = *reinterpret_cast<const float4*>(bufD + tma::tile_off(row, i));
+        d[4 * i] = v.x; d[4 * i + 1] = v.y; d[4 * i + 2] = v.z; d[4 * i + 3] = v.w;
+      }
+      float s1[4] = {0.f, 0.f, 0.f, 0.f}, s2[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int i = 0; i < 64; ++i) {
+        y[i] *= rstd;                                  // normalised row
+        const float t = d[i] * sLnW[i];
+        s1[i & 3] += t;
+        s2[i & 3] = fmaf(t, y[i], s2[i & 3]);
+      }
+      const float m1 = ((s1[0] + s1[1]) + (s1[2] + s1[3])) * (1.0f / 64.f);
+      const float m2 = ((s2[0] + s2[1]) + (s2[2] + s2[3])) * (1.0f / 64.f);
+      warp_colsum64([&](int i) { return d[i] * y[i]; }, lane, dg_0, dg_1);      // d_ln_w
+      warp_colsum64([&](int i) { return d[i]; }, lane, dbe_0, dbe_1);           // d_ln_b
+#pragma unroll
+      for (int i = 0; i < 64; ++i) y[i] = rstd * (fmaf(d[i], sLnW[i], -m1) - y[i] * m2);   // dy
+      warp_colsum64([&](int i) { return y[i]; }, lane, db2_0, db2_1);           // d_fc2_b
+      uint32_t dq[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) dq[i] = tc::pack_bf16(y[2 * i], y[2 * i + 1]);
+      tc::tmem_st32(tl + cA, reinterpret_cast<const float(&)[32]>(dq));
+      // dy16 export over this thread's own dout row bytes of box 0 (the row stays in registers)
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        *reinterpret_cast<uint4*>(bufD + off16(row, i)) = make_uint4(dq[4 * i], dq[4 * i + 1], dq[4 * i + 2], dq[4 * i + 3]);
+    }
+    tc::tmem_wait_st();
+    tc::fence_async_smem();
+    tc::tc_fence_before();
+    if (leader) tma::wait_read_all();                  // the g16 store has left bufG
+    tc::worker_sync(1 + wk);
+    if (leader) { tma::store_2d(&mapDy16, bufD, 0, r0); tma::commit_group(); }
+    // ---- dg = dy W2 in four quarters of 32 hidden channels (B = the fc2 tile read MN-major)
+    if (wq == 0) {
+      tc::tc_fence_after();
+      if (tc::elect_one()) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const uint32_t dcol = q == 0 ? 0u : (q == 1 ? 64u : (q == 2 ? 128u : 160u));
+#pragma unroll
+          for (int ks = 0; ks < 4; ++ks)
+            tc::mma_f16_ts(tbase + dcol, tbase + cA + ks * 8, dW2mn + q * 256 + ks * 16, kI32mn, ks > 0);
+        }
+        tc::mma_commit(bar + 2);
+      }
+      __syncwarp();
+    }
+    tc::mbar_wait(bar + 2, ph, &g_tc_error);
+    tc::tc_fence_after();
+    // ---- P3: dh = dg * GELU'(pre) -> packed bf16 over gp (A operand of da) + export
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const uint32_t dcol = q == 0 ? 0u : (q == 1 ? 64u : (q == 2 ? 128u : 160u));
+      const uint32_t gcol = q == 0 ? 32u : (q == 1 ? 48u : (q == 2 ? 96u : 112u));
+      float dg[32], gp[16];
+      tc::tmem_ld32(tl + dcol, dg);
+      tc::tmem_ld16(tl + gcol, gp);
+      uint32_t hq[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const uint32_t u = __float_as_uint(gp[i]);
+        hq[i] = tc::pack_bf16(dg[2 * i] * bf16_lo(u), dg[2 * i + 1] * bf16_hi(u));
+      }
+      tc::tmem_st16(tl + gcol, reinterpret_cast<const float(&)[16]>(hq));
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        *reinterpret_cast<uint4*>(bufG + (q >> 1) * 16384 + off16(row, (q & 1) * 4 + i)) =
+            make_uint4(hq[4 * i], hq[4 * i + 1], hq[4 * i + 2], hq[4 * i + 3]);
+    }
+    tc::tmem_wait_st();
+    tc::fence_async_smem();
+    tc::tc_fence_before();
+    if (leader) tma::wait_read_all();                  // the dy16 store has left bufD
+    tc::worker_sync(1 + wk);
+    if (leader) { tma::store_2d(&mapDh16, bufG, 0, r0); tma::store_2d(&mapDh16, bufG + 16384, 64, r0); tma::commit_group(); }
+    // ---- da = dout + dh W1 (B = the fc1 tile read MN-major)
+    if (wq == 0) {
+      tc::tc_fence_after();
+      if (tc::elect_one()) {
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          tc::mma_f16_ts(tbase + cD2, tbase + (ks < 4 ? 32 + ks * 8 : 96 + (ks - 4) * 8), dW1mn + ks * 16, kI64mn, ks > 0);
+        tc::mma_commit(bar + 3);
+      }
+      __syncwarp();
+    }
+    tc::mbar_wait(bar + 3, ph, &g_tc_error);
+    tc::tc_fence_after();
+    {
+      float v[64];
+      tc::tmem_ld64(tl + cD2, v);
+#pragma unroll
+      for (int i = 0; i < 16; ++i)
+        *reinterpret_cast<float4*>(bufD + tma::tile_off(row, i)) =
+            make_float4(d[4 * i] + v[4 * i], d[4 * i + 1] + v[4 * i + 1], d[4 * i + 2] + v[4 * i + 2], d[4 * i + 3] + v[4 * i + 3]);
+    }
+    tc::fence_async_smem();
+    tc::tc_fence_before();
+    tc::worker_sync(1 + wk);
+    if (leader) {
+      tma::store_2d(&mapDa, bufD, 0, r0); tma::store_2d(&mapDa, bufD + 16384, 32, r0); tma::commit_group();
+      if (tile + tstride < ntile) {
+        tma::wait_read_all();                          // the da store has left bufD
+        load_tile(&mapDout, barD, bufD, tile + tstride);
+      }
+    }
+    ph ^= 1;
+  }
+  if (leader) tma::wait_all();
+  // ---- flush the column sums (lane l of every warp holds columns 2l, 2l+1)
+  atomicAdd(p.d_fc2_b + 2 * lane, db2_0); atomicAdd(p.d_fc2_b + 2 * lane + 1, db2_1);
+  atomicAdd(p.d_ln_w + 2 * lane, dg_0);   atomicAdd(p.d_ln_w + 2 * lane + 1, dg_1);
+  atomicAdd(p.d_ln_b + 2 * lane, dbe_0);  atomicAdd(p.d_ln_b + 2 * lane + 1, dbe_1);
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc<512>(*tmem_slot);
+}
+
 int launch_wgrad(const uint16_t* in16, const uint16_t* g16, float* dw, float* dbias, long long n_tok,
                  int cin, int cout, int ld, int cin_valid, int hs, int ps, int hd, int A, cudaStream_t st) {
   if (n_tok <= 0 || (cin != 64 && cin != 128) || cout % 32 || cout < 64 || cout > 256) return -1;
@@ -487,7 +807,22 @@ extern "C" int b200mar_mlp_bwd_tc(const float* a, const float* dout, const float
   const long long ntile = (n_tok + 127) / 128;
   long long grid = (ntile + kBwdWorkers - 1) / kBwdWorkers;
   if (grid > sm_count()) grid = sm_count();
-  mlp_bwd_tc_kernel<<<(int)grid, 128 * kBwdWorkers, smem, st>>>(p);
+  static const bool plain = getenv("B200MAR_MLP_BWD_PLAIN") != nullptr;   // development knob: the plain-load kernel
+  CUtensorMap mA, mDo, mDa, mA16, mG16, mDh16, mDy16;
+  if (!plain && n_tok * 1 <= 0x7fffffffLL &&
+      !tma::encode_rows64(&mA, a, n_tok) && !tma::encode_rows64(&mDo, dout, n_tok) && !tma::encode_rows64(&mDa, da, n_tok) &&
+      !tma::encode_rows64_16(&mA16, p.a16, n_tok) && !tma::encode_rows16_box64(&mG16, p.g16, n_tok, 128) &&
+      !tma::encode_rows16_box64(&mDh16, p.dh16, n_tok, 128) && !tma::encode_rows64_16(&mDy16, p.dy16, n_tok)) {
+    static DeviceOnce configured_tma;
+    if (configured_tma.first()) {
+      B200MAR_CHECK(cudaFuncSetAttribute(mlp_bwd_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)MlpBwdTmaSmem::kBytes));
+      configured_tma.done();
+    }
+    mlp_bwd_tma_kernel<<<(int)grid, 128 * kBwdWorkers, MlpBwdTmaSmem::kBytes, st>>>(mA, mDo, mDa, mA16, mG16, mDh16, mDy16, p);
+  } else {
+    mlp_bwd_tc_kernel<<<(int)grid, 128 * kBwdWorkers, smem, st>>>(p);
+  }
   B200MAR_CHECK(cudaGetLastError());
   if (int rc = launch_wgrad(p.a16, p.dh16, d_fc1_w, d_fc1_b, n_tok, 64, 128, 64, 64, 0, 0, 0, 0, st)) return rc;   // dW1 [128][64], db1
   if (int rc = launch_wgrad(p.g16, p.dy16, d_fc2_w, nullptr, n_tok, 128, 64, 128, 128, 0, 0, 0, 0, st)) return rc;  // dW2 [64][128]

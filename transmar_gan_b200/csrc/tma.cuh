@@ -174,6 +174,21 @@ inline int encode_rows64_16(CUtensorMap* out, const void* base, long long n_rows
   return r == CUDA_SUCCESS ? 0 : -3;
 }
 
+// ---- host: a token-major BF16 matrix [n_rows][C] (C a multiple of 64): box [128 rows][64 bf16 = 128 B] at a channel
+// offset that is a multiple of 64, 128 B swizzle (16 KB) - the store side of kernels that stage a bf16 export tile
+inline int encode_rows16_box64(CUtensorMap* out, const void* base, long long n_rows, int C) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) return -2;
+  const cuuint64_t gdim[2] = {(cuuint64_t)C, (cuuint64_t)n_rows};
+  const cuuint64_t gstride[1] = {(cuuint64_t)C * 2};
+  const cuuint32_t box[2] = {64, 128};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride,
+                        box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? 0 : -3;
+}
+
 // ---- host: general form over a token grid [B][H][W][64] fp32: box = [1][by rows][bx tokens][32 floats]
 // taking every `step`-th token in x and y (step = 2: one parity class of the 2x2 PatchMerging
 // neighbourhood), 128 B swizzle.  The box lands as by*bx rows of 128 B, row = y*bx + x.
