@@ -709,7 +709,8 @@ struct AttnDxSmem {
   static constexpr int kLd = 68;                     // fp32 row stride of the dX tile
   static constexpr int wDx = 0;                      // fp32 [128][68]
   static constexpr int wCw = wDx + 128 * kLd * 4;    // int [128] source window of each row
-  static constexpr int kWorkBytes = wCw + 512;
+  static constexpr int wTok = wCw + 512;             // long long [128] token of each row (-1: no token)
+  static constexpr int kWorkBytes = wTok + 1024;
   static constexpr int kBytes = oWork + kDxWorkers * kWorkBytes;
 };
 
@@ -728,6 +729,7 @@ __global__ void __launch_bounds__(128 * kDxWorkers, 1) attn_bwd_dx_kernel(AttnBw
   unsigned char* sW = smem_raw + L::oWork + wk * L::kWorkBytes;
   float* sDx = reinterpret_cast<float*>(sW + L::wDx);
   int* sCw = reinterpret_cast<int*>(sW + L::wCw);
+  long long* sTok = reinterpret_cast<long long*>(sW + L::wTok);
   uint64_t* bar = bars + wk;
 
   for (int idx = tid; idx < 192 * 8; idx += 128 * kDxWorkers) {
@@ -768,6 +770,7 @@ __global__ void __launch_bounds__(128 * kDxWorkers, 1) attn_bwd_dx_kernel(AttnBw
     int cwin = 0;
     if (wvalid) { const Slot sl = slot_of(g, win, lrow); tok = sl.tok; cwin = sl.cwin; }
     sCw[row] = cwin;
+    sTok[row] = wvalid ? tok : -1;
     {
       const uint4* src = reinterpret_cast<const uint4*>(pp.dqkv16 + ((size_t)tile * 128 + row) * 192);
 #pragma unroll
@@ -802,18 +805,25 @@ __global__ void __launch_bounds__(128 * kDxWorkers, 1) attn_bwd_dx_kernel(AttnBw
 #pragma unroll
       for (int i = 0; i < 16; ++i)
         *reinterpret_cast<float4*>(sDx + row * L::kLd + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-      if (wvalid) {
-        const float4* src = reinterpret_cast<const float4*>(p.da + (size_t)tok * 64);
-        float4* dst = reinterpret_cast<float4*>(p.dz + (size_t)tok * 64);
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          const float4 gv = __ldg(src + i);
-          dst[i] = make_float4(gv.x + v[4 * i], gv.y + v[4 * i + 1], gv.z + v[4 * i + 2], gv.w + v[4 * i + 3]);
-        }
-      }
     }
     tc::tc_fence_before();
     tc::worker_sync(1 + wk);
+    // dz = da + dX, COOPERATIVELY: a warp instruction covers two whole token rows (2 x 256 contiguous bytes) instead
+    // of one 16-byte piece of 32 different rows (32 L1 lines per instruction made the one-row-per-thread form
+    // LSU-bound); the rows of this warp's quarter of the tile come from the fp32 dX tile in shared memory
+    {
+      const int half = lane >> 4, c4 = (lane & 15) * 4;
+#pragma unroll 4
+      for (int it = 0; it < 16; ++it) {
+        const int r = wq * 32 + it * 2 + half;
+        const long long t = sTok[r];
+        if (t >= 0) {
+          const float4 gv = __ldg(reinterpret_cast<const float4*>(p.da + (size_t)t * 64 + c4));
+          const float4 dx = *reinterpret_cast<const float4*>(sDx + r * L::kLd + c4);
+          *reinterpret_cast<float4*>(p.dz + (size_t)t * 64 + c4) = make_float4(gv.x + dx.x, gv.y + dx.y, gv.z + dx.z, gv.w + dx.w);
+        }
+      }
+    }
     // dctx: the 16 slots of a window quadrant share one source window (shift 4) / all 64 do (shift 0)
 #pragma unroll
     for (int it = 0; it < 4; ++it) {
