@@ -105,3 +105,47 @@ def test_glue_tc_kernels_stay_inside_their_outputs(geom):
     ar.check()                                        # the inputs' bands: nothing was written around x
     assert written(y) and written(x2) and written(p0)
     assert ops.tc_error() == 0
+
+
+@pytest.mark.parametrize("case", [("encoder_layer1.blocks.1.", 6, 4), ("encoder_layer2.blocks.0.", 4, 0)])
+@pytest.mark.parametrize("geom", [(1, 24, 40), (3, 8, 24), (2, 16, 16)])
+def test_compensated_and_backward_kernels_stay_inside_their_outputs(case, geom):
+    """The precision-level "tf32c" kernels (attention incl. the saved-O form, MLP) and the TMA-fed MLP backward, whose
+    bf16 exports go to a caller-owned scratch of n_tok * 384 elements: bands around every output and the scratch."""
+    import transmar_gan_b200 as T
+    ops, lib = T.ops, T._cabi.lib()
+    prefix, nh, shift = case
+    B, ph, pw = geom
+    wh, ww = ph // 8, pw // 8
+    sd = O.synthetic_state_dict("W1", seed=1)
+    P = [sd[prefix + n].cuda().contiguous() for n in ops.NSTB_PARAM_NAMES]
+    p = [t.data_ptr() for t in P]
+    g = torch.Generator().manual_seed(5)
+    n = B * ph * pw                                   # a multiple of 64, not always of 128
+    ntile = (B * wh * ww + 1) // 2
+    ar = Arena(40 * BAND + 16 * n * 64 + 2 * ntile * 128 * 64)
+    z = ar.take((B, n // B, 64), fill=torch.randn(B, n // B, 64, generator=g).cuda())
+    ctx = ar.take((B, wh * ww, 64), fill=(torch.randn(B, wh * ww, 64, generator=g) * 0.5).cuda())
+    dout = ar.take((B, n // B, 64), fill=torch.randn(B, n // B, 64, generator=g).cuda())
+    a = ar.take((B, n // B, 64))
+    a2 = ar.take((B, n // B, 64))
+    o16 = ar.take((ntile * 128, 64), torch.bfloat16)
+    out = ar.take((B, n // B, 64))
+    zs = ar.take((B, n // B, 64), fill=z)
+    da = ar.take((B, n // B, 64))
+    scratch = ar.take((n * 384,), torch.bfloat16)
+    G = [ar.take(tuple(t.shape), fill=torch.zeros_like(t)) for t in P[18:24]]
+    st = torch.cuda.current_stream().cuda_stream
+    assert lib.b200mar_attn_tc_fwd_comp(z.data_ptr(), ctx.data_ptr(), *p[10:18], a.data_ptr(), 0, B, ph, pw, nh, shift, st) == 0
+    assert lib.b200mar_attn_tc_fwd_comp(z.data_ptr(), ctx.data_ptr(), *p[10:18], a2.data_ptr(), o16.data_ptr(), B, ph, pw, nh,
+                                        shift, st) == 0
+    assert lib.b200mar_mlp_tma_fwd_comp(a.data_ptr(), zs.data_ptr(), *p[18:24], out.data_ptr(), n, st) == 0
+    assert lib.b200mar_mlp_bwd_tc(a.data_ptr(), dout.data_ptr(), *p[18:24], da.data_ptr(), *[t.data_ptr() for t in G],
+                                  scratch.data_ptr(), n, st) == 0
+    ar.check()
+    assert ops.tc_error() == 0
+    assert torch.equal(a, a2)
+    for t in (a, out, zs, da, scratch):
+        assert written(t)
+    valid = B * wh * ww * 64                           # the rows of a half-empty last tile are never written
+    assert written(o16[:valid])
