@@ -61,6 +61,35 @@ __device__ unsigned long long g_attn_prof[32];
 #endif
 
 constexpr float kLog2e = 1.4426950408889634f;
+// The kernel is bound by the latency of each worker's serial per-head chain (measured: halving the MUFU work or
+// cutting 8 % of all instructions elsewhere changes nothing), so the row arithmetic ON that chain is kept short:
+//  * TF32 operands are rounded by an integer add: cvt.rna.tf32.f32 compiles to FSETP + IADD + LOP3, and the tensor
+//    core ignores the low 13 bits of a kind::tf32 operand, so adding half an ulp of the 10-bit significand IS
+//    round-to-nearest, ties away from zero, for every finite value (results bit-identical);
+//  * the per-head bias / normalisation arithmetic uses the packed .f32x2 instructions of sm_100;
+//  * 1 / x and 1 / sqrt(x) are single MUFU operations (the IEEE forms add a Newton step, denormal pre-scaling and a
+//    range-check branch).  The compensated kernel (COMP) keeps the IEEE forms.
+// Together 1.470 / 1.529 -> 1.407 / 1.469 ms per launch at 32 x 416^2.  Packing the LayerNorm epilogue or the row
+// conversion the same way (more spills) and moving the O_h scaling behind the S_h issue were measured and lost.
+__device__ __forceinline__ float round_tf32_add(float x) { return __uint_as_float(__float_as_uint(x) + 0x1000u); }
+template <bool COMP>
+__device__ __forceinline__ float rcp_op(float x) {
+  if constexpr (!COMP) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+  else return 1.0f / x;
+}
+template <bool COMP>
+__device__ __forceinline__ float rsqrt_op(float x) {     // callers pass x >= 1e-24: no denormal pre-scaling needed
+  if constexpr (!COMP) { float y; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+  else return rsqrtf(x);
+}
+__device__ __forceinline__ void mul2(float& a, float& b, float c) {
+  const float2 r = __fmul2_rn(make_float2(a, b), make_float2(c, c));
+  a = r.x; b = r.y;
+}
+__device__ __forceinline__ void fma2(float& a, float& b, float c, float e, float f) {   // (a, b) = (a, b) * c + (e, f)
+  const float2 r = __ffma2_rn(make_float2(a, b), make_float2(c, c), make_float2(e, f));
+  a = r.x; b = r.y;
+}
 // workers (tiles in flight) per CTA.  NH = 6: heads are packed as [q10|k10|v10|0 0] = 32 accumulator
 // columns, so a worker needs 2 x 32 (qkv, double-buffered; O_h over the dead buffer) + 64 (S/P/Y) = 128
 // TMEM columns and FOUR fit; NH = 4 (head dim 16): 2 x 48 + 64 = 160 columns, three workers.
@@ -540,19 +569,49 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
       float qs = 0.f, ks = 0.f;
       {
         const float* b = sBqkv + h * HS;               // packed [q | k | v] with stride PS; pad rows are exact zeros
+        if constexpr (!COMP) {                         // two values per instruction
+          static_assert(HD % 2 == 0 && PS % 2 == 0, "pairs");
+          float q0 = 0.f, q1 = 0.f, k0 = 0.f, k1 = 0.f;
 #pragma unroll
-        for (int d = 0; d < HD; ++d) {
-          qkv[d] = fmaf(qkv[d], xinv, b[d]);           // undo the row's power-of-two input scale
-          qkv[PS + d] = fmaf(qkv[PS + d], xinv, b[PS + d]);
-          qkv[2 * PS + d] = fmaf(qkv[2 * PS + d], xinv, b[2 * PS + d]);
-          qs = fmaf(qkv[d], qkv[d], qs);
-          ks = fmaf(qkv[PS + d], qkv[PS + d], ks);
+          for (int d = 0; d < 3 * PS; d += 2)          // undo the row's power-of-two input scale
+            if (d % PS < HD) fma2(qkv[d], qkv[d + 1], xinv, b[d], b[d + 1]);
+#pragma unroll
+          for (int d = 0; d < HD; d += 2) {
+            const float2 sq = __ffma2_rn(make_float2(qkv[d], qkv[d + 1]), make_float2(qkv[d], qkv[d + 1]), make_float2(q0, q1));
+            q0 = sq.x; q1 = sq.y;
+            const float2 sk = __ffma2_rn(make_float2(qkv[PS + d], qkv[PS + d + 1]), make_float2(qkv[PS + d], qkv[PS + d + 1]),
+                                         make_float2(k0, k1));
+            k0 = sk.x; k1 = sk.y;
+          }
+          qs = q0 + q1;
+          ks = k0 + k1;
+        } else {
+#pragma unroll
+          for (int d = 0; d < HD; ++d) {
+            qkv[d] = fmaf(qkv[d], xinv, b[d]);           // undo the row's power-of-two input scale
+            qkv[PS + d] = fmaf(qkv[PS + d], xinv, b[PS + d]);
+            qkv[2 * PS + d] = fmaf(qkv[2 * PS + d], xinv, b[2 * PS + d]);
+            qs = fmaf(qkv[d], qkv[d], qs);
+            ks = fmaf(qkv[PS + d], qkv[PS + d], ks);
+          }
         }
       }
-      const float qmul = sScale[h] * rsqrtf(fmaxf(qs, kNormEps * kNormEps));   // v / max(|v|, eps)
-      const float kmul = rsqrtf(fmaxf(ks, kNormEps * kNormEps));
+      const float qmul = sScale[h] * rsqrt_op<COMP>(fmaxf(qs, kNormEps * kNormEps));   // v / max(|v|, eps)
+      const float kmul = rsqrt_op<COMP>(fmaxf(ks, kNormEps * kNormEps));
       uint32_t qp[8], kp[8];
       [[maybe_unused]] uint32_t ql[8], kl[8];
+      if constexpr (!COMP) {
+#pragma unroll
+        for (int d = 0; d < HD; d += 2) {
+          mul2(qkv[d], qkv[d + 1], qmul);
+          mul2(qkv[PS + d], qkv[PS + d + 1], kmul);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          qp[j] = 2 * j < HD ? tc::pack_f16(qkv[2 * j], qkv[2 * j + 1]) : 0u;
+          kp[j] = 2 * j < HD ? tc::pack_f16(qkv[PS + 2 * j], qkv[PS + 2 * j + 1]) : 0u;
+        }
+      } else
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         qp[j] = 2 * j < HD ? tc::pack_f16(qkv[2 * j] * qmul, qkv[2 * j + 1] * qmul) : 0u;
@@ -574,9 +633,13 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
           if (tc::elect_one()) issue_bias(h);
           __syncwarp();
         }
-        if constexpr (NH == 6) inv_prev = 1.0f / ov[HD];   // the ones row of V^T: sum of the row's (tf32) P
+        if constexpr (NH == 6) inv_prev = rcp_op<COMP>(ov[HD]);   // the ones row of V^T: sum of the row's (tf32) P
 #pragma unroll
-        for (int d = 0; d < HD; ++d) o[(h - 1) * HD + d] = ov[d] * inv_prev;
+        for (int d = 0; d < HD; d += 2) {
+          mul2(ov[d], ov[d + 1], inv_prev);
+          o[(h - 1) * HD + d] = ov[d];
+          o[(h - 1) * HD + d + 1] = ov[d + 1];
+        }
       }
       PROF(5);                                         // wait PV(h-1) + O read
       // ---- operands of head h: Q' = [q|0] or [0|q], K' = [k(w0)|k(w1)], V^T rows (window, d)
@@ -617,7 +680,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
         } else {
         float* vt = reinterpret_cast<float*>(sV + (lrow >> 2) * kVChunk + wsel * 256) + (lrow & 3);
 #pragma unroll
-        for (int d = 0; d < HD; ++d) vt[d * 4] = tc::round_tf32(qkv[2 * PS + d]);
+        for (int d = 0; d < HD; ++d) vt[d * 4] = round_tf32_add(qkv[2 * PS + d]);
         if (NH == 6 && h == 0) vt[HD * 4] = 1.0f;      // ones row (both windows): O column HD = row sum of P
         }
       }
@@ -669,7 +732,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
           float sum4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
           for (int c = 0; c < 64; ++c) sum4[c & 3] += s[c];
-          inv_prev = 1.0f / ((sum4[0] + sum4[1]) + (sum4[2] + sum4[3]));
+          inv_prev = rcp_op<COMP>((sum4[0] + sum4[1]) + (sum4[2] + sum4[3]));
         }
         if constexpr (COMP) {                            // P <= 1 as a BF16 pair: hi in columns [0,32), mid in [32,64)
           float ph[32], pl[32];
@@ -718,7 +781,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
       tc::tc_fence_after();
       float ov[16];
       tc::tmem_ld16(tbase + lane_addr + kTQ + ((NH - 1) & 1) * HS + wsel * 16, ov);
-      if constexpr (NH == 6) inv_prev = 1.0f / ov[HD];
+      if constexpr (NH == 6) inv_prev = rcp_op<COMP>(ov[HD]);
 #pragma unroll
       for (int d = 0; d < HD; ++d) o[(NH - 1) * HD + d] = ov[d] * inv_prev;
     }
@@ -755,7 +818,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
         tc::fence_async_smem();
       } else {
 #pragma unroll
-        for (int i = 0; i < 64; ++i) ot[i] = tc::round_tf32(o[i]);
+        for (int i = 0; i < 64; ++i) ot[i] = round_tf32_add(o[i]);
         tc::tmem_st64(tbase + lane_addr + kTQ, ot);
       }
       if (SAVEO && wvalid) {                             // bf16 copy for the backward (window order)
@@ -807,7 +870,7 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
 #pragma unroll
       for (int i = 0; i < 64; ++i) { y[i] -= mean; var4[i & 3] = fmaf(y[i], y[i], var4[i & 3]); }
       const float var = (var4[0] + var4[1]) + (var4[2] + var4[3]);
-      const float rstd = 1.0f / sqrtf(var * (1.0f / 64.f) + kLnEps);
+      const float rstd = COMP ? 1.0f / sqrtf(var * (1.0f / 64.f) + kLnEps) : rsqrt_op<COMP>(var * (1.0f / 64.f) + kLnEps);
 #pragma unroll
       for (int i = 0; i < 64; ++i) y[i] = y[i] * rstd * sLnW[i] + sLnB[i];
       PROF(13);                                        // LN epilogue
