@@ -53,7 +53,7 @@ __global__ void __launch_bounds__(128) wgrad_tc_kernel(const __grid_constant__ C
   extern __shared__ __align__(128) unsigned char smem_raw[];
   __shared__ uint64_t full[kWgStages], empty[kWgStages], done;
   __shared__ uint32_t slot;
-  __shared__ int sRowMap[256];                   // accumulator column -> row of dw / dbias (-1: padding)
+  __shared__ __align__(16) int sRowMap[256];     // accumulator column -> row of dw / dbias (-1: padding)
   const int tid = threadIdx.x, lane = tid & 31;
   for (int c = tid; c < p.cout; c += 128) {      // (per-head packed [q|k|v] columns: divisions done once, here)
     int orow = c;
@@ -124,19 +124,32 @@ __global__ void __launch_bounds__(128) wgrad_tc_kernel(const __grid_constant__ C
     const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
     // every CTA starts at a different 16-column group: the CTAs reach the flush together, and in the
     // same order all of them would queue on the same L2 addresses
+    // (branch-free inside a group: the destination of element i is base + orow_i * stride for weight and bias
+    // lanes alike, the 16 row indices of a group are read with four 16-byte loads, and the reductions are
+    // predicated - a "load index, branch, compute address, reduce" chain per element cost 39 K cycles = 20 us
+    // per launch, two thirds of a small launch)
     const int ngroup = p.cout >> 4;
     const bool isw = ci < p.cin_valid, isb = ci == 64 && p.cin == 64 && p.dbias;
+    float* const dst = isw ? p.dw + ci : p.dbias;
+    const int stride = isw ? p.ld : 1;
+    int c0 = ((int)blockIdx.x % ngroup) << 4;
     for (int it = 0; it < ngroup; ++it) {
-      const int c0 = ((it + (int)blockIdx.x) % ngroup) << 4;
       float v[16];
       tc::tmem_ld16(tbase + lane_addr + c0, v);
       if (isw || isb) {
+        int orow[16];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          const int orow = sRowMap[c0 + i];
-          if (orow >= 0) atomicAdd(isw ? p.dw + (size_t)orow * p.ld + ci : p.dbias + orow, v[i]);
+        for (int i = 0; i < 4; ++i) {
+          const int4 r = *reinterpret_cast<const int4*>(sRowMap + c0 + 4 * i);
+          orow[4 * i] = r.x; orow[4 * i + 1] = r.y; orow[4 * i + 2] = r.z; orow[4 * i + 3] = r.w;
         }
+#pragma unroll
+        for (int i = 0; i < 16; ++i)                   // predicated reduction: no branch per element
+          asm volatile("{\n\t.reg .pred p;\n\tsetp.ge.s32 p, %2, 0;\n\t@p red.global.add.f32 [%0], %1;\n\t}"
+                       :: "l"(dst + (long long)orow[i] * (long long)stride), "f"(v[i]), "r"(orow[i]) : "memory");
       }
+      c0 += 16;
+      if (c0 >= p.cout) c0 = 0;
     }
   }
   tc::tc_fence_before();
