@@ -406,8 +406,19 @@ __global__ void __launch_bounds__(kThreads) ngram_ctx_bwd_kernel(NgramParams p) 
   {
     const int tid = threadIdx.x;
     const int mo = tid >> 2, mc = (tid & 3) * 16, pc = tid >> 3, pj = (tid & 7) * 4;
+    // the merge / qkv gradients of a thread are runs of 16 / 4 consecutive floats: 16-byte vector reductions when
+    // the destinations are 16-byte aligned (dp.FlatGradBucket views are), as in unigram_bwd_kernel - every CTA hits
+    // the same addresses, so the flush is bound by the number of reduction operations at L2
+    const bool vec = ((reinterpret_cast<uintptr_t>(p.d_merge_w) | reinterpret_cast<uintptr_t>(p.d_qkv_w)) & 15) == 0;
+    if (vec) {
 #pragma unroll
-    for (int i = 0; i < 16; ++i) atomicAdd(p.d_merge_w + mo * 64 + mc + i, accM[i]);
+      for (int i = 0; i < 4; ++i)
+        atomicAdd(reinterpret_cast<float4*>(p.d_merge_w + mo * 64 + mc + 4 * i),
+                  make_float4(accM[4 * i], accM[4 * i + 1], accM[4 * i + 2], accM[4 * i + 3]));
+    } else {
+#pragma unroll
+      for (int i = 0; i < 16; ++i) atomicAdd(p.d_merge_w + mo * 64 + mc + i, accM[i]);
+    }
 #pragma unroll
     for (int i = 0; i < 4; ++i)
       if (pj + i < NA) atomicAdd(p.d_proj_w + pc * NA + pj + i, accP[i]);
@@ -415,8 +426,13 @@ __global__ void __launch_bounds__(kThreads) ngram_ctx_bwd_kernel(NgramParams p) 
     for (int i = 0; i < 3; ++i) {
       const int j = pc + 32 * i;
       if (j < 3 * NA) {
+        if (vec) {
+          atomicAdd(reinterpret_cast<float4*>(p.d_qkv_w + j * 32 + pj),
+                    make_float4(accQ[4 * i], accQ[4 * i + 1], accQ[4 * i + 2], accQ[4 * i + 3]));
+        } else {
 #pragma unroll
-        for (int k = 0; k < 4; ++k) atomicAdd(p.d_qkv_w + j * 32 + pj + k, accQ[4 * i + k]);
+          for (int k = 0; k < 4; ++k) atomicAdd(p.d_qkv_w + j * 32 + pj + k, accQ[4 * i + k]);
+        }
       }
     }
   }
