@@ -59,59 +59,73 @@ __device__ __forceinline__ float hidden_half_scale(float amax, float maxL1, floa
 // Stage fc1/fc2 as fp16 K-major operands, each matrix scaled by one power of two (the inverse
 // scales go to sMisc[0], sMisc[1]); biases and LN affine as fp32.  Called by all `nthreads` threads;
 // contains __syncthreads().
+template <int NT>
 __device__ __forceinline__ void stage_mlp_weights_f16(const MlpParams& p, __half* sW1, __half* sW2,
                                                       float* sB1, float* sB2, float* sLnW,
-                                                      float* sLnB, float* sMisc, int nthreads,
+                                                      float* sLnB, float* sMisc,
                                                       __half* sW1lo = nullptr, __half* sW2lo = nullptr) {
+  // One pass over global memory: every thread fetches its share of the two matrices (4096 float4 in all) with
+  // back-to-back 16-byte loads and KEEPS them in registers while the matrix maxima / row L1 norms are reduced, then
+  // converts and stores them.  (The first version read the matrices three times - a scalar loop for the maxima, a
+  // 64-load strided loop per row for the L1 norms, the staging loops - each a chain of global-latency rounds:
+  // 20 K cycles = 11 us of prologue per launch, a quarter of the kernel at the 16 x 128^2 training size.)
+  static_assert(NT % 32 == 0, "whole warps");
+  constexpr int NPER = (4096 + NT - 1) / NT;
   const int tid = threadIdx.x;
   uint32_t* sMax = reinterpret_cast<uint32_t*>(sMisc + 2);     // [2],[3]: scratch; [4]: maxL1; [5]: maxb
   if (tid < 4) sMax[tid] = 0u;
   __syncthreads();
+  float4 w[NPER];
+#pragma unroll
+  for (int j = 0; j < NPER; ++j) {
+    const int f = tid + j * NT;                                // [0, 2048): fc1 [128][64]; [2048, 4096): fc2 [64][128]
+    w[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (f < 4096)
+      w[j] = __ldg(reinterpret_cast<const float4*>(f < 2048 ? p.fc1_w : p.fc2_w) + (f & 2047));
+  }
   {
     float m1 = 0.f, m2 = 0.f;
-    for (int i = tid; i < 128 * 64; i += nthreads) {
-      m1 = fmaxf(m1, fabsf(p.fc1_w[i]));
-      m2 = fmaxf(m2, fabsf(p.fc2_w[i]));
+#pragma unroll
+    for (int j = 0; j < NPER; ++j) {
+      const int f = tid + j * NT;                              // (warp-uniform: 2048 and 4096 are multiples of 32)
+      const float ax = fabsf(w[j].x), ay = fabsf(w[j].y), az = fabsf(w[j].z), aw = fabsf(w[j].w);
+      const float am = fmaxf(fmaxf(ax, ay), fmaxf(az, aw));
+      if (f < 2048) {
+        m1 = fmaxf(m1, am);
+        float l1 = (ax + ay) + (az + aw);                      // L1 norm of an fc1 row: its 16 float4 sit in 16 lanes
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) l1 += __shfl_xor_sync(0xffffffffu, l1, o);
+        if ((f & 15) == 0) atomicMax(sMax + 2, __float_as_uint(l1));
+      } else if (f < 4096) {
+        m2 = fmaxf(m2, am);
+      }
     }
-    atomicMax(sMax, __float_as_uint(m1));
+    atomicMax(sMax, __float_as_uint(m1));                     // non-negative floats order like unsigned ints
     atomicMax(sMax + 1, __float_as_uint(m2));
   }
-  if (tid < 128) {
-    float l1 = 0.f;
-    for (int k = 0; k < 64; ++k) l1 += fabsf(p.fc1_w[tid * 64 + k]);
-    atomicMax(sMax + 2, __float_as_uint(l1));
-    atomicMax(sMax + 3, __float_as_uint(fabsf(p.fc1_b[tid])));
-  }
+  if (tid < 128) atomicMax(sMax + 3, __float_as_uint(fabsf(p.fc1_b[tid])));
   __syncthreads();
   uint32_t e1 = (sMax[0] >> 23) & 0xFFu, e2 = (sMax[1] >> 23) & 0xFFu;
   e1 = e1 < 1u ? 127u : (e1 > 253u ? 253u : e1);
   e2 = e2 < 1u ? 127u : (e2 > 253u ? 253u : e2);
   const float sc1 = __uint_as_float((254u - e1) << 23), sc2 = __uint_as_float((254u - e2) << 23);
-  __syncthreads();
   if (tid == 0) { sMisc[0] = __uint_as_float(e1 << 23); sMisc[1] = __uint_as_float(e2 << 23); }
-  for (int idx = tid; idx < 128 * 8; idx += nthreads) {                 // fc1 [128][64]
-    const int n = idx & 127, kc = idx >> 7;
-    const float4* src = reinterpret_cast<const float4*>(p.fc1_w + n * 64 + kc * 8);
-    const float4 a = src[0], b = src[1];
-    const uint4 hv = make_uint4(tc::pack_f16(a.x * sc1, a.y * sc1), tc::pack_f16(a.z * sc1, a.w * sc1),
-                                tc::pack_f16(b.x * sc1, b.y * sc1), tc::pack_f16(b.z * sc1, b.w * sc1));
-    *reinterpret_cast<uint4*>(sW1 + kc * 1024 + n * 8) = hv;
-    if (sW1lo)                                                          // compensated level: lo = fp16(w - hi)
-      *reinterpret_cast<uint4*>(sW1lo + kc * 1024 + n * 8) =
-          make_uint4(tc::lo_f16(a.x * sc1, a.y * sc1, hv.x), tc::lo_f16(a.z * sc1, a.w * sc1, hv.y),
-                     tc::lo_f16(b.x * sc1, b.y * sc1, hv.z), tc::lo_f16(b.z * sc1, b.w * sc1, hv.w));
-  }
-  for (int idx = tid; idx < 64 * 16; idx += nthreads) {                 // fc2 [64][128]
-    const int n = idx & 63, kc = idx >> 6;
-    const float4* src = reinterpret_cast<const float4*>(p.fc2_w + n * 128 + kc * 8);
-    const float4 a = src[0], b = src[1];
-    const uint4 hv = make_uint4(tc::pack_f16(a.x * sc2, a.y * sc2), tc::pack_f16(a.z * sc2, a.w * sc2),
-                                tc::pack_f16(b.x * sc2, b.y * sc2), tc::pack_f16(b.z * sc2, b.w * sc2));
-    *reinterpret_cast<uint4*>(sW2 + kc * 512 + n * 8) = hv;
-    if (sW2lo)
-      *reinterpret_cast<uint4*>(sW2lo + kc * 512 + n * 8) =
-          make_uint4(tc::lo_f16(a.x * sc2, a.y * sc2, hv.x), tc::lo_f16(a.z * sc2, a.w * sc2, hv.y),
-                     tc::lo_f16(b.x * sc2, b.y * sc2, hv.z), tc::lo_f16(b.z * sc2, b.w * sc2, hv.w));
+#pragma unroll
+  for (int j = 0; j < NPER; ++j) {
+    const int f = tid + j * NT;
+    if (f < 4096) {
+      const bool one = f < 2048;
+      const int g = f & 2047;
+      // fc1: row n = g / 16, k0 = 4 (g % 16), chunk-major [k/8][128 rows][8]; fc2: n = g / 32, k0 = 4 (g % 32), [k/8][64][8]
+      const int n = one ? g >> 4 : g >> 5, k0 = one ? (g & 15) << 2 : (g & 31) << 2;
+      const int off = (k0 >> 3) * (one ? 1024 : 512) + n * 8 + (k0 & 7);
+      const float sc = one ? sc1 : sc2;
+      const float a = w[j].x * sc, b = w[j].y * sc, c = w[j].z * sc, d = w[j].w * sc;
+      const uint2 hv = make_uint2(tc::pack_f16(a, b), tc::pack_f16(c, d));
+      *reinterpret_cast<uint2*>((one ? sW1 : sW2) + off) = hv;
+      if (sW1lo)                                               // compensated level: lo = fp16(w - hi)
+        *reinterpret_cast<uint2*>((one ? sW1lo : sW2lo) + off) = make_uint2(tc::lo_f16(a, b, hv.x), tc::lo_f16(c, d, hv.y));
+    }
   }
   if (tid < 128) sB1[tid] = p.fc1_b[tid];
   if (tid < 64) { sB2[tid] = p.fc2_b[tid]; sLnW[tid] = p.ln_w[tid]; sLnB[tid] = p.ln_b[tid]; }
@@ -152,7 +166,7 @@ __global__ void __launch_bounds__(128 * kMlpWorkers, 1) mlp_tc_fwd_kernel(MlpPar
   uint64_t* bar1 = bars + wk * 2;
   uint64_t* bar2 = bar1 + 1;
 
-  stage_mlp_weights_f16(p, sW1, sW2, sB1, sB2, sLnW, sLnB, sMisc, 128 * kMlpWorkers);
+  stage_mlp_weights_f16<128 * kMlpWorkers>(p, sW1, sW2, sB1, sB2, sLnW, sLnB, sMisc);
   if (tid == 0) {
     for (int i = 0; i < 2 * kMlpWorkers; ++i) tc::mbar_init(bars + i, 1);
     tc::fence_barrier_init();
@@ -428,7 +442,7 @@ mlp_tma_fwd_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_consta
   uint64_t* bar1 = full + 2;
   uint64_t* bar2 = full + 3;
 
-  stage_mlp_weights_f16(p, sW1, sW2, sB1, sB2, sLnW, sLnB, sMisc, 128 * kTmaWorkers,
+  stage_mlp_weights_f16<128 * kTmaWorkers>(p, sW1, sW2, sB1, sB2, sLnW, sLnB, sMisc,
                         COMP ? reinterpret_cast<__half*>(smem_raw + MlpTmaSmem::oW1lo) : nullptr,
                         COMP ? reinterpret_cast<__half*>(smem_raw + MlpTmaSmem::oW2lo) : nullptr);
   if (tid == 0) {
