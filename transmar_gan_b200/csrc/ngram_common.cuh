@@ -63,25 +63,62 @@ __device__ __forceinline__ int ngram_rel_index(int p, int q) {
 template <int NH>
 __device__ __forceinline__ void load_ngram_weights(float* smem, const NgramParams& p) {
   using L = NgramSmem<NH>;
+  // All global loads of a thread are issued back to back (fixed trip counts for the 256-thread CTAs of these
+  // kernels, 16- / 8-byte loads), then scattered into the padded shared-memory rows: one round of global latency
+  // instead of ~30 dependent scalar rounds (the prologue was most of the 15 us fixed cost of a launch).
+  const int tid = threadIdx.x;
+  constexpr int NT = kThreads;
+  constexpr int kQ = (3 * L::NA * 8 + NT - 1) / NT;            // qkv [3 NA][32]: float4 pieces
+  constexpr int kP = (32 * L::NA / 2 + NT - 1) / NT;           // proj [32][NA]: float2 pieces (NA is even)
+  constexpr int kM = 64 * 16 / NT;                             // merge [64][64]: float4 pieces
+  static_assert(L::NA % 2 == 0 && (64 * 16) % NT == 0, "piece counts");
+  float4 q[kQ], m[kM];
+  float2 pr[kP];
   if (p.qkv_w) {                               // null when the qkv rows are precomputed per window
-    for (int i = threadIdx.x; i < 96 * 32; i += blockDim.x) {
-      const int r = i >> 5, c = i & 31;
-      smem[L::oWqkv + r * 33 + c] = r < 3 * L::NA ? p.qkv_w[r * 32 + c] : 0.f;
+#pragma unroll
+    for (int j = 0; j < kQ; ++j) {
+      const int f = tid + j * NT;
+      q[j] = f < 3 * L::NA * 8 ? __ldg(reinterpret_cast<const float4*>(p.qkv_w) + f) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    for (int i = threadIdx.x; i < 96; i += blockDim.x)
-      smem[L::oBqkv + i] = i < 3 * L::NA ? p.qkv_b[i] : 0.f;
   }
-  for (int i = threadIdx.x; i < 32 * L::NA; i += blockDim.x) {
-    const int r = i / L::NA, c = i - r * L::NA;
-    smem[L::oWp + r * 33 + c] = p.proj_w[i];
+#pragma unroll
+  for (int j = 0; j < kP; ++j) {
+    const int f = tid + j * NT;
+    pr[j] = f < 32 * L::NA / 2 ? __ldg(reinterpret_cast<const float2*>(p.proj_w) + f) : make_float2(0.f, 0.f);
   }
-  for (int i = threadIdx.x; i < 32; i += blockDim.x) smem[L::oBp + i] = p.proj_b[i];
-  for (int i = threadIdx.x; i < 64 * 64; i += blockDim.x)
-    smem[L::oWm + (i >> 6) * 65 + (i & 63)] = p.merge_w[i];
-  for (int i = threadIdx.x; i < 64; i += blockDim.x) smem[L::oBm + i] = p.merge_b[i];
-  if (threadIdx.x < NH)
-    smem[L::oScale + threadIdx.x] = expf(fminf(p.logit_scale[threadIdx.x], kLogitMax));
-  for (int i = threadIdx.x; i < NH * 9; i += blockDim.x) {
+#pragma unroll
+  for (int j = 0; j < kM; ++j) m[j] = __ldg(reinterpret_cast<const float4*>(p.merge_w) + tid + j * NT);
+  if (p.qkv_w) {
+#pragma unroll
+    for (int j = 0; j < kQ; ++j) {
+      const int f = tid + j * NT;                // rows >= 3 NA of the [96][33] tile are zero
+      if (f < 96 * 8) {
+        float* d = smem + L::oWqkv + (f >> 3) * 33 + ((f & 7) << 2);
+        d[0] = q[j].x; d[1] = q[j].y; d[2] = q[j].z; d[3] = q[j].w;
+      }
+    }
+    for (int i = tid; i < 96; i += NT) smem[L::oBqkv + i] = i < 3 * L::NA ? p.qkv_b[i] : 0.f;
+  }
+#pragma unroll
+  for (int j = 0; j < kP; ++j) {
+    const int f = tid + j * NT;
+    if (f < 32 * L::NA / 2) {
+      const int r = (2 * f) / L::NA, c = 2 * f - r * L::NA;
+      smem[L::oWp + r * 33 + c] = pr[j].x;
+      smem[L::oWp + r * 33 + c + 1] = pr[j].y;
+    }
+  }
+  for (int i = tid; i < 32; i += NT) smem[L::oBp + i] = p.proj_b[i];
+#pragma unroll
+  for (int j = 0; j < kM; ++j) {
+    const int f = tid + j * NT;
+    float* d = smem + L::oWm + (f >> 4) * 65 + ((f & 15) << 2);
+    d[0] = m[j].x; d[1] = m[j].y; d[2] = m[j].z; d[3] = m[j].w;
+  }
+  for (int i = tid; i < 64; i += NT) smem[L::oBm + i] = p.merge_b[i];
+  if (tid < NH)
+    smem[L::oScale + tid] = expf(fminf(p.logit_scale[tid], kLogitMax));
+  for (int i = tid; i < NH * 9; i += NT) {
     const int h = i / 9, e = i - h * 9;
     smem[L::oBias + h * 12 + e] = p.bias_table[e * NH + h];
   }
