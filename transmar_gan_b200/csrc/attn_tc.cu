@@ -208,38 +208,53 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
 
   // ---- stage the block's weights as K-major operands (once per CTA).  The qkv matrix is scaled by
   //      one power of two to max|w| in [1,2) so that fp16 keeps 11 significant bits at any scale.
+  // (One pass over global memory: every thread fetches its float4 share of the qkv matrix with back-to-back loads
+  //  and keeps it in registers while the matrix maximum is reduced, then scales, converts and scatters it into the
+  //  packed per-head order; the bias table is copied once, coalesced, into the - still idle - staging tile of worker 0
+  //  and the compressed bias operands / bounded-logit flags are built from that copy.  The first version walked the
+  //  matrix twice with scalar / strided loads and gathered the bias operands from global memory.)
   uint32_t* sWmax = reinterpret_cast<uint32_t*>(sScale + 7);
+  float* sTab = reinterpret_cast<float*>(smem_raw + L::oWork);     // [225][NH] copy of the bias table (prologue only)
+  constexpr int NT = 128 * kWorkers;
+  constexpr int kQ4 = 3 * A * 16;                                  // float4 pieces of qkv_w [3 A][64]
+  constexpr int NPER = (kQ4 + NT - 1) / NT;
   if (tid == 0) *sWmax = 0u;
   __syncthreads();
+  float4 wq4[NPER];
+#pragma unroll
+  for (int j = 0; j < NPER; ++j) {
+    const int f = tid + j * NT;
+    wq4[j] = f < kQ4 ? __ldg(reinterpret_cast<const float4*>(p.qkv_w) + f) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  for (int i = tid; i < NH * 225; i += NT) sTab[i] = p.bias_table[i];
+  for (int idx = tid; idx < L::kWRows * 8; idx += NT) {            // pad rows / columns of the packed operand are zero
+    *reinterpret_cast<uint4*>(sWqkv + (size_t)idx * 8) = make_uint4(0u, 0u, 0u, 0u);
+    if constexpr (COMP) *reinterpret_cast<uint4*>(smem_raw + L::oWqkvLo + (size_t)idx * 16) = make_uint4(0u, 0u, 0u, 0u);
+  }
   {
     float m = 0.f;
-    for (int i = tid; i < 3 * A * 64; i += 128 * kWorkers) m = fmaxf(m, fabsf(p.qkv_w[i]));
+#pragma unroll
+    for (int j = 0; j < NPER; ++j)
+      m = fmaxf(m, fmaxf(fmaxf(fabsf(wq4[j].x), fabsf(wq4[j].y)), fmaxf(fabsf(wq4[j].z), fabsf(wq4[j].w))));
     atomicMax(sWmax, __float_as_uint(m));               // non-negative floats order like unsigned ints
   }
   __syncthreads();
   uint32_t we = (*sWmax >> 23) & 0xFFu;
   we = we < 1u ? 127u : (we > 253u ? 253u : we);
   const float wsc = __uint_as_float((254u - we) << 23);   // 2^(127-we)
-  for (int idx = tid; idx < L::kWRows * 8; idx += 128 * kWorkers) {
-    const int n = idx % L::kWRows, kc = idx / L::kWRows;      // packed row n = h*HS + part*PS + d
-    const int h = n / HS, part = (n % HS) / PS, d = (n % HS) % PS;
-    uint4 v = make_uint4(0u, 0u, 0u, 0u);
-    if (h < NH && part < 3 && d < HD) {
-      const float4* src = reinterpret_cast<const float4*>(p.qkv_w + (part * A + h * HD + d) * 64 + kc * 8);
-      const float4 a = src[0], b = src[1];
-      v = make_uint4(tc::pack_f16(a.x * wsc, a.y * wsc), tc::pack_f16(a.z * wsc, a.w * wsc),
-                     tc::pack_f16(b.x * wsc, b.y * wsc), tc::pack_f16(b.z * wsc, b.w * wsc));
-    }
-    *reinterpret_cast<uint4*>(sWqkv + (size_t)kc * (L::kWRows * 8) + n * 8) = v;
-    if constexpr (COMP) {                      // lo = fp16(w * wsc - hi): exact difference, 11 more bits
-      uint4 l = make_uint4(0u, 0u, 0u, 0u);
-      if (h < NH && part < 3 && d < HD) {
-        const float4* src = reinterpret_cast<const float4*>(p.qkv_w + (part * A + h * HD + d) * 64 + kc * 8);
-        const float4 a = src[0], b = src[1];
-        l = make_uint4(tc::lo_f16(a.x * wsc, a.y * wsc, v.x), tc::lo_f16(a.z * wsc, a.w * wsc, v.y),
-                       tc::lo_f16(b.x * wsc, b.y * wsc, v.z), tc::lo_f16(b.z * wsc, b.w * wsc, v.w));
-      }
-      *reinterpret_cast<uint4*>(smem_raw + L::oWqkvLo + ((size_t)kc * (L::kWRows * 8) + n * 8) * 2) = l;
+#pragma unroll
+  for (int j = 0; j < NPER; ++j) {
+    const int f = tid + j * NT;
+    if (f < kQ4) {
+      const int r = f >> 4, k0 = (f & 15) << 2;           // source row r = part * A + h * HD + d, columns k0 .. k0 + 3
+      const int part = r / A, rem = r - part * A, h = rem / HD, d = rem - h * HD;
+      const int n = h * HS + part * PS + d;               // packed row
+      const size_t off = (size_t)(k0 >> 3) * (L::kWRows * 8) + n * 8 + (k0 & 7);
+      const float a = wq4[j].x * wsc, b = wq4[j].y * wsc, c = wq4[j].z * wsc, e = wq4[j].w * wsc;
+      const uint2 hv = make_uint2(tc::pack_f16(a, b), tc::pack_f16(c, e));
+      *reinterpret_cast<uint2*>(sWqkv + off) = hv;
+      if constexpr (COMP)                      // lo = fp16(w * wsc - hi): exact difference, 11 more bits
+        *reinterpret_cast<uint2*>(smem_raw + L::oWqkvLo + off * 2) = make_uint2(tc::lo_f16(a, b, hv.x), tc::lo_f16(c, e, hv.y));
     }
   }
   __shared__ float sProjInv;                   // COMP: inverse of the projection weights' power-of-two scale
@@ -289,14 +304,16 @@ attn_tc_fwd_kernel(const __grid_constant__ CUtensorMap mapZ, const __grid_consta
   // row's own key is never masked).  Any other head (logit scales near the ln 100 clamp, huge biases)
   // always takes the exact max-subtracting path.
   __shared__ int sFast[8];
-  if (tid < NH) {
+  if (warp < NH) {                               // one warp per head, from the shared-memory copy of the table
     float mb = 0.f;
-    for (int e = 0; e < 225; ++e) mb = fmaxf(mb, fabsf(p.bias_table[e * NH + tid]));
-    sFast[tid] = (expf(fminf(p.logit_scale[tid], kLogitMax)) + mb) * kLog2e <= 60.0f ? 1 : 0;
+    for (int e = lane; e < 225; e += 32) mb = fmaxf(mb, fabsf(sTab[e * NH + warp]));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mb = fmaxf(mb, __shfl_xor_sync(0xffffffffu, mb, o));
+    if (lane == 0) sFast[warp] = (expf(fminf(p.logit_scale[warp], kLogitMax)) + mb) * kLog2e <= 60.0f ? 1 : 0;
   }
   for (int i = tid; i < NH * 15 * 64; i += 128 * kWorkers) {
     const int h = i / 960, r = i - h * 960, m = r >> 6, cj = (r >> 3) & 7, rj = r & 7;
-    sBiasT[i] = __float2half_rn(p.bias_table[(m * 15 + rj - cj + 7) * NH + h] * kLog2e);
+    sBiasT[i] = __float2half_rn(sTab[(m * 15 + rj - cj + 7) * NH + h] * kLog2e);
   }
   for (int i = tid; i < 23 * 64; i += 128 * kWorkers) {
     const int m = i >> 6, j = (i >> 3) & 7, e = i & 7;
