@@ -31,4 +31,5 @@ a = t(lambda: ops.ngram_ctx_bwd(u, dctx, P[2:10], du, G[2:10], 6))
 b = t(lambda: ops.unigram_bwd(z, P[0], du, dz, G[0], G[1], ph, pw))
 c = t(lambda: ops.ngram_ctx_fwd(u, *P[2:10], 6))
 d = t(lambda: ops.unigram_fwd(z, P[0], P[1], ph, pw))
-print(f"{os.path.basename(T.LIB_PATH)} | ngram_ctx_bwd {a:.1f} us | unigram_bwd {b:.1f} us | ngram_ctx_fwd {c:.1f} us | unigram_fwd {d:.1f} us")
+e = t(lambda: ops.ngram_ctx_infer(z, *P[0:10], ph, pw, 6))
+print(f"{os.path.basename(T.LIB_PATH)} | ngram_ctx_bwd {a:.1f} us | unigram_bwd {b:.1f} us | ngram_ctx_fwd {c:.1f} us | unigram_fwd {d:.1f} us | ngram_ctx_infer (unigram_qkv + ctx_pre) {e:.1f} us")
