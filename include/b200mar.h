@@ -32,7 +32,7 @@ extern "C" {
 #endif
 
 /* ABI version, bumped whenever a signature changes. */
-int b200mar_abi_version(void);   /* 6 */
+int b200mar_abi_version(void);   /* 7 */
 /* Name of the last failing CUDA call of this thread (static string; never NULL). */
 const char* b200mar_last_error(void);
 /* 1 iff device `dev` is compute capability 10.x (B200); no kernels are launched. */
@@ -72,6 +72,11 @@ int b200mar_ngram_ctx_fwd(const float* u,
 int b200mar_unigram_qkv_fwd(const float* z, const float* weight, const float* bias,
                             const float* qkv_w, const float* qkv_b, float* nq,
                             int B, int ph, int pw, int nh, void* stream);
+/* Training form of b200mar_unigram_qkv_fwd (components/window_utils.py:36-38,75-78): the same pass also writes the
+ * unigram embedding u [B, ph/8, pw/8, 32] that b200mar_ngram_ctx_bwd / b200mar_unigram_bwd consume.            */
+int b200mar_unigram_qkv_u_fwd(const float* z, const float* weight, const float* bias,
+                              const float* qkv_w, const float* qkv_b, float* nq, float* u,
+                              int B, int ph, int pw, int nh, void* stream);
 int b200mar_ngram_ctx_pre_fwd(const float* nq, const float* proj_w, const float* proj_b,
                               const float* logit_scale, const float* bias_table,
                               const float* merge_w, const float* merge_b, float* ctx,

@@ -127,7 +127,7 @@ def test_cabi_exports_every_declared_symbol():
     lib = _cabi.lib()
     for name in declared:
         assert hasattr(lib, name), name
-    assert lib.b200mar_abi_version() == 6
+    assert lib.b200mar_abi_version() == 7
     assert lib.b200mar_last_error() == b"no error"
 
 

@@ -362,6 +362,24 @@ def test_ngram_ctx_infer_matches_two_step(nh, B, ph, pw):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("nh,B,ph,pw", [(6, 2, 16, 16), (6, 1, 24, 40), (4, 3, 32, 16), (6, 16, 128, 128)])
+def test_ngram_ctx_train_fwd_matches_two_step(nh, B, ph, pw):
+    """Training form of the inference pair: (u, ctx) == (unigram_fwd, ngram_ctx_fwd); u is what the backward reads."""
+    from transmar_gan_b200 import ops
+    sd = {k: v.cuda() for k, v in O.synthetic_state_dict("W2", seed=5).items()}
+    pre = "encoder_layer1.blocks.3." if nh == 6 else "encoder_layer2.blocks.1."
+    P = [sd[pre + n].contiguous() for n in ops.NSTB_PARAM_NAMES[:10]]
+    g = torch.Generator().manual_seed(ph * pw + nh + 1)
+    z = torch.randn(B, ph * pw, 64, generator=g).cuda()
+    u_ref = ops.unigram_fwd(z, P[0], P[1], ph, pw)
+    c_ref = ops.ngram_ctx_fwd(u_ref, *P[2:10], nh)
+    u, c = ops.ngram_ctx_train_fwd(z, *P, ph, pw, nh)
+    assert u.shape == u_ref.shape and c.shape == c_ref.shape
+    assert (u - u_ref).abs().max().item() <= 2e-5 * max(1.0, u_ref.abs().max().item())
+    assert (c - c_ref).abs().max().item() <= 2e-5 * max(1.0, c_ref.abs().max().item())
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("n_tok", [1, 2, 33, 4096, 148 * 8 * 16 * 3 + 5])
 def test_ln64_fwd_bwd_vs_torch(n_tok):
     """ln64.cu (LayerNorm(64) of the training-path stage glue: bottleneck.norm, NGswin.norm - ngswin.py:204)

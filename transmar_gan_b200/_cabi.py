@@ -36,6 +36,7 @@ SIGNATURES = {
     "b200mar_unigram_bwd_add": [_P] * 7 + [_I] * 3 + [_P],
     "b200mar_ngram_ctx_fwd": [_P] * 10 + [_I] * 4 + [_P],
     "b200mar_unigram_qkv_fwd": [_P] * 6 + [_I] * 4 + [_P],
+    "b200mar_unigram_qkv_u_fwd": [_P] * 7 + [_I] * 4 + [_P],
     "b200mar_ngram_ctx_pre_fwd": [_P] * 8 + [_I] * 4 + [_P],
     "b200mar_ngram_ctx_infer_noalloc": [_P] * 12 + [_I] * 4 + [_P],
     "b200mar_ngram_ctx_infer_noalloc_max_windows": [],

@@ -35,7 +35,7 @@ extern "C" int b200mar_tc_error(void) {
   return (a | b | c | d | e | f) ? 1 : 0;
 }
 
-extern "C" int b200mar_abi_version(void) { return 6; }
+extern "C" int b200mar_abi_version(void) { return 7; }
 extern "C" const char* b200mar_last_error(void) { return b200mar::last_error_ref(); }
 extern "C" int b200mar_device_ok(int dev) {
   int major = 0;

@@ -56,7 +56,7 @@ template <bool S16>
 __global__ void __launch_bounds__(kThreads, 2) unigram_qkv_fwd_kernel(
     const float* __restrict__ z, const float* __restrict__ w, const float* __restrict__ bias,
     const float* __restrict__ qkv_w, const float* __restrict__ qkv_b, int n_qkv,
-    float* __restrict__ nq, int B, int ph, int pw) {
+    float* __restrict__ nq, float* __restrict__ u_out, int B, int ph, int pw) {
   __shared__ __align__(16) float sW[kTok * kDim];  // [t = 8i+j][c = 2g+k]
   __shared__ __align__(16) float sWq[32 * 96];     // [c][j]
   __shared__ __align__(16) float sU[8][32 * 4];    // per warp: [channel][window of the group]
@@ -119,6 +119,11 @@ __global__ void __launch_bounds__(kThreads, 2) unigram_qkv_fwd_kernel(
       }
     }
     *reinterpret_cast<float4*>(&sU[warp][lane * 4]) = make_float4(acc[0] + bl, acc[1] + bl, acc[2] + bl, acc[3] + bl);
+    if (u_out) {                                      // training: the unigram embedding itself, saved for the backward
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (ok[k]) u_out[(size_t)(grp * 4 + k) * 32 + lane] = acc[k] + bl;
+    }
     __syncwarp();
     float q[3][4];
 #pragma unroll
@@ -427,7 +432,22 @@ extern "C" int b200mar_unigram_qkv_fwd(const float* z, const float* weight, cons
   int grid = ((nwin + 3) / 4 + 7) / 8;               // a warp takes groups of four windows
   if (grid > 2 * sm_count()) grid = 2 * sm_count();
   unigram_qkv_fwd_kernel<false><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
-      z, weight, bias, qkv_w, qkv_b, 3 * (32 / nh) * nh, nq, B, ph, pw);
+      z, weight, bias, qkv_w, qkv_b, 3 * (32 / nh) * nh, nq, nullptr, B, ph, pw);
+  B200MAR_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// Training form: the same pass also writes the unigram embedding u [B*wh*ww][32] that the backward kernels consume.
+extern "C" int b200mar_unigram_qkv_u_fwd(const float* z, const float* weight, const float* bias,
+                                         const float* qkv_w, const float* qkv_b, float* nq, float* u, int B,
+                                         int ph, int pw, int nh, void* stream) {
+  using namespace b200mar;
+  if (ph % kWin || pw % kWin || ph < kWin || pw < kWin || (nh != 6 && nh != 4) || !u) return -1;
+  const int nwin = B * (ph / kWin) * (pw / kWin);
+  int grid = ((nwin + 3) / 4 + 7) / 8;
+  if (grid > 2 * sm_count()) grid = 2 * sm_count();
+  unigram_qkv_fwd_kernel<false><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
+      z, weight, bias, qkv_w, qkv_b, 3 * (32 / nh) * nh, nq, u, B, ph, pw);
   B200MAR_CHECK(cudaGetLastError());
   return 0;
 }
@@ -442,7 +462,7 @@ extern "C" int b200mar_unigram_qkv_fwd_s16(const void* z16, const float* weight,
   int grid = ((nwin + 3) / 4 + 7) / 8;
   if (grid > 2 * sm_count()) grid = 2 * sm_count();
   unigram_qkv_fwd_kernel<true><<<grid, kThreads, 0, (cudaStream_t)stream>>>(
-      (const float*)z16, weight, bias, qkv_w, qkv_b, 3 * (32 / nh) * nh, nq, B, ph, pw);
+      (const float*)z16, weight, bias, qkv_w, qkv_b, 3 * (32 / nh) * nh, nq, nullptr, B, ph, pw);
   B200MAR_CHECK(cudaGetLastError());
   return 0;
 }
@@ -513,7 +533,7 @@ extern "C" int b200mar_ngram_ctx_infer_noalloc(const float* z, const float* uni_
   cudaStream_t st = (cudaStream_t)stream;
   int grid = (((int)nwin + 3) / 4 + 7) / 8;          // a warp takes groups of four windows
   if (grid > 2 * sm_count()) grid = 2 * sm_count();
-  unigram_qkv_fwd_kernel<false><<<grid, kThreads, 0, st>>>(z, uni_w, uni_b, qkv_w, qkv_b, 3 * (32 / nh) * nh, nq, B, ph, pw);
+  unigram_qkv_fwd_kernel<false><<<grid, kThreads, 0, st>>>(z, uni_w, uni_b, qkv_w, qkv_b, 3 * (32 / nh) * nh, nq, nullptr, B, ph, pw);
   B200MAR_CHECK(cudaGetLastError());
   NgramParams p{};
   p.u = nq; p.proj_w = proj_w; p.proj_b = proj_b;

@@ -317,6 +317,33 @@ def _(z, uni_w, uni_b, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, me
     return z.new_empty((z.shape[0], ph // 8, pw // 8, 64))
 
 
+@torch.library.custom_op(f"{_NS}::ngram_ctx_train_fwd", mutates_args=())
+def ngram_ctx_train_fwd(z: Tensor, uni_w: Tensor, uni_b: Tensor, qkv_w: Tensor, qkv_b: Tensor,
+                        proj_w: Tensor, proj_b: Tensor, logit_scale: Tensor, bias_table: Tensor,
+                        merge_w: Tensor, merge_b: Tensor, ph: int, pw: int, nh: int) -> Tuple[Tensor, Tensor]:
+    """(u, ctx) = (unigram_fwd(z), ngram_ctx_fwd(u)) for the training forward on the inference pair of kernels: the
+    streaming unigram pass also applies the n-gram qkv Linear once per window and writes u for the backward
+    (40 us instead of 50 us per block at 16 x 128^2)."""
+    _chk(z, uni_w, uni_b, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, merge_w, merge_b)
+    B, wh, ww = z.shape[0], ph // 8, pw // 8
+    if wh < 2 or ww < 2:
+        raise RuntimeError("NGramContext needs at least 2x2 windows per stage "
+                           "(the reference raises for smaller inputs, SURVEY.md A.4)")
+    nq = torch.empty((B, wh, ww, 96), device=z.device, dtype=torch.float32)
+    u = torch.empty((B, wh, ww, 32), device=z.device, dtype=torch.float32)
+    ctx = torch.empty((B, wh, ww, 64), device=z.device, dtype=torch.float32)
+    _call("unigram_qkv_u_fwd", _p(z), _p(uni_w), _p(uni_b), _p(qkv_w), _p(qkv_b), _p(nq), _p(u), B, ph, pw, nh,
+          _stream())
+    _call("ngram_ctx_pre_fwd", _p(nq), _p(proj_w), _p(proj_b), _p(logit_scale), _p(bias_table),
+          _p(merge_w), _p(merge_b), _p(ctx), B, wh, ww, nh, _stream())
+    return u, ctx
+
+
+@ngram_ctx_train_fwd.register_fake
+def _(z, uni_w, uni_b, qkv_w, qkv_b, proj_w, proj_b, logit_scale, bias_table, merge_w, merge_b, ph, pw, nh):
+    return (z.new_empty((z.shape[0], ph // 8, pw // 8, 32)), z.new_empty((z.shape[0], ph // 8, pw // 8, 64)))
+
+
 @torch.library.custom_op(f"{_NS}::ngram_ctx_bwd", mutates_args=("du", "grads"))
 def ngram_ctx_bwd(u: Tensor, dctx: Tensor, params: List[Tensor], du: Tensor,
                   grads: List[Tensor], nh: int) -> None:
@@ -892,6 +919,11 @@ def nstb_infer_mixed_(z: Tensor, ph: int, pw: int, nh: int, shift: int, want_out
     return out, (z if want_zsum else out.new_empty(0))
 
 
+# development knob: B200MAR_NGRAM_TRAIN_PAIR=0 runs the training forward's n-gram context on unigram_fwd +
+# ngram_ctx_fwd (the qkv Linear re-derived for every neighbourhood) instead of the inference pair of kernels
+_NGRAM_TRAIN_PAIR = os.environ.get("B200MAR_NGRAM_TRAIN_PAIR", "1") != "0"
+
+
 class NSTBFunction(torch.autograd.Function):
     """One N-Gram Swin Transformer Block (components/transformer_blocks.py:114-120) plus the
     within-stage residual sum (components/encoder_decoder.py:138-141):
@@ -902,8 +934,11 @@ class NSTBFunction(torch.autograd.Function):
     @staticmethod
     def forward(ctx_, z, ph, pw, nh, shift, want_out, want_zsum, save, *params):
         P = [p.detach() for p in params]
-        u = unigram_fwd(z, P[0], P[1], ph, pw)
-        c = ngram_ctx_fwd(u, P[2], P[3], P[4], P[5], P[6], P[7], P[8], P[9], nh)
+        if _NGRAM_TRAIN_PAIR:
+            u, c = ngram_ctx_train_fwd(z, *P[0:10], ph, pw, nh)
+        else:
+            u = unigram_fwd(z, P[0], P[1], ph, pw)
+            c = ngram_ctx_fwd(u, P[2], P[3], P[4], P[5], P[6], P[7], P[8], P[9], nh)
         ma, mm = unit_modes()                      # the backward runs in the modes the forward ran in
         tc_a = ctx_.tc_attn = ma != "fp32"
         tc_m = ctx_.tc_mlp = mm != "fp32"
