@@ -72,6 +72,37 @@ def test_gan_graph_step_matches_eager():
         assert abs(a - c) < 5e-3 * max(1.0, abs(a)) and abs(b - d) < 5e-3 * max(1.0, abs(b)), (le, lg)
 
 
+def test_gan_split_graph_step_matches_single_graph():
+    """The multi-rank capture of the GAN step (pieces around the two all-reduces, the discriminator's all-reduce +
+    Adam update on a side stream UNDER the generator forward of the G step), forced on one GPU with
+    split_graphs=True, against the single-graph capture: same losses over several steps (the backward kernels
+    accumulate with fp32 atomics, so not bitwise) and the same discriminator weights."""
+    import transmar_gan_b200 as T
+    from transmar_gan_b200 import gan, train
+    from oracle import ngswin_oracle as O
+
+    def make(split):
+        g = T.NGswin()
+        g.load_state_dict(O.synthetic_state_dict("W1", seed=1), strict=True)
+        torch.manual_seed(5)
+        d = gan.MultiScaleDiscriminator(2, 16, 5, 3, True)
+        d.apply(gan.weights_init)
+        return train.GANTrainStep(g.cuda().train(), d.cuda().train(), graph=True, split_graphs=split)
+
+    ct = O.synthetic_input(2, 128, 128, seed=999)
+    ct[:, :, 30:40, 50:60] = 1.0
+    ct, real = ct.cuda(), O.synthetic_input(2, 128, 128, seed=1000).cuda()
+    s1, s2 = make(False), make(True)
+    l1 = [tuple(float(v) for v in s1(ct, real)) for _ in range(4)]
+    l2 = [tuple(float(v) for v in s2(ct, real)) for _ in range(4)]
+    assert len(s1._graphs) == 1 and len(s2._graphs) == 5
+    for (a, b), (c, d) in zip(l1, l2):
+        assert abs(a - c) < 5e-3 * max(1.0, abs(a)) and abs(b - d) < 5e-3 * max(1.0, abs(b)), (l1, l2)
+    w1 = torch.cat([p.detach().flatten() for p in s1.netD.parameters()])
+    w2 = torch.cat([p.detach().flatten() for p in s2.netD.parameters()])
+    assert (w1 - w2).norm() <= 2e-3 * w1.norm(), ((w1 - w2).norm().item(), w1.norm().item())
+
+
 def test_fused_grad_accumulation_matches_autograd():
     """ops.fused_grad_accumulation: the backward kernels add their parameter gradients straight into the
     parameters' .grad (views of the flat bucket) instead of returning them to AccumulateGrad.

@@ -163,7 +163,7 @@ class GANTrainStep:
     def __init__(self, netG: torch.nn.Module, netD: torch.nn.Module, lrG: float = 1e-4, lrD: float = 2e-4,
                  betas: Tuple[float, float] = (0.5, 0.999), graph: bool = True, group=None, warmup: int = 3,
                  fused_losses: Optional[bool] = None, reuse_fake: bool = False, projector=None,
-                 lambda_phys: float = 0.02):
+                 lambda_phys: float = 0.02, split_graphs: Optional[bool] = None):
         from . import gan
         self.gan, self.netG, self.netD, self.group, self.use_graph = gan, netG, netD, group, graph
         on_cuda = next(netG.parameters()).is_cuda
@@ -179,6 +179,11 @@ class GANTrainStep:
         self._warmup = max(int(warmup), 1)
         self._graphs = None
         self._ct = self._real = self._lD = self._lG = None
+        # graph mode with several ranks (or split_graphs=True, which the single-GPU test uses): the step is captured
+        # in pieces around the two all-reduces, and the discriminator's all-reduce + Adam update run on a side stream
+        # UNDER the generator forward of the G step, which does not depend on the discriminator
+        self._split = (self.world > 1) if split_graphs is None else bool(split_graphs)
+        self._side = None
 
     # -- the recipe, in the three pieces the all-reduces separate ---------------------------
     def _d_fwd_bwd(self, ct, real):
@@ -196,14 +201,22 @@ class GANTrainStep:
         return loss.detach()
 
     def _d_step_g_fwd_bwd(self, ct, real):
-        gan, lam, mt = self.gan, self.LAMBDAS, self.METAL
         self.optD.step()
+        return self._g_rest(ct, real, self._g_fwd(ct))
+
+    def _g_fwd(self, ct):
+        """Generator forward of the G step (independent of the discriminator and of its update)."""
         self.bucketG.zero()
+        fake = self._fake if self.reuse_fake else self.netG(ct)
+        self._fake = None
+        return fake
+
+    def _g_rest(self, ct, real, fake):
+        """The rest of the G step: the (updated) discriminator on the fake, the losses, the generator backward."""
+        gan, lam, mt = self.gan, self.LAMBDAS, self.METAL
         for p in self.bucketD.params:
             p.requires_grad_(False)
         try:
-            fake = self._fake if self.reuse_fake else self.netG(ct)
-            self._fake = None
             fake_logits, fake_feats = self.netD(torch.cat([ct, fake], 1), return_features=True)
             with torch.no_grad():
                 _, real_feats = self.netD(torch.cat([ct, real], 1), return_features=True)
@@ -273,7 +286,7 @@ class GANTrainStep:
                             v.copy_(old[k]) if old is not None and k in old else v.zero_()
         torch.cuda.synchronize()
         g1 = torch.cuda.CUDAGraph()
-        if self.world == 1:
+        if not self._split:
             with torch.cuda.graph(g1):
                 self._lD = self._d_fwd_bwd(self._ct, self._real)
                 self._lG = self._d_step_g_fwd_bwd(self._ct, self._real)
@@ -282,13 +295,20 @@ class GANTrainStep:
         else:
             with torch.cuda.graph(g1):
                 self._lD = self._d_fwd_bwd(self._ct, self._real)
-            g2 = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g2, pool=g1.pool()):
-                self._lG = self._d_step_g_fwd_bwd(self._ct, self._real)
+            g2a = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g2a, pool=g1.pool()):
+                fake = self._g_fwd(self._ct)
+            gD = torch.cuda.CUDAGraph()             # replayed on the side stream CONCURRENTLY with g2a: its own memory
+            with torch.cuda.graph(gD):              # pool, so that none of its temporaries aliases the forward's
+                self.optD.step()
+            g2b = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g2b, pool=g1.pool()):
+                self._lG = self._g_rest(self._ct, self._real, fake)
             g3 = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g3, pool=g1.pool()):
                 self.optG.step()
-            self._graphs = (g1, g2, g3)
+            self._side = torch.cuda.Stream()
+            self._graphs = (g1, g2a, gD, g2b, g3)
 
     def __call__(self, ct: torch.Tensor, real: torch.Tensor):
         if not self.use_graph:
@@ -304,9 +324,16 @@ class GANTrainStep:
         if len(self._graphs) == 1:
             self._graphs[0].replay()
         else:
-            self._graphs[0].replay()
-            self.bucketD.all_reduce(self.group)
-            self._graphs[1].replay()
+            g1, g2a, gD, g2b, g3 = self._graphs
+            cur = torch.cuda.current_stream()
+            g1.replay()
+            self._side.wait_stream(cur)
+            with torch.cuda.stream(self._side):     # discriminator: all-reduce + Adam ...
+                self.bucketD.all_reduce(self.group)
+                gD.replay()
+            g2a.replay()                            # ... under the generator forward
+            cur.wait_stream(self._side)
+            g2b.replay()
             self.bucketG.all_reduce(self.group)
-            self._graphs[2].replay()
+            g3.replay()
         return self._lD.clone(), self._lG.clone()   # the static buffers are overwritten by the next replay
